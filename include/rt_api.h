@@ -1,0 +1,144 @@
+/*
+ * rt_api.h — C ABI of librt_b200.so, the B200-native replacement for the
+ * reference's compute-shader dispatch.
+ *
+ * What it replaces in the reference (Junacik99/opengl-ray-tracer):
+ *   - class ComputeShader (src/computeShader.hpp:13-114): load/compile/link of
+ *     gpu_shader.comp, use(), setBool/setInt/setFloat/setVec2 uniform setters;
+ *   - the SSBO/texture plumbing in src/main.cpp: output image creation
+ *     (:182-191), the five glGenBuffers/glBufferData/glBindBufferBase blocks
+ *     (:238-275, bindings 1..5 = Light, Camera, Shapes, Nodes, Indices),
+ *     the per-frame glBufferSubData updates (:328-348, :981-992) and the
+ *     dispatch glDispatchCompute(W,H,1) + glMemoryBarrier + uniforms (:352-361);
+ *   - gpu_shader.comp:433-624 itself (the per-pixel program).
+ *
+ * Conventions: every entry point returns RT_OK (0) or a negative rt_status and
+ * never prints or aborts (the reference only prints, computeShader.hpp:64-79).
+ * The caller keeps ownership of every host pointer; data is copied into pinned
+ * staging before the call returns.  A context is single-threaded, like a GL
+ * context.  All device work runs on one internal stream.  There is NO CPU
+ * fallback: without a CUDA device rt_create fails with RT_ERR_CUDA.
+ *
+ * Plain C: pointers and sizes only, no torch / glm / STL types.
+ */
+#ifndef RT_API_H
+#define RT_API_H
+
+#include "rt_flat.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rt_ctx rt_ctx;
+
+typedef enum rt_status {
+    RT_OK            =  0,
+    RT_ERR_ARG       = -1,  /* NULL / out-of-range argument                          */
+    RT_ERR_CUDA      = -2,  /* a CUDA runtime call failed (see rt_last_error)         */
+    RT_ERR_SCENE     = -3,  /* malformed BVH: bad child/shape index, cycle, depth>64  */
+    RT_ERR_STATE     = -4,  /* call order: render before upload, etc.                 */
+    RT_ERR_NOMEM     = -5
+} rt_status;
+
+/* The five uniforms of gpu_shader.comp:126-130 (set at src/main.cpp:357-361).
+ * Unlike the reference, which sets them after the dispatch (Appendix B of
+ * SURVEY.md), they are passed with the render call. */
+typedef struct rt_params {
+    float screenRes[2];      /* uniform vec2 screenRes  (W, H)                 */
+    int   maxBounces;        /* uniform int  maxBounces (GUI range 1..10)      */
+    int   useBVH;            /* uniform bool useBVH                            */
+    int   useFresnel;        /* uniform bool useFresnel                        */
+    int   useMollerTrumbore; /* uniform bool useMollerTrumbore                 */
+} rt_params;
+
+/* rt_create flags */
+enum {
+    RT_FLAG_DEFAULT   = 0u,
+    /* Allow distance culling of BVH nodes for closest-hit rays (a conservative
+     * margin keeps ids identical on every tested scene; the default visits
+     * exactly the reference's node set and is identical by construction). */
+    RT_FLAG_CULL      = 1u << 0,
+    /* Record per-pixel primary-hit shape ids (an AOV the reference lacks;
+     * needed by the parity criterion).  Off = the id buffer is not written. */
+    RT_FLAG_HIT_IDS   = 1u << 1
+};
+
+/* Tile geometry used when a frame is sharded over several GPUs: tile k
+ * (row-major over the tile grid) belongs to rank k % world. */
+#define RT_TILE_W 32
+#define RT_TILE_H 8
+
+/* ---- lifetime ------------------------------------------------------------
+ * Replaces ComputeShader::ComputeShader + the output-texture creation
+ * (computeShader.hpp:29-83, main.cpp:182-191).  device = CUDA ordinal. */
+int  rt_create(rt_ctx** out, int width, int height, int device, unsigned flags);
+void rt_destroy(rt_ctx* ctx);
+const char* rt_last_error(const rt_ctx* ctx);
+
+/* ---- scene upload ----------------------------------------------------------
+ * Replaces the five glBufferData blocks (main.cpp:238-275).  Any pointer may
+ * be NULL = keep what is resident.  shapes/nodes/indices are the reference's
+ * FlatShape[]/FlatNode[]/int[] bytes; the root is nodes[nNodes-1]
+ * (gpu_shader.comp:386).  The buffers are staged through pinned memory with
+ * cudaMemcpyAsync and repacked on the device into float4 SoA. */
+int rt_upload_scene(rt_ctx* ctx,
+                    const void* light32, const void* camera80,
+                    const void* shapes, int nShapes,
+                    const void* nodes, int nNodes,
+                    const int32_t* indices, int nIndices);
+
+/* Per-frame partial updates (main.cpp:328-334 camera/light, :981-992 one
+ * 192-byte sub-update per animated shape, :343-344 all nodes). */
+int rt_update_camera(rt_ctx* ctx, const void* camera80);
+int rt_update_light(rt_ctx* ctx, const void* light32);
+int rt_update_shapes(rt_ctx* ctx, int first, int count, const void* shapes);
+int rt_update_nodes(rt_ctx* ctx, const void* nodes, int nNodes);
+
+/* ---- multi-GPU sharding ----------------------------------------------------
+ * This context renders only the RT_TILE_W x RT_TILE_H tiles k with
+ * k % world == rank, into a compact tile-major buffer (tile j of this rank at
+ * offset j*RT_TILE_W*RT_TILE_H pixels).  rank=0, world=1 restores full frames.
+ * rt_shard_pixels returns the number of pixels (incl. padding of edge tiles)
+ * in this rank's compact buffer. */
+int     rt_set_shard(rt_ctx* ctx, int rank, int world);
+int64_t rt_shard_pixels(const rt_ctx* ctx);
+
+/* ---- dispatch --------------------------------------------------------------
+ * Replaces use() + glDispatchCompute(W,H,1) + glMemoryBarrier + the uniform
+ * setters (main.cpp:352-361).  Renders into the context's device image and,
+ * if host_rgba != NULL, copies the row-major W*H float4 image
+ * (imgOutput, rgba32f) to the host; host_hit_ids (W*H int32, -1 = miss) needs
+ * RT_FLAG_HIT_IDS.  Synchronous.  With a shard set (world>1) the host copies
+ * are the compact tile-major shard instead. */
+int rt_render(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* host_hit_ids);
+
+/* Same, but writes into caller-provided DEVICE buffers (e.g. torch tensors)
+ * and returns without synchronising: work is ordered on rt_stream(ctx). */
+int rt_render_device(rt_ctx* ctx, const rt_params* params, float* dev_rgba, int32_t* dev_hit_ids);
+
+/* K3: scatter `world` compact tile-major shards, laid out rank after rank in
+ * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one
+ * row-major W*H image. */
+int rt_untile(rt_ctx* ctx, const float* dev_shards, int world, float* dev_rgba_out);
+
+/* K4: the display quad's arithmetic (shader.frag:8-12 + default-framebuffer
+ * conversion): alpha forced to 1, clamp to [0,1], quantise to RGBA8. */
+int rt_present(rt_ctx* ctx, const float* dev_rgba, uint8_t* dev_rgba8_out, int64_t pixels);
+
+/* ---- plumbing --------------------------------------------------------------*/
+void* rt_stream(rt_ctx* ctx);                 /* cudaStream_t of the context     */
+int   rt_synchronize(rt_ctx* ctx);
+float* rt_device_image(rt_ctx* ctx);          /* internal float4 image           */
+/* CUDA-event timings of the last calls, milliseconds (-1 = not measured yet):
+ * [0] H2D staging copy  [1] repack kernel(s)  [2] render kernel  [3] D2H */
+int   rt_last_timings(rt_ctx* ctx, float out_ms[4]);
+/* Number of kernels launched by this context since creation. */
+int64_t rt_launch_count(const rt_ctx* ctx);
+/* Build description: "sm_100a fmad=off ..." */
+const char* rt_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_API_H */

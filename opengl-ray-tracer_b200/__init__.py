@@ -1,0 +1,9 @@
+"""B200-native drop-in for the opengl-ray-tracer compute-shader dispatch.
+
+The product is csrc/librt_b200.so (C ABI in include/rt_api.h).  This package only
+holds the build recipe, the ctypes harness bindings and the headless host library.
+The directory name contains '-', so load it with `rtload.load()` at the repo root.
+"""
+from . import build  # noqa: F401
+from .binding import (CAMERA_DTYPE, LIGHT_DTYPE, NODE_DTYPE, SHAPE_DTYPE, RT_FLAG_CULL, RT_FLAG_HIT_IDS,  # noqa: F401
+                      API_SYMBOLS, Params, RayTracer, RtError, Scene, hostlib, lib, lib_path, make_params)

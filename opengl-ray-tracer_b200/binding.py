@@ -1,0 +1,302 @@
+"""ctypes bindings of the C ABI (include/rt_api.h) and of the headless host library.
+
+This is harness plumbing for tests/ and bench.py; the product is librt_b200.so.
+There is no fallback: if the CUDA library is missing or cannot be loaded, import
+of `lib()` raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+# ---- std430 wire format (include/rt_flat.h; reference src/flatStructures.hpp:7-106) ----
+LIGHT_DTYPE = np.dtype({"names": ["position", "color"], "formats": [("f4", 3), ("f4", 3)],
+                        "offsets": [0, 16], "itemsize": 32})
+CAMERA_DTYPE = np.dtype({"names": ["Position", "aspectRatio", "Front", "Up", "Right", "fov"],
+                         "formats": [("f4", 3), "f4", ("f4", 3), ("f4", 3), ("f4", 3), "f4"],
+                         "offsets": [0, 12, 16, 32, 48, 64], "itemsize": 80})
+SHAPE_DTYPE = np.dtype({
+    "names": ["type", "color", "fresnelStrength", "ambientStrength", "diffuseStrength", "specularStrength",
+              "shininess", "sphereCenter", "sphereRadius", "planeNormal", "planeD", "wallStart", "wallWidth",
+              "wallHeight", "triP1", "triP2", "triP3"],
+    "formats": ["i4", ("f4", 3), "f4", "f4", "f4", "f4", "i4", ("f4", 3), "f4", ("f4", 3), "f4", ("f4", 3), "f4",
+                "f4", ("f4", 3), ("f4", 3), ("f4", 3)],
+    "offsets": [0, 32, 44, 48, 52, 56, 60, 64, 76, 80, 92, 96, 108, 112, 144, 160, 176],
+    "itemsize": 192})
+NODE_DTYPE = np.dtype({"names": ["boundsMin", "boundsMax", "leftChild", "rightChild", "startShapeIdx", "numShapes"],
+                       "formats": [("f4", 3), ("f4", 3), "i4", "i4", "i4", "i4"],
+                       "offsets": [0, 16, 32, 36, 40, 44], "itemsize": 48})
+
+RT_FLAG_CULL = 1
+RT_FLAG_HIT_IDS = 2
+TILE_W, TILE_H = 32, 8
+
+
+class Params(C.Structure):
+    """rt_params == the five uniforms of gpu_shader.comp:126-130."""
+    _fields_ = [("screenRes", C.c_float * 2), ("maxBounces", C.c_int), ("useBVH", C.c_int),
+                ("useFresnel", C.c_int), ("useMollerTrumbore", C.c_int)]
+
+
+def make_params(width, height, maxBounces=3, useBVH=True, useFresnel=False, useMollerTrumbore=False):
+    """Defaults as in src/main.cpp:118,135-137."""
+    p = Params()
+    p.screenRes[0], p.screenRes[1] = float(width), float(height)
+    p.maxBounces, p.useBVH, p.useFresnel, p.useMollerTrumbore = int(maxBounces), int(useBVH), int(useFresnel), int(useMollerTrumbore)
+    return p
+
+
+_lib = None
+_hostlib = None
+
+# every symbol include/rt_api.h declares
+API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
+               "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
+               "rt_render_device", "rt_untile", "rt_present", "rt_stream", "rt_synchronize", "rt_device_image",
+               "rt_last_timings", "rt_launch_count", "rt_build_info"]
+
+
+def lib_path():
+    return os.path.join(_build.CSRC, "librt_b200.so")
+
+
+def lib():
+    """Load librt_b200.so (building it if nvcc is here).  Raises if unavailable."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.build_cuda()
+    L = C.CDLL(path)
+    vp, ip, fp = C.c_void_p, C.c_int, C.POINTER(C.c_float)
+    L.rt_create.argtypes = [C.POINTER(vp), ip, ip, ip, C.c_uint]; L.rt_create.restype = ip
+    L.rt_destroy.argtypes = [vp]; L.rt_destroy.restype = None
+    L.rt_last_error.argtypes = [vp]; L.rt_last_error.restype = C.c_char_p
+    L.rt_upload_scene.argtypes = [vp, vp, vp, vp, ip, vp, ip, vp, ip]; L.rt_upload_scene.restype = ip
+    L.rt_update_camera.argtypes = [vp, vp]; L.rt_update_camera.restype = ip
+    L.rt_update_light.argtypes = [vp, vp]; L.rt_update_light.restype = ip
+    L.rt_update_shapes.argtypes = [vp, ip, ip, vp]; L.rt_update_shapes.restype = ip
+    L.rt_update_nodes.argtypes = [vp, vp, ip]; L.rt_update_nodes.restype = ip
+    L.rt_set_shard.argtypes = [vp, ip, ip]; L.rt_set_shard.restype = ip
+    L.rt_shard_pixels.argtypes = [vp]; L.rt_shard_pixels.restype = C.c_int64
+    L.rt_render.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render.restype = ip
+    L.rt_render_device.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_device.restype = ip
+    L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
+    L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
+    L.rt_stream.argtypes = [vp]; L.rt_stream.restype = vp
+    L.rt_synchronize.argtypes = [vp]; L.rt_synchronize.restype = ip
+    L.rt_device_image.argtypes = [vp]; L.rt_device_image.restype = vp
+    L.rt_last_timings.argtypes = [vp, fp]; L.rt_last_timings.restype = ip
+    L.rt_launch_count.argtypes = [vp]; L.rt_launch_count.restype = C.c_int64
+    L.rt_build_info.argtypes = []; L.rt_build_info.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def hostlib():
+    global _hostlib
+    if _hostlib is not None:
+        return _hostlib
+    H = C.CDLL(_build.build_host())
+    vp, ip = C.c_void_p, C.c_int
+    H.rh_scene_create.argtypes = [C.c_char_p, ip, ip, ip, ip]; H.rh_scene_create.restype = vp
+    H.rh_scene_from_shapes.argtypes = [vp, ip, vp, vp, ip]; H.rh_scene_from_shapes.restype = vp
+    H.rh_scene_destroy.argtypes = [vp]; H.rh_scene_destroy.restype = None
+    for name in ("rh_light", "rh_camera"):
+        getattr(H, name).argtypes = [vp]; getattr(H, name).restype = vp
+    for name in ("rh_shapes", "rh_nodes", "rh_indices", "rh_animated"):
+        getattr(H, name).argtypes = [vp, C.POINTER(ip)]; getattr(H, name).restype = vp
+    H.rh_bvh_stats.argtypes = [vp, C.POINTER(ip * 4)]; H.rh_bvh_stats.restype = None
+    H.rh_scene_animate.argtypes = [vp, C.c_float, C.c_float, ip]; H.rh_scene_animate.restype = ip
+    H.rh_set_camera.argtypes = [vp, C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 3), C.c_float, C.c_float]
+    H.rh_set_camera.restype = None
+    _hostlib = H
+    return H
+
+
+class RtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("rt error %d: %s" % (code, msg))
+        self.code = code
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data_as(C.c_void_p)
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    return C.cast(a, C.c_void_p)
+
+
+class Scene:
+    """A host-side scene: the reference's FlatScene + flatNodes + bvhIndices (numpy views)."""
+
+    def __init__(self, name, width=800, height=600, n_override=0, bvh_depth=0, _handle=None):
+        self._H = hostlib()
+        self._h = _handle if _handle is not None else self._H.rh_scene_create(name.encode(), width, height, n_override, bvh_depth)
+        if not self._h:
+            raise ValueError("unknown scene %r" % name)
+        self.name, self.width, self.height = name, width, height
+
+    @classmethod
+    def from_shapes(cls, shapes, light, camera, bvh_depth=15, width=800, height=600):
+        H = hostlib()
+        shapes = np.ascontiguousarray(shapes)
+        h = H.rh_scene_from_shapes(_ptr(shapes), len(shapes), _ptr(light), _ptr(camera), bvh_depth)
+        return cls("custom", width, height, _handle=h)
+
+    def _arr(self, fn, dtype):
+        n = C.c_int(0)
+        p = fn(self._h, C.byref(n))
+        if n.value == 0:
+            return np.zeros(0, dtype=dtype)
+        buf = (C.c_char * (n.value * dtype.itemsize)).from_address(p)
+        return np.frombuffer(buf, dtype=dtype, count=n.value).copy()
+
+    @property
+    def light(self):
+        return np.frombuffer((C.c_char * 32).from_address(self._H.rh_light(self._h)), dtype=LIGHT_DTYPE, count=1).copy()
+
+    @property
+    def camera(self):
+        return np.frombuffer((C.c_char * 80).from_address(self._H.rh_camera(self._h)), dtype=CAMERA_DTYPE, count=1).copy()
+
+    @property
+    def shapes(self):
+        return self._arr(self._H.rh_shapes, SHAPE_DTYPE)
+
+    @property
+    def nodes(self):
+        return self._arr(self._H.rh_nodes, NODE_DTYPE)
+
+    @property
+    def indices(self):
+        return self._arr(self._H.rh_indices, np.dtype("i4"))
+
+    @property
+    def animated(self):
+        return self._arr(self._H.rh_animated, np.dtype("i4"))
+
+    def bvh_stats(self):
+        out = (C.c_int * 4)()
+        self._H.rh_bvh_stats(self._h, C.byref(out))
+        return dict(nodes=out[0], leaves=out[1], max_leaf=out[2], depth=out[3])
+
+    def animate(self, t, dt, mode=0):
+        return self._H.rh_scene_animate(self._h, float(t), float(dt), int(mode))
+
+    def set_camera(self, pos, target, fov=60.0, aspect=None):
+        a = aspect if aspect is not None else self.width / self.height
+        self._H.rh_set_camera(self._h, C.byref((C.c_float * 3)(*pos)), C.byref((C.c_float * 3)(*target)), fov, a)
+
+    def close(self):
+        if self._h:
+            self._H.rh_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class RayTracer:
+    """Thin object wrapper over rt_create/rt_upload_scene/rt_render/rt_destroy."""
+
+    def __init__(self, width, height, device=0, flags=RT_FLAG_HIT_IDS):
+        self._L = lib()
+        self._c = C.c_void_p()
+        rc = self._L.rt_create(C.byref(self._c), width, height, device, flags)
+        if rc != 0:
+            raise RtError(rc, "rt_create failed (no CUDA device? there is no CPU fallback)")
+        self.width, self.height, self.flags = width, height, flags
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise RtError(rc, (self._L.rt_last_error(self._c) or b"").decode())
+
+    def upload_scene(self, light=None, camera=None, shapes=None, nodes=None, indices=None):
+        keep = [np.ascontiguousarray(a) if a is not None else None for a in (light, camera, shapes, nodes, indices)]
+        li, ca, sh, no, ix = keep
+        self._chk(self._L.rt_upload_scene(self._c, _ptr(li), _ptr(ca), _ptr(sh), 0 if sh is None else len(sh),
+                                          _ptr(no), 0 if no is None else len(no), _ptr(ix), 0 if ix is None else len(ix)))
+
+    def upload(self, scene):
+        self.upload_scene(scene.light, scene.camera, scene.shapes, scene.nodes, scene.indices)
+
+    def update_camera(self, camera):
+        self._chk(self._L.rt_update_camera(self._c, _ptr(np.ascontiguousarray(camera))))
+
+    def update_light(self, light):
+        self._chk(self._L.rt_update_light(self._c, _ptr(np.ascontiguousarray(light))))
+
+    def update_shapes(self, first, shapes):
+        shapes = np.ascontiguousarray(shapes)
+        self._chk(self._L.rt_update_shapes(self._c, int(first), len(shapes), _ptr(shapes)))
+
+    def update_nodes(self, nodes):
+        nodes = np.ascontiguousarray(nodes)
+        self._chk(self._L.rt_update_nodes(self._c, _ptr(nodes), len(nodes)))
+
+    def set_shard(self, rank, world):
+        self._chk(self._L.rt_set_shard(self._c, rank, world))
+
+    def shard_pixels(self):
+        return int(self._L.rt_shard_pixels(self._c))
+
+    def render(self, params, want_ids=True, out=None, out_ids=None):
+        """Synchronous render into host numpy arrays (the rt_render entry point)."""
+        px = self.shard_pixels()
+        full = px == self.width * self.height
+        rgba = out if out is not None else np.empty((px, 4), dtype=np.float32)
+        ids = None
+        if want_ids and (self.flags & RT_FLAG_HIT_IDS):
+            ids = out_ids if out_ids is not None else np.empty(px, dtype=np.int32)
+        self._chk(self._L.rt_render(self._c, C.byref(params), _ptr(rgba), _ptr(ids)))
+        if full and out is None:
+            rgba = rgba.reshape(self.height, self.width, 4)
+            ids = ids.reshape(self.height, self.width) if ids is not None else None
+        return rgba, ids
+
+    def render_device(self, params, dev_rgba_ptr=None, dev_ids_ptr=None):
+        """Asynchronous render into device memory (pointers as ints, e.g. tensor.data_ptr())."""
+        self._chk(self._L.rt_render_device(self._c, C.byref(params), _ptr(dev_rgba_ptr), _ptr(dev_ids_ptr)))
+
+    def untile(self, dev_shards_ptr, world, dev_out_ptr):
+        self._chk(self._L.rt_untile(self._c, _ptr(dev_shards_ptr), world, _ptr(dev_out_ptr)))
+
+    def present(self, dev_rgba_ptr, dev_rgba8_ptr, pixels):
+        self._chk(self._L.rt_present(self._c, _ptr(dev_rgba_ptr), _ptr(dev_rgba8_ptr), pixels))
+
+    def stream(self):
+        return self._L.rt_stream(self._c)
+
+    def synchronize(self):
+        self._chk(self._L.rt_synchronize(self._c))
+
+    def device_image(self):
+        return self._L.rt_device_image(self._c)
+
+    def timings(self):
+        out = (C.c_float * 4)()
+        self._chk(self._L.rt_last_timings(self._c, out))
+        return dict(h2d_ms=out[0], repack_ms=out[1], render_ms=out[2], d2h_ms=out[3])
+
+    def launch_count(self):
+        return int(self._L.rt_launch_count(self._c))
+
+    def close(self):
+        if self._c:
+            self._L.rt_destroy(self._c)
+            self._c = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

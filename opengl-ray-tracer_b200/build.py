@@ -1,0 +1,64 @@
+"""In-tree builds: librt_b200.so (CUDA, sm_100a), librt_host.so (headless host side).
+
+The .so files are git-ignored but travel to the GPU box with the gpurun snapshot.
+"""
+import os
+import shutil
+import subprocess
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+CSRC = os.path.join(PKG, "csrc")
+HOST = os.path.join(PKG, "host")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-Xcompiler", "-fPIC", "-shared"]
+CXX_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-pthread"]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.getmtime(s) <= t for s in sources)
+
+
+def _run(cmd):
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("build failed: %s\n%s\n%s" % (" ".join(cmd), r.stdout, r.stderr))
+
+
+def cuda_sources():
+    return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh"))] + \
+           [os.path.join(ROOT, "include", "rt_api.h"), os.path.join(ROOT, "include", "rt_flat.h")]
+
+
+def build_cuda(force=False):
+    out = os.path.join(CSRC, "librt_b200.so")
+    if not force and _newer(out, cuda_sources()):
+        return out
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        if os.path.exists(out):
+            return out
+        raise RuntimeError("nvcc not found and no prebuilt librt_b200.so")
+    _run([nvcc] + NVCC_FLAGS + ["-o", out, os.path.join(CSRC, "rt_api.cu")])
+    return out
+
+
+def build_host(force=False):
+    out = os.path.join(HOST, "librt_host.so")
+    srcs = [os.path.join(HOST, "rt_host.cpp"), os.path.join(HOST, "rt_host.h")]
+    if not force and _newer(out, srcs):
+        return out
+    _run(["g++"] + CXX_FLAGS + ["-o", out, srcs[0]])
+    return out
+
+
+def build_all(force=False):
+    return build_cuda(force), build_host(force)
+
+
+if __name__ == "__main__":
+    print(build_all(force=True))

@@ -1,0 +1,439 @@
+// rt_api.cu — librt_b200.so: the C ABI of include/rt_api.h on top of the
+// kernels in rt_kernels.cuh.  Context = what the reference keeps in GL objects
+// (program, 5 SSBOs, output texture; src/main.cpp:182-275).  No CPU fallback.
+#include "rt_kernels.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace rt;
+
+namespace {
+
+template <class T>
+struct DevBuf {                       // capacity-based device array
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 4 + 16;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+template <class T>
+struct PinBuf {                       // capacity-based pinned host array (keeps contents on growth)
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n, size_t keep) {
+        if (n <= cap) return cudaSuccess;
+        size_t want = n + n / 4 + 16;
+        T* q = nullptr;
+        cudaError_t e = cudaMallocHost(&q, want * sizeof(T));
+        if (e != cudaSuccess) return e;
+        if (p && keep) std::memcpy(q, p, keep * sizeof(T));
+        if (p) cudaFreeHost(p);
+        p = q; cap = want;
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct rt_ctx {
+    int device = 0, W = 0, H = 0;
+    unsigned flags = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};          // h2d0,h2d1, repack0,repack1, render0,render1, d2h0,d2h1
+    cudaEvent_t copyDone = nullptr;  // last H2D out of the pinned shadows has finished
+    bool copyPending = false;
+    bool timed[4] = {false, false, false, false};
+    std::string err;
+    int64_t launches = 0;
+    int smCount = 148;
+
+    // raw scene, pinned shadow + device copy
+    PinBuf<rt_flat_shape> hShapes; DevBuf<rt_flat_shape> dShapes; int nShapes = 0;
+    PinBuf<rt_flat_node>  hNodes;  DevBuf<rt_flat_node>  dNodes;  int nNodes = 0;
+    std::vector<int32_t> indices;                                 // host only (feeds the visit-order map)
+    rt_flat_light light{}; rt_flat_camera cam{};
+    bool haveScene = false, haveCam = false, haveLight = false;
+
+    // visit-order maps (host-built, pinned) and the repacked device scene
+    PinBuf<int>  hOrder;   DevBuf<int>  dOrder;
+    PinBuf<int2> hLinkCnt; DevBuf<int2> dLinkCnt;
+    PinBuf<int>  hPshape;  DevBuf<int>  dPshape;
+    DevBuf<float4> dNodesT, q0, q1, q2, q3;
+    DevBuf<int> ptype;
+    int nDfs = 0, nPrims = 0;
+
+    // pending work, flushed at render time so per-shape updates coalesce (main.cpp:981-992)
+    int shapeLo = 0, shapeHi = 0;     // dirty raw-shape range [lo,hi)
+    bool nodesDirty = false, topoDirty = false;
+
+    // output
+    DevBuf<float4> image; DevBuf<int> ids;
+    int shardRank = 0, shardWorld = 1;
+};
+
+namespace {
+
+int fail(rt_ctx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
+    if (c) {
+        c->err = what;
+        if (e != cudaSuccess) { c->err += ": "; c->err += cudaGetErrorString(e); }
+    }
+    return code;
+}
+#define CU(c, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail((c), RT_ERR_CUDA, #call, e_); } while (0)
+
+inline int tiles_x(const rt_ctx* c) { return (c->W + RT_TILE_W - 1) / RT_TILE_W; }
+inline int tiles_y(const rt_ctx* c) { return (c->H + RT_TILE_H - 1) / RT_TILE_H; }
+inline int tiles_mine(const rt_ctx* c) {
+    int n = tiles_x(c) * tiles_y(c);
+    return n > c->shardRank ? (n - c->shardRank + c->shardWorld - 1) / c->shardWorld : 0;
+}
+// Shards are padded to rank 0's tile count so that every rank gathers the same size.
+inline int64_t out_pixels(const rt_ctx* c) {
+    if (c->shardWorld == 1) return (int64_t)c->W * c->H;
+    const int nT = tiles_x(c) * tiles_y(c);
+    return (int64_t)((nT + c->shardWorld - 1) / c->shardWorld) * RT_TILE_W * RT_TILE_H;
+}
+// The pinned shadows are the source of async copies: wait for the last one before
+// the host overwrites them (lets the next frame's update overlap the previous render).
+inline void wait_copies(rt_ctx* c) {
+    if (c->copyPending) { cudaEventSynchronize(c->copyDone); c->copyPending = false; }
+}
+
+// Threaded visit order of the reference traversal: root = last node, right child
+// first (gpu_shader.comp:386, :424-425).  Validates what the shader would trust.
+int build_visit_order(rt_ctx* c) {
+    const int n = c->nNodes;
+    const rt_flat_node* nd = c->hNodes.p;
+    std::vector<int> order; order.reserve((size_t)n);
+    if (n > 0) {
+        struct Item { int node, depth; };
+        std::vector<Item> st; st.push_back({n - 1, 1});
+        const size_t limit = (size_t)n * 4 + 64;
+        while (!st.empty()) {
+            Item it = st.back(); st.pop_back();
+            if (it.node < 0 || it.node >= n) return fail(c, RT_ERR_SCENE, "BVH child index out of range");
+            if (order.size() >= limit) return fail(c, RT_ERR_SCENE, "BVH is cyclic or shares subtrees excessively");
+            order.push_back(it.node);
+            const rt_flat_node& x = nd[it.node];
+            if (x.leftChild != -1) {
+                if (it.depth + 1 > 64) return fail(c, RT_ERR_SCENE, "BVH deeper than the reference's 64-entry stack");
+                st.push_back({x.leftChild, it.depth + 1});
+                st.push_back({x.rightChild, it.depth + 1});
+            }
+        }
+    }
+    const int m = (int)order.size();
+    std::vector<int> size((size_t)m, 1);
+    CU(c, c->hOrder.reserve((size_t)m, 0));
+    CU(c, c->hLinkCnt.reserve((size_t)m, 0));
+    for (int k = m - 1; k >= 0; --k) {
+        if (nd[order[(size_t)k]].leftChild != -1) {
+            const int r = k + 1, l = r + size[(size_t)r];
+            size[(size_t)k] = 1 + size[(size_t)r] + size[(size_t)l];
+        }
+    }
+    size_t prims = 0;
+    for (int k = 0; k < m; ++k) {
+        const rt_flat_node& x = nd[order[(size_t)k]];
+        if (x.leftChild == -1) {
+            if (x.numShapes < 0 || x.startShapeIdx < 0 || (size_t)x.startShapeIdx + (size_t)x.numShapes > c->indices.size())
+                return fail(c, RT_ERR_SCENE, "leaf index range outside bvhIndices");
+            prims += (size_t)x.numShapes;
+        }
+    }
+    if (prims > 0x7fffffffu) return fail(c, RT_ERR_SCENE, "too many leaf primitives");
+    CU(c, c->hPshape.reserve(prims, 0));
+    size_t slot = 0;
+    for (int k = 0; k < m; ++k) {
+        const rt_flat_node& x = nd[order[(size_t)k]];
+        c->hOrder.p[k] = order[(size_t)k];
+        if (x.leftChild == -1) {
+            c->hLinkCnt.p[k] = make_int2((int)slot, x.numShapes);
+            for (int i = 0; i < x.numShapes; ++i) {
+                const int s = c->indices[(size_t)x.startShapeIdx + (size_t)i];
+                if (s < 0 || s >= c->nShapes) return fail(c, RT_ERR_SCENE, "bvhIndices entry outside the shape buffer");
+                c->hPshape.p[slot++] = s;
+            }
+        } else {
+            c->hLinkCnt.p[k] = make_int2(k + size[(size_t)k], -1);
+        }
+    }
+    c->nDfs = m; c->nPrims = (int)prims;
+    return RT_OK;
+}
+
+// Bring the device scene up to date: coalesced H2D of whatever changed, then K2.
+int flush_scene(rt_ctx* c) {
+    const bool anyCopy = c->shapeHi > c->shapeLo || c->nodesDirty || c->topoDirty;
+    if (!anyCopy) return RT_OK;
+    const bool shapesChanged = c->shapeHi > c->shapeLo;
+    cudaEventRecord(c->ev[0], c->stream);
+    if (shapesChanged) {
+        CU(c, c->dShapes.reserve((size_t)c->nShapes));
+        CU(c, cudaMemcpyAsync(c->dShapes.p + c->shapeLo, c->hShapes.p + c->shapeLo,
+                              (size_t)(c->shapeHi - c->shapeLo) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+    }
+    if (c->nodesDirty && c->nNodes > 0) {
+        CU(c, c->dNodes.reserve((size_t)c->nNodes));
+        CU(c, cudaMemcpyAsync(c->dNodes.p, c->hNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyHostToDevice, c->stream));
+    }
+    if (c->topoDirty) {
+        wait_copies(c);
+        int rc = build_visit_order(c);
+        if (rc != RT_OK) return rc;
+        CU(c, c->dOrder.reserve((size_t)c->nDfs)); CU(c, c->dLinkCnt.reserve((size_t)c->nDfs));
+        CU(c, c->dPshape.reserve((size_t)c->nPrims));
+        CU(c, c->dNodesT.reserve((size_t)c->nDfs * 2));
+        CU(c, c->q0.reserve((size_t)c->nPrims)); CU(c, c->q1.reserve((size_t)c->nPrims));
+        CU(c, c->q2.reserve((size_t)c->nPrims)); CU(c, c->q3.reserve((size_t)c->nPrims));
+        CU(c, c->ptype.reserve((size_t)c->nPrims));
+        if (c->nDfs > 0) {
+            CU(c, cudaMemcpyAsync(c->dOrder.p, c->hOrder.p, (size_t)c->nDfs * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+            CU(c, cudaMemcpyAsync(c->dLinkCnt.p, c->hLinkCnt.p, (size_t)c->nDfs * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
+        }
+        if (c->nPrims > 0)
+            CU(c, cudaMemcpyAsync(c->dPshape.p, c->hPshape.p, (size_t)c->nPrims * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    }
+    cudaEventRecord(c->ev[1], c->stream); c->timed[0] = true;
+    cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
+    cudaEventRecord(c->ev[2], c->stream);
+    if ((c->nodesDirty || c->topoDirty) && c->nDfs > 0) {
+        repack_nodes_kernel<<<(c->nDfs + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dOrder.p, c->dLinkCnt.p, c->dNodesT.p, c->nDfs);
+        c->launches++;
+    }
+    if ((shapesChanged || c->topoDirty) && c->nPrims > 0) {
+        repack_prims_kernel<<<(c->nPrims + 255) / 256, 256, 0, c->stream>>>(c->dShapes.p, c->dPshape.p, c->q0.p, c->q1.p, c->q2.p, c->q3.p, c->ptype.p, c->nPrims);
+        c->launches++;
+    }
+    cudaEventRecord(c->ev[3], c->stream); c->timed[1] = true;
+    CU(c, cudaGetLastError());
+    c->shapeLo = c->shapeHi = 0; c->nodesDirty = c->topoDirty = false;
+    return RT_OK;
+}
+
+bool same_topology(const rt_flat_node* a, const rt_flat_node* b, int n) {
+    for (int i = 0; i < n; ++i)
+        if (a[i].leftChild != b[i].leftChild || a[i].rightChild != b[i].rightChild ||
+            (a[i].leftChild == -1 && (a[i].startShapeIdx != b[i].startShapeIdx || a[i].numShapes != b[i].numShapes)))
+            return false;
+    return true;
+}
+
+int set_nodes(rt_ctx* c, const void* nodes, int nNodes) {
+    const rt_flat_node* in = static_cast<const rt_flat_node*>(nodes);
+    const bool sameTopo = c->haveScene && nNodes == c->nNodes && !c->topoDirty && same_topology(in, c->hNodes.p, nNodes);
+    wait_copies(c);
+    CU(c, c->hNodes.reserve((size_t)nNodes, 0));
+    if (nNodes > 0) std::memcpy(c->hNodes.p, in, (size_t)nNodes * sizeof(rt_flat_node));
+    c->nNodes = nNodes;
+    c->nodesDirty = true;
+    if (!sameTopo) c->topoDirty = true;
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_create(rt_ctx** out, int width, int height, int device, unsigned flags) {
+    if (!out || width <= 0 || height <= 0 || device < 0) return RT_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device >= count) return RT_ERR_CUDA;   // no CPU fallback
+    rt_ctx* c = new (std::nothrow) rt_ctx();
+    if (!c) return RT_ERR_NOMEM;
+    c->device = device; c->W = width; c->H = height; c->flags = flags;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return RT_ERR_CUDA; }
+    for (auto& e : c->ev) if (cudaEventCreate(&e) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+    if (cudaEventCreateWithFlags(&c->copyDone, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+    cudaDeviceGetAttribute(&c->smCount, cudaDevAttrMultiProcessorCount, device);
+    *out = c;
+    return RT_OK;
+}
+
+void rt_destroy(rt_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    c->hShapes.release(); c->dShapes.release(); c->hNodes.release(); c->dNodes.release();
+    c->hOrder.release(); c->dOrder.release(); c->hLinkCnt.release(); c->dLinkCnt.release();
+    c->hPshape.release(); c->dPshape.release(); c->dNodesT.release();
+    c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
+    c->image.release(); c->ids.release();
+    for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->copyDone) cudaEventDestroy(c->copyDone);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* rt_last_error(const rt_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const void* shapes, int nShapes,
+                    const void* nodes, int nNodes, const int32_t* indices, int nIndices) {
+    if (!c) return RT_ERR_ARG;
+    if ((shapes && nShapes < 0) || (nodes && nNodes < 0) || (indices && nIndices < 0)) return fail(c, RT_ERR_ARG, "negative count");
+    CU(c, cudaSetDevice(c->device));
+    if (light32)  { std::memcpy(&c->light, light32, sizeof c->light); c->haveLight = true; }
+    if (camera80) { std::memcpy(&c->cam, camera80, sizeof c->cam); c->haveCam = true; }
+    if (shapes) {
+        wait_copies(c);
+        CU(c, c->hShapes.reserve((size_t)nShapes, 0));
+        if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
+        c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes; c->topoDirty = true;
+    }
+    if (indices) { c->indices.assign(indices, indices + nIndices); c->topoDirty = true; }
+    if (nodes) { int rc = set_nodes(c, nodes, nNodes); if (rc != RT_OK) return rc; if (indices || shapes) c->topoDirty = true; }
+    if (shapes || nodes || indices) c->haveScene = true;
+    return flush_scene(c);
+}
+
+int rt_update_camera(rt_ctx* c, const void* camera80) {
+    if (!c || !camera80) return RT_ERR_ARG;
+    std::memcpy(&c->cam, camera80, sizeof c->cam); c->haveCam = true;
+    return RT_OK;
+}
+int rt_update_light(rt_ctx* c, const void* light32) {
+    if (!c || !light32) return RT_ERR_ARG;
+    std::memcpy(&c->light, light32, sizeof c->light); c->haveLight = true;
+    return RT_OK;
+}
+int rt_update_shapes(rt_ctx* c, int first, int count, const void* shapes) {
+    if (!c || !shapes) return RT_ERR_ARG;
+    if (first < 0 || count < 0 || first + count > c->nShapes) return fail(c, RT_ERR_ARG, "shape range outside the uploaded buffer");
+    if (count == 0) return RT_OK;
+    wait_copies(c);
+    std::memcpy(c->hShapes.p + first, shapes, (size_t)count * sizeof(rt_flat_shape));
+    if (c->shapeHi <= c->shapeLo) { c->shapeLo = first; c->shapeHi = first + count; }
+    else { if (first < c->shapeLo) c->shapeLo = first; if (first + count > c->shapeHi) c->shapeHi = first + count; }
+    return RT_OK;
+}
+int rt_update_nodes(rt_ctx* c, const void* nodes, int nNodes) {
+    if (!c || !nodes || nNodes < 0) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    return set_nodes(c, nodes, nNodes);
+}
+
+int rt_set_shard(rt_ctx* c, int rank, int world) {
+    if (!c || world < 1 || rank < 0 || rank >= world) return RT_ERR_ARG;
+    c->shardRank = rank; c->shardWorld = world;
+    return RT_OK;
+}
+int64_t rt_shard_pixels(const rt_ctx* c) { return c ? out_pixels(c) : 0; }
+
+int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids) {
+    if (!c || !p) return RT_ERR_ARG;
+    if (!c->haveScene || !c->haveCam || !c->haveLight) return fail(c, RT_ERR_STATE, "render before scene/camera/light upload");
+    if (dev_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
+    CU(c, cudaSetDevice(c->device));
+    int rc = flush_scene(c);
+    if (rc != RT_OK) return rc;
+    const int64_t px = out_pixels(c);
+    if (!dev_rgba) { CU(c, c->image.reserve((size_t)px)); dev_rgba = reinterpret_cast<float*>(c->image.p); }
+    const bool wantIds = (c->flags & RT_FLAG_HIT_IDS) != 0;
+    if (wantIds && !dev_ids) { CU(c, c->ids.reserve((size_t)px)); dev_ids = c->ids.p; }
+
+    DeviceScene S;
+    S.nodes = c->dNodesT.p; S.q0 = c->q0.p; S.q1 = c->q1.p; S.q2 = c->q2.p; S.q3 = c->q3.p;
+    S.ptype = c->ptype.p; S.pshape = c->dPshape.p; S.shapes = c->dShapes.p;
+    S.nNodes = c->nDfs; S.nPrims = c->nPrims; S.nShapes = c->nShapes;
+
+    FrameParams F;
+    std::memcpy(F.camP, c->cam.Position, 12); std::memcpy(F.camF, c->cam.Front, 12);
+    std::memcpy(F.camU, c->cam.Up, 12); std::memcpy(F.camR, c->cam.Right, 12);
+    // getRay's per-frame constants (gpu_shader.comp:156-157), evaluated once on the host
+    F.planeH = 2.0f * std::tan((c->cam.fov / 2.0f) * 0.017453292519943295f);
+    F.planeW = F.planeH * c->cam.aspectRatio;
+    std::memcpy(F.lightPos, c->light.position, 12); std::memcpy(F.lightCol, c->light.color, 12);
+    F.resW = p->screenRes[0]; F.resH = p->screenRes[1];
+    F.maxBounces = p->maxBounces; F.useBVH = p->useBVH != 0; F.useFresnel = p->useFresnel != 0; F.useMT = p->useMollerTrumbore != 0;
+    F.W = c->W; F.H = c->H; F.tilesX = tiles_x(c); F.tilesY = tiles_y(c);
+    F.shardRank = c->shardRank; F.shardWorld = c->shardWorld; F.nTilesMine = tiles_mine(c);
+    F.writeIds = wantIds ? 1 : 0;
+
+    cudaEventRecord(c->ev[4], c->stream);
+    if (F.nTilesMine > 0) {
+        const int grid = F.nTilesMine;
+        if (F.useMT) render_kernel<true><<<grid, RT_TILE_W * RT_TILE_H, 0, c->stream>>>(S, F, reinterpret_cast<float4*>(dev_rgba), dev_ids);
+        else         render_kernel<false><<<grid, RT_TILE_W * RT_TILE_H, 0, c->stream>>>(S, F, reinterpret_cast<float4*>(dev_rgba), dev_ids);
+        c->launches++;
+    }
+    cudaEventRecord(c->ev[5], c->stream); c->timed[2] = true;
+    CU(c, cudaGetLastError());
+    return RT_OK;
+}
+
+int rt_render(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* host_hit_ids) {
+    if (!c || !p) return RT_ERR_ARG;
+    if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
+    int rc = rt_render_device(c, p, nullptr, nullptr);
+    if (rc != RT_OK) return rc;
+    const size_t px = (size_t)out_pixels(c);
+    cudaEventRecord(c->ev[6], c->stream);
+    if (host_rgba) CU(c, cudaMemcpyAsync(host_rgba, c->image.p, px * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    if (host_hit_ids) CU(c, cudaMemcpyAsync(host_hit_ids, c->ids.p, px * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    cudaEventRecord(c->ev[7], c->stream); c->timed[3] = true;
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_untile(rt_ctx* c, const float* dev_shards, int world, float* dev_rgba_out) {
+    if (!c || !dev_shards || !dev_rgba_out || world < 1) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    const int nT = tiles_x(c) * tiles_y(c);
+    const long long shardPixels = (long long)((nT + world - 1) / world) * RT_TILE_W * RT_TILE_H;   // rank 0's (largest) shard
+    const long long n = (long long)c->W * c->H;
+    untile_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(dev_shards),
+        reinterpret_cast<float4*>(dev_rgba_out), c->W, c->H, tiles_x(c), world, shardPixels);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    return RT_OK;
+}
+
+int rt_present(rt_ctx* c, const float* dev_rgba, uint8_t* dev_rgba8_out, int64_t pixels) {
+    if (!c || !dev_rgba || !dev_rgba8_out || pixels < 0) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    if (pixels > 0) {
+        present_kernel<<<(unsigned)((pixels + 255) / 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(dev_rgba),
+            reinterpret_cast<uchar4*>(dev_rgba8_out), (long long)pixels);
+        c->launches++;
+    }
+    CU(c, cudaGetLastError());
+    return RT_OK;
+}
+
+void* rt_stream(rt_ctx* c) { return c ? (void*)c->stream : nullptr; }
+int rt_synchronize(rt_ctx* c) {
+    if (!c) return RT_ERR_ARG;
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+float* rt_device_image(rt_ctx* c) { return c ? reinterpret_cast<float*>(c->image.p) : nullptr; }
+
+int rt_last_timings(rt_ctx* c, float out_ms[4]) {
+    if (!c || !out_ms) return RT_ERR_ARG;
+    CU(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 4; ++i) {
+        out_ms[i] = -1.0f;
+        if (c->timed[i]) cudaEventElapsedTime(&out_ms[i], c->ev[2 * i], c->ev[2 * i + 1]);
+    }
+    return RT_OK;
+}
+int64_t rt_launch_count(const rt_ctx* c) { return c ? c->launches : 0; }
+const char* rt_build_info(void) { return "librt_b200 sm_100a fmad=off prec-div prec-sqrt tile=32x8"; }
+
+}  // extern "C"

@@ -1,0 +1,201 @@
+// rt_device.cuh — device-side data layout, exact-arithmetic helpers, primitive
+// tests and BVH traversal for the sm_100a ray-tracing kernel.
+//
+// Written from the behavioural spec in SURVEY.md §8(a) (what gpu_shader.comp
+// computes), not translated from the GLSL: the scene is repacked into float4
+// SoA in the reference's *visit order*, the BVH becomes a stackless threaded
+// list, per-primitive ray-independent terms are precomputed once at upload, and
+// shadow rays are any-hit.  Every hit/miss DECISION is still made with exactly
+// the IEEE fp32 operations, in exactly the order, of the shader (compiled with
+// -fmad=false), so closest-hit shape ids are bit-identical to the oracle.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rt_api.h"
+
+namespace rt {
+
+// ---------------------------------------------------------------------------
+// Device scene (built by the repack kernels, K2)
+// ---------------------------------------------------------------------------
+// Threaded BVH: nodes in the reference's DFS order (root, right subtree, left
+// subtree — gpu_shader.comp:424-425 pushes left then right and pops LIFO).
+//   n[2k]   = (boundsMin.xyz, bits(link))   inner: index of the node that follows
+//                                           this subtree;  leaf: first prim slot
+//   n[2k+1] = (boundsMax.xyz, bits(count))  inner: -1;     leaf: numShapes >= 0
+// A box hit on an inner node continues at k+1; a miss jumps to link.
+// Leaves' primitives are laid out contiguously in the same visit order, so
+// "first improvement wins on ties" (strict <, :411) is preserved by construction.
+//
+// Primitive slot s (SoA, 16-byte loads):
+//   type 0 sphere   q0=(center, r*r)
+//   type 1 plane    q0=(n, D)
+//   type 2 wall     q0=(n, D) q1=(start, width) q2=(u, height) q3=(v, 0)
+//   type 3 triangle q0=(n, D) q1=(P1, d00)      q2=(e1, d01)   q3=(e2, d11)
+struct DeviceScene {
+    const float4* __restrict__ nodes;   // 2 per node
+    const float4* __restrict__ q0;
+    const float4* __restrict__ q1;
+    const float4* __restrict__ q2;
+    const float4* __restrict__ q3;
+    const int*    __restrict__ ptype;   // per slot
+    const int*    __restrict__ pshape;  // per slot: original shape index
+    const rt_flat_shape* __restrict__ shapes;   // raw std430 shapes (materials, brute-force path)
+    int nNodes;
+    int nPrims;
+    int nShapes;
+};
+
+struct FrameParams {
+    float camP[3], camF[3], camU[3], camR[3];
+    float planeH, planeW;      // imagePlaneHeight / Width (tan hoisted to the host)
+    float lightPos[3], lightCol[3];
+    float resW, resH;          // uniform screenRes
+    int   maxBounces, useBVH, useFresnel, useMT;
+    int   W, H;                // image size in pixels
+    int   tilesX, tilesY;      // tile grid
+    int   shardRank, shardWorld;
+    int   nTilesMine;          // tiles owned by this rank
+    int   writeIds;
+};
+
+// ---------------------------------------------------------------------------
+// Exact helpers (GLSL-spec definitions; see oracle/oracle_rt.cpp header)
+// ---------------------------------------------------------------------------
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ V3 mk(const float* p) { return mk(p[0], p[1], p[2]); }
+__device__ __forceinline__ V3 xyz(float4 q) { return mk(q.x, q.y, q.z); }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float gmin(float x, float y) { return y < x ? y : x; }
+__device__ __forceinline__ float gmax(float x, float y) { return x < y ? y : x; }
+__device__ __forceinline__ float dot3(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float length3(V3 v) { return sqrtf(dot3(v, v)); }
+__device__ __forceinline__ float distance3(V3 a, V3 b) { return length3(a - b); }
+__device__ __forceinline__ V3 normalize3(V3 v) { float inv = 1.0f / sqrtf(dot3(v, v)); return v * inv; }
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+    return mk(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
+}
+__device__ __forceinline__ V3 reflect3(V3 I, V3 N) { float d = dot3(N, I); return I - N * d * 2.0f; }
+__device__ __forceinline__ float mix1(float x, float y, float a) { return x * (1.0f - a) + y * a; }
+
+struct Ray {
+    V3 o, d;
+    V3 inv;        // 1/d, hoisted out of the per-node slab test (gpu_shader.comp:365)
+    float aa;      // dot(d,d), hoisted out of the sphere test (:250)
+};
+__device__ __forceinline__ Ray make_ray(V3 o, V3 d) {
+    Ray r; r.o = o; r.d = d;
+    r.inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    r.aa = dot3(d, d);
+    return r;
+}
+
+// One primitive's precomputed record.
+struct Prim { float4 q0, q1, q2, q3; int type; };
+
+// Ray-independent terms of a raw std430 shape, with the shader's own operation
+// order (gpu_shader.comp:218-229 edges/dots, :305-307 wall basis, :252 r*r).
+__device__ __forceinline__ Prim prim_from_shape(const rt_flat_shape* __restrict__ s) {
+    Prim p;
+    p.type = s->type;
+    p.q0 = p.q1 = p.q2 = p.q3 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.type == RT_SHAPE_SPHERE) {
+        float r = s->sphereRadius;
+        p.q0 = make_float4(s->sphereCenter[0], s->sphereCenter[1], s->sphereCenter[2], r * r);
+    } else if (p.type == RT_SHAPE_PLANE || p.type == RT_SHAPE_WALL || p.type == RT_SHAPE_TRIANGLE) {
+        V3 n = mk(s->planeNormal);
+        p.q0 = make_float4(n.x, n.y, n.z, s->planeD);
+        if (p.type == RT_SHAPE_WALL) {
+            V3 u = normalize3(cross3(n, mk(0.f, 1.f, 0.f)));
+            if (length3(u) < 1e-5f) u = normalize3(cross3(n, mk(1.f, 0.f, 0.f)));   // false for NaN: kept
+            V3 v = normalize3(cross3(n, u));
+            p.q1 = make_float4(s->wallStart[0], s->wallStart[1], s->wallStart[2], s->wallWidth);
+            p.q2 = make_float4(u.x, u.y, u.z, s->wallHeight);
+            p.q3 = make_float4(v.x, v.y, v.z, 0.f);
+        } else if (p.type == RT_SHAPE_TRIANGLE) {
+            V3 p1 = mk(s->triP1);
+            V3 e1 = mk(s->triP2) - p1;
+            V3 e2 = mk(s->triP3) - p1;
+            p.q1 = make_float4(p1.x, p1.y, p1.z, dot3(e1, e1));
+            p.q2 = make_float4(e1.x, e1.y, e1.z, dot3(e1, e2));
+            p.q3 = make_float4(e2.x, e2.y, e2.z, dot3(e2, e2));
+        }
+    }
+    return p;
+}
+
+// ---------------------------------------------------------------------------
+// Primitive tests.  Return true for an INNER hit and set hp (OUTER == no hit for
+// every caller in the shader).  a5-a9 of SURVEY.md §8(a).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ bool plane_stage(float4 q0, const Ray& r, V3& hp) {
+    V3 n = xyz(q0);
+    float np = dot3(n, r.d);
+    if (np == 0.0f) return false;
+    float t = -(q0.w + dot3(n, r.o)) / np;
+    if (!(t > 0.0f)) return false;
+    if (np <= 0.0f) return false;          // OUTER
+    hp = r.o + t * r.d;
+    return true;
+}
+
+__device__ __forceinline__ bool hit_sphere(float4 q0, const Ray& r, V3& hp) {
+    V3 oc = r.o - xyz(q0);
+    float bb = 2.0f * dot3(r.d, oc);
+    float cc = dot3(oc, oc) - q0.w;
+    float D = bb * bb - 4.0f * r.aa * cc;
+    if (!(D > 0.0f)) return false;
+    float sD = sqrtf(D);
+    float t1 = (-bb - sD) / (2.0f * r.aa);
+    if (!(t1 > 0.0f)) return false;        // t2 > 0 would be OUTER
+    hp = r.o + t1 * r.d;
+    return true;
+}
+
+__device__ __forceinline__ bool wall_stage2(float4 q1, float4 q2, float4 q3, V3 hp) {
+    V3 local = hp - xyz(q1);
+    float uProj = dot3(local, xyz(q2));
+    float vProj = dot3(local, xyz(q3));
+    return !(uProj < 0.0f || uProj > q1.w || vProj < 0.0f || vProj > q2.w);
+}
+
+__device__ __forceinline__ bool bary_stage2(float4 q1, float4 q2, float4 q3, V3 hp) {
+    V3 toPoint = hp - xyz(q1);
+    V3 e1 = xyz(q2), e2 = xyz(q3);
+    float d00 = q1.w, d01 = q2.w, d11 = q3.w;
+    float d20 = dot3(toPoint, e1);
+    float d21 = dot3(toPoint, e2);
+    float denom = d00 * d11 - d01 * d01;
+    float v = (d11 * d20 - d01 * d21) / denom;
+    float w = (d00 * d21 - d01 * d20) / denom;
+    float u = 1.0f - v - w;
+    return !(u < 0.0f || v < 0.0f || w < 0.0f);
+}
+
+__device__ __forceinline__ bool hit_tri_mt(float4 q1, float4 q2, float4 q3, const Ray& r, V3& hp) {
+    V3 e1 = xyz(q2), e2 = xyz(q3);
+    V3 h = cross3(r.d, e2);
+    float a = dot3(e1, h);
+    if (fabsf(a) < 1e-5f) return false;
+    float f = 1.0f / a;
+    V3 s = r.o - xyz(q1);
+    float u = f * dot3(s, h);
+    if (u < 0.0f || u > 1.0f) return false;
+    V3 q = cross3(s, e1);
+    float v = f * dot3(r.d, q);
+    if (v < 0.0f || u + v > 1.0f) return false;
+    float t = f * dot3(e2, q);
+    if (!(t > 0.0f)) return false;
+    hp = r.o + t * r.d;
+    return true;
+}
+
+}  // namespace rt

@@ -1,0 +1,306 @@
+// rt_kernels.cuh — K1 (render), K2 (repack), K3 (untile), K4 (present).
+#pragma once
+#include "rt_device.cuh"
+
+namespace rt {
+
+// ---------------------------------------------------------------------------
+// Traversal
+// ---------------------------------------------------------------------------
+struct Hit { float dist; int slot; V3 p; };
+
+// Slab test with the shader's select semantics for min/max (a4, :364-377).
+__device__ __forceinline__ bool slab(const Ray& r, float4 a, float4 b) {
+    float t0x = (a.x - r.o.x) * r.inv.x, t1x = (b.x - r.o.x) * r.inv.x;
+    float t0y = (a.y - r.o.y) * r.inv.y, t1y = (b.y - r.o.y) * r.inv.y;
+    float t0z = (a.z - r.o.z) * r.inv.z, t1z = (b.z - r.o.z) * r.inv.z;
+    float tMin = gmax(gmax(gmin(t0x, t1x), gmin(t0y, t1y)), gmin(t0z, t1z));
+    float tMax = gmin(gmin(gmax(t0x, t1x), gmax(t0y, t1y)), gmax(t0z, t1z));
+    return tMax >= tMin && tMax > 0.0f;
+}
+
+template <bool MT>
+__device__ __forceinline__ bool test_prim(const Prim& p, const Ray& r, V3& hp) {
+    if (p.type == RT_SHAPE_TRIANGLE) {
+        if (MT) return hit_tri_mt(p.q1, p.q2, p.q3, r, hp);
+        return plane_stage(p.q0, r, hp) && bary_stage2(p.q1, p.q2, p.q3, hp);
+    }
+    if (p.type == RT_SHAPE_SPHERE) return hit_sphere(p.q0, r, hp);
+    if (p.type == RT_SHAPE_WALL) return plane_stage(p.q0, r, hp) && wall_stage2(p.q1, p.q2, p.q3, hp);
+    if (p.type == RT_SHAPE_PLANE) return plane_stage(p.q0, r, hp);
+    return false;
+}
+
+// Test the primitive in slot s, loading only what its type and stage need.
+template <bool MT>
+__device__ __forceinline__ bool test_slot(const DeviceScene& S, int s, const Ray& r, V3& hp) {
+    const int type = __ldg(S.ptype + s);
+    if (type == RT_SHAPE_TRIANGLE) {
+        if (MT) return hit_tri_mt(__ldg(S.q1 + s), __ldg(S.q2 + s), __ldg(S.q3 + s), r, hp);
+        if (!plane_stage(__ldg(S.q0 + s), r, hp)) return false;
+        return bary_stage2(__ldg(S.q1 + s), __ldg(S.q2 + s), __ldg(S.q3 + s), hp);
+    }
+    if (type == RT_SHAPE_SPHERE) return hit_sphere(__ldg(S.q0 + s), r, hp);
+    if (type == RT_SHAPE_WALL) {
+        if (!plane_stage(__ldg(S.q0 + s), r, hp)) return false;
+        return wall_stage2(__ldg(S.q1 + s), __ldg(S.q2 + s), __ldg(S.q3 + s), hp);
+    }
+    if (type == RT_SHAPE_PLANE) return plane_stage(__ldg(S.q0 + s), r, hp);
+    return false;
+}
+
+// Closest hit (a3).  Visits exactly the reference's node set in the reference's
+// order; dist is distance(ray.start, hit_point) with strict '<' (:410-411).
+template <bool MT>
+__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, Hit& h) {
+    h.dist = 1e20f; h.slot = -1; h.p = mk(0.f, 0.f, 0.f);
+    int k = 0;
+    const int n = S.nNodes;
+    while (k < n) {
+        const float4 a = __ldg(S.nodes + 2 * k);
+        const float4 b = __ldg(S.nodes + 2 * k + 1);
+        const int cnt = __float_as_int(b.w);
+        const int lnk = __float_as_int(a.w);
+        if (!slab(r, a, b)) { k = cnt < 0 ? lnk : k + 1; continue; }
+        if (cnt >= 0) {
+            const int end = lnk + cnt;
+            for (int s = lnk; s < end; ++s) {
+                V3 hp;
+                if (test_slot<MT>(S, s, r, hp)) {
+                    float dist = distance3(r.o, hp);
+                    if (dist < h.dist) { h.dist = dist; h.slot = s; h.p = hp; }
+                }
+            }
+        }
+        ++k;
+    }
+}
+
+// Shadow query (a12): the shader runs a full closest-hit query and then tests
+// hitDist < lightDist; "some INNER hit has dist < lightDist" is the same boolean
+// (the closest hit has the minimum dist), so this returns at the first occluder.
+template <bool MT>
+__device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, float lightDist) {
+    int k = 0;
+    const int n = S.nNodes;
+    while (k < n) {
+        const float4 a = __ldg(S.nodes + 2 * k);
+        const float4 b = __ldg(S.nodes + 2 * k + 1);
+        const int cnt = __float_as_int(b.w);
+        const int lnk = __float_as_int(a.w);
+        if (!slab(r, a, b)) { k = cnt < 0 ? lnk : k + 1; continue; }
+        if (cnt >= 0) {
+            const int end = lnk + cnt;
+            for (int s = lnk; s < end; ++s) {
+                V3 hp;
+                if (test_slot<MT>(S, s, r, hp)) {
+                    float dist = distance3(r.o, hp);
+                    if (dist < 1e20f && dist < lightDist) return true;
+                }
+            }
+        }
+        ++k;
+    }
+    return false;
+}
+
+// Brute-force twins (a14, useBVH == false): linear scan over the raw shapes.
+template <bool MT>
+__device__ __forceinline__ void scan_closest(const DeviceScene& S, const Ray& r, Hit& h) {
+    h.dist = 1e20f; h.slot = -1; h.p = mk(0.f, 0.f, 0.f);
+    for (int i = 0; i < S.nShapes; ++i) {
+        Prim p = prim_from_shape(S.shapes + i);
+        V3 hp;
+        if (test_prim<MT>(p, r, hp)) {
+            float dist = distance3(r.o, hp);
+            if (dist < h.dist) { h.dist = dist; h.slot = i; h.p = hp; }
+        }
+    }
+}
+template <bool MT>
+__device__ __forceinline__ bool scan_any(const DeviceScene& S, const Ray& r, float lightDist) {
+    for (int i = 0; i < S.nShapes; ++i) {
+        Prim p = prim_from_shape(S.shapes + i);
+        V3 hp;
+        if (test_prim<MT>(p, r, hp)) {
+            float dist = distance3(r.o, hp);
+            if (dist < lightDist) return true;       // :572-578 (no 1e20 gate in this twin)
+        }
+    }
+    return false;
+}
+
+// ---------------------------------------------------------------------------
+// Shading (a1, a2, a10-a13)
+// ---------------------------------------------------------------------------
+struct Material { V3 color; float fresnel, ambient, diffuse, specular; int shininess; };
+
+__device__ __forceinline__ Material load_material(const rt_flat_shape* __restrict__ s) {
+    const float4* m = reinterpret_cast<const float4*>(&s->material);
+    float4 m0 = __ldg(m), m1 = __ldg(m + 1);
+    Material r;
+    r.color = mk(m0.x, m0.y, m0.z); r.fresnel = m0.w;
+    r.ambient = m1.x; r.diffuse = m1.y; r.specular = m1.z; r.shininess = __float_as_int(m1.w);
+    return r;
+}
+
+__device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3 lcol, const Material& m) {
+    float distToLight = distance3(lpos, point);
+    V3 lightColor = lcol / distToLight;
+    V3 ambient = m.ambient * lightColor;
+    V3 lightDir = normalize3(lpos - point);
+    float diff = gmax(dot3(normal, lightDir), 0.0f);
+    V3 diffuse = (m.diffuse * diff) * lightColor;
+    V3 specular = mk(0.f, 0.f, 0.f);
+    if (diff > 0.0f) {
+        V3 reflectDir = reflect3(-lightDir, normal);
+        float spec = powf(gmax(dot3(viewDir, reflectDir), 0.0f), (float)m.shininess);
+        specular = (m.specular * spec) * lightColor;
+    }
+    return ((ambient + diffuse) + specular) * m.color;
+}
+
+template <bool MT>
+__device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, int& idOut) {
+    const float a = (float)y / P.resH;
+    const V3 bg = mk(mix1(0.05f, 0.5f, a), mix1(0.07f, 0.7f, a), mix1(0.1f, 1.0f, a));
+    const float ndcX = 2.0f * (float)x / P.resW - 1.0f;
+    const float ndcY = 1.0f - 2.0f * (float)y / P.resH;
+    const V3 camP = mk(P.camP);
+    V3 ipp = ((camP + mk(P.camF)) + (ndcX * P.planeW / 2.0f) * mk(P.camR)) + (ndcY * P.planeH / 2.0f) * mk(P.camU);
+    Ray ray = make_ray(camP, normalize3(ipp - camP));
+    const V3 lpos = mk(P.lightPos), lcol = mk(P.lightCol);
+    V3 acc = mk(0.f, 0.f, 0.f), att = mk(1.f, 1.f, 1.f);
+    idOut = -1;
+
+    for (int depth = 0; depth < P.maxBounces; ++depth) {
+        Hit h;
+        int shape;
+        if (P.useBVH) { trace_closest<MT>(S, ray, h); shape = h.slot >= 0 ? __ldg(S.pshape + h.slot) : -1; }
+        else          { scan_closest<MT>(S, ray, h);  shape = h.slot; }
+        if (depth == 0) idOut = shape;
+        if (shape < 0) { acc = acc + att * bg; break; }
+
+        const rt_flat_shape* sh = S.shapes + shape;
+        const Material m = load_material(sh);
+        const V3 hp = h.p;
+        V3 nrm;
+        if (__ldg(&sh->type) == RT_SHAPE_SPHERE) nrm = normalize3(hp - mk(__ldg(&sh->sphereCenter[0]), __ldg(&sh->sphereCenter[1]), __ldg(&sh->sphereCenter[2])));
+        else nrm = mk(__ldg(&sh->planeNormal[0]), __ldg(&sh->planeNormal[1]), __ldg(&sh->planeNormal[2]));
+
+        const V3 sdir = normalize3(lpos - hp);
+        const float lightDist = distance3(lpos, hp);
+        bool inShadow;
+        if (P.useBVH) inShadow = trace_any<MT>(S, make_ray(hp + nrm * 1e-3f, sdir), lightDist);
+        else          inShadow = scan_any<MT>(S, make_ray(hp + nrm * 1e-5f, sdir), lightDist);
+
+        V3 pc = phong(hp, nrm, ray.d, lpos, lcol, m);
+        if (inShadow) pc = pc * 0.3f;
+        acc = acc + att * pc;
+
+        if (!(m.specular > 0.0f)) break;
+        const V3 rd = reflect3(ray.d, nrm);
+        ray = make_ray(hp + nrm * 1e-3f, rd);
+        if (P.useFresnel) {
+            float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
+            fr = gmin(gmax(fr, 0.0f), 0.8f);
+            const float rw = m.fresnel * fr, mw = 1.0f - rw;
+            att = att * mk(mix1(m.color.x, 1.0f, rw), mix1(m.color.y, 1.0f, rw), mix1(m.color.z, 1.0f, rw));
+            acc = acc + (mw * m.color) * pc;
+        } else {
+            att = att * m.specular;
+        }
+    }
+    return make_float4(acc.x, acc.y, acc.z, 1.0f);
+}
+
+// ---------------------------------------------------------------------------
+// K1: render.  One CTA works on RT_TILE_W x RT_TILE_H tiles (grid-stride over
+// this rank's tiles); a warp covers an 8x4 pixel block for ray coherence.
+// world == 1 writes row-major W*H; world > 1 writes the compact tile-major shard.
+// ---------------------------------------------------------------------------
+template <bool MT>
+__global__ void __launch_bounds__(RT_TILE_W * RT_TILE_H)
+render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __restrict__ ids) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lx = ((warp & 3) << 3) + (lane & 7);
+    const int ly = ((warp >> 2) << 2) + (lane >> 3);
+    for (int t = blockIdx.x; t < P.nTilesMine; t += gridDim.x) {
+        const int tile = P.shardRank + t * P.shardWorld;
+        const int x = (tile % P.tilesX) * RT_TILE_W + lx;
+        const int y = (tile / P.tilesX) * RT_TILE_H + ly;
+        const bool inside = x < P.W && y < P.H;
+        float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+        int id = -1;
+        if (inside) c = shade_pixel<MT>(S, P, x, y, id);
+        if (P.shardWorld == 1) {
+            if (inside) {
+                const size_t o = (size_t)y * (size_t)P.W + (size_t)x;
+                out[o] = c;
+                if (P.writeIds) ids[o] = id;
+            }
+        } else {
+            const size_t o = (size_t)t * (RT_TILE_W * RT_TILE_H) + (size_t)(ly * RT_TILE_W + lx);
+            out[o] = c;
+            if (P.writeIds) ids[o] = id;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// K2: repack.  nodes: gather the raw 48-byte nodes into the threaded layout;
+// prims: gather the raw 192-byte shapes into float4 SoA in visit order.
+// ---------------------------------------------------------------------------
+__global__ void repack_nodes_kernel(const rt_flat_node* __restrict__ raw, const int* __restrict__ order,
+                                    const int2* __restrict__ linkCnt, float4* __restrict__ out, int n) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const float4* src = reinterpret_cast<const float4*>(raw + order[k]);
+    const float4 mn = __ldg(src), mx = __ldg(src + 1);
+    const int2 lc = linkCnt[k];
+    out[2 * k]     = make_float4(mn.x, mn.y, mn.z, __int_as_float(lc.x));
+    out[2 * k + 1] = make_float4(mx.x, mx.y, mx.z, __int_as_float(lc.y));
+}
+
+__global__ void repack_prims_kernel(const rt_flat_shape* __restrict__ shapes, const int* __restrict__ pshape,
+                                    float4* __restrict__ q0, float4* __restrict__ q1, float4* __restrict__ q2,
+                                    float4* __restrict__ q3, int* __restrict__ ptype, int n) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const Prim p = prim_from_shape(shapes + pshape[s]);
+    q0[s] = p.q0; q1[s] = p.q1; q2[s] = p.q2; q3[s] = p.q3; ptype[s] = p.type;
+}
+
+// ---------------------------------------------------------------------------
+// K3: untile.  shards = `world` compact buffers of shardPixels float4 each, rank
+// after rank (the NCCL gather's landing layout) -> row-major W*H.
+// ---------------------------------------------------------------------------
+__global__ void untile_kernel(const float4* __restrict__ shards, float4* __restrict__ out, int W, int H,
+                              int tilesX, int world, long long shardPixels) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)W * H) return;
+    const int x = (int)(i % W), y = (int)(i / W);
+    const int tile = (y / RT_TILE_H) * tilesX + (x / RT_TILE_W);
+    const int rank = tile % world, t = tile / world;
+    const long long src = (long long)rank * shardPixels + (long long)t * (RT_TILE_W * RT_TILE_H) +
+                          (y % RT_TILE_H) * RT_TILE_W + (x % RT_TILE_W);
+    out[i] = __ldg(shards + src);
+}
+
+// ---------------------------------------------------------------------------
+// K4: present.  shader.frag:8-12 samples the image 1:1 and writes
+// vec4(color.rgb, 1); the default framebuffer clamps to [0,1] and stores RGBA8.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ unsigned quant8(float v) {
+    v = gmin(gmax(v, 0.0f), 1.0f);
+    if (!(v == v)) v = 0.0f;
+    return (unsigned)(int)(v * 255.0f + 0.5f);
+}
+__global__ void present_kernel(const float4* __restrict__ in, uchar4* __restrict__ out, long long n) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 c = __ldg(in + i);
+    out[i] = make_uchar4((unsigned char)quant8(c.x), (unsigned char)quant8(c.y), (unsigned char)quant8(c.z), 255);
+}
+
+}  // namespace rt

@@ -1,0 +1,62 @@
+/*
+ * rt_host.h — headless stand-in for the reference's CPU side (layers L3/L4 of
+ * SURVEY.md §1): deterministic scene generators, the reference's midpoint-split
+ * BVH builder / grow-only refit, flattening to the std430 wire format and the
+ * scene animations.  It exists to FEED the hot path (librt_b200.so) and the
+ * oracle identical bytes; it is not part of the hot path.
+ *
+ * Restates (never copies): generateScene1/2/3 src/main.cpp:583-804,1196-1229,
+ * buildBVH/split/updateBVH :1068-1077,1111-1193, serializeBVH/serializeShape
+ * :955-1066, bounceSphere/updateWheelAnimations :1079-1109, BoundingBox.hpp,
+ * Camera::LookAt camera.hpp:139-163, shape constructors shapes/*.hpp.
+ */
+#ifndef RT_HOST_H
+#define RT_HOST_H
+
+#include "../../include/rt_api.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rh_scene rh_scene;
+
+/* name: "monkey" (1240 shapes, buildBVH(15)), "car" (4022 tris + 100 spheres,
+ * buildBVH(25)), "soup" (n_override triangles, default 1 000 000, + n/100
+ * spheres, buildBVH(40)), "triangle" (reference scene 3 + a BVH), "toy"
+ * (a handful of shapes of every type incl. the NaN-basis floor wall).
+ * The model files are absent upstream (.gitignore:78); meshes are synthetic
+ * stand-ins with identical primitive counts.
+ * bvh_depth <= 0 selects the scene's default. */
+rh_scene* rh_scene_create(const char* name, int width, int height, int n_override, int bvh_depth);
+
+/* Wrap caller-provided flat shapes (any mix of types) and build the reference
+ * BVH over them.  Infinite planes (type 1) get no bounds, as upstream. */
+rh_scene* rh_scene_from_shapes(const rt_flat_shape* shapes, int nShapes,
+                               const rt_flat_light* light, const rt_flat_camera* camera, int bvh_depth);
+void rh_scene_destroy(rh_scene* s);
+
+const rt_flat_light*  rh_light(const rh_scene* s);
+const rt_flat_camera* rh_camera(const rh_scene* s);
+const rt_flat_shape*  rh_shapes(const rh_scene* s, int* n);
+const rt_flat_node*   rh_nodes(const rh_scene* s, int* n);
+const int32_t*        rh_indices(const rh_scene* s, int* n);
+
+/* BVH statistics: out[0]=nodes out[1]=leaves out[2]=max leaf size out[3]=depth */
+void rh_bvh_stats(const rh_scene* s, int out[4]);
+
+/* Advance the scene's animation to absolute time t (seconds) with frame delta
+ * dt, re-serialise the animated shapes and update the BVH:
+ * mode 0 = grow-only refit (reference behaviour, main.cpp:336-345),
+ * mode 1 = full rebuild (buildBVH again; node count may change).
+ * Returns the number of animated shapes; their indices via rh_animated. */
+int rh_scene_animate(rh_scene* s, float t, float dt, int mode);
+const int32_t* rh_animated(const rh_scene* s, int* n);
+
+/* Camera helper (camera.hpp:139-163): place + LookAt, fov in degrees. */
+void rh_set_camera(rh_scene* s, const float pos[3], const float target[3], float fov, float aspect);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

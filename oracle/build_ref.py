@@ -1,0 +1,75 @@
+#!/usr/bin/env python3
+"""Build oracle/_ref/libref_shader.so: the reference's gpu_shader.comp compiled as C++.
+
+TEST INFRASTRUCTURE.  Reads the shader where it lies under the reference tree
+(default /root/reference, read-only), applies a mechanical text transform and
+writes ONLY into oracle/_ref/ (git-ignored; the built .so travels to the GPU
+box with the snapshot).  Nothing is copied into tracked files.
+
+Transform:
+  * drop `#version` and the `layout(...)` interface block (-> REF_BUFFERS, which
+    the glue defines as plain statics of the same names);
+  * suffix every floating literal with `f` (GLSL literals are fp32);
+  * `out float` parameters -> `float&`;
+  * `value.xyz = accumulatedColor;` -> vec4 constructor (no swizzle stores in GLM);
+  * `ivec2(gl_GlobalInvocationID.xy)` -> a thread-local ivec2.
+"""
+import os
+import re
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def transform(src: str) -> str:
+    lines = src.split("\n")
+    out = []
+    in_layout = False
+    emitted = False
+    for ln in lines:
+        s = ln.strip()
+        if s.startswith("#version"):
+            continue
+        if s.startswith("layout("):
+            in_layout = not s.endswith(";")
+            if not emitted:
+                out.append("REF_BUFFERS")
+                emitted = True
+            continue
+        if in_layout:
+            if s.startswith("};") or s == "}":
+                in_layout = False
+            continue
+        out.append(ln)
+    body = "\n".join(out)
+    lit = re.compile(r"(?<![A-Za-z0-9_.])((?:[0-9]+\.[0-9]*|\.[0-9]+)(?:[eE][-+]?[0-9]+)?|[0-9]+[eE][-+]?[0-9]+)(?![0-9A-Za-z_.])")
+    body = lit.sub(lambda m: m.group(1) + "f", body)
+    body = body.replace("out float", "float&")
+    body = body.replace("value.xyz = accumulatedColor;", "value = vec4(accumulatedColor, value.w);")
+    body = body.replace("ivec2(gl_GlobalInvocationID.xy)", "gl_GlobalInvocationID_xy")
+    return body
+
+
+def main() -> int:
+    ref = sys.argv[1] if len(sys.argv) > 1 else os.environ.get("RT_REFERENCE_DIR", "/root/reference")
+    shader = os.path.join(ref, "src", "shaders", "gpu_shader.comp")
+    glm = os.path.join(ref, "glm")
+    if not os.path.isfile(shader) or not os.path.isdir(glm):
+        print(f"build_ref: reference not present at {ref}; keeping any prebuilt oracle/_ref", file=sys.stderr)
+        return 0
+    outdir = os.path.join(HERE, "_ref")
+    os.makedirs(outdir, exist_ok=True)
+    with open(shader, "r", encoding="utf-8", errors="replace") as f:
+        body = transform(f.read())
+    with open(os.path.join(outdir, "gpu_shader_body.inc"), "w") as f:
+        f.write(body)
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared", "-pthread",
+           "-I", glm, "-I", HERE, os.path.join(HERE, "ref_shader_glue.cpp"),
+           "-o", os.path.join(outdir, "libref_shader.so")]
+    print(" ".join(cmd))
+    return subprocess.call(cmd)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

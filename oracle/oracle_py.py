@@ -1,0 +1,123 @@
+"""ctypes binding of the CPU oracle (TEST INFRASTRUCTURE).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs import this module.  The product path never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+class Counters(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("primary_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("reflect_rays", C.c_uint64), ("node_visits", C.c_uint64), ("index_reads", C.c_uint64),
+                ("tests", C.c_uint64 * 4), ("tri_stage2", C.c_uint64), ("ray_hits", C.c_uint64),
+                ("alg_bytes", C.c_uint64)]
+
+    def as_dict(self):
+        d = {k: int(getattr(self, k)) for k, _ in self._fields_ if k != "tests"}
+        d["tests"] = [int(x) for x in self.tests]
+        return d
+
+
+def build(force=False):
+    out = os.path.join(HERE, "liboracle_rt.so")
+    srcs = [os.path.join(HERE, "oracle_rt.cpp"), os.path.join(HERE, "oracle_rt.h")]
+    if force or not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in srcs):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-pthread",
+                               "-o", out, srcs[0]])
+    return out
+
+
+def build_ref():
+    """(Re)build oracle/_ref from the reference tree when it is present; returns the .so path or None."""
+    subprocess.call(["python3", os.path.join(HERE, "build_ref.py")])
+    p = os.path.join(HERE, "_ref", "libref_shader.so")
+    return p if os.path.exists(p) else None
+
+
+_lib = None
+_ref = None
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(build())
+        vp, ip = C.c_void_p, C.c_int
+        L.oracle_render.argtypes = [vp, vp, vp, ip, vp, ip, vp, ip, vp, ip, ip, ip, ip, vp, vp, vp, vp, ip]
+        L.oracle_render.restype = ip
+        L.oracle_intersect_shape.argtypes = [vp, vp, vp, ip, vp]; L.oracle_intersect_shape.restype = ip
+        L.oracle_intersect_scene.argtypes = [vp, ip, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp]; L.oracle_intersect_scene.restype = ip
+        L.oracle_present.argtypes = [vp, vp, C.c_int64]; L.oracle_present.restype = None
+        _lib = L
+    return _lib
+
+
+def ref_lib():
+    """The reference shader compiled as C++ (oracle/_ref/libref_shader.so), or None if never built."""
+    global _ref
+    if _ref is None:
+        p = os.path.join(HERE, "_ref", "libref_shader.so")
+        if not os.path.exists(p):
+            return None
+        R = C.CDLL(p)
+        vp, ip = C.c_void_p, C.c_int
+        R.ref_render.argtypes = [vp, vp, vp, ip, vp, ip, vp, ip, vp, ip, ip, ip, ip, vp, ip]
+        R.ref_render.restype = ip
+        _ref = R
+    return _ref
+
+
+def render(light, camera, shapes, nodes, indices, params, W, H, threads=None, row_step=1, row_phase=0,
+           want_counters=True):
+    """Returns (rgba[H,W,4] f32, ids[H,W] i32, dists[H,W] f32, counters dict|None)."""
+    threads = threads or os.cpu_count() or 1
+    rgba = np.zeros((H, W, 4), np.float32)
+    ids = np.full((H, W), -1, np.int32)
+    dists = np.full((H, W), 1e20, np.float32)
+    cnt = Counters() if want_counters else None
+    arrs = [np.ascontiguousarray(a) for a in (light, camera, shapes, nodes, indices)]
+    rc = lib().oracle_render(_p(arrs[0]), _p(arrs[1]), _p(arrs[2]), len(arrs[2]), _p(arrs[3]), len(arrs[3]),
+                             _p(arrs[4]), len(arrs[4]), C.addressof(params), W, H, row_step, row_phase,
+                             _p(rgba), _p(ids), _p(dists), C.addressof(cnt) if cnt is not None else None, threads)
+    if rc != 0:
+        raise RuntimeError("oracle_render failed")
+    return rgba, ids, dists, (cnt.as_dict() if cnt is not None else None)
+
+
+def ref_render(light, camera, shapes, nodes, indices, params, W, H, threads=None, row_step=1, row_phase=0):
+    R = ref_lib()
+    if R is None:
+        raise RuntimeError("oracle/_ref not built")
+    threads = threads or os.cpu_count() or 1
+    rgba = np.zeros((H, W, 4), np.float32)
+    arrs = [np.ascontiguousarray(a) for a in (light, camera, shapes, nodes, indices)]
+    rc = R.ref_render(_p(arrs[0]), _p(arrs[1]), _p(arrs[2]), len(arrs[2]), _p(arrs[3]), len(arrs[3]),
+                      _p(arrs[4]), len(arrs[4]), C.addressof(params), W, H, row_step, row_phase, _p(rgba), threads)
+    if rc != 0:
+        raise RuntimeError("ref_render failed")
+    return rgba
+
+
+def intersect_shape(shape, start, direction, useMT=False):
+    hp = np.zeros(3, np.float32)
+    s = np.ascontiguousarray(shape)
+    t = lib().oracle_intersect_shape(_p(s), _p(np.asarray(start, np.float32)), _p(np.asarray(direction, np.float32)),
+                                     int(useMT), _p(hp))
+    return t, hp
+
+
+def present(rgba):
+    rgba = np.ascontiguousarray(rgba, np.float32)
+    out = np.zeros(rgba.shape[:-1] + (4,), np.uint8)
+    lib().oracle_present(_p(rgba), _p(out), rgba.size // 4)
+    return out
