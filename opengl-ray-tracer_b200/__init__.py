@@ -4,6 +4,6 @@ The product is csrc/librt_b200.so (C ABI in include/rt_api.h).  This package onl
 holds the build recipe, the ctypes harness bindings and the headless host library.
 The directory name contains '-', so load it with `rtload.load()` at the repo root.
 """
-from . import build  # noqa: F401
+from . import build, shard  # noqa: F401
 from .binding import (CAMERA_DTYPE, LIGHT_DTYPE, NODE_DTYPE, SHAPE_DTYPE, RT_FLAG_CULL, RT_FLAG_HIT_IDS,  # noqa: F401
                       API_SYMBOLS, Params, RayTracer, RtError, Scene, hostlib, lib, lib_path, make_params)

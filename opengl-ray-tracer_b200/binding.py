@@ -54,7 +54,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_device", "rt_untile", "rt_present", "rt_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_device", "rt_render_stats", "rt_untile", "rt_present", "rt_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -82,6 +82,7 @@ def lib():
     L.rt_shard_pixels.argtypes = [vp]; L.rt_shard_pixels.restype = C.c_int64
     L.rt_render.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render.restype = ip
     L.rt_render_device.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_device.restype = ip
+    L.rt_render_stats.argtypes = [vp, C.POINTER(Params), C.POINTER(C.c_uint64)]; L.rt_render_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
     L.rt_stream.argtypes = [vp]; L.rt_stream.restype = vp
@@ -155,15 +156,15 @@ class Scene:
         if n.value == 0:
             return np.zeros(0, dtype=dtype)
         buf = (C.c_char * (n.value * dtype.itemsize)).from_address(p)
-        return np.frombuffer(buf, dtype=dtype, count=n.value).copy()
+        return np.frombuffer(buf, dtype=np.uint8).copy().view(dtype)      # byte copy: keeps the std430 padding
 
     @property
     def light(self):
-        return np.frombuffer((C.c_char * 32).from_address(self._H.rh_light(self._h)), dtype=LIGHT_DTYPE, count=1).copy()
+        return np.frombuffer((C.c_char * 32).from_address(self._H.rh_light(self._h)), dtype=np.uint8).copy().view(LIGHT_DTYPE)
 
     @property
     def camera(self):
-        return np.frombuffer((C.c_char * 80).from_address(self._H.rh_camera(self._h)), dtype=CAMERA_DTYPE, count=1).copy()
+        return np.frombuffer((C.c_char * 80).from_address(self._H.rh_camera(self._h)), dtype=np.uint8).copy().view(CAMERA_DTYPE)
 
     @property
     def shapes(self):
@@ -266,6 +267,13 @@ class RayTracer:
     def render_device(self, params, dev_rgba_ptr=None, dev_ids_ptr=None):
         """Asynchronous render into device memory (pointers as ints, e.g. tensor.data_ptr())."""
         self._chk(self._L.rt_render_device(self._c, C.byref(params), _ptr(dev_rgba_ptr), _ptr(dev_ids_ptr)))
+
+    def render_stats(self, params):
+        """Untimed counting render: dict of work counters of the CUDA path."""
+        out = (C.c_uint64 * 8)()
+        self._chk(self._L.rt_render_stats(self._c, C.byref(params), out))
+        keys = ["rays", "primary_rays", "shadow_rays", "reflect_rays", "node_visits", "prim_tests", "ray_hits", "shadowed"]
+        return dict(zip(keys, [int(x) for x in out]))
 
     def untile(self, dev_shards_ptr, world, dev_out_ptr):
         self._chk(self._L.rt_untile(self._c, _ptr(dev_shards_ptr), world, _ptr(dev_out_ptr)))

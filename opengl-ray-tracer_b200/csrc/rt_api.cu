@@ -81,6 +81,7 @@ struct rt_ctx {
 
     // output
     DevBuf<float4> image; DevBuf<int> ids;
+    DevBuf<unsigned long long> tally;
     int shardRank = 0, shardWorld = 1;
 };
 
@@ -274,7 +275,7 @@ void rt_destroy(rt_ctx* c) {
     c->hOrder.release(); c->dOrder.release(); c->hLinkCnt.release(); c->dLinkCnt.release();
     c->hPshape.release(); c->dPshape.release(); c->dNodesT.release();
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
-    c->image.release(); c->ids.release();
+    c->image.release(); c->ids.release(); c->tally.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->copyDone) cudaEventDestroy(c->copyDone);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -335,7 +336,25 @@ int rt_set_shard(rt_ctx* c, int rank, int world) {
 }
 int64_t rt_shard_pixels(const rt_ctx* c) { return c ? out_pixels(c) : 0; }
 
+static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count);
+
 int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids) {
+    return render_impl(c, p, dev_rgba, dev_ids, false);
+}
+
+int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8]) {
+    if (!c || !p || !out) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->tally.reserve(8));
+    CU(c, cudaMemsetAsync(c->tally.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    int rc = render_impl(c, p, nullptr, nullptr, true);
+    if (rc != RT_OK) return rc;
+    CU(c, cudaMemcpyAsync(out, c->tally.p, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count) {
     if (!c || !p) return RT_ERR_ARG;
     if (!c->haveScene || !c->haveCam || !c->haveLight) return fail(c, RT_ERR_STATE, "render before scene/camera/light upload");
     if (dev_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
@@ -368,8 +387,16 @@ int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* de
     cudaEventRecord(c->ev[4], c->stream);
     if (F.nTilesMine > 0) {
         const int grid = F.nTilesMine;
-        if (F.useMT) render_kernel<true><<<grid, RT_TILE_W * RT_TILE_H, 0, c->stream>>>(S, F, reinterpret_cast<float4*>(dev_rgba), dev_ids);
-        else         render_kernel<false><<<grid, RT_TILE_W * RT_TILE_H, 0, c->stream>>>(S, F, reinterpret_cast<float4*>(dev_rgba), dev_ids);
+        const dim3 blk(RT_TILE_W * RT_TILE_H);
+        float4* o4 = reinterpret_cast<float4*>(dev_rgba);
+        unsigned long long* tl = c->tally.p;
+        if (count) {
+            if (F.useMT) render_kernel<true, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl);
+            else         render_kernel<false, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl);
+        } else {
+            if (F.useMT) render_kernel<true, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr);
+            else         render_kernel<false, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr);
+        }
         c->launches++;
     }
     cudaEventRecord(c->ev[5], c->stream); c->timed[2] = true;

@@ -61,7 +61,7 @@ struct FrameParams {
 };
 
 // ---------------------------------------------------------------------------
-// Exact helpers (GLSL-spec definitions; see oracle/oracle_rt.cpp header)
+// Exact helpers (GLSL-spec definitions, listed in DESIGN.md)
 // ---------------------------------------------------------------------------
 struct V3 { float x, y, z; };
 __device__ __forceinline__ V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }

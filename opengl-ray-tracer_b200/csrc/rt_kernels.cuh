@@ -9,6 +9,12 @@ namespace rt {
 // ---------------------------------------------------------------------------
 struct Hit { float dist; int slot; V3 p; };
 
+// Optional work counters (stats launches only; the timed kernel is compiled without them).
+// [0] rays (BVH/scan queries) [1] primary [2] shadow [3] reflection [4] nodes visited
+// [5] primitive tests [6] closest-hit queries that hit [7] shadow queries that were occluded
+struct Tally { unsigned long long v[8]; };
+#define RT_TALLY(i, n) do { if (COUNT) tl.v[i] += (n); } while (0)
+
 // Slab test with the shader's select semantics for min/max (a4, :364-377).
 __device__ __forceinline__ bool slab(const Ray& r, float4 a, float4 b) {
     float t0x = (a.x - r.o.x) * r.inv.x, t1x = (b.x - r.o.x) * r.inv.x;
@@ -51,8 +57,8 @@ __device__ __forceinline__ bool test_slot(const DeviceScene& S, int s, const Ray
 
 // Closest hit (a3).  Visits exactly the reference's node set in the reference's
 // order; dist is distance(ray.start, hit_point) with strict '<' (:410-411).
-template <bool MT>
-__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, Hit& h) {
+template <bool MT, bool COUNT>
+__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, Hit& h, Tally& tl) {
     h.dist = 1e20f; h.slot = -1; h.p = mk(0.f, 0.f, 0.f);
     int k = 0;
     const int n = S.nNodes;
@@ -61,9 +67,11 @@ __device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r
         const float4 b = __ldg(S.nodes + 2 * k + 1);
         const int cnt = __float_as_int(b.w);
         const int lnk = __float_as_int(a.w);
+        RT_TALLY(4, 1);
         if (!slab(r, a, b)) { k = cnt < 0 ? lnk : k + 1; continue; }
         if (cnt >= 0) {
             const int end = lnk + cnt;
+            RT_TALLY(5, cnt);
             for (int s = lnk; s < end; ++s) {
                 V3 hp;
                 if (test_slot<MT>(S, s, r, hp)) {
@@ -79,8 +87,8 @@ __device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r
 // Shadow query (a12): the shader runs a full closest-hit query and then tests
 // hitDist < lightDist; "some INNER hit has dist < lightDist" is the same boolean
 // (the closest hit has the minimum dist), so this returns at the first occluder.
-template <bool MT>
-__device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, float lightDist) {
+template <bool MT, bool COUNT>
+__device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, float lightDist, Tally& tl) {
     int k = 0;
     const int n = S.nNodes;
     while (k < n) {
@@ -88,11 +96,13 @@ __device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, fl
         const float4 b = __ldg(S.nodes + 2 * k + 1);
         const int cnt = __float_as_int(b.w);
         const int lnk = __float_as_int(a.w);
+        RT_TALLY(4, 1);
         if (!slab(r, a, b)) { k = cnt < 0 ? lnk : k + 1; continue; }
         if (cnt >= 0) {
             const int end = lnk + cnt;
             for (int s = lnk; s < end; ++s) {
                 V3 hp;
+                RT_TALLY(5, 1);
                 if (test_slot<MT>(S, s, r, hp)) {
                     float dist = distance3(r.o, hp);
                     if (dist < 1e20f && dist < lightDist) return true;
@@ -160,8 +170,8 @@ __device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3
     return ((ambient + diffuse) + specular) * m.color;
 }
 
-template <bool MT>
-__device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, int& idOut) {
+template <bool MT, bool COUNT>
+__device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, int& idOut, Tally& tl) {
     const float a = (float)y / P.resH;
     const V3 bg = mk(mix1(0.05f, 0.5f, a), mix1(0.07f, 0.7f, a), mix1(0.1f, 1.0f, a));
     const float ndcX = 2.0f * (float)x / P.resW - 1.0f;
@@ -176,8 +186,9 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
     for (int depth = 0; depth < P.maxBounces; ++depth) {
         Hit h;
         int shape;
-        if (P.useBVH) { trace_closest<MT>(S, ray, h); shape = h.slot >= 0 ? __ldg(S.pshape + h.slot) : -1; }
-        else          { scan_closest<MT>(S, ray, h);  shape = h.slot; }
+        if (P.useBVH) { trace_closest<MT, COUNT>(S, ray, h, tl); shape = h.slot >= 0 ? __ldg(S.pshape + h.slot) : -1; }
+        else          { scan_closest<MT>(S, ray, h);  shape = h.slot; RT_TALLY(5, S.nShapes); }
+        RT_TALLY(0, 1); RT_TALLY(depth == 0 ? 1 : 3, 1); RT_TALLY(6, shape >= 0 ? 1 : 0);
         if (depth == 0) idOut = shape;
         if (shape < 0) { acc = acc + att * bg; break; }
 
@@ -191,8 +202,9 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
         const V3 sdir = normalize3(lpos - hp);
         const float lightDist = distance3(lpos, hp);
         bool inShadow;
-        if (P.useBVH) inShadow = trace_any<MT>(S, make_ray(hp + nrm * 1e-3f, sdir), lightDist);
+        if (P.useBVH) inShadow = trace_any<MT, COUNT>(S, make_ray(hp + nrm * 1e-3f, sdir), lightDist, tl);
         else          inShadow = scan_any<MT>(S, make_ray(hp + nrm * 1e-5f, sdir), lightDist);
+        RT_TALLY(0, 1); RT_TALLY(2, 1); RT_TALLY(7, inShadow ? 1 : 0);
 
         V3 pc = phong(hp, nrm, ray.d, lpos, lcol, m);
         if (inShadow) pc = pc * 0.3f;
@@ -219,9 +231,12 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
 // this rank's tiles); a warp covers an 8x4 pixel block for ray coherence.
 // world == 1 writes row-major W*H; world > 1 writes the compact tile-major shard.
 // ---------------------------------------------------------------------------
-template <bool MT>
+template <bool MT, bool COUNT>
 __global__ void __launch_bounds__(RT_TILE_W * RT_TILE_H)
-render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __restrict__ ids) {
+render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __restrict__ ids,
+              unsigned long long* __restrict__ tally) {
+    Tally tl;
+    if (COUNT) { for (int i = 0; i < 8; ++i) tl.v[i] = 0; }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int lx = ((warp & 3) << 3) + (lane & 7);
     const int ly = ((warp >> 2) << 2) + (lane >> 3);
@@ -232,7 +247,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         const bool inside = x < P.W && y < P.H;
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         int id = -1;
-        if (inside) c = shade_pixel<MT>(S, P, x, y, id);
+        if (inside) c = shade_pixel<MT, COUNT>(S, P, x, y, id, tl);
         if (P.shardWorld == 1) {
             if (inside) {
                 const size_t o = (size_t)y * (size_t)P.W + (size_t)x;
@@ -243,6 +258,13 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
             const size_t o = (size_t)t * (RT_TILE_W * RT_TILE_H) + (size_t)(ly * RT_TILE_W + lx);
             out[o] = c;
             if (P.writeIds) ids[o] = id;
+        }
+    }
+    if (COUNT) {
+        for (int i = 0; i < 8; ++i) {
+            unsigned long long v = tl.v[i];
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && v) atomicAdd(tally + i, v);
         }
     }
 }

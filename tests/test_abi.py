@@ -1,0 +1,67 @@
+"""CPU: the C-ABI library builds for sm_100a, loads, and exports every symbol include/rt_api.h
+declares; the wire-format mirrors have the reference's std430 sizes; without a GPU the library
+fails loudly (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "rt_api.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rt_[a-z_]+)\s*\(", text)))
+
+
+def test_header_and_binding_agree(rt):
+    assert _declared() == sorted(rt.API_SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol(rt):
+    L = rt.lib()
+    for name in _declared():
+        assert hasattr(L, name), name
+    assert b"sm_100a" in L.rt_build_info()
+
+
+def test_library_contains_sm100a_code(rt):
+    out = subprocess.run(["cuobjdump", "-lelf", rt.lib_path()], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    assert "sm_100a" in out.stdout
+
+
+def test_wire_format_sizes(rt):
+    assert rt.LIGHT_DTYPE.itemsize == 32 and rt.CAMERA_DTYPE.itemsize == 80
+    assert rt.SHAPE_DTYPE.itemsize == 192 and rt.NODE_DTYPE.itemsize == 48
+    assert C.sizeof(rt.Params) == 24
+
+
+def test_flat_header_compiles_as_c():
+    src = '#include "rt_api.h"\nint main(void){return sizeof(rt_flat_shape)==192?0:1;}\n'
+    r = subprocess.run(["gcc", "-std=c11", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-x", "c", "-", "-o", "/dev/null"],
+                       input=src, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
+def test_no_cpu_fallback(rt):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(rt.RtError) as e:
+        rt.RayTracer(64, 48)
+    assert e.value.code == -2       # RT_ERR_CUDA
+
+
+def test_product_does_not_reference_oracle():
+    """The shipped path must never import, link or call anything under oracle/."""
+    pkg = os.path.join(ROOT, "opengl-ray-tracer_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "oracle_py" not in text and "liboracle" not in text and "oracle_rt" not in text, f

