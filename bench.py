@@ -1,0 +1,419 @@
+#!/usr/bin/env python3
+"""bench.py — the reference's headline metric (Mrays/s, frames/s on the car scene) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one frame of the hot path (primary ray -> BVH traversal -> closest hit -> shadow ray ->
+Phong/Fresnel -> reflection bounces) over the whole image.  Workload: BASELINE.json configs[2]/[1],
+the car scene (4022 triangles + 100 spheres; synthetic stand-in mesh, the .obj is absent upstream)
+at 3840x2160, defaults maxBounces=3 useBVH=1 useFresnel=0 useMollerTrumbore=0, tile-sharded over
+the N ranks with an NCCL gather to rank 0 (strong scaling: the frame is fixed).  At N=1 the 800x600
+frame of configs[1] is measured too and reported under "extra".
+
+  value     Mrays/s with the scene resident in HBM: rays of the REFERENCE algorithm for this frame
+            (oracle-counted constants in tests/golden/workloads.json, cross-checked against the CUDA
+            path's own counter) / device time of render (+ gather + untile when N > 1), CUDA events,
+            max over ranks, L2 flushed between steps.
+  e2e       same metric through the C ABI with HOST buffers: rt_upload_scene (pinned staging, H2D,
+            repack) + render + D2H of the rgba32f frame inside the timed region.
+  roofline  algorithmic bytes of the reference traversal per launch / render-kernel time vs the
+            measured HBM peak (the scene is L1/L2 resident, so this is a normalising figure).
+  cpu_baseline  the reference shader compiled as C++ (oracle/_ref) or the oracle port, on the host
+            cores, on a bounded row sample of the same frame (N=1, rank 0 only).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scene", default="car")
+    ap.add_argument("--width", type=int, default=3840)
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--mt", type=int, default=0)
+    ap.add_argument("--fresnel", type=int, default=0)
+    ap.add_argument("--bounces", type=int, default=3)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (core-seconds are bounded by a row sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true")
+    return ap.parse_args()
+
+
+def workload_constants(scene, W, H, mt, fresnel, bounces):
+    path = os.path.join(ROOT, "tests", "golden", "workloads.json")
+    key = "%s_%dx%d_mt%d_fr%d_b%d" % (scene, W, H, mt, fresnel, bounces)
+    try:
+        return json.load(open(path)).get(key)
+    except OSError:
+        return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU legs (the ONLY place bench.py touches oracle/): cpu_baseline and --impl reference
+# ---------------------------------------------------------------------------------------------
+def cpu_sample_plan(rt, O, sc, params, W, H, budget_s, threads):
+    """Choose a row stride so that one sample frame costs about budget_s seconds of wall time."""
+    probe_step = max(1, H // 16)
+    t0 = time.perf_counter()
+    O.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H, threads=threads,
+             row_step=probe_step, row_phase=probe_step // 2, want_counters=False)
+    dt = max(time.perf_counter() - t0, 1e-4)
+    rows_probe = len(range(probe_step // 2, H, probe_step))
+    per_row = dt / rows_probe
+    rows = int(min(H, max(8, budget_s / per_row)))
+    step = max(1, H // rows)
+    return step, step // 2
+
+
+_RAYS_CACHE = {}
+
+
+def cpu_render_timed(O, sc, params, W, H, threads, step, phase, use_ref):
+    """Time one sample frame on the host cores; returns (seconds, rays in the sampled rows)."""
+    args = (sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H)
+    key = (W, H, step, phase)
+    if key not in _RAYS_CACHE:      # rays in exactly these rows, from the oracle's counters (untimed, once)
+        _RAYS_CACHE[key] = O.render(*args, threads=threads, row_step=step, row_phase=phase)[3]["rays"]
+    t0 = time.perf_counter()
+    if use_ref:
+        O.ref_render(*args, threads=threads, row_step=step, row_phase=phase)
+    else:
+        O.render(*args, threads=threads, row_step=step, row_phase=phase, want_counters=False)
+    return time.perf_counter() - t0, _RAYS_CACHE[key]
+
+
+def cpu_baseline(rt, sc, params, W, H, budget_s, repeats=1):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as O
+    O.build()
+    threads = os.cpu_count() or 1
+    use_ref = O.ref_lib() is not None
+    step, phase = cpu_sample_plan(rt, O, sc, params, W, H, budget_s, threads)
+    best, rays = None, 0
+    for _ in range(repeats):
+        dt, rays = cpu_render_timed(O, sc, params, W, H, threads, step, phase, use_ref)
+        best = dt if best is None else min(best, dt)
+    rows = len(range(phase, H, step))
+    return {"value": rays / best / 1e6, "unit": "Mrays/s", "cores": threads,
+            "kind": "reference" if use_ref else "port",
+            "sample": "rows y%%%d==%d (%d of %d rows, %d rays) of the %dx%d frame, %.2f s, %s" %
+                      (step, phase, rows, H, rays, W, H, best,
+                       "reference gpu_shader.comp compiled as C++ (oracle/_ref)" if use_ref else "oracle port (oracle_rt.cpp)"),
+            "ms_per_frame_extrapolated": best * 1e3 * H / rows}, (step, phase, use_ref, threads)
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's own CPU implementation of the path (its shader compiled as
+    C++ when oracle/_ref travelled with the snapshot, else the oracle port), all host threads,
+    each step a bounded row sample of the same frame."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import rtload
+    rt = rtload.load()
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as O
+    O.build()
+    W, H = args.width, args.height
+    sc = rt.Scene(args.scene, W, H)
+    params = rt.make_params(W, H, maxBounces=args.bounces, useFresnel=bool(args.fresnel), useMollerTrumbore=bool(args.mt))
+    threads = os.cpu_count() or 1
+    use_ref = O.ref_lib() is not None
+    total = max(1, args.steps + args.warmup)
+    step, phase = cpu_sample_plan(rt, O, sc, params, W, H, min(args.cpu_seconds, 120.0 / total), threads)
+    for _ in range(args.warmup):
+        cpu_render_timed(O, sc, params, W, H, threads, step, phase, use_ref)
+    times, rays = [], 0
+    for _ in range(args.steps):
+        dt, rays = cpu_render_timed(O, sc, params, W, H, threads, step, phase, use_ref)
+        times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    value = rays / (ms / 1e3) / 1e6
+    rows = len(range(phase, H, step))
+    kind = "reference" if use_ref else "port"
+    sample = "rows y%%%d==%d (%d of %d rows, %d rays/step) of the %s %dx%d frame" % (step, phase, rows, H, rays, args.scene, W, H)
+    print(json.dumps({
+        "impl": "reference", "metric": "Mrays/s (car scene)", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, sample=sample),
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "fps_extrapolated": 1e3 / (ms * H / rows),
+        "note": "reference GLSL through llvmpipe/GL: unavailable on this box; this is the shader's arithmetic on the host cores",
+    }))
+
+
+def workload_config(args, **more):
+    cfg = {"workload": "%s scene %dx%d, maxBounces=%d useBVH=1 useFresnel=%d useMollerTrumbore=%d "
+                       "(BASELINE.json configs[2]; synthetic stand-in mesh, same primitive counts)" %
+                       (args.scene, args.width, args.height, args.bounces, args.fresnel, args.mt),
+           "scene": args.scene, "width": args.width, "height": args.height,
+           "parallelism": "tiles%d" % args.gpus, "tile": "32x8 interleaved", "l2": "flushed between steps (256 MiB write)"}
+    cfg.update(more)
+    return cfg
+
+
+# ---------------------------------------------------------------------------------------------
+# The B200 arm
+# ---------------------------------------------------------------------------------------------
+def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, flush):
+    """Device-timed frames with the scene resident.  Returns per-rank mean ms (total, render, gather)."""
+    px = tr.shard_pixels()
+    shard = torch.empty((px, 4), dtype=torch.float32, device="cuda")
+    full = torch.empty((H, W, 4), dtype=torch.float32, device="cuda") if (rank == 0 and world > 1) else None
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+
+    def frame(timed):
+        e0, e1, e2 = ev(), ev(), ev()
+        if flush is not None:
+            flush.zero_()                       # evict the scene and the image from L2 (untimed)
+        e0.record()
+        tr.render_device(params, shard.data_ptr())
+        e1.record()
+        if world > 1:
+            got = rt.shard.gather_shards(shard, rank, world)
+            if rank == 0:
+                tr.untile(got.data_ptr(), world, full.data_ptr())
+        e2.record()
+        return (e0, e1, e2) if timed else None
+
+    for _ in range(warmup):
+        frame(False)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    evs = [frame(True) for _ in range(steps)]
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    tot = sum(a.elapsed_time(c) for a, _, c in evs) / steps
+    ren = sum(a.elapsed_time(b) for a, b, _ in evs) / steps
+    return tot, ren, tot - ren, (full if full is not None else shard)
+
+
+def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup):
+    """End to end through the C ABI from HOST buffers: upload (pinned staging + H2D + repack), render,
+    (gather + untile), D2H of the rgba32f frame into pinned host memory.  Wall clock, sync both sides."""
+    light, cam, shapes, nodes, idx = sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices
+    px = tr.shard_pixels()
+    if world == 1:
+        host = torch.empty((H * W, 4), dtype=torch.float32, pin_memory=True).numpy()
+    else:
+        shard = torch.empty((px, 4), dtype=torch.float32, device="cuda")
+        full = torch.empty((H, W, 4), dtype=torch.float32, device="cuda") if rank == 0 else None
+        host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
+
+    def frame():
+        tr.upload_scene(light, cam, shapes, nodes, idx)
+        if world == 1:
+            tr.render(params, want_ids=False, out=host)
+        else:
+            tr.render_device(params, shard.data_ptr())
+            got = rt.shard.gather_shards(shard, rank, world)
+            if rank == 0:
+                tr.untile(got.data_ptr(), world, full.data_ptr())
+                host.copy_(full, non_blocking=True)
+            torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        frame()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        frame()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    # bytes that cross PCIe per step on every rank / on rank 0
+    h2d = int(shapes.nbytes + nodes.nbytes + len(nodes) * 12 + len(idx) * 4)     # raw scene + visit-order maps
+    d2h = int(W * H * 16)
+    return ms, h2d, d2h
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+    import torch
+    import torch.distributed as dist
+    import rtload
+    rt = rtload.load()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the hot path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W, H = args.width, args.height
+    sc = rt.Scene(args.scene, W, H)
+    params = rt.make_params(W, H, maxBounces=args.bounces, useFresnel=bool(args.fresnel), useMollerTrumbore=bool(args.mt))
+    consts = workload_constants(args.scene, W, H, args.mt, args.fresnel, args.bounces)
+
+    stream = torch.cuda.Stream()
+    out = {}
+    with torch.cuda.stream(stream):
+        tr = rt.RayTracer(W, H, device=local, flags=0)
+        tr.set_stream(stream.cuda_stream)
+        tr.set_shard(rank, world)
+        tr.upload(sc)
+        # the CUDA path's own ray count for this rank's tiles (untimed counting launch)
+        mine = tr.render_stats(params)
+        rays_t = torch.tensor([mine["rays"], mine["node_visits"], mine["prim_tests"]], dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.all_reduce(rays_t)
+        rays_gpu, nodes_gpu, tests_gpu = (int(x) for x in rays_t.tolist())
+        rays = consts["rays"] if consts else rays_gpu
+        rays_match = (consts is None) or (rays_gpu == consts["rays"])
+
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        clocks = ClockSampler(local)
+        launches0 = tr.launch_count()
+        if rank == 0:
+            clocks.start()
+        tot, ren, gat, _ = time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush)
+        clk = clocks.stop() if rank == 0 else None
+        launches = (tr.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
+        t = torch.tensor([tot, ren, gat], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tot, ren, gat = t.tolist()
+        e2e_ms, h2d, d2h = time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, max(3, args.steps // 3), 3)
+        t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = t.item()
+
+        extra = {}
+        if world == 1 and not args.no_extra and (W, H) != (800, 600):
+            # BASELINE.json configs[1]: the same scene at the reference's own 800x600
+            sc2 = rt.Scene(args.scene, 800, 600)
+            p2 = rt.make_params(800, 600, maxBounces=args.bounces, useFresnel=bool(args.fresnel), useMollerTrumbore=bool(args.mt))
+            tr2 = rt.RayTracer(800, 600, device=local, flags=0)
+            tr2.set_stream(stream.cuda_stream)
+            tr2.upload(sc2)
+            c2 = workload_constants(args.scene, 800, 600, args.mt, args.fresnel, args.bounces)
+            r2 = tr2.render_stats(p2)["rays"]
+            tot2, ren2, _, _ = time_frames(torch, dist, rt, tr2, p2, 800, 600, 0, 1, args.steps, args.warmup, flush)
+            e2, _, _ = time_e2e(torch, dist, rt, tr2, sc2, p2, 800, 600, 0, 1, max(3, args.steps // 3), 3)
+            extra["car_800x600"] = {"workload": "BASELINE.json configs[1]", "Mrays_per_s": (c2["rays"] if c2 else r2) / ren2 / 1e3,
+                                    "ms_per_frame": tot2, "fps": 1e3 / tot2, "e2e_ms": e2, "e2e_fps": 1e3 / e2,
+                                    "rays": r2, "rays_match_oracle": (c2 is None) or r2 == c2["rays"]}
+            if c2:
+                extra["car_800x600"]["alg_GBps"] = c2["alg_bytes"] / ren2 / 1e6
+            tr2.close()
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
+        alg = (consts["alg_bytes"] / world) if consts else None        # per launch: one rank's share of the frame
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("render_kernel_dram_bytes_per_launch")
+        except (OSError, ValueError):
+            pass
+        achieved = alg / ren / 1e6 if alg else None
+        line = {
+            "metric": "Mrays/s (car scene)", "value": rays / tot / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": tot, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(args),
+            "fps": 1e3 / tot, "render_ms": ren, "gather_untile_ms": gat,
+            "rays_per_frame": rays, "rays_counted_by_kernel": rays_gpu, "rays_match_oracle": rays_match,
+            "kernel_work": {"node_visits": nodes_gpu, "prim_tests": tests_gpu,
+                            "reference_node_visits": consts["node_visits"] if consts else None,
+                            "reference_prim_tests": sum(consts["tests"]) if consts else None},
+            "e2e": {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                         "kernel": "rt::render_kernel", "kernel_ms": ren,
+                         "note": "algorithmic bytes of the reference's unculled traversal (oracle-counted) / render time; "
+                                 "the scene (~1 MB) is L1/L2-resident, DRAM sees the image write only"},
+            "extra": extra,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"], _ = cpu_baseline(rt, sc, params, W, H, args.cpu_seconds)
+        print(json.dumps(line))
+    tr.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

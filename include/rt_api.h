@@ -134,6 +134,10 @@ int rt_present(rt_ctx* ctx, const float* dev_rgba, uint8_t* dev_rgba8_out, int64
 
 /* ---- plumbing --------------------------------------------------------------*/
 void* rt_stream(rt_ctx* ctx);                 /* cudaStream_t of the context     */
+/* Run all further work of this context on a caller-owned cudaStream_t (e.g. the
+ * stream a framework times with its own events); NULL restores the internal one.
+ * The previous stream is drained first. */
+int   rt_set_stream(rt_ctx* ctx, void* cuda_stream);
 int   rt_synchronize(rt_ctx* ctx);
 float* rt_device_image(rt_ctx* ctx);          /* internal float4 image           */
 /* CUDA-event timings of the last calls, milliseconds (-1 = not measured yet):

@@ -54,7 +54,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_device", "rt_render_stats", "rt_untile", "rt_present", "rt_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_device", "rt_render_stats", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -86,6 +86,7 @@ def lib():
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
     L.rt_stream.argtypes = [vp]; L.rt_stream.restype = vp
+    L.rt_set_stream.argtypes = [vp, vp]; L.rt_set_stream.restype = ip
     L.rt_synchronize.argtypes = [vp]; L.rt_synchronize.restype = ip
     L.rt_device_image.argtypes = [vp]; L.rt_device_image.restype = vp
     L.rt_last_timings.argtypes = [vp, fp]; L.rt_last_timings.restype = ip
@@ -283,6 +284,10 @@ class RayTracer:
 
     def stream(self):
         return self._L.rt_stream(self._c)
+
+    def set_stream(self, cuda_stream):
+        """Share a caller-owned stream (int handle, e.g. torch.cuda.current_stream().cuda_stream)."""
+        self._chk(self._L.rt_set_stream(self._c, C.c_void_p(cuda_stream) if cuda_stream else None))
 
     def synchronize(self):
         self._chk(self._L.rt_synchronize(self._c))

@@ -52,6 +52,7 @@ struct rt_ctx {
     int device = 0, W = 0, H = 0;
     unsigned flags = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t ownStream = nullptr;
     cudaEvent_t ev[8] = {};          // h2d0,h2d1, repack0,repack1, render0,render1, d2h0,d2h1
     cudaEvent_t copyDone = nullptr;  // last H2D out of the pinned shadows has finished
     bool copyPending = false;
@@ -263,6 +264,7 @@ int rt_create(rt_ctx** out, int width, int height, int device, unsigned flags) {
     for (auto& e : c->ev) if (cudaEventCreate(&e) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     if (cudaEventCreateWithFlags(&c->copyDone, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     cudaDeviceGetAttribute(&c->smCount, cudaDevAttrMultiProcessorCount, device);
+    c->ownStream = c->stream;
     *out = c;
     return RT_OK;
 }
@@ -278,7 +280,8 @@ void rt_destroy(rt_ctx* c) {
     c->image.release(); c->ids.release(); c->tally.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->copyDone) cudaEventDestroy(c->copyDone);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (!c->ownStream) c->ownStream = c->stream;      // rt_create failed half-way
+    if (c->ownStream) cudaStreamDestroy(c->ownStream);
     delete c;
 }
 
@@ -444,6 +447,14 @@ int rt_present(rt_ctx* c, const float* dev_rgba, uint8_t* dev_rgba8_out, int64_t
 }
 
 void* rt_stream(rt_ctx* c) { return c ? (void*)c->stream : nullptr; }
+int rt_set_stream(rt_ctx* c, void* s) {
+    if (!c) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->copyPending = false;
+    c->stream = s ? static_cast<cudaStream_t>(s) : c->ownStream;
+    return RT_OK;
+}
 int rt_synchronize(rt_ctx* c) {
     if (!c) return RT_ERR_ARG;
     CU(c, cudaStreamSynchronize(c->stream));
