@@ -79,10 +79,13 @@ struct rt_ctx {
     // pending work, flushed at render time so per-shape updates coalesce (main.cpp:981-992)
     int shapeLo = 0, shapeHi = 0;     // dirty raw-shape range [lo,hi)
     bool nodesDirty = false, topoDirty = false;
+    bool boxesFinite = false;
 
     // output
     DevBuf<float4> image; DevBuf<int> ids;
     DevBuf<unsigned long long> tally;
+    DevBuf<unsigned int> queue;       // work-stealing counter of K1
+    int gridBlocks[4] = {0, 0, 0, 0}; // persistent grid per kernel variant
     int shardRank = 0, shardWorld = 1;
 };
 
@@ -164,12 +167,20 @@ int build_visit_order(rt_ctx* c) {
         const rt_flat_node& x = nd[order[(size_t)k]];
         c->hOrder.p[k] = order[(size_t)k];
         if (x.leftChild == -1) {
-            c->hLinkCnt.p[k] = make_int2((int)slot, x.numShapes);
+            if (x.numShapes > RT_LEAF_COUNT_MASK) return fail(c, RT_ERR_SCENE, "leaf with more than 2^28 shapes");
+            const int first = (int)slot;
+            int nTri = 0, nSph = 0;
             for (int i = 0; i < x.numShapes; ++i) {
                 const int s = c->indices[(size_t)x.startShapeIdx + (size_t)i];
                 if (s < 0 || s >= c->nShapes) return fail(c, RT_ERR_SCENE, "bvhIndices entry outside the shape buffer");
+                const int type = c->hShapes.p[s].type;
+                nTri += type == RT_SHAPE_TRIANGLE; nSph += type == RT_SHAPE_SPHERE;
                 c->hPshape.p[slot++] = s;
             }
+            // type-homogeneous leaves skip the per-primitive type load on the device
+            const int kind = x.numShapes == 0 ? RT_LEAF_MIXED : nTri == x.numShapes ? RT_LEAF_TRIANGLES
+                           : nSph == x.numShapes ? RT_LEAF_SPHERES : RT_LEAF_MIXED;
+            c->hLinkCnt.p[k] = make_int2(first, x.numShapes | (kind << RT_LEAF_KIND_SHIFT));
         } else {
             c->hLinkCnt.p[k] = make_int2(k + size[(size_t)k], -1);
         }
@@ -200,8 +211,9 @@ int flush_scene(rt_ctx* c) {
         CU(c, c->dOrder.reserve((size_t)c->nDfs)); CU(c, c->dLinkCnt.reserve((size_t)c->nDfs));
         CU(c, c->dPshape.reserve((size_t)c->nPrims));
         CU(c, c->dNodesT.reserve((size_t)c->nDfs * 2));
-        CU(c, c->q0.reserve((size_t)c->nPrims)); CU(c, c->q1.reserve((size_t)c->nPrims));
-        CU(c, c->q2.reserve((size_t)c->nPrims)); CU(c, c->q3.reserve((size_t)c->nPrims));
+        // +4 slots of padding: the batched triangle loop loads q0[s..s+3] before masking by the leaf end
+        CU(c, c->q0.reserve((size_t)c->nPrims + 4)); CU(c, c->q1.reserve((size_t)c->nPrims + 4));
+        CU(c, c->q2.reserve((size_t)c->nPrims + 4)); CU(c, c->q3.reserve((size_t)c->nPrims + 4));
         CU(c, c->ptype.reserve((size_t)c->nPrims));
         if (c->nDfs > 0) {
             CU(c, cudaMemcpyAsync(c->dOrder.p, c->hOrder.p, (size_t)c->nDfs * sizeof(int), cudaMemcpyHostToDevice, c->stream));
@@ -242,6 +254,10 @@ int set_nodes(rt_ctx* c, const void* nodes, int nNodes) {
     CU(c, c->hNodes.reserve((size_t)nNodes, 0));
     if (nNodes > 0) std::memcpy(c->hNodes.p, in, (size_t)nNodes * sizeof(rt_flat_node));
     c->nNodes = nNodes;
+    c->boxesFinite = true;            // NaN-free slab fast path needs |bound| <= 1e37 everywhere
+    for (int i = 0; i < nNodes && c->boxesFinite; ++i)
+        for (int k = 0; k < 3; ++k)
+            if (!(std::fabs(in[i].boundsMin[k]) <= RT_SAFE_COORD) || !(std::fabs(in[i].boundsMax[k]) <= RT_SAFE_COORD)) c->boxesFinite = false;
     c->nodesDirty = true;
     if (!sameTopo) c->topoDirty = true;
     return RT_OK;
@@ -277,7 +293,7 @@ void rt_destroy(rt_ctx* c) {
     c->hOrder.release(); c->dOrder.release(); c->hLinkCnt.release(); c->dLinkCnt.release();
     c->hPshape.release(); c->dPshape.release(); c->dNodesT.release();
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
-    c->image.release(); c->ids.release(); c->tally.release();
+    c->image.release(); c->ids.release(); c->tally.release(); c->queue.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->copyDone) cudaEventDestroy(c->copyDone);
     if (!c->ownStream) c->ownStream = c->stream;      // rt_create failed half-way
@@ -321,6 +337,10 @@ int rt_update_shapes(rt_ctx* c, int first, int count, const void* shapes) {
     if (first < 0 || count < 0 || first + count > c->nShapes) return fail(c, RT_ERR_ARG, "shape range outside the uploaded buffer");
     if (count == 0) return RT_OK;
     wait_copies(c);
+    {   // a type change invalidates the leaf kind tags: rebuild the visit-order maps
+        const rt_flat_shape* in = static_cast<const rt_flat_shape*>(shapes);
+        for (int i = 0; i < count; ++i) if (in[i].type != c->hShapes.p[first + i].type) { c->topoDirty = true; break; }
+    }
     std::memcpy(c->hShapes.p + first, shapes, (size_t)count * sizeof(rt_flat_shape));
     if (c->shapeHi <= c->shapeLo) { c->shapeLo = first; c->shapeHi = first + count; }
     else { if (first < c->shapeLo) c->shapeLo = first; if (first + count > c->shapeHi) c->shapeHi = first + count; }
@@ -372,7 +392,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     DeviceScene S;
     S.nodes = c->dNodesT.p; S.q0 = c->q0.p; S.q1 = c->q1.p; S.q2 = c->q2.p; S.q3 = c->q3.p;
     S.ptype = c->ptype.p; S.pshape = c->dPshape.p; S.shapes = c->dShapes.p;
-    S.nNodes = c->nDfs; S.nPrims = c->nPrims; S.nShapes = c->nShapes;
+    S.nNodes = c->nDfs; S.nPrims = c->nPrims; S.nShapes = c->nShapes; S.boxesFinite = c->boxesFinite ? 1 : 0;
 
     FrameParams F;
     std::memcpy(F.camP, c->cam.Position, 12); std::memcpy(F.camF, c->cam.Front, 12);
@@ -389,16 +409,29 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
 
     cudaEventRecord(c->ev[4], c->stream);
     if (F.nTilesMine > 0) {
-        const int grid = F.nTilesMine;
-        const dim3 blk(RT_TILE_W * RT_TILE_H);
+        const int variant = (F.useMT ? 1 : 0) + (count ? 2 : 0);
+        if (c->gridBlocks[variant] == 0) {       // persistent grid: fill every SM once
+            int perSM = 0;
+            const void* fn = variant == 0 ? (const void*)render_kernel<false, false> : variant == 1 ? (const void*)render_kernel<true, false>
+                           : variant == 2 ? (const void*)render_kernel<false, true> : (const void*)render_kernel<true, true>;
+            CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, RT_BLOCK_THREADS, 0));
+            c->gridBlocks[variant] = c->smCount * (perSM > 0 ? perSM : 1);
+        }
+        const int items = F.nTilesMine * RT_WARPS_PER_TILE;
+        const int needed = (items + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
+        const int grid = needed < c->gridBlocks[variant] ? needed : c->gridBlocks[variant];
+        CU(c, c->queue.reserve(1));
+        CU(c, cudaMemsetAsync(c->queue.p, 0, sizeof(unsigned int), c->stream));
+        const dim3 blk(RT_BLOCK_THREADS);
         float4* o4 = reinterpret_cast<float4*>(dev_rgba);
         unsigned long long* tl = c->tally.p;
+        unsigned int* q = c->queue.p;
         if (count) {
-            if (F.useMT) render_kernel<true, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl);
-            else         render_kernel<false, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl);
+            if (F.useMT) render_kernel<true, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl, q);
+            else         render_kernel<false, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl, q);
         } else {
-            if (F.useMT) render_kernel<true, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr);
-            else         render_kernel<false, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr);
+            if (F.useMT) render_kernel<true, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr, q);
+            else         render_kernel<false, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr, q);
         }
         c->launches++;
     }
@@ -472,6 +505,6 @@ int rt_last_timings(rt_ctx* c, float out_ms[4]) {
     return RT_OK;
 }
 int64_t rt_launch_count(const rt_ctx* c) { return c ? c->launches : 0; }
-const char* rt_build_info(void) { return "librt_b200 sm_100a fmad=off prec-div prec-sqrt tile=32x8"; }
+const char* rt_build_info(void) { return "librt_b200 sm_100a fmad=off prec-div prec-sqrt tile=32x8 persistent-warps"; }
 
 }  // extern "C"

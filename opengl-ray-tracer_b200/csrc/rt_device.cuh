@@ -45,7 +45,14 @@ struct DeviceScene {
     int nNodes;
     int nPrims;
     int nShapes;
+    int boxesFinite;      // every node bound is finite: the NaN-free slab fast path is legal
 };
+
+// Leaf "kind" tag kept in bits 28..30 of a leaf's count word (host-computed at upload):
+// all primitives of the leaf have one type, so the per-primitive type load is skipped.
+#define RT_LEAF_COUNT_MASK 0x0fffffff
+#define RT_LEAF_KIND_SHIFT 28
+enum { RT_LEAF_MIXED = 0, RT_LEAF_TRIANGLES = 1, RT_LEAF_SPHERES = 2 };
 
 struct FrameParams {
     float camP[3], camF[3], camU[3], camR[3];
@@ -90,11 +97,17 @@ struct Ray {
     V3 o, d;
     V3 inv;        // 1/d, hoisted out of the per-node slab test (gpu_shader.comp:365)
     float aa;      // dot(d,d), hoisted out of the sphere test (:250)
+    bool fast;     // origin and 1/d all finite: (bound - o) * inv can never be NaN for finite bounds
 };
-__device__ __forceinline__ Ray make_ray(V3 o, V3 d) {
+__device__ __forceinline__ bool bounded3(V3 v, float lim) {      // false for NaN / inf
+    return fabsf(v.x) <= lim && fabsf(v.y) <= lim && fabsf(v.z) <= lim;
+}
+#define RT_SAFE_COORD 1e37f   // |bound|,|origin| <= 1e37: (bound - origin) cannot overflow to inf
+__device__ __forceinline__ Ray make_ray(V3 o, V3 d, bool boxesFinite) {
     Ray r; r.o = o; r.d = d;
     r.inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     r.aa = dot3(d, d);
+    r.fast = boxesFinite && bounded3(o, RT_SAFE_COORD) && bounded3(r.inv, 3.402823466e38f);
     return r;
 }
 
@@ -139,10 +152,14 @@ __device__ __forceinline__ Prim prim_from_shape(const rt_flat_shape* __restrict_
 __device__ __forceinline__ bool plane_stage(float4 q0, const Ray& r, V3& hp) {
     V3 n = xyz(q0);
     float np = dot3(n, r.d);
-    if (np == 0.0f) return false;
-    float t = -(q0.w + dot3(n, r.o)) / np;
-    if (!(t > 0.0f)) return false;
-    if (np <= 0.0f) return false;          // OUTER
+    // INNER needs np > 0 and t > 0 (np == 0 -> NONE, np < 0 -> OUTER/NONE, NaN -> NONE).
+    if (!(np > 0.0f)) return false;
+    // With np > 0 the quotient t = num/np can only be > 0 if num > 0: the IEEE division is
+    // skipped for every primitive behind the ray without changing any decision.
+    float num = -(q0.w + dot3(n, r.o));
+    if (!(num > 0.0f)) return false;
+    float t = num / np;
+    if (!(t > 0.0f)) return false;         // underflow to 0
     hp = r.o + t * r.d;
     return true;
 }
@@ -174,8 +191,14 @@ __device__ __forceinline__ bool bary_stage2(float4 q1, float4 q2, float4 q3, V3 
     float d20 = dot3(toPoint, e1);
     float d21 = dot3(toPoint, e2);
     float denom = d00 * d11 - d01 * d01;
-    float v = (d11 * d20 - d01 * d21) / denom;
-    float w = (d00 * d21 - d01 * d20) / denom;
+    float X = d11 * d20 - d01 * d21;
+    float Y = d00 * d21 - d01 * d20;
+    // Sufficient, exact rejects before the two IEEE divisions: for 0 < denom < 1e30 and
+    // X < -1e-12 the quotient X/denom is a non-zero negative float (|X/denom| > 1e-42), so
+    // v < 0 holds in the shader as well; same for w.  Everything else takes the full path.
+    if (denom > 0.0f && denom < 1e30f && (X < -1e-12f || Y < -1e-12f)) return false;
+    float v = X / denom;
+    float w = Y / denom;
     float u = 1.0f - v - w;
     return !(u < 0.0f || v < 0.0f || w < 0.0f);
 }

@@ -2,6 +2,10 @@
 #pragma once
 #include "rt_device.cuh"
 
+#ifndef RT_BLOCK_THREADS
+#define RT_BLOCK_THREADS 128
+#endif
+
 namespace rt {
 
 // ---------------------------------------------------------------------------
@@ -22,6 +26,17 @@ __device__ __forceinline__ bool slab(const Ray& r, float4 a, float4 b) {
     float t0z = (a.z - r.o.z) * r.inv.z, t1z = (b.z - r.o.z) * r.inv.z;
     float tMin = gmax(gmax(gmin(t0x, t1x), gmin(t0y, t1y)), gmin(t0z, t1z));
     float tMax = gmin(gmin(gmax(t0x, t1x), gmax(t0y, t1y)), gmax(t0z, t1z));
+    return tMax >= tMin && tMax > 0.0f;
+}
+// Same arithmetic with single-instruction FMNMX min/max.  Legal only when no operand can be
+// NaN (Ray::fast): then fminf/fmaxf and the GLSL selects return the same value up to the sign
+// of zero, which the two comparisons below cannot see.
+__device__ __forceinline__ bool slab_fast(const Ray& r, float4 a, float4 b) {
+    float t0x = (a.x - r.o.x) * r.inv.x, t1x = (b.x - r.o.x) * r.inv.x;
+    float t0y = (a.y - r.o.y) * r.inv.y, t1y = (b.y - r.o.y) * r.inv.y;
+    float t0z = (a.z - r.o.z) * r.inv.z, t1z = (b.z - r.o.z) * r.inv.z;
+    float tMin = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+    float tMax = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
     return tMax >= tMin && tMax > 0.0f;
 }
 
@@ -55,63 +70,123 @@ __device__ __forceinline__ bool test_slot(const DeviceScene& S, int s, const Ray
     return false;
 }
 
-// Closest hit (a3).  Visits exactly the reference's node set in the reference's
-// order; dist is distance(ray.start, hit_point) with strict '<' (:410-411).
-template <bool MT, bool COUNT>
-__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, Hit& h, Tally& tl) {
-    h.dist = 1e20f; h.slot = -1; h.p = mk(0.f, 0.f, 0.f);
+// A hit candidate is handed to `sink(slot, hp)`, which returns true to stop the query
+// (any-hit).  Candidates arrive in slot order == the reference's visit order.
+//
+// Triangle leaf, Barycentric mode: the plane stage of four consecutive slots is evaluated
+// as four independent dependency chains (the loads are issued together; the slot arrays
+// are padded so reading past `end` is safe), then the survivors go through the division
+// and the barycentric stage in slot order.
+template <class Sink>
+__device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, const Ray& r, int s0, int end, Sink& sink) {
+    for (int s = s0; s < end; s += 4) {
+        float4 q[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) q[i] = __ldg(S.q0 + s + i);
+        float np[4], num[4];
+        bool pass[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const V3 n = xyz(q[i]);
+            np[i] = dot3(n, r.d);
+            num[i] = -(q[i].w + dot3(n, r.o));
+            pass[i] = (np[i] > 0.0f) && (num[i] > 0.0f) && (s + i < end);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (pass[i]) {
+                const float t = num[i] / np[i];
+                if (t > 0.0f) {
+                    const V3 hp = r.o + t * r.d;
+                    if (bary_stage2(__ldg(S.q1 + s + i), __ldg(S.q2 + s + i), __ldg(S.q3 + s + i), hp))
+                        if (sink(s + i, hp)) return true;
+                }
+            }
+        }
+    }
+    return false;
+}
+
+template <bool MT, class Sink>
+__device__ __forceinline__ bool leaf_generic(const DeviceScene& S, const Ray& r, int s0, int end, Sink& sink) {
+    for (int s = s0; s < end; ++s) {
+        V3 hp;
+        if (test_slot<MT>(S, s, r, hp))
+            if (sink(s, hp)) return true;
+    }
+    return false;
+}
+
+template <bool MT, class Sink>
+__device__ __forceinline__ bool leaf_spheres(const DeviceScene& S, const Ray& r, int s0, int end, Sink& sink) {
+    for (int s = s0; s < end; ++s) {
+        V3 hp;
+        if (hit_sphere(__ldg(S.q0 + s), r, hp))
+            if (sink(s, hp)) return true;
+    }
+    return false;
+}
+
+// Stackless walk of the threaded BVH.  Visits exactly the reference's node set in the
+// reference's order (gpu_shader.comp:390-427) unless the sink stops it.
+template <bool MT, bool COUNT, class Sink>
+__device__ __forceinline__ void walk(const DeviceScene& S, const Ray& r, Sink& sink, Tally& tl) {
     int k = 0;
     const int n = S.nNodes;
     while (k < n) {
         const float4 a = __ldg(S.nodes + 2 * k);
         const float4 b = __ldg(S.nodes + 2 * k + 1);
-        const int cnt = __float_as_int(b.w);
+        const int cw = __float_as_int(b.w);
         const int lnk = __float_as_int(a.w);
         RT_TALLY(4, 1);
-        if (!slab(r, a, b)) { k = cnt < 0 ? lnk : k + 1; continue; }
-        if (cnt >= 0) {
+        const bool hit = r.fast ? slab_fast(r, a, b) : slab(r, a, b);
+        if (!hit) { k = cw < 0 ? lnk : k + 1; continue; }
+        if (cw >= 0) {
+            const int cnt = cw & RT_LEAF_COUNT_MASK, kind = cw >> RT_LEAF_KIND_SHIFT;
             const int end = lnk + cnt;
             RT_TALLY(5, cnt);
-            for (int s = lnk; s < end; ++s) {
-                V3 hp;
-                if (test_slot<MT>(S, s, r, hp)) {
-                    float dist = distance3(r.o, hp);
-                    if (dist < h.dist) { h.dist = dist; h.slot = s; h.p = hp; }
-                }
-            }
+            bool stop;
+            if (!MT && kind == RT_LEAF_TRIANGLES) stop = leaf_triangles_bary(S, r, lnk, end, sink);
+            else if (kind == RT_LEAF_SPHERES)     stop = leaf_spheres<MT>(S, r, lnk, end, sink);
+            else                                   stop = leaf_generic<MT>(S, r, lnk, end, sink);
+            if (stop) return;
         }
         ++k;
     }
 }
 
+// Closest hit (a3): dist is distance(ray.start, hit_point) with strict '<' (:410-411).
+struct ClosestSink {
+    const Ray& r; Hit& h;
+    __device__ __forceinline__ bool operator()(int slot, V3 hp) {
+        const float dist = distance3(r.o, hp);
+        if (dist < h.dist) { h.dist = dist; h.slot = slot; h.p = hp; }
+        return false;
+    }
+};
+template <bool MT, bool COUNT>
+__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, Hit& h, Tally& tl) {
+    h.dist = 1e20f; h.slot = -1; h.p = mk(0.f, 0.f, 0.f);
+    ClosestSink sink{r, h};
+    walk<MT, COUNT>(S, r, sink, tl);
+}
+
 // Shadow query (a12): the shader runs a full closest-hit query and then tests
-// hitDist < lightDist; "some INNER hit has dist < lightDist" is the same boolean
-// (the closest hit has the minimum dist), so this returns at the first occluder.
+// hitDist < lightDist; "some INNER hit has dist < 1e20 and dist < lightDist" is the same
+// boolean (the closest hit has the minimum dist), so this stops at the first occluder.
+struct AnySink {
+    const Ray& r; float lightDist; bool found;
+    __device__ __forceinline__ bool operator()(int, V3 hp) {
+        const float dist = distance3(r.o, hp);
+        if (dist < 1e20f && dist < lightDist) { found = true; return true; }
+        return false;
+    }
+};
 template <bool MT, bool COUNT>
 __device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, float lightDist, Tally& tl) {
-    int k = 0;
-    const int n = S.nNodes;
-    while (k < n) {
-        const float4 a = __ldg(S.nodes + 2 * k);
-        const float4 b = __ldg(S.nodes + 2 * k + 1);
-        const int cnt = __float_as_int(b.w);
-        const int lnk = __float_as_int(a.w);
-        RT_TALLY(4, 1);
-        if (!slab(r, a, b)) { k = cnt < 0 ? lnk : k + 1; continue; }
-        if (cnt >= 0) {
-            const int end = lnk + cnt;
-            for (int s = lnk; s < end; ++s) {
-                V3 hp;
-                RT_TALLY(5, 1);
-                if (test_slot<MT>(S, s, r, hp)) {
-                    float dist = distance3(r.o, hp);
-                    if (dist < 1e20f && dist < lightDist) return true;
-                }
-            }
-        }
-        ++k;
-    }
-    return false;
+    AnySink sink{r, lightDist, false};
+    walk<MT, COUNT>(S, r, sink, tl);
+    return sink.found;
 }
 
 // Brute-force twins (a14, useBVH == false): linear scan over the raw shapes.
@@ -178,7 +253,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
     const float ndcY = 1.0f - 2.0f * (float)y / P.resH;
     const V3 camP = mk(P.camP);
     V3 ipp = ((camP + mk(P.camF)) + (ndcX * P.planeW / 2.0f) * mk(P.camR)) + (ndcY * P.planeH / 2.0f) * mk(P.camU);
-    Ray ray = make_ray(camP, normalize3(ipp - camP));
+    Ray ray = make_ray(camP, normalize3(ipp - camP), S.boxesFinite != 0);
     const V3 lpos = mk(P.lightPos), lcol = mk(P.lightCol);
     V3 acc = mk(0.f, 0.f, 0.f), att = mk(1.f, 1.f, 1.f);
     idOut = -1;
@@ -202,8 +277,8 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
         const V3 sdir = normalize3(lpos - hp);
         const float lightDist = distance3(lpos, hp);
         bool inShadow;
-        if (P.useBVH) inShadow = trace_any<MT, COUNT>(S, make_ray(hp + nrm * 1e-3f, sdir), lightDist, tl);
-        else          inShadow = scan_any<MT>(S, make_ray(hp + nrm * 1e-5f, sdir), lightDist);
+        if (P.useBVH) inShadow = trace_any<MT, COUNT>(S, make_ray(hp + nrm * 1e-3f, sdir, S.boxesFinite != 0), lightDist, tl);
+        else          inShadow = scan_any<MT>(S, make_ray(hp + nrm * 1e-5f, sdir, S.boxesFinite != 0), lightDist);
         RT_TALLY(0, 1); RT_TALLY(2, 1); RT_TALLY(7, inShadow ? 1 : 0);
 
         V3 pc = phong(hp, nrm, ray.d, lpos, lcol, m);
@@ -212,7 +287,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
 
         if (!(m.specular > 0.0f)) break;
         const V3 rd = reflect3(ray.d, nrm);
-        ray = make_ray(hp + nrm * 1e-3f, rd);
+        ray = make_ray(hp + nrm * 1e-3f, rd, S.boxesFinite != 0);
         if (P.useFresnel) {
             float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
             fr = gmin(gmax(fr, 0.0f), 0.8f);
@@ -227,27 +302,39 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
 }
 
 // ---------------------------------------------------------------------------
-// K1: render.  One CTA works on RT_TILE_W x RT_TILE_H tiles (grid-stride over
-// this rank's tiles); a warp covers an 8x4 pixel block for ray coherence.
+// K1: render.  Persistent warps with work stealing: the grid is sized to fill the
+// SMs once and every WARP pulls the next 8x4-pixel block from an atomic queue
+// (lane 0 claims, __shfl broadcasts), so a heavy block delays one warp, not a CTA.
+// Work item w: shard tile t = w / 8 of this rank (tile index rank + t*world), warp
+// block b = w % 8 inside the 32x8 tile (4 across, 2 down).
 // world == 1 writes row-major W*H; world > 1 writes the compact tile-major shard.
 // ---------------------------------------------------------------------------
+#define RT_WARPS_PER_TILE ((RT_TILE_W / 8) * (RT_TILE_H / 4))
+
 template <bool MT, bool COUNT>
-__global__ void __launch_bounds__(RT_TILE_W * RT_TILE_H)
+__global__ void __launch_bounds__(RT_BLOCK_THREADS)
 render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __restrict__ ids,
-              unsigned long long* __restrict__ tally) {
+              unsigned long long* __restrict__ tally, unsigned int* __restrict__ queue) {
     Tally tl;
     if (COUNT) { for (int i = 0; i < 8; ++i) tl.v[i] = 0; }
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int lx = ((warp & 3) << 3) + (lane & 7);
-    const int ly = ((warp >> 2) << 2) + (lane >> 3);
-    for (int t = blockIdx.x; t < P.nTilesMine; t += gridDim.x) {
+    const int lane = threadIdx.x & 31;
+    const int nItems = P.nTilesMine * RT_WARPS_PER_TILE;
+    for (;;) {
+        int w = 0;
+        if (lane == 0) w = (int)atomicAdd(queue, 1u);
+        w = __shfl_sync(0xffffffffu, w, 0);
+        if (w >= nItems) break;
+        const int t = w / RT_WARPS_PER_TILE, b = w % RT_WARPS_PER_TILE;
         const int tile = P.shardRank + t * P.shardWorld;
+        const int lx = ((b & 3) << 3) + (lane & 7);
+        const int ly = ((b >> 2) << 2) + (lane >> 3);
         const int x = (tile % P.tilesX) * RT_TILE_W + lx;
         const int y = (tile / P.tilesX) * RT_TILE_H + ly;
         const bool inside = x < P.W && y < P.H;
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         int id = -1;
         if (inside) c = shade_pixel<MT, COUNT>(S, P, x, y, id, tl);
+        __syncwarp();
         if (P.shardWorld == 1) {
             if (inside) {
                 const size_t o = (size_t)y * (size_t)P.W + (size_t)x;
