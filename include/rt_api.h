@@ -120,8 +120,9 @@ int rt_render_device(rt_ctx* ctx, const rt_params* params, float* dev_rgba, int3
 /* Untimed diagnostic render with work counters (the timed kernel carries none):
  * out[0] rays = BVH queries (primary+shadow+reflection), [1] primary, [2] shadow,
  * [3] reflection, [4] BVH nodes visited, [5] primitive tests, [6] closest-hit
- * queries that hit, [7] occluded shadow queries.  Synchronous. */
-int rt_render_stats(rt_ctx* ctx, const rt_params* params, uint64_t out[8]);
+ * queries that hit, [7] occluded shadow queries.  host_cost_or_null (one int32 per
+ * output pixel) receives nodes visited + primitive tests of that pixel.  Synchronous. */
+int rt_render_stats(rt_ctx* ctx, const rt_params* params, uint64_t out[8], int32_t* host_cost_or_null);
 
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in
  * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one

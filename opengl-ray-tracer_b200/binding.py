@@ -82,7 +82,7 @@ def lib():
     L.rt_shard_pixels.argtypes = [vp]; L.rt_shard_pixels.restype = C.c_int64
     L.rt_render.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render.restype = ip
     L.rt_render_device.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_device.restype = ip
-    L.rt_render_stats.argtypes = [vp, C.POINTER(Params), C.POINTER(C.c_uint64)]; L.rt_render_stats.restype = ip
+    L.rt_render_stats.argtypes = [vp, C.POINTER(Params), C.POINTER(C.c_uint64), vp]; L.rt_render_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
     L.rt_stream.argtypes = [vp]; L.rt_stream.restype = vp
@@ -269,10 +269,10 @@ class RayTracer:
         """Asynchronous render into device memory (pointers as ints, e.g. tensor.data_ptr())."""
         self._chk(self._L.rt_render_device(self._c, C.byref(params), _ptr(dev_rgba_ptr), _ptr(dev_ids_ptr)))
 
-    def render_stats(self, params):
+    def render_stats(self, params, cost=None):
         """Untimed counting render: dict of work counters of the CUDA path."""
         out = (C.c_uint64 * 8)()
-        self._chk(self._L.rt_render_stats(self._c, C.byref(params), out))
+        self._chk(self._L.rt_render_stats(self._c, C.byref(params), out, _ptr(cost)))
         keys = ["rays", "primary_rays", "shadow_rays", "reflect_rays", "node_visits", "prim_tests", "ray_hits", "shadowed"]
         return dict(zip(keys, [int(x) for x in out]))
 

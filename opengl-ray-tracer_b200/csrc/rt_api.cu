@@ -365,13 +365,16 @@ int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* de
     return render_impl(c, p, dev_rgba, dev_ids, false);
 }
 
-int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8]) {
+int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8], int32_t* host_cost) {
     if (!c || !p || !out) return RT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
     CU(c, c->tally.reserve(8));
     CU(c, cudaMemsetAsync(c->tally.p, 0, 8 * sizeof(unsigned long long), c->stream));
-    int rc = render_impl(c, p, nullptr, nullptr, true);
+    int32_t* dcost = nullptr;
+    if (host_cost) { CU(c, c->ids.reserve((size_t)out_pixels(c))); dcost = c->ids.p; }
+    int rc = render_impl(c, p, nullptr, dcost, true);
     if (rc != RT_OK) return rc;
+    if (host_cost) CU(c, cudaMemcpyAsync(host_cost, dcost, (size_t)out_pixels(c) * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaMemcpyAsync(out, c->tally.p, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     return RT_OK;
@@ -380,7 +383,7 @@ int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8]) {
 static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count) {
     if (!c || !p) return RT_ERR_ARG;
     if (!c->haveScene || !c->haveCam || !c->haveLight) return fail(c, RT_ERR_STATE, "render before scene/camera/light upload");
-    if (dev_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
+    if (dev_ids && !count && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
     CU(c, cudaSetDevice(c->device));
     int rc = flush_scene(c);
     if (rc != RT_OK) return rc;
@@ -405,7 +408,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     F.maxBounces = p->maxBounces; F.useBVH = p->useBVH != 0; F.useFresnel = p->useFresnel != 0; F.useMT = p->useMollerTrumbore != 0;
     F.W = c->W; F.H = c->H; F.tilesX = tiles_x(c); F.tilesY = tiles_y(c);
     F.shardRank = c->shardRank; F.shardWorld = c->shardWorld; F.nTilesMine = tiles_mine(c);
-    F.writeIds = wantIds ? 1 : 0;
+    F.writeIds = (count && dev_ids) ? 2 : wantIds ? 1 : 0;
 
     cudaEventRecord(c->ev[4], c->stream);
     if (F.nTilesMine > 0) {

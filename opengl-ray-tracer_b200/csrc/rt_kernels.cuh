@@ -127,21 +127,36 @@ __device__ __forceinline__ bool leaf_spheres(const DeviceScene& S, const Ray& r,
     return false;
 }
 
-// Stackless walk of the threaded BVH.  Visits exactly the reference's node set in the
-// reference's order (gpu_shader.comp:390-427) unless the sink stops it.
+// Warp-synchronous ("packet") walk of the threaded BVH.  Every lane visits exactly the
+// reference's node set for ITS ray in the reference's order (gpu_shader.comp:390-427),
+// but the warp advances together: each iteration handles the smallest pending node index
+// over the lanes (one REDUX), lanes whose next node is further along wait.  Because the
+// list is in visit order every lane's index only grows, so the warp walks the UNION of
+// the lanes' node sets once, all node and primitive loads are warp-uniform (one L1
+// wavefront), and a fat leaf is looped once for all lanes that hit its box instead of once
+// per lane at unrelated iterations.  Must be called by all 32 lanes; `active` masks lanes.
+#define RT_FULL 0xffffffffu
+#define RT_DONE 0x7fffffff
 template <bool MT, bool COUNT, class Sink>
-__device__ __forceinline__ void walk(const DeviceScene& S, const Ray& r, Sink& sink, Tally& tl) {
-    int k = 0;
+__device__ __forceinline__ void walk(const DeviceScene& S, const Ray& r, bool active, Sink& sink, Tally& tl) {
     const int n = S.nNodes;
-    while (k < n) {
-        const float4 a = __ldg(S.nodes + 2 * k);
-        const float4 b = __ldg(S.nodes + 2 * k + 1);
+    int k = active ? 0 : RT_DONE;
+    for (;;) {
+        const int km = __reduce_min_sync(RT_FULL, k);
+        if (km >= n) break;
+        const float4 a = __ldg(S.nodes + 2 * km);
+        const float4 b = __ldg(S.nodes + 2 * km + 1);
         const int cw = __float_as_int(b.w);
         const int lnk = __float_as_int(a.w);
-        RT_TALLY(4, 1);
-        const bool hit = r.fast ? slab_fast(r, a, b) : slab(r, a, b);
-        if (!hit) { k = cw < 0 ? lnk : k + 1; continue; }
-        if (cw >= 0) {
+        const bool mine = (k == km);
+        RT_TALLY(4, mine ? 1 : 0);
+        const bool hit = mine && (r.fast ? slab_fast(r, a, b) : slab(r, a, b));
+        if (cw < 0) {                                   // inner: hit -> next in list, miss -> skip subtree
+            if (mine) k = hit ? km + 1 : lnk;
+            continue;
+        }
+        if (mine) k = km + 1;
+        if (hit) {
             const int cnt = cw & RT_LEAF_COUNT_MASK, kind = cw >> RT_LEAF_KIND_SHIFT;
             const int end = lnk + cnt;
             RT_TALLY(5, cnt);
@@ -149,9 +164,8 @@ __device__ __forceinline__ void walk(const DeviceScene& S, const Ray& r, Sink& s
             if (!MT && kind == RT_LEAF_TRIANGLES) stop = leaf_triangles_bary(S, r, lnk, end, sink);
             else if (kind == RT_LEAF_SPHERES)     stop = leaf_spheres<MT>(S, r, lnk, end, sink);
             else                                   stop = leaf_generic<MT>(S, r, lnk, end, sink);
-            if (stop) return;
+            if (stop) k = RT_DONE;
         }
-        ++k;
     }
 }
 
@@ -165,10 +179,10 @@ struct ClosestSink {
     }
 };
 template <bool MT, bool COUNT>
-__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, Hit& h, Tally& tl) {
+__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, bool active, Hit& h, Tally& tl) {
     h.dist = 1e20f; h.slot = -1; h.p = mk(0.f, 0.f, 0.f);
     ClosestSink sink{r, h};
-    walk<MT, COUNT>(S, r, sink, tl);
+    walk<MT, COUNT>(S, r, active, sink, tl);
 }
 
 // Shadow query (a12): the shader runs a full closest-hit query and then tests
@@ -183,9 +197,9 @@ struct AnySink {
     }
 };
 template <bool MT, bool COUNT>
-__device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, float lightDist, Tally& tl) {
+__device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, bool active, float lightDist, Tally& tl) {
     AnySink sink{r, lightDist, false};
-    walk<MT, COUNT>(S, r, sink, tl);
+    walk<MT, COUNT>(S, r, active, sink, tl);
     return sink.found;
 }
 
@@ -245,57 +259,76 @@ __device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3
     return ((ambient + diffuse) + specular) * m.color;
 }
 
+// One pixel per lane, executed by all 32 lanes of the warp in lock step (the packet walks
+// need the whole warp); `inside`/`alive` mask the lanes that have work.
 template <bool MT, bool COUNT>
-__device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, int& idOut, Tally& tl) {
+__device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, bool inside,
+                                              int& idOut, Tally& tl) {
     const float a = (float)y / P.resH;
     const V3 bg = mk(mix1(0.05f, 0.5f, a), mix1(0.07f, 0.7f, a), mix1(0.1f, 1.0f, a));
     const float ndcX = 2.0f * (float)x / P.resW - 1.0f;
     const float ndcY = 1.0f - 2.0f * (float)y / P.resH;
     const V3 camP = mk(P.camP);
     V3 ipp = ((camP + mk(P.camF)) + (ndcX * P.planeW / 2.0f) * mk(P.camR)) + (ndcY * P.planeH / 2.0f) * mk(P.camU);
-    Ray ray = make_ray(camP, normalize3(ipp - camP), S.boxesFinite != 0);
+    const bool bf = S.boxesFinite != 0;
+    Ray ray = make_ray(camP, normalize3(ipp - camP), bf);
     const V3 lpos = mk(P.lightPos), lcol = mk(P.lightCol);
     V3 acc = mk(0.f, 0.f, 0.f), att = mk(1.f, 1.f, 1.f);
     idOut = -1;
+    bool alive = inside;
 
     for (int depth = 0; depth < P.maxBounces; ++depth) {
+        if (!__any_sync(RT_FULL, alive)) break;
         Hit h;
-        int shape;
-        if (P.useBVH) { trace_closest<MT, COUNT>(S, ray, h, tl); shape = h.slot >= 0 ? __ldg(S.pshape + h.slot) : -1; }
-        else          { scan_closest<MT>(S, ray, h);  shape = h.slot; RT_TALLY(5, S.nShapes); }
-        RT_TALLY(0, 1); RT_TALLY(depth == 0 ? 1 : 3, 1); RT_TALLY(6, shape >= 0 ? 1 : 0);
-        if (depth == 0) idOut = shape;
-        if (shape < 0) { acc = acc + att * bg; break; }
+        int shape = -1;
+        if (P.useBVH) {
+            trace_closest<MT, COUNT>(S, ray, alive, h, tl);
+            if (alive && h.slot >= 0) shape = __ldg(S.pshape + h.slot);
+        } else if (alive) {
+            scan_closest<MT>(S, ray, h); shape = h.slot; RT_TALLY(5, S.nShapes);
+        }
+        if (alive) {
+            RT_TALLY(0, 1); RT_TALLY(depth == 0 ? 1 : 3, 1); RT_TALLY(6, shape >= 0 ? 1 : 0);
+            if (depth == 0) idOut = shape;
+            if (shape < 0) { acc = acc + att * bg; alive = false; }
+        }
 
-        const rt_flat_shape* sh = S.shapes + shape;
-        const Material m = load_material(sh);
-        const V3 hp = h.p;
-        V3 nrm;
-        if (__ldg(&sh->type) == RT_SHAPE_SPHERE) nrm = normalize3(hp - mk(__ldg(&sh->sphereCenter[0]), __ldg(&sh->sphereCenter[1]), __ldg(&sh->sphereCenter[2])));
-        else nrm = mk(__ldg(&sh->planeNormal[0]), __ldg(&sh->planeNormal[1]), __ldg(&sh->planeNormal[2]));
+        Material m; m.color = mk(0.f, 0.f, 0.f); m.fresnel = m.ambient = m.diffuse = m.specular = 0.f; m.shininess = 0;
+        V3 hp = mk(0.f, 0.f, 0.f), nrm = mk(0.f, 0.f, 1.f), sdir = mk(0.f, 0.f, 1.f);
+        float lightDist = 0.f;
+        if (alive) {
+            const rt_flat_shape* sh = S.shapes + shape;
+            m = load_material(sh);
+            hp = h.p;
+            if (__ldg(&sh->type) == RT_SHAPE_SPHERE) nrm = normalize3(hp - mk(__ldg(&sh->sphereCenter[0]), __ldg(&sh->sphereCenter[1]), __ldg(&sh->sphereCenter[2])));
+            else nrm = mk(__ldg(&sh->planeNormal[0]), __ldg(&sh->planeNormal[1]), __ldg(&sh->planeNormal[2]));
+            sdir = normalize3(lpos - hp);
+            lightDist = distance3(lpos, hp);
+        }
+        bool inShadow = false;
+        if (P.useBVH) inShadow = trace_any<MT, COUNT>(S, make_ray(hp + nrm * 1e-3f, sdir, bf), alive, lightDist, tl);
+        else if (alive) inShadow = scan_any<MT>(S, make_ray(hp + nrm * 1e-5f, sdir, bf), lightDist);
 
-        const V3 sdir = normalize3(lpos - hp);
-        const float lightDist = distance3(lpos, hp);
-        bool inShadow;
-        if (P.useBVH) inShadow = trace_any<MT, COUNT>(S, make_ray(hp + nrm * 1e-3f, sdir, S.boxesFinite != 0), lightDist, tl);
-        else          inShadow = scan_any<MT>(S, make_ray(hp + nrm * 1e-5f, sdir, S.boxesFinite != 0), lightDist);
-        RT_TALLY(0, 1); RT_TALLY(2, 1); RT_TALLY(7, inShadow ? 1 : 0);
-
-        V3 pc = phong(hp, nrm, ray.d, lpos, lcol, m);
-        if (inShadow) pc = pc * 0.3f;
-        acc = acc + att * pc;
-
-        if (!(m.specular > 0.0f)) break;
-        const V3 rd = reflect3(ray.d, nrm);
-        ray = make_ray(hp + nrm * 1e-3f, rd, S.boxesFinite != 0);
-        if (P.useFresnel) {
-            float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
-            fr = gmin(gmax(fr, 0.0f), 0.8f);
-            const float rw = m.fresnel * fr, mw = 1.0f - rw;
-            att = att * mk(mix1(m.color.x, 1.0f, rw), mix1(m.color.y, 1.0f, rw), mix1(m.color.z, 1.0f, rw));
-            acc = acc + (mw * m.color) * pc;
-        } else {
-            att = att * m.specular;
+        if (alive) {
+            RT_TALLY(0, 1); RT_TALLY(2, 1); RT_TALLY(7, inShadow ? 1 : 0);
+            V3 pc = phong(hp, nrm, ray.d, lpos, lcol, m);
+            if (inShadow) pc = pc * 0.3f;
+            acc = acc + att * pc;
+            if (!(m.specular > 0.0f)) {
+                alive = false;
+            } else {
+                const V3 rd = reflect3(ray.d, nrm);
+                ray = make_ray(hp + nrm * 1e-3f, rd, bf);
+                if (P.useFresnel) {
+                    float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
+                    fr = gmin(gmax(fr, 0.0f), 0.8f);
+                    const float rw = m.fresnel * fr, mw = 1.0f - rw;
+                    att = att * mk(mix1(m.color.x, 1.0f, rw), mix1(m.color.y, 1.0f, rw), mix1(m.color.z, 1.0f, rw));
+                    acc = acc + (mw * m.color) * pc;
+                } else {
+                    att = att * m.specular;
+                }
+            }
         }
     }
     return make_float4(acc.x, acc.y, acc.z, 1.0f);
@@ -333,7 +366,10 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         const bool inside = x < P.W && y < P.H;
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         int id = -1;
-        if (inside) c = shade_pixel<MT, COUNT>(S, P, x, y, id, tl);
+        unsigned long long cost0 = 0;
+        if (COUNT) cost0 = tl.v[4] + tl.v[5];
+        c = shade_pixel<MT, COUNT>(S, P, x, y, inside, id, tl);
+        if (COUNT && P.writeIds == 2) id = (int)(tl.v[4] + tl.v[5] - cost0);   // diagnostic: per-pixel work AOV
         __syncwarp();
         if (P.shardWorld == 1) {
             if (inside) {
