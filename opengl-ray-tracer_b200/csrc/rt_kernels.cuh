@@ -52,54 +52,56 @@ __device__ __forceinline__ bool test_prim(const Prim& p, const Ray& r, V3& hp) {
     return false;
 }
 
-// Test the primitive in slot s, loading only what its type and stage need.
-template <bool MT>
-__device__ __forceinline__ bool test_slot(const DeviceScene& S, int s, const Ray& r, V3& hp) {
-    const int type = __ldg(S.ptype + s);
-    if (type == RT_SHAPE_TRIANGLE) {
-        if (MT) return hit_tri_mt(__ldg(S.q1 + s), __ldg(S.q2 + s), __ldg(S.q3 + s), r, hp);
-        if (!plane_stage(__ldg(S.q0 + s), r, hp)) return false;
-        return bary_stage2(__ldg(S.q1 + s), __ldg(S.q2 + s), __ldg(S.q3 + s), hp);
-    }
-    if (type == RT_SHAPE_SPHERE) return hit_sphere(__ldg(S.q0 + s), r, hp);
-    if (type == RT_SHAPE_WALL) {
-        if (!plane_stage(__ldg(S.q0 + s), r, hp)) return false;
-        return wall_stage2(__ldg(S.q1 + s), __ldg(S.q2 + s), __ldg(S.q3 + s), hp);
-    }
-    if (type == RT_SHAPE_PLANE) return plane_stage(__ldg(S.q0 + s), r, hp);
-    return false;
+// One BVH query of one lane.  Closest-hit (a3): best starts at 1e20 and every candidate with
+// dist < best replaces it (strict '<', first in visit order wins ties, :410-411).  Shadow
+// (a12): the shader runs a full closest-hit query and then tests hitDist < lightDist; "some
+// INNER hit has dist < 1e20 and dist < lightDist" is the same boolean (the closest hit has
+// the minimum dist), so best starts at min(1e20, lightDist) and the first candidate below it
+// ends the query.
+struct Query {
+    Ray r;
+    float best;      // current bound: candidates need dist < best
+    int slot;        // slot of the accepted candidate, -1 = none
+    V3 p;            // its hit point
+};
+struct Cand { float dist; int slot; V3 p; };
+
+__device__ __forceinline__ void offer(Query& q, int s, V3 hp) {
+    const float dist = distance3(q.r.o, hp);
+    if (dist < q.best) { q.best = dist; q.slot = s; q.p = hp; }
 }
 
-// A hit candidate is handed to `sink(slot, hp)`, which returns true to stop the query
-// (any-hit).  Candidates arrive in slot order == the reference's visit order.
-//
-// Triangle leaf, Barycentric mode: the plane stage of four consecutive slots is evaluated
-// as four independent dependency chains (the loads are issued together; the slot arrays
-// are padded so reading past `end` is safe), then the survivors go through the division
-// and the barycentric stage in slot order.
-template <class Sink>
-__device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, const Ray& r, int s0, int end, Sink& sink) {
+// Triangle leaf, Barycentric mode.  The plane stage of four consecutive slots is evaluated as
+// four independent dependency chains (the loads are issued together; the slot arrays are
+// padded so reading past `end` is safe); the survivors then go through the division and the
+// barycentric stage in slot order in ONE rolled loop body (code size: the hot loop must stay
+// inside the instruction cache).  Returns true when an any-hit query is satisfied.
+__device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, Query& q, int s0, int end, bool anyMode) {
+    const Ray& r = q.r;
     for (int s = s0; s < end; s += 4) {
-        float4 q[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) q[i] = __ldg(S.q0 + s + i);
         float np[4], num[4];
-        bool pass[4];
+        unsigned pm = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const V3 n = xyz(q[i]);
+            const float4 qq = __ldg(S.q0 + s + i);
+            const V3 n = xyz(qq);
             np[i] = dot3(n, r.d);
-            num[i] = -(q[i].w + dot3(n, r.o));
-            pass[i] = (np[i] > 0.0f) && (num[i] > 0.0f) && (s + i < end);
+            num[i] = -(qq.w + dot3(n, r.o));
+            if ((np[i] > 0.0f) && (num[i] > 0.0f) && (s + i < end)) pm |= 1u << i;
         }
-#pragma unroll
+#pragma unroll 1
         for (int i = 0; i < 4; ++i) {
-            if (pass[i]) {
-                const float t = num[i] / np[i];
+            if (pm & (1u << i)) {
+                const float npi = i == 0 ? np[0] : i == 1 ? np[1] : i == 2 ? np[2] : np[3];
+                const float numi = i == 0 ? num[0] : i == 1 ? num[1] : i == 2 ? num[2] : num[3];
+                const float t = numi / npi;
                 if (t > 0.0f) {
                     const V3 hp = r.o + t * r.d;
-                    if (bary_stage2(__ldg(S.q1 + s + i), __ldg(S.q2 + s + i), __ldg(S.q3 + s + i), hp))
-                        if (sink(s + i, hp)) return true;
+                    if (bary_stage2(__ldg(S.q1 + s + i), __ldg(S.q2 + s + i), __ldg(S.q3 + s + i), hp)) {
+                        const int before = q.slot;
+                        offer(q, s + i, hp);
+                        if (anyMode && q.slot != before) return true;
+                    }
                 }
             }
         }
@@ -107,24 +109,34 @@ __device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, const 
     return false;
 }
 
-template <bool MT, class Sink>
-__device__ __forceinline__ bool leaf_generic(const DeviceScene& S, const Ray& r, int s0, int end, Sink& sink) {
+// Everything that is not a pure Barycentric-triangle leaf (spheres, walls, planes, mixed leaves,
+// Moller-Trumbore mode) goes through one out-of-line routine so that the hot loop stays small.
+// By-value in, by-value out: nothing of the caller's state is forced into local memory.
+template <bool MT>
+__device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const float4* __restrict__ q1,
+                                          const float4* __restrict__ q2, const float4* __restrict__ q3,
+                                          const int* __restrict__ ptype, Ray r, int s0, int end, float best, int anyMode) {
+    Cand c; c.dist = best; c.slot = -1; c.p = mk(0.f, 0.f, 0.f);
     for (int s = s0; s < end; ++s) {
+        const int type = __ldg(ptype + s);
         V3 hp;
-        if (test_slot<MT>(S, s, r, hp))
-            if (sink(s, hp)) return true;
+        bool hit = false;
+        if (type == RT_SHAPE_TRIANGLE) {
+            if (MT) hit = hit_tri_mt(__ldg(q1 + s), __ldg(q2 + s), __ldg(q3 + s), r, hp);
+            else hit = plane_stage(__ldg(q0 + s), r, hp) && bary_stage2(__ldg(q1 + s), __ldg(q2 + s), __ldg(q3 + s), hp);
+        } else if (type == RT_SHAPE_SPHERE) {
+            hit = hit_sphere(__ldg(q0 + s), r, hp);
+        } else if (type == RT_SHAPE_WALL) {
+            hit = plane_stage(__ldg(q0 + s), r, hp) && wall_stage2(__ldg(q1 + s), __ldg(q2 + s), __ldg(q3 + s), hp);
+        } else if (type == RT_SHAPE_PLANE) {
+            hit = plane_stage(__ldg(q0 + s), r, hp);
+        }
+        if (hit) {
+            const float dist = distance3(r.o, hp);
+            if (dist < c.dist) { c.dist = dist; c.slot = s; c.p = hp; if (anyMode) break; }
+        }
     }
-    return false;
-}
-
-template <bool MT, class Sink>
-__device__ __forceinline__ bool leaf_spheres(const DeviceScene& S, const Ray& r, int s0, int end, Sink& sink) {
-    for (int s = s0; s < end; ++s) {
-        V3 hp;
-        if (hit_sphere(__ldg(S.q0 + s), r, hp))
-            if (sink(s, hp)) return true;
-    }
-    return false;
+    return c;
 }
 
 // Warp-synchronous ("packet") walk of the threaded BVH.  Every lane visits exactly the
@@ -137,9 +149,10 @@ __device__ __forceinline__ bool leaf_spheres(const DeviceScene& S, const Ray& r,
 // per lane at unrelated iterations.  Must be called by all 32 lanes; `active` masks lanes.
 #define RT_FULL 0xffffffffu
 #define RT_DONE 0x7fffffff
-template <bool MT, bool COUNT, class Sink>
-__device__ __forceinline__ void walk(const DeviceScene& S, const Ray& r, bool active, Sink& sink, Tally& tl) {
+template <bool MT, bool COUNT>
+__device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active, bool anyMode, Tally& tl) {
     const int n = S.nNodes;
+    const Ray& r = q.r;
     int k = active ? 0 : RT_DONE;
     for (;;) {
         const int km = __reduce_min_sync(RT_FULL, k);
@@ -160,47 +173,16 @@ __device__ __forceinline__ void walk(const DeviceScene& S, const Ray& r, bool ac
             const int cnt = cw & RT_LEAF_COUNT_MASK, kind = cw >> RT_LEAF_KIND_SHIFT;
             const int end = lnk + cnt;
             RT_TALLY(5, cnt);
-            bool stop;
-            if (!MT && kind == RT_LEAF_TRIANGLES) stop = leaf_triangles_bary(S, r, lnk, end, sink);
-            else if (kind == RT_LEAF_SPHERES)     stop = leaf_spheres<MT>(S, r, lnk, end, sink);
-            else                                   stop = leaf_generic<MT>(S, r, lnk, end, sink);
+            bool stop = false;
+            if (!MT && kind == RT_LEAF_TRIANGLES) {
+                stop = leaf_triangles_bary(S, q, lnk, end, anyMode);
+            } else {
+                const Cand c = leaf_generic<MT>(S.q0, S.q1, S.q2, S.q3, S.ptype, r, lnk, end, q.best, anyMode ? 1 : 0);
+                if (c.slot >= 0) { q.best = c.dist; q.slot = c.slot; q.p = c.p; stop = anyMode; }
+            }
             if (stop) k = RT_DONE;
         }
     }
-}
-
-// Closest hit (a3): dist is distance(ray.start, hit_point) with strict '<' (:410-411).
-struct ClosestSink {
-    const Ray& r; Hit& h;
-    __device__ __forceinline__ bool operator()(int slot, V3 hp) {
-        const float dist = distance3(r.o, hp);
-        if (dist < h.dist) { h.dist = dist; h.slot = slot; h.p = hp; }
-        return false;
-    }
-};
-template <bool MT, bool COUNT>
-__device__ __forceinline__ void trace_closest(const DeviceScene& S, const Ray& r, bool active, Hit& h, Tally& tl) {
-    h.dist = 1e20f; h.slot = -1; h.p = mk(0.f, 0.f, 0.f);
-    ClosestSink sink{r, h};
-    walk<MT, COUNT>(S, r, active, sink, tl);
-}
-
-// Shadow query (a12): the shader runs a full closest-hit query and then tests
-// hitDist < lightDist; "some INNER hit has dist < 1e20 and dist < lightDist" is the same
-// boolean (the closest hit has the minimum dist), so this stops at the first occluder.
-struct AnySink {
-    const Ray& r; float lightDist; bool found;
-    __device__ __forceinline__ bool operator()(int, V3 hp) {
-        const float dist = distance3(r.o, hp);
-        if (dist < 1e20f && dist < lightDist) { found = true; return true; }
-        return false;
-    }
-};
-template <bool MT, bool COUNT>
-__device__ __forceinline__ bool trace_any(const DeviceScene& S, const Ray& r, bool active, float lightDist, Tally& tl) {
-    AnySink sink{r, lightDist, false};
-    walk<MT, COUNT>(S, r, active, sink, tl);
-    return sink.found;
 }
 
 // Brute-force twins (a14, useBVH == false): linear scan over the raw shapes.
@@ -259,8 +241,11 @@ __device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3
     return ((ambient + diffuse) + specular) * m.color;
 }
 
-// One pixel per lane, executed by all 32 lanes of the warp in lock step (the packet walks
-// need the whole warp); `inside`/`alive` mask the lanes that have work.
+// One pixel per lane, executed by all 32 lanes of the warp in lock step (the packet walk
+// needs the whole warp); `alive` masks the lanes that still have work.  The bounce loop
+// (gpu_shader.comp:450-517) is run as a two-phase machine — even steps are the closest-hit
+// query of the current ray, odd steps the shadow query and the shading that depends on it —
+// so that the walk is instantiated ONCE and both kinds of query share its code.
 template <bool MT, bool COUNT>
 __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, bool inside,
                                               int& idOut, Tally& tl) {
@@ -277,57 +262,59 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
     idOut = -1;
     bool alive = inside;
 
-    for (int depth = 0; depth < P.maxBounces; ++depth) {
+    Material m; m.color = mk(0.f, 0.f, 0.f); m.fresnel = m.ambient = m.diffuse = m.specular = 0.f; m.shininess = 0;
+    V3 hp = mk(0.f, 0.f, 0.f), nrm = mk(0.f, 0.f, 1.f);
+    float lightDist = 0.f;
+    Query q;
+
+    for (int step = 0; step < 2 * P.maxBounces; ++step) {
         if (!__any_sync(RT_FULL, alive)) break;
-        Hit h;
+        const bool shadowStep = (step & 1) != 0;
+        if (!shadowStep) {
+            q.r = ray; q.best = 1e20f;
+        } else {
+            q.r = make_ray(hp + nrm * (P.useBVH ? 1e-3f : 1e-5f), normalize3(lpos - hp), bf);
+            // dist < 1e20 && dist < lightDist  ==  dist < min; a NaN lightDist can never be beaten
+            q.best = lightDist < 1e20f ? lightDist : (lightDist >= 1e20f ? 1e20f : -1.0f);
+        }
+        q.slot = -1; q.p = mk(0.f, 0.f, 0.f);
         int shape = -1;
         if (P.useBVH) {
-            trace_closest<MT, COUNT>(S, ray, alive, h, tl);
-            if (alive && h.slot >= 0) shape = __ldg(S.pshape + h.slot);
+            walk<MT, COUNT>(S, q, alive, shadowStep, tl);
+            if (alive && !shadowStep && q.slot >= 0) shape = __ldg(S.pshape + q.slot);
         } else if (alive) {
-            scan_closest<MT>(S, ray, h); shape = h.slot; RT_TALLY(5, S.nShapes);
+            if (!shadowStep) { Hit h; scan_closest<MT>(S, q.r, h); shape = h.slot; q.slot = h.slot; q.p = h.p; RT_TALLY(5, S.nShapes); }
+            else if (scan_any<MT>(S, q.r, lightDist)) q.slot = 0;
         }
-        if (alive) {
-            RT_TALLY(0, 1); RT_TALLY(depth == 0 ? 1 : 3, 1); RT_TALLY(6, shape >= 0 ? 1 : 0);
-            if (depth == 0) idOut = shape;
-            if (shape < 0) { acc = acc + att * bg; alive = false; }
-        }
-
-        Material m; m.color = mk(0.f, 0.f, 0.f); m.fresnel = m.ambient = m.diffuse = m.specular = 0.f; m.shininess = 0;
-        V3 hp = mk(0.f, 0.f, 0.f), nrm = mk(0.f, 0.f, 1.f), sdir = mk(0.f, 0.f, 1.f);
-        float lightDist = 0.f;
-        if (alive) {
+        if (!alive) continue;
+        RT_TALLY(0, 1);
+        if (!shadowStep) {                                 // closest-hit result (:452-464)
+            RT_TALLY(step == 0 ? 1 : 3, 1); RT_TALLY(6, shape >= 0 ? 1 : 0);
+            if (step == 0) idOut = shape;
+            if (shape < 0) { acc = acc + att * bg; alive = false; continue; }
             const rt_flat_shape* sh = S.shapes + shape;
             m = load_material(sh);
-            hp = h.p;
+            hp = q.p;
             if (__ldg(&sh->type) == RT_SHAPE_SPHERE) nrm = normalize3(hp - mk(__ldg(&sh->sphereCenter[0]), __ldg(&sh->sphereCenter[1]), __ldg(&sh->sphereCenter[2])));
             else nrm = mk(__ldg(&sh->planeNormal[0]), __ldg(&sh->planeNormal[1]), __ldg(&sh->planeNormal[2]));
-            sdir = normalize3(lpos - hp);
             lightDist = distance3(lpos, hp);
-        }
-        bool inShadow = false;
-        if (P.useBVH) inShadow = trace_any<MT, COUNT>(S, make_ray(hp + nrm * 1e-3f, sdir, bf), alive, lightDist, tl);
-        else if (alive) inShadow = scan_any<MT>(S, make_ray(hp + nrm * 1e-5f, sdir, bf), lightDist);
-
-        if (alive) {
-            RT_TALLY(0, 1); RT_TALLY(2, 1); RT_TALLY(7, inShadow ? 1 : 0);
+        } else {                                           // shadow result, shading, next ray (:474-516)
+            const bool inShadow = q.slot >= 0;
+            RT_TALLY(2, 1); RT_TALLY(7, inShadow ? 1 : 0);
             V3 pc = phong(hp, nrm, ray.d, lpos, lcol, m);
             if (inShadow) pc = pc * 0.3f;
             acc = acc + att * pc;
-            if (!(m.specular > 0.0f)) {
-                alive = false;
+            if (!(m.specular > 0.0f)) { alive = false; continue; }
+            const V3 rd = reflect3(ray.d, nrm);
+            ray = make_ray(hp + nrm * 1e-3f, rd, bf);
+            if (P.useFresnel) {
+                float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
+                fr = gmin(gmax(fr, 0.0f), 0.8f);
+                const float rw = m.fresnel * fr, mw = 1.0f - rw;
+                att = att * mk(mix1(m.color.x, 1.0f, rw), mix1(m.color.y, 1.0f, rw), mix1(m.color.z, 1.0f, rw));
+                acc = acc + (mw * m.color) * pc;
             } else {
-                const V3 rd = reflect3(ray.d, nrm);
-                ray = make_ray(hp + nrm * 1e-3f, rd, bf);
-                if (P.useFresnel) {
-                    float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
-                    fr = gmin(gmax(fr, 0.0f), 0.8f);
-                    const float rw = m.fresnel * fr, mw = 1.0f - rw;
-                    att = att * mk(mix1(m.color.x, 1.0f, rw), mix1(m.color.y, 1.0f, rw), mix1(m.color.z, 1.0f, rw));
-                    acc = acc + (mw * m.color) * pc;
-                } else {
-                    att = att * m.specular;
-                }
+                att = att * m.specular;
             }
         }
     }
