@@ -55,10 +55,12 @@ typedef struct rt_params {
 /* rt_create flags */
 enum {
     RT_FLAG_DEFAULT   = 0u,
-    /* Allow distance culling of BVH nodes for closest-hit rays (a conservative
-     * margin keeps ids identical on every tested scene; the default visits
-     * exactly the reference's node set and is identical by construction). */
-    RT_FLAG_CULL      = 1u << 0,
+    /* Walk exactly the reference's node and primitive sequence.  By default the
+     * reference's fat leaves (its builder stops splitting when one side of a
+     * midpoint split is empty, src/main.cpp:1156-1161) are expanded at upload
+     * into private sub-trees whose boxes are conservative bounds of each
+     * primitive's fp32 acceptance region, so no hit/miss decision changes. */
+    RT_FLAG_REFERENCE_WALK = 1u << 0,
     /* Record per-pixel primary-hit shape ids (an AOV the reference lacks;
      * needed by the parity criterion).  Off = the id buffer is not written. */
     RT_FLAG_HIT_IDS   = 1u << 1

@@ -29,7 +29,7 @@ NODE_DTYPE = np.dtype({"names": ["boundsMin", "boundsMax", "leftChild", "rightCh
                        "formats": [("f4", 3), ("f4", 3), "i4", "i4", "i4", "i4"],
                        "offsets": [0, 16, 32, 36, 40, 44], "itemsize": 48})
 
-RT_FLAG_CULL = 1
+RT_FLAG_REFERENCE_WALK = 1
 RT_FLAG_HIT_IDS = 2
 TILE_W, TILE_H = 32, 8
 

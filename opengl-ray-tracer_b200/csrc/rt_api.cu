@@ -2,6 +2,7 @@
 // kernels in rt_kernels.cuh.  Context = what the reference keeps in GL objects
 // (program, 5 SSBOs, output texture; src/main.cpp:182-275).  No CPU fallback.
 #include "rt_kernels.cuh"
+#include "rt_layout.h"
 
 #include <cmath>
 #include <cstdio>
@@ -72,6 +73,12 @@ struct rt_ctx {
     PinBuf<int>  hOrder;   DevBuf<int>  dOrder;
     PinBuf<int2> hLinkCnt; DevBuf<int2> dLinkCnt;
     PinBuf<int>  hPshape;  DevBuf<int>  dPshape;
+    PinBuf<int>  hPrank;   DevBuf<int>  dPrank;
+    PinBuf<float4> hSubBox; DevBuf<float4> dSubBox;   // 2 float4 per sub-tree node (host-computed conservative boxes)
+    rtl::Layout layout;               // host copy of the threaded layout (refit of the sub-tree boxes)
+    int nSub = 0;
+    bool subDirty = false;            // sub-tree boxes must be recomputed (shapes moved / omax grew)
+    float omax = 0.f;
     DevBuf<float4> dNodesT, q0, q1, q2, q3;
     DevBuf<int> ptype;
     int nDfs = 0, nPrims = 0;
@@ -118,82 +125,70 @@ inline void wait_copies(rt_ctx* c) {
     if (c->copyPending) { cudaEventSynchronize(c->copyDone); c->copyPending = false; }
 }
 
-// Threaded visit order of the reference traversal: root = last node, right child
-// first (gpu_shader.comp:386, :424-425).  Validates what the shader would trust.
-int build_visit_order(rt_ctx* c) {
-    const int n = c->nNodes;
-    const rt_flat_node* nd = c->hNodes.p;
-    std::vector<int> order; order.reserve((size_t)n);
-    if (n > 0) {
-        struct Item { int node, depth; };
-        std::vector<Item> st; st.push_back({n - 1, 1});
-        const size_t limit = (size_t)n * 4 + 64;
-        while (!st.empty()) {
-            Item it = st.back(); st.pop_back();
-            if (it.node < 0 || it.node >= n) return fail(c, RT_ERR_SCENE, "BVH child index out of range");
-            if (order.size() >= limit) return fail(c, RT_ERR_SCENE, "BVH is cyclic or shares subtrees excessively");
-            order.push_back(it.node);
-            const rt_flat_node& x = nd[it.node];
-            if (x.leftChild != -1) {
-                if (it.depth + 1 > 64) return fail(c, RT_ERR_SCENE, "BVH deeper than the reference's 64-entry stack");
-                st.push_back({x.leftChild, it.depth + 1});
-                st.push_back({x.rightChild, it.depth + 1});
-            }
+// Build the threaded layout (rt_layout.h): reference nodes in the reference's visit order (root =
+// last node, right child first, gpu_shader.comp:386, :424-425) with fat leaves expanded into
+// conservative sub-trees.  Validates what the shader would trust.
+double pick_omax(const rt_ctx* c) {
+    double m = 1.0;
+    if (c->nNodes > 0) {
+        const rt_flat_node& root = c->hNodes.p[c->nNodes - 1];
+        for (int k = 0; k < 3; ++k) {
+            const double a = std::fabs((double)root.boundsMin[k]), b = std::fabs((double)root.boundsMax[k]);
+            if (std::isfinite(a) && a > m) m = a;
+            if (std::isfinite(b) && b > m) m = b;
         }
     }
-    const int m = (int)order.size();
-    std::vector<int> size((size_t)m, 1);
+    if (c->haveCam) for (int k = 0; k < 3; ++k) { const double a = std::fabs((double)c->cam.Position[k]); if (std::isfinite(a) && a > m) m = a; }
+    if (c->haveLight) for (int k = 0; k < 3; ++k) { const double a = std::fabs((double)c->light.position[k]); if (std::isfinite(a) && a > m) m = a; }
+    return 4.0 * m;
+}
+
+void stage_subboxes(rt_ctx* c) {
+    const rtl::Layout& L = c->layout;
+    for (size_t j = 0; j < L.subBox.size(); ++j) {
+        const rtl::Box& b = L.subBox[j];
+        c->hSubBox.p[2 * j]     = make_float4(b.mn[0], b.mn[1], b.mn[2], 0.f);
+        c->hSubBox.p[2 * j + 1] = make_float4(b.mx[0], b.mx[1], b.mx[2], 0.f);
+    }
+}
+
+int build_visit_order(rt_ctx* c) {
+    rtl::Layout& L = c->layout;
+    const bool subtrees = c->boxesFinite && !(c->flags & RT_FLAG_REFERENCE_WALK);
+    c->omax = (float)pick_omax(c);
+    if (!rtl::build_layout(c->hNodes.p, c->nNodes, c->indices.data(), c->indices.size(), c->hShapes.p, c->nShapes,
+                           subtrees, (double)c->omax, L))
+        return fail(c, RT_ERR_SCENE, L.error ? L.error : "malformed BVH");
+    const int m = L.nodes(), prims = L.prims();
+    c->nSub = (int)L.subBox.size();
     CU(c, c->hOrder.reserve((size_t)m, 0));
     CU(c, c->hLinkCnt.reserve((size_t)m, 0));
-    for (int k = m - 1; k >= 0; --k) {
-        if (nd[order[(size_t)k]].leftChild != -1) {
-            const int r = k + 1, l = r + size[(size_t)r];
-            size[(size_t)k] = 1 + size[(size_t)r] + size[(size_t)l];
-        }
+    CU(c, c->hPshape.reserve((size_t)prims, 0));
+    CU(c, c->hPrank.reserve((size_t)prims, 0));
+    CU(c, c->hSubBox.reserve((size_t)c->nSub * 2, 0));
+    for (int k = 0; k < m; ++k) { c->hOrder.p[k] = L.src[(size_t)k]; c->hLinkCnt.p[k] = make_int2(L.link[(size_t)k], L.cw[(size_t)k]); }
+    if (prims > 0) {
+        std::memcpy(c->hPshape.p, L.pshape.data(), (size_t)prims * sizeof(int));
+        std::memcpy(c->hPrank.p, L.prank.data(), (size_t)prims * sizeof(int));
     }
-    size_t prims = 0;
-    for (int k = 0; k < m; ++k) {
-        const rt_flat_node& x = nd[order[(size_t)k]];
-        if (x.leftChild == -1) {
-            if (x.numShapes < 0 || x.startShapeIdx < 0 || (size_t)x.startShapeIdx + (size_t)x.numShapes > c->indices.size())
-                return fail(c, RT_ERR_SCENE, "leaf index range outside bvhIndices");
-            prims += (size_t)x.numShapes;
-        }
-    }
-    if (prims > 0x7fffffffu) return fail(c, RT_ERR_SCENE, "too many leaf primitives");
-    CU(c, c->hPshape.reserve(prims, 0));
-    size_t slot = 0;
-    for (int k = 0; k < m; ++k) {
-        const rt_flat_node& x = nd[order[(size_t)k]];
-        c->hOrder.p[k] = order[(size_t)k];
-        if (x.leftChild == -1) {
-            if (x.numShapes > RT_LEAF_COUNT_MASK) return fail(c, RT_ERR_SCENE, "leaf with more than 2^28 shapes");
-            const int first = (int)slot;
-            int nTri = 0, nSph = 0;
-            for (int i = 0; i < x.numShapes; ++i) {
-                const int s = c->indices[(size_t)x.startShapeIdx + (size_t)i];
-                if (s < 0 || s >= c->nShapes) return fail(c, RT_ERR_SCENE, "bvhIndices entry outside the shape buffer");
-                const int type = c->hShapes.p[s].type;
-                nTri += type == RT_SHAPE_TRIANGLE; nSph += type == RT_SHAPE_SPHERE;
-                c->hPshape.p[slot++] = s;
-            }
-            // type-homogeneous leaves skip the per-primitive type load on the device
-            const int kind = x.numShapes == 0 ? RT_LEAF_MIXED : nTri == x.numShapes ? RT_LEAF_TRIANGLES
-                           : nSph == x.numShapes ? RT_LEAF_SPHERES : RT_LEAF_MIXED;
-            c->hLinkCnt.p[k] = make_int2(first, x.numShapes | (kind << RT_LEAF_KIND_SHIFT));
-        } else {
-            c->hLinkCnt.p[k] = make_int2(k + size[(size_t)k], -1);
-        }
-    }
-    c->nDfs = m; c->nPrims = (int)prims;
+    stage_subboxes(c);
+    c->nDfs = m; c->nPrims = prims;
+    c->subDirty = false;
     return RT_OK;
 }
 
 // Bring the device scene up to date: coalesced H2D of whatever changed, then K2.
 int flush_scene(rt_ctx* c) {
-    const bool anyCopy = c->shapeHi > c->shapeLo || c->nodesDirty || c->topoDirty;
+    // the camera may have left the region the sub-tree margins were computed for
+    if (c->nSub > 0 && !c->topoDirty && c->haveCam) {
+        double m = 0;
+        for (int k = 0; k < 3; ++k) m = std::fmax(m, std::fabs((double)c->cam.Position[k]));
+        if (!(m <= 0.5 * (double)c->omax)) { c->omax = (float)pick_omax(c); c->subDirty = true; }
+    }
+    const bool anyCopy = c->shapeHi > c->shapeLo || c->nodesDirty || c->topoDirty || c->subDirty;
     if (!anyCopy) return RT_OK;
     const bool shapesChanged = c->shapeHi > c->shapeLo;
+    if (shapesChanged && c->nSub > 0) c->subDirty = true;
     cudaEventRecord(c->ev[0], c->stream);
     if (shapesChanged) {
         CU(c, c->dShapes.reserve((size_t)c->nShapes));
@@ -204,12 +199,21 @@ int flush_scene(rt_ctx* c) {
         CU(c, c->dNodes.reserve((size_t)c->nNodes));
         CU(c, cudaMemcpyAsync(c->dNodes.p, c->hNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyHostToDevice, c->stream));
     }
+    bool subUpload = false;
+    if (c->subDirty && !c->topoDirty) {
+        // shapes moved under a sub-tree (or omax grew): refit its boxes on the host; a primitive that
+        // stopped being boundable forces a rebuild of the layout
+        wait_copies(c);
+        if (rtl::refit_subboxes(c->layout, c->hShapes.p, (double)c->omax)) { stage_subboxes(c); subUpload = true; }
+        else c->topoDirty = true;
+        c->subDirty = false;
+    }
     if (c->topoDirty) {
         wait_copies(c);
         int rc = build_visit_order(c);
         if (rc != RT_OK) return rc;
         CU(c, c->dOrder.reserve((size_t)c->nDfs)); CU(c, c->dLinkCnt.reserve((size_t)c->nDfs));
-        CU(c, c->dPshape.reserve((size_t)c->nPrims));
+        CU(c, c->dPshape.reserve((size_t)c->nPrims)); CU(c, c->dPrank.reserve((size_t)c->nPrims));
         CU(c, c->dNodesT.reserve((size_t)c->nDfs * 2));
         // +4 slots of padding: the batched triangle loop loads q0[s..s+3] before masking by the leaf end
         CU(c, c->q0.reserve((size_t)c->nPrims + 4)); CU(c, c->q1.reserve((size_t)c->nPrims + 4));
@@ -219,14 +223,21 @@ int flush_scene(rt_ctx* c) {
             CU(c, cudaMemcpyAsync(c->dOrder.p, c->hOrder.p, (size_t)c->nDfs * sizeof(int), cudaMemcpyHostToDevice, c->stream));
             CU(c, cudaMemcpyAsync(c->dLinkCnt.p, c->hLinkCnt.p, (size_t)c->nDfs * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
         }
-        if (c->nPrims > 0)
+        if (c->nPrims > 0) {
             CU(c, cudaMemcpyAsync(c->dPshape.p, c->hPshape.p, (size_t)c->nPrims * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+            CU(c, cudaMemcpyAsync(c->dPrank.p, c->hPrank.p, (size_t)c->nPrims * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        }
+        subUpload = true;
+    }
+    if (subUpload && c->nSub > 0) {
+        CU(c, c->dSubBox.reserve((size_t)c->nSub * 2));
+        CU(c, cudaMemcpyAsync(c->dSubBox.p, c->hSubBox.p, (size_t)c->nSub * 2 * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     }
     cudaEventRecord(c->ev[1], c->stream); c->timed[0] = true;
     cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
     cudaEventRecord(c->ev[2], c->stream);
-    if ((c->nodesDirty || c->topoDirty) && c->nDfs > 0) {
-        repack_nodes_kernel<<<(c->nDfs + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dOrder.p, c->dLinkCnt.p, c->dNodesT.p, c->nDfs);
+    if ((c->nodesDirty || c->topoDirty || subUpload) && c->nDfs > 0) {
+        repack_nodes_kernel<<<(c->nDfs + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dSubBox.p, c->dOrder.p, c->dLinkCnt.p, c->dNodesT.p, c->nDfs);
         c->launches++;
     }
     if ((shapesChanged || c->topoDirty) && c->nPrims > 0) {
@@ -291,7 +302,8 @@ void rt_destroy(rt_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->hShapes.release(); c->dShapes.release(); c->hNodes.release(); c->dNodes.release();
     c->hOrder.release(); c->dOrder.release(); c->hLinkCnt.release(); c->dLinkCnt.release();
-    c->hPshape.release(); c->dPshape.release(); c->dNodesT.release();
+    c->hPshape.release(); c->dPshape.release(); c->hPrank.release(); c->dPrank.release();
+    c->hSubBox.release(); c->dSubBox.release(); c->dNodesT.release();
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
     c->image.release(); c->ids.release(); c->tally.release(); c->queue.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
@@ -394,8 +406,9 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
 
     DeviceScene S;
     S.nodes = c->dNodesT.p; S.q0 = c->q0.p; S.q1 = c->q1.p; S.q2 = c->q2.p; S.q3 = c->q3.p;
-    S.ptype = c->ptype.p; S.pshape = c->dPshape.p; S.shapes = c->dShapes.p;
+    S.ptype = c->ptype.p; S.pshape = c->dPshape.p; S.prank = c->dPrank.p; S.shapes = c->dShapes.p;
     S.nNodes = c->nDfs; S.nPrims = c->nPrims; S.nShapes = c->nShapes; S.boxesFinite = c->boxesFinite ? 1 : 0;
+    S.omax = c->omax;
 
     FrameParams F;
     std::memcpy(F.camP, c->cam.Position, 12); std::memcpy(F.camF, c->cam.Front, 12);

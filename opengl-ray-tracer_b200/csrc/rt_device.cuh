@@ -9,8 +9,19 @@
 // the IEEE fp32 operations, in exactly the order, of the shader (compiled with
 // -fmad=false), so closest-hit shape ids are bit-identical to the oracle.
 #pragma once
-#include <cuda_runtime.h>
 #include <stdint.h>
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#define RT_DEV __device__ __forceinline__
+#else
+// Host compilation (g++ -ffp-contract=off) is used ONLY by tests/emu: a scalar emulation of the
+// walk that checks the layout builder and the conservative sub-tree bounds without a GPU.  The
+// product library is always built by nvcc and has no host execution path.
+#include <math.h>
+#include <vector_types.h>
+#include <vector_functions.h>
+#define RT_DEV inline
+#endif
 
 #include "../../include/rt_api.h"
 
@@ -41,17 +52,24 @@ struct DeviceScene {
     const float4* __restrict__ q3;
     const int*    __restrict__ ptype;   // per slot
     const int*    __restrict__ pshape;  // per slot: original shape index
+    const int*    __restrict__ prank;   // per slot: position in the reference's primitive visit sequence
     const rt_flat_shape* __restrict__ shapes;   // raw std430 shapes (materials, brute-force path)
     int nNodes;
     int nPrims;
     int nShapes;
     int boxesFinite;      // every node bound is finite: the NaN-free slab fast path is legal
+    float omax;           // sub-tree boxes are conservative for ray origins with |o|_inf <= omax
 };
 
 // Leaf "kind" tag kept in bits 28..30 of a leaf's count word (host-computed at upload):
 // all primitives of the leaf have one type, so the per-primitive type load is skipped.
+// Bit 30 marks a leaf of one of OUR sub-trees (rt_layout.h): its box is a conservative bound, not a
+// reference box.  Inner nodes: count word -1 = reference node, -2 = sub-tree node.
 #define RT_LEAF_COUNT_MASK 0x0fffffff
 #define RT_LEAF_KIND_SHIFT 28
+#define RT_LEAF_SUB_BIT (1 << 30)
+#define RT_INNER_REF (-1)
+#define RT_INNER_SUB (-2)
 enum { RT_LEAF_MIXED = 0, RT_LEAF_TRIANGLES = 1, RT_LEAF_SPHERES = 2 };
 
 struct FrameParams {
@@ -71,43 +89,45 @@ struct FrameParams {
 // Exact helpers (GLSL-spec definitions, listed in DESIGN.md)
 // ---------------------------------------------------------------------------
 struct V3 { float x, y, z; };
-__device__ __forceinline__ V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
-__device__ __forceinline__ V3 mk(const float* p) { return mk(p[0], p[1], p[2]); }
-__device__ __forceinline__ V3 xyz(float4 q) { return mk(q.x, q.y, q.z); }
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
-__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
-__device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
-__device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
-__device__ __forceinline__ float gmin(float x, float y) { return y < x ? y : x; }
-__device__ __forceinline__ float gmax(float x, float y) { return x < y ? y : x; }
-__device__ __forceinline__ float dot3(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-__device__ __forceinline__ float length3(V3 v) { return sqrtf(dot3(v, v)); }
-__device__ __forceinline__ float distance3(V3 a, V3 b) { return length3(a - b); }
-__device__ __forceinline__ V3 normalize3(V3 v) { float inv = 1.0f / sqrtf(dot3(v, v)); return v * inv; }
-__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+RT_DEV V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+RT_DEV V3 mk(const float* p) { return mk(p[0], p[1], p[2]); }
+RT_DEV V3 xyz(float4 q) { return mk(q.x, q.y, q.z); }
+RT_DEV V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+RT_DEV V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+RT_DEV V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+RT_DEV V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+RT_DEV V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+RT_DEV V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+RT_DEV V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+RT_DEV float gmin(float x, float y) { return y < x ? y : x; }
+RT_DEV float gmax(float x, float y) { return x < y ? y : x; }
+RT_DEV float dot3(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+RT_DEV float length3(V3 v) { return sqrtf(dot3(v, v)); }
+RT_DEV float distance3(V3 a, V3 b) { return length3(a - b); }
+RT_DEV V3 normalize3(V3 v) { float inv = 1.0f / sqrtf(dot3(v, v)); return v * inv; }
+RT_DEV V3 cross3(V3 a, V3 b) {
     return mk(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
 }
-__device__ __forceinline__ V3 reflect3(V3 I, V3 N) { float d = dot3(N, I); return I - N * d * 2.0f; }
-__device__ __forceinline__ float mix1(float x, float y, float a) { return x * (1.0f - a) + y * a; }
+RT_DEV V3 reflect3(V3 I, V3 N) { float d = dot3(N, I); return I - N * d * 2.0f; }
+RT_DEV float mix1(float x, float y, float a) { return x * (1.0f - a) + y * a; }
 
 struct Ray {
     V3 o, d;
     V3 inv;        // 1/d, hoisted out of the per-node slab test (gpu_shader.comp:365)
     float aa;      // dot(d,d), hoisted out of the sphere test (:250)
     bool fast;     // origin and 1/d all finite: (bound - o) * inv can never be NaN for finite bounds
+    bool sub;      // fast and |o|_inf <= omax: the sub-tree boxes may cull for this ray
 };
-__device__ __forceinline__ bool bounded3(V3 v, float lim) {      // false for NaN / inf
+RT_DEV bool bounded3(V3 v, float lim) {      // false for NaN / inf
     return fabsf(v.x) <= lim && fabsf(v.y) <= lim && fabsf(v.z) <= lim;
 }
 #define RT_SAFE_COORD 1e37f   // |bound|,|origin| <= 1e37: (bound - origin) cannot overflow to inf
-__device__ __forceinline__ Ray make_ray(V3 o, V3 d, bool boxesFinite) {
+RT_DEV Ray make_ray(V3 o, V3 d, bool boxesFinite, float omax) {
     Ray r; r.o = o; r.d = d;
     r.inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     r.aa = dot3(d, d);
     r.fast = boxesFinite && bounded3(o, RT_SAFE_COORD) && bounded3(r.inv, 3.402823466e38f);
+    r.sub = r.fast && bounded3(o, omax);
     return r;
 }
 
@@ -116,7 +136,7 @@ struct Prim { float4 q0, q1, q2, q3; int type; };
 
 // Ray-independent terms of a raw std430 shape, with the shader's own operation
 // order (gpu_shader.comp:218-229 edges/dots, :305-307 wall basis, :252 r*r).
-__device__ __forceinline__ Prim prim_from_shape(const rt_flat_shape* __restrict__ s) {
+RT_DEV Prim prim_from_shape(const rt_flat_shape* __restrict__ s) {
     Prim p;
     p.type = s->type;
     p.q0 = p.q1 = p.q2 = p.q3 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -149,7 +169,7 @@ __device__ __forceinline__ Prim prim_from_shape(const rt_flat_shape* __restrict_
 // Primitive tests.  Return true for an INNER hit and set hp (OUTER == no hit for
 // every caller in the shader).  a5-a9 of SURVEY.md §8(a).
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ bool plane_stage(float4 q0, const Ray& r, V3& hp) {
+RT_DEV bool plane_stage(float4 q0, const Ray& r, V3& hp) {
     V3 n = xyz(q0);
     float np = dot3(n, r.d);
     // INNER needs np > 0 and t > 0 (np == 0 -> NONE, np < 0 -> OUTER/NONE, NaN -> NONE).
@@ -164,7 +184,7 @@ __device__ __forceinline__ bool plane_stage(float4 q0, const Ray& r, V3& hp) {
     return true;
 }
 
-__device__ __forceinline__ bool hit_sphere(float4 q0, const Ray& r, V3& hp) {
+RT_DEV bool hit_sphere(float4 q0, const Ray& r, V3& hp) {
     V3 oc = r.o - xyz(q0);
     float bb = 2.0f * dot3(r.d, oc);
     float cc = dot3(oc, oc) - q0.w;
@@ -177,14 +197,14 @@ __device__ __forceinline__ bool hit_sphere(float4 q0, const Ray& r, V3& hp) {
     return true;
 }
 
-__device__ __forceinline__ bool wall_stage2(float4 q1, float4 q2, float4 q3, V3 hp) {
+RT_DEV bool wall_stage2(float4 q1, float4 q2, float4 q3, V3 hp) {
     V3 local = hp - xyz(q1);
     float uProj = dot3(local, xyz(q2));
     float vProj = dot3(local, xyz(q3));
     return !(uProj < 0.0f || uProj > q1.w || vProj < 0.0f || vProj > q2.w);
 }
 
-__device__ __forceinline__ bool bary_stage2(float4 q1, float4 q2, float4 q3, V3 hp) {
+RT_DEV bool bary_stage2(float4 q1, float4 q2, float4 q3, V3 hp) {
     V3 toPoint = hp - xyz(q1);
     V3 e1 = xyz(q2), e2 = xyz(q3);
     float d00 = q1.w, d01 = q2.w, d11 = q3.w;
@@ -203,7 +223,7 @@ __device__ __forceinline__ bool bary_stage2(float4 q1, float4 q2, float4 q3, V3 
     return !(u < 0.0f || v < 0.0f || w < 0.0f);
 }
 
-__device__ __forceinline__ bool hit_tri_mt(float4 q1, float4 q2, float4 q3, const Ray& r, V3& hp) {
+RT_DEV bool hit_tri_mt(float4 q1, float4 q2, float4 q3, const Ray& r, V3& hp) {
     V3 e1 = xyz(q2), e2 = xyz(q3);
     V3 h = cross3(r.d, e2);
     float a = dot3(e1, h);
@@ -219,6 +239,42 @@ __device__ __forceinline__ bool hit_tri_mt(float4 q1, float4 q2, float4 q3, cons
     if (!(t > 0.0f)) return false;
     hp = r.o + t * r.d;
     return true;
+}
+
+// ---------------------------------------------------------------------------
+// Box tests (a4) and the per-type dispatch
+// ---------------------------------------------------------------------------
+// Slab test with the shader's select semantics for min/max (a4, :364-377).
+RT_DEV bool slab(const Ray& r, float4 a, float4 b) {
+    float t0x = (a.x - r.o.x) * r.inv.x, t1x = (b.x - r.o.x) * r.inv.x;
+    float t0y = (a.y - r.o.y) * r.inv.y, t1y = (b.y - r.o.y) * r.inv.y;
+    float t0z = (a.z - r.o.z) * r.inv.z, t1z = (b.z - r.o.z) * r.inv.z;
+    float tMin = gmax(gmax(gmin(t0x, t1x), gmin(t0y, t1y)), gmin(t0z, t1z));
+    float tMax = gmin(gmin(gmax(t0x, t1x), gmax(t0y, t1y)), gmax(t0z, t1z));
+    return tMax >= tMin && tMax > 0.0f;
+}
+// Same arithmetic with single-instruction FMNMX min/max.  Legal only when no operand can be
+// NaN (Ray::fast): then fminf/fmaxf and the GLSL selects return the same value up to the sign
+// of zero, which the two comparisons below cannot see.
+RT_DEV bool slab_fast(const Ray& r, float4 a, float4 b) {
+    float t0x = (a.x - r.o.x) * r.inv.x, t1x = (b.x - r.o.x) * r.inv.x;
+    float t0y = (a.y - r.o.y) * r.inv.y, t1y = (b.y - r.o.y) * r.inv.y;
+    float t0z = (a.z - r.o.z) * r.inv.z, t1z = (b.z - r.o.z) * r.inv.z;
+    float tMin = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+    float tMax = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+    return tMax >= tMin && tMax > 0.0f;
+}
+
+template <bool MT>
+RT_DEV bool test_prim(const Prim& p, const Ray& r, V3& hp) {
+    if (p.type == RT_SHAPE_TRIANGLE) {
+        if (MT) return hit_tri_mt(p.q1, p.q2, p.q3, r, hp);
+        return plane_stage(p.q0, r, hp) && bary_stage2(p.q1, p.q2, p.q3, hp);
+    }
+    if (p.type == RT_SHAPE_SPHERE) return hit_sphere(p.q0, r, hp);
+    if (p.type == RT_SHAPE_WALL) return plane_stage(p.q0, r, hp) && wall_stage2(p.q1, p.q2, p.q3, hp);
+    if (p.type == RT_SHAPE_PLANE) return plane_stage(p.q0, r, hp);
+    return false;
 }
 
 }  // namespace rt

@@ -19,39 +19,6 @@ struct Hit { float dist; int slot; V3 p; };
 struct Tally { unsigned long long v[8]; };
 #define RT_TALLY(i, n) do { if (COUNT) tl.v[i] += (n); } while (0)
 
-// Slab test with the shader's select semantics for min/max (a4, :364-377).
-__device__ __forceinline__ bool slab(const Ray& r, float4 a, float4 b) {
-    float t0x = (a.x - r.o.x) * r.inv.x, t1x = (b.x - r.o.x) * r.inv.x;
-    float t0y = (a.y - r.o.y) * r.inv.y, t1y = (b.y - r.o.y) * r.inv.y;
-    float t0z = (a.z - r.o.z) * r.inv.z, t1z = (b.z - r.o.z) * r.inv.z;
-    float tMin = gmax(gmax(gmin(t0x, t1x), gmin(t0y, t1y)), gmin(t0z, t1z));
-    float tMax = gmin(gmin(gmax(t0x, t1x), gmax(t0y, t1y)), gmax(t0z, t1z));
-    return tMax >= tMin && tMax > 0.0f;
-}
-// Same arithmetic with single-instruction FMNMX min/max.  Legal only when no operand can be
-// NaN (Ray::fast): then fminf/fmaxf and the GLSL selects return the same value up to the sign
-// of zero, which the two comparisons below cannot see.
-__device__ __forceinline__ bool slab_fast(const Ray& r, float4 a, float4 b) {
-    float t0x = (a.x - r.o.x) * r.inv.x, t1x = (b.x - r.o.x) * r.inv.x;
-    float t0y = (a.y - r.o.y) * r.inv.y, t1y = (b.y - r.o.y) * r.inv.y;
-    float t0z = (a.z - r.o.z) * r.inv.z, t1z = (b.z - r.o.z) * r.inv.z;
-    float tMin = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
-    float tMax = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-    return tMax >= tMin && tMax > 0.0f;
-}
-
-template <bool MT>
-__device__ __forceinline__ bool test_prim(const Prim& p, const Ray& r, V3& hp) {
-    if (p.type == RT_SHAPE_TRIANGLE) {
-        if (MT) return hit_tri_mt(p.q1, p.q2, p.q3, r, hp);
-        return plane_stage(p.q0, r, hp) && bary_stage2(p.q1, p.q2, p.q3, hp);
-    }
-    if (p.type == RT_SHAPE_SPHERE) return hit_sphere(p.q0, r, hp);
-    if (p.type == RT_SHAPE_WALL) return plane_stage(p.q0, r, hp) && wall_stage2(p.q1, p.q2, p.q3, hp);
-    if (p.type == RT_SHAPE_PLANE) return plane_stage(p.q0, r, hp);
-    return false;
-}
-
 // One BVH query of one lane.  Closest-hit (a3): best starts at 1e20 and every candidate with
 // dist < best replaces it (strict '<', first in visit order wins ties, :410-411).  Shadow
 // (a12): the shader runs a full closest-hit query and then tests hitDist < lightDist; "some
@@ -66,9 +33,14 @@ struct Query {
 };
 struct Cand { float dist; int slot; V3 p; };
 
-__device__ __forceinline__ void offer(Query& q, int s, V3 hp) {
+// Candidate acceptance.  The reference keeps the FIRST candidate in its visit order among equal
+// distances (strict '<', :410-411).  Slots of our sub-trees are not in that order, so equal
+// distances are resolved by the slot's rank in the reference sequence (S.prank) instead.
+__device__ __forceinline__ void offer(const DeviceScene& S, Query& q, int s, V3 hp, bool anyMode) {
     const float dist = distance3(q.r.o, hp);
-    if (dist < q.best) { q.best = dist; q.slot = s; q.p = hp; }
+    bool take = dist < q.best;
+    if (!anyMode && dist == q.best && q.slot >= 0) take = __ldg(S.prank + s) < __ldg(S.prank + q.slot);
+    if (take) { q.best = dist; q.slot = s; q.p = hp; }
 }
 
 // Triangle leaf, Barycentric mode.  The plane stage of four consecutive slots is evaluated as
@@ -99,7 +71,7 @@ __device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, Query&
                     const V3 hp = r.o + t * r.d;
                     if (bary_stage2(__ldg(S.q1 + s + i), __ldg(S.q2 + s + i), __ldg(S.q3 + s + i), hp)) {
                         const int before = q.slot;
-                        offer(q, s + i, hp);
+                        offer(S, q, s + i, hp, anyMode);
                         if (anyMode && q.slot != before) return true;
                     }
                 }
@@ -115,8 +87,9 @@ __device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, Query&
 template <bool MT>
 __device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const float4* __restrict__ q1,
                                           const float4* __restrict__ q2, const float4* __restrict__ q3,
-                                          const int* __restrict__ ptype, Ray r, int s0, int end, float best, int anyMode) {
-    Cand c; c.dist = best; c.slot = -1; c.p = mk(0.f, 0.f, 0.f);
+                                          const int* __restrict__ ptype, const int* __restrict__ prank, Ray r, int s0, int end,
+                                          float best, int bestSlot, int anyMode) {
+    Cand c; c.dist = best; c.slot = bestSlot; c.p = mk(0.f, 0.f, 0.f);
     for (int s = s0; s < end; ++s) {
         const int type = __ldg(ptype + s);
         V3 hp;
@@ -133,7 +106,9 @@ __device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const f
         }
         if (hit) {
             const float dist = distance3(r.o, hp);
-            if (dist < c.dist) { c.dist = dist; c.slot = s; c.p = hp; if (anyMode) break; }
+            bool take = dist < c.dist;
+            if (!anyMode && dist == c.dist && c.slot >= 0) take = __ldg(prank + s) < __ldg(prank + c.slot);
+            if (take) { c.dist = dist; c.slot = s; c.p = hp; if (anyMode) break; }
         }
     }
     return c;
@@ -163,22 +138,25 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
         const int lnk = __float_as_int(a.w);
         const bool mine = (k == km);
         RT_TALLY(4, mine ? 1 : 0);
-        const bool hit = mine && (r.fast ? slab_fast(r, a, b) : slab(r, a, b));
+        // reference nodes: the shader's exact slab test; nodes of our own sub-trees (cw == -2 or
+        // leaf bit 30): conservative boxes, skipped only for rays the margins were computed for
+        const bool ours = cw == RT_INNER_SUB || (cw >= 0 && (cw & RT_LEAF_SUB_BIT));
+        const bool hit = mine && (ours ? (!r.sub || slab_fast(r, a, b)) : (r.fast ? slab_fast(r, a, b) : slab(r, a, b)));
         if (cw < 0) {                                   // inner: hit -> next in list, miss -> skip subtree
             if (mine) k = hit ? km + 1 : lnk;
             continue;
         }
         if (mine) k = km + 1;
         if (hit) {
-            const int cnt = cw & RT_LEAF_COUNT_MASK, kind = cw >> RT_LEAF_KIND_SHIFT;
+            const int cnt = cw & RT_LEAF_COUNT_MASK, kind = (cw >> RT_LEAF_KIND_SHIFT) & 3;
             const int end = lnk + cnt;
             RT_TALLY(5, cnt);
             bool stop = false;
             if (!MT && kind == RT_LEAF_TRIANGLES) {
                 stop = leaf_triangles_bary(S, q, lnk, end, anyMode);
             } else {
-                const Cand c = leaf_generic<MT>(S.q0, S.q1, S.q2, S.q3, S.ptype, r, lnk, end, q.best, anyMode ? 1 : 0);
-                if (c.slot >= 0) { q.best = c.dist; q.slot = c.slot; q.p = c.p; stop = anyMode; }
+                const Cand c = leaf_generic<MT>(S.q0, S.q1, S.q2, S.q3, S.ptype, S.prank, r, lnk, end, q.best, q.slot, anyMode ? 1 : 0);
+                if (c.slot != q.slot) { q.best = c.dist; q.slot = c.slot; q.p = c.p; stop = anyMode; }
             }
             if (stop) k = RT_DONE;
         }
@@ -256,7 +234,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
     const V3 camP = mk(P.camP);
     V3 ipp = ((camP + mk(P.camF)) + (ndcX * P.planeW / 2.0f) * mk(P.camR)) + (ndcY * P.planeH / 2.0f) * mk(P.camU);
     const bool bf = S.boxesFinite != 0;
-    Ray ray = make_ray(camP, normalize3(ipp - camP), bf);
+    Ray ray = make_ray(camP, normalize3(ipp - camP), bf, S.omax);
     const V3 lpos = mk(P.lightPos), lcol = mk(P.lightCol);
     V3 acc = mk(0.f, 0.f, 0.f), att = mk(1.f, 1.f, 1.f);
     idOut = -1;
@@ -273,7 +251,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
         if (!shadowStep) {
             q.r = ray; q.best = 1e20f;
         } else {
-            q.r = make_ray(hp + nrm * (P.useBVH ? 1e-3f : 1e-5f), normalize3(lpos - hp), bf);
+            q.r = make_ray(hp + nrm * (P.useBVH ? 1e-3f : 1e-5f), normalize3(lpos - hp), bf, S.omax);
             // dist < 1e20 && dist < lightDist  ==  dist < min; a NaN lightDist can never be beaten
             q.best = lightDist < 1e20f ? lightDist : (lightDist >= 1e20f ? 1e20f : -1.0f);
         }
@@ -306,7 +284,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
             acc = acc + att * pc;
             if (!(m.specular > 0.0f)) { alive = false; continue; }
             const V3 rd = reflect3(ray.d, nrm);
-            ray = make_ray(hp + nrm * 1e-3f, rd, bf);
+            ray = make_ray(hp + nrm * 1e-3f, rd, bf, S.omax);
             if (P.useFresnel) {
                 float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
                 fr = gmin(gmax(fr, 0.0f), 0.8f);
@@ -383,11 +361,13 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
 // K2: repack.  nodes: gather the raw 48-byte nodes into the threaded layout;
 // prims: gather the raw 192-byte shapes into float4 SoA in visit order.
 // ---------------------------------------------------------------------------
-__global__ void repack_nodes_kernel(const rt_flat_node* __restrict__ raw, const int* __restrict__ order,
-                                    const int2* __restrict__ linkCnt, float4* __restrict__ out, int n) {
+__global__ void repack_nodes_kernel(const rt_flat_node* __restrict__ raw, const float4* __restrict__ subBox,
+                                    const int* __restrict__ order, const int2* __restrict__ linkCnt,
+                                    float4* __restrict__ out, int n) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
-    const float4* src = reinterpret_cast<const float4*>(raw + order[k]);
+    const int o = order[k];                 // >= 0: raw reference node; < 0: sub-tree node -1-o (host-computed box)
+    const float4* src = o >= 0 ? reinterpret_cast<const float4*>(raw + o) : subBox + 2 * (size_t)(-1 - o);
     const float4 mn = __ldg(src), mx = __ldg(src + 1);
     const int2 lc = linkCnt[k];
     out[2 * k]     = make_float4(mn.x, mn.y, mn.z, __int_as_float(lc.x));

@@ -1,0 +1,409 @@
+// rt_layout.h — host-side builder of the device scene layout (pure C++17, no CUDA).
+//
+// Input: the reference's raw FlatNode[] / bvhIndices[] / FlatShape[] (src/flatStructures.hpp).
+// Output: the threaded node list the render kernel walks:
+//   * reference nodes in the reference's visit order (root = last raw node, right child first,
+//     gpu_shader.comp:386, 424-425), each with a skip link;
+//   * FAT leaves (more than RT_FAT_LEAF shapes — the reference builder stops splitting as soon as
+//     one side of a midpoint split is empty, src/main.cpp:1156-1161, and leaves reach hundreds of
+//     shapes) become inner nodes over a private binned-SAH sub-tree whose boxes are CONSERVATIVE
+//     bounds of each primitive's acceptance region (see prim_bound): a ray that misses such a box
+//     cannot be accepted by any primitive below it, so skipping the subtree changes no decision.
+//     Primitives whose acceptance region cannot be bounded (infinite planes, NaN wall bases,
+//     degenerate / sliver triangles, non-finite data) stay in an "always tested" leaf.
+//   * every primitive slot carries its RANK = position in the reference's own primitive visit
+//     sequence; the kernel resolves equal-distance candidates by smaller rank, which is exactly
+//     "first candidate in visit order wins" (strict '<', gpu_shader.comp:410-411) whatever the
+//     order the sub-tree presents them in.
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "../../include/rt_flat.h"
+
+namespace rtl {
+
+#define RT_FAT_LEAF      8      // reference leaves with more shapes than this get a sub-tree
+#define RT_SUB_LEAF      4      // sub-tree leaves hold at most this many primitives
+#define RTL_COUNT_MASK   0x0fffffff
+#define RTL_KIND_SHIFT   28
+#define RTL_SUB_BIT      (1 << 30)   // leaf count word: box is one of ours (conservative test allowed)
+#define RTL_INNER_REF    (-1)        // inner count word: reference node (exact reference slab test)
+#define RTL_INNER_SUB    (-2)        // inner count word: sub-tree node
+enum { KIND_MIXED = 0, KIND_TRIANGLES = 1, KIND_SPHERES = 2 };
+
+struct Box {
+    float mn[3], mx[3];
+    void reset() { for (int a = 0; a < 3; ++a) { mn[a] = INFINITY; mx[a] = -INFINITY; } }
+    void grow(const Box& b) { for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], b.mn[a]); mx[a] = std::max(mx[a], b.mx[a]); } }
+    void grow(const double p[3]) { for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], (float)p[a]); mx[a] = std::max(mx[a], (float)p[a]); } }
+    double area() const {
+        double d[3] = {(double)mx[0] - mn[0], (double)mx[1] - mn[1], (double)mx[2] - mn[2]};
+        return d[0] < 0 ? 0.0 : 2.0 * (d[0] * d[1] + d[1] * d[2] + d[2] * d[0]);
+    }
+};
+
+// ---------------------------------------------------------------------------
+// Conservative bound of a primitive's ACCEPTANCE REGION.
+//
+// Needed property: if get_intersection (gpu_shader.comp:242-328, either triangle mode) returns
+// INNER for a ray whose origin satisfies |o|_inf <= omax, then the ray's line passes through the
+// returned box (with a positive exit parameter).  fp32 rounding makes the accepted set slightly
+// larger than the geometric primitive, by an amount that scales with the magnitude of the ray
+// origin (e.g. the sphere discriminant bb^2 - 4 aa cc carries an absolute error ~ eps |o-c|^2),
+// so the margins below are expressed with S = omax + |primitive coordinates| and E = 2^-23, with
+// generous safety factors.  Rays with a larger origin ignore the sub-tree boxes in the kernel.
+// Returns false = unbounded (primitive goes to the always-tested leaf).
+// ---------------------------------------------------------------------------
+inline bool finite3(const float* p) { return std::isfinite(p[0]) && std::isfinite(p[1]) && std::isfinite(p[2]); }
+inline double amax3(const float* p) { return std::max(std::fabs((double)p[0]), std::max(std::fabs((double)p[1]), std::fabs((double)p[2]))); }
+
+inline void inflate(Box& b, double m) {
+    for (int a = 0; a < 3; ++a) {
+        // outward rounding of the double arithmetic to float
+        b.mn[a] = std::nextafter((float)((double)b.mn[a] - m), -INFINITY);
+        b.mx[a] = std::nextafter((float)((double)b.mx[a] + m), INFINITY);
+    }
+}
+
+inline bool prim_bound(const rt_flat_shape& s, double omax, Box& out) {
+    const double E = 1.1920929e-7;
+    out.reset();
+    if (s.type == RT_SHAPE_SPHERE) {
+        if (!finite3(s.sphereCenter) || !std::isfinite(s.sphereRadius)) return false;
+        const double S = omax + amax3(s.sphereCenter) + std::fabs((double)s.sphereRadius);
+        const double r = std::fabs((double)s.sphereRadius);
+        // D > 0 can be decided wrongly while p^2 < r^2 + c E |o-c|^2 (p = distance line-centre)
+        const double reach = std::sqrt(r * r + 64.0 * E * S * S) + 64.0 * E * S;
+        if (!(reach < 1e30)) return false;
+        double c[3] = {s.sphereCenter[0], s.sphereCenter[1], s.sphereCenter[2]};
+        out.grow(c);
+        inflate(out, reach);
+        return true;
+    }
+    if (s.type == RT_SHAPE_WALL) {
+        const float* n = s.planeNormal;
+        if (!finite3(n) || !finite3(s.wallStart) || !std::isfinite(s.planeD) || !std::isfinite(s.wallWidth) || !std::isfinite(s.wallHeight)) return false;
+        const double nn = (double)n[0] * n[0] + (double)n[1] * n[1] + (double)n[2] * n[2];
+        if (!(nn > 1e-12) || !(nn < 1e12)) return false;
+        // the shader's tangent basis (gpu_shader.comp:305-307), here in double; a degenerate first
+        // cross product gives NaN in fp32 (the wall then accepts its whole plane)
+        double u[3] = {-(double)n[2], 0.0, (double)n[0]};                 // n x (0,1,0)
+        double ul = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+        if (!(ul > 1e-3 * std::sqrt(nn))) return false;                    // near the NaN / fallback switch: do not bound
+        for (double& x : u) x /= ul;
+        double v[3] = {n[1] * u[2] - u[1] * n[2], n[2] * u[0] - u[2] * n[0], n[0] * u[1] - u[0] * n[1]};
+        double vl = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        if (!(vl > 0)) return false;
+        for (double& x : v) x /= vl;
+        const double w = s.wallWidth, h = s.wallHeight;
+        if (w < 0 || h < 0) { /* empty acceptance set; still bound it by the corner */ }
+        const double S = omax + amax3(s.wallStart) + std::fabs(w) + std::fabs(h);
+        for (int i = 0; i < 4; ++i) {
+            double a = (i & 1) ? std::max(w, 0.0) : 0.0, b = (i & 2) ? std::max(h, 0.0) : 0.0, c[3];
+            for (int k = 0; k < 3; ++k) c[k] = s.wallStart[k] + a * u[k] + b * v[k];
+            // hit points lie on the stored plane (n, D): project the corner onto it along n
+            const double off = ((double)n[0] * c[0] + (double)n[1] * c[1] + (double)n[2] * c[2] + (double)s.planeD) / nn;
+            for (int k = 0; k < 3; ++k) c[k] -= off * n[k];
+            if (!std::isfinite(c[0]) || !std::isfinite(c[1]) || !std::isfinite(c[2])) return false;
+            out.grow(c);
+        }
+        const double m = 128.0 * E * (S + amax3(out.mn) + amax3(out.mx));
+        if (!(m < 1e30)) return false;
+        inflate(out, m);
+        return true;
+    }
+    if (s.type == RT_SHAPE_TRIANGLE) {
+        const float* n = s.planeNormal;
+        if (!finite3(n) || !finite3(s.triP1) || !finite3(s.triP2) || !finite3(s.triP3) || !std::isfinite(s.planeD)) return false;
+        double P[3][3], e1[3], e2[3];
+        for (int k = 0; k < 3; ++k) { P[0][k] = s.triP1[k]; P[1][k] = s.triP2[k]; P[2][k] = s.triP3[k]; e1[k] = P[1][k] - P[0][k]; e2[k] = P[2][k] - P[0][k]; }
+        const double d00 = e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2], d11 = e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2];
+        const double d01 = e1[0] * e2[0] + e1[1] * e2[1] + e1[2] * e2[2];
+        const double denom = d00 * d11 - d01 * d01;
+        if (!(d00 > 0) || !(d11 > 0)) return false;
+        const double sin2 = denom / (d00 * d11);
+        if (!(sin2 > 1e-4)) return false;                                  // sliver / degenerate: hits everywhere on its plane
+        const double l1 = std::sqrt(d00), l2 = std::sqrt(d11);
+        if (std::max(l1, l2) > 1e4 * std::min(l1, l2)) return false;
+        double nt[3] = {e1[1] * e2[2] - e2[1] * e1[2], e1[2] * e2[0] - e2[2] * e1[0], e1[0] * e2[1] - e2[0] * e1[1]};
+        const double ntl = std::sqrt(nt[0] * nt[0] + nt[1] * nt[1] + nt[2] * nt[2]);
+        const double nn = (double)n[0] * n[0] + (double)n[1] * n[1] + (double)n[2] * n[2];
+        if (!(nn > 1e-12) || !(nn < 1e12)) return false;
+        const double cosv = ((double)n[0] * nt[0] + (double)n[1] * nt[1] + (double)n[2] * nt[2]) / (ntl * std::sqrt(nn));
+        // Barycentric mode accepts points of the STORED plane (n, D) whose projection along the
+        // triangle normal falls into the triangle; animated triangles carry a stale plane
+        // (src/main.cpp:1101-1106), so the region is the triangle projected onto (n, D) along nt.
+        if (!(std::fabs(cosv) > 0.05)) return false;
+        const double S = omax + amax3(s.triP1) + amax3(s.triP2) + amax3(s.triP3);
+        // barycentric fuzz (relative to the triangle, independent of the ray origin: the origin-dependent
+        // error of the hit point itself is the absolute margin m below): accepted while u,v,w >= -delta  ==  triangle scaled by (1+3 delta) about its centroid
+        const double delta = 64.0 * E * (1.0 + (l1 + l2) / std::min(l1, l2)) / sin2;
+        if (!(delta < 0.5)) return false;
+        double cen[3];
+        for (int k = 0; k < 3; ++k) cen[k] = (P[0][k] + P[1][k] + P[2][k]) / 3.0;
+        const double nd = (double)n[0] * nt[0] + (double)n[1] * nt[1] + (double)n[2] * nt[2];
+        for (int i = 0; i < 3; ++i) {
+            double q[3];
+            for (int k = 0; k < 3; ++k) q[k] = cen[k] + (P[i][k] - cen[k]) * (1.0 + 3.0 * delta);
+            out.grow(q);                                                   // Moller-Trumbore mode: the triangle itself
+            const double off = ((double)n[0] * q[0] + (double)n[1] * q[1] + (double)n[2] * q[2] + (double)s.planeD) / nd;
+            for (int k = 0; k < 3; ++k) q[k] -= off * nt[k];
+            if (!std::isfinite(q[0]) || !std::isfinite(q[1]) || !std::isfinite(q[2])) return false;
+            out.grow(q);                                                   // Barycentric mode: its image on the stored plane
+        }
+        const double m = 128.0 * E * (S + amax3(out.mn) + amax3(out.mx)) / std::sqrt(sin2) / std::fabs(cosv);
+        if (!(m < 1e30)) return false;
+        inflate(out, m);
+        return true;
+    }
+    return false;   // infinite planes (type 1) and unknown types
+}
+
+// ---------------------------------------------------------------------------
+// Sub-tree over the bounded primitives of one fat leaf: binned SAH, leaves <= RT_SUB_LEAF.
+// ---------------------------------------------------------------------------
+struct SubNode { Box box; int left = -1, right = -1; int first = 0, count = 0; };   // leaf: left == -1, prims [first, first+count) of `items`
+
+struct SubBuilder {
+    const std::vector<Box>& pb;          // bound per item
+    std::vector<int>& items;             // permuted in place
+    std::vector<SubNode> nodes;
+    SubBuilder(const std::vector<Box>& b, std::vector<int>& it) : pb(b), items(it) {}
+
+    int build(int first, int count) {
+        const int id = (int)nodes.size();
+        nodes.emplace_back();
+        Box bb; bb.reset();
+        Box cb; cb.reset();
+        for (int i = first; i < first + count; ++i) {
+            const Box& b = pb[(size_t)items[(size_t)i]];
+            bb.grow(b);
+            double c[3] = {0.5 * ((double)b.mn[0] + b.mx[0]), 0.5 * ((double)b.mn[1] + b.mx[1]), 0.5 * ((double)b.mn[2] + b.mx[2])};
+            cb.grow(c);
+        }
+        nodes[(size_t)id].box = bb; nodes[(size_t)id].first = first; nodes[(size_t)id].count = count;
+        if (count <= RT_SUB_LEAF) return id;
+        // binned SAH over the centroid bounds
+        const int NB = 16;
+        int bestAxis = -1, bestSplit = -1; double bestCost = INFINITY;
+        for (int a = 0; a < 3; ++a) {
+            const double lo = cb.mn[a], ext = (double)cb.mx[a] - lo;
+            if (!(ext > 0)) continue;
+            Box bins[NB]; int cnt[NB];
+            for (int b = 0; b < NB; ++b) { bins[b].reset(); cnt[b] = 0; }
+            for (int i = first; i < first + count; ++i) {
+                const Box& b = pb[(size_t)items[(size_t)i]];
+                int k = (int)((0.5 * ((double)b.mn[a] + b.mx[a]) - lo) / ext * NB);
+                k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
+                bins[k].grow(b); cnt[k]++;
+            }
+            double rightArea[NB]; int rightCnt[NB];
+            Box acc; acc.reset(); int n = 0;
+            for (int b = NB - 1; b > 0; --b) { acc.grow(bins[b]); n += cnt[b]; rightArea[b] = acc.area(); rightCnt[b] = n; }
+            acc.reset(); n = 0;
+            for (int b = 0; b < NB - 1; ++b) {
+                acc.grow(bins[b]); n += cnt[b];
+                if (n == 0 || rightCnt[b + 1] == 0) continue;
+                const double cost = acc.area() * n + rightArea[b + 1] * rightCnt[b + 1];
+                if (cost < bestCost) { bestCost = cost; bestAxis = a; bestSplit = b; }
+            }
+        }
+        int mid;
+        if (bestAxis < 0) {
+            mid = first + count / 2;                                        // identical centroids: split by count
+        } else {
+            const int a = bestAxis;
+            const double lo = cb.mn[a], ext = (double)cb.mx[a] - lo;
+            auto binOf = [&](int item) {
+                const Box& b = pb[(size_t)item];
+                int k = (int)((0.5 * ((double)b.mn[a] + b.mx[a]) - lo) / ext * NB);
+                return k < 0 ? 0 : k >= NB ? NB - 1 : k;
+            };
+            auto it = std::stable_partition(items.begin() + first, items.begin() + first + count, [&](int item) { return binOf(item) <= bestSplit; });
+            mid = (int)(it - items.begin());
+            if (mid == first || mid == first + count) mid = first + count / 2;
+        }
+        const int l = build(first, mid - first);
+        const int r = build(mid, first + count - mid);
+        nodes[(size_t)id].left = l; nodes[(size_t)id].right = r;
+        return id;
+    }
+};
+
+// ---------------------------------------------------------------------------
+// The layout.
+// ---------------------------------------------------------------------------
+struct Layout {
+    // per emitted node k
+    std::vector<int> src;        // raw node index (reference node) or -1-j for sub node j (box = subBox[j])
+    std::vector<int> link;       // inner: first node after the subtree; leaf: first primitive slot
+    std::vector<int> cw;         // count word (see RTL_* above)
+    // per primitive slot
+    std::vector<int> pshape;     // original shape index
+    std::vector<int> prank;      // position in the reference's primitive visit sequence
+    // sub nodes
+    std::vector<Box> subBox;     // box of sub node j
+    std::vector<int> subPos;     // emitted position of sub node j
+    double omax = 0;             // the margins hold for ray origins with |o|_inf <= omax
+    int nRefLeavesFat = 0;
+    const char* error = nullptr;
+
+    int nodes() const { return (int)src.size(); }
+    int prims() const { return (int)pshape.size(); }
+};
+
+inline int leaf_kind(const rt_flat_shape* shapes, const int* slots, int n) {
+    if (n == 0) return KIND_MIXED;
+    int nTri = 0, nSph = 0;
+    for (int i = 0; i < n; ++i) { const int t = shapes[slots[i]].type; nTri += t == RT_SHAPE_TRIANGLE; nSph += t == RT_SHAPE_SPHERE; }
+    return nTri == n ? KIND_TRIANGLES : nSph == n ? KIND_SPHERES : KIND_MIXED;
+}
+
+// Builds the layout.  subtrees = false reproduces the plain reference walk (every leaf kept).
+// Returns false and sets L.error on a malformed BVH (what the shader would blindly trust).
+inline bool build_layout(const rt_flat_node* nd, int nNodes, const int32_t* indices, size_t nIndices,
+                         const rt_flat_shape* shapes, int nShapes, bool subtrees, double omax, Layout& L) {
+    L = Layout();
+    L.omax = omax;
+    if (nNodes <= 0) return true;
+    struct Item { int node; int depth; int sub; int parent; };       // node >= 0: raw node; node == -1: entry `sub` of the pending sub list
+    // pending sub-tree emissions are described by (builder index, sub node id)
+    struct Pending { int kind; int a, b, c; };            // kind 0: always-leaf (slot range a..a+b), kind 1: sub node (tree a, node b)
+    std::vector<Pending> pend;
+    std::vector<SubBuilder*> trees;
+    std::vector<std::vector<int>*> treeItems;
+    std::vector<std::vector<Box>*> treeBoxes;
+    std::vector<int> treeSlot0;                           // first slot of the tree's bounded primitives
+    std::vector<Item> st; st.push_back({nNodes - 1, 1, -1, -1});
+    std::vector<int> parent;                              // emitted position of each emitted node's parent
+    const size_t limit = (size_t)nNodes * 4 + 64;
+    size_t refEmitted = 0;
+    int rank = 0;
+    bool ok = true;
+    auto fail = [&](const char* e) { L.error = e; ok = false; };
+    while (!st.empty() && ok) {
+        const Item it = st.back(); st.pop_back();
+        const int k = L.nodes();
+        parent.push_back(it.parent);
+        if (it.node >= 0) {
+            if (it.node >= nNodes) { fail("BVH child index out of range"); break; }
+            if (++refEmitted > limit) { fail("BVH is cyclic or shares subtrees excessively"); break; }
+            const rt_flat_node& x = nd[it.node];
+            if (x.leftChild != -1) {
+                if (it.depth + 1 > 64) { fail("BVH deeper than the reference's 64-entry stack"); break; }
+                if (x.leftChild < 0 || x.rightChild < 0) { fail("BVH child index out of range"); break; }
+                L.src.push_back(it.node); L.link.push_back(0); L.cw.push_back(RTL_INNER_REF);
+                st.push_back({x.leftChild, it.depth + 1, -1, k});
+                st.push_back({x.rightChild, it.depth + 1, -1, k});
+                continue;
+            }
+            if (x.numShapes < 0 || x.startShapeIdx < 0 || (size_t)x.startShapeIdx + (size_t)x.numShapes > nIndices) { fail("leaf index range outside bvhIndices"); break; }
+            if (x.numShapes > RTL_COUNT_MASK) { fail("leaf with more than 2^28 shapes"); break; }
+            if ((size_t)L.prims() + (size_t)x.numShapes > 0x7fffffffu) { fail("too many leaf primitives"); break; }
+            const int n = x.numShapes, slot0 = L.prims();
+            for (int i = 0; i < n; ++i) {
+                const int s = indices[(size_t)x.startShapeIdx + (size_t)i];
+                if (s < 0 || s >= nShapes) { fail("bvhIndices entry outside the shape buffer"); break; }
+                L.pshape.push_back(s); L.prank.push_back(rank++);
+            }
+            if (!ok) break;
+            if (!subtrees || n <= RT_FAT_LEAF) {
+                L.src.push_back(it.node); L.link.push_back(slot0);
+                L.cw.push_back(n | (leaf_kind(shapes, L.pshape.data() + slot0, n) << RTL_KIND_SHIFT));
+                continue;
+            }
+            // fat leaf: partition its slots into [unbounded | bounded], build the sub-tree over the bounded ones
+            std::vector<Box>* boxes = new std::vector<Box>((size_t)n);
+            std::vector<int>* items = new std::vector<int>();
+            std::vector<int> unb;
+            for (int i = 0; i < n; ++i) {
+                if (prim_bound(shapes[L.pshape[(size_t)(slot0 + i)]], omax, (*boxes)[(size_t)i])) items->push_back(i);
+                else unb.push_back(i);
+            }
+            SubBuilder* sb = new SubBuilder(*boxes, *items);
+            if (!items->empty()) sb->build(0, (int)items->size());
+            // rewrite the slot range in the new order
+            std::vector<int> ps((size_t)n), pr((size_t)n);
+            int w = 0;
+            for (int i : unb) { ps[(size_t)w] = L.pshape[(size_t)(slot0 + i)]; pr[(size_t)w] = L.prank[(size_t)(slot0 + i)]; ++w; }
+            for (int i : *items) { ps[(size_t)w] = L.pshape[(size_t)(slot0 + i)]; pr[(size_t)w] = L.prank[(size_t)(slot0 + i)]; ++w; }
+            std::copy(ps.begin(), ps.end(), L.pshape.begin() + slot0);
+            std::copy(pr.begin(), pr.end(), L.prank.begin() + slot0);
+            // boxes re-indexed by position inside the bounded range
+            std::vector<Box> nb(items->size());
+            for (size_t j = 0; j < items->size(); ++j) nb[j] = (*boxes)[(size_t)(*items)[j]];
+            boxes->swap(nb);
+            const int t = (int)trees.size();
+            trees.push_back(sb); treeItems.push_back(items); treeBoxes.push_back(boxes); treeSlot0.push_back(slot0 + (int)unb.size());
+            L.nRefLeavesFat++;
+            // the reference leaf becomes an inner node with the reference box (exact reference test)
+            L.src.push_back(it.node); L.link.push_back(0); L.cw.push_back(RTL_INNER_REF);
+            // children (popped in reverse push order): always-leaf first, then the sub-tree root
+            if (!items->empty()) { pend.push_back({1, t, 0, 0}); st.push_back({-1, it.depth + 1, (int)pend.size() - 1, k}); }
+            if (!unb.empty() || items->empty()) { pend.push_back({0, slot0, (int)unb.size(), it.node}); st.push_back({-1, it.depth + 1, (int)pend.size() - 1, k}); }
+            continue;
+        }
+        const Pending p = pend[(size_t)it.sub];
+        if (p.kind == 0) {      // always-tested leaf: carries the reference leaf's own box and test
+            L.src.push_back(p.c); L.link.push_back(p.a);
+            L.cw.push_back(p.b | (leaf_kind(shapes, L.pshape.data() + p.a, p.b) << RTL_KIND_SHIFT));
+            continue;
+        }
+        const SubNode& sn = trees[(size_t)p.a]->nodes[(size_t)p.b];
+        const int j = (int)L.subBox.size();
+        L.subBox.push_back(sn.box); L.subPos.push_back(k);
+        L.src.push_back(-1 - j);
+        if (sn.left < 0) {
+            const int s0 = treeSlot0[(size_t)p.a] + sn.first;
+            L.link.push_back(s0);
+            L.cw.push_back(sn.count | (leaf_kind(shapes, L.pshape.data() + s0, sn.count) << RTL_KIND_SHIFT) | RTL_SUB_BIT);
+        } else {
+            L.link.push_back(0); L.cw.push_back(RTL_INNER_SUB);
+            pend.push_back({1, p.a, sn.right, 0}); st.push_back({-1, it.depth + 1, (int)pend.size() - 1, k});
+            pend.push_back({1, p.a, sn.left, 0});  st.push_back({-1, it.depth + 1, (int)pend.size() - 1, k});
+        }
+    }
+    for (auto* p : trees) delete p;
+    for (auto* p : treeItems) delete p;
+    for (auto* p : treeBoxes) delete p;
+    if (!ok) return false;
+    // skip links of inner nodes: pre-order => link[k] = k + size of the subtree rooted at k
+    const int m = L.nodes();
+    std::vector<int> size((size_t)m, 1);
+    for (int k = m - 1; k >= 1; --k) size[(size_t)parent[(size_t)k]] += size[(size_t)k];
+    for (int k = 0; k < m; ++k) if (L.cw[(size_t)k] < 0) L.link[(size_t)k] = k + size[(size_t)k];
+    return true;
+}
+
+
+// Recompute the sub-tree boxes after shapes moved (rt_update_shapes) or omax changed; topology and
+// slot order stay.  Returns false when a primitive below a sub-tree is no longer boundable (it has
+// to move to the always-tested leaf): the caller then rebuilds the layout.
+inline bool refit_subboxes(Layout& L, const rt_flat_shape* shapes, double omax) {
+    L.omax = omax;
+    for (int j = (int)L.subBox.size() - 1; j >= 0; --j) {
+        const int k = L.subPos[(size_t)j];
+        Box b; b.reset();
+        if (L.cw[(size_t)k] >= 0) {
+            const int n = L.cw[(size_t)k] & RTL_COUNT_MASK, s0 = L.link[(size_t)k];
+            for (int i = 0; i < n; ++i) {
+                Box pb;
+                if (!prim_bound(shapes[L.pshape[(size_t)(s0 + i)]], omax, pb)) return false;
+                b.grow(pb);
+            }
+        } else {
+            const int c1 = k + 1;
+            const int c2 = L.cw[(size_t)c1] < 0 ? L.link[(size_t)c1] : c1 + 1;
+            b.grow(L.subBox[(size_t)(-1 - L.src[(size_t)c1])]);
+            b.grow(L.subBox[(size_t)(-1 - L.src[(size_t)c2])]);
+        }
+        L.subBox[(size_t)j] = b;
+    }
+    return true;
+}
+
+}  // namespace rtl

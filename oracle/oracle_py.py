@@ -57,6 +57,7 @@ def lib():
         L.oracle_render.restype = ip
         L.oracle_intersect_shape.argtypes = [vp, vp, vp, ip, vp]; L.oracle_intersect_shape.restype = ip
         L.oracle_intersect_scene.argtypes = [vp, ip, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp]; L.oracle_intersect_scene.restype = ip
+        L.oracle_intersect_scene_batch.argtypes = [vp, ip, vp, ip, vp, ip, ip, vp, vp, ip, vp, vp, vp]; L.oracle_intersect_scene_batch.restype = None
         L.oracle_present.argtypes = [vp, vp, C.c_int64]; L.oracle_present.restype = None
         _lib = L
     return _lib
@@ -114,6 +115,17 @@ def intersect_shape(shape, start, direction, useMT=False):
     t = lib().oracle_intersect_shape(_p(s), _p(np.asarray(start, np.float32)), _p(np.asarray(direction, np.float32)),
                                      int(useMT), _p(hp))
     return t, hp
+
+
+def intersect_scene_batch(shapes, nodes, indices, starts, dirs, useMT=False):
+    """Closest-hit BVH query (intersectScene2) for n rays: returns (shape ids, closestDist, hit points)."""
+    arrs = [np.ascontiguousarray(a) for a in (shapes, nodes, indices)]
+    starts = np.ascontiguousarray(starts, np.float32); dirs = np.ascontiguousarray(dirs, np.float32)
+    n = len(starts)
+    ids = np.empty(n, np.int32); dist = np.empty(n, np.float32); pts = np.empty((n, 3), np.float32)
+    lib().oracle_intersect_scene_batch(_p(arrs[0]), len(arrs[0]), _p(arrs[1]), len(arrs[1]), _p(arrs[2]), len(arrs[2]),
+                                       n, _p(starts), _p(dirs), int(useMT), _p(ids), _p(dist), _p(pts))
+    return ids, dist, pts
 
 
 def present(rgba):

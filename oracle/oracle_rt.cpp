@@ -454,6 +454,22 @@ int oracle_intersect_scene(const rt_flat_shape* shapes, int nShapes,
     return h.shape;
 }
 
+void oracle_intersect_scene_batch(const rt_flat_shape* shapes, int nShapes, const rt_flat_node* nodes, int nNodes,
+                                  const int32_t* indices, int nIndices, int n, const float* starts, const float* dirs,
+                                  int useMollerTrumbore, int32_t* out_shape, float* out_dist, float* out_point) {
+    Scene sc{nullptr, nullptr, shapes, nShapes, nodes, nNodes, indices, nIndices, useMollerTrumbore != 0};
+    for (int i = 0; i < n; ++i) {
+        Ray r{v3(starts + 3 * (size_t)i), v3(dirs + 3 * (size_t)i)};
+        Hit h = intersect_scene2(sc, r, nullptr);
+        out_shape[i] = h.shape;
+        out_dist[i] = h.dist;
+        if (out_point) {
+            const bool in = h.type == INNER;
+            out_point[3 * (size_t)i] = in ? h.point.x : 0.f; out_point[3 * (size_t)i + 1] = in ? h.point.y : 0.f; out_point[3 * (size_t)i + 2] = in ? h.point.z : 0.f;
+        }
+    }
+}
+
 void oracle_present(const float* rgba, uint8_t* rgba8, int64_t pixels) {
     for (int64_t i = 0; i < pixels; ++i) {
         for (int k = 0; k < 4; ++k) {

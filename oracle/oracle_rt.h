@@ -57,6 +57,11 @@ int oracle_intersect_scene(const rt_flat_shape* shapes, int nShapes,
                            const float start[3], const float dir[3], int useMollerTrumbore,
                            float hit_point[3], float hit_normal[3], float* dist);
 
+/* The same query for n rays (starts/dirs: n*3 floats).  out_dist is closestDist (1e20 on a miss). */
+void oracle_intersect_scene_batch(const rt_flat_shape* shapes, int nShapes, const rt_flat_node* nodes, int nNodes,
+                                  const int32_t* indices, int nIndices, int n, const float* starts, const float* dirs,
+                                  int useMollerTrumbore, int32_t* out_shape, float* out_dist, float* out_point);
+
 /* K4 restatement: clamp [0,1], alpha=1, quantise to RGBA8 (round to nearest). */
 void oracle_present(const float* rgba, uint8_t* rgba8, int64_t pixels);
 

@@ -1,0 +1,125 @@
+// walk_emu.cpp — TEST INFRASTRUCTURE.  A scalar host emulation of the render kernel's BVH query
+// (opengl-ray-tracer_b200/csrc/rt_kernels.cuh: walk) over the layout built by rt_layout.h, using
+// the very same primitive/box test source (rt_device.cuh compiled by g++ -ffp-contract=off).
+// It lets the CPU suite check, ray by ray against the oracle, that the conservative sub-trees and
+// the rank tie-break change no decision.  Never loaded by the product.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "../../opengl-ray-tracer_b200/csrc/rt_device.cuh"
+#include "../../opengl-ray-tracer_b200/csrc/rt_layout.h"
+
+using namespace rt;
+
+namespace {
+struct Emu {
+    rtl::Layout L;
+    std::vector<Prim> prims;
+    std::vector<float4> nodes;     // 2 per node
+    bool boxesFinite = true;
+    float omax = 0.f;
+};
+
+template <bool MT>
+void query(const Emu& E, const float* o, const float* d, int anyMode, float bound, int* outShape, float* outDist,
+           float* outP, uint64_t* cnt) {
+    Ray r = make_ray(mk(o), mk(d), E.boxesFinite, E.omax);
+    float best = anyMode ? bound : 1e20f;
+    int slot = -1; V3 bp = mk(0.f, 0.f, 0.f);
+    const int n = E.L.nodes();
+    int k = 0;
+    while (k < n) {
+        const float4 a = E.nodes[2 * (size_t)k], b = E.nodes[2 * (size_t)k + 1];
+        const int cw = E.L.cw[(size_t)k], lnk = E.L.link[(size_t)k];
+        cnt[0]++;
+        const bool ours = cw == RT_INNER_SUB || (cw >= 0 && (cw & RT_LEAF_SUB_BIT));
+        const bool hit = ours ? (!r.sub || slab_fast(r, a, b)) : (r.fast ? slab_fast(r, a, b) : slab(r, a, b));
+        if (cw < 0) { k = hit ? k + 1 : lnk; continue; }
+        k = k + 1;
+        if (!hit) continue;
+        const int c = cw & RT_LEAF_COUNT_MASK;
+        cnt[1] += (uint64_t)c;
+        bool stop = false;
+        for (int s = lnk; s < lnk + c && !stop; ++s) {
+            V3 hp;
+            if (!test_prim<MT>(E.prims[(size_t)s], r, hp)) continue;
+            const float dist = distance3(r.o, hp);
+            bool take = dist < best;
+            if (!anyMode && dist == best && slot >= 0) take = E.L.prank[(size_t)s] < E.L.prank[(size_t)slot];
+            if (take) { best = dist; slot = s; bp = hp; if (anyMode) stop = true; }
+        }
+        if (stop) break;
+    }
+    *outShape = slot >= 0 ? E.L.pshape[(size_t)slot] : -1;
+    *outDist = best;
+    if (outP) { outP[0] = bp.x; outP[1] = bp.y; outP[2] = bp.z; }
+}
+}  // namespace
+
+extern "C" {
+
+void* emu_create(const rt_flat_shape* shapes, int nShapes, const rt_flat_node* nodes, int nNodes,
+                 const int32_t* indices, int nIndices, int subtrees, double omax) {
+    Emu* E = new Emu();
+    for (int i = 0; i < nNodes && E->boxesFinite; ++i)
+        for (int k = 0; k < 3; ++k)
+            if (!(fabsf(nodes[i].boundsMin[k]) <= RT_SAFE_COORD) || !(fabsf(nodes[i].boundsMax[k]) <= RT_SAFE_COORD)) E->boxesFinite = false;
+    E->omax = (float)omax;
+    if (!rtl::build_layout(nodes, nNodes, indices, (size_t)nIndices, shapes, nShapes, subtrees && E->boxesFinite, omax, E->L)) { delete E; return nullptr; }
+    E->prims.resize((size_t)E->L.prims());
+    for (int s = 0; s < E->L.prims(); ++s) E->prims[(size_t)s] = prim_from_shape(shapes + E->L.pshape[(size_t)s]);
+    E->nodes.resize(2 * (size_t)E->L.nodes());
+    for (int k = 0; k < E->L.nodes(); ++k) {
+        const int src = E->L.src[(size_t)k];
+        if (src >= 0) {
+            E->nodes[2 * (size_t)k] = make_float4(nodes[src].boundsMin[0], nodes[src].boundsMin[1], nodes[src].boundsMin[2], 0.f);
+            E->nodes[2 * (size_t)k + 1] = make_float4(nodes[src].boundsMax[0], nodes[src].boundsMax[1], nodes[src].boundsMax[2], 0.f);
+        } else {
+            const rtl::Box& b = E->L.subBox[(size_t)(-1 - src)];
+            E->nodes[2 * (size_t)k] = make_float4(b.mn[0], b.mn[1], b.mn[2], 0.f);
+            E->nodes[2 * (size_t)k + 1] = make_float4(b.mx[0], b.mx[1], b.mx[2], 0.f);
+        }
+    }
+    return E;
+}
+void emu_destroy(void* e) { delete static_cast<Emu*>(e); }
+
+// info: [0] emitted nodes [1] sub nodes [2] prims [3] fat leaves [4] max leaf size
+void emu_info(void* e, int out[5]) {
+    const Emu* E = static_cast<Emu*>(e);
+    out[0] = E->L.nodes(); out[1] = (int)E->L.subBox.size(); out[2] = E->L.prims(); out[3] = E->L.nRefLeavesFat; out[4] = 0;
+    for (int k = 0; k < E->L.nodes(); ++k) if (E->L.cw[(size_t)k] >= 0 && (E->L.cw[(size_t)k] & RT_LEAF_COUNT_MASK) > out[4]) out[4] = E->L.cw[(size_t)k] & RT_LEAF_COUNT_MASK;
+}
+
+// Refit after the caller changed shapes in place (same pointer semantics as rt_update_shapes): returns 1 ok, 0 = rebuild needed.
+int emu_refit(void* e, const rt_flat_shape* shapes, const rt_flat_node* nodes) {
+    Emu* E = static_cast<Emu*>(e);
+    if (!rtl::refit_subboxes(E->L, shapes, (double)E->omax)) return 0;
+    for (int s = 0; s < E->L.prims(); ++s) E->prims[(size_t)s] = prim_from_shape(shapes + E->L.pshape[(size_t)s]);
+    for (int k = 0; k < E->L.nodes(); ++k) {
+        const int src = E->L.src[(size_t)k];
+        if (src >= 0) {
+            E->nodes[2 * (size_t)k] = make_float4(nodes[src].boundsMin[0], nodes[src].boundsMin[1], nodes[src].boundsMin[2], 0.f);
+            E->nodes[2 * (size_t)k + 1] = make_float4(nodes[src].boundsMax[0], nodes[src].boundsMax[1], nodes[src].boundsMax[2], 0.f);
+        } else {
+            const rtl::Box& b = E->L.subBox[(size_t)(-1 - src)];
+            E->nodes[2 * (size_t)k] = make_float4(b.mn[0], b.mn[1], b.mn[2], 0.f);
+            E->nodes[2 * (size_t)k + 1] = make_float4(b.mx[0], b.mx[1], b.mx[2], 0.f);
+        }
+    }
+    return 1;
+}
+
+// n rays; anyMode: bounds[i] is the any-hit limit.  counters: [0] nodes visited [1] primitive tests.
+void emu_query(void* e, int n, const float* origins, const float* dirs, int mt, int anyMode, const float* bounds,
+               int* outShape, float* outDist, float* outPoint, uint64_t counters[2]) {
+    const Emu* E = static_cast<Emu*>(e);
+    counters[0] = counters[1] = 0;
+    for (int i = 0; i < n; ++i) {
+        float* P = outPoint ? outPoint + 3 * (size_t)i : nullptr;
+        if (mt) query<true>(*E, origins + 3 * (size_t)i, dirs + 3 * (size_t)i, anyMode, anyMode ? bounds[i] : 0.f, outShape + i, outDist + i, P, counters);
+        else    query<false>(*E, origins + 3 * (size_t)i, dirs + 3 * (size_t)i, anyMode, anyMode ? bounds[i] : 0.f, outShape + i, outDist + i, P, counters);
+    }
+}
+}

@@ -180,3 +180,64 @@ def test_errors(rt):
     tr.upload(sc)
     tr.render(p)
     tr.close()
+
+
+def test_reference_walk_flag_matches_default(rt, oracle):
+    """RT_FLAG_REFERENCE_WALK (no sub-trees: the reference's exact node/primitive sequence) and the default
+    (fat leaves expanded into conservative sub-trees) give the same ids and bit-identical colours."""
+    W, H = 400, 300
+    sc = rt.Scene("car", W, H)
+    for kw in (dict(), dict(useMollerTrumbore=True, useFresnel=True)):
+        p = rt.make_params(W, H, **kw)
+        outs = []
+        for flags in (rt.RT_FLAG_HIT_IDS, rt.RT_FLAG_HIT_IDS | rt.RT_FLAG_REFERENCE_WALK):
+            tr = rt.RayTracer(W, H, flags=flags)
+            tr.upload(sc)
+            rgba, ids = tr.render(p)
+            stats = tr.render_stats(p)
+            tr.close()
+            outs.append((rgba, ids, stats))
+        assert np.array_equal(outs[0][1], outs[1][1])
+        assert np.array_equal(outs[0][0].view(np.uint32), outs[1][0].view(np.uint32))
+        assert outs[0][2]["rays"] == outs[1][2]["rays"]
+        assert outs[0][2]["prim_tests"] < outs[1][2]["prim_tests"] / 3
+
+
+def test_animated_car_refit(rt, oracle):
+    """Rotating wheels (stale planes upstream, src/main.cpp:1101-1106) + grow-only refit: the sub-tree boxes are
+    refitted on rt_update_shapes and every frame still matches the oracle."""
+    W, H = 400, 300
+    sc = rt.Scene("car", W, H)
+    p = rt.make_params(W, H)
+    tr = rt.RayTracer(W, H)
+    tr.upload(sc)
+    tr.render(p)
+    for frame in range(1, 4):
+        sc.animate(frame * 0.21, 0.21, mode=0)
+        shapes = sc.shapes
+        an = sc.animated
+        lo, hi = int(an.min()), int(an.max()) + 1
+        tr.update_shapes(lo, shapes[lo:hi])
+        tr.update_nodes(sc.nodes)
+        rgba, ids = tr.render(p)
+        o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
+        assert_parity(compare(rgba, ids, o_rgba, o_ids), "animated car frame %d" % frame)
+    tr.close()
+
+
+def test_camera_far_away(rt, oracle):
+    """Camera beyond the region the sub-tree margins were computed for (omax): margins are recomputed / ignored."""
+    W, H = 200, 150
+    sc = rt.Scene("car", W, H)
+    p = rt.make_params(W, H)
+    tr = rt.RayTracer(W, H)
+    tr.upload(sc)
+    tr.render(p)
+    for dist in (500.0, 20000.0):
+        sc.set_camera((0.0, -10.0, dist), (0.0, 0.0, 0.0), fov=2.0 if dist > 1000 else 10.0)
+        tr.update_camera(sc.camera)
+        rgba, ids = tr.render(p)
+        o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
+        assert_parity(compare(rgba, ids, o_rgba, o_ids), "camera at %g" % dist)
+        assert (o_ids >= 0).any()
+    tr.close()

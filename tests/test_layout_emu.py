@@ -1,0 +1,226 @@
+"""CPU: the host-side layout builder (rt_layout.h: threaded BVH, conservative sub-trees in fat leaves,
+rank tie-break) walked by a scalar emulation of the kernel's query (tests/emu/walk_emu.cpp, same
+primitive/box test source as the kernel, compiled by g++ -ffp-contract=off) against the oracle's
+intersectScene2, ray by ray: shape ids and closestDist must be bit-identical."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from util import random_shapes
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+EMU_SRC = os.path.join(HERE, "emu", "walk_emu.cpp")
+EMU_SO = os.path.join(HERE, "emu", "libwalk_emu.so")
+CSRC = os.path.join(os.path.dirname(HERE), "opengl-ray-tracer_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    deps = [EMU_SRC, os.path.join(CSRC, "rt_layout.h"), os.path.join(CSRC, "rt_device.cuh")]
+    if not os.path.exists(EMU_SO) or any(os.path.getmtime(d) > os.path.getmtime(EMU_SO) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared",
+                               "-I/usr/local/cuda/include", "-o", EMU_SO, EMU_SRC])
+    L = C.CDLL(EMU_SO)
+    vp, ip = C.c_void_p, C.c_int
+    L.emu_create.argtypes = [vp, ip, vp, ip, vp, ip, ip, C.c_double]; L.emu_create.restype = vp
+    L.emu_destroy.argtypes = [vp]; L.emu_destroy.restype = None
+    L.emu_info.argtypes = [vp, vp]; L.emu_info.restype = None
+    L.emu_refit.argtypes = [vp, vp, vp]; L.emu_refit.restype = ip
+    L.emu_query.argtypes = [vp, ip, vp, vp, ip, ip, vp, vp, vp, vp, vp]; L.emu_query.restype = None
+    return L
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Emu:
+    def __init__(self, L, shapes, nodes, indices, subtrees=True, omax=None):
+        self.L = L
+        self.keep = [np.ascontiguousarray(a) for a in (shapes, nodes, indices)]
+        sh, nd, ix = self.keep
+        if omax is None:
+            omax = 4.0 * max(1.0, float(np.abs(nd["boundsMin"][-1]).max()), float(np.abs(nd["boundsMax"][-1]).max())) if len(nd) else 4.0
+        self.omax = omax
+        self.h = L.emu_create(_p(sh), len(sh), _p(nd), len(nd), _p(ix), len(ix), int(subtrees), float(omax))
+        assert self.h
+
+    def info(self):
+        out = (C.c_int * 5)()
+        self.L.emu_info(self.h, out)
+        return dict(nodes=out[0], sub=out[1], prims=out[2], fat=out[3], max_leaf=out[4])
+
+    def query(self, o, d, mt=False, bounds=None):
+        o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)
+        n = len(o)
+        ids = np.empty(n, np.int32); dist = np.empty(n, np.float32); pts = np.empty((n, 3), np.float32)
+        cnt = (C.c_uint64 * 2)()
+        b = None if bounds is None else np.ascontiguousarray(bounds, np.float32)
+        self.L.emu_query(self.h, n, _p(o), _p(d), int(mt), int(bounds is not None), _p(b), _p(ids), _p(dist), _p(pts), cnt)
+        return ids, dist, pts, (int(cnt[0]), int(cnt[1]))
+
+    def refit(self, shapes, nodes):
+        self.keep[0] = np.ascontiguousarray(shapes); self.keep[1] = np.ascontiguousarray(nodes)
+        return self.L.emu_refit(self.h, _p(self.keep[0]), _p(self.keep[1]))
+
+    def close(self):
+        self.L.emu_destroy(self.h)
+
+
+def normalize(v):
+    v = v.astype(np.float32)
+    return (v * (np.float32(1.0) / np.sqrt((v * v).sum(axis=1, keepdims=True, dtype=np.float32)))).astype(np.float32)
+
+
+def make_rays(rng, sc_shapes, nodes, cam_pos, n):
+    """Camera rays, rays between random points of the scene box, and adversarial rays aimed at triangle
+    edges/vertices and sphere silhouettes (where a wrong conservative bound would show)."""
+    lo, hi = nodes["boundsMin"][-1].astype(np.float64), nodes["boundsMax"][-1].astype(np.float64)
+    lo, hi = np.where(np.isfinite(lo), lo, -50), np.where(np.isfinite(hi), hi, 50)
+    O, D = [], []
+    # (1) from the camera towards random points of the box
+    tgt = rng.uniform(lo, hi, (n, 3))
+    O.append(np.repeat(cam_pos[None], n, 0)); D.append(tgt - cam_pos)
+    # (2) between random points (secondary-ray like)
+    a = rng.uniform(lo, hi, (n, 3)); b = rng.uniform(lo, hi, (n, 3))
+    O.append(a); D.append(b - a)
+    # (3) adversarial: aim at points on triangle edges / vertices / just outside, and sphere limbs
+    tri = sc_shapes[sc_shapes["type"] == 3]
+    if len(tri):
+        k = rng.integers(0, len(tri), n)
+        P1, P2, P3 = tri["triP1"][k].astype(np.float64), tri["triP2"][k].astype(np.float64), tri["triP3"][k].astype(np.float64)
+        u = rng.uniform(0, 1, (n, 1)); mode = rng.integers(0, 4, (n, 1))
+        edge = np.where(mode == 0, P1 + u * (P2 - P1), np.where(mode == 1, P2 + u * (P3 - P2), np.where(mode == 2, P3 + u * (P1 - P3), P1)))
+        edge = edge + rng.normal(0, 1, (n, 3)) * rng.choice([0.0, 1e-6, 1e-4, 1e-2], (n, 1))
+        src = np.where(rng.uniform(0, 1, (n, 1)) < 0.5, np.repeat(cam_pos[None], n, 0), rng.uniform(lo, hi, (n, 3)))
+        O.append(src); D.append(edge - src)
+    sph = sc_shapes[sc_shapes["type"] == 0]
+    if len(sph):
+        k = rng.integers(0, len(sph), n)
+        c, r = sph["sphereCenter"][k].astype(np.float64), sph["sphereRadius"][k].astype(np.float64)[:, None]
+        src = np.where(rng.uniform(0, 1, (n, 1)) < 0.5, np.repeat(cam_pos[None], n, 0), rng.uniform(lo, hi, (n, 3)))
+        to = c - src
+        perp = np.cross(to, rng.normal(0, 1, (n, 3)))
+        perp /= np.linalg.norm(perp, axis=1, keepdims=True) + 1e-30
+        limb = c + perp * r * (1 + rng.choice([0.0, 1e-6, -1e-6, 1e-4, -1e-4, 1e-2], (n, 1)))
+        O.append(src); D.append(limb - src)
+    O = np.concatenate(O).astype(np.float32); D = np.concatenate(D)
+    ok = np.linalg.norm(D, axis=1) > 1e-9
+    return O[ok], normalize(D[ok])
+
+
+def check_scene(emu, oracle, sc, rng, n=20000, label=""):
+    shapes, nodes, idx = sc.shapes, sc.nodes, sc.indices
+    cam = sc.camera["Position"][0].astype(np.float64)
+    e = Emu(emu, shapes, nodes, idx, subtrees=True)
+    o, d = make_rays(rng, shapes, nodes, cam, n)
+    out = {}
+    for mt in (False, True):
+        rid, rdist, rpt = oracle.intersect_scene_batch(shapes, nodes, idx, o, d, mt)
+        gid, gdist, gpt, cnt = e.query(o, d, mt)
+        bad = np.nonzero((gid != rid) | (gdist.view(np.uint32) != rdist.view(np.uint32)))[0]
+        assert len(bad) == 0, "%s mt=%s: %d of %d rays differ, first %d: emu (%d, %r) oracle (%d, %r)" % (
+            label, mt, len(bad), len(o), bad[0], gid[bad[0]], gdist[bad[0]], rid[bad[0]], rdist[bad[0]])
+        hitm = rid >= 0
+        assert np.array_equal(gpt[hitm].view(np.uint32), rpt[hitm].view(np.uint32))
+        # any-hit (shadow) queries: the boolean "closest INNER hit is nearer than the bound"
+        bounds = (rdist * rng.choice([0.5, 0.999999, 1.0, 1.000001, 2.0], len(o))).astype(np.float32)
+        bounds = np.where(hitm, bounds, rng.uniform(1, 100, len(o)).astype(np.float32))
+        aid, _, _, _ = e.query(o, d, mt, bounds=np.minimum(bounds, np.float32(1e20)))
+        assert np.array_equal(aid >= 0, rdist < bounds), "%s mt=%s any-hit differs" % (label, mt)
+        out[mt] = cnt
+    info = e.info()
+    e.close()
+    return info, out, len(o)
+
+
+@pytest.mark.parametrize("name", ["toy", "triangle", "monkey", "car"])
+def test_named_scenes(rt, oracle, emu, name):
+    rng = np.random.default_rng(11)
+    sc = rt.Scene(name, 800, 600)
+    info, cnt, n = check_scene(emu, oracle, sc, rng, label=name)
+    if name == "car":
+        assert info["fat"] > 0 and info["max_leaf"] <= 8
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_scenes_fat_leaves(rt, oracle, emu, seed):
+    """Shallow reference BVHs (depth 1-3) put hundreds of mixed shapes into one leaf."""
+    rng = np.random.default_rng(100 + seed)
+    base = rt.Scene("toy", 160, 120)
+    shapes = random_shapes(rt, rng, 300, types=(0, 2, 3) if seed % 2 else (0, 1, 2, 3), extent=10.0 * (1 + 10 * (seed % 3)))
+    sc = rt.Scene.from_shapes(shapes, base.light, base.camera, bvh_depth=1 + seed % 3, width=160, height=120)
+    info, _, _ = check_scene(emu, oracle, sc, rng, n=8000, label="random %d" % seed)
+    assert info["sub"] > 0
+
+
+def test_degenerate_and_stale_planes(rt, oracle, emu):
+    """Slivers, zero-area triangles, NaN vertices and triangles whose stored plane no longer matches their
+    vertices (upstream's animated wheels, src/main.cpp:1101-1106) must not be culled wrongly."""
+    rng = np.random.default_rng(5)
+    base = rt.Scene("toy", 160, 120)
+    shapes = random_shapes(rt, rng, 200, types=(3,), extent=8.0)
+    shapes["triP3"][0:10] = shapes["triP2"][0:10]                                     # zero area
+    shapes["triP3"][10:20] = shapes["triP1"][10:20] + (shapes["triP2"][10:20] - shapes["triP1"][10:20]) * np.float32(1.5)   # collinear
+    shapes["triP3"][20:30] += np.float32(1e-6)
+    shapes["triP2"][30:33] = np.nan
+    # stale planes: rotate the vertices of 60 triangles about z, keep planeNormal/planeD
+    for i in range(40, 100):
+        a = rng.uniform(0, 2 * np.pi)
+        R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]], np.float32)
+        for f in ("triP1", "triP2", "triP3"):
+            shapes[f][i] = R @ shapes[f][i]
+    sc = rt.Scene.from_shapes(shapes, base.light, base.camera, bvh_depth=2, width=160, height=120)
+    check_scene(emu, oracle, sc, rng, n=20000, label="degenerate")
+
+
+def test_far_origins_ignore_subtrees(rt, oracle, emu):
+    """Origins beyond omax: the margins do not hold, the walk must treat sub-tree boxes as hit."""
+    rng = np.random.default_rng(9)
+    sc = rt.Scene("car", 800, 600)
+    shapes, nodes, idx = sc.shapes, sc.nodes, sc.indices
+    e = Emu(emu, shapes, nodes, idx)
+    n = 4000
+    tgt = rng.uniform(-10, 10, (n, 3))
+    src = normalize(rng.normal(0, 1, (n, 3))).astype(np.float64) * rng.choice([1e3, 1e4, 1e5, 1e6], (n, 1))
+    d = normalize(tgt - src)
+    rid, rdist, _ = oracle.intersect_scene_batch(shapes, nodes, idx, src.astype(np.float32), d)
+    gid, gdist, _, _ = e.query(src.astype(np.float32), d)
+    assert np.array_equal(gid, rid) and np.array_equal(gdist.view(np.uint32), rdist.view(np.uint32))
+    e.close()
+
+
+def test_refit_after_animation(rt, oracle, emu):
+    """Wheels rotate (stale planes), boxes grow: refit of the sub-tree boxes keeps every decision."""
+    rng = np.random.default_rng(3)
+    sc = rt.Scene("car", 800, 600)
+    e = Emu(emu, sc.shapes, sc.nodes, sc.indices)
+    cam = sc.camera["Position"][0].astype(np.float64)
+    for frame in range(1, 4):
+        sc.animate(frame * 0.37, 0.37, mode=0)
+        shapes, nodes = sc.shapes, sc.nodes
+        assert e.refit(shapes, nodes) == 1
+        o, d = make_rays(rng, shapes, nodes, cam, 6000)
+        for mt in (False, True):
+            rid, rdist, _ = oracle.intersect_scene_batch(shapes, nodes, sc.indices, o, d, mt)
+            gid, gdist, _, _ = e.query(o, d, mt)
+            assert np.array_equal(gid, rid) and np.array_equal(gdist.view(np.uint32), rdist.view(np.uint32)), "frame %d mt=%s" % (frame, mt)
+    e.close()
+
+
+def test_subtrees_cut_the_work(rt, oracle, emu):
+    """The point of the sub-trees: far fewer primitive tests on the car scene, same answers."""
+    rng = np.random.default_rng(1)
+    sc = rt.Scene("car", 800, 600)
+    cam = sc.camera["Position"][0].astype(np.float64)
+    o, d = make_rays(rng, sc.shapes, sc.nodes, cam, 5000)
+    a = Emu(emu, sc.shapes, sc.nodes, sc.indices, subtrees=False)
+    b = Emu(emu, sc.shapes, sc.nodes, sc.indices, subtrees=True)
+    ia, da, _, ca = a.query(o, d)
+    ib, db, _, cb = b.query(o, d)
+    assert np.array_equal(ia, ib) and np.array_equal(da.view(np.uint32), db.view(np.uint32))
+    assert cb[1] < ca[1] / 3, (ca, cb)
+    a.close(); b.close()
