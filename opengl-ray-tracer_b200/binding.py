@@ -67,7 +67,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.build_cuda()
+    path = os.environ.get("RT_B200_LIB") or _build.build_cuda()      # RT_B200_LIB: kernel-variant experiments (tools/)
     L = C.CDLL(path)
     vp, ip, fp = C.c_void_p, C.c_int, C.POINTER(C.c_float)
     L.rt_create.argtypes = [C.POINTER(vp), ip, ip, ip, C.c_uint]; L.rt_create.restype = ip

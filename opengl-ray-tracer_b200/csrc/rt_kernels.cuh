@@ -5,6 +5,9 @@
 #ifndef RT_BLOCK_THREADS
 #define RT_BLOCK_THREADS 128
 #endif
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 8          // resident CTAs per SM the register allocation aims for
+#endif
 
 namespace rt {
 
@@ -203,6 +206,13 @@ __device__ __forceinline__ Material load_material(const rt_flat_shape* __restric
     return r;
 }
 
+// getNormalFromShape (a10, :64-71)
+__device__ __forceinline__ V3 shape_normal(const rt_flat_shape* __restrict__ sh, V3 hp) {
+    if (__ldg(&sh->type) == RT_SHAPE_SPHERE)
+        return normalize3(hp - mk(__ldg(&sh->sphereCenter[0]), __ldg(&sh->sphereCenter[1]), __ldg(&sh->sphereCenter[2])));
+    return mk(__ldg(&sh->planeNormal[0]), __ldg(&sh->planeNormal[1]), __ldg(&sh->planeNormal[2]));
+}
+
 __device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3 lcol, const Material& m) {
     float distToLight = distance3(lpos, point);
     V3 lightColor = lcol / distToLight;
@@ -227,64 +237,70 @@ __device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3
 template <bool MT, bool COUNT>
 __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, bool inside,
                                               int& idOut, Tally& tl) {
-    const float a = (float)y / P.resH;
-    const V3 bg = mk(mix1(0.05f, 0.5f, a), mix1(0.07f, 0.7f, a), mix1(0.1f, 1.0f, a));
-    const float ndcX = 2.0f * (float)x / P.resW - 1.0f;
-    const float ndcY = 1.0f - 2.0f * (float)y / P.resH;
-    const V3 camP = mk(P.camP);
-    V3 ipp = ((camP + mk(P.camF)) + (ndcX * P.planeW / 2.0f) * mk(P.camR)) + (ndcY * P.planeH / 2.0f) * mk(P.camU);
     const bool bf = S.boxesFinite != 0;
-    Ray ray = make_ray(camP, normalize3(ipp - camP), bf, S.omax);
-    const V3 lpos = mk(P.lightPos), lcol = mk(P.lightCol);
+    // Live state across the walks is kept small (occupancy): the view direction, the hit point, the hit
+    // shape's index, and the two colour accumulators.  Normal and material are re-read after the shadow walk.
+    V3 vd, hp = mk(0.f, 0.f, 0.f);
     V3 acc = mk(0.f, 0.f, 0.f), att = mk(1.f, 1.f, 1.f);
+    int shape = -1;
     idOut = -1;
     bool alive = inside;
-
-    Material m; m.color = mk(0.f, 0.f, 0.f); m.fresnel = m.ambient = m.diffuse = m.specular = 0.f; m.shininess = 0;
-    V3 hp = mk(0.f, 0.f, 0.f), nrm = mk(0.f, 0.f, 1.f);
-    float lightDist = 0.f;
     Query q;
+    {
+        const float ndcX = 2.0f * (float)x / P.resW - 1.0f;
+        const float ndcY = 1.0f - 2.0f * (float)y / P.resH;
+        const V3 camP = mk(P.camP);
+        const V3 ipp = ((camP + mk(P.camF)) + (ndcX * P.planeW / 2.0f) * mk(P.camR)) + (ndcY * P.planeH / 2.0f) * mk(P.camU);
+        q.r = make_ray(camP, normalize3(ipp - camP), bf, S.omax);
+        vd = q.r.d;
+    }
 
     for (int step = 0; step < 2 * P.maxBounces; ++step) {
         if (!__any_sync(RT_FULL, alive)) break;
         const bool shadowStep = (step & 1) != 0;
+        float lightDist = 0.f;
         if (!shadowStep) {
-            q.r = ray; q.best = 1e20f;
+            q.best = 1e20f;                                // q.r is the current ray
         } else {
+            const V3 lpos = mk(P.lightPos);
+            const V3 nrm = shape >= 0 ? shape_normal(S.shapes + shape, hp) : mk(0.f, 0.f, 1.f);
+            lightDist = distance3(lpos, hp);
             q.r = make_ray(hp + nrm * (P.useBVH ? 1e-3f : 1e-5f), normalize3(lpos - hp), bf, S.omax);
             // dist < 1e20 && dist < lightDist  ==  dist < min; a NaN lightDist can never be beaten
             q.best = lightDist < 1e20f ? lightDist : (lightDist >= 1e20f ? 1e20f : -1.0f);
         }
         q.slot = -1; q.p = mk(0.f, 0.f, 0.f);
-        int shape = -1;
         if (P.useBVH) {
             walk<MT, COUNT>(S, q, alive, shadowStep, tl);
-            if (alive && !shadowStep && q.slot >= 0) shape = __ldg(S.pshape + q.slot);
         } else if (alive) {
-            if (!shadowStep) { Hit h; scan_closest<MT>(S, q.r, h); shape = h.slot; q.slot = h.slot; q.p = h.p; RT_TALLY(5, S.nShapes); }
+            if (!shadowStep) { Hit h; scan_closest<MT>(S, q.r, h); q.slot = h.slot; q.p = h.p; RT_TALLY(5, S.nShapes); }
             else if (scan_any<MT>(S, q.r, lightDist)) q.slot = 0;
         }
         if (!alive) continue;
         RT_TALLY(0, 1);
         if (!shadowStep) {                                 // closest-hit result (:452-464)
+            shape = q.slot < 0 ? -1 : P.useBVH ? __ldg(S.pshape + q.slot) : q.slot;
             RT_TALLY(step == 0 ? 1 : 3, 1); RT_TALLY(6, shape >= 0 ? 1 : 0);
             if (step == 0) idOut = shape;
-            if (shape < 0) { acc = acc + att * bg; alive = false; continue; }
-            const rt_flat_shape* sh = S.shapes + shape;
-            m = load_material(sh);
+            if (shape < 0) {
+                const float a = (float)y / P.resH;
+                const V3 bg = mk(mix1(0.05f, 0.5f, a), mix1(0.07f, 0.7f, a), mix1(0.1f, 1.0f, a));
+                acc = acc + att * bg; alive = false; continue;
+            }
             hp = q.p;
-            if (__ldg(&sh->type) == RT_SHAPE_SPHERE) nrm = normalize3(hp - mk(__ldg(&sh->sphereCenter[0]), __ldg(&sh->sphereCenter[1]), __ldg(&sh->sphereCenter[2])));
-            else nrm = mk(__ldg(&sh->planeNormal[0]), __ldg(&sh->planeNormal[1]), __ldg(&sh->planeNormal[2]));
-            lightDist = distance3(lpos, hp);
         } else {                                           // shadow result, shading, next ray (:474-516)
             const bool inShadow = q.slot >= 0;
             RT_TALLY(2, 1); RT_TALLY(7, inShadow ? 1 : 0);
-            V3 pc = phong(hp, nrm, ray.d, lpos, lcol, m);
+            const rt_flat_shape* sh = S.shapes + shape;
+            const Material m = load_material(sh);
+            const V3 nrm = shape_normal(sh, hp);
+            V3 pc = phong(hp, nrm, vd, mk(P.lightPos), mk(P.lightCol), m);
             if (inShadow) pc = pc * 0.3f;
             acc = acc + att * pc;
             if (!(m.specular > 0.0f)) { alive = false; continue; }
-            const V3 rd = reflect3(ray.d, nrm);
-            ray = make_ray(hp + nrm * 1e-3f, rd, bf, S.omax);
+            const V3 rd = reflect3(vd, nrm);
+            q.r = make_ray(hp + nrm * 1e-3f, rd, bf, S.omax);
+            vd = rd;
             if (P.useFresnel) {
                 float fr = powf(1.0f - gmax(dot3(-rd, nrm), 0.0f), 5.0f);
                 fr = gmin(gmax(fr, 0.0f), 0.8f);
@@ -310,7 +326,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
 #define RT_WARPS_PER_TILE ((RT_TILE_W / 8) * (RT_TILE_H / 4))
 
 template <bool MT, bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK_THREADS)
+__global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __restrict__ ids,
               unsigned long long* __restrict__ tally, unsigned int* __restrict__ queue) {
     Tally tl;
