@@ -132,6 +132,8 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
     const int n = S.nNodes;
     const Ray& r = q.r;
     int k = active ? 0 : RT_DONE;
+    // lanes whose ray cannot use the NaN-free fast slab test (non-finite origin / 1/d): rare, warp-uniform flag
+    const bool anySlow = __any_sync(RT_FULL, active && !r.fast);
     for (;;) {
         const int km = __reduce_min_sync(RT_FULL, k);
         if (km >= n) break;
@@ -141,10 +143,15 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
         const int lnk = __float_as_int(a.w);
         const bool mine = (k == km);
         RT_TALLY(4, mine ? 1 : 0);
-        // reference nodes: the shader's exact slab test; nodes of our own sub-trees (cw == -2 or
-        // leaf bit 30): conservative boxes, skipped only for rays the margins were computed for
+        // The box test is evaluated by ALL lanes without a branch (idle lanes cost no issue slots;
+        // a divergent branch around it would).  Reference nodes: the shader's exact slab test; nodes
+        // of our own sub-trees (cw == -2 or leaf bit 30, warp-uniform): conservative boxes, skipped
+        // only for rays the margins were computed for.
+        bool h = slab_fast(r, a, b);
         const bool ours = cw == RT_INNER_SUB || (cw >= 0 && (cw & RT_LEAF_SUB_BIT));
-        const bool hit = mine && (ours ? (!r.sub || slab_fast(r, a, b)) : (r.fast ? slab_fast(r, a, b) : slab(r, a, b)));
+        if (ours) h = h || !r.sub;
+        else if (anySlow) { if (!r.fast) h = slab(r, a, b); }
+        const bool hit = mine && h;
         if (cw < 0) {                                   // inner: hit -> next in list, miss -> skip subtree
             if (mine) k = hit ? km + 1 : lnk;
             continue;
