@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (core-seconds are bounded by a row sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-flush", action="store_true", help="diagnostic only: keep L2 warm between steps (not a valid bench line)")
     return ap.parse_args()
 
 
@@ -209,7 +210,8 @@ def workload_config(args, **more):
                        "(BASELINE.json configs[2]; synthetic stand-in mesh, same primitive counts)" %
                        (args.scene, args.width, args.height, args.bounces, args.fresnel, args.mt),
            "scene": args.scene, "width": args.width, "height": args.height,
-           "parallelism": "tiles%d" % args.gpus, "tile": "32x8 interleaved", "l2": "flushed between steps (256 MiB write)"}
+           "parallelism": "tiles%d" % args.gpus, "tile": "32x8 interleaved",
+           "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between steps (256 MiB write)"}
     cfg.update(more)
     return cfg
 
@@ -335,7 +337,7 @@ def main():
         rays = consts["rays"] if consts else rays_gpu
         rays_match = (consts is None) or (rays_gpu == consts["rays"])
 
-        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
         clocks = ClockSampler(local)
         launches0 = tr.launch_count()
         if rank == 0:

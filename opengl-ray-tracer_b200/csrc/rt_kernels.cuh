@@ -127,6 +127,9 @@ __device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const f
 // per lane at unrelated iterations.  Must be called by all 32 lanes; `active` masks lanes.
 #define RT_FULL 0xffffffffu
 #define RT_DONE 0x7fffffff
+#ifndef RT_LOW_RUNS
+#define RT_LOW_RUNS 4
+#endif
 template <bool MT, bool COUNT>
 __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active, bool anyMode, Tally& tl) {
     const int n = S.nNodes;
@@ -134,14 +137,28 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
     int k = active ? 0 : RT_DONE;
     // lanes whose ray cannot use the NaN-free fast slab test (non-finite origin / 1/d): rare, warp-uniform flag
     const bool anySlow = __any_sync(RT_FULL, active && !r.fast);
+    // Two modes share this loop and the per-lane cursor k.  PACKET: the warp handles the smallest
+    // pending node (uniform loads, the union of the lanes' node sets is walked once) — best for
+    // coherent rays.  LANE: every lane handles its own node (divergent loads, no union) — best for
+    // incoherent rays (reflections off curved surfaces), where the union approaches the whole tree.
+    // The walk starts in packet mode and switches for the rest of the query after RT_LOW_RUNS
+    // consecutive iterations that served fewer than a quarter of the query's lanes.
+    bool packet = true;
+    int low = 0;
+    const int quarter = (__popc(__ballot_sync(RT_FULL, active)) + 3) >> 2;
     for (;;) {
-        const int km = __reduce_min_sync(RT_FULL, k);
-        if (km >= n) break;
+        const int kmin = __reduce_min_sync(RT_FULL, k);
+        if (kmin >= n) break;
+        const bool mine = packet ? (k == kmin) : (k < n);
+        const int km = mine ? k : kmin;                 // packet mode: kmin for every lane
+        if (packet) {
+            low = __popc(__ballot_sync(RT_FULL, mine)) < quarter ? low + 1 : 0;
+            if (low >= RT_LOW_RUNS) packet = false;
+        }
         const float4 a = __ldg(S.nodes + 2 * km);
         const float4 b = __ldg(S.nodes + 2 * km + 1);
         const int cw = __float_as_int(b.w);
         const int lnk = __float_as_int(a.w);
-        const bool mine = (k == km);
         RT_TALLY(4, mine ? 1 : 0);
         // The box test is evaluated by ALL lanes without a branch (idle lanes cost no issue slots;
         // a divergent branch around it would).  Reference nodes: the shader's exact slab test; nodes
