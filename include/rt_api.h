@@ -126,6 +126,11 @@ int rt_render_device(rt_ctx* ctx, const rt_params* params, float* dev_rgba, int3
  * output pixel) receives nodes visited + primitive tests of that pixel.  Synchronous. */
 int rt_render_stats(rt_ctx* ctx, const rt_params* params, uint64_t out[8], int32_t* host_cost_or_null);
 
+/* Walk-efficiency diagnostics of the last rt_render_stats call: out[0..3] for primary segments,
+ * out[4..7] for later (bounce) segments: warp iterations in packet mode, warp iterations in lane
+ * mode, lanes served in packet mode, lanes served in lane mode. */
+int rt_walk_stats(rt_ctx* ctx, uint64_t out[8]);
+
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in
  * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one
  * row-major W*H image. */

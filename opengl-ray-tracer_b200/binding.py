@@ -54,7 +54,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_device", "rt_render_stats", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -83,6 +83,7 @@ def lib():
     L.rt_render.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render.restype = ip
     L.rt_render_device.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_device.restype = ip
     L.rt_render_stats.argtypes = [vp, C.POINTER(Params), C.POINTER(C.c_uint64), vp]; L.rt_render_stats.restype = ip
+    L.rt_walk_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_walk_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
     L.rt_stream.argtypes = [vp]; L.rt_stream.restype = vp
@@ -275,6 +276,13 @@ class RayTracer:
         self._chk(self._L.rt_render_stats(self._c, C.byref(params), out, _ptr(cost)))
         keys = ["rays", "primary_rays", "shadow_rays", "reflect_rays", "node_visits", "prim_tests", "ray_hits", "shadowed"]
         return dict(zip(keys, [int(x) for x in out]))
+
+    def walk_stats(self):
+        out = (C.c_uint64 * 8)()
+        self._chk(self._L.rt_walk_stats(self._c, out))
+        keys = ["packet_iters", "lane_iters", "packet_served", "lane_served"]
+        v = [int(x) for x in out]
+        return {"primary": dict(zip(keys, v[:4])), "bounce": dict(zip(keys, v[4:]))}
 
     def untile(self, dev_shards_ptr, world, dev_out_ptr):
         self._chk(self._L.rt_untile(self._c, _ptr(dev_shards_ptr), world, _ptr(dev_out_ptr)))

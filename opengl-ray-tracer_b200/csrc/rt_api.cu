@@ -60,6 +60,7 @@ struct rt_ctx {
     bool timed[4] = {false, false, false, false};
     std::string err;
     int64_t launches = 0;
+    uint64_t lastTally[RT_NTALLY] = {};
     int smCount = 148;
 
     // raw scene, pinned shadow + device copy
@@ -380,15 +381,22 @@ int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* de
 int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8], int32_t* host_cost) {
     if (!c || !p || !out) return RT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
-    CU(c, c->tally.reserve(8));
-    CU(c, cudaMemsetAsync(c->tally.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    CU(c, c->tally.reserve(RT_NTALLY));
+    CU(c, cudaMemsetAsync(c->tally.p, 0, RT_NTALLY * sizeof(unsigned long long), c->stream));
     int32_t* dcost = nullptr;
     if (host_cost) { CU(c, c->ids.reserve((size_t)out_pixels(c))); dcost = c->ids.p; }
     int rc = render_impl(c, p, nullptr, dcost, true);
     if (rc != RT_OK) return rc;
     if (host_cost) CU(c, cudaMemcpyAsync(host_cost, dcost, (size_t)out_pixels(c) * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaMemcpyAsync(out, c->tally.p, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaMemcpyAsync(c->lastTally, c->tally.p, RT_NTALLY * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 8; ++i) out[i] = c->lastTally[i];
+    return RT_OK;
+}
+
+int rt_walk_stats(rt_ctx* c, uint64_t out[8]) {
+    if (!c || !out) return RT_ERR_ARG;
+    for (int i = 0; i < 8; ++i) out[i] = c->lastTally[8 + i];
     return RT_OK;
 }
 

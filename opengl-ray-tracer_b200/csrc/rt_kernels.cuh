@@ -19,7 +19,10 @@ struct Hit { float dist; int slot; V3 p; };
 // Optional work counters (stats launches only; the timed kernel is compiled without them).
 // [0] rays (BVH/scan queries) [1] primary [2] shadow [3] reflection [4] nodes visited
 // [5] primitive tests [6] closest-hit queries that hit [7] shadow queries that were occluded
-struct Tally { unsigned long long v[8]; };
+// [8..11] primary segments, [12..15] later segments: packet-mode warp iterations, lane-mode warp
+// iterations, lanes served in packet mode, lanes served in lane mode (walk efficiency diagnostics)
+#define RT_NTALLY 16
+struct Tally { unsigned long long v[RT_NTALLY]; };
 #define RT_TALLY(i, n) do { if (COUNT) tl.v[i] += (n); } while (0)
 
 // One BVH query of one lane.  Closest-hit (a3): best starts at 1e20 and every candidate with
@@ -128,53 +131,62 @@ __device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const f
 #define RT_FULL 0xffffffffu
 #define RT_DONE 0x7fffffff
 #ifndef RT_LOW_RUNS
-#define RT_LOW_RUNS 4
+#define RT_LOW_RUNS 2
+#endif
+#ifndef RT_SAMPLE
+#define RT_SAMPLE 4         // power of two
 #endif
 template <bool MT, bool COUNT>
-__device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active, bool anyMode, Tally& tl) {
+__device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active, bool anyMode, Tally& tl, int tbase) {
     const int n = S.nNodes;
     const Ray& r = q.r;
     int k = active ? 0 : RT_DONE;
-    // lanes whose ray cannot use the NaN-free fast slab test (non-finite origin / 1/d): rare, warp-uniform flag
-    const bool anySlow = __any_sync(RT_FULL, active && !r.fast);
+    // Rays that cannot use the NaN-free fast slab test (non-finite origin or 1/d) or for which the
+    // sub-tree margins do not hold (|o| > omax) are rare: one warp-uniform flag keeps their handling
+    // out of the hot loop (r.sub implies r.fast).
+    const bool anyOdd = __any_sync(RT_FULL, active && !r.sub);
     // Two modes share this loop and the per-lane cursor k.  PACKET: the warp handles the smallest
     // pending node (uniform loads, the union of the lanes' node sets is walked once) — best for
     // coherent rays.  LANE: every lane handles its own node (divergent loads, no union) — best for
-    // incoherent rays (reflections off curved surfaces), where the union approaches the whole tree.
-    // The walk starts in packet mode and switches for the rest of the query after RT_LOW_RUNS
-    // consecutive iterations that served fewer than a quarter of the query's lanes.
-    bool packet = true;
-    int low = 0;
+    // incoherent rays, where the union approaches the whole tree.  The walk starts in packet mode;
+    // every RT_SAMPLE-th iteration it checks how many lanes the iteration serves and switches for
+    // the rest of the query after RT_LOW_RUNS consecutive samples below a quarter of the query's lanes.
+    int pm = -1;                          // -1: packet mode, 0: lane mode (a mask: see kcmp below)
+    int low = 0, it = 0;
     const int quarter = (__popc(__ballot_sync(RT_FULL, active)) + 3) >> 2;
+    const char* __restrict__ nbase = reinterpret_cast<const char*>(S.nodes);
     for (;;) {
         const int kmin = __reduce_min_sync(RT_FULL, k);
         if (kmin >= n) break;
-        const bool mine = packet ? (k == kmin) : (k < n);
+        const int kcmp = (kmin & pm) | (k & ~pm);       // packet: the warp's node; lane: the lane's own node
+        const bool mine = (k == kcmp) && (k < n);
         const int km = mine ? k : kmin;                 // packet mode: kmin for every lane
-        if (packet) {
+        const bool packet = pm != 0;
+        if (((++it) & (RT_SAMPLE - 1)) == 0 && packet) {
             low = __popc(__ballot_sync(RT_FULL, mine)) < quarter ? low + 1 : 0;
-            if (low >= RT_LOW_RUNS) packet = false;
+            if (low >= RT_LOW_RUNS) pm = 0;
         }
-        const float4 a = __ldg(S.nodes + 2 * km);
-        const float4 b = __ldg(S.nodes + 2 * km + 1);
+        const float4* np = reinterpret_cast<const float4*>(nbase + (unsigned)km * 32u);
+        const float4 a = __ldg(np);
+        const float4 b = __ldg(np + 1);
         const int cw = __float_as_int(b.w);
         const int lnk = __float_as_int(a.w);
         RT_TALLY(4, mine ? 1 : 0);
+        if (COUNT) { if ((threadIdx.x & 31) == 0) tl.v[tbase + (packet ? 0 : 1)] += 1; tl.v[tbase + (packet ? 2 : 3)] += mine ? 1 : 0; }
         // The box test is evaluated by ALL lanes without a branch (idle lanes cost no issue slots;
         // a divergent branch around it would).  Reference nodes: the shader's exact slab test; nodes
-        // of our own sub-trees (cw == -2 or leaf bit 30, warp-uniform): conservative boxes, skipped
-        // only for rays the margins were computed for.
+        // of our own sub-trees (cw == -2 or leaf bit 30): conservative boxes, skipped only for
+        // rays the margins were computed for.
         bool h = slab_fast(r, a, b);
-        const bool ours = cw == RT_INNER_SUB || (cw >= 0 && (cw & RT_LEAF_SUB_BIT));
-        if (ours) h = h || !r.sub;
-        else if (anySlow) { if (!r.fast) h = slab(r, a, b); }
-        const bool hit = mine && h;
-        if (cw < 0) {                                   // inner: hit -> next in list, miss -> skip subtree
-            if (mine) k = hit ? km + 1 : lnk;
-            continue;
+        if (anyOdd) {
+            const bool ours = cw == RT_INNER_SUB || (cw >= 0 && (cw & RT_LEAF_SUB_BIT));
+            if (ours) h = h || !r.sub;
+            else if (!r.fast) h = slab(r, a, b);
         }
-        if (mine) k = km + 1;
-        if (hit) {
+        const bool inner = cw < 0;
+        const int next = (inner && !h) ? lnk : km + 1;  // inner: hit -> next in list, miss -> skip the subtree
+        if (mine) k = next;
+        if (!inner && mine && h) {
             const int cnt = cw & RT_LEAF_COUNT_MASK, kind = (cw >> RT_LEAF_KIND_SHIFT) & 3;
             const int end = lnk + cnt;
             RT_TALLY(5, cnt);
@@ -295,7 +307,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
         }
         q.slot = -1; q.p = mk(0.f, 0.f, 0.f);
         if (P.useBVH) {
-            walk<MT, COUNT>(S, q, alive, shadowStep, tl);
+            walk<MT, COUNT>(S, q, alive, shadowStep, tl, step < 2 ? 8 : 12);
         } else if (alive) {
             if (!shadowStep) { Hit h; scan_closest<MT>(S, q.r, h); q.slot = h.slot; q.p = h.p; RT_TALLY(5, S.nShapes); }
             else if (scan_any<MT>(S, q.r, lightDist)) q.slot = 0;
@@ -354,7 +366,7 @@ __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
 render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __restrict__ ids,
               unsigned long long* __restrict__ tally, unsigned int* __restrict__ queue) {
     Tally tl;
-    if (COUNT) { for (int i = 0; i < 8; ++i) tl.v[i] = 0; }
+    if (COUNT) { for (int i = 0; i < RT_NTALLY; ++i) tl.v[i] = 0; }
     const int lane = threadIdx.x & 31;
     const int nItems = P.nTilesMine * RT_WARPS_PER_TILE;
     for (;;) {
@@ -389,7 +401,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         }
     }
     if (COUNT) {
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < RT_NTALLY; ++i) {
             unsigned long long v = tl.v[i];
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             if (lane == 0 && v) atomicAdd(tally + i, v);
