@@ -49,6 +49,8 @@ struct PinBuf {                       // capacity-based pinned host array (keeps
 
 }  // namespace
 
+#define RT_MAX_BANDS 8
+
 struct rt_ctx {
     int device = 0, W = 0, H = 0;
     unsigned flags = 0;
@@ -56,6 +58,8 @@ struct rt_ctx {
     cudaStream_t ownStream = nullptr;
     cudaEvent_t ev[8] = {};          // h2d0,h2d1, repack0,repack1, render0,render1, d2h0,d2h1
     cudaEvent_t copyDone = nullptr;  // last H2D out of the pinned shadows has finished
+    cudaStream_t stream2 = nullptr, copyStream = nullptr;   // banded rt_render: second render stream, D2H stream
+    cudaEvent_t evBand[RT_MAX_BANDS + 3] = {};
     bool copyPending = false;
     bool timed[4] = {false, false, false, false};
     std::string err;
@@ -293,6 +297,9 @@ int rt_create(rt_ctx** out, int width, int height, int device, unsigned flags) {
     if (cudaEventCreateWithFlags(&c->copyDone, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     cudaDeviceGetAttribute(&c->smCount, cudaDevAttrMultiProcessorCount, device);
     c->ownStream = c->stream;
+    if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+    for (auto& e : c->evBand) if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     *out = c;
     return RT_OK;
 }
@@ -309,6 +316,9 @@ void rt_destroy(rt_ctx* c) {
     c->image.release(); c->ids.release(); c->tally.release(); c->queue.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->copyDone) cudaEventDestroy(c->copyDone);
+    for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
+    if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
+    if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
     if (!c->ownStream) c->ownStream = c->stream;      // rt_create failed half-way
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
     delete c;
@@ -323,14 +333,24 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
     CU(c, cudaSetDevice(c->device));
     if (light32)  { std::memcpy(&c->light, light32, sizeof c->light); c->haveLight = true; }
     if (camera80) { std::memcpy(&c->cam, camera80, sizeof c->cam); c->haveCam = true; }
+    // A re-upload of an unchanged topology (same shape types, same index list, same node graph) keeps
+    // the host-built layout: only the bytes go up again and the sub-tree boxes are refitted.
     if (shapes) {
         wait_copies(c);
+        bool sameTypes = c->haveScene && nShapes == c->nShapes && !c->topoDirty;
+        const rt_flat_shape* in = static_cast<const rt_flat_shape*>(shapes);
+        for (int i = 0; sameTypes && i < nShapes; ++i) sameTypes = in[i].type == c->hShapes.p[i].type;
         CU(c, c->hShapes.reserve((size_t)nShapes, 0));
         if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
-        c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes; c->topoDirty = true;
+        c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes;
+        if (!sameTypes) c->topoDirty = true;
     }
-    if (indices) { c->indices.assign(indices, indices + nIndices); c->topoDirty = true; }
-    if (nodes) { int rc = set_nodes(c, nodes, nNodes); if (rc != RT_OK) return rc; if (indices || shapes) c->topoDirty = true; }
+    if (indices) {
+        const bool same = c->haveScene && (size_t)nIndices == c->indices.size() &&
+                          (nIndices == 0 || std::memcmp(indices, c->indices.data(), (size_t)nIndices * sizeof(int32_t)) == 0);
+        if (!same) { c->indices.assign(indices, indices + nIndices); c->topoDirty = true; }
+    }
+    if (nodes) { int rc = set_nodes(c, nodes, nNodes); if (rc != RT_OK) return rc; }
     if (shapes || nodes || indices) c->haveScene = true;
     return flush_scene(c);
 }
@@ -372,7 +392,8 @@ int rt_set_shard(rt_ctx* c, int rank, int world) {
 }
 int64_t rt_shard_pixels(const rt_ctx* c) { return c ? out_pixels(c) : 0; }
 
-static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count);
+static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count,
+                       float* host_rgba = nullptr, int32_t* host_ids = nullptr);
 
 int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids) {
     return render_impl(c, p, dev_rgba, dev_ids, false);
@@ -400,7 +421,12 @@ int rt_walk_stats(rt_ctx* c, uint64_t out[8]) {
     return RT_OK;
 }
 
-static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count) {
+// host_rgba / host_ids != NULL: BANDED mode — the frame is rendered as up to RT_MAX_BANDS launches over
+// consecutive tile rows, alternating between two streams (the next band's CTAs fill the SMs as the
+// previous band's retire), and each finished band is copied to the host on a third stream while
+// the following bands render, so the D2H of the 16 B/pixel frame overlaps the kernel.
+static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count,
+                       float* host_rgba, int32_t* host_ids) {
     if (!c || !p) return RT_ERR_ARG;
     if (!c->haveScene || !c->haveCam || !c->haveLight) return fail(c, RT_ERR_STATE, "render before scene/camera/light upload");
     if (dev_ids && !count && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
@@ -431,35 +457,79 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     F.shardRank = c->shardRank; F.shardWorld = c->shardWorld; F.nTilesMine = tiles_mine(c);
     F.writeIds = (count && dev_ids) ? 2 : wantIds ? 1 : 0;
 
+    const int tilesMine = tiles_mine(c);
+    const bool toHost = host_rgba || host_ids;
+    // bands: whole tile rows (world == 1: a band is a contiguous block of image rows)
+    const int rowTiles = c->shardWorld == 1 ? F.tilesX : 1;
+    int nBands = 1;
+    if (toHost && !count) {
+        const int rows = (tilesMine + rowTiles - 1) / rowTiles;
+        nBands = rows / 16;                              // at least 16 tile rows (128 pixel rows) per band
+        if (nBands > RT_MAX_BANDS) nBands = RT_MAX_BANDS;
+        if (nBands < 1) nBands = 1;
+    }
+    CU(c, c->queue.reserve(RT_MAX_BANDS));
+    CU(c, cudaMemsetAsync(c->queue.p, 0, RT_MAX_BANDS * sizeof(unsigned int), c->stream));
     cudaEventRecord(c->ev[4], c->stream);
-    if (F.nTilesMine > 0) {
-        const int variant = (F.useMT ? 1 : 0) + (count ? 2 : 0);
-        if (c->gridBlocks[variant] == 0) {       // persistent grid: fill every SM once
-            int perSM = 0;
-            const void* fn = variant == 0 ? (const void*)render_kernel<false, false> : variant == 1 ? (const void*)render_kernel<true, false>
-                           : variant == 2 ? (const void*)render_kernel<false, true> : (const void*)render_kernel<true, true>;
-            CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, RT_BLOCK_THREADS, 0));
-            c->gridBlocks[variant] = c->smCount * (perSM > 0 ? perSM : 1);
-        }
+    const int variant = (F.useMT ? 1 : 0) + (count ? 2 : 0);
+    if (tilesMine > 0 && c->gridBlocks[variant] == 0) {       // persistent grid: fill every SM once
+        int perSM = 0;
+        const void* fn = variant == 0 ? (const void*)render_kernel<false, false> : variant == 1 ? (const void*)render_kernel<true, false>
+                       : variant == 2 ? (const void*)render_kernel<false, true> : (const void*)render_kernel<true, true>;
+        CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, RT_BLOCK_THREADS, 0));
+        c->gridBlocks[variant] = c->smCount * (perSM > 0 ? perSM : 1);
+    }
+    cudaEvent_t evFork = c->evBand[RT_MAX_BANDS], evJoin = c->evBand[RT_MAX_BANDS + 1], evCopied = c->evBand[RT_MAX_BANDS + 2];
+    if (nBands > 1 || toHost) {
+        cudaEventRecord(evFork, c->stream);
+        if (nBands > 1) cudaStreamWaitEvent(c->stream2, evFork, 0);
+    }
+    const int rowsTotal = (tilesMine + rowTiles - 1) / rowTiles;
+    bool firstCopy = true;
+    for (int band = 0; band < nBands && tilesMine > 0; ++band) {
+        const int r0 = (int)((long long)rowsTotal * band / nBands), r1 = (int)((long long)rowsTotal * (band + 1) / nBands);
+        const int tb = r0 * rowTiles, te = r1 * rowTiles < tilesMine ? r1 * rowTiles : tilesMine;
+        if (te <= tb) continue;
+        F.tileBegin = tb; F.nTilesMine = te - tb;
+        cudaStream_t rs = (band & 1) ? c->stream2 : c->stream;
         const int items = F.nTilesMine * RT_WARPS_PER_TILE;
         const int needed = (items + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
         const int grid = needed < c->gridBlocks[variant] ? needed : c->gridBlocks[variant];
-        CU(c, c->queue.reserve(1));
-        CU(c, cudaMemsetAsync(c->queue.p, 0, sizeof(unsigned int), c->stream));
         const dim3 blk(RT_BLOCK_THREADS);
         float4* o4 = reinterpret_cast<float4*>(dev_rgba);
         unsigned long long* tl = c->tally.p;
-        unsigned int* q = c->queue.p;
+        unsigned int* q = c->queue.p + band;
         if (count) {
-            if (F.useMT) render_kernel<true, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl, q);
-            else         render_kernel<false, true><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, tl, q);
+            if (F.useMT) render_kernel<true, true><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);
+            else         render_kernel<false, true><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);
         } else {
-            if (F.useMT) render_kernel<true, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr, q);
-            else         render_kernel<false, false><<<grid, blk, 0, c->stream>>>(S, F, o4, dev_ids, nullptr, q);
+            if (F.useMT) render_kernel<true, false><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
+            else         render_kernel<false, false><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
         }
         c->launches++;
+        if (toHost) {
+            // pixels of this band in the output buffer: whole image rows (world == 1) or whole compact tiles
+            size_t p0, p1;
+            if (c->shardWorld == 1) {
+                const size_t y0 = (size_t)r0 * RT_TILE_H, y1 = (size_t)r1 * RT_TILE_H < (size_t)c->H ? (size_t)r1 * RT_TILE_H : (size_t)c->H;
+                p0 = y0 * (size_t)c->W; p1 = y1 * (size_t)c->W;
+            } else {
+                p0 = (size_t)tb * RT_TILE_W * RT_TILE_H; p1 = (size_t)te * RT_TILE_W * RT_TILE_H;
+            }
+            cudaEventRecord(c->evBand[band], rs);
+            cudaStreamWaitEvent(c->copyStream, c->evBand[band], 0);
+            if (firstCopy) { cudaEventRecord(c->ev[6], c->copyStream); firstCopy = false; }
+            if (host_rgba) CU(c, cudaMemcpyAsync(host_rgba + 4 * p0, dev_rgba + 4 * p0, (p1 - p0) * sizeof(float4), cudaMemcpyDeviceToHost, c->copyStream));
+            if (host_ids) CU(c, cudaMemcpyAsync(host_ids + p0, dev_ids + p0, (p1 - p0) * sizeof(int), cudaMemcpyDeviceToHost, c->copyStream));
+        }
     }
+    if (nBands > 1) { cudaEventRecord(evJoin, c->stream2); cudaStreamWaitEvent(c->stream, evJoin, 0); }
     cudaEventRecord(c->ev[5], c->stream); c->timed[2] = true;
+    if (toHost && !firstCopy) {
+        cudaEventRecord(c->ev[7], c->copyStream); c->timed[3] = true;
+        cudaEventRecord(evCopied, c->copyStream);
+        cudaStreamWaitEvent(c->stream, evCopied, 0);      // everything is ordered on the context stream again
+    }
     CU(c, cudaGetLastError());
     return RT_OK;
 }
@@ -467,13 +537,8 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
 int rt_render(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* host_hit_ids) {
     if (!c || !p) return RT_ERR_ARG;
     if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
-    int rc = rt_render_device(c, p, nullptr, nullptr);
+    int rc = render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids);
     if (rc != RT_OK) return rc;
-    const size_t px = (size_t)out_pixels(c);
-    cudaEventRecord(c->ev[6], c->stream);
-    if (host_rgba) CU(c, cudaMemcpyAsync(host_rgba, c->image.p, px * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-    if (host_hit_ids) CU(c, cudaMemcpyAsync(host_hit_ids, c->ids.p, px * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    cudaEventRecord(c->ev[7], c->stream); c->timed[3] = true;
     CU(c, cudaStreamSynchronize(c->stream));
     return RT_OK;
 }

@@ -81,7 +81,8 @@ struct FrameParams {
     int   W, H;                // image size in pixels
     int   tilesX, tilesY;      // tile grid
     int   shardRank, shardWorld;
-    int   nTilesMine;          // tiles owned by this rank
+    int   nTilesMine;          // tiles of this rank handled by this launch ...
+    int   tileBegin;           // ... starting at this index of the rank's tile list (banded launches)
     int   writeIds;
 };
 

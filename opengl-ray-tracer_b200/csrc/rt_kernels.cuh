@@ -374,7 +374,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         if (lane == 0) w = (int)atomicAdd(queue, 1u);
         w = __shfl_sync(0xffffffffu, w, 0);
         if (w >= nItems) break;
-        const int t = w / RT_WARPS_PER_TILE, b = w % RT_WARPS_PER_TILE;
+        const int t = P.tileBegin + w / RT_WARPS_PER_TILE, b = w % RT_WARPS_PER_TILE;
         const int tile = P.shardRank + t * P.shardWorld;
         const int lx = ((b & 3) << 3) + (lane & 7);
         const int ly = ((b >> 2) << 2) + (lane >> 3);
