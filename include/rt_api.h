@@ -115,6 +115,11 @@ int64_t rt_shard_pixels(const rt_ctx* ctx);
  * are the compact tile-major shard instead. */
 int rt_render(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* host_hit_ids);
 
+/* rt_render without the final wait: the frame lands in host_rgba (pinned memory for a truly
+ * asynchronous copy) once rt_synchronize(ctx) returns.  Lets the host prepare the next frame's
+ * scene update (main.cpp:438-457 animation step) while this one renders and copies. */
+int rt_render_async(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* host_hit_ids);
+
 /* Same, but writes into caller-provided DEVICE buffers (e.g. torch tensors)
  * and returns without synchronising: work is ordered on rt_stream(ctx). */
 int rt_render_device(rt_ctx* ctx, const rt_params* params, float* dev_rgba, int32_t* dev_hit_ids);

@@ -54,7 +54,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -81,6 +81,7 @@ def lib():
     L.rt_set_shard.argtypes = [vp, ip, ip]; L.rt_set_shard.restype = ip
     L.rt_shard_pixels.argtypes = [vp]; L.rt_shard_pixels.restype = C.c_int64
     L.rt_render.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render.restype = ip
+    L.rt_render_async.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_async.restype = ip
     L.rt_render_device.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_device.restype = ip
     L.rt_render_stats.argtypes = [vp, C.POINTER(Params), C.POINTER(C.c_uint64), vp]; L.rt_render_stats.restype = ip
     L.rt_walk_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_walk_stats.restype = ip
@@ -265,6 +266,10 @@ class RayTracer:
             rgba = rgba.reshape(self.height, self.width, 4)
             ids = ids.reshape(self.height, self.width) if ids is not None else None
         return rgba, ids
+
+    def render_async(self, params, out, out_ids=None):
+        """rt_render_async: returns at once; `out` (pinned) is complete after synchronize()."""
+        self._chk(self._L.rt_render_async(self._c, C.byref(params), _ptr(out), _ptr(out_ids)))
 
     def render_device(self, params, dev_rgba_ptr=None, dev_ids_ptr=None):
         """Asynchronous render into device memory (pointers as ints, e.g. tensor.data_ptr())."""

@@ -543,6 +543,12 @@ int rt_render(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* host_hit
     return RT_OK;
 }
 
+int rt_render_async(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* host_hit_ids) {
+    if (!c || !p) return RT_ERR_ARG;
+    if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
+    return render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids);
+}
+
 int rt_untile(rt_ctx* c, const float* dev_shards, int world, float* dev_rgba_out) {
     if (!c || !dev_shards || !dev_rgba_out || world < 1) return RT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));

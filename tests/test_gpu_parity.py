@@ -241,3 +241,37 @@ def test_camera_far_away(rt, oracle):
         assert_parity(compare(rgba, ids, o_rgba, o_ids), "camera at %g" % dist)
         assert (o_ids >= 0).any()
     tr.close()
+
+
+@pytest.mark.parametrize("n,W,H", [(20000, 320, 240), (1000000, 256, 144)])
+def test_soup_parity(rt, oracle, n, W, H):
+    """BASELINE configs[3]: triangle soup + spheres, deep BVH (traversal-bound); the full 1M-triangle scene at a
+    resolution the oracle finishes in seconds."""
+    sc = rt.Scene("soup", W, H, n_override=n)
+    stats, *_ = _render_both(rt, oracle, sc, W, H)
+    assert_parity(stats, "soup %d" % n)
+
+
+def test_render_async_and_banded_copy(rt, oracle):
+    """rt_render_async (banded launches, D2H overlapped) delivers the same bytes as rt_render / rt_render_device."""
+    import torch
+    W, H = 640, 520                                  # 65 tile rows -> 4 bands, ragged last tile row
+    sc = rt.Scene("monkey", W, H)
+    p = rt.make_params(W, H, useFresnel=True)
+    tr = rt.RayTracer(W, H)
+    tr.upload(sc)
+    ref, ref_ids = tr.render(p)
+    pin = torch.empty((H * W, 4), dtype=torch.float32, pin_memory=True).numpy()
+    pin_ids = torch.empty(H * W, dtype=torch.int32, pin_memory=True).numpy()
+    pin[:] = -7.0
+    tr.render_async(p, pin, pin_ids)
+    tr.synchronize()
+    assert np.array_equal(pin.reshape(H, W, 4).view(np.uint32), ref.view(np.uint32))
+    assert np.array_equal(pin_ids.reshape(H, W), ref_ids)
+    dev = torch.empty((H, W, 4), dtype=torch.float32, device="cuda")
+    tr.render_device(p, dev.data_ptr())
+    tr.synchronize()
+    assert np.array_equal(dev.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+    o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
+    assert_parity(compare(ref, ref_ids, o_rgba, o_ids), "banded")
+    tr.close()
