@@ -52,6 +52,9 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (core-seconds are bounded by a row sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--gather", default="fused", choices=["fused", "nccl"],
+                    help="N>1: fused = every rank's render kernel stores its tiles into rank 0's frame over NVLink peer memory "
+                         "(one tiny all-reduce as completion barrier); nccl = compact shards + dist.gather + untile kernel")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic only: keep L2 warm between steps (not a valid bench line)")
     return ap.parse_args()
 
@@ -219,9 +222,20 @@ def workload_config(args, **more):
 # ---------------------------------------------------------------------------------------------
 # The B200 arm
 # ---------------------------------------------------------------------------------------------
-def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, flush):
+def setup_fused(torch, dist, tr, rank, world):
+    """Rank 0 exports its full frame over CUDA IPC, the others map it (peer access over NVLink)."""
+    box = [tr.frame_export() if rank == 0 else None]
+    handle = [box[0][0] if rank == 0 else None]
+    dist.broadcast_object_list(handle, src=0)
+    if rank != 0:
+        tr.frame_open(handle[0])
+    return box[0][1] if rank == 0 else None
+
+
+def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, flush, fused=False):
     """Device-timed frames with the scene resident.  Returns per-rank mean ms (total, render, gather)."""
     px = tr.shard_pixels()
+    token = torch.zeros(1, dtype=torch.int32, device="cuda") if (fused and world > 1) else None
     shard = torch.empty((px, 4), dtype=torch.float32, device="cuda")
     full = torch.empty((H, W, 4), dtype=torch.float32, device="cuda") if (rank == 0 and world > 1) else None
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
@@ -231,12 +245,17 @@ def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, f
         if flush is not None:
             flush.zero_()                       # evict the scene and the image from L2 (untimed)
         e0.record()
-        tr.render_device(params, shard.data_ptr())
-        e1.record()
-        if world > 1:
-            got = rt.shard.gather_shards(shard, rank, world)
-            if rank == 0:
-                tr.untile(got.data_ptr(), world, full.data_ptr())
+        if token is not None:
+            tr.render_device(params)            # tiles go straight into rank 0's frame (peer stores)
+            e1.record()
+            dist.all_reduce(token)              # completion barrier: the only collective left
+        else:
+            tr.render_device(params, shard.data_ptr())
+            e1.record()
+            if world > 1:
+                got = rt.shard.gather_shards(shard, rank, world)
+                if rank == 0:
+                    tr.untile(got.data_ptr(), world, full.data_ptr())
         e2.record()
         return (e0, e1, e2) if timed else None
 
@@ -256,7 +275,7 @@ def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, f
     return tot, ren, tot - ren, (full if full is not None else shard)
 
 
-def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup):
+def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup, frame_ptr=None, fused=False):
     """End to end through the C ABI from HOST buffers: upload (pinned staging + H2D + repack), render,
     (gather + untile), D2H of the rgba32f frame into pinned host memory.  Wall clock, sync both sides."""
     light, cam, shapes, nodes, idx = sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices
@@ -267,11 +286,18 @@ def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup):
         shard = torch.empty((px, 4), dtype=torch.float32, device="cuda")
         full = torch.empty((H, W, 4), dtype=torch.float32, device="cuda") if rank == 0 else None
         host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
+        token = torch.zeros(1, dtype=torch.int32, device="cuda")
 
     def frame():
         tr.upload_scene(light, cam, shapes, nodes, idx)
         if world == 1:
             tr.render(params, want_ids=False, out=host)
+        elif fused:
+            tr.render_device(params)
+            dist.all_reduce(token)
+            if rank == 0:
+                tr.frame_download(host.data_ptr())
+            torch.cuda.synchronize()
         else:
             tr.render_device(params, shard.data_ptr())
             got = rt.shard.gather_shards(shard, rank, world)
@@ -390,14 +416,37 @@ def main():
         launches0 = tr.launch_count()
         if rank == 0:
             clocks.start()
-        tot, ren, gat, _ = time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush)
-        clk = clocks.stop() if rank == 0 else None
+        fused = world > 1 and args.gather == "fused"
+        frame_ptr = setup_fused(torch, dist, tr, rank, world) if fused else None
+        tot, ren, gat, _ = time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush, fused=fused)
         launches = (tr.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
+        nccl_ms = None
+        if fused:                               # the NCCL-gather path beside it (north_star: gather timed separately)
+            t2 = torch.tensor(list(time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush)[:3]),
+                              dtype=torch.float64, device="cuda")
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+            nccl_ms = dict(zip(["total_ms", "render_ms", "gather_untile_ms"], t2.tolist()))
+        clk = clocks.stop() if rank == 0 else None
+        frame_ok = None
+        if fused:                               # the gathered frame must equal a single-GPU render bit for bit
+            tr.render_device(params)
+            dist.all_reduce(torch.zeros(1, dtype=torch.int32, device="cuda"))
+            torch.cuda.synchronize()
+            if rank == 0:
+                got = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+                tr.frame_download(got.data_ptr()); tr.synchronize()
+                solo = rt.RayTracer(W, H, device=local, flags=0)
+                solo.upload(sc)
+                want, _ = solo.render(params, want_ids=False)
+                solo.close()
+                frame_ok = bool(np.array_equal(got.numpy().view(np.uint32), want.view(np.uint32)))
+            dist.barrier()
         t = torch.tensor([tot, ren, gat], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         tot, ren, gat = t.tolist()
-        e2e_ms, h2d, d2h = time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, max(3, args.steps // 3), 3)
+        e2e_ms, h2d, d2h = time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, max(3, args.steps // 3), 3,
+                                     frame_ptr=frame_ptr, fused=fused)
         t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -442,6 +491,8 @@ def main():
             "warmup": args.warmup, "ms_per_step": tot, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "fps": 1e3 / tot, "render_ms": ren, "gather_untile_ms": gat,
+            "gather": ("fused: peer stores from the render kernel + 1 all-reduce barrier" if fused else "nccl gather + untile") if world > 1 else None,
+            "nccl_gather_path": nccl_ms, "gathered_frame_equals_single_gpu": frame_ok,
             "rays_per_frame": rays, "rays_counted_by_kernel": rays_gpu, "rays_match_oracle": rays_match,
             "kernel_work": {"node_visits": nodes_gpu, "prim_tests": tests_gpu,
                             "reference_node_visits": consts["node_visits"] if consts else None,

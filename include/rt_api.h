@@ -136,6 +136,22 @@ int rt_render_stats(rt_ctx* ctx, const rt_params* params, uint64_t out[8], int32
  * mode, lanes served in packet mode, lanes served in lane mode. */
 int rt_walk_stats(rt_ctx* ctx, uint64_t out[8]);
 
+/* ---- fused gather (multi-GPU) -----------------------------------------------
+ * Instead of gathering compact shards and untiling them, every rank's render kernel can store
+ * its pixels straight into their row-major place of ONE full W*H frame that lives on rank 0,
+ * through a peer mapping over NVLink (the exchange step happens inside the render kernel, tile
+ * by tile).  Rank 0 calls rt_frame_export (allocates the frame, returns a 64-byte CUDA IPC
+ * handle to ship to the other processes and the frame's device pointer); the others call
+ * rt_frame_open.  A single-process driver can hand any device pointer to rt_set_frame_target
+ * (NULL switches the mode off).  While a frame target is set and world > 1,
+ * rt_render_device(ctx, params, NULL, NULL) writes there; the frame is complete once every rank
+ * has synchronised (a barrier is the only collective left). */
+int rt_set_frame_target(rt_ctx* ctx, float* dev_frame);
+int rt_frame_export(rt_ctx* ctx, unsigned char handle[64], float** dev_frame);
+int rt_frame_open(rt_ctx* ctx, const unsigned char handle[64]);
+/* Rank 0: asynchronous copy of the exported frame to the host (ordered on rt_stream). */
+int rt_frame_download(rt_ctx* ctx, float* host_rgba);
+
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in
  * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one
  * row-major W*H image. */

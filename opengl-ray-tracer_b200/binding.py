@@ -54,7 +54,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -85,6 +85,10 @@ def lib():
     L.rt_render_device.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_device.restype = ip
     L.rt_render_stats.argtypes = [vp, C.POINTER(Params), C.POINTER(C.c_uint64), vp]; L.rt_render_stats.restype = ip
     L.rt_walk_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_walk_stats.restype = ip
+    L.rt_set_frame_target.argtypes = [vp, vp]; L.rt_set_frame_target.restype = ip
+    L.rt_frame_export.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; L.rt_frame_export.restype = ip
+    L.rt_frame_open.argtypes = [vp, C.c_char_p]; L.rt_frame_open.restype = ip
+    L.rt_frame_download.argtypes = [vp, vp]; L.rt_frame_download.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
     L.rt_stream.argtypes = [vp]; L.rt_stream.restype = vp
@@ -288,6 +292,22 @@ class RayTracer:
         keys = ["packet_iters", "lane_iters", "packet_served", "lane_served"]
         v = [int(x) for x in out]
         return {"primary": dict(zip(keys, v[:4])), "bounce": dict(zip(keys, v[4:]))}
+
+    def set_frame_target(self, dev_ptr):
+        self._chk(self._L.rt_set_frame_target(self._c, _ptr(dev_ptr) if dev_ptr else None))
+
+    def frame_export(self):
+        """Rank 0: returns (64-byte IPC handle, device pointer of the full frame)."""
+        h = C.create_string_buffer(64)
+        p = C.c_void_p()
+        self._chk(self._L.rt_frame_export(self._c, h, C.byref(p)))
+        return h.raw, p.value
+
+    def frame_open(self, handle):
+        self._chk(self._L.rt_frame_open(self._c, C.create_string_buffer(handle, 64)))
+
+    def frame_download(self, host):
+        self._chk(self._L.rt_frame_download(self._c, _ptr(host)))
 
     def untile(self, dev_shards_ptr, world, dev_out_ptr):
         self._chk(self._L.rt_untile(self._c, _ptr(dev_shards_ptr), world, _ptr(dev_out_ptr)))

@@ -95,6 +95,9 @@ struct rt_ctx {
 
     // output
     DevBuf<float4> image; DevBuf<int> ids;
+    DevBuf<float4> frame;             // full W*H frame other ranks write into (rt_frame_export)
+    float* frameTarget = nullptr;     // where this rank's tiles go row-major (local frame, peer mapping, or caller's)
+    void* ipcOpened = nullptr;        // mapping obtained from cudaIpcOpenMemHandle
     DevBuf<unsigned long long> tally;
     DevBuf<unsigned int> queue;       // work-stealing counter of K1
     int gridBlocks[4] = {0, 0, 0, 0}; // persistent grid per kernel variant
@@ -313,6 +316,8 @@ void rt_destroy(rt_ctx* c) {
     c->hPshape.release(); c->dPshape.release(); c->hPrank.release(); c->dPrank.release();
     c->hSubBox.release(); c->dSubBox.release(); c->dNodesT.release();
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
+    if (c->ipcOpened) cudaIpcCloseMemHandle(c->ipcOpened);
+    c->frame.release();
     c->image.release(); c->ids.release(); c->tally.release(); c->queue.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->copyDone) cudaEventDestroy(c->copyDone);
@@ -434,7 +439,9 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     int rc = flush_scene(c);
     if (rc != RT_OK) return rc;
     const int64_t px = out_pixels(c);
-    if (!dev_rgba) { CU(c, c->image.reserve((size_t)px)); dev_rgba = reinterpret_cast<float*>(c->image.p); }
+    // fused gather: no explicit output buffer, a frame target set, several ranks
+    const bool useFrame = !dev_rgba && !host_rgba && !count && c->frameTarget && c->shardWorld > 1;
+    if (!dev_rgba && !useFrame) { CU(c, c->image.reserve((size_t)px)); dev_rgba = reinterpret_cast<float*>(c->image.p); }
     const bool wantIds = (c->flags & RT_FLAG_HIT_IDS) != 0;
     if (wantIds && !dev_ids) { CU(c, c->ids.reserve((size_t)px)); dev_ids = c->ids.p; }
 
@@ -456,6 +463,8 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     F.W = c->W; F.H = c->H; F.tilesX = tiles_x(c); F.tilesY = tiles_y(c);
     F.shardRank = c->shardRank; F.shardWorld = c->shardWorld; F.nTilesMine = tiles_mine(c);
     F.writeIds = (count && dev_ids) ? 2 : wantIds ? 1 : 0;
+    F.frameTarget = 0;
+    if (useFrame) { F.frameTarget = 1; dev_rgba = c->frameTarget; }
 
     const int tilesMine = tiles_mine(c);
     const bool toHost = host_rgba || host_ids;
@@ -547,6 +556,46 @@ int rt_render_async(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* ho
     if (!c || !p) return RT_ERR_ARG;
     if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
     return render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids);
+}
+
+int rt_set_frame_target(rt_ctx* c, float* dev_frame) {
+    if (!c) return RT_ERR_ARG;
+    c->frameTarget = dev_frame;
+    return RT_OK;
+}
+
+int rt_frame_export(rt_ctx* c, unsigned char handle[64], float** dev_frame) {
+    if (!c || !handle) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->frame.reserve((size_t)c->W * (size_t)c->H));
+    cudaIpcMemHandle_t h;
+    CU(c, cudaIpcGetMemHandle(&h, c->frame.p));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    std::memcpy(handle, &h, 64);
+    c->frameTarget = reinterpret_cast<float*>(c->frame.p);
+    if (dev_frame) *dev_frame = c->frameTarget;
+    return RT_OK;
+}
+
+int rt_frame_open(rt_ctx* c, const unsigned char handle[64]) {
+    if (!c || !handle) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    if (c->ipcOpened) { cudaIpcCloseMemHandle(c->ipcOpened); c->ipcOpened = nullptr; c->frameTarget = nullptr; }
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    void* p = nullptr;
+    CU(c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->ipcOpened = p;
+    c->frameTarget = static_cast<float*>(p);
+    return RT_OK;
+}
+
+int rt_frame_download(rt_ctx* c, float* host_rgba) {
+    if (!c || !host_rgba) return RT_ERR_ARG;
+    if (!c->frame.p) return fail(c, RT_ERR_STATE, "no exported frame on this context");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemcpyAsync(host_rgba, c->frame.p, (size_t)c->W * (size_t)c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    return RT_OK;
 }
 
 int rt_untile(rt_ctx* c, const float* dev_shards, int world, float* dev_rgba_out) {

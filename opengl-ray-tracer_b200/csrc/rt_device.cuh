@@ -84,6 +84,7 @@ struct FrameParams {
     int   nTilesMine;          // tiles of this rank handled by this launch ...
     int   tileBegin;           // ... starting at this index of the rank's tile list (banded launches)
     int   writeIds;
+    int   frameTarget;         // world > 1: colours go row-major into a full W*H frame (rank 0's, possibly peer memory)
 };
 
 // ---------------------------------------------------------------------------

@@ -396,7 +396,10 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
             }
         } else {
             const size_t o = (size_t)t * (RT_TILE_W * RT_TILE_H) + (size_t)(ly * RT_TILE_W + lx);
-            out[o] = c;
+            // fused gather: the pixel goes straight to its row-major place in the full frame, which
+            // may live on another GPU (peer mapping over NVLink); 128-byte row segments per warp
+            if (P.frameTarget) { if (inside) out[(size_t)y * (size_t)P.W + (size_t)x] = c; }
+            else out[o] = c;
             if (P.writeIds) ids[o] = id;
         }
     }

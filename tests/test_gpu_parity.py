@@ -275,3 +275,30 @@ def test_render_async_and_banded_copy(rt, oracle):
     o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
     assert_parity(compare(ref, ref_ids, o_rgba, o_ids), "banded")
     tr.close()
+
+
+def test_fused_gather_frame_target(rt):
+    """Fused gather on one device: the contexts of `world` ranks store their tiles straight into one row-major
+    frame (rt_set_frame_target; across processes the same pointer is a CUDA-IPC peer mapping) == the 1-GPU image."""
+    import torch
+    W, H = 333, 201
+    sc = rt.Scene("monkey", W, H)
+    p = rt.make_params(W, H)
+    tr = rt.RayTracer(W, H)
+    tr.upload(sc)
+    full, _ = tr.render(p)
+    tr.close()
+    for world in (2, 5):
+        frame = torch.full((H, W, 4), -1.0, dtype=torch.float32, device="cuda")
+        ranks = []
+        for r in range(world):
+            t = rt.RayTracer(W, H, flags=0)
+            t.upload(sc)
+            t.set_shard(r, world)
+            t.set_frame_target(frame.data_ptr())
+            t.render_device(p)
+            ranks.append(t)
+        for t in ranks:
+            t.synchronize()
+            t.close()
+        assert np.array_equal(frame.cpu().numpy().view(np.uint32), full.view(np.uint32)), "world=%d" % world
