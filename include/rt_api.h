@@ -61,6 +61,12 @@ enum {
      * into private sub-trees whose boxes are conservative bounds of each
      * primitive's fp32 acceptance region, so no hit/miss decision changes. */
     RT_FLAG_REFERENCE_WALK = 1u << 0,
+    /* Keep the reference's tree above its leaves.  By default, when the reference
+     * boxes are nested (children inside parents), a binned-SAH tree of exact union
+     * boxes over the reference LEAVES replaces it for rays with finite origin and
+     * 1/d whenever its SAH estimate is >10% cheaper: the fp32 slab test is monotone
+     * for such rays, so the same leaves pass. */
+    RT_FLAG_NO_TOP_TREE = 1u << 2,
     /* Record per-pixel primary-hit shape ids (an AOV the reference lacks;
      * needed by the parity criterion).  Off = the id buffer is not written. */
     RT_FLAG_HIT_IDS   = 1u << 1
@@ -135,6 +141,8 @@ int rt_render_stats(rt_ctx* ctx, const rt_params* params, uint64_t out[8], int32
  * out[4..7] for later (bounce) segments: warp iterations in packet mode, warp iterations in lane
  * mode, lanes served in packet mode, lanes served in lane mode. */
 int rt_walk_stats(rt_ctx* ctx, uint64_t out[8]);
+/* Same call: out[0] = SM cycles of the slowest 8x4-pixel warp item, out[1] = sum over items, out[2] = items. */
+int rt_item_stats(rt_ctx* ctx, uint64_t out[3]);
 
 /* ---- fused gather (multi-GPU) -----------------------------------------------
  * Instead of gathering compact shards and untiling them, every rank's render kernel can store

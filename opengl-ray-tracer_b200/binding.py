@@ -31,6 +31,7 @@ NODE_DTYPE = np.dtype({"names": ["boundsMin", "boundsMax", "leftChild", "rightCh
 
 RT_FLAG_REFERENCE_WALK = 1
 RT_FLAG_HIT_IDS = 2
+RT_FLAG_NO_TOP_TREE = 4
 TILE_W, TILE_H = 32, 8
 
 
@@ -54,7 +55,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -89,6 +90,7 @@ def lib():
     L.rt_frame_export.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; L.rt_frame_export.restype = ip
     L.rt_frame_open.argtypes = [vp, C.c_char_p]; L.rt_frame_open.restype = ip
     L.rt_frame_download.argtypes = [vp, vp]; L.rt_frame_download.restype = ip
+    L.rt_item_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_item_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
     L.rt_stream.argtypes = [vp]; L.rt_stream.restype = vp
@@ -308,6 +310,11 @@ class RayTracer:
 
     def frame_download(self, host):
         self._chk(self._L.rt_frame_download(self._c, _ptr(host)))
+
+    def item_stats(self):
+        out = (C.c_uint64 * 3)()
+        self._chk(self._L.rt_item_stats(self._c, out))
+        return dict(max_item_cycles=int(out[0]), mean_item_cycles=int(out[1]) / max(1, int(out[2])), items=int(out[2]))
 
     def untile(self, dev_shards_ptr, world, dev_out_ptr):
         self._chk(self._L.rt_untile(self._c, _ptr(dev_shards_ptr), world, _ptr(dev_out_ptr)))

@@ -79,6 +79,10 @@ struct rt_ctx {
     PinBuf<int2> hLinkCnt; DevBuf<int2> dLinkCnt;
     PinBuf<int>  hPshape;  DevBuf<int>  dPshape;
     PinBuf<int>  hPrank;   DevBuf<int>  dPrank;
+    PinBuf<int>  hOrderB;   DevBuf<int>  dOrderB;      // list B (own tree over the reference leaves)
+    PinBuf<int2> hLinkCntB; DevBuf<int2> dLinkCntB;
+    DevBuf<float4> dNodesB;
+    int nDfsB = 0;
     PinBuf<float4> hSubBox; DevBuf<float4> dSubBox;   // 2 float4 per sub-tree node (host-computed conservative boxes)
     rtl::Layout layout;               // host copy of the threaded layout (refit of the sub-tree boxes)
     int nSub = 0;
@@ -167,8 +171,13 @@ int build_visit_order(rt_ctx* c) {
     if (!rtl::build_layout(c->hNodes.p, c->nNodes, c->indices.data(), c->indices.size(), c->hShapes.p, c->nShapes,
                            subtrees, (double)c->omax, L))
         return fail(c, RT_ERR_SCENE, L.error ? L.error : "malformed BVH");
+    if (subtrees && !(c->flags & RT_FLAG_NO_TOP_TREE)) rtl::build_top(L, c->hNodes.p, c->nNodes);
     const int m = L.nodes(), prims = L.prims();
     c->nSub = (int)L.subBox.size();
+    c->nDfsB = L.useB ? (int)L.srcB.size() : 0;
+    CU(c, c->hOrderB.reserve((size_t)c->nDfsB, 0));
+    CU(c, c->hLinkCntB.reserve((size_t)c->nDfsB, 0));
+    for (int k = 0; k < c->nDfsB; ++k) { c->hOrderB.p[k] = L.srcB[(size_t)k]; c->hLinkCntB.p[k] = make_int2(L.linkB[(size_t)k], L.cwB[(size_t)k]); }
     CU(c, c->hOrder.reserve((size_t)m, 0));
     CU(c, c->hLinkCnt.reserve((size_t)m, 0));
     CU(c, c->hPshape.reserve((size_t)prims, 0));
@@ -208,6 +217,13 @@ int flush_scene(rt_ctx* c) {
         CU(c, cudaMemcpyAsync(c->dNodes.p, c->hNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyHostToDevice, c->stream));
     }
     bool subUpload = false;
+    if (c->nodesDirty && !c->topoDirty && c->nDfsB > 0) {
+        // reference boxes changed under an unchanged topology (grow-only refit): B's union boxes follow;
+        // if the reference tree stopped being nested, B is no longer equivalent and is switched off
+        wait_copies(c);
+        if (rtl::ref_tree_nested(c->hNodes.p, c->nNodes)) { rtl::refit_top(c->layout, c->hNodes.p); stage_subboxes(c); subUpload = true; }
+        else { c->nDfsB = 0; c->layout.useB = false; }
+    }
     if (c->subDirty && !c->topoDirty) {
         // shapes moved under a sub-tree (or omax grew): refit its boxes on the host; a primitive that
         // stopped being boundable forces a rebuild of the layout
@@ -231,6 +247,11 @@ int flush_scene(rt_ctx* c) {
             CU(c, cudaMemcpyAsync(c->dOrder.p, c->hOrder.p, (size_t)c->nDfs * sizeof(int), cudaMemcpyHostToDevice, c->stream));
             CU(c, cudaMemcpyAsync(c->dLinkCnt.p, c->hLinkCnt.p, (size_t)c->nDfs * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
         }
+        if (c->nDfsB > 0) {
+            CU(c, c->dOrderB.reserve((size_t)c->nDfsB)); CU(c, c->dLinkCntB.reserve((size_t)c->nDfsB)); CU(c, c->dNodesB.reserve((size_t)c->nDfsB * 2));
+            CU(c, cudaMemcpyAsync(c->dOrderB.p, c->hOrderB.p, (size_t)c->nDfsB * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+            CU(c, cudaMemcpyAsync(c->dLinkCntB.p, c->hLinkCntB.p, (size_t)c->nDfsB * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
+        }
         if (c->nPrims > 0) {
             CU(c, cudaMemcpyAsync(c->dPshape.p, c->hPshape.p, (size_t)c->nPrims * sizeof(int), cudaMemcpyHostToDevice, c->stream));
             CU(c, cudaMemcpyAsync(c->dPrank.p, c->hPrank.p, (size_t)c->nPrims * sizeof(int), cudaMemcpyHostToDevice, c->stream));
@@ -247,6 +268,10 @@ int flush_scene(rt_ctx* c) {
     if ((c->nodesDirty || c->topoDirty || subUpload) && c->nDfs > 0) {
         repack_nodes_kernel<<<(c->nDfs + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dSubBox.p, c->dOrder.p, c->dLinkCnt.p, c->dNodesT.p, c->nDfs);
         c->launches++;
+        if (c->nDfsB > 0) {
+            repack_nodes_kernel<<<(c->nDfsB + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dSubBox.p, c->dOrderB.p, c->dLinkCntB.p, c->dNodesB.p, c->nDfsB);
+            c->launches++;
+        }
     }
     if ((shapesChanged || c->topoDirty) && c->nPrims > 0) {
         repack_prims_kernel<<<(c->nPrims + 255) / 256, 256, 0, c->stream>>>(c->dShapes.p, c->dPshape.p, c->q0.p, c->q1.p, c->q2.p, c->q3.p, c->ptype.p, c->nPrims);
@@ -315,6 +340,7 @@ void rt_destroy(rt_ctx* c) {
     c->hOrder.release(); c->dOrder.release(); c->hLinkCnt.release(); c->dLinkCnt.release();
     c->hPshape.release(); c->dPshape.release(); c->hPrank.release(); c->dPrank.release();
     c->hSubBox.release(); c->dSubBox.release(); c->dNodesT.release();
+    c->hOrderB.release(); c->dOrderB.release(); c->hLinkCntB.release(); c->dLinkCntB.release(); c->dNodesB.release();
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
     if (c->ipcOpened) cudaIpcCloseMemHandle(c->ipcOpened);
     c->frame.release();
@@ -420,9 +446,16 @@ int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8], int32_t* hos
     return RT_OK;
 }
 
+int rt_item_stats(rt_ctx* c, uint64_t out[3]) {
+    if (!c || !out) return RT_ERR_ARG;
+    out[0] = c->lastTally[16]; out[1] = c->lastTally[17]; out[2] = c->lastTally[18];
+    return RT_OK;
+}
+
 int rt_walk_stats(rt_ctx* c, uint64_t out[8]) {
     if (!c || !out) return RT_ERR_ARG;
     for (int i = 0; i < 8; ++i) out[i] = c->lastTally[8 + i];
+
     return RT_OK;
 }
 
@@ -446,7 +479,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     if (wantIds && !dev_ids) { CU(c, c->ids.reserve((size_t)px)); dev_ids = c->ids.p; }
 
     DeviceScene S;
-    S.nodes = c->dNodesT.p; S.q0 = c->q0.p; S.q1 = c->q1.p; S.q2 = c->q2.p; S.q3 = c->q3.p;
+    S.nodes = c->dNodesT.p; S.nodesB = c->nDfsB > 0 ? c->dNodesB.p : nullptr; S.nNodesB = c->nDfsB; S.q0 = c->q0.p; S.q1 = c->q1.p; S.q2 = c->q2.p; S.q3 = c->q3.p;
     S.ptype = c->ptype.p; S.pshape = c->dPshape.p; S.prank = c->dPrank.p; S.shapes = c->dShapes.p;
     S.nNodes = c->nDfs; S.nPrims = c->nPrims; S.nShapes = c->nShapes; S.boxesFinite = c->boxesFinite ? 1 : 0;
     S.omax = c->omax;
@@ -503,7 +536,12 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         cudaStream_t rs = (band & 1) ? c->stream2 : c->stream;
         const int items = F.nTilesMine * RT_WARPS_PER_TILE;
         const int needed = (items + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
-        const int grid = needed < c->gridBlocks[variant] ? needed : c->gridBlocks[variant];
+        int grid = needed < c->gridBlocks[variant] ? needed : c->gridBlocks[variant];
+        {   // experiment knob: RT_ITEMS_PER_WARP=n launches a regular (non-persistent) grid
+            static const int ipw = std::getenv("RT_ITEMS_PER_WARP") ? std::atoi(std::getenv("RT_ITEMS_PER_WARP")) : 0;
+            F.itemsPerWarp = ipw;
+            if (ipw > 0) grid = (needed + ipw - 1) / ipw;
+        }
         const dim3 blk(RT_BLOCK_THREADS);
         float4* o4 = reinterpret_cast<float4*>(dev_rgba);
         unsigned long long* tl = c->tally.p;

@@ -45,7 +45,9 @@ namespace rt {
 //   type 2 wall     q0=(n, D) q1=(start, width) q2=(u, height) q3=(v, 0)
 //   type 3 triangle q0=(n, D) q1=(P1, d00)      q2=(e1, d01)   q3=(e2, d11)
 struct DeviceScene {
-    const float4* __restrict__ nodes;   // 2 per node
+    const float4* __restrict__ nodes;   // 2 per node: list A (reference tree order, fat leaves expanded)
+    const float4* __restrict__ nodesB;  // list B: own SAH tree over the reference leaves (rt_layout.h build_top), or NULL
+    int nNodesB;
     const float4* __restrict__ q0;
     const float4* __restrict__ q1;
     const float4* __restrict__ q2;
@@ -84,6 +86,7 @@ struct FrameParams {
     int   nTilesMine;          // tiles of this rank handled by this launch ...
     int   tileBegin;           // ... starting at this index of the rank's tile list (banded launches)
     int   writeIds;
+    int   itemsPerWarp;        // 0: persistent warps (loop until the queue is empty); n: a warp retires after n items
     int   frameTarget;         // world > 1: colours go row-major into a full W*H frame (rank 0's, possibly peer memory)
 };
 

@@ -21,7 +21,7 @@ struct Hit { float dist; int slot; V3 p; };
 // [5] primitive tests [6] closest-hit queries that hit [7] shadow queries that were occluded
 // [8..11] primary segments, [12..15] later segments: packet-mode warp iterations, lane-mode warp
 // iterations, lanes served in packet mode, lanes served in lane mode (walk efficiency diagnostics)
-#define RT_NTALLY 16
+#define RT_NTALLY 20       // [16] max cycles of one warp item, [17] sum of item cycles, [18] items, [19] kernel cycles (max over warps)
 struct Tally { unsigned long long v[RT_NTALLY]; };
 #define RT_TALLY(i, n) do { if (COUNT) tl.v[i] += (n); } while (0)
 
@@ -138,7 +138,6 @@ __device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const f
 #endif
 template <bool MT, bool COUNT>
 __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active, bool anyMode, Tally& tl, int tbase) {
-    const int n = S.nNodes;
     const Ray& r = q.r;
     int k = active ? 0 : RT_DONE;
     // Rays that cannot use the NaN-free fast slab test (non-finite origin or 1/d) or for which the
@@ -154,7 +153,11 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
     int pm = -1;                          // -1: packet mode, 0: lane mode (a mask: see kcmp below)
     int low = 0, it = 0;
     const int quarter = (__popc(__ballot_sync(RT_FULL, active)) + 3) >> 2;
-    const char* __restrict__ nbase = reinterpret_cast<const char*>(S.nodes);
+    // List B (own tree over the reference leaves) is valid for rays with finite origin and 1/d inside
+    // omax; a warp with any other ray walks list A, the reference's own tree order.
+    const bool useB = S.nNodesB > 0 && !anyOdd;
+    const int n = useB ? S.nNodesB : S.nNodes;
+    const char* __restrict__ nbase = reinterpret_cast<const char*>(useB ? S.nodesB : S.nodes);
     for (;;) {
         const int kmin = __reduce_min_sync(RT_FULL, k);
         if (kmin >= n) break;
@@ -369,7 +372,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
     if (COUNT) { for (int i = 0; i < RT_NTALLY; ++i) tl.v[i] = 0; }
     const int lane = threadIdx.x & 31;
     const int nItems = P.nTilesMine * RT_WARPS_PER_TILE;
-    for (;;) {
+    for (int round = 0; P.itemsPerWarp == 0 || round < P.itemsPerWarp; ++round) {
         int w = 0;
         if (lane == 0) w = (int)atomicAdd(queue, 1u);
         w = __shfl_sync(0xffffffffu, w, 0);
@@ -384,9 +387,27 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         int id = -1;
         unsigned long long cost0 = 0;
-        if (COUNT) cost0 = tl.v[4] + tl.v[5];
+        long long clk0 = 0;
+        unsigned long long it0[4] = {0, 0, 0, 0};
+        if (COUNT) { cost0 = tl.v[4] + tl.v[5]; clk0 = clock64(); it0[0] = tl.v[8]; it0[1] = tl.v[9]; it0[2] = tl.v[12]; it0[3] = tl.v[13]; }
         c = shade_pixel<MT, COUNT>(S, P, x, y, inside, id, tl);
         if (COUNT && P.writeIds == 2) id = (int)(tl.v[4] + tl.v[5] - cost0);   // diagnostic: per-pixel work AOV
+        if (COUNT) {
+            const unsigned long long dt = (unsigned long long)(clock64() - clk0);
+            if (lane == 0) { atomicMax(tally + 16, dt); tl.v[17] += dt; tl.v[18] += 1; }
+            if (P.writeIds == 2) {                          // walk iterations of this item (lane 0 counts them): pixels 4..7
+                const unsigned d0 = __shfl_sync(0xffffffffu, (unsigned)(tl.v[8] - it0[0]), 0), d1 = __shfl_sync(0xffffffffu, (unsigned)(tl.v[9] - it0[1]), 0);
+                const unsigned d2 = __shfl_sync(0xffffffffu, (unsigned)(tl.v[12] - it0[2]), 0), d3 = __shfl_sync(0xffffffffu, (unsigned)(tl.v[13] - it0[3]), 0);
+                if (lane >= 4 && lane < 8) id = (int)(lane == 4 ? d0 : lane == 5 ? d1 : lane == 6 ? d2 : d3);
+            }
+            if (P.writeIds == 2 && lane < 4) {              // timeline AOV in the first four pixels of the block
+                unsigned long long gt; unsigned smid, wid;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+                asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+                asm volatile("mov.u32 %0, %%warpid;" : "=r"(wid));
+                id = lane == 0 ? (int)(gt & 0x7fffffff) : lane == 1 ? (int)(dt >> 2) : lane == 2 ? (int)smid : (int)wid;
+            }
+        }
         __syncwarp();
         if (P.shardWorld == 1) {
             if (inside) {
@@ -407,7 +428,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         for (int i = 0; i < RT_NTALLY; ++i) {
             unsigned long long v = tl.v[i];
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (lane == 0 && v) atomicAdd(tally + i, v);
+            if (lane == 0 && v && i != 16 && i != 19) atomicAdd(tally + i, v);
         }
     }
 }

@@ -172,6 +172,7 @@ struct SubBuilder {
     const std::vector<Box>& pb;          // bound per item
     std::vector<int>& items;             // permuted in place
     std::vector<SubNode> nodes;
+    int maxLeaf = RT_SUB_LEAF;
     SubBuilder(const std::vector<Box>& b, std::vector<int>& it) : pb(b), items(it) {}
 
     int build(int first, int count) {
@@ -186,7 +187,7 @@ struct SubBuilder {
             cb.grow(c);
         }
         nodes[(size_t)id].box = bb; nodes[(size_t)id].first = first; nodes[(size_t)id].count = count;
-        if (count <= RT_SUB_LEAF) return id;
+        if (count <= maxLeaf) return id;
         // binned SAH over the centroid bounds
         const int NB = 16;
         int bestAxis = -1, bestSplit = -1; double bestCost = INFINITY;
@@ -250,6 +251,14 @@ struct Layout {
     std::vector<int> subPos;     // emitted position of sub node j
     double omax = 0;             // the margins hold for ray origins with |o|_inf <= omax
     int nRefLeavesFat = 0;
+    // reference leaves ("entries") in visit order: position of their node (leaf, or fat leaf turned inner) in the list
+    std::vector<int> entryPos, entryRaw;
+    // Layout B (see build_top): our own SAH tree over the reference LEAVES, used for well-behaved rays
+    std::vector<int> srcB, linkB, cwB;
+    std::vector<int> topPos;     // position in B of top node t; its box is subBox[nSubA + t]
+    int nSubA = 0;               // sub boxes [0, nSubA) belong to the fat-leaf sub-trees, the rest to B's top nodes
+    double costA = 0, costB = 0; // SAH estimates (expected box tests per random ray) of the two node lists
+    bool useB = false;
     const char* error = nullptr;
 
     int nodes() const { return (int)src.size(); }
@@ -312,6 +321,7 @@ inline bool build_layout(const rt_flat_node* nd, int nNodes, const int32_t* indi
             }
             if (!ok) break;
             if (!subtrees || n <= RT_FAT_LEAF) {
+                L.entryPos.push_back(k); L.entryRaw.push_back(it.node);
                 L.src.push_back(it.node); L.link.push_back(slot0);
                 L.cw.push_back(n | (leaf_kind(shapes, L.pshape.data() + slot0, n) << RTL_KIND_SHIFT));
                 continue;
@@ -340,6 +350,7 @@ inline bool build_layout(const rt_flat_node* nd, int nNodes, const int32_t* indi
             const int t = (int)trees.size();
             trees.push_back(sb); treeItems.push_back(items); treeBoxes.push_back(boxes); treeSlot0.push_back(slot0 + (int)unb.size());
             L.nRefLeavesFat++;
+            L.entryPos.push_back(k); L.entryRaw.push_back(it.node);
             // the reference leaf becomes an inner node with the reference box (exact reference test)
             L.src.push_back(it.node); L.link.push_back(0); L.cw.push_back(RTL_INNER_REF);
             // children (popped in reverse push order): always-leaf first, then the sub-tree root
@@ -376,6 +387,7 @@ inline bool build_layout(const rt_flat_node* nd, int nNodes, const int32_t* indi
     std::vector<int> size((size_t)m, 1);
     for (int k = m - 1; k >= 1; --k) size[(size_t)parent[(size_t)k]] += size[(size_t)k];
     for (int k = 0; k < m; ++k) if (L.cw[(size_t)k] < 0) L.link[(size_t)k] = k + size[(size_t)k];
+    L.nSubA = (int)L.subBox.size();
     return true;
 }
 
@@ -385,7 +397,7 @@ inline bool build_layout(const rt_flat_node* nd, int nNodes, const int32_t* indi
 // to move to the always-tested leaf): the caller then rebuilds the layout.
 inline bool refit_subboxes(Layout& L, const rt_flat_shape* shapes, double omax) {
     L.omax = omax;
-    for (int j = (int)L.subBox.size() - 1; j >= 0; --j) {
+    for (int j = L.nSubA - 1; j >= 0; --j) {
         const int k = L.subPos[(size_t)j];
         Box b; b.reset();
         if (L.cw[(size_t)k] >= 0) {
@@ -404,6 +416,117 @@ inline bool refit_subboxes(Layout& L, const rt_flat_shape* shapes, double omax) 
         L.subBox[(size_t)j] = b;
     }
     return true;
+}
+
+
+// ---------------------------------------------------------------------------
+// Layout B: our own tree over the reference LEAVES.
+//
+// When every reference node's box contains its children's boxes coordinate-wise (true for the
+// reference builder, whose boxes are unions; checked here), the fp32 slab test is monotone for a
+// ray with finite origin and finite 1/d: a ray that passes a leaf's box test passes the test of
+// every box containing it.  The reference then tests a leaf's primitives iff the ray passes the
+// LEAF's own box test, and any tree of exact union boxes over the leaves selects the same leaves.
+// B is a binned-SAH tree over the leaf boxes (the reference's midpoint-split tree is shallow on
+// quality: the 1M-triangle soup costs ~290 box tests per ray through it), entries copied from A
+// (fat-leaf sub-trees included), candidates ordered by rank as before.  Rays with a non-finite
+// origin or 1/d (NaN semantics are not monotone) and rays beyond omax walk list A.
+// ---------------------------------------------------------------------------
+inline Box raw_box(const rt_flat_node& x) {
+    Box b;
+    for (int a = 0; a < 3; ++a) { b.mn[a] = x.boundsMin[a]; b.mx[a] = x.boundsMax[a]; }
+    return b;
+}
+
+inline bool ref_tree_nested(const rt_flat_node* nd, int nNodes) {
+    for (int i = 0; i < nNodes; ++i) {
+        const rt_flat_node& x = nd[i];
+        for (int a = 0; a < 3; ++a) if (!std::isfinite(x.boundsMin[a]) || !std::isfinite(x.boundsMax[a])) return false;
+        if (x.leftChild == -1) continue;
+        const int ch[2] = {x.leftChild, x.rightChild};
+        for (int c : ch) {
+            if (c < 0 || c >= nNodes) return false;
+            for (int a = 0; a < 3; ++a) {
+                // an EMPTY child box (min > max: a leaf without shapes keeps the +inf/-inf initial box) never passes its own test
+                if (!(nd[c].boundsMin[a] >= x.boundsMin[a]) || !(nd[c].boundsMax[a] <= x.boundsMax[a])) return false;
+            }
+        }
+    }
+    return true;
+}
+
+// Recompute the boxes of B's top nodes from the current raw node boxes (bottom-up) and the SAH estimates.
+inline void refit_top(Layout& L, const rt_flat_node* nd) {
+    const int mB = (int)L.srcB.size();
+    auto boxOf = [&](int k) -> Box { const int s = L.srcB[(size_t)k]; return s >= 0 ? raw_box(nd[s]) : L.subBox[(size_t)(-1 - s)]; };
+    for (int t = (int)L.topPos.size() - 1; t >= 0; --t) {
+        const int k = L.topPos[(size_t)t];
+        const int c1 = k + 1, c2 = L.cwB[(size_t)c1] < 0 ? L.linkB[(size_t)c1] : c1 + 1;
+        Box b; b.reset();
+        b.grow(boxOf(c1)); b.grow(boxOf(c2));
+        L.subBox[(size_t)(L.nSubA + t)] = b;
+    }
+    // SAH estimate: sum of node areas relative to the root (every node whose parent is hit costs one test)
+    auto cost = [&](const std::vector<int>& src, int n) {
+        if (n == 0) return 0.0;
+        auto bx = [&](int k) { const int s = src[(size_t)k]; return s >= 0 ? raw_box(nd[s]) : L.subBox[(size_t)(-1 - s)]; };
+        const double root = bx(0).area();
+        double c = 0;
+        for (int k = 0; k < n; ++k) c += bx(k).area();
+        return root > 0 ? c / root : 0.0;
+    };
+    L.costA = cost(L.src, L.nodes());
+    L.costB = cost(L.srcB, mB);
+}
+
+inline void build_top(Layout& L, const rt_flat_node* nd, int nNodes) {
+    L.srcB.clear(); L.linkB.clear(); L.cwB.clear(); L.topPos.clear();
+    L.subBox.resize((size_t)L.nSubA);
+    L.useB = false;
+    const int nE = (int)L.entryPos.size();
+    if (nE < 4 || !ref_tree_nested(nd, nNodes)) return;
+    std::vector<Box> eb((size_t)nE);
+    std::vector<int> items((size_t)nE);
+    for (int e = 0; e < nE; ++e) { eb[(size_t)e] = raw_box(nd[L.entryRaw[(size_t)e]]); items[(size_t)e] = e; }
+    // empty leaves (min > max) can never be hit: leave them out of B
+    items.erase(std::remove_if(items.begin(), items.end(), [&](int e) {
+        const Box& b = eb[(size_t)e];
+        return b.mn[0] > b.mx[0] || b.mn[1] > b.mx[1] || b.mn[2] > b.mx[2];
+    }), items.end());
+    if (items.size() < 4) return;
+    SubBuilder sb(eb, items);
+    sb.maxLeaf = 1;
+    sb.build(0, (int)items.size());
+    // emit B in pre-order with an explicit stack; a top inner node's link is patched when its subtree is complete
+    struct Item { int node; int patch; };      // node >= 0: visit; node < 0: patch link of B position `patch`
+    std::vector<Item> st; st.push_back({0, -1});
+    while (!st.empty()) {
+        const Item it = st.back(); st.pop_back();
+        if (it.node < 0) { L.linkB[(size_t)it.patch] = (int)L.srcB.size(); continue; }
+        const SubNode& sn = sb.nodes[(size_t)it.node];
+        const int k = (int)L.srcB.size();
+        if (sn.left < 0) {                       // one reference leaf: copy its nodes from A
+            const int e = items[(size_t)sn.first];
+            const int p0 = L.entryPos[(size_t)e];
+            const int p1 = L.cw[(size_t)p0] < 0 ? L.link[(size_t)p0] : p0 + 1;
+            const int delta = k - p0;
+            for (int q = p0; q < p1; ++q) {
+                L.srcB.push_back(L.src[(size_t)q]); L.cwB.push_back(L.cw[(size_t)q]);
+                L.linkB.push_back(L.cw[(size_t)q] < 0 ? L.link[(size_t)q] + delta : L.link[(size_t)q]);
+            }
+            continue;
+        }
+        const int t = (int)L.topPos.size();
+        L.topPos.push_back(k);
+        L.subBox.emplace_back();
+        L.srcB.push_back(-1 - (L.nSubA + t)); L.cwB.push_back(RTL_INNER_REF); L.linkB.push_back(0);
+        st.push_back({-1, k});
+        st.push_back({sn.right, -1});
+        st.push_back({sn.left, -1});
+    }
+    refit_top(L, nd);
+    L.useB = L.costB < 0.9 * L.costA;
+    if (!L.useB) { L.srcB.clear(); L.linkB.clear(); L.cwB.clear(); L.topPos.clear(); L.subBox.resize((size_t)L.nSubA); }
 }
 
 }  // namespace rtl

@@ -16,8 +16,11 @@ namespace {
 struct Emu {
     rtl::Layout L;
     std::vector<Prim> prims;
-    std::vector<float4> nodes;     // 2 per node
+    std::vector<float4> nodes;     // 2 per node (list A)
+    std::vector<float4> nodesB;    // list B (own tree over the reference leaves), empty if unused
+    const rt_flat_node* raw = nullptr;
     bool boxesFinite = true;
+    int nNodes = 0;
     float omax = 0.f;
 };
 
@@ -27,11 +30,16 @@ void query(const Emu& E, const float* o, const float* d, int anyMode, float boun
     Ray r = make_ray(mk(o), mk(d), E.boxesFinite, E.omax);
     float best = anyMode ? bound : 1e20f;
     int slot = -1; V3 bp = mk(0.f, 0.f, 0.f);
-    const int n = E.L.nodes();
+    // well-behaved rays walk list B when it exists (the kernel decides per warp; per ray here)
+    const bool useB = r.sub && !E.nodesB.empty();
+    const std::vector<float4>& N = useB ? E.nodesB : E.nodes;
+    const std::vector<int>& CW = useB ? E.L.cwB : E.L.cw;
+    const std::vector<int>& LNK = useB ? E.L.linkB : E.L.link;
+    const int n = (int)CW.size();
     int k = 0;
     while (k < n) {
-        const float4 a = E.nodes[2 * (size_t)k], b = E.nodes[2 * (size_t)k + 1];
-        const int cw = E.L.cw[(size_t)k], lnk = E.L.link[(size_t)k];
+        const float4 a = N[2 * (size_t)k], b = N[2 * (size_t)k + 1];
+        const int cw = CW[(size_t)k], lnk = LNK[(size_t)k];
         cnt[0]++;
         const bool ours = cw == RT_INNER_SUB || (cw >= 0 && (cw & RT_LEAF_SUB_BIT));
         const bool hit = ours ? (!r.sub || slab_fast(r, a, b)) : (r.fast ? slab_fast(r, a, b) : slab(r, a, b));
@@ -57,38 +65,51 @@ void query(const Emu& E, const float* o, const float* d, int anyMode, float boun
 }
 }  // namespace
 
+static void fill_nodes(Emu* E, const rt_flat_node* nodes) {
+    auto fill = [&](const std::vector<int>& src, std::vector<float4>& out) {
+        out.resize(2 * src.size());
+        for (size_t k = 0; k < src.size(); ++k) {
+            const int s = src[k];
+            if (s >= 0) {
+                out[2 * k] = make_float4(nodes[s].boundsMin[0], nodes[s].boundsMin[1], nodes[s].boundsMin[2], 0.f);
+                out[2 * k + 1] = make_float4(nodes[s].boundsMax[0], nodes[s].boundsMax[1], nodes[s].boundsMax[2], 0.f);
+            } else {
+                const rtl::Box& b = E->L.subBox[(size_t)(-1 - s)];
+                out[2 * k] = make_float4(b.mn[0], b.mn[1], b.mn[2], 0.f);
+                out[2 * k + 1] = make_float4(b.mx[0], b.mx[1], b.mx[2], 0.f);
+            }
+        }
+    };
+    fill(E->L.src, E->nodes);
+    if (E->L.useB) fill(E->L.srcB, E->nodesB); else E->nodesB.clear();
+}
+
 extern "C" {
 
 void* emu_create(const rt_flat_shape* shapes, int nShapes, const rt_flat_node* nodes, int nNodes,
                  const int32_t* indices, int nIndices, int subtrees, double omax) {
+    const bool topTree = (subtrees & 2) != 0;
+    subtrees &= 1;
     Emu* E = new Emu();
     for (int i = 0; i < nNodes && E->boxesFinite; ++i)
         for (int k = 0; k < 3; ++k)
             if (!(fabsf(nodes[i].boundsMin[k]) <= RT_SAFE_COORD) || !(fabsf(nodes[i].boundsMax[k]) <= RT_SAFE_COORD)) E->boxesFinite = false;
     E->omax = (float)omax;
+    E->nNodes = nNodes;
     if (!rtl::build_layout(nodes, nNodes, indices, (size_t)nIndices, shapes, nShapes, subtrees && E->boxesFinite, omax, E->L)) { delete E; return nullptr; }
     E->prims.resize((size_t)E->L.prims());
     for (int s = 0; s < E->L.prims(); ++s) E->prims[(size_t)s] = prim_from_shape(shapes + E->L.pshape[(size_t)s]);
-    E->nodes.resize(2 * (size_t)E->L.nodes());
-    for (int k = 0; k < E->L.nodes(); ++k) {
-        const int src = E->L.src[(size_t)k];
-        if (src >= 0) {
-            E->nodes[2 * (size_t)k] = make_float4(nodes[src].boundsMin[0], nodes[src].boundsMin[1], nodes[src].boundsMin[2], 0.f);
-            E->nodes[2 * (size_t)k + 1] = make_float4(nodes[src].boundsMax[0], nodes[src].boundsMax[1], nodes[src].boundsMax[2], 0.f);
-        } else {
-            const rtl::Box& b = E->L.subBox[(size_t)(-1 - src)];
-            E->nodes[2 * (size_t)k] = make_float4(b.mn[0], b.mn[1], b.mn[2], 0.f);
-            E->nodes[2 * (size_t)k + 1] = make_float4(b.mx[0], b.mx[1], b.mx[2], 0.f);
-        }
-    }
+    if (subtrees && E->boxesFinite && topTree) rtl::build_top(E->L, nodes, nNodes);
+    fill_nodes(E, nodes);
     return E;
 }
 void emu_destroy(void* e) { delete static_cast<Emu*>(e); }
 
-// info: [0] emitted nodes [1] sub nodes [2] prims [3] fat leaves [4] max leaf size
-void emu_info(void* e, int out[5]) {
+// info: [0] emitted nodes [1] sub nodes [2] prims [3] fat leaves [4] max leaf size [5] nodes of list B (0 = unused)
+void emu_info(void* e, int out[6]) {
+    out[5] = static_cast<Emu*>(e)->L.useB ? (int)static_cast<Emu*>(e)->L.srcB.size() : 0;
     const Emu* E = static_cast<Emu*>(e);
-    out[0] = E->L.nodes(); out[1] = (int)E->L.subBox.size(); out[2] = E->L.prims(); out[3] = E->L.nRefLeavesFat; out[4] = 0;
+    out[0] = E->L.nodes(); out[1] = E->L.nSubA; out[2] = E->L.prims(); out[3] = E->L.nRefLeavesFat; out[4] = 0;
     for (int k = 0; k < E->L.nodes(); ++k) if (E->L.cw[(size_t)k] >= 0 && (E->L.cw[(size_t)k] & RT_LEAF_COUNT_MASK) > out[4]) out[4] = E->L.cw[(size_t)k] & RT_LEAF_COUNT_MASK;
 }
 
@@ -97,17 +118,8 @@ int emu_refit(void* e, const rt_flat_shape* shapes, const rt_flat_node* nodes) {
     Emu* E = static_cast<Emu*>(e);
     if (!rtl::refit_subboxes(E->L, shapes, (double)E->omax)) return 0;
     for (int s = 0; s < E->L.prims(); ++s) E->prims[(size_t)s] = prim_from_shape(shapes + E->L.pshape[(size_t)s]);
-    for (int k = 0; k < E->L.nodes(); ++k) {
-        const int src = E->L.src[(size_t)k];
-        if (src >= 0) {
-            E->nodes[2 * (size_t)k] = make_float4(nodes[src].boundsMin[0], nodes[src].boundsMin[1], nodes[src].boundsMin[2], 0.f);
-            E->nodes[2 * (size_t)k + 1] = make_float4(nodes[src].boundsMax[0], nodes[src].boundsMax[1], nodes[src].boundsMax[2], 0.f);
-        } else {
-            const rtl::Box& b = E->L.subBox[(size_t)(-1 - src)];
-            E->nodes[2 * (size_t)k] = make_float4(b.mn[0], b.mn[1], b.mn[2], 0.f);
-            E->nodes[2 * (size_t)k + 1] = make_float4(b.mx[0], b.mx[1], b.mx[2], 0.f);
-        }
-    }
+    if (E->L.useB) { if (rtl::ref_tree_nested(nodes, E->nNodes)) rtl::refit_top(E->L, nodes); else E->L.useB = false; }
+    fill_nodes(E, nodes);
     return 1;
 }
 

@@ -302,3 +302,28 @@ def test_fused_gather_frame_target(rt):
             t.synchronize()
             t.close()
         assert np.array_equal(frame.cpu().numpy().view(np.uint32), full.view(np.uint32)), "world=%d" % world
+
+
+def test_top_tree_flag_matches(rt, oracle):
+    """List B (own SAH tree over the reference leaves) against RT_FLAG_NO_TOP_TREE: same ids, bit-identical colours,
+    fewer box tests; also after a grow-only refit of the reference boxes (rt_update_nodes)."""
+    W, H = 400, 300
+    sc = rt.Scene("car", W, H)
+    p = rt.make_params(W, H, useFresnel=True)
+    a = rt.RayTracer(W, H, flags=rt.RT_FLAG_HIT_IDS)
+    b = rt.RayTracer(W, H, flags=rt.RT_FLAG_HIT_IDS | rt.RT_FLAG_NO_TOP_TREE)
+    a.upload(sc); b.upload(sc)
+    for frame in range(3):
+        if frame:
+            sc.animate(frame * 0.3, 0.3, mode=0)
+            an = sc.animated
+            lo, hi = int(an.min()), int(an.max()) + 1
+            for t in (a, b):
+                t.update_shapes(lo, sc.shapes[lo:hi]); t.update_nodes(sc.nodes)
+        ra, ia = a.render(p); rb, ib = b.render(p)
+        assert np.array_equal(ia, ib) and np.array_equal(ra.view(np.uint32), rb.view(np.uint32)), "frame %d" % frame
+        sa, sb = a.render_stats(p), b.render_stats(p)
+        assert sa["rays"] == sb["rays"] and sa["node_visits"] < sb["node_visits"]
+    o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
+    assert_parity(compare(ra, ia, o_rgba, o_ids), "top tree, animated")
+    a.close(); b.close()

@@ -38,20 +38,20 @@ def _p(a):
 
 
 class Emu:
-    def __init__(self, L, shapes, nodes, indices, subtrees=True, omax=None):
+    def __init__(self, L, shapes, nodes, indices, subtrees=True, omax=None, top=True):
         self.L = L
         self.keep = [np.ascontiguousarray(a) for a in (shapes, nodes, indices)]
         sh, nd, ix = self.keep
         if omax is None:
             omax = 4.0 * max(1.0, float(np.abs(nd["boundsMin"][-1]).max()), float(np.abs(nd["boundsMax"][-1]).max())) if len(nd) else 4.0
         self.omax = omax
-        self.h = L.emu_create(_p(sh), len(sh), _p(nd), len(nd), _p(ix), len(ix), int(subtrees), float(omax))
+        self.h = L.emu_create(_p(sh), len(sh), _p(nd), len(nd), _p(ix), len(ix), int(subtrees) | (2 if (top and subtrees) else 0), float(omax))
         assert self.h
 
     def info(self):
-        out = (C.c_int * 5)()
+        out = (C.c_int * 6)()
         self.L.emu_info(self.h, out)
-        return dict(nodes=out[0], sub=out[1], prims=out[2], fat=out[3], max_leaf=out[4])
+        return dict(nodes=out[0], sub=out[1], prims=out[2], fat=out[3], max_leaf=out[4], nodes_b=out[5])
 
     def query(self, o, d, mt=False, bounds=None):
         o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)

@@ -15,4 +15,5 @@ for b in (1, 3):
     st = tr.render_stats(p)
     print("bounces", b, st)
     print("   ", tr.walk_stats())
+    print("   ", tr.item_stats())
 tr.close()
