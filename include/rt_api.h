@@ -67,6 +67,10 @@ enum {
      * 1/d whenever its SAH estimate is >10% cheaper: the fp32 slab test is monotone
      * for such rays, so the same leaves pass. */
     RT_FLAG_NO_TOP_TREE = 1u << 2,
+    /* Claim the 8x4-pixel blocks in plain order.  By default rt_render_device records every block's
+     * cost and the next frame claims the blocks that were slow first (frame-to-frame coherence), so
+     * the long dependent walks of incoherent bounce packets overlap the bulk instead of forming the tail. */
+    RT_FLAG_NO_HEAVY_FIRST = 1u << 3,
     /* Record per-pixel primary-hit shape ids (an AOV the reference lacks;
      * needed by the parity criterion).  Off = the id buffer is not written. */
     RT_FLAG_HIT_IDS   = 1u << 1

@@ -32,6 +32,7 @@ NODE_DTYPE = np.dtype({"names": ["boundsMin", "boundsMax", "leftChild", "rightCh
 RT_FLAG_REFERENCE_WALK = 1
 RT_FLAG_HIT_IDS = 2
 RT_FLAG_NO_TOP_TREE = 4
+RT_FLAG_NO_HEAVY_FIRST = 8
 TILE_W, TILE_H = 32, 8
 
 

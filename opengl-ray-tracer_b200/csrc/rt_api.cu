@@ -104,6 +104,9 @@ struct rt_ctx {
     void* ipcOpened = nullptr;        // mapping obtained from cudaIpcOpenMemHandle
     DevBuf<unsigned long long> tally;
     DevBuf<unsigned int> queue;       // work-stealing counter of K1
+    DevBuf<unsigned> itemCost, heavyList, lptCtl;   // heavy-first scheduling from the previous frame's item costs
+    DevBuf<unsigned char> heavyFlag;
+    int lptItems = -1;                // item count the recorded costs belong to (-1: none yet)
     int gridBlocks[4] = {0, 0, 0, 0}; // persistent grid per kernel variant
     int shardRank = 0, shardWorld = 1;
 };
@@ -344,6 +347,7 @@ void rt_destroy(rt_ctx* c) {
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
     if (c->ipcOpened) cudaIpcCloseMemHandle(c->ipcOpened);
     c->frame.release();
+    c->itemCost.release(); c->heavyList.release(); c->lptCtl.release(); c->heavyFlag.release();
     c->image.release(); c->ids.release(); c->tally.release(); c->queue.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->copyDone) cudaEventDestroy(c->copyDone);
@@ -418,7 +422,7 @@ int rt_update_nodes(rt_ctx* c, const void* nodes, int nNodes) {
 
 int rt_set_shard(rt_ctx* c, int rank, int world) {
     if (!c || world < 1 || rank < 0 || rank >= world) return RT_ERR_ARG;
-    c->shardRank = rank; c->shardWorld = world;
+    c->shardRank = rank; c->shardWorld = world; c->lptItems = -1;
     return RT_OK;
 }
 int64_t rt_shard_pixels(const rt_ctx* c) { return c ? out_pixels(c) : 0; }
@@ -520,6 +524,21 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
                        : variant == 2 ? (const void*)render_kernel<false, true> : (const void*)render_kernel<true, true>;
         CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, RT_BLOCK_THREADS, 0));
         c->gridBlocks[variant] = c->smCount * (perSM > 0 ? perSM : 1);
+    }
+    // heavy-first order (single-launch renders): build the list from the previous frame's item costs
+    F.itemCost = nullptr; F.heavyList = nullptr; F.heavyFlag = nullptr; F.lptCtl = nullptr;
+    if (nBands == 1 && !count && tilesMine > 0 && !(c->flags & RT_FLAG_NO_HEAVY_FIRST)) {
+        const int items = tilesMine * RT_WARPS_PER_TILE;
+        CU(c, c->itemCost.reserve((size_t)items)); CU(c, c->heavyList.reserve((size_t)items));
+        CU(c, c->heavyFlag.reserve((size_t)items)); CU(c, c->lptCtl.reserve(4));
+        CU(c, cudaMemsetAsync(c->lptCtl.p, 0, 4 * sizeof(unsigned), c->stream));
+        if (c->lptItems == items) {
+            lpt_sum_kernel<<<64, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p);
+            lpt_mark_kernel<<<(items + 255) / 256, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p, c->heavyList.p, c->heavyFlag.p);
+            c->launches += 2;
+        }
+        c->lptItems = items;
+        F.itemCost = c->itemCost.p; F.heavyList = c->heavyList.p; F.heavyFlag = c->heavyFlag.p; F.lptCtl = c->lptCtl.p;
     }
     cudaEvent_t evFork = c->evBand[RT_MAX_BANDS], evJoin = c->evBand[RT_MAX_BANDS + 1], evCopied = c->evBand[RT_MAX_BANDS + 2];
     if (nBands > 1 || toHost) {

@@ -86,6 +86,11 @@ struct FrameParams {
     int   nTilesMine;          // tiles of this rank handled by this launch ...
     int   tileBegin;           // ... starting at this index of the rank's tile list (banded launches)
     int   writeIds;
+    // Heavy-first scheduling (LPT with last frame's measured item costs, see lpt_*_kernel): NULL = off
+    unsigned* itemCost;        // [items] SM cycles >> 4 of every warp item, written by this launch
+    const unsigned* heavyList; // items whose last cost exceeded RT_HEAVY_FACTOR x mean, claimed first
+    const unsigned char* heavyFlag;
+    const unsigned* lptCtl;    // [0] number of heavy items
     int   itemsPerWarp;        // 0: persistent warps (loop until the queue is empty); n: a warp retires after n items
     int   frameTarget;         // world > 1: colours go row-major into a full W*H frame (rank 0's, possibly peer memory)
 };

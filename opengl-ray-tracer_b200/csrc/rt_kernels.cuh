@@ -133,6 +133,9 @@ __device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const f
 #ifndef RT_LOW_RUNS
 #define RT_LOW_RUNS 2
 #endif
+#ifndef RT_LANE_SHIFT
+#define RT_LANE_SHIFT 2     // switch to lane mode when an iteration serves fewer than 1/2^shift of the query's lanes
+#endif
 #ifndef RT_SAMPLE
 #define RT_SAMPLE 4         // power of two
 #endif
@@ -152,7 +155,7 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
     // the rest of the query after RT_LOW_RUNS consecutive samples below a quarter of the query's lanes.
     int pm = -1;                          // -1: packet mode, 0: lane mode (a mask: see kcmp below)
     int low = 0, it = 0;
-    const int quarter = (__popc(__ballot_sync(RT_FULL, active)) + 3) >> 2;
+    const int quarter = (__popc(__ballot_sync(RT_FULL, active)) + (1 << RT_LANE_SHIFT) - 1) >> RT_LANE_SHIFT;
     // List B (own tree over the reference leaves) is valid for rays with finite origin and 1/d inside
     // omax; a warp with any other ray walks list A, the reference's own tree order.
     const bool useB = S.nNodesB > 0 && !anyOdd;
@@ -372,11 +375,22 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
     if (COUNT) { for (int i = 0; i < RT_NTALLY; ++i) tl.v[i] = 0; }
     const int lane = threadIdx.x & 31;
     const int nItems = P.nTilesMine * RT_WARPS_PER_TILE;
+    // Heavy-first order: the critical path of a frame is its slowest 8x4 block (an incoherent bounce
+    // packet walks hundreds of nodes in sequence); blocks that were slow in the previous frame are
+    // claimed first so that their chains overlap the bulk of the work instead of forming the tail.
+    const int nHeavy = P.lptCtl ? (int)__ldg(P.lptCtl) : 0;
     for (int round = 0; P.itemsPerWarp == 0 || round < P.itemsPerWarp; ++round) {
         int w = 0;
         if (lane == 0) w = (int)atomicAdd(queue, 1u);
         w = __shfl_sync(0xffffffffu, w, 0);
-        if (w >= nItems) break;
+        if (w < nHeavy) {
+            w = (int)__ldg(P.heavyList + w);
+        } else {
+            w -= nHeavy;
+            if (w >= nItems) break;
+            if (nHeavy > 0 && __ldg(P.heavyFlag + w)) continue;
+        }
+        const long long itemClk0 = P.itemCost ? clock64() : 0;
         const int t = P.tileBegin + w / RT_WARPS_PER_TILE, b = w % RT_WARPS_PER_TILE;
         const int tile = P.shardRank + t * P.shardWorld;
         const int lx = ((b & 3) << 3) + (lane & 7);
@@ -423,6 +437,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
             else out[o] = c;
             if (P.writeIds) ids[o] = id;
         }
+        if (P.itemCost && lane == 0) P.itemCost[w] = (unsigned)((unsigned long long)(clock64() - itemClk0) >> 4);
     }
     if (COUNT) {
         for (int i = 0; i < RT_NTALLY; ++i) {
@@ -431,6 +446,29 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
             if (lane == 0 && v && i != 16 && i != 19) atomicAdd(tally + i, v);
         }
     }
+}
+
+// ---------------------------------------------------------------------------
+// Heavy-first list for the next launch from this launch's item costs.  ctl[0] = number of heavy
+// items (out), ctl[2..3] = 64-bit sum of costs (scratch).  Two tiny launches per frame.
+// ---------------------------------------------------------------------------
+#ifndef RT_HEAVY_FACTOR
+#define RT_HEAVY_FACTOR 3
+#endif
+__global__ void lpt_sum_kernel(const unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl) {
+    unsigned long long s = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) s += cost[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0 && s) atomicAdd(reinterpret_cast<unsigned long long*>(ctl + 2), s);
+}
+__global__ void lpt_mark_kernel(const unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl,
+                                unsigned* __restrict__ heavyList, unsigned char* __restrict__ heavyFlag) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long sum = *reinterpret_cast<const unsigned long long*>(ctl + 2);
+    const bool heavy = (unsigned long long)cost[i] * (unsigned long long)n > (unsigned long long)RT_HEAVY_FACTOR * sum;
+    heavyFlag[i] = heavy ? 1 : 0;
+    if (heavy) heavyList[atomicAdd(ctl, 1u)] = (unsigned)i;
 }
 
 // ---------------------------------------------------------------------------
