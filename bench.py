@@ -480,11 +480,16 @@ def main():
             pass
         peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
         alg = (consts["alg_bytes"] / world) if consts else None        # per launch: one rank's share of the frame
-        traffic = None
+        traffic, prof = None, {}
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("render_kernel_dram_bytes_per_launch")
+            prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            if world == 1 and (W, H, args.scene) == (3840, 2160, "car"):
+                traffic = prof.get("render_kernel_dram_bytes_per_launch")
         except (OSError, ValueError):
             pass
+        sm_clk = (clk or {}).get("sm_mhz") or 1965.0
+        issue_peak = 148 * 4 * sm_clk * 1e6                      # warp instructions / s: one per SM sub-partition per cycle
+        winst = prof.get("render_kernel_warp_instructions_per_launch") if traffic is not None else None
         achieved = alg / ren / 1e6 if alg else None
         line = {
             "metric": "Mrays/s (car scene)", "value": rays / tot / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
@@ -504,8 +509,14 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "rt::render_kernel", "kernel_ms": ren,
-                         "note": "algorithmic bytes of the reference's unculled traversal (oracle-counted) / render time; "
-                                 "the scene (~1 MB) is L1/L2-resident, DRAM sees the image write only"},
+                         "note": "algorithmic bytes of the REFERENCE's unculled traversal (oracle-counted) / render time; the scene "
+                                 "(~1 MB) is L1/L2-resident and our walk skips most of that traffic, so HBM is not the limiter and "
+                                 "frac can exceed 1: DRAM sees the image write only (traffic).  The binding resource is "
+                                 "instruction issue: see issue_roofline"},
+            "issue_roofline": {"bound": "warp-instruction issue (4 schedulers x 148 SMs x SM clock)",
+                               "warp_instructions_per_launch": winst, "source": "profiles/traffic.json (ncu smsp__inst_executed.sum)",
+                               "achieved_Ginst_s": (winst / ren / 1e6) if winst else None, "peak_Ginst_s": issue_peak / 1e9,
+                               "frac": (winst / (ren * 1e-3) / issue_peak) if winst else None},
             "extra": extra,
         }
         if world == 1 and not args.no_cpu_baseline:
