@@ -224,3 +224,52 @@ def test_subtrees_cut_the_work(rt, oracle, emu):
     assert np.array_equal(ia, ib) and np.array_equal(da.view(np.uint32), db.view(np.uint32))
     assert cb[1] < ca[1] / 3, (ca, cb)
     a.close(); b.close()
+
+
+def test_list_b_used_and_equivalent(rt, oracle, emu):
+    """List B (SAH tree over the reference leaves) is chosen on the car scene and changes no answer."""
+    rng = np.random.default_rng(21)
+    sc = rt.Scene("car", 800, 600)
+    cam = sc.camera["Position"][0].astype(np.float64)
+    o, d = make_rays(rng, sc.shapes, sc.nodes, cam, 8000)
+    a = Emu(emu, sc.shapes, sc.nodes, sc.indices, top=False)
+    b = Emu(emu, sc.shapes, sc.nodes, sc.indices, top=True)
+    assert a.info()["nodes_b"] == 0 and b.info()["nodes_b"] > 0
+    for mt in (False, True):
+        ia, da, _, ca = a.query(o, d, mt)
+        ib, db, _, cb = b.query(o, d, mt)
+        assert np.array_equal(ia, ib) and np.array_equal(da.view(np.uint32), db.view(np.uint32))
+        assert cb[0] < ca[0]
+    a.close(); b.close()
+
+
+def test_axis_parallel_and_degenerate_rays(rt, oracle, emu):
+    """Directions with exact zero components (1/d = inf: NaN slab arithmetic, GLSL select semantics) and
+    non-finite origins must take the reference tree (list A) and still match the oracle bit for bit."""
+    rng = np.random.default_rng(4)
+    for name in ("car", "monkey", "toy"):
+        sc = rt.Scene(name, 800, 600)
+        shapes, nodes, idx = sc.shapes, sc.nodes, sc.indices
+        e = Emu(emu, shapes, nodes, idx)
+        n = 6000
+        lo, hi = nodes["boundsMin"][-1].astype(np.float64), nodes["boundsMax"][-1].astype(np.float64)
+        lo, hi = np.where(np.isfinite(lo), lo, -50), np.where(np.isfinite(hi), hi, 50)
+        o = rng.uniform(lo - 5, hi + 5, (n, 3)).astype(np.float32)
+        # snap some origins onto box planes of random nodes: (bound - o) == 0 against 1/d == inf gives NaN
+        pick = rng.integers(0, len(nodes), n)
+        ax = rng.integers(0, 3, n)
+        snap = rng.uniform(0, 1, n) < 0.5
+        o[snap, ax[snap]] = nodes["boundsMin"][pick[snap], ax[snap]]
+        d = rng.normal(0, 1, (n, 3))
+        zero = rng.integers(0, 3, n)
+        d[np.arange(n), zero] = 0.0
+        two = rng.uniform(0, 1, n) < 0.3
+        d[two, (zero[two] + 1) % 3] = 0.0
+        d = normalize(d)
+        o[:5] = np.nan; o[5:10, 0] = np.inf
+        for mt in (False, True):
+            rid, rdist, _ = oracle.intersect_scene_batch(shapes, nodes, idx, o, d, mt)
+            gid, gdist, _, _ = e.query(o, d, mt)
+            assert np.array_equal(gid, rid), "%s mt=%s: %d ids differ" % (name, mt, int((gid != rid).sum()))
+            assert np.array_equal(gdist.view(np.uint32), rdist.view(np.uint32))
+        e.close()
