@@ -366,6 +366,9 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
 // world == 1 writes row-major W*H; world > 1 writes the compact tile-major shard.
 // ---------------------------------------------------------------------------
 #define RT_WARPS_PER_TILE ((RT_TILE_W / 8) * (RT_TILE_H / 4))
+#ifndef RT_HEAVY_SLOTS
+#define RT_HEAVY_SLOTS 24      // warp slots (of 32 resident) that claim heavy blocks first
+#endif
 
 template <bool MT, bool COUNT>
 __global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
@@ -378,18 +381,30 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
     // Heavy-first order: the critical path of a frame is its slowest 8x4 block (an incoherent bounce
     // packet walks hundreds of nodes in sequence); blocks that were slow in the previous frame are
     // claimed first so that their chains overlap the bulk of the work instead of forming the tail.
+    // The SM's warp schedulers favour the low warp slots (measured: slots 0-7 complete twice as many
+    // blocks as slots 28-31, tools/timeline.py), and a slow block on a starved slot runs three times
+    // longer — so only the favoured half of the slots claims from the heavy list while it lasts.
     const int nHeavy = P.lptCtl ? (int)__ldg(P.lptCtl) : 0;
+    unsigned warpSlot;
+    asm("mov.u32 %0, %%warpid;" : "=r"(warpSlot));
+    const bool favoured = warpSlot < RT_HEAVY_SLOTS;
+    bool heavyLeft = nHeavy > 0, lightLeft = true;
     for (int round = 0; P.itemsPerWarp == 0 || round < P.itemsPerWarp; ++round) {
-        int w = 0;
-        if (lane == 0) w = (int)atomicAdd(queue, 1u);
-        w = __shfl_sync(0xffffffffu, w, 0);
-        if (w < nHeavy) {
-            w = (int)__ldg(P.heavyList + w);
-        } else {
-            w -= nHeavy;
-            if (w >= nItems) break;
-            if (nHeavy > 0 && __ldg(P.heavyFlag + w)) continue;
+        int w = -1;
+        if (heavyLeft && (favoured || !lightLeft)) {
+            int hq = 0;
+            if (lane == 0) hq = (int)atomicAdd(P.lptCtl + 1, 1u);
+            hq = __shfl_sync(0xffffffffu, hq, 0);
+            if (hq < nHeavy) w = (int)__ldg(P.heavyList + hq); else heavyLeft = false;
         }
+        if (w < 0 && lightLeft) {
+            int lq = 0;
+            if (lane == 0) lq = (int)atomicAdd(queue, 1u);
+            lq = __shfl_sync(0xffffffffu, lq, 0);
+            if (lq >= nItems) lightLeft = false;
+            else if (!(nHeavy > 0 && __ldg(P.heavyFlag + lq))) w = lq;
+        }
+        if (w < 0) { if (!heavyLeft && !lightLeft) break; --round; continue; }
         const long long itemClk0 = P.itemCost ? clock64() : 0;
         const int t = P.tileBegin + w / RT_WARPS_PER_TILE, b = w % RT_WARPS_PER_TILE;
         const int tile = P.shardRank + t * P.shardWorld;
