@@ -232,6 +232,24 @@ def setup_fused(torch, dist, tr, rank, world):
     return box[0][1] if rank == 0 else None
 
 
+def setup_host_frame(dist, tr, rank, world, W, H):
+    """One W*H rgba32f frame in POSIX shared memory, mapped by every rank and pinned + mapped into each
+    rank's GPU (rt_host_frame_register): the render kernels store their tiles straight into it, every
+    GPU over its own PCIe link.  Returns (numpy view, device alias)."""
+    name = ["/dev/shm/rt_b200_frame_%d" % os.getpid() if rank == 0 else None]
+    if rank == 0:
+        arr = np.memmap(name[0], dtype=np.float32, mode="w+", shape=(H * W * 4,))
+        arr[:] = 0
+    if world > 1:
+        dist.broadcast_object_list(name, src=0)
+        if rank != 0:
+            arr = np.memmap(name[0], dtype=np.float32, mode="r+", shape=(H * W * 4,))
+        dist.barrier()
+    if rank == 0:
+        os.unlink(name[0])                      # the mappings keep the segment alive
+    return arr, tr.host_frame_register(arr)
+
+
 def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, flush, fused=False):
     """Device-timed frames with the scene resident.  Returns per-rank mean ms (total, render, gather)."""
     px = tr.shard_pixels()
@@ -275,12 +293,15 @@ def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, f
     return tot, ren, tot - ren, (full if full is not None else shard)
 
 
-def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup, frame_ptr=None, fused=False):
+def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup, frame_ptr=None, fused=False, host_alias=None):
     """End to end through the C ABI from HOST buffers: upload (pinned staging + H2D + repack), render,
-    (gather + untile), D2H of the rgba32f frame into pinned host memory.  Wall clock, sync both sides."""
+    (gather + untile), D2H of the rgba32f frame into pinned host memory.  Wall clock, sync both sides.
+    host_alias: the frame target is a mapped host frame (setup_host_frame), the kernels' own stores are the D2H."""
     light, cam, shapes, nodes, idx = sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices
     px = tr.shard_pixels()
-    if world == 1:
+    if host_alias is not None:
+        token = torch.zeros(1, dtype=torch.int32, device="cuda")
+    elif world == 1:
         host = torch.empty((H * W, 4), dtype=torch.float32, pin_memory=True).numpy()
     else:
         shard = torch.empty((px, 4), dtype=torch.float32, device="cuda")
@@ -290,7 +311,12 @@ def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup, 
 
     def frame():
         tr.upload_scene(light, cam, shapes, nodes, idx)
-        if world == 1:
+        if host_alias is not None:
+            tr.render_device(params)
+            if world > 1:
+                dist.all_reduce(token)
+            torch.cuda.synchronize()
+        elif world == 1:
             tr.render(params, want_ids=False, out=host)
         elif fused:
             tr.render_device(params)
@@ -445,12 +471,27 @@ def main():
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         tot, ren, gat = t.tolist()
-        e2e_ms, h2d, d2h = time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, max(3, args.steps // 3), 3,
-                                     frame_ptr=frame_ptr, fused=fused)
-        t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+        e2e_copy, h2d, d2h = time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, max(3, args.steps // 3), 3,
+                                      frame_ptr=frame_ptr, fused=fused)
+        # the same step with the frame target in mapped host memory: the kernels' own stores are the D2H
+        hostf, alias = setup_host_frame(dist, tr, rank, world, W, H)
+        tr.set_frame_target(alias)
+        e2e_host, _, _ = time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, max(3, args.steps // 3), 3, host_alias=alias)
+        host_ok = None
+        if rank == 0:                           # the host frame must equal a single-GPU rt_render bit for bit
+            solo = rt.RayTracer(W, H, device=local, flags=0)
+            solo.upload(sc)
+            want, _ = solo.render(params, want_ids=False)
+            solo.close()
+            host_ok = bool(np.array_equal(np.asarray(hostf).view(np.uint32).reshape(-1), want.view(np.uint32).reshape(-1)))
+        tr.set_frame_target(None)
+        tr.host_frame_unregister(hostf)
+        t = torch.tensor([e2e_copy, e2e_host], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = t.item()
+        e2e_copy, e2e_host = t.tolist()
+        e2e_ms = min(e2e_copy, e2e_host)
+        e2e_path = "host_frame" if e2e_host <= e2e_copy else "device_frame_copy"
 
         extra = {}
         if world == 1 and not args.no_extra and (W, H) != (800, 600):
@@ -503,7 +544,10 @@ def main():
                             "reference_node_visits": consts["node_visits"] if consts else None,
                             "reference_prim_tests": sum(consts["tests"]) if consts else None},
             "e2e": {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms},
+                    "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms, "path": e2e_path,
+                    "paths_ms": {"host_frame: kernels store into mapped (shared) host memory, every GPU over its own PCIe link": e2e_host,
+                                 "device_frame_copy: render (+ gather) on the device, D2H copy of the frame from rank 0": e2e_copy},
+                    "host_frame_equals_single_gpu": host_ok},
             "gpu_launches": int(launches),
             "clocks": clk,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -155,7 +155,7 @@ int rt_item_stats(rt_ctx* ctx, uint64_t out[3]);
  * by tile).  Rank 0 calls rt_frame_export (allocates the frame, returns a 64-byte CUDA IPC
  * handle to ship to the other processes and the frame's device pointer); the others call
  * rt_frame_open.  A single-process driver can hand any device pointer to rt_set_frame_target
- * (NULL switches the mode off).  While a frame target is set and world > 1,
+ * (NULL switches the mode off).  While a frame target is set,
  * rt_render_device(ctx, params, NULL, NULL) writes there; the frame is complete once every rank
  * has synchronised (a barrier is the only collective left). */
 int rt_set_frame_target(rt_ctx* ctx, float* dev_frame);
@@ -163,6 +163,14 @@ int rt_frame_export(rt_ctx* ctx, unsigned char handle[64], float** dev_frame);
 int rt_frame_open(rt_ctx* ctx, const unsigned char handle[64]);
 /* Rank 0: asynchronous copy of the exported frame to the host (ordered on rt_stream). */
 int rt_frame_download(rt_ctx* ctx, float* host_rgba);
+/* Host frame: pin and map a caller-owned host buffer of W*H float4 (for several ranks: one POSIX
+ * shared-memory segment that every process maps) and return its device alias.  Passed to
+ * rt_set_frame_target, the render kernel stores its pixels straight into host memory over this
+ * GPU's own PCIe link while it renders: no device frame, no gather and no separate D2H copy, and
+ * with N ranks the N links carry the frame in parallel.  The pixels are visible to the host after
+ * rt_synchronize (all ranks).  rt_host_frame_unregister undoes the pinning. */
+int rt_host_frame_register(rt_ctx* ctx, void* host_frame, size_t bytes, float** dev_alias);
+int rt_host_frame_unregister(rt_ctx* ctx, void* host_frame);
 
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in
  * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one

@@ -56,7 +56,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -91,6 +91,8 @@ def lib():
     L.rt_frame_export.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; L.rt_frame_export.restype = ip
     L.rt_frame_open.argtypes = [vp, C.c_char_p]; L.rt_frame_open.restype = ip
     L.rt_frame_download.argtypes = [vp, vp]; L.rt_frame_download.restype = ip
+    L.rt_host_frame_register.argtypes = [vp, vp, C.c_size_t, C.POINTER(vp)]; L.rt_host_frame_register.restype = ip
+    L.rt_host_frame_unregister.argtypes = [vp, vp]; L.rt_host_frame_unregister.restype = ip
     L.rt_item_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_item_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
@@ -311,6 +313,15 @@ class RayTracer:
 
     def frame_download(self, host):
         self._chk(self._L.rt_frame_download(self._c, _ptr(host)))
+
+    def host_frame_register(self, host):
+        """host: a C-contiguous numpy float32 array of W*H*4 (may live in shared memory); returns the device alias."""
+        d = C.c_void_p()
+        self._chk(self._L.rt_host_frame_register(self._c, _ptr(host), host.nbytes, C.byref(d)))
+        return d.value
+
+    def host_frame_unregister(self, host):
+        self._chk(self._L.rt_host_frame_unregister(self._c, _ptr(host)))
 
     def item_stats(self):
         out = (C.c_uint64 * 3)()

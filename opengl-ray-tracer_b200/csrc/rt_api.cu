@@ -3,6 +3,7 @@
 // (program, 5 SSBOs, output texture; src/main.cpp:182-275).  No CPU fallback.
 #include "rt_kernels.cuh"
 #include "rt_layout.h"
+#include "rt_refit.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -84,7 +85,13 @@ struct rt_ctx {
     DevBuf<float4> dNodesB;
     int nDfsB = 0;
     PinBuf<float4> hSubBox; DevBuf<float4> dSubBox;   // 2 float4 per sub-tree node (host-computed conservative boxes)
-    rtl::Layout layout;               // host copy of the threaded layout (refit of the sub-tree boxes)
+    rtl::Layout layout;               // host copy of the threaded layout
+    // refit graph of the boxes that are ours (rt_refit.cuh), uploaded with the layout
+    PinBuf<int> hRf; DevBuf<int> dRf;           // [child 2nE | leaf 2nE | parent nE | start nStart]
+    DevBuf<unsigned> dRfArrived;                // nE counters + 1 "degraded" flag
+    int nRfStart = 0;
+    int* hRfDegraded = nullptr;                 // pinned: lazily read back flag of the last refit
+    cudaEvent_t rfDone = nullptr; bool rfPending = false;
     int nSub = 0;
     bool subDirty = false;            // sub-tree boxes must be recomputed (shapes moved / omax grew)
     float omax = 0.f;
@@ -192,6 +199,15 @@ int build_visit_order(rt_ctx* c) {
         std::memcpy(c->hPrank.p, L.prank.data(), (size_t)prims * sizeof(int));
     }
     stage_subboxes(c);
+    rtl::build_refit_graph(L);
+    c->nRfStart = (int)L.rfStart.size();
+    CU(c, c->hRf.reserve((size_t)c->nSub * 5 + (size_t)c->nRfStart, 0));
+    if (c->nSub > 0) {
+        std::memcpy(c->hRf.p, L.rfChild.data(), (size_t)c->nSub * 2 * sizeof(int));
+        std::memcpy(c->hRf.p + 2 * (size_t)c->nSub, L.rfLeaf.data(), (size_t)c->nSub * 2 * sizeof(int));
+        std::memcpy(c->hRf.p + 4 * (size_t)c->nSub, L.rfParent.data(), (size_t)c->nSub * sizeof(int));
+        if (c->nRfStart > 0) std::memcpy(c->hRf.p + 5 * (size_t)c->nSub, L.rfStart.data(), (size_t)c->nRfStart * sizeof(int));
+    }
     c->nDfs = m; c->nPrims = prims;
     c->subDirty = false;
     return RT_OK;
@@ -199,6 +215,11 @@ int build_visit_order(rt_ctx* c) {
 
 // Bring the device scene up to date: coalesced H2D of whatever changed, then K2.
 int flush_scene(rt_ctx* c) {
+    // a refit on the device of an earlier frame met a primitive it could not bound any more: rebuild the layout
+    if (c->rfPending && cudaEventQuery(c->rfDone) == cudaSuccess) {
+        c->rfPending = false;
+        if (*c->hRfDegraded) { *c->hRfDegraded = 0; c->topoDirty = true; }
+    }
     // the camera may have left the region the sub-tree margins were computed for
     if (c->nSub > 0 && !c->topoDirty && c->haveCam) {
         double m = 0;
@@ -219,20 +240,16 @@ int flush_scene(rt_ctx* c) {
         CU(c, c->dNodes.reserve((size_t)c->nNodes));
         CU(c, cudaMemcpyAsync(c->dNodes.p, c->hNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyHostToDevice, c->stream));
     }
-    bool subUpload = false;
+    bool subUpload = false, devRefit = false;
     if (c->nodesDirty && !c->topoDirty && c->nDfsB > 0) {
         // reference boxes changed under an unchanged topology (grow-only refit): B's union boxes follow;
         // if the reference tree stopped being nested, B is no longer equivalent and is switched off
-        wait_copies(c);
-        if (rtl::ref_tree_nested(c->hNodes.p, c->nNodes)) { rtl::refit_top(c->layout, c->hNodes.p); stage_subboxes(c); subUpload = true; }
+        if (rtl::ref_tree_nested(c->hNodes.p, c->nNodes)) devRefit = true;
         else { c->nDfsB = 0; c->layout.useB = false; }
     }
     if (c->subDirty && !c->topoDirty) {
-        // shapes moved under a sub-tree (or omax grew): refit its boxes on the host; a primitive that
-        // stopped being boundable forces a rebuild of the layout
-        wait_copies(c);
-        if (rtl::refit_subboxes(c->layout, c->hShapes.p, (double)c->omax)) { stage_subboxes(c); subUpload = true; }
-        else c->topoDirty = true;
+        // shapes moved under a sub-tree (or omax grew): its boxes are refitted on the device (K4)
+        devRefit = true;
         c->subDirty = false;
     }
     if (c->topoDirty) {
@@ -259,7 +276,12 @@ int flush_scene(rt_ctx* c) {
             CU(c, cudaMemcpyAsync(c->dPshape.p, c->hPshape.p, (size_t)c->nPrims * sizeof(int), cudaMemcpyHostToDevice, c->stream));
             CU(c, cudaMemcpyAsync(c->dPrank.p, c->hPrank.p, (size_t)c->nPrims * sizeof(int), cudaMemcpyHostToDevice, c->stream));
         }
-        subUpload = true;
+        if (c->nSub > 0) {
+            CU(c, c->dRf.reserve((size_t)c->nSub * 5 + (size_t)c->nRfStart));
+            CU(c, c->dRfArrived.reserve((size_t)c->nSub + 1));
+            CU(c, cudaMemcpyAsync(c->dRf.p, c->hRf.p, ((size_t)c->nSub * 5 + (size_t)c->nRfStart) * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        }
+        subUpload = true; devRefit = false;       // the layout build computed every box on the host
     }
     if (subUpload && c->nSub > 0) {
         CU(c, c->dSubBox.reserve((size_t)c->nSub * 2));
@@ -268,6 +290,20 @@ int flush_scene(rt_ctx* c) {
     cudaEventRecord(c->ev[1], c->stream); c->timed[0] = true;
     cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
     cudaEventRecord(c->ev[2], c->stream);
+    if (devRefit && c->nSub > 0 && c->nRfStart > 0) {
+        const int nE = c->nSub;
+        CU(c, cudaMemsetAsync(c->dRfArrived.p, 0, ((size_t)nE + 1) * sizeof(unsigned), c->stream));
+        refit_kernel<<<(c->nRfStart + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dNodes.p, c->dPshape.p,
+            c->dRf.p + 5 * (size_t)nE, c->nRfStart, c->dRf.p + 4 * (size_t)nE, reinterpret_cast<const int2*>(c->dRf.p),
+            reinterpret_cast<const int2*>(c->dRf.p + 2 * (size_t)nE), c->dRfArrived.p, c->dSubBox.p, (double)c->omax,
+            reinterpret_cast<int*>(c->dRfArrived.p + nE));
+        c->launches++;
+        if (!c->rfPending) {
+            CU(c, cudaMemcpyAsync(c->hRfDegraded, c->dRfArrived.p + nE, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+            cudaEventRecord(c->rfDone, c->stream); c->rfPending = true;
+        }
+        subUpload = true;                          // the node lists take the new boxes below
+    }
     if ((c->nodesDirty || c->topoDirty || subUpload) && c->nDfs > 0) {
         repack_nodes_kernel<<<(c->nDfs + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dSubBox.p, c->dOrder.p, c->dLinkCnt.p, c->dNodesT.p, c->nDfs);
         c->launches++;
@@ -326,6 +362,9 @@ int rt_create(rt_ctx** out, int width, int height, int device, unsigned flags) {
         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return RT_ERR_CUDA; }
     for (auto& e : c->ev) if (cudaEventCreate(&e) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     if (cudaEventCreateWithFlags(&c->copyDone, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+    if (cudaEventCreateWithFlags(&c->rfDone, cudaEventDisableTiming) != cudaSuccess ||
+        cudaMallocHost(&c->hRfDegraded, sizeof(int)) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+    *c->hRfDegraded = 0;
     cudaDeviceGetAttribute(&c->smCount, cudaDevAttrMultiProcessorCount, device);
     c->ownStream = c->stream;
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
@@ -351,6 +390,9 @@ void rt_destroy(rt_ctx* c) {
     c->image.release(); c->ids.release(); c->tally.release(); c->queue.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->copyDone) cudaEventDestroy(c->copyDone);
+    if (c->rfDone) cudaEventDestroy(c->rfDone);
+    if (c->hRfDegraded) cudaFreeHost(c->hRfDegraded);
+    c->hRf.release(); c->dRf.release(); c->dRfArrived.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
@@ -477,7 +519,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     if (rc != RT_OK) return rc;
     const int64_t px = out_pixels(c);
     // fused gather: no explicit output buffer, a frame target set, several ranks
-    const bool useFrame = !dev_rgba && !host_rgba && !count && c->frameTarget && c->shardWorld > 1;
+    const bool useFrame = !dev_rgba && !host_rgba && !count && c->frameTarget;
     if (!dev_rgba && !useFrame) { CU(c, c->image.reserve((size_t)px)); dev_rgba = reinterpret_cast<float*>(c->image.p); }
     const bool wantIds = (c->flags & RT_FLAG_HIT_IDS) != 0;
     if (wantIds && !dev_ids) { CU(c, c->ids.reserve((size_t)px)); dev_ids = c->ids.p; }
@@ -652,6 +694,26 @@ int rt_frame_download(rt_ctx* c, float* host_rgba) {
     if (!c->frame.p) return fail(c, RT_ERR_STATE, "no exported frame on this context");
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaMemcpyAsync(host_rgba, c->frame.p, (size_t)c->W * (size_t)c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    return RT_OK;
+}
+
+int rt_host_frame_register(rt_ctx* c, void* host_frame, size_t bytes, float** dev_alias) {
+    if (!c || !host_frame || !dev_alias) return RT_ERR_ARG;
+    if (bytes < (size_t)c->W * (size_t)c->H * sizeof(float4)) return fail(c, RT_ERR_ARG, "host frame smaller than W*H float4");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaHostRegister(host_frame, bytes, cudaHostRegisterMapped | cudaHostRegisterPortable));
+    void* d = nullptr;
+    cudaError_t e = cudaHostGetDevicePointer(&d, host_frame, 0);
+    if (e != cudaSuccess) { cudaHostUnregister(host_frame); CU(c, e); }
+    *dev_alias = static_cast<float*>(d);
+    return RT_OK;
+}
+
+int rt_host_frame_unregister(rt_ctx* c, void* host_frame) {
+    if (!c || !host_frame) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    CU(c, cudaHostUnregister(host_frame));
     return RT_OK;
 }
 

@@ -1,4 +1,6 @@
-// rt_layout.h — host-side builder of the device scene layout (pure C++17, no CUDA).
+// rt_layout.h — host-side builder of the device scene layout (C++17; no CUDA needed: the test
+// emulator compiles it with g++.  Box / prim_bound are also compiled for the device, where the
+// refit kernel (rt_kernels.cuh: refit_kernel) recomputes the conservative boxes after shapes moved).
 //
 // Input: the reference's raw FlatNode[] / bvhIndices[] / FlatShape[] (src/flatStructures.hpp).
 // Output: the threaded node list the render kernel walks:
@@ -24,7 +26,29 @@
 
 #include "../../include/rt_flat.h"
 
+#if defined(__CUDACC__)
+#define RTL_HD __host__ __device__
+#else
+#define RTL_HD
+#endif
+
 namespace rtl {
+
+// math that must compile for host and device alike
+RTL_HD inline double dmin(double a, double b) { return a < b ? a : b; }
+RTL_HD inline double dmax(double a, double b) { return a > b ? a : b; }
+RTL_HD inline double dabs(double a) { return a < 0 ? -a : a; }
+RTL_HD inline float  fmin_(float a, float b) { return b < a ? b : a; }      // std::min semantics (keeps a on NaN b)
+RTL_HD inline float  fmax_(float a, float b) { return a < b ? b : a; }
+RTL_HD inline bool   fin(double x) { return dabs(x) <= 1.7976931348623157e308; }   // false for NaN and +-inf
+RTL_HD inline float  f_up(float x) {        // nextafter(x, +inf) for finite x
+    if (!(x < INFINITY)) return x;             // +inf, NaN
+    if (x == 0.f) return 1.401298464e-45f;
+    union { float f; uint32_t u; } v; v.f = x;
+    v.u = x > 0.f ? v.u + 1u : v.u - 1u;
+    return v.f;
+}
+RTL_HD inline float  f_down(float x) { return -f_up(-x); }
 
 #define RT_FAT_LEAF      8      // reference leaves with more shapes than this get a sub-tree
 #define RT_SUB_LEAF      4      // sub-tree leaves hold at most this many primitives
@@ -37,9 +61,10 @@ enum { KIND_MIXED = 0, KIND_TRIANGLES = 1, KIND_SPHERES = 2 };
 
 struct Box {
     float mn[3], mx[3];
-    void reset() { for (int a = 0; a < 3; ++a) { mn[a] = INFINITY; mx[a] = -INFINITY; } }
-    void grow(const Box& b) { for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], b.mn[a]); mx[a] = std::max(mx[a], b.mx[a]); } }
-    void grow(const double p[3]) { for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], (float)p[a]); mx[a] = std::max(mx[a], (float)p[a]); } }
+    RTL_HD void reset() { for (int a = 0; a < 3; ++a) { mn[a] = INFINITY; mx[a] = -INFINITY; } }
+    RTL_HD void grow(const Box& b) { for (int a = 0; a < 3; ++a) { mn[a] = fmin_(mn[a], b.mn[a]); mx[a] = fmax_(mx[a], b.mx[a]); } }
+    RTL_HD void grow(const double p[3]) { for (int a = 0; a < 3; ++a) { mn[a] = fmin_(mn[a], (float)p[a]); mx[a] = fmax_(mx[a], (float)p[a]); } }
+    RTL_HD void everything() { for (int a = 0; a < 3; ++a) { mn[a] = -INFINITY; mx[a] = INFINITY; } }   // a box every finite ray passes
     double area() const {
         double d[3] = {(double)mx[0] - mn[0], (double)mx[1] - mn[1], (double)mx[2] - mn[2]};
         return d[0] < 0 ? 0.0 : 2.0 * (d[0] * d[1] + d[1] * d[2] + d[2] * d[0]);
@@ -58,26 +83,26 @@ struct Box {
 // generous safety factors.  Rays with a larger origin ignore the sub-tree boxes in the kernel.
 // Returns false = unbounded (primitive goes to the always-tested leaf).
 // ---------------------------------------------------------------------------
-inline bool finite3(const float* p) { return std::isfinite(p[0]) && std::isfinite(p[1]) && std::isfinite(p[2]); }
-inline double amax3(const float* p) { return std::max(std::fabs((double)p[0]), std::max(std::fabs((double)p[1]), std::fabs((double)p[2]))); }
+RTL_HD inline bool finite3(const float* p) { return fin(p[0]) && fin(p[1]) && fin(p[2]); }
+RTL_HD inline double amax3(const float* p) { return dmax(dabs((double)p[0]), dmax(dabs((double)p[1]), dabs((double)p[2]))); }
 
-inline void inflate(Box& b, double m) {
+RTL_HD inline void inflate(Box& b, double m) {
     for (int a = 0; a < 3; ++a) {
-        // outward rounding of the double arithmetic to float
-        b.mn[a] = std::nextafter((float)((double)b.mn[a] - m), -INFINITY);
-        b.mx[a] = std::nextafter((float)((double)b.mx[a] + m), INFINITY);
+        // outward rounding of the double arithmetic to float (callers guarantee finite values below 1e30)
+        b.mn[a] = f_down((float)((double)b.mn[a] - m));
+        b.mx[a] = f_up((float)((double)b.mx[a] + m));
     }
 }
 
-inline bool prim_bound(const rt_flat_shape& s, double omax, Box& out) {
+RTL_HD inline bool prim_bound(const rt_flat_shape& s, double omax, Box& out) {
     const double E = 1.1920929e-7;
     out.reset();
     if (s.type == RT_SHAPE_SPHERE) {
-        if (!finite3(s.sphereCenter) || !std::isfinite(s.sphereRadius)) return false;
-        const double S = omax + amax3(s.sphereCenter) + std::fabs((double)s.sphereRadius);
-        const double r = std::fabs((double)s.sphereRadius);
+        if (!finite3(s.sphereCenter) || !fin(s.sphereRadius)) return false;
+        const double S = omax + amax3(s.sphereCenter) + dabs((double)s.sphereRadius);
+        const double r = dabs((double)s.sphereRadius);
         // D > 0 can be decided wrongly while p^2 < r^2 + c E |o-c|^2 (p = distance line-centre)
-        const double reach = std::sqrt(r * r + 64.0 * E * S * S) + 64.0 * E * S;
+        const double reach = ::sqrt(r * r + 64.0 * E * S * S) + 64.0 * E * S;
         if (!(reach < 1e30)) return false;
         double c[3] = {s.sphereCenter[0], s.sphereCenter[1], s.sphereCenter[2]};
         out.grow(c);
@@ -86,29 +111,29 @@ inline bool prim_bound(const rt_flat_shape& s, double omax, Box& out) {
     }
     if (s.type == RT_SHAPE_WALL) {
         const float* n = s.planeNormal;
-        if (!finite3(n) || !finite3(s.wallStart) || !std::isfinite(s.planeD) || !std::isfinite(s.wallWidth) || !std::isfinite(s.wallHeight)) return false;
+        if (!finite3(n) || !finite3(s.wallStart) || !fin(s.planeD) || !fin(s.wallWidth) || !fin(s.wallHeight)) return false;
         const double nn = (double)n[0] * n[0] + (double)n[1] * n[1] + (double)n[2] * n[2];
         if (!(nn > 1e-12) || !(nn < 1e12)) return false;
         // the shader's tangent basis (gpu_shader.comp:305-307), here in double; a degenerate first
         // cross product gives NaN in fp32 (the wall then accepts its whole plane)
         double u[3] = {-(double)n[2], 0.0, (double)n[0]};                 // n x (0,1,0)
-        double ul = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
-        if (!(ul > 1e-3 * std::sqrt(nn))) return false;                    // near the NaN / fallback switch: do not bound
+        double ul = ::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+        if (!(ul > 1e-3 * ::sqrt(nn))) return false;                    // near the NaN / fallback switch: do not bound
         for (double& x : u) x /= ul;
         double v[3] = {n[1] * u[2] - u[1] * n[2], n[2] * u[0] - u[2] * n[0], n[0] * u[1] - u[0] * n[1]};
-        double vl = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        double vl = ::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
         if (!(vl > 0)) return false;
         for (double& x : v) x /= vl;
         const double w = s.wallWidth, h = s.wallHeight;
         if (w < 0 || h < 0) { /* empty acceptance set; still bound it by the corner */ }
-        const double S = omax + amax3(s.wallStart) + std::fabs(w) + std::fabs(h);
+        const double S = omax + amax3(s.wallStart) + dabs(w) + dabs(h);
         for (int i = 0; i < 4; ++i) {
-            double a = (i & 1) ? std::max(w, 0.0) : 0.0, b = (i & 2) ? std::max(h, 0.0) : 0.0, c[3];
+            double a = (i & 1) ? dmax(w, 0.0) : 0.0, b = (i & 2) ? dmax(h, 0.0) : 0.0, c[3];
             for (int k = 0; k < 3; ++k) c[k] = s.wallStart[k] + a * u[k] + b * v[k];
             // hit points lie on the stored plane (n, D): project the corner onto it along n
             const double off = ((double)n[0] * c[0] + (double)n[1] * c[1] + (double)n[2] * c[2] + (double)s.planeD) / nn;
             for (int k = 0; k < 3; ++k) c[k] -= off * n[k];
-            if (!std::isfinite(c[0]) || !std::isfinite(c[1]) || !std::isfinite(c[2])) return false;
+            if (!fin(c[0]) || !fin(c[1]) || !fin(c[2])) return false;
             out.grow(c);
         }
         const double m = 128.0 * E * (S + amax3(out.mn) + amax3(out.mx));
@@ -118,7 +143,7 @@ inline bool prim_bound(const rt_flat_shape& s, double omax, Box& out) {
     }
     if (s.type == RT_SHAPE_TRIANGLE) {
         const float* n = s.planeNormal;
-        if (!finite3(n) || !finite3(s.triP1) || !finite3(s.triP2) || !finite3(s.triP3) || !std::isfinite(s.planeD)) return false;
+        if (!finite3(n) || !finite3(s.triP1) || !finite3(s.triP2) || !finite3(s.triP3) || !fin(s.planeD)) return false;
         double P[3][3], e1[3], e2[3];
         for (int k = 0; k < 3; ++k) { P[0][k] = s.triP1[k]; P[1][k] = s.triP2[k]; P[2][k] = s.triP3[k]; e1[k] = P[1][k] - P[0][k]; e2[k] = P[2][k] - P[0][k]; }
         const double d00 = e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2], d11 = e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2];
@@ -127,21 +152,21 @@ inline bool prim_bound(const rt_flat_shape& s, double omax, Box& out) {
         if (!(d00 > 0) || !(d11 > 0)) return false;
         const double sin2 = denom / (d00 * d11);
         if (!(sin2 > 1e-4)) return false;                                  // sliver / degenerate: hits everywhere on its plane
-        const double l1 = std::sqrt(d00), l2 = std::sqrt(d11);
-        if (std::max(l1, l2) > 1e4 * std::min(l1, l2)) return false;
+        const double l1 = ::sqrt(d00), l2 = ::sqrt(d11);
+        if (dmax(l1, l2) > 1e4 * dmin(l1, l2)) return false;
         double nt[3] = {e1[1] * e2[2] - e2[1] * e1[2], e1[2] * e2[0] - e2[2] * e1[0], e1[0] * e2[1] - e2[0] * e1[1]};
-        const double ntl = std::sqrt(nt[0] * nt[0] + nt[1] * nt[1] + nt[2] * nt[2]);
+        const double ntl = ::sqrt(nt[0] * nt[0] + nt[1] * nt[1] + nt[2] * nt[2]);
         const double nn = (double)n[0] * n[0] + (double)n[1] * n[1] + (double)n[2] * n[2];
         if (!(nn > 1e-12) || !(nn < 1e12)) return false;
-        const double cosv = ((double)n[0] * nt[0] + (double)n[1] * nt[1] + (double)n[2] * nt[2]) / (ntl * std::sqrt(nn));
+        const double cosv = ((double)n[0] * nt[0] + (double)n[1] * nt[1] + (double)n[2] * nt[2]) / (ntl * ::sqrt(nn));
         // Barycentric mode accepts points of the STORED plane (n, D) whose projection along the
         // triangle normal falls into the triangle; animated triangles carry a stale plane
         // (src/main.cpp:1101-1106), so the region is the triangle projected onto (n, D) along nt.
-        if (!(std::fabs(cosv) > 0.05)) return false;
+        if (!(dabs(cosv) > 0.05)) return false;
         const double S = omax + amax3(s.triP1) + amax3(s.triP2) + amax3(s.triP3);
         // barycentric fuzz (relative to the triangle, independent of the ray origin: the origin-dependent
         // error of the hit point itself is the absolute margin m below): accepted while u,v,w >= -delta  ==  triangle scaled by (1+3 delta) about its centroid
-        const double delta = 64.0 * E * (1.0 + (l1 + l2) / std::min(l1, l2)) / sin2;
+        const double delta = 64.0 * E * (1.0 + (l1 + l2) / dmin(l1, l2)) / sin2;
         if (!(delta < 0.5)) return false;
         double cen[3];
         for (int k = 0; k < 3; ++k) cen[k] = (P[0][k] + P[1][k] + P[2][k]) / 3.0;
@@ -152,10 +177,10 @@ inline bool prim_bound(const rt_flat_shape& s, double omax, Box& out) {
             out.grow(q);                                                   // Moller-Trumbore mode: the triangle itself
             const double off = ((double)n[0] * q[0] + (double)n[1] * q[1] + (double)n[2] * q[2] + (double)s.planeD) / nd;
             for (int k = 0; k < 3; ++k) q[k] -= off * nt[k];
-            if (!std::isfinite(q[0]) || !std::isfinite(q[1]) || !std::isfinite(q[2])) return false;
+            if (!fin(q[0]) || !fin(q[1]) || !fin(q[2])) return false;
             out.grow(q);                                                   // Barycentric mode: its image on the stored plane
         }
-        const double m = 128.0 * E * (S + amax3(out.mn) + amax3(out.mx)) / std::sqrt(sin2) / std::fabs(cosv);
+        const double m = 128.0 * E * (S + amax3(out.mn) + amax3(out.mx)) / ::sqrt(sin2) / dabs(cosv);
         if (!(m < 1e30)) return false;
         inflate(out, m);
         return true;
@@ -259,6 +284,11 @@ struct Layout {
     int nSubA = 0;               // sub boxes [0, nSubA) belong to the fat-leaf sub-trees, the rest to B's top nodes
     double costA = 0, costB = 0; // SAH estimates (expected box tests per random ray) of the two node lists
     bool useB = false;
+    // refit graph (build_refit_graph): what the device needs to recompute every box of subBox bottom-up
+    std::vector<int> rfParent;   // per subBox entry: the entry whose box is the union containing it, -1 = none
+    std::vector<int> rfChild;    // 2 per entry: >= 0 = entry, < 0 = raw reference node -1-x; unused for sub-tree leaves
+    std::vector<int> rfLeaf;     // 2 per entry: first primitive slot, count (count 0 = inner node)
+    std::vector<int> rfStart;    // work items: >= 0 = sub-tree leaf entry; < 0 = a raw child arriving at entry -1-x
     const char* error = nullptr;
 
     int nodes() const { return (int)src.size(); }
@@ -527,6 +557,36 @@ inline void build_top(Layout& L, const rt_flat_node* nd, int nNodes) {
     refit_top(L, nd);
     L.useB = L.costB < 0.9 * L.costA;
     if (!L.useB) { L.srcB.clear(); L.linkB.clear(); L.cwB.clear(); L.topPos.clear(); L.subBox.resize((size_t)L.nSubA); }
+}
+
+// The dependency graph of the boxes in subBox, for the device refit (rt_kernels.cuh: refit_kernel):
+// a sub-tree leaf's box is the union of its primitives' bounds, every other entry the union of its
+// two children (entries, or raw reference nodes under B's top nodes).  Call after build_layout / build_top.
+inline void build_refit_graph(Layout& L) {
+    const int nE = (int)L.subBox.size();
+    L.rfParent.assign((size_t)nE, -1); L.rfChild.assign((size_t)nE * 2, 0); L.rfLeaf.assign((size_t)nE * 2, 0); L.rfStart.clear();
+    for (int j = 0; j < L.nSubA; ++j) {
+        const int k = L.subPos[(size_t)j];
+        if (L.cw[(size_t)k] >= 0) {
+            L.rfLeaf[2 * (size_t)j] = L.link[(size_t)k]; L.rfLeaf[2 * (size_t)j + 1] = L.cw[(size_t)k] & RTL_COUNT_MASK;
+            L.rfStart.push_back(j);
+        } else {
+            const int c1 = k + 1, c2 = L.cw[(size_t)c1] < 0 ? L.link[(size_t)c1] : c1 + 1;
+            const int e1 = -1 - L.src[(size_t)c1], e2 = -1 - L.src[(size_t)c2];
+            L.rfChild[2 * (size_t)j] = e1; L.rfChild[2 * (size_t)j + 1] = e2;
+            L.rfParent[(size_t)e1] = j; L.rfParent[(size_t)e2] = j;
+        }
+    }
+    for (int t = 0; t < (int)L.topPos.size(); ++t) {
+        const int j = L.nSubA + t, k = L.topPos[(size_t)t];
+        const int c1 = k + 1, c2 = L.cwB[(size_t)c1] < 0 ? L.linkB[(size_t)c1] : c1 + 1;
+        const int cs[2] = {c1, c2};
+        for (int i = 0; i < 2; ++i) {
+            const int s = L.srcB[(size_t)cs[i]];
+            if (s >= 0) { L.rfChild[2 * (size_t)j + i] = -1 - s; L.rfStart.push_back(-1 - j); }
+            else        { L.rfChild[2 * (size_t)j + i] = -1 - s; L.rfParent[(size_t)(-1 - s)] = j; }
+        }
+    }
 }
 
 }  // namespace rtl

@@ -123,6 +123,45 @@ int emu_refit(void* e, const rt_flat_shape* shapes, const rt_flat_node* nodes) {
     return 1;
 }
 
+// The refit graph (rtl::build_refit_graph, executed by the device's refit_kernel) replayed sequentially with
+// the kernel's arrival rule: returns the number of subBox entries whose box differs from the host refit
+// (rtl::refit_subboxes / refit_top), or -1 if some entry never got computed.
+int emu_refit_graph_check(void* e, const rt_flat_shape* shapes, const rt_flat_node* nodes) {
+    Emu* E = static_cast<Emu*>(e);
+    rtl::Layout& L = E->L;
+    rtl::build_refit_graph(L);
+    const int nE = (int)L.subBox.size();
+    std::vector<rtl::Box> box((size_t)nE);
+    std::vector<int> arrived((size_t)nE, 0), done((size_t)nE, 0);
+    auto childBox = [&](int ref) { return ref >= 0 ? box[(size_t)ref] : rtl::raw_box(nodes[-1 - ref]); };
+    for (int st : L.rfStart) {
+        int j = st;
+        if (j >= 0) {
+            rtl::Box b; b.reset();
+            for (int q = 0; q < L.rfLeaf[2 * (size_t)j + 1]; ++q) {
+                rtl::Box pb;
+                if (!rtl::prim_bound(shapes[L.pshape[(size_t)(L.rfLeaf[2 * (size_t)j] + q)]], L.omax, pb)) pb.everything();
+                b.grow(pb);
+            }
+            box[(size_t)j] = b; done[(size_t)j] = 1;
+            j = L.rfParent[(size_t)j];
+        } else j = -1 - j;
+        while (j >= 0) {
+            if (arrived[(size_t)j]++ == 0) break;
+            rtl::Box b; b.reset();
+            b.grow(childBox(L.rfChild[2 * (size_t)j])); b.grow(childBox(L.rfChild[2 * (size_t)j + 1]));
+            box[(size_t)j] = b; done[(size_t)j] = 1;
+            j = L.rfParent[(size_t)j];
+        }
+    }
+    int bad = 0;
+    for (int j = 0; j < nE; ++j) {
+        if (!done[(size_t)j]) return -1;
+        if (std::memcmp(&box[(size_t)j], &L.subBox[(size_t)j], sizeof(rtl::Box)) != 0) bad++;
+    }
+    return bad;
+}
+
 // n rays; anyMode: bounds[i] is the any-hit limit.  counters: [0] nodes visited [1] primitive tests.
 void emu_query(void* e, int n, const float* origins, const float* dirs, int mt, int anyMode, const float* bounds,
                int* outShape, float* outDist, float* outPoint, uint64_t counters[2]) {

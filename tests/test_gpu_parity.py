@@ -225,6 +225,50 @@ def test_animated_car_refit(rt, oracle):
     tr.close()
 
 
+def test_device_refit_keeps_the_boxes_tight(rt):
+    """K4 (refit_kernel): after rt_update_shapes + rt_update_nodes the boxes refitted ON THE DEVICE give the same image
+    as a context that got the moved scene as a fresh upload (boxes built on the host), with the same amount of
+    work: no box degenerated to the all-covering fallback; a shape that stops being boundable (a triangle squashed
+    to a sliver) still renders exactly and the layout is rebuilt at the next upload."""
+    W, H = 400, 300
+    sc = rt.Scene("car", W, H)
+    p = rt.make_params(W, H)
+    a = rt.RayTracer(W, H)
+    a.upload(sc)
+    a.render(p)
+    for frame in range(1, 3):
+        sc.animate(frame * 0.33, 0.33, mode=0)
+        an = sc.animated
+        lo, hi = int(an.min()), int(an.max()) + 1
+        a.update_shapes(lo, sc.shapes[lo:hi]); a.update_nodes(sc.nodes)
+        ra, ia = a.render(p)
+        b = rt.RayTracer(W, H)
+        b.upload(sc)
+        rb, ib = b.render(p)
+        assert np.array_equal(ia, ib) and np.array_equal(ra.view(np.uint32), rb.view(np.uint32))
+        sa, sb = a.render_stats(p), b.render_stats(p)
+        assert sa["rays"] == sb["rays"]
+        assert sa["prim_tests"] <= 1.25 * sb["prim_tests"] and sa["node_visits"] <= 1.25 * sb["node_visits"], (sa, sb)
+        b.close()
+    # squash every 7th triangle into a sliver: prim_bound gives up on those (some of them live in fat leaves)
+    shapes = sc.shapes.copy()
+    tri = np.flatnonzero(shapes["type"] == 3)[::7]
+    shapes["triP3"][tri] = shapes["triP1"][tri] + (shapes["triP2"][tri] - shapes["triP1"][tri]) * np.float32(0.5)
+    k = 0
+    a.update_shapes(0, shapes)
+    ra, ia = a.render(p)
+    b = rt.RayTracer(W, H)
+    b.upload_scene(sc.light, sc.camera, shapes, sc.nodes, sc.indices)
+    rb, ib = b.render(p)
+    assert np.array_equal(ia, ib) and np.array_equal(ra.view(np.uint32), rb.view(np.uint32))
+    a.update_shapes(k, shapes[k:k + 1])            # next upload: the degraded flag has arrived, the layout is rebuilt
+    ra2, ia2 = a.render(p)
+    assert np.array_equal(ia2, ib) and np.array_equal(ra2.view(np.uint32), rb.view(np.uint32))
+    sa, sb = a.render_stats(p), b.render_stats(p)
+    assert sa["prim_tests"] == sb["prim_tests"], (sa, sb)
+    a.close(); b.close()
+
+
 def test_camera_far_away(rt, oracle):
     """Camera beyond the region the sub-tree margins were computed for (omax): margins are recomputed / ignored."""
     W, H = 200, 150
@@ -302,6 +346,41 @@ def test_fused_gather_frame_target(rt):
             t.synchronize()
             t.close()
         assert np.array_equal(frame.cpu().numpy().view(np.uint32), full.view(np.uint32)), "world=%d" % world
+
+
+def test_host_frame_target(rt):
+    """rt_host_frame_register: the kernels store straight into a pinned, mapped host frame (here an mmap'd
+    /dev/shm file, as several ranks would share it) == rt_render's frame, for world 1 and for 3 ranks."""
+    import os
+    W, H = 333, 201
+    sc = rt.Scene("monkey", W, H)
+    p = rt.make_params(W, H)
+    tr = rt.RayTracer(W, H, flags=0)
+    tr.upload(sc)
+    full, _ = tr.render(p, want_ids=False)
+    path = "/dev/shm/rt_b200_test_%d" % os.getpid()
+    host = np.memmap(path, dtype=np.float32, mode="w+", shape=(H * W * 4,))
+    os.unlink(path)
+    try:
+        for world in (1, 3):
+            host[:] = -1.0
+            ranks = []
+            for r in range(world):
+                t = rt.RayTracer(W, H, flags=0)
+                t.upload(sc)
+                t.set_shard(r, world)
+                alias = t.host_frame_register(host) if r == 0 else alias
+                t.set_frame_target(alias)
+                t.render_device(p)
+                ranks.append(t)
+            for t in ranks:
+                t.synchronize()
+            assert np.array_equal(np.asarray(host).view(np.uint32), full.view(np.uint32).reshape(-1)), "world=%d" % world
+            ranks[0].host_frame_unregister(host)
+            for t in ranks:
+                t.close()
+    finally:
+        tr.close()
 
 
 def test_top_tree_flag_matches(rt, oracle):

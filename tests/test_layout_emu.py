@@ -29,6 +29,7 @@ def emu():
     L.emu_destroy.argtypes = [vp]; L.emu_destroy.restype = None
     L.emu_info.argtypes = [vp, vp]; L.emu_info.restype = None
     L.emu_refit.argtypes = [vp, vp, vp]; L.emu_refit.restype = ip
+    L.emu_refit_graph_check.argtypes = [vp, vp, vp]; L.emu_refit_graph_check.restype = ip
     L.emu_query.argtypes = [vp, ip, vp, vp, ip, ip, vp, vp, vp, vp, vp]; L.emu_query.restype = None
     return L
 
@@ -65,6 +66,9 @@ class Emu:
     def refit(self, shapes, nodes):
         self.keep[0] = np.ascontiguousarray(shapes); self.keep[1] = np.ascontiguousarray(nodes)
         return self.L.emu_refit(self.h, _p(self.keep[0]), _p(self.keep[1]))
+
+    def refit_graph_check(self):
+        return self.L.emu_refit_graph_check(self.h, _p(self.keep[0]), _p(self.keep[1]))
 
     def close(self):
         self.L.emu_destroy(self.h)
@@ -208,6 +212,23 @@ def test_refit_after_animation(rt, oracle, emu):
             rid, rdist, _ = oracle.intersect_scene_batch(shapes, nodes, sc.indices, o, d, mt)
             gid, gdist, _, _ = e.query(o, d, mt)
             assert np.array_equal(gid, rid) and np.array_equal(gdist.view(np.uint32), rdist.view(np.uint32)), "frame %d mt=%s" % (frame, mt)
+    e.close()
+
+
+@pytest.mark.parametrize("name", ["car", "monkey", "toy"])
+def test_refit_graph_reproduces_host_refit(rt, emu, name):
+    """The dependency graph the device refit kernel executes (rtl::build_refit_graph), replayed on the host with
+    the kernel's arrival rule, gives bit for bit the boxes of the host refit, before and after the scene moved."""
+    sc = rt.Scene(name, 800, 600)
+    e = Emu(emu, sc.shapes, sc.nodes, sc.indices)
+    if e.info()["sub"] == 0 and e.info()["nodes_b"] == 0:
+        e.close(); pytest.skip("no boxes of ours in this scene")
+    assert e.refit(sc.shapes, sc.nodes) == 1
+    assert e.refit_graph_check() == 0
+    for frame in range(1, 3):
+        sc.animate(frame * 0.41, 0.41, mode=0)
+        assert e.refit(sc.shapes, sc.nodes) == 1
+        assert e.refit_graph_check() == 0
     e.close()
 
 
