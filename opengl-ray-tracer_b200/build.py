@@ -30,7 +30,7 @@ def _run(cmd):
 
 
 def cuda_sources():
-    return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh"))] + \
+    return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh", ".h"))] + \
            [os.path.join(ROOT, "include", "rt_api.h"), os.path.join(ROOT, "include", "rt_flat.h")]
 
 

@@ -52,8 +52,8 @@ __device__ __forceinline__ void offer(const DeviceScene& S, Query& q, int s, V3 
 // Triangle leaf, Barycentric mode.  The plane stage of four consecutive slots is evaluated as
 // four independent dependency chains (the loads are issued together; the slot arrays are
 // padded so reading past `end` is safe); the survivors then go through the division and the
-// barycentric stage in slot order in ONE rolled loop body (code size: the hot loop must stay
-// inside the instruction cache).  Returns true when an any-hit query is satisfied.
+// barycentric stage in slot order (unrolled: the rolled body with its index selects was 8 % slower
+// and spilled more).  Returns true when an any-hit query is satisfied.
 __device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, Query& q, int s0, int end, bool anyMode) {
     const Ray& r = q.r;
     for (int s = s0; s < end; s += 4) {
@@ -67,12 +67,10 @@ __device__ __forceinline__ bool leaf_triangles_bary(const DeviceScene& S, Query&
             num[i] = -(qq.w + dot3(n, r.o));
             if ((np[i] > 0.0f) && (num[i] > 0.0f) && (s + i < end)) pm |= 1u << i;
         }
-#pragma unroll 1
+#pragma unroll
         for (int i = 0; i < 4; ++i) {
             if (pm & (1u << i)) {
-                const float npi = i == 0 ? np[0] : i == 1 ? np[1] : i == 2 ? np[2] : np[3];
-                const float numi = i == 0 ? num[0] : i == 1 ? num[1] : i == 2 ? num[2] : num[3];
-                const float t = numi / npi;
+                const float t = num[i] / np[i];
                 if (t > 0.0f) {
                     const V3 hp = r.o + t * r.d;
                     if (bary_stage2(__ldg(S.q1 + s + i), __ldg(S.q2 + s + i), __ldg(S.q3 + s + i), hp)) {
