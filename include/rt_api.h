@@ -172,6 +172,24 @@ int rt_frame_download(rt_ctx* ctx, float* host_rgba);
 int rt_host_frame_register(rt_ctx* ctx, void* host_frame, size_t bytes, float** dev_alias);
 int rt_host_frame_unregister(rt_ctx* ctx, void* host_frame);
 
+/* ---- device-side animation (flag-gated addition, the host path above stays the default) ----
+ * The reference animates on the host and re-uploads (bounceSphere src/main.cpp:1079-1082,
+ * updateWheelAnimations :1084-1109, updateScene :981-992, updateBVH :1068-1077 + node re-upload :342-344).
+ * With the animations registered here, rt_animate does the same frame step on the device copies: K6 moves
+ * the registered shapes (the per-entry sin / cos come from the host's libm, so the shapes are bit-identical
+ * to the host path), K7 grows the reference node boxes (updateBVH semantics), then the library's own boxes
+ * are refitted and the scene repacked as after an upload.  Nothing crosses PCIe but a few scalars.
+ *   rt_anim_bounce   sphere `shape`: centre.y = origin_y + amplitude * sin(frequency * t)
+ *   rt_anim_rotate_z triangles `shapes[0..count)`: vertices rotate about the z axis through `center` by
+ *                    speed * dt per frame; planeNormal / planeD stay as they are (stale, as upstream)
+ * The host copies kept by the context go stale; rt_download_scene fetches the current device shapes and
+ * nodes (parity checks, or to continue on the host). */
+int rt_anim_clear(rt_ctx* ctx);
+int rt_anim_bounce(rt_ctx* ctx, int shape, float origin_y, float amplitude, float frequency);
+int rt_anim_rotate_z(rt_ctx* ctx, const int32_t* shapes, int count, const float center[3], float speed);
+int rt_animate(rt_ctx* ctx, float t, float dt);
+int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
+
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in
  * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one
  * row-major W*H image. */

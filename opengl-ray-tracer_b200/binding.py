@@ -56,7 +56,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -93,6 +93,11 @@ def lib():
     L.rt_frame_download.argtypes = [vp, vp]; L.rt_frame_download.restype = ip
     L.rt_host_frame_register.argtypes = [vp, vp, C.c_size_t, C.POINTER(vp)]; L.rt_host_frame_register.restype = ip
     L.rt_host_frame_unregister.argtypes = [vp, vp]; L.rt_host_frame_unregister.restype = ip
+    L.rt_anim_clear.argtypes = [vp]; L.rt_anim_clear.restype = ip
+    L.rt_anim_bounce.argtypes = [vp, ip, C.c_float, C.c_float, C.c_float]; L.rt_anim_bounce.restype = ip
+    L.rt_anim_rotate_z.argtypes = [vp, vp, ip, vp, C.c_float]; L.rt_anim_rotate_z.restype = ip
+    L.rt_animate.argtypes = [vp, C.c_float, C.c_float]; L.rt_animate.restype = ip
+    L.rt_download_scene.argtypes = [vp, vp, vp]; L.rt_download_scene.restype = ip
     L.rt_item_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_item_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
@@ -122,6 +127,8 @@ def hostlib():
         getattr(H, name).argtypes = [vp, C.POINTER(ip)]; getattr(H, name).restype = vp
     H.rh_bvh_stats.argtypes = [vp, C.POINTER(ip * 4)]; H.rh_bvh_stats.restype = None
     H.rh_scene_animate.argtypes = [vp, C.c_float, C.c_float, ip]; H.rh_scene_animate.restype = ip
+    H.rh_anim_count.argtypes = [vp]; H.rh_anim_count.restype = ip
+    H.rh_anim_get.argtypes = [vp, ip, C.POINTER(ip), C.POINTER(ip), C.POINTER(C.c_float * 4)]; H.rh_anim_get.restype = vp
     H.rh_set_camera.argtypes = [vp, C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 3), C.c_float, C.c_float]
     H.rh_set_camera.restype = None
     _hostlib = H
@@ -201,6 +208,16 @@ class Scene:
 
     def animate(self, t, dt, mode=0):
         return self._H.rh_scene_animate(self._h, float(t), float(dt), int(mode))
+
+    def animations(self):
+        """[(kind, shape indices, params)]: kind 0 bounce (origin y, amplitude, frequency), 1 rotation about z (centre xyz, speed)."""
+        out = []
+        for k in range(self._H.rh_anim_count(self._h)):
+            kind, count, params = C.c_int(), C.c_int(), (C.c_float * 4)()
+            p = self._H.rh_anim_get(self._h, k, C.byref(kind), C.byref(count), C.byref(params))
+            idx = np.frombuffer((C.c_int32 * count.value).from_address(p), dtype=np.int32).copy()
+            out.append((kind.value, idx, [float(x) for x in params]))
+        return out
 
     def set_camera(self, pos, target, fov=60.0, aspect=None):
         a = aspect if aspect is not None else self.width / self.height
@@ -319,6 +336,24 @@ class RayTracer:
         d = C.c_void_p()
         self._chk(self._L.rt_host_frame_register(self._c, _ptr(host), host.nbytes, C.byref(d)))
         return d.value
+
+    def register_animations(self, scene):
+        """Registers the scene's animation list (bouncing spheres / rotating wheels) for rt_animate."""
+        self._chk(self._L.rt_anim_clear(self._c))
+        for kind, shapes, params in scene.animations():
+            if kind == 0:
+                self._chk(self._L.rt_anim_bounce(self._c, int(shapes[0]), params[0], params[1], params[2]))
+            else:
+                ctr = np.array(params[:3], np.float32)
+                self._chk(self._L.rt_anim_rotate_z(self._c, _ptr(np.ascontiguousarray(shapes, np.int32)), len(shapes), _ptr(ctr), params[3]))
+
+    def animate(self, t, dt):
+        self._chk(self._L.rt_animate(self._c, t, dt))
+
+    def download_scene(self, n_shapes, n_nodes):
+        shapes = np.zeros(n_shapes, dtype=SHAPE_DTYPE); nodes = np.zeros(n_nodes, dtype=NODE_DTYPE)
+        self._chk(self._L.rt_download_scene(self._c, _ptr(shapes), _ptr(nodes)))
+        return shapes, nodes
 
     def host_frame_unregister(self, host):
         self._chk(self._L.rt_host_frame_unregister(self._c, _ptr(host)))

@@ -1,0 +1,121 @@
+// rt_anim.cuh — K6 / K7: the reference's per-frame animation step on the device.
+//
+// Upstream, an animated frame is: move the animated shapes on the host (bounceSphere main.cpp:1079-1082,
+// updateWheelAnimations :1084-1109), re-serialize each one and push it with its own 192-byte
+// glBufferSubData (:981-992), grow the boxes of every BVH node that holds an animated shape
+// (updateBVH :1068-1077, grow-only) and re-upload all nodes (:342-344).  Here the shapes and nodes stay
+// on the device:
+//   K6 anim_kernel   one thread per animated shape; the per-entry scalars (the bounced y, cos/sin of the
+//                    frame's wheel angle) are computed on the host with the host's libm and passed in,
+//                    the per-vertex arithmetic runs here with the reference's operation order — the
+//                    result is bit-identical to the host path (checked by tests/test_gpu_parity.py).
+//                    Wheels keep their stale planeNormal / planeD, as upstream does (:1101-1106).
+//   K7 grow_kernel   grow-only refit of the raw reference nodes: one thread per leaf grows its box by the
+//                    leaf's animated shapes (BoundingBox::growToInclude, BoundingBox.hpp:60-95) and walks
+//                    towards the root; the second thread to arrive at an inner node joins its children
+//                    into it.  For a tree whose parents contain their children (the reference builder's)
+//                    this equals updateBVH, which grows every node by the animated shapes below it.
+// K4 (our own boxes) and K2 (repack) follow as after an upload.
+#pragma once
+#include "rt_kernels.cuh"
+
+namespace rt {
+
+enum { RT_ANIM_BOUNCE = 0, RT_ANIM_ROTATE_Z = 1 };
+struct AnimEntry { int kind; float a, b, cx, cy; };           // bounce: a = new centre y; rotate: a = cos, b = sin, (cx, cy) = wheel centre
+struct AnimItem  { int shape; int entry; };
+
+__global__ void anim_kernel(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
+                            const AnimEntry* __restrict__ entries) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nItems) return;
+    const AnimItem it = items[i];
+    const AnimEntry e = entries[it.entry];
+    rt_flat_shape* s = shapes + it.shape;
+    if (e.kind == RT_ANIM_BOUNCE) {
+        s->sphereCenter[1] = e.a;
+    } else {
+        float* P[3] = {s->triP1, s->triP2, s->triP3};
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+            const float x = P[v][0] - e.cx, y = P[v][1] - e.cy;
+            P[v][0] = (e.a * x - e.b * y) + e.cx;
+            P[v][1] = (e.b * x + e.a * y) + e.cy;
+        }
+    }
+}
+
+struct GBox { float mn[3], mx[3]; };
+__device__ __forceinline__ void g_grow(GBox& b, float x, float y, float z) {       // glm::min / glm::max select order
+    b.mn[0] = x < b.mn[0] ? x : b.mn[0]; b.mn[1] = y < b.mn[1] ? y : b.mn[1]; b.mn[2] = z < b.mn[2] ? z : b.mn[2];
+    b.mx[0] = b.mx[0] < x ? x : b.mx[0]; b.mx[1] = b.mx[1] < y ? y : b.mx[1]; b.mx[2] = b.mx[2] < z ? z : b.mx[2];
+}
+// BoundingBox::growToInclude(Shape*) (BoundingBox.hpp:60-95): spheres by centre +- radius, walls by start and
+// the opposite corner (wall.hpp:16-31), triangles by their vertices; infinite planes are ignored.
+__device__ __forceinline__ void g_grow_shape(GBox& b, const rt_flat_shape* __restrict__ s) {
+    const int type = s->type;
+    if (type == RT_SHAPE_SPHERE) {
+        const float r = s->sphereRadius;
+        g_grow(b, s->sphereCenter[0] + r, s->sphereCenter[1] + r, s->sphereCenter[2] + r);
+        g_grow(b, s->sphereCenter[0] - r, s->sphereCenter[1] - r, s->sphereCenter[2] - r);
+    } else if (type == RT_SHAPE_WALL) {
+        const V3 n = mk(s->planeNormal), st = mk(s->wallStart);
+        V3 t1;
+        if (fabsf(n.x) > fabsf(n.y)) t1 = normalize3(mk(-n.z, 0.f, n.x));
+        else t1 = normalize3(mk(0.f, -n.z, n.y));
+        const V3 t2 = normalize3(cross3(n, t1));
+        const V3 e = (st + (s->wallWidth * t1)) + (s->wallHeight * t2);
+        g_grow(b, st.x, st.y, st.z); g_grow(b, e.x, e.y, e.z);
+    } else if (type == RT_SHAPE_TRIANGLE) {
+        if (isfinite(s->triP1[0]) && isfinite(s->triP2[0]) && isfinite(s->triP3[0])) {
+            g_grow(b, s->triP1[0], s->triP1[1], s->triP1[2]);
+            g_grow(b, s->triP2[0], s->triP2[1], s->triP2[2]);
+            g_grow(b, s->triP3[0], s->triP3[1], s->triP3[2]);
+        }
+    }
+}
+__device__ __forceinline__ GBox g_load(const rt_flat_node* n) {
+    const float4 a = __ldcg(reinterpret_cast<const float4*>(n)), c = __ldcg(reinterpret_cast<const float4*>(n) + 1);
+    GBox b; b.mn[0] = a.x; b.mn[1] = a.y; b.mn[2] = a.z; b.mx[0] = c.x; b.mx[1] = c.y; b.mx[2] = c.z;
+    return b;
+}
+__device__ __forceinline__ void g_store(rt_flat_node* n, const GBox& b) {
+    float* p = reinterpret_cast<float*>(n);
+    __stcg(p + 0, b.mn[0]); __stcg(p + 1, b.mn[1]); __stcg(p + 2, b.mn[2]);
+    __stcg(p + 4, b.mx[0]); __stcg(p + 5, b.mx[1]); __stcg(p + 6, b.mx[2]);
+}
+
+// leaves[i]: raw index of leaf i; parent[n]: raw index of n's parent (-1 at the root); arrived: zeroed counters
+__global__ void grow_kernel(rt_flat_node* __restrict__ nodes, const rt_flat_shape* __restrict__ shapes,
+                            const int* __restrict__ indices, const unsigned char* __restrict__ animated,
+                            const int* __restrict__ leaves, int nLeaves, const int* __restrict__ parent,
+                            unsigned* __restrict__ arrived) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nLeaves) return;
+    int n = leaves[i];
+    {
+        GBox b = g_load(nodes + n);
+        const int s0 = nodes[n].startShapeIdx, cnt = nodes[n].numShapes;
+        bool any = false;
+        for (int q = 0; q < cnt; ++q) {
+            const int s = indices[s0 + q];
+            if (animated[s]) { g_grow_shape(b, shapes + s); any = true; }
+        }
+        if (any) g_store(nodes + n, b);
+    }
+    for (int j = parent[n]; j >= 0; j = parent[j]) {
+        __threadfence();
+        if (atomicAdd(arrived + j, 1u) == 0u) return;
+        __threadfence();
+        GBox b = g_load(nodes + j);
+        const GBox l = g_load(nodes + nodes[j].leftChild), r = g_load(nodes + nodes[j].rightChild);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {            // union (an empty child, min > max, changes nothing)
+            b.mn[a] = l.mn[a] < b.mn[a] ? l.mn[a] : b.mn[a]; b.mn[a] = r.mn[a] < b.mn[a] ? r.mn[a] : b.mn[a];
+            b.mx[a] = b.mx[a] < l.mx[a] ? l.mx[a] : b.mx[a]; b.mx[a] = b.mx[a] < r.mx[a] ? r.mx[a] : b.mx[a];
+        }
+        g_store(nodes + j, b);
+    }
+}
+
+}  // namespace rt

@@ -4,6 +4,7 @@
 #include "rt_kernels.cuh"
 #include "rt_layout.h"
 #include "rt_refit.cuh"
+#include "rt_anim.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -91,6 +92,16 @@ struct rt_ctx {
     DevBuf<unsigned> dRfArrived;                // nE counters + 1 "degraded" flag
     int nRfStart = 0;
     int* hRfDegraded = nullptr;                 // pinned: lazily read back flag of the last refit
+    // device-side animation (rt_anim.cuh)
+    struct AnimDef { int kind; float originY, amp, freq, cx, cy, speed; };
+    std::vector<AnimDef> animDefs; std::vector<AnimItem> animItems;
+    PinBuf<AnimEntry> hAnimEntries; DevBuf<AnimEntry> dAnimEntries; DevBuf<AnimItem> dAnimItems;
+    DevBuf<unsigned char> dAnimFlag; DevBuf<int> dIndices, dNodeAux; DevBuf<unsigned> dGrowArrived;   // dNodeAux: [parent nNodes | leaves nLeaves]
+    int nLeavesRaw = 0;
+    bool animDirty = true;            // registrations changed: item list / flags / tree maps must go up again
+    bool devShapesDirty = false, devNodesDirty = false;   // the device copies were changed by K6 / K7: repack without an upload
+    bool hostStale = false;           // the host shadows no longer describe the device scene (shapes and / or node boxes)
+    bool hostShapesStale = false, hostNodesStale = false;
     cudaEvent_t rfDone = nullptr; bool rfPending = false;
     int nSub = 0;
     bool subDirty = false;            // sub-tree boxes must be recomputed (shapes moved / omax grew)
@@ -226,10 +237,23 @@ int flush_scene(rt_ctx* c) {
         for (int k = 0; k < 3; ++k) m = std::fmax(m, std::fabs((double)c->cam.Position[k]));
         if (!(m <= 0.5 * (double)c->omax)) { c->omax = (float)pick_omax(c); c->subDirty = true; }
     }
-    const bool anyCopy = c->shapeHi > c->shapeLo || c->nodesDirty || c->topoDirty || c->subDirty;
+    const bool anyCopy = c->shapeHi > c->shapeLo || c->nodesDirty || c->topoDirty || c->subDirty || c->devShapesDirty || c->devNodesDirty;
     if (!anyCopy) return RT_OK;
+    if (c->topoDirty && c->hostStale) {
+        // the layout is rebuilt from the host shadows: bring them up to date with what the device animated
+        CU(c, cudaStreamSynchronize(c->stream));
+        wait_copies(c);
+        if (c->hostShapesStale && c->nShapes > 0) {        // everything but the range the host has just rewritten
+            const int lo = c->shapeHi > c->shapeLo ? c->shapeLo : c->nShapes, hi = c->shapeHi > c->shapeLo ? c->shapeHi : c->nShapes;
+            if (lo > 0) CU(c, cudaMemcpy(c->hShapes.p, c->dShapes.p, (size_t)lo * sizeof(rt_flat_shape), cudaMemcpyDeviceToHost));
+            if (hi < c->nShapes) CU(c, cudaMemcpy(c->hShapes.p + hi, c->dShapes.p + hi, (size_t)(c->nShapes - hi) * sizeof(rt_flat_shape), cudaMemcpyDeviceToHost));
+        }
+        if (c->hostNodesStale && !c->nodesDirty && c->nNodes > 0)
+            CU(c, cudaMemcpy(c->hNodes.p, c->dNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost));
+        c->hostStale = c->hostShapesStale = c->hostNodesStale = false;
+    }
     const bool shapesChanged = c->shapeHi > c->shapeLo;
-    if (shapesChanged && c->nSub > 0) c->subDirty = true;
+    if ((shapesChanged || c->devShapesDirty) && c->nSub > 0) c->subDirty = true;
     cudaEventRecord(c->ev[0], c->stream);
     if (shapesChanged) {
         CU(c, c->dShapes.reserve((size_t)c->nShapes));
@@ -247,6 +271,7 @@ int flush_scene(rt_ctx* c) {
         if (rtl::ref_tree_nested(c->hNodes.p, c->nNodes)) devRefit = true;
         else { c->nDfsB = 0; c->layout.useB = false; }
     }
+    if (c->devNodesDirty && !c->topoDirty && c->nDfsB > 0) devRefit = true;   // K7 keeps parents around their children
     if (c->subDirty && !c->topoDirty) {
         // shapes moved under a sub-tree (or omax grew): its boxes are refitted on the device (K4)
         devRefit = true;
@@ -282,6 +307,7 @@ int flush_scene(rt_ctx* c) {
             CU(c, cudaMemcpyAsync(c->dRf.p, c->hRf.p, ((size_t)c->nSub * 5 + (size_t)c->nRfStart) * sizeof(int), cudaMemcpyHostToDevice, c->stream));
         }
         subUpload = true; devRefit = false;       // the layout build computed every box on the host
+        c->animDirty = true;                      // tree maps of the device animation follow the new topology
     }
     if (subUpload && c->nSub > 0) {
         CU(c, c->dSubBox.reserve((size_t)c->nSub * 2));
@@ -304,7 +330,7 @@ int flush_scene(rt_ctx* c) {
         }
         subUpload = true;                          // the node lists take the new boxes below
     }
-    if ((c->nodesDirty || c->topoDirty || subUpload) && c->nDfs > 0) {
+    if ((c->nodesDirty || c->topoDirty || subUpload || c->devNodesDirty) && c->nDfs > 0) {
         repack_nodes_kernel<<<(c->nDfs + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dSubBox.p, c->dOrder.p, c->dLinkCnt.p, c->dNodesT.p, c->nDfs);
         c->launches++;
         if (c->nDfsB > 0) {
@@ -312,13 +338,14 @@ int flush_scene(rt_ctx* c) {
             c->launches++;
         }
     }
-    if ((shapesChanged || c->topoDirty) && c->nPrims > 0) {
+    if ((shapesChanged || c->topoDirty || c->devShapesDirty) && c->nPrims > 0) {
         repack_prims_kernel<<<(c->nPrims + 255) / 256, 256, 0, c->stream>>>(c->dShapes.p, c->dPshape.p, c->q0.p, c->q1.p, c->q2.p, c->q3.p, c->ptype.p, c->nPrims);
         c->launches++;
     }
     cudaEventRecord(c->ev[3], c->stream); c->timed[1] = true;
     CU(c, cudaGetLastError());
     c->shapeLo = c->shapeHi = 0; c->nodesDirty = c->topoDirty = false;
+    c->devShapesDirty = c->devNodesDirty = false;
     return RT_OK;
 }
 
@@ -342,6 +369,7 @@ int set_nodes(rt_ctx* c, const void* nodes, int nNodes) {
         for (int k = 0; k < 3; ++k)
             if (!(std::fabs(in[i].boundsMin[k]) <= RT_SAFE_COORD) || !(std::fabs(in[i].boundsMax[k]) <= RT_SAFE_COORD)) c->boxesFinite = false;
     c->nodesDirty = true;
+    c->hostNodesStale = false;
     if (!sameTopo) c->topoDirty = true;
     return RT_OK;
 }
@@ -393,6 +421,8 @@ void rt_destroy(rt_ctx* c) {
     if (c->rfDone) cudaEventDestroy(c->rfDone);
     if (c->hRfDegraded) cudaFreeHost(c->hRfDegraded);
     c->hRf.release(); c->dRf.release(); c->dRfArrived.release();
+    c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
+    c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
@@ -420,6 +450,7 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
         CU(c, c->hShapes.reserve((size_t)nShapes, 0));
         if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
         c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes;
+        c->hostShapesStale = false;
         if (!sameTypes) c->topoDirty = true;
     }
     if (indices) {
@@ -714,6 +745,121 @@ int rt_host_frame_unregister(rt_ctx* c, void* host_frame) {
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaHostUnregister(host_frame));
+    return RT_OK;
+}
+
+int rt_anim_clear(rt_ctx* c) {
+    if (!c) return RT_ERR_ARG;
+    c->animDefs.clear(); c->animItems.clear(); c->animDirty = true;
+    return RT_OK;
+}
+
+int rt_anim_bounce(rt_ctx* c, int shape, float origin_y, float amplitude, float frequency) {
+    if (!c) return RT_ERR_ARG;
+    if (shape < 0 || shape >= c->nShapes) return fail(c, RT_ERR_ARG, "animated shape outside the uploaded buffer");
+    if (c->hShapes.p[shape].type != RT_SHAPE_SPHERE) return fail(c, RT_ERR_ARG, "rt_anim_bounce wants a sphere");
+    c->animItems.push_back(AnimItem{shape, (int)c->animDefs.size()});
+    c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_BOUNCE, origin_y, amplitude, frequency, 0.f, 0.f, 0.f});
+    c->animDirty = true;
+    return RT_OK;
+}
+
+int rt_anim_rotate_z(rt_ctx* c, const int32_t* shapes, int count, const float center[3], float speed) {
+    if (!c || !shapes || !center || count < 0) return RT_ERR_ARG;
+    for (int i = 0; i < count; ++i) {
+        if (shapes[i] < 0 || shapes[i] >= c->nShapes) return fail(c, RT_ERR_ARG, "animated shape outside the uploaded buffer");
+        if (c->hShapes.p[shapes[i]].type != RT_SHAPE_TRIANGLE) return fail(c, RT_ERR_ARG, "rt_anim_rotate_z wants triangles");
+    }
+    for (int i = 0; i < count; ++i) c->animItems.push_back(AnimItem{shapes[i], (int)c->animDefs.size()});
+    c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_ROTATE_Z, 0.f, 0.f, 0.f, center[0], center[1], speed});
+    c->animDirty = true;
+    return RT_OK;
+}
+
+namespace {
+// Tables of the device animation: items, per-shape flags, bvhIndices and the raw tree's parent / leaf lists.
+int upload_anim_tables(rt_ctx* c) {
+    const int nN = c->nNodes, nS = c->nShapes;
+    std::vector<int> aux((size_t)nN, -1);            // parent per raw node, then the leaf list
+    std::vector<int> leaves;
+    for (int i = 0; i < nN; ++i) {
+        const rt_flat_node& x = c->hNodes.p[i];
+        if (x.leftChild == -1) {
+            if (x.numShapes < 0 || x.startShapeIdx < 0 || (size_t)x.startShapeIdx + (size_t)x.numShapes > c->indices.size())
+                return fail(c, RT_ERR_SCENE, "leaf index range outside bvhIndices");
+            leaves.push_back(i);
+            continue;
+        }
+        const int ch[2] = {x.leftChild, x.rightChild};
+        for (int k : ch) {
+            if (k < 0 || k >= nN || k == i || aux[(size_t)k] != -1) return fail(c, RT_ERR_SCENE, "device animation needs a proper tree (one parent per node)");
+            aux[(size_t)k] = i;
+        }
+    }
+    if (nN > 0 && aux[(size_t)nN - 1] != -1) return fail(c, RT_ERR_SCENE, "the root (last node) has a parent");
+    c->nLeavesRaw = (int)leaves.size();
+    aux.insert(aux.end(), leaves.begin(), leaves.end());
+    std::vector<unsigned char> flag((size_t)nS, 0);
+    for (const AnimItem& it : c->animItems) if (it.shape < nS) flag[(size_t)it.shape] = 1;
+    CU(c, c->dNodeAux.reserve(aux.size())); CU(c, c->dGrowArrived.reserve((size_t)nN));
+    CU(c, c->dAnimFlag.reserve((size_t)nS)); CU(c, c->dIndices.reserve(c->indices.size()));
+    CU(c, c->dAnimItems.reserve(c->animItems.size())); CU(c, c->dAnimEntries.reserve(c->animDefs.size()));
+    CU(c, c->hAnimEntries.reserve(c->animDefs.size(), 0));
+    // pageable sources: these copies return after the data has been staged
+    if (!aux.empty()) CU(c, cudaMemcpyAsync(c->dNodeAux.p, aux.data(), aux.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    if (nS > 0) CU(c, cudaMemcpyAsync(c->dAnimFlag.p, flag.data(), (size_t)nS, cudaMemcpyHostToDevice, c->stream));
+    if (!c->indices.empty()) CU(c, cudaMemcpyAsync(c->dIndices.p, c->indices.data(), c->indices.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    if (!c->animItems.empty()) CU(c, cudaMemcpyAsync(c->dAnimItems.p, c->animItems.data(), c->animItems.size() * sizeof(AnimItem), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->animDirty = false;
+    return RT_OK;
+}
+}  // namespace
+
+int rt_animate(rt_ctx* c, float t, float dt) {
+    if (!c) return RT_ERR_ARG;
+    if (!c->haveScene) return fail(c, RT_ERR_STATE, "rt_animate before a scene upload");
+    CU(c, cudaSetDevice(c->device));
+    int rc = flush_scene(c);                       // pending host updates first: K6 works on the device copies
+    if (rc != RT_OK) return rc;
+    if (c->animDefs.empty() || c->animItems.empty()) return RT_OK;
+    for (const AnimItem& it : c->animItems) if (it.shape >= c->nShapes) return fail(c, RT_ERR_STATE, "animation registered for a shape that is gone");
+    if (c->animDirty) { rc = upload_anim_tables(c); if (rc != RT_OK) return rc; }
+    wait_copies(c);                                // the pinned entry table is the source of an async copy
+    for (size_t e = 0; e < c->animDefs.size(); ++e) {
+        const rt_ctx::AnimDef& d = c->animDefs[e];
+        AnimEntry& o = c->hAnimEntries.p[e];
+        o.kind = d.kind; o.cx = d.cx; o.cy = d.cy;
+        if (d.kind == RT_ANIM_BOUNCE) { o.a = d.originY + d.amp * std::sin(d.freq * t); o.b = 0.f; }     // main.cpp:1079-1082
+        else { const float ang = d.speed * dt; o.a = std::cos(ang); o.b = std::sin(ang); }                 // main.cpp:1084-1109
+    }
+    CU(c, cudaMemcpyAsync(c->dAnimEntries.p, c->hAnimEntries.p, c->animDefs.size() * sizeof(AnimEntry), cudaMemcpyHostToDevice, c->stream));
+    cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
+    const int nI = (int)c->animItems.size();
+    anim_kernel<<<(nI + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, c->dAnimEntries.p);
+    c->launches++;
+    if (c->nNodes > 0 && c->nLeavesRaw > 0) {
+        CU(c, cudaMemsetAsync(c->dGrowArrived.p, 0, (size_t)c->nNodes * sizeof(unsigned), c->stream));
+        grow_kernel<<<(c->nLeavesRaw + 127) / 128, 128, 0, c->stream>>>(c->dNodes.p, c->dShapes.p, c->dIndices.p, c->dAnimFlag.p,
+            c->dNodeAux.p + c->nNodes, c->nLeavesRaw, c->dNodeAux.p, c->dGrowArrived.p);
+        c->launches++;
+        c->devNodesDirty = true;
+    }
+    CU(c, cudaGetLastError());
+    c->devShapesDirty = true; c->hostStale = c->hostShapesStale = true;
+    if (c->devNodesDirty) c->hostNodesStale = true;
+    return RT_OK;
+}
+
+int rt_download_scene(rt_ctx* c, void* shapes, void* nodes) {
+    if (!c) return RT_ERR_ARG;
+    if (!c->haveScene) return fail(c, RT_ERR_STATE, "no scene");
+    CU(c, cudaSetDevice(c->device));
+    int rc = flush_scene(c);
+    if (rc != RT_OK) return rc;
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (shapes && c->nShapes > 0) CU(c, cudaMemcpy(shapes, c->dShapes.p, (size_t)c->nShapes * sizeof(rt_flat_shape), cudaMemcpyDeviceToHost));
+    if (nodes && c->nNodes > 0) CU(c, cudaMemcpy(nodes, c->dNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost));
     return RT_OK;
 }
 

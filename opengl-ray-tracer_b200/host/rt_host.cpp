@@ -476,6 +476,31 @@ int rh_scene_animate(rh_scene* s, float t, float dt, int mode) {
     return (int)s->animated.size();
 }
 
+int rh_anim_count(const rh_scene* s) {
+    if (s->name == "monkey") return 3;
+    if (s->name == "car") return 4;
+    if (s->name == "toy") return 1;
+    return 0;
+}
+const int32_t* rh_anim_get(const rh_scene* s, int k, int* kind, int* count, float params[4]) {
+    static thread_local std::vector<int32_t> list;
+    list.clear();
+    if (k < 0 || k >= rh_anim_count(s)) return nullptr;
+    if (s->name == "car") {
+        const Wheel& w = s->wheels[k];
+        for (int i : w.idx) list.push_back(i);
+        *kind = 1; *count = (int)list.size();
+        params[0] = w.center.x; params[1] = w.center.y; params[2] = w.center.z; params[3] = 1.0f;
+        return list.data();
+    }
+    const float amp[3] = {10, 7, 15}, freq[3] = {1, 0.8f, 1.5f};
+    const bool toy = s->name == "toy";
+    list.push_back(k);
+    *kind = 0; *count = 1;
+    params[0] = s->shapes[(size_t)k].origin.y; params[1] = toy ? 2.f : amp[k]; params[2] = toy ? 1.f : freq[k]; params[3] = 0.f;
+    return list.data();
+}
+
 void rh_set_camera(rh_scene* s, const float pos[3], const float target[3], float fov, float aspect) {
     look_at(*s, v3(pos), v3(target), fov, aspect);
 }

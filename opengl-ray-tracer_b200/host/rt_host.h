@@ -53,6 +53,13 @@ void rh_bvh_stats(const rh_scene* s, int out[4]);
 int rh_scene_animate(rh_scene* s, float t, float dt, int mode);
 const int32_t* rh_animated(const rh_scene* s, int* n);
 
+/* The scene's animation list, for callers that animate on the device (rt_anim_bounce / rt_anim_rotate_z):
+ * entry k: kind 0 = bounce (shapes[0] = the sphere; params = origin y, amplitude, frequency),
+ *          kind 1 = rotation about z (shapes[0..count) = triangles; params = centre x, y, z, speed).
+ * rh_anim_count = number of entries; rh_anim_get returns the shape list. */
+int rh_anim_count(const rh_scene* s);
+const int32_t* rh_anim_get(const rh_scene* s, int k, int* kind, int* count, float params[4]);
+
 /* Camera helper (camera.hpp:139-163): place + LookAt, fov in degrees. */
 void rh_set_camera(rh_scene* s, const float pos[3], const float target[3], float fov, float aspect);
 

@@ -269,6 +269,42 @@ def test_device_refit_keeps_the_boxes_tight(rt):
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("name", ["monkey", "car"])
+def test_device_animation_equals_host_path(rt, name):
+    """rt_animate (K6 anim_kernel + K7 grow_kernel on the device copies) against the reference's frame step done on
+    the host (animate, per-shape update, grow-only updateBVH, node re-upload): the shapes, the node boxes and the
+    rendered frames are bit-identical, frame after frame."""
+    W, H = 320, 240
+    sc = rt.Scene(name, W, H)
+    p = rt.make_params(W, H)
+    a = rt.RayTracer(W, H); b = rt.RayTracer(W, H)
+    a.upload(sc); b.upload(sc)
+    b.register_animations(sc)
+    an = sc.animated
+    lo, hi = int(an.min()), int(an.max()) + 1
+    for frame in range(1, 5):
+        t, dt = frame * 0.21, 0.21
+        sc.animate(t, dt, mode=0)
+        a.update_shapes(lo, sc.shapes[lo:hi]); a.update_nodes(sc.nodes)
+        b.animate(t, dt)
+        ra, ia = a.render(p); rb, ib = b.render(p)
+        assert np.array_equal(ia, ib) and np.array_equal(ra.view(np.uint32), rb.view(np.uint32)), "frame %d" % frame
+        shapes_d, nodes_d = b.download_scene(len(sc.shapes), len(sc.nodes))
+        assert shapes_d.tobytes() == np.ascontiguousarray(sc.shapes).tobytes(), "shapes, frame %d" % frame
+        assert nodes_d.tobytes() == np.ascontiguousarray(sc.nodes).tobytes(), "nodes, frame %d" % frame
+    # a host-side change after device animation: the layout is rebuilt from the downloaded state
+    shapes = shapes_d.copy()
+    k = int(np.flatnonzero(shapes["type"] == 0)[-1])
+    shapes["type"][k] = 3                                        # a sphere becomes a (degenerate) triangle: topology change
+    b.update_shapes(k, shapes[k:k + 1])
+    rb, ib = b.render(p)
+    c = rt.RayTracer(W, H)
+    c.upload_scene(sc.light, sc.camera, shapes, sc.nodes, sc.indices)
+    rc, ic = c.render(p)
+    assert np.array_equal(ib, ic) and np.array_equal(rb.view(np.uint32), rc.view(np.uint32))
+    a.close(); b.close(); c.close()
+
+
 def test_camera_far_away(rt, oracle):
     """Camera beyond the region the sub-tree margins were computed for (omax): margins are recomputed / ignored."""
     W, H = 200, 150
