@@ -600,14 +600,15 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     }
     // heavy-first order (single-launch renders): build the list from the previous frame's item costs
     F.itemCost = nullptr; F.heavyList = nullptr; F.heavyFlag = nullptr; F.lptCtl = nullptr;
-    if (nBands == 1 && !count && tilesMine > 0 && !(c->flags & RT_FLAG_NO_HEAVY_FIRST)) {
+    if (nBands == 1 && !count && tilesMine > 0 && tilesMine * RT_WARPS_PER_TILE < (1 << 24) && !(c->flags & RT_FLAG_NO_HEAVY_FIRST)) {
         const int items = tilesMine * RT_WARPS_PER_TILE;
-        CU(c, c->itemCost.reserve((size_t)items)); CU(c, c->heavyList.reserve((size_t)items));
+        CU(c, c->itemCost.reserve((size_t)items)); CU(c, c->heavyList.reserve((size_t)items * (1u << RT_SPLIT_MAXLG)));
         CU(c, c->heavyFlag.reserve((size_t)items)); CU(c, c->lptCtl.reserve(4));
         CU(c, cudaMemsetAsync(c->lptCtl.p, 0, 4 * sizeof(unsigned), c->stream));
         if (c->lptItems == items) {
             lpt_sum_kernel<<<64, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p);
-            lpt_mark_kernel<<<(items + 255) / 256, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p, c->heavyList.p, c->heavyFlag.p);
+            lpt_mark_kernel<<<(items + 255) / 256, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p, c->heavyList.p, c->heavyFlag.p,
+                                                                         c->gridBlocks[variant] * (RT_BLOCK_THREADS / 32));
             c->launches += 2;
         }
         c->lptItems = items;

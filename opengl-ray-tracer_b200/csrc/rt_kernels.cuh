@@ -389,11 +389,15 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
     bool heavyLeft = nHeavy > 0, lightLeft = true;
     for (int round = 0; P.itemsPerWarp == 0 || round < P.itemsPerWarp; ++round) {
         int w = -1;
+        int parts = 1, part = 0;                 // a heavy block may come as 2 or 4 row groups (see lpt_mark_kernel)
         if (heavyLeft && (favoured || !lightLeft)) {
             int hq = 0;
             if (lane == 0) hq = (int)atomicAdd(P.lptCtl + 1, 1u);
             hq = __shfl_sync(0xffffffffu, hq, 0);
-            if (hq < nHeavy) w = (int)__ldg(P.heavyList + hq); else heavyLeft = false;
+            if (hq < nHeavy) {
+                const unsigned e = __ldg(P.heavyList + hq);
+                w = (int)(e & 0x00ffffffu); part = (int)((e >> 24) & 31u); parts = 1 << (e >> 29);
+            } else heavyLeft = false;
         }
         if (w < 0 && lightLeft) {
             int lq = 0;
@@ -410,7 +414,8 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         const int ly = ((b >> 2) << 2) + (lane >> 3);
         const int x = (tile % P.tilesX) * RT_TILE_W + lx;
         const int y = (tile / P.tilesX) * RT_TILE_H + ly;
-        const bool inside = x < P.W && y < P.H;
+        const bool partOK = ((lane * parts) >> 5) == part;             // the lanes (rows / row pieces of the 8x4 block) this warp renders
+        const bool inside = x < P.W && y < P.H && partOK;
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
         int id = -1;
         unsigned long long cost0 = 0;
@@ -447,10 +452,13 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
             // fused gather: the pixel goes straight to its row-major place in the full frame, which
             // may live on another GPU (peer mapping over NVLink); 128-byte row segments per warp
             if (P.frameTarget) { if (inside) out[(size_t)y * (size_t)P.W + (size_t)x] = c; }
-            else out[o] = c;
-            if (P.writeIds) ids[o] = id;
+            else if (partOK) out[o] = c;
+            if (P.writeIds && partOK) ids[o] = id;
         }
-        if (P.itemCost && lane == 0) P.itemCost[w] = (unsigned)((unsigned long long)(clock64() - itemClk0) >> 4);
+        if (P.itemCost && lane == 0) {           // parts add up (lpt_mark_kernel zeroed the entry of a split block)
+            const unsigned dtc = (unsigned)((unsigned long long)(clock64() - itemClk0) >> 4);
+            if (parts == 1) P.itemCost[w] = dtc; else atomicAdd(P.itemCost + w, dtc);
+        }
     }
     if (COUNT) {
         for (int i = 0; i < RT_NTALLY; ++i) {
@@ -474,14 +482,32 @@ __global__ void lpt_sum_kernel(const unsigned* __restrict__ cost, int n, unsigne
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if ((threadIdx.x & 31) == 0 && s) atomicAdd(reinterpret_cast<unsigned long long*>(ctl + 2), s);
 }
-__global__ void lpt_mark_kernel(const unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl,
-                                unsigned* __restrict__ heavyList, unsigned char* __restrict__ heavyFlag) {
+// A block whose cost is a large share of what ONE warp would ideally do in the whole frame (sum / warps of the
+// grid) bounds the frame however early it starts — the case of small frames and of many GPUs sharing a frame.
+// Such a block is listed as 2^k lane groups (8x2, 8x1, 4x1 ... pixels each, other lanes idle) that different
+// warps pick up: the dependent walk of each group is shorter because its lane-mode iterations serve fewer lanes.
+#ifndef RT_SPLIT_MAXLG
+#define RT_SPLIT_MAXLG 3       // at most 2^this parts
+#endif
+#ifndef RT_SPLIT_K
+#define RT_SPLIT_K 2           // parts ~ K * cost / share, rounded down to a power of two (two parts from cost > share on)
+#endif
+__global__ void lpt_mark_kernel(unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl,
+                                unsigned* __restrict__ heavyList, unsigned char* __restrict__ heavyFlag, int gridWarps) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const unsigned long long sum = *reinterpret_cast<const unsigned long long*>(ctl + 2);
-    const bool heavy = (unsigned long long)cost[i] * (unsigned long long)n > (unsigned long long)RT_HEAVY_FACTOR * sum;
+    const unsigned long long ci = cost[i];
+    const bool heavy = ci * (unsigned long long)n > (unsigned long long)RT_HEAVY_FACTOR * sum;
     heavyFlag[i] = heavy ? 1 : 0;
-    if (heavy) heavyList[atomicAdd(ctl, 1u)] = (unsigned)i;
+    if (!heavy) return;
+    const unsigned long long want = sum > 0 ? ci * (unsigned long long)gridWarps * RT_SPLIT_K / sum : 0;   // ~ K * cost / share
+    unsigned lg = 0;
+    while (lg < RT_SPLIT_MAXLG && (2ull << lg) <= want) ++lg;
+    const unsigned parts = 1u << lg;
+    const unsigned at = atomicAdd(ctl, parts);
+    for (unsigned p = 0; p < parts; ++p) heavyList[at + p] = (unsigned)i | (p << 24) | (lg << 29);
+    if (parts > 1) cost[i] = 0;                  // the parts add their costs up
 }
 
 // ---------------------------------------------------------------------------
