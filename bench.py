@@ -540,7 +540,7 @@ def main():
         winst = prof.get("render_kernel_warp_instructions_per_launch") if traffic is not None else None
         achieved = alg / ren / 1e6 if alg else None
         line = {
-            "metric": "Mrays/s (car scene)", "value": rays / tot / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "metric": "Mrays/s (%s scene)" % args.scene, "value": rays / tot / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": tot, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "fps": 1e3 / tot, "render_ms": ren, "gather_untile_ms": gat,
