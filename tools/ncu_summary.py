@@ -11,7 +11,7 @@ KEEP = ['Kernel Name','Block Size','Grid Size','gpu__time_duration.sum','dram__b
  'smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio','smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio',
  'smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio','smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio',
  'smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio','smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio',
- 'l1tex__t_bytes.sum','lts__t_bytes.sum','l1tex__t_bytes.sum.per_second','lts__t_bytes.sum.per_second','sm__inst_executed_pipe_fma.sum','sm__inst_executed_pipe_alu.sum','sm__inst_executed_pipe_xu.sum','sm__inst_executed_pipe_lsu.sum',
+ 'l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum','l1tex__t_sectors_pipe_lsu_mem_global_op_ld_lookup_miss.sum','l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum','l1tex__t_sectors_pipe_lsu_mem_local_op_ld.sum','l1tex__t_sectors_pipe_lsu_mem_local_op_st.sum','lts__t_sectors.sum','lts__t_sectors_srcunit_tex_op_read.sum','lts__t_sectors_srcunit_tex_op_read_lookup_miss.sum','l1tex__t_bytes.sum','lts__t_bytes.sum','l1tex__t_bytes.sum.per_second','lts__t_bytes.sum.per_second','sm__inst_executed_pipe_fma.sum','sm__inst_executed_pipe_alu.sum','sm__inst_executed_pipe_xu.sum','sm__inst_executed_pipe_lsu.sum',
  'smsp__inst_executed_pipe_fma.sum','smsp__inst_executed_pipe_alu.sum','smsp__inst_executed_pipe_xu.sum','smsp__inst_executed_pipe_lsu.sum','smsp__inst_executed_pipe_fmaheavy.sum','smsp__inst_executed_pipe_fp32.sum']
 rep = sys.argv[1]
 raw = subprocess.run(['ncu','-i',rep,'--page','raw','--csv'],capture_output=True,text=True).stdout
