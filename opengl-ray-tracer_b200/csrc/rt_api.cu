@@ -630,11 +630,6 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         const int items = F.nTilesMine * RT_WARPS_PER_TILE;
         const int needed = (items + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
         int grid = needed < c->gridBlocks[variant] ? needed : c->gridBlocks[variant];
-        {   // experiment knob: RT_ITEMS_PER_WARP=n launches a regular (non-persistent) grid
-            static const int ipw = std::getenv("RT_ITEMS_PER_WARP") ? std::atoi(std::getenv("RT_ITEMS_PER_WARP")) : 0;
-            F.itemsPerWarp = ipw;
-            if (ipw > 0) grid = (needed + ipw - 1) / ipw;
-        }
         const dim3 blk(RT_BLOCK_THREADS);
         float4* o4 = reinterpret_cast<float4*>(dev_rgba);
         unsigned long long* tl = c->tally.p;

@@ -91,7 +91,6 @@ struct FrameParams {
     const unsigned* heavyList; // items whose last cost exceeded RT_HEAVY_FACTOR x mean, claimed first
     const unsigned char* heavyFlag;
     unsigned* lptCtl;          // [0] number of heavy items, [1] claim counter of the heavy list
-    int   itemsPerWarp;        // 0: persistent warps (loop until the queue is empty); n: a warp retires after n items
     int   frameTarget;         // world > 1: colours go row-major into a full W*H frame (rank 0's, possibly peer memory)
 };
 

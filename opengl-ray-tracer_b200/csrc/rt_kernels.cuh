@@ -387,7 +387,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
     asm("mov.u32 %0, %%warpid;" : "=r"(warpSlot));
     const bool favoured = warpSlot < RT_HEAVY_SLOTS;
     bool heavyLeft = nHeavy > 0, lightLeft = true;
-    for (int round = 0; P.itemsPerWarp == 0 || round < P.itemsPerWarp; ++round) {
+    for (;;) {                                   // persistent warp: until both lists are empty
         int w = -1;
         int parts = 1, part = 0;                 // a heavy block may come as 2 or 4 row groups (see lpt_mark_kernel)
         if (heavyLeft && (favoured || !lightLeft)) {
@@ -406,7 +406,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
             if (lq >= nItems) lightLeft = false;
             else if (!(nHeavy > 0 && __ldg(P.heavyFlag + lq))) w = lq;
         }
-        if (w < 0) { if (!heavyLeft && !lightLeft) break; --round; continue; }
+        if (w < 0) { if (!heavyLeft && !lightLeft) break; continue; }
         const long long itemClk0 = P.itemCost ? clock64() : 0;
         const int t = P.tileBegin + w / RT_WARPS_PER_TILE, b = w % RT_WARPS_PER_TILE;
         const int tile = P.shardRank + t * P.shardWorld;
