@@ -354,8 +354,8 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
     """BASELINE.json configs[4]: the animated monkey scene, `frames` frames, per-frame CPU animation +
     BVH refit (reference behaviour: grow-only updateBVH, main.cpp:1068-1077) or full rebuild, per-shape
     rt_update_shapes + rt_update_nodes / full upload through pinned staging, render, D2H of the frame.
-    End-to-end wall-clock fps, host buffers double-buffered (rt_render_async) so that the host's
-    animation step of frame i+1 overlaps the GPU work of frame i."""
+    End-to-end wall-clock fps, host buffers double-buffered (rt_render_async / rt_wait_frames) so that the
+    host's animation step and the render of frame i+1 overlap the copy of frame i."""
     import ctypes as C
     out = {}
     L, Hl = rt.lib(), rt.hostlib()
@@ -374,7 +374,7 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
 
         def frame(i):
             if mode == 2:                         # K6 + K7 on the device copies: nothing to upload
-                tr.synchronize()
+                tr.wait_frames(1)
                 tr.animate(i / 60.0, 1.0 / 60.0)
                 tr.render_async(params, bufs[i & 1])
                 return
@@ -387,7 +387,7 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
             else:
                 idx = Hl.rh_indices(sc._h, C.byref(n)); ni = n.value
                 tr._chk(L.rt_upload_scene(tr._c, None, None, C.c_void_p(shp), ns, C.c_void_p(nod), nn, C.c_void_p(idx), ni))
-            tr.synchronize()                      # frame i-1 is complete (its buffer may be consumed)
+            tr.wait_frames(1)                     # frame i-2 is complete: its buffer (this one) may be consumed / reused
             tr.render_async(params, bufs[i & 1])
 
         for i in range(10):

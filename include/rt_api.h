@@ -127,8 +127,12 @@ int rt_render(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* h
 
 /* rt_render without the final wait: the frame lands in host_rgba (pinned memory for a truly
  * asynchronous copy) once rt_synchronize(ctx) returns.  Lets the host prepare the next frame's
- * scene update (main.cpp:438-457 animation step) while this one renders and copies. */
+ * scene update (main.cpp:438-457 animation step) while this one renders and copies.
+ * Frames are pipelined over two device images: the copy of frame i overlaps the render of frame i+1.
+ * rt_wait_frames(ctx, n) blocks until at most n of the issued frames are still in flight (n = 1: the
+ * older one is complete and its host buffer may be read / reused; n = 0: all of them). */
 int rt_render_async(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* host_hit_ids);
+int rt_wait_frames(rt_ctx* ctx, int max_in_flight);
 
 /* Same, but writes into caller-provided DEVICE buffers (e.g. torch tensors)
  * and returns without synchronising: work is ordered on rt_stream(ctx). */

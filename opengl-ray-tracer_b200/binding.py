@@ -56,7 +56,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -93,6 +93,7 @@ def lib():
     L.rt_frame_download.argtypes = [vp, vp]; L.rt_frame_download.restype = ip
     L.rt_host_frame_register.argtypes = [vp, vp, C.c_size_t, C.POINTER(vp)]; L.rt_host_frame_register.restype = ip
     L.rt_host_frame_unregister.argtypes = [vp, vp]; L.rt_host_frame_unregister.restype = ip
+    L.rt_wait_frames.argtypes = [vp, ip]; L.rt_wait_frames.restype = ip
     L.rt_anim_clear.argtypes = [vp]; L.rt_anim_clear.restype = ip
     L.rt_anim_bounce.argtypes = [vp, ip, C.c_float, C.c_float, C.c_float]; L.rt_anim_bounce.restype = ip
     L.rt_anim_rotate_z.argtypes = [vp, vp, ip, vp, C.c_float]; L.rt_anim_rotate_z.restype = ip
@@ -296,6 +297,9 @@ class RayTracer:
     def render_async(self, params, out, out_ids=None):
         """rt_render_async: returns at once; `out` (pinned) is complete after synchronize()."""
         self._chk(self._L.rt_render_async(self._c, C.byref(params), _ptr(out), _ptr(out_ids)))
+
+    def wait_frames(self, max_in_flight=1):
+        self._chk(self._L.rt_wait_frames(self._c, int(max_in_flight)))
 
     def render_device(self, params, dev_rgba_ptr=None, dev_ids_ptr=None):
         """Asynchronous render into device memory (pointers as ints, e.g. tensor.data_ptr())."""

@@ -117,6 +117,13 @@ struct rt_ctx {
 
     // output
     DevBuf<float4> image; DevBuf<int> ids;
+    // rt_render_async pipelines frames: two device images alternate, so that the D2H of frame i (copy stream)
+    // overlaps the render of frame i+1; evFrame[k] = the copy out of image k has finished
+    DevBuf<float4> image2; DevBuf<int> ids2;
+    cudaEvent_t evFrame[2] = {nullptr, nullptr};
+    bool framePending[2] = {false, false};
+    int imgPar = 0;                   // image the next pipelined frame renders into
+    float4* lastImage = nullptr;
     DevBuf<float4> frame;             // full W*H frame other ranks write into (rt_frame_export)
     float* frameTarget = nullptr;     // where this rank's tiles go row-major (local frame, peer mapping, or caller's)
     void* ipcOpened = nullptr;        // mapping obtained from cudaIpcOpenMemHandle
@@ -398,6 +405,7 @@ int rt_create(rt_ctx** out, int width, int height, int device, unsigned flags) {
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     for (auto& e : c->evBand) if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+    for (auto& e : c->evFrame) if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     *out = c;
     return RT_OK;
 }
@@ -424,6 +432,8 @@ void rt_destroy(rt_ctx* c) {
     c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
     c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
+    for (auto& e : c->evFrame) if (e) cudaEventDestroy(e);
+    c->image2.release(); c->ids2.release();
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
     if (!c->ownStream) c->ownStream = c->stream;      // rt_create failed half-way
@@ -501,10 +511,10 @@ int rt_set_shard(rt_ctx* c, int rank, int world) {
 int64_t rt_shard_pixels(const rt_ctx* c) { return c ? out_pixels(c) : 0; }
 
 static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count,
-                       float* host_rgba = nullptr, int32_t* host_ids = nullptr);
+                       float* host_rgba, int32_t* host_ids, bool pipeline);
 
 int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids) {
-    return render_impl(c, p, dev_rgba, dev_ids, false);
+    return render_impl(c, p, dev_rgba, dev_ids, false, nullptr, nullptr, false);
 }
 
 int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8], int32_t* host_cost) {
@@ -514,7 +524,7 @@ int rt_render_stats(rt_ctx* c, const rt_params* p, uint64_t out[8], int32_t* hos
     CU(c, cudaMemsetAsync(c->tally.p, 0, RT_NTALLY * sizeof(unsigned long long), c->stream));
     int32_t* dcost = nullptr;
     if (host_cost) { CU(c, c->ids.reserve((size_t)out_pixels(c))); dcost = c->ids.p; }
-    int rc = render_impl(c, p, nullptr, dcost, true);
+    int rc = render_impl(c, p, nullptr, dcost, true, nullptr, nullptr, false);
     if (rc != RT_OK) return rc;
     if (host_cost) CU(c, cudaMemcpyAsync(host_cost, dcost, (size_t)out_pixels(c) * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaMemcpyAsync(c->lastTally, c->tally.p, RT_NTALLY * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
@@ -541,7 +551,7 @@ int rt_walk_stats(rt_ctx* c, uint64_t out[8]) {
 // previous band's retire), and each finished band is copied to the host on a third stream while
 // the following bands render, so the D2H of the 16 B/pixel frame overlaps the kernel.
 static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count,
-                       float* host_rgba, int32_t* host_ids) {
+                       float* host_rgba, int32_t* host_ids, bool pipeline) {
     if (!c || !p) return RT_ERR_ARG;
     if (!c->haveScene || !c->haveCam || !c->haveLight) return fail(c, RT_ERR_STATE, "render before scene/camera/light upload");
     if (dev_ids && !count && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
@@ -551,9 +561,22 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     const int64_t px = out_pixels(c);
     // fused gather: no explicit output buffer, a frame target set, several ranks
     const bool useFrame = !dev_rgba && !host_rgba && !count && c->frameTarget;
-    if (!dev_rgba && !useFrame) { CU(c, c->image.reserve((size_t)px)); dev_rgba = reinterpret_cast<float*>(c->image.p); }
     const bool wantIds = (c->flags & RT_FLAG_HIT_IDS) != 0;
-    if (wantIds && !dev_ids) { CU(c, c->ids.reserve((size_t)px)); dev_ids = c->ids.p; }
+    const bool ownImage = !dev_rgba && !useFrame, ownIds = wantIds && !dev_ids;
+    pipeline = pipeline && ownImage && (host_rgba || host_ids) && !count;
+    const int par = pipeline ? c->imgPar : 0;
+    if (pipeline) c->imgPar ^= 1;
+    if (ownImage) {
+        DevBuf<float4>& img = par ? c->image2 : c->image;
+        CU(c, img.reserve((size_t)px)); dev_rgba = reinterpret_cast<float*>(img.p);
+        c->lastImage = img.p;
+    }
+    if (ownIds) { DevBuf<int>& idb = par ? c->ids2 : c->ids; CU(c, idb.reserve((size_t)px)); dev_ids = idb.p; }
+    if ((ownImage || ownIds) && c->framePending[par]) {
+        // an earlier pipelined frame's copy may still be reading this image: the kernels below wait for it
+        cudaStreamWaitEvent(c->stream, c->evFrame[par], 0);
+        if (!pipeline) c->framePending[par] = false;
+    }
 
     DeviceScene S;
     S.nodes = c->dNodesT.p; S.nodesB = c->nDfsB > 0 ? c->dNodesB.p : nullptr; S.nNodesB = c->nDfsB; S.q0 = c->q0.p; S.q1 = c->q1.p; S.q2 = c->q2.p; S.q3 = c->q3.p;
@@ -581,7 +604,9 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     // bands: whole tile rows (world == 1: a band is a contiguous block of image rows)
     const int rowTiles = c->shardWorld == 1 ? F.tilesX : 1;
     int nBands = 1;
-    if (toHost && !count) {
+    // a small pipelined frame is one launch (heavy-first order and split blocks need the whole frame; its copy
+    // overlaps the NEXT frame's render instead of this one's)
+    if (toHost && !count && !(pipeline && px <= (int64_t)1 << 21)) {
         const int rows = (tilesMine + rowTiles - 1) / rowTiles;
         nBands = rows / 16;                              // at least 16 tile rows (128 pixel rows) per band
         if (nBands > RT_MAX_BANDS) nBands = RT_MAX_BANDS;
@@ -662,8 +687,12 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     cudaEventRecord(c->ev[5], c->stream); c->timed[2] = true;
     if (toHost && !firstCopy) {
         cudaEventRecord(c->ev[7], c->copyStream); c->timed[3] = true;
-        cudaEventRecord(evCopied, c->copyStream);
-        cudaStreamWaitEvent(c->stream, evCopied, 0);      // everything is ordered on the context stream again
+        if (pipeline) {
+            cudaEventRecord(c->evFrame[par], c->copyStream); c->framePending[par] = true;
+        } else {
+            cudaEventRecord(evCopied, c->copyStream);
+            cudaStreamWaitEvent(c->stream, evCopied, 0);  // everything is ordered on the context stream again
+        }
     }
     CU(c, cudaGetLastError());
     return RT_OK;
@@ -672,7 +701,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
 int rt_render(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* host_hit_ids) {
     if (!c || !p) return RT_ERR_ARG;
     if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
-    int rc = render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids);
+    int rc = render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids, false);
     if (rc != RT_OK) return rc;
     CU(c, cudaStreamSynchronize(c->stream));
     return RT_OK;
@@ -681,7 +710,17 @@ int rt_render(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* host_hit
 int rt_render_async(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* host_hit_ids) {
     if (!c || !p) return RT_ERR_ARG;
     if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
-    return render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids);
+    return render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids, true);
+}
+
+int rt_wait_frames(rt_ctx* c, int max_in_flight) {
+    if (!c || max_in_flight < 0) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    // at most two frames are ever in flight (two device images); imgPar is the image of the OLDER one
+    const int older = c->imgPar, newer = c->imgPar ^ 1;
+    if (max_in_flight <= 1 && c->framePending[older]) { CU(c, cudaEventSynchronize(c->evFrame[older])); c->framePending[older] = false; }
+    if (max_in_flight == 0 && c->framePending[newer]) { CU(c, cudaEventSynchronize(c->evFrame[newer])); c->framePending[newer] = false; }
+    return RT_OK;
 }
 
 int rt_set_frame_target(rt_ctx* c, float* dev_frame) {
@@ -896,13 +935,18 @@ int rt_set_stream(rt_ctx* c, void* s) {
 int rt_synchronize(rt_ctx* c) {
     if (!c) return RT_ERR_ARG;
     CU(c, cudaStreamSynchronize(c->stream));
+    if (c->framePending[0] || c->framePending[1]) {       // pipelined frames finish on the copy stream
+        CU(c, cudaStreamSynchronize(c->copyStream));
+        c->framePending[0] = c->framePending[1] = false;
+    }
     return RT_OK;
 }
-float* rt_device_image(rt_ctx* c) { return c ? reinterpret_cast<float*>(c->image.p) : nullptr; }
+float* rt_device_image(rt_ctx* c) { return c ? reinterpret_cast<float*>(c->lastImage ? c->lastImage : c->image.p) : nullptr; }
 
 int rt_last_timings(rt_ctx* c, float out_ms[4]) {
     if (!c || !out_ms) return RT_ERR_ARG;
     CU(c, cudaStreamSynchronize(c->stream));
+    CU(c, cudaStreamSynchronize(c->copyStream));
     for (int i = 0; i < 4; ++i) {
         out_ms[i] = -1.0f;
         if (c->timed[i]) cudaEventElapsedTime(&out_ms[i], c->ev[2 * i], c->ev[2 * i + 1]);

@@ -387,7 +387,8 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
     asm("mov.u32 %0, %%warpid;" : "=r"(warpSlot));
     const bool favoured = warpSlot < RT_HEAVY_SLOTS;
     bool heavyLeft = nHeavy > 0, lightLeft = true;
-    for (;;) {                                   // persistent warp: until both lists are empty
+    while (heavyLeft || lightLeft) {             // persistent warp: until both lists are empty (this form of the loop
+                                                 // header matters: with for (;;) ptxas spills 154 instead of 54 bytes)
         int w = -1;
         int parts = 1, part = 0;                 // a heavy block may come as 2 or 4 row groups (see lpt_mark_kernel)
         if (heavyLeft && (favoured || !lightLeft)) {

@@ -357,6 +357,40 @@ def test_render_async_and_banded_copy(rt, oracle):
     tr.close()
 
 
+@pytest.mark.parametrize("W,H", [(400, 300), (2048, 1100)])
+def test_pipelined_async_frames(rt, W, H):
+    """rt_render_async pipelines frames over two device images (small frames: one launch with the heavy-first order;
+    large ones banded): with two host buffers and rt_wait_frames(1) every frame of an animated sequence arrives
+    complete and equal to a synchronous render of the same scene state."""
+    import torch
+    sc = rt.Scene("monkey", W, H)
+    p = rt.make_params(W, H)
+    a = rt.RayTracer(W, H, flags=0); b = rt.RayTracer(W, H, flags=0)
+    a.upload(sc); b.upload(sc)
+    an = sc.animated
+    lo, hi = int(an.min()), int(an.max()) + 1
+    bufs = [torch.empty((H * W, 4), dtype=torch.float32, pin_memory=True).numpy() for _ in range(2)]
+    expected = []
+    n = 7
+    for i in range(n):
+        sc.animate(i * 0.17, 0.17, mode=0)
+        for t in (a, b):
+            t.update_shapes(lo, sc.shapes[lo:hi]); t.update_nodes(sc.nodes)
+        expected.append(b.render(p, want_ids=False)[0].copy())
+        a.wait_frames(1)
+        if i >= 2:
+            assert np.array_equal(bufs[i & 1].view(np.uint32).reshape(H, W, 4), expected[i - 2].view(np.uint32)), "frame %d" % (i - 2)
+        bufs[i & 1][:] = -3.0
+        a.render_async(p, bufs[i & 1])
+    a.wait_frames(0)
+    for i in (n - 2, n - 1):
+        assert np.array_equal(bufs[i & 1].view(np.uint32).reshape(H, W, 4), expected[i].view(np.uint32)), "frame %d" % i
+    # a synchronous render after pipelined ones still works on the same context
+    r, _ = a.render(p, want_ids=False)
+    assert np.array_equal(r.view(np.uint32), expected[-1].view(np.uint32))
+    a.close(); b.close()
+
+
 def test_fused_gather_frame_target(rt):
     """Fused gather on one device: the contexts of `world` ranks store their tiles straight into one row-major
     frame (rt_set_frame_target; across processes the same pointer is a CUDA-IPC peer mapping) == the 1-GPU image."""
