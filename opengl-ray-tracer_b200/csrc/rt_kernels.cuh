@@ -276,7 +276,7 @@ __device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3
 // so that the walk is instantiated ONCE and both kinds of query share its code.
 template <bool MT, bool COUNT>
 __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, bool inside,
-                                              int& idOut, Tally& tl) {
+                                              int& idOut, Tally& tl, bool paired) {
     const bool bf = S.boxesFinite != 0;
     // Live state across the walks is kept small (occupancy): the view direction, the hit point, the hit
     // shape's index, and the two colour accumulators.  Normal and material are re-read after the shadow walk.
@@ -295,10 +295,18 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
         vd = q.r.d;
     }
 
-    for (int step = 0; step < 2 * P.maxBounces; ++step) {
+    // PAIRED mode (a row group of a split heavy block: at most 16 pixel lanes, lane ^ 16 is idle): the shadow
+    // query of bounce b and the closest-hit query of bounce b+1 do not depend on each other — the reflected ray
+    // follows from the hit and the incoming direction alone (:495-497) — so the idle partner lane walks the
+    // reflection while the pixel's own lane walks the shadow ray: the pixel's chain of dependent walks shrinks
+    // from 2 * maxBounces to maxBounces + 1.  Same queries, same arithmetic, same pixel.
+    paired = paired && P.useBVH && !COUNT;
+    const int nSteps = paired ? P.maxBounces + 1 : 2 * P.maxBounces;
+    for (int step = 0; step < nSteps; ++step) {
         if (!__any_sync(RT_FULL, alive)) break;
-        const bool shadowStep = (step & 1) != 0;
+        const bool shadowStep = paired ? step > 0 : (step & 1) != 0;
         float lightDist = 0.f;
+        bool helper = false;                               // this lane walks its partner's reflected ray in this step
         if (!shadowStep) {
             q.best = 1e20f;                                // q.r is the current ray
         } else {
@@ -308,10 +316,27 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
             q.r = make_ray(hp + nrm * (P.useBVH ? 1e-3f : 1e-5f), normalize3(lpos - hp), bf, S.omax);
             // dist < 1e20 && dist < lightDist  ==  dist < min; a NaN lightDist can never be beaten
             q.best = lightDist < 1e20f ? lightDist : (lightDist >= 1e20f ? 1e20f : -1.0f);
+            if (paired) {
+                bool cont = false;
+                V3 ro = mk(0.f, 0.f, 0.f), rd = ro;
+                if (alive && step < P.maxBounces) {         // bounce step-1 continues iff specular > 0 (:495) and a bounce is left
+                    cont = __ldg(&S.shapes[shape].material.specularStrength) > 0.0f;
+                    ro = hp + nrm * 1e-3f; rd = reflect3(vd, nrm);
+                }
+                const bool pc = __shfl_xor_sync(RT_FULL, cont ? 1 : 0, 16) != 0;
+                const V3 po = mk(__shfl_xor_sync(RT_FULL, ro.x, 16), __shfl_xor_sync(RT_FULL, ro.y, 16), __shfl_xor_sync(RT_FULL, ro.z, 16));
+                const V3 pd = mk(__shfl_xor_sync(RT_FULL, rd.x, 16), __shfl_xor_sync(RT_FULL, rd.y, 16), __shfl_xor_sync(RT_FULL, rd.z, 16));
+                if (!alive && pc) { helper = true; q.r = make_ray(po, pd, bf, S.omax); q.best = 1e20f; }
+            }
         }
         q.slot = -1; q.p = mk(0.f, 0.f, 0.f);
+        int nextSlot = -1; V3 nextP = mk(0.f, 0.f, 0.f);   // paired: the partner's closest hit of the reflected ray
         if (P.useBVH) {
-            walk<MT, COUNT>(S, q, alive, shadowStep, tl, step < 2 ? 8 : 12);
+            walk<MT, COUNT>(S, q, alive || helper, shadowStep && !helper, tl, step < 2 ? 8 : 12);
+            if (paired && shadowStep) {
+                nextSlot = __shfl_xor_sync(RT_FULL, q.slot, 16);
+                nextP = mk(__shfl_xor_sync(RT_FULL, q.p.x, 16), __shfl_xor_sync(RT_FULL, q.p.y, 16), __shfl_xor_sync(RT_FULL, q.p.z, 16));
+            }
         } else if (alive) {
             if (!shadowStep) { Hit h; scan_closest<MT>(S, q.r, h); q.slot = h.slot; q.p = h.p; RT_TALLY(5, S.nShapes); }
             else if (scan_any<MT>(S, q.r, lightDist)) q.slot = 0;
@@ -349,6 +374,16 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
                 acc = acc + (mw * m.color) * pc;
             } else {
                 att = att * m.specular;
+            }
+            if (paired) {                                  // the reflected ray's closest hit is already here (:452-464)
+                if (step >= P.maxBounces) { alive = false; continue; }   // bounces exhausted: no background (:450)
+                shape = nextSlot < 0 ? -1 : __ldg(S.pshape + nextSlot);
+                if (shape < 0) {
+                    const float a = (float)y / P.resH;
+                    const V3 bg = mk(mix1(0.05f, 0.5f, a), mix1(0.07f, 0.7f, a), mix1(0.1f, 1.0f, a));
+                    acc = acc + att * bg; alive = false; continue;
+                }
+                hp = nextP;
             }
         }
     }
@@ -423,7 +458,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         long long clk0 = 0;
         unsigned long long it0[4] = {0, 0, 0, 0};
         if (COUNT) { cost0 = tl.v[4] + tl.v[5]; clk0 = clock64(); it0[0] = tl.v[8]; it0[1] = tl.v[9]; it0[2] = tl.v[12]; it0[3] = tl.v[13]; }
-        c = shade_pixel<MT, COUNT>(S, P, x, y, inside, id, tl);
+        c = shade_pixel<MT, COUNT>(S, P, x, y, inside, id, tl, parts >= 2);
         if (COUNT && P.writeIds == 2) id = (int)(tl.v[4] + tl.v[5] - cost0);   // diagnostic: per-pixel work AOV
         if (COUNT) {
             const unsigned long long dt = (unsigned long long)(clock64() - clk0);

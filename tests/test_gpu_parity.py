@@ -391,6 +391,30 @@ def test_pipelined_async_frames(rt, W, H):
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("mt,fresnel,bounces", [(False, False, 3), (True, True, 3), (False, True, 6)])
+def test_scheduled_frames_identical(rt, mt, fresnel, bounces):
+    """From the second frame on a context orders its blocks by last frame's costs, splits the heaviest into lane groups
+    and lets the idle partner lanes of a group walk the reflected ray beside the shadow ray (paired mode): every frame
+    must stay bit-identical to the first one and to a context with RT_FLAG_NO_HEAVY_FIRST."""
+    import torch
+    W, H = 800, 600
+    sc = rt.Scene("car", W, H)
+    p = rt.make_params(W, H, maxBounces=bounces, useFresnel=fresnel, useMollerTrumbore=mt)
+    a = rt.RayTracer(W, H, flags=rt.RT_FLAG_HIT_IDS)
+    b = rt.RayTracer(W, H, flags=rt.RT_FLAG_HIT_IDS | rt.RT_FLAG_NO_HEAVY_FIRST)
+    a.upload(sc); b.upload(sc)
+    dev = torch.empty((H, W, 4), dtype=torch.float32, device="cuda")
+    ids = torch.empty((H, W), dtype=torch.int32, device="cuda")
+    b.render_device(p, dev.data_ptr(), ids.data_ptr()); b.synchronize()
+    want, want_ids = dev.cpu().numpy().copy(), ids.cpu().numpy().copy()
+    for frame in range(5):
+        dev.fill_(-1.0); ids.fill_(-5)
+        a.render_device(p, dev.data_ptr(), ids.data_ptr()); a.synchronize()
+        assert np.array_equal(ids.cpu().numpy(), want_ids), "ids, frame %d" % frame
+        assert np.array_equal(dev.cpu().numpy().view(np.uint32), want.view(np.uint32)), "frame %d" % frame
+    a.close(); b.close()
+
+
 def test_fused_gather_frame_target(rt):
     """Fused gather on one device: the contexts of `world` ranks store their tiles straight into one row-major
     frame (rt_set_frame_target; across processes the same pointer is a CUDA-IPC peer mapping) == the 1-GPU image."""
