@@ -146,6 +146,50 @@ def test_sharded_tiles_reassemble(rt):
     tr.close()
 
 
+def test_sharded_scheduled_frames(rt):
+    """The compact tile-major shard path with the heavy-first order, split blocks and paired walks in effect (one
+    context per rank, several frames each so that the previous frame's costs exist): every frame untiles to the
+    1-GPU image, ids included."""
+    import torch
+    W, H = 640, 360
+    sc = rt.Scene("car", W, H)
+    p = rt.make_params(W, H)
+    one = rt.RayTracer(W, H)
+    one.upload(sc)
+    full, full_ids = one.render(p)
+    world = 3
+    ranks = []
+    for r in range(world):
+        t = rt.RayTracer(W, H)
+        t.upload(sc); t.set_shard(r, world)
+        ranks.append(t)
+    px = ranks[0].shard_pixels()
+    shards = torch.zeros((world, px, 4), dtype=torch.float32, device="cuda")
+    sid = torch.zeros((world, px), dtype=torch.int32, device="cuda")
+    out = torch.empty((H, W, 4), dtype=torch.float32, device="cuda")
+    for frame in range(4):
+        shards.fill_(-2.0)
+        for r, t in enumerate(ranks):
+            t.render_device(p, shards[r].data_ptr(), sid[r].data_ptr())
+        for t in ranks:
+            t.synchronize()
+        one.untile(shards.data_ptr(), world, out.data_ptr())
+        one.synchronize()
+        assert np.array_equal(out.cpu().numpy().view(np.uint32), full.view(np.uint32)), "frame %d" % frame
+    # ids of rank 0's shard against the full id map (tile k of the shard = tile k*world of the frame)
+    ids0 = sid[0].cpu().numpy()
+    tx = (W + 31) // 32
+    for k in range(0, px // 256, 7):
+        tile = k * world
+        x0, y0 = (tile % tx) * 32, (tile // tx) * 8
+        if y0 + 8 > H or x0 + 32 > W:
+            continue
+        assert np.array_equal(ids0[k * 256:(k + 1) * 256].reshape(8, 32), full_ids[y0:y0 + 8, x0:x0 + 32]), "tile %d" % tile
+    for t in ranks:
+        t.close()
+    one.close()
+
+
 def test_present_matches_oracle(rt, oracle):
     import torch
     W, H = 200, 150
