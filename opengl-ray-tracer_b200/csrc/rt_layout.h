@@ -50,8 +50,12 @@ RTL_HD inline float  f_up(float x) {        // nextafter(x, +inf) for finite x
 }
 RTL_HD inline float  f_down(float x) { return -f_up(-x); }
 
+#ifndef RT_FAT_LEAF
 #define RT_FAT_LEAF      8      // reference leaves with more shapes than this get a sub-tree
+#endif
+#ifndef RT_SUB_LEAF
 #define RT_SUB_LEAF      4      // sub-tree leaves hold at most this many primitives
+#endif
 #define RTL_COUNT_MASK   0x0fffffff
 #define RTL_KIND_SHIFT   28
 #define RTL_SUB_BIT      (1 << 30)   // leaf count word: box is one of ours (conservative test allowed)
