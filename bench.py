@@ -197,7 +197,7 @@ def run_reference_arm(args):
     kind = "reference" if use_ref else "port"
     sample = "rows y%%%d==%d (%d of %d rows, %d rays/step) of the %s %dx%d frame" % (step, phase, rows, H, rays, args.scene, W, H)
     print(json.dumps({
-        "impl": "reference", "metric": "Mrays/s (car scene)", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": "Mrays/s (%s scene)" % args.scene, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, sample=sample),
