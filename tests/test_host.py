@@ -84,3 +84,46 @@ def test_camera_basis_is_orthonormal(rt):
         assert abs(np.linalg.norm(v) - 1) < 1e-6
     assert abs(F @ U) < 1e-6 and abs(F @ R) < 1e-6 and abs(U @ R) < 1e-6
     assert cam["fov"] == 60 and abs(cam["aspectRatio"] - 800 / 600) < 1e-6
+
+
+def test_animation_list_reproduces_the_host_animation(rt):
+    """Scene.animations() (what rt_anim_bounce / rt_anim_rotate_z are fed) carries the parameters of the host's own
+    animation step: applying the reference formulas (main.cpp:1079-1109) to them with libm's sinf / cosf and fp32
+    arithmetic gives the animated shapes of Scene.animate bit for bit — the arithmetic K6 performs on the device."""
+    import ctypes as C
+    m = C.CDLL("libm.so.6")
+    m.sinf.restype = C.c_float; m.sinf.argtypes = [C.c_float]
+    m.cosf.restype = C.c_float; m.cosf.argtypes = [C.c_float]
+    f32 = np.float32
+    # bouncing spheres
+    sc = rt.Scene("monkey", 200, 150)
+    an = sc.animations()
+    assert sorted(int(i[0]) for _, i, _ in an) == sorted(int(x) for x in sc.animated)
+    t, dt = f32(0.7), f32(1.0 / 60.0)
+    sc.animate(float(t), float(dt), mode=0)
+    for kind, idx, p in an:
+        assert kind == 0
+        want = f32(p[0]) + f32(p[1]) * f32(m.sinf(f32(p[2]) * t))
+        got = sc.shapes["sphereCenter"][int(idx[0])][1]
+        assert f32(want).tobytes() == f32(got).tobytes()
+    # rotating wheels (vertices only: the planes stay stale, as upstream)
+    sc = rt.Scene("car", 200, 150)
+    before = sc.shapes.copy()
+    an = sc.animations()
+    assert sorted(int(x) for _, i, _ in an for x in i) == sorted(int(x) for x in sc.animated)
+    sc.animate(0.3, 0.3, mode=0)
+    after = sc.shapes
+    for kind, idx, p in an:
+        assert kind == 1
+        ang = f32(p[3]) * f32(0.3)
+        cs, sn = f32(m.cosf(ang)), f32(m.sinf(ang))
+        cx, cy = f32(p[0]), f32(p[1])
+        for key in ("triP1", "triP2", "triP3"):
+            v = before[key][idx].astype(f32)
+            x, y = v[:, 0] - cx, v[:, 1] - cy
+            nx = (cs * x - sn * y) + cx
+            ny = (sn * x + cs * y) + cy
+            assert nx.astype(f32).tobytes() == after[key][idx][:, 0].astype(f32).tobytes()
+            assert ny.astype(f32).tobytes() == after[key][idx][:, 1].astype(f32).tobytes()
+            assert np.array_equal(v[:, 2], after[key][idx][:, 2])
+        assert np.array_equal(before["planeNormal"][idx], after["planeNormal"][idx])
