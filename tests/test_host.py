@@ -127,3 +127,41 @@ def test_animation_list_reproduces_the_host_animation(rt):
             assert ny.astype(f32).tobytes() == after[key][idx][:, 1].astype(f32).tobytes()
             assert np.array_equal(v[:, 2], after[key][idx][:, 2])
         assert np.array_equal(before["planeNormal"][idx], after["planeNormal"][idx])
+
+
+@pytest.mark.parametrize("name", ["monkey", "car", "toy"])
+def test_leaf_growth_plus_child_union_equals_updateBVH(rt, name):
+    """K7's rule (grow every leaf by its animated shapes, then make every inner node contain its children) gives the
+    node array of the reference's updateBVH (main.cpp:1068-1077), which grows EVERY node by the animated shapes it
+    holds — true for trees whose parents contain their children, which the reference builder's do."""
+    f32 = np.float32
+    sc = rt.Scene(name, 200, 150)
+    nodes0 = sc.nodes.copy()
+    idx = sc.indices
+    animated = set(int(x) for x in sc.animated)
+    for frame in range(1, 4):
+        sc.animate(frame * 0.4, 0.4, mode=0)
+        shapes, want = sc.shapes, sc.nodes
+        mn = nodes0["boundsMin"].astype(f32).copy(); mx = nodes0["boundsMax"].astype(f32).copy()
+        for n in range(len(nodes0)):                               # post-order array: children come before parents
+            if nodes0["leftChild"][n] == -1:
+                s0, c = int(nodes0["startShapeIdx"][n]), int(nodes0["numShapes"][n])
+                for s in idx[s0:s0 + c]:
+                    if int(s) not in animated:
+                        continue
+                    sh = shapes[int(s)]
+                    if sh["type"] == 0:
+                        r = f32(sh["sphereRadius"]); ctr = sh["sphereCenter"].astype(f32)
+                        pts = [ctr + r, ctr - r]
+                    elif sh["type"] == 3:
+                        pts = [sh["triP1"].astype(f32), sh["triP2"].astype(f32), sh["triP3"].astype(f32)]
+                    else:
+                        pts = []
+                    for p in pts:
+                        mn[n] = np.minimum(mn[n], p); mx[n] = np.maximum(mx[n], p)
+            else:
+                for ch in (int(nodes0["leftChild"][n]), int(nodes0["rightChild"][n])):
+                    mn[n] = np.minimum(mn[n], mn[ch]); mx[n] = np.maximum(mx[n], mx[ch])
+        assert mn.tobytes() == want["boundsMin"].astype(f32).tobytes(), "frame %d" % frame
+        assert mx.tobytes() == want["boundsMax"].astype(f32).tobytes(), "frame %d" % frame
+        nodes0 = want.copy()
