@@ -1,0 +1,473 @@
+// rt_build.cuh — K8: the reference's BVH builder on the device ("rebuild").
+//
+// Upstream builds its tree on the host (buildBVH / split, src/main.cpp:1111-1193): a top-down midpoint
+// split of the longest box axis, stable in the order of the shape list, stopped by a depth budget or as
+// soon as one side of a split is empty; serializeBVH (:955-979) then numbers the nodes in the order the
+// recursion pushed them (both sub-trees first, then the left child, then the right child, the root last)
+// and concatenates the leaves' shape lists into bvhIndices.  A DIFFERENT tree would change the visit
+// order of the shader's traversal and with it which of two equally distant shapes wins, so this builder
+// does not invent a new tree: it emits the reference's FlatNode[] and bvhIndices[] BYTE FOR BYTE, level
+// by level instead of recursively:
+//
+//   per level   classify  every shape of a pending node: centre[axis] < splitPos (the host's fp32 operations)
+//               scan      exclusive prefix sum of the "left" flags over the whole position array
+//               heads     the first position of each pending node decides (both sides non-empty, depth left)
+//                         and allocates the two children
+//               scatter   stable partition inside each node's segment; every shape folds its points into
+//                         its child's box with 64-bit atomicMin / atomicMax on (ordered value, sequence) keys:
+//                         min / max are exact and the key's low word keeps "first in list order wins among
+//                         equal values", i.e. the sign of a zero the host's `x < mn ? x : mn` would keep
+//               boxes     the keys become floats
+//   then        desc      descendants per node, leaves upwards (second arrival at a parent adds its children)
+//               number    the reference's node index and startShapeIdx of every node from the sums along
+//                         its path to the root
+//               emit      FlatNode[] and bvhIndices[]
+//
+// No host round trip inside the level loop: every launch covers all n positions, a level at which nothing
+// is pending exits at once.  Everything that decides a byte of the output lives in the RT_DEV functions
+// below; tests/emu/build_emu.cpp compiles exactly those with g++ and tests/test_build_emu.py compares
+// their output with the host builder's on the CPU.  The __global__ wrappers add only indexing, the block
+// scan and the warp-aggregated form of the box atomics.
+#pragma once
+#include "rt_device.cuh"
+
+namespace rt {
+namespace bld {
+
+typedef unsigned long long u64;
+
+#define RT_BLD_PENDING (-2)
+#define RT_BLD_LEAF (-1)
+
+#ifdef __CUDACC__
+RT_DEV void amin64(u64* p, u64 v) { atomicMin(p, v); }
+RT_DEV void amax64(u64* p, u64 v) { atomicMax(p, v); }
+RT_DEV int  aadd(int* p, int v) { return atomicAdd(p, v); }
+RT_DEV unsigned aaddu(unsigned* p, unsigned v) { return atomicAdd(p, v); }
+RT_DEV void fence() { __threadfence(); }
+RT_DEV int  ld_int(const int* p) { return __ldcg(p); }
+RT_DEV unsigned f2u(float f) { return __float_as_uint(f); }
+RT_DEV float u2f(unsigned u) { return __uint_as_float(u); }
+#else
+// host emulation (tests only): one thread at a time
+inline void amin64(u64* p, u64 v) { if (v < *p) *p = v; }
+inline void amax64(u64* p, u64 v) { if (v > *p) *p = v; }
+inline int  aadd(int* p, int v) { int o = *p; *p += v; return o; }
+inline unsigned aaddu(unsigned* p, unsigned v) { unsigned o = *p; *p += v; return o; }
+inline void fence() {}
+inline int  ld_int(const int* p) { return *p; }
+inline unsigned f2u(float f) { unsigned u; memcpy(&u, &f, 4); return u; }
+inline float u2f(unsigned u) { float f; memcpy(&f, &u, 4); return f; }
+#endif
+
+// Build-time node table, indexed by build id: root = 0, the children of one node are (id, id + 1).
+struct Nodes {
+    int* start;        // first position of the node's segment in the position array
+    int* count;        // shapes in the segment (= numShapes of the flat node, inner nodes too)
+    int* left;         // RT_BLD_PENDING, RT_BLD_LEAF or the build id of the left child
+    int* parent;       // build id, -1 at the root
+    int* depth;        // depth budget left (split's `depth` argument)
+    u64* key;          // 6 per node: min x y z, max x y z as (ordered value << 32 | sequence)
+    float* box;        // 6 per node
+    int* desc;         // number of descendants
+    unsigned* arrived; // counters of the upward pass
+    int* idx;          // index in the reference's node array
+    int* first;        // startShapeIdx
+};
+
+// Control words on the device.
+struct Ctl {
+    int nNodes;        // build ids handed out so far
+    int parity;        // which of the two position arrays holds the final order
+    int active[66];    // active[L]: some node is pending at level L
+};
+
+// ---- ordered keys -------------------------------------------------------------------------------------
+RT_DEV unsigned ord32(float v) {              // monotone map of the non-NaN floats onto unsigned, -0 and +0 together
+    unsigned u = f2u(v);
+    if ((u << 1) == 0u) u = 0u;
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+RT_DEV float unord32(unsigned hi, unsigned neg) {
+    unsigned u = (hi & 0x80000000u) ? (hi ^ 0x80000000u) : ~hi;
+    if (u == 0u && neg) u = 0x80000000u;
+    return u2f(u);
+}
+RT_DEV u64 key_min(float v, unsigned seq) { return ((u64)ord32(v) << 32) | (u64)((seq << 1) | (f2u(v) >> 31)); }
+RT_DEV u64 key_max(float v, unsigned seq) { return ((u64)ord32(v) << 32) | (u64)(((0x7fffffffu - seq) << 1) | (f2u(v) >> 31)); }
+#define RT_BLD_KEY_MIN_ID 0xff800000ffffffffull   /* +inf, last sequence */
+#define RT_BLD_KEY_MAX_ID 0x007fffff00000000ull   /* -inf */
+RT_DEV float key_value(u64 k) { return unord32((unsigned)(k >> 32), (unsigned)k & 1u); }
+
+// ---- the shape side of BoundingBox::growToInclude and of split's centre --------------------------------
+// The points a shape grows a box by, in the order the host grows them (BoundingBox.hpp:60-95): spheres
+// centre + r then centre - r, walls start then the opposite corner (wall.hpp:16-31), triangles their
+// vertices unless an x is not finite; infinite planes (and unknown types) none.
+RT_DEV V3 wall_end(const rt_flat_shape* __restrict__ s) {
+    const V3 n = mk(s->planeNormal), st = mk(s->wallStart);
+    V3 t1;
+    if (fabsf(n.x) > fabsf(n.y)) t1 = normalize3(mk(-n.z, 0.f, n.x));
+    else t1 = normalize3(mk(0.f, -n.z, n.y));
+    const V3 t2 = normalize3(cross3(n, t1));
+    return (st + (s->wallWidth * t1)) + (s->wallHeight * t2);
+}
+RT_DEV int shape_points(const rt_flat_shape* __restrict__ s, V3 pt[3]) {
+    const int type = s->type;
+    if (type == RT_SHAPE_SPHERE) {
+        const float r = s->sphereRadius;
+        pt[0] = mk(s->sphereCenter[0] + r, s->sphereCenter[1] + r, s->sphereCenter[2] + r);
+        pt[1] = mk(s->sphereCenter[0] - r, s->sphereCenter[1] - r, s->sphereCenter[2] - r);
+        return 2;
+    }
+    if (type == RT_SHAPE_WALL) { pt[0] = mk(s->wallStart); pt[1] = wall_end(s); return 2; }
+    if (type == RT_SHAPE_TRIANGLE) {
+        if (!(isfinite(s->triP1[0]) && isfinite(s->triP2[0]) && isfinite(s->triP3[0]))) return 0;
+        pt[0] = mk(s->triP1); pt[1] = mk(s->triP2); pt[2] = mk(s->triP3);
+        return 3;
+    }
+    return 0;
+}
+RT_DEV float comp(V3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; }
+
+// The six keys of the shape at position `pos` (sequence = pos * 4 + point number); identity where it has none.
+RT_DEV void shape_keys(const rt_flat_shape* __restrict__ s, unsigned pos, u64 k[6]) {
+    V3 pt[3];
+    const int np = shape_points(s, pt);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { k[a] = RT_BLD_KEY_MIN_ID; k[3 + a] = RT_BLD_KEY_MAX_ID; }
+    for (int j = 0; j < np; ++j) {
+        const unsigned seq = pos * 4u + (unsigned)j;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float v = comp(pt[j], a);
+            if (v != v) continue;                       // `NaN < mn` and `mx < NaN` are false: the host keeps the old bound
+            const u64 lo = key_min(v, seq), hi = key_max(v, seq);
+            if (lo < k[a]) k[a] = lo;
+            if (hi > k[3 + a]) k[3 + a] = hi;
+        }
+    }
+}
+
+// split's centre test (main.cpp:1119-1142): does the shape go to the left child of a node with this box?
+RT_DEV bool goes_left(const rt_flat_shape* __restrict__ s, const float* __restrict__ box) {
+    const float sx = box[3] - box[0], sy = box[4] - box[1], sz = box[5] - box[2];
+    const int axis = sx > (sy < sz ? sz : sy) ? 0 : sy > sz ? 1 : 2;
+    const float pos = (box[axis] + box[3 + axis]) * 0.5f;
+    float c = 0.f;                                       // upstream leaves a plane's centre uninitialised; 0 as in rt_host.cpp
+    const int type = s->type;
+    if (type == RT_SHAPE_SPHERE) c = s->sphereCenter[axis];
+    else if (type == RT_SHAPE_WALL) c = comp((mk(s->wallStart) + wall_end(s)) * 0.5f, axis);
+    else if (type == RT_SHAPE_TRIANGLE) c = ((s->triP1[axis] + s->triP2[axis]) + s->triP3[axis]) / 3.0f;
+    return c < pos;
+}
+
+// ---- per-thread bodies of the level loop -------------------------------------------------------------------
+RT_DEV void setup_root(const Nodes& N, Ctl* ctl, int n, int maxDepth) {
+    N.start[0] = 0; N.count[0] = n; N.parent[0] = -1; N.depth[0] = maxDepth;
+    N.left[0] = maxDepth > 0 ? RT_BLD_PENDING : RT_BLD_LEAF;
+    for (int a = 0; a < 3; ++a) { N.key[a] = RT_BLD_KEY_MIN_ID; N.key[3 + a] = RT_BLD_KEY_MAX_ID; }
+    ctl->nNodes = 1; ctl->parity = 0;
+    for (int l = 0; l < 66; ++l) ctl->active[l] = 0;
+    ctl->active[0] = maxDepth > 0 ? 1 : 0;
+}
+
+// position p of level 0: the identity order, everything in the root; returns the shape's keys
+RT_DEV void init_position(int p, int* __restrict__ ord, int* __restrict__ pnode) { ord[p] = p; pnode[p] = 0; }
+
+RT_DEV int classify(int p, const rt_flat_shape* __restrict__ shapes, const int* __restrict__ ord,
+                    const int* __restrict__ pnode, const Nodes& N) {
+    const int node = pnode[p];
+    if (N.left[node] != RT_BLD_PENDING) return 0;
+    return goes_left(shapes + ord[p], N.box + 6 * (size_t)node) ? 1 : 0;
+}
+
+// scanL: exclusive prefix sums of the flags, n + 1 entries
+RT_DEV void head(int p, int level, const int* __restrict__ pnode, const int* __restrict__ scanL, const Nodes& N, Ctl* ctl) {
+    const int node = pnode[p];
+    if (N.left[node] != RT_BLD_PENDING || p != N.start[node]) return;
+    const int cnt = N.count[node];
+    const int nL = scanL[p + cnt] - scanL[p];
+    if (nL == 0 || nL == cnt) { N.left[node] = RT_BLD_LEAF; return; }      // "no reason to split anymore" (:1156-1161)
+    const int l = aadd(&ctl->nNodes, 2);
+    const int d = N.depth[node] - 1;
+    for (int s = 0; s < 2; ++s) {
+        const int id = l + s;
+        N.start[id] = s == 0 ? p : p + nL;
+        N.count[id] = s == 0 ? nL : cnt - nL;
+        N.parent[id] = node;
+        N.depth[id] = d;
+        N.left[id] = d > 0 ? RT_BLD_PENDING : RT_BLD_LEAF;                 // split(child, 0) makes a leaf (:1113-1118)
+        for (int a = 0; a < 3; ++a) { N.key[6 * (size_t)id + a] = RT_BLD_KEY_MIN_ID; N.key[6 * (size_t)id + 3 + a] = RT_BLD_KEY_MAX_ID; }
+    }
+    N.left[node] = l;
+    if (d > 0) ctl->active[level + 1] = 1;
+}
+
+// Where position p goes and which node it then belongs to; child < 0: it stays where it is.
+RT_DEV void scatter_target(int p, int flag, const int* __restrict__ pnode, const int* __restrict__ scanL, const Nodes& N,
+                           int& newPos, int& newNode, bool& moved) {
+    const int node = pnode[p];
+    const int l = N.left[node];
+    if (l < 0) { newPos = p; newNode = node; moved = false; return; }
+    const int st = N.start[node];
+    const int nL = scanL[st + N.count[node]] - scanL[st];
+    const int rankL = scanL[p] - scanL[st];
+    if (flag) { newPos = st + rankL; newNode = l; }
+    else { newPos = st + nL + ((p - st) - rankL); newNode = l + 1; }
+    moved = true;
+}
+
+RT_DEV void fold_keys(u64* __restrict__ nodeKeys, const u64 k[6]) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        if (k[a] != RT_BLD_KEY_MIN_ID) amin64(nodeKeys + a, k[a]);
+        if (k[3 + a] != RT_BLD_KEY_MAX_ID) amax64(nodeKeys + 3 + a, k[3 + a]);
+    }
+}
+
+RT_DEV void box_from_keys(int p, const int* __restrict__ pnode, const Nodes& N) {
+    const int node = pnode[p];
+    if (p != N.start[node]) return;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) N.box[6 * (size_t)node + a] = key_value(N.key[6 * (size_t)node + a]);
+}
+
+// ---- numbering ---------------------------------------------------------------------------------------------
+RT_DEV void count_descendants(int id, const Nodes& N) {
+    if (N.left[id] >= 0) return;                  // leaves start
+    N.desc[id] = 0;
+    for (int j = N.parent[id]; j >= 0; j = N.parent[j]) {
+        fence();
+        if (aaddu(N.arrived + j, 1u) == 0u) return;
+        fence();
+        const int l = N.left[j];
+        N.desc[j] = ld_int(N.desc + l) + ld_int(N.desc + l + 1) + 2;
+    }
+}
+
+RT_DEV int leaf_shapes_below(const Nodes& N, int id) { return N.left[id] >= 0 ? N.count[id] : 0; }   // indices emitted by id's descendants
+
+// The reference pushes, for a node P whose descendants start at node index b and whose indices start at e:
+// [descendants of L] [descendants of R] L R.  Hence for a child: index and first bvhIndices entry follow from
+// b(P), e(P), and b / e of a node follow from its ancestors: a right child starts after its left sibling's block.
+RT_DEV void number_node(int id, const Nodes& N) {
+    if (id == 0) { N.idx[0] = N.desc[0]; N.first[0] = leaf_shapes_below(N, 0); return; }
+    const int par = N.parent[id];
+    int b = 0, e = 0;
+    for (int a = par; a != 0; a = N.parent[a]) {
+        const int pa = N.parent[a], sib = N.left[pa];
+        if (a != sib) { b += N.desc[sib]; e += leaf_shapes_below(N, sib); }
+    }
+    const int l = N.left[par], r = l + 1;
+    const int idxL = b + N.desc[l] + N.desc[r];
+    const int firstL = e + leaf_shapes_below(N, l) + leaf_shapes_below(N, r);
+    if (id == l) { N.idx[id] = idxL; N.first[id] = firstL; }
+    else { N.idx[id] = idxL + 1; N.first[id] = firstL + (N.left[l] >= 0 ? 0 : N.count[l]); }
+}
+
+RT_DEV void emit_node(int id, const Nodes& N, const int* __restrict__ ord, rt_flat_node* __restrict__ out, int32_t* __restrict__ indices) {
+    rt_flat_node f;
+    const float* b = N.box + 6 * (size_t)id;
+    f.boundsMin[0] = b[0]; f.boundsMin[1] = b[1]; f.boundsMin[2] = b[2]; f.padding1 = 0.f;
+    f.boundsMax[0] = b[3]; f.boundsMax[1] = b[4]; f.boundsMax[2] = b[5]; f.padding2 = 0.f;
+    const int l = N.left[id];
+    f.leftChild = l >= 0 ? N.idx[l] : -1;
+    f.rightChild = l >= 0 ? N.idx[l + 1] : -1;
+    f.startShapeIdx = N.first[id];
+    f.numShapes = N.count[id];
+    out[N.idx[id]] = f;
+    if (l < 0) {
+        const int st = N.start[id], cnt = N.count[id], o = N.first[id];
+        for (int k = 0; k < cnt; ++k) indices[o + k] = ord[st + k];
+    }
+}
+
+}  // namespace bld
+
+#ifdef __CUDACC__
+// ---- kernels ------------------------------------------------------------------------------------------------
+#define RT_BLD_THREADS 256
+
+struct BuildBufs {
+    bld::Nodes N;
+    bld::Ctl* ctl;
+    int* ord[2];
+    int* pnode[2];
+    unsigned char* flag;
+    int* scanL;          // n + 1
+    int* bsum;           // one per block of RT_BLD_THREADS positions (+1)
+};
+
+__global__ void bld_setup_kernel(BuildBufs B, int n, int maxDepth) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) bld::setup_root(B.N, B.ctl, n, maxDepth);
+}
+
+// Fold the keys of this thread's shape into `keys` of node `node` (node < 0: nothing to fold).  When every
+// lane of the warp that has something to fold aims at the same pair of siblings (the common case while the
+// segments are longer than a warp), the warp reduces first and issues one atomic per key and side.
+__device__ __forceinline__ void bld_fold_warp(bld::u64* __restrict__ keyBase, int node, const bld::u64 k[6], bool agg) {
+    const unsigned full = 0xffffffffu;
+    const int pair = node < 0 ? -1 : (node + 1) >> 1;                 // siblings (l, l + 1) with l odd share (l + 1) / 2
+    const unsigned have = __ballot_sync(full, node >= 0);
+    if (have == 0u) return;
+    const int lead = __ffs(have) - 1;
+    const int pair0 = __shfl_sync(full, pair, lead);
+    const bool uniform = agg && __all_sync(full, node < 0 || pair == pair0);
+    if (!uniform) {
+        if (node >= 0) bld::fold_keys(keyBase + 6 * (size_t)node, k);
+        return;
+    }
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+        const int target = 2 * pair0 - 1 + side;                       // pair0 = (l + 1) / 2, l odd  =>  l = 2 * pair0 - 1
+        const bool mine = node == target;
+        if (__ballot_sync(full, mine) == 0u) continue;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            const bool isMin = a < 3;
+            const bld::u64 id = isMin ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
+            const bld::u64 v = mine ? k[a] : id;
+            const unsigned hi = (unsigned)(v >> 32), lo = (unsigned)v;
+            const unsigned bestHi = isMin ? __reduce_min_sync(full, hi) : __reduce_max_sync(full, hi);
+            const unsigned cand = hi == bestHi ? lo : (isMin ? 0xffffffffu : 0u);
+            const unsigned bestLo = isMin ? __reduce_min_sync(full, cand) : __reduce_max_sync(full, cand);
+            const bld::u64 best = ((bld::u64)bestHi << 32) | bestLo;
+            if (lane == 0 && best != id) {
+                if (isMin) bld::amin64(keyBase + 6 * (size_t)target + a, best);
+                else bld::amax64(keyBase + 6 * (size_t)target + a, best);
+            }
+        }
+    }
+}
+
+__global__ void bld_init_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int agg) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    bld::u64 k[6];
+    int node = -1;
+    if (p < n) {
+        bld::init_position(p, B.ord[0], B.pnode[0]);
+        bld::shape_keys(shapes + p, (unsigned)p, k);
+        node = 0;
+    }
+    // the root has no sibling: the pair test of bld_fold_warp works on (node + 1) >> 1 = 0 for it, target would be -1;
+    // fold directly, one warp-reduced atomic per key
+    const unsigned full = 0xffffffffu;
+    if (!agg) { if (node == 0) bld::fold_keys(B.N.key, k); return; }
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+        const bool isMin = a < 3;
+        const bld::u64 id = isMin ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
+        const bld::u64 v = node == 0 ? k[a] : id;
+        const unsigned hi = (unsigned)(v >> 32), lo = (unsigned)v;
+        const unsigned bestHi = isMin ? __reduce_min_sync(full, hi) : __reduce_max_sync(full, hi);
+        const unsigned cand = hi == bestHi ? lo : (isMin ? 0xffffffffu : 0u);
+        const unsigned bestLo = isMin ? __reduce_min_sync(full, cand) : __reduce_max_sync(full, cand);
+        const bld::u64 best = ((bld::u64)bestHi << 32) | bestLo;
+        if (lane == 0 && best != id) { if (isMin) bld::amin64(B.N.key + a, best); else bld::amax64(B.N.key + a, best); }
+    }
+}
+
+__global__ void bld_boxes_kernel(BuildBufs B, int n, int level) {      // level < 0: unconditional (the root)
+    if (level >= 0 && !B.ctl->active[level]) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const int cur = level < 0 ? 0 : ((level + 1) & 1);
+    bld::box_from_keys(p, B.pnode[cur], B.N);
+}
+
+// classify + block totals of the flags
+__global__ void bld_classify_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int level) {
+    if (!B.ctl->active[level]) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int cur = level & 1;
+    int f = 0;
+    if (p < n) { f = bld::classify(p, shapes, B.ord[cur], B.pnode[cur], B.N); B.flag[p] = (unsigned char)f; }
+    const int total = __syncthreads_count(f);
+    if (threadIdx.x == 0) B.bsum[blockIdx.x] = total;
+}
+
+// one block: exclusive scan of the block totals in place, grand total into scanL[n]
+__global__ void bld_scan_blocks_kernel(BuildBufs B, int n, int nBlocks, int level) {
+    if (!B.ctl->active[level]) return;
+    __shared__ int sh[1024];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nBlocks; base += 1024) {
+        const int i = base + (int)threadIdx.x;
+        const int v = i < nBlocks ? B.bsum[i] : 0;
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {                     // inclusive Hillis-Steele
+            const int add = (int)threadIdx.x >= off ? sh[threadIdx.x - off] : 0;
+            __syncthreads();
+            sh[threadIdx.x] += add;
+            __syncthreads();
+        }
+        const int incl = sh[threadIdx.x];
+        const int c = carry;
+        if (i < nBlocks) B.bsum[i] = c + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) B.scanL[n] = carry;
+}
+
+// scanL[p] = block offset + exclusive prefix of the flags inside the block
+__global__ void bld_scan_apply_kernel(BuildBufs B, int n, int level) {
+    if (!B.ctl->active[level]) return;
+    __shared__ int warpTot[RT_BLD_THREADS / 32];
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int f = p < n ? (int)B.flag[p] : 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, f);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) warpTot[w] = __popc(bal);
+    __syncthreads();
+    int before = 0;
+    for (int i = 0; i < w; ++i) before += warpTot[i];
+    if (p < n) B.scanL[p] = B.bsum[blockIdx.x] + before + __popc(bal & ((1u << lane) - 1u));
+}
+
+__global__ void bld_heads_kernel(BuildBufs B, int n, int level) {
+    if (!B.ctl->active[level]) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    bld::head(p, level, B.pnode[level & 1], B.scanL, B.N, B.ctl);
+}
+
+__global__ void bld_scatter_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int level, int agg) {
+    if (!B.ctl->active[level]) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int cur = level & 1, nxt = cur ^ 1;
+    bld::u64 k[6];
+    int node = -1;
+    if (p < n) {
+        int newPos, newNode; bool moved;
+        bld::scatter_target(p, (int)B.flag[p], B.pnode[cur], B.scanL, B.N, newPos, newNode, moved);
+        const int shape = B.ord[cur][p];
+        B.ord[nxt][newPos] = shape;
+        B.pnode[nxt][newPos] = newNode;
+        if (moved) { bld::shape_keys(shapes + shape, (unsigned)newPos, k); node = newNode; }
+    }
+    bld_fold_warp(B.N.key, node, k, agg != 0);
+    if (p == 0) B.ctl->parity = nxt;
+}
+
+__global__ void bld_desc_kernel(BuildBufs B, int nNodes) {
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id < nNodes) bld::count_descendants(id, B.N);
+}
+__global__ void bld_number_kernel(BuildBufs B, int nNodes) {
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id < nNodes) bld::number_node(id, B.N);
+}
+__global__ void bld_emit_kernel(BuildBufs B, int nNodes, rt_flat_node* __restrict__ out, int32_t* __restrict__ indices) {
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id < nNodes) bld::emit_node(id, B.N, B.ord[B.ctl->parity], out, indices);
+}
+#endif  // __CUDACC__
+
+}  // namespace rt

@@ -1,0 +1,77 @@
+// build_emu.cpp — TEST INFRASTRUCTURE.  Runs the per-thread bodies of the device BVH builder
+// (opengl-ray-tracer_b200/csrc/rt_build.cuh, namespace rt::bld — the very source nvcc compiles into K8)
+// on the host, one "thread" at a time and one "kernel" after the other in the order rt_api.cu launches
+// them, so that the CPU suite can compare the emitted FlatNode[] / bvhIndices[] with the host builder's
+// byte for byte.  `threadOrder` != 0 walks the threads of every kernel in a scrambled order: the result
+// must not depend on it (atomics, allocation order of the build ids).  Never loaded by the product.
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <numeric>
+#include <random>
+#include <vector>
+
+#include "../../opengl-ray-tracer_b200/csrc/rt_build.cuh"
+
+using namespace rt;
+
+extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, rt_flat_node* outNodes, int32_t* outIdx,
+                             unsigned threadOrder) {
+    if (n <= 0) return -1;
+    const size_t maxNodes = 2 * (size_t)n;
+    std::vector<int> start(maxNodes), count(maxNodes), left(maxNodes), parent(maxNodes), depth(maxNodes), desc(maxNodes), idx(maxNodes), first(maxNodes);
+    std::vector<bld::u64> key(6 * maxNodes);
+    std::vector<float> box(6 * maxNodes);
+    std::vector<unsigned> arrived(maxNodes, 0u);
+    bld::Nodes N{start.data(), count.data(), left.data(), parent.data(), depth.data(), key.data(), box.data(), desc.data(), arrived.data(), idx.data(), first.data()};
+    bld::Ctl ctl;
+    std::vector<int> ord[2] = {std::vector<int>((size_t)n), std::vector<int>((size_t)n)};
+    std::vector<int> pnode[2] = {std::vector<int>((size_t)n), std::vector<int>((size_t)n)};
+    std::vector<int> flag((size_t)n), scanL((size_t)n + 1);
+
+    std::mt19937 rng(threadOrder);
+    auto threads = [&](int m) {
+        std::vector<int> t((size_t)m);
+        std::iota(t.begin(), t.end(), 0);
+        if (threadOrder) std::shuffle(t.begin(), t.end(), rng);
+        return t;
+    };
+
+    bld::setup_root(N, &ctl, n, maxDepth);
+    for (int p : threads(n)) {
+        bld::init_position(p, ord[0].data(), pnode[0].data());
+        bld::u64 k[6];
+        bld::shape_keys(shapes + p, (unsigned)p, k);
+        bld::fold_keys(N.key, k);
+    }
+    for (int p : threads(n)) bld::box_from_keys(p, pnode[0].data(), N);
+
+    for (int level = 0; level < maxDepth; ++level) {
+        if (!ctl.active[level]) continue;
+        const int cur = level & 1, nxt = cur ^ 1;
+        for (int p : threads(n)) flag[(size_t)p] = bld::classify(p, shapes, ord[cur].data(), pnode[cur].data(), N);
+        int run = 0;
+        for (int p = 0; p < n; ++p) { scanL[(size_t)p] = run; run += flag[(size_t)p]; }
+        scanL[(size_t)n] = run;
+        for (int p : threads(n)) bld::head(p, level, pnode[cur].data(), scanL.data(), N, &ctl);
+        for (int p : threads(n)) {
+            int newPos, newNode; bool moved;
+            bld::scatter_target(p, flag[(size_t)p], pnode[cur].data(), scanL.data(), N, newPos, newNode, moved);
+            const int shape = ord[cur][(size_t)p];
+            ord[nxt][(size_t)newPos] = shape;
+            pnode[nxt][(size_t)newPos] = newNode;
+            if (moved) {
+                bld::u64 k[6];
+                bld::shape_keys(shapes + shape, (unsigned)newPos, k);
+                bld::fold_keys(N.key + 6 * (size_t)newNode, k);
+            }
+        }
+        ctl.parity = nxt;
+        for (int p : threads(n)) bld::box_from_keys(p, pnode[nxt].data(), N);
+    }
+    const int nNodes = ctl.nNodes;
+    for (int id : threads(nNodes)) bld::count_descendants(id, N);
+    for (int id : threads(nNodes)) bld::number_node(id, N);
+    for (int id : threads(nNodes)) bld::emit_node(id, N, ord[ctl.parity].data(), outNodes, outIdx);
+    return nNodes;
+}

@@ -1,0 +1,126 @@
+"""CPU: the device BVH builder K8 (opengl-ray-tracer_b200/csrc/rt_build.cuh).  tests/emu/build_emu.cpp compiles the
+per-thread bodies of its kernels with g++ and runs them one thread at a time, kernel after kernel; the emitted
+FlatNode[] and bvhIndices[] must equal the host restatement of the reference builder (buildBVH / split /
+serializeBVH, src/main.cpp:955-979, 1111-1193; opengl-ray-tracer_b200/host/rt_host.cpp) BYTE FOR BYTE, whatever the
+order the threads of a kernel run in."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from util import random_shapes
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+EMU_SRC = os.path.join(HERE, "emu", "build_emu.cpp")
+EMU_SO = os.path.join(HERE, "emu", "libbuild_emu.so")
+CSRC = os.path.join(os.path.dirname(HERE), "opengl-ray-tracer_b200", "csrc")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    deps = [EMU_SRC, os.path.join(CSRC, "rt_build.cuh"), os.path.join(CSRC, "rt_device.cuh")]
+    if not os.path.exists(EMU_SO) or any(os.path.getmtime(d) > os.path.getmtime(EMU_SO) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared",
+                               "-I/usr/local/cuda/include", "-o", EMU_SO, EMU_SRC])
+    L = C.CDLL(EMU_SO)
+    L.emu_build_bvh.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint]
+    L.emu_build_bvh.restype = C.c_int
+    return L
+
+
+def device_build(emu, rt, shapes, depth, order=0):
+    shapes = np.ascontiguousarray(shapes)
+    n = len(shapes)
+    nodes = np.zeros(2 * n, dtype=rt.NODE_DTYPE)
+    idx = np.full(n, -7, dtype=np.int32)
+    nn = emu.emu_build_bvh(shapes.ctypes.data, n, depth, nodes.ctypes.data, idx.ctypes.data, order)
+    assert 1 <= nn <= 2 * n - 1
+    return nodes[:nn], idx
+
+
+def check(emu, rt, shapes, depth, orders=(0, 1, 7)):
+    ref = rt.Scene.from_shapes(shapes, np.zeros(1, rt.LIGHT_DTYPE), np.zeros(1, rt.CAMERA_DTYPE), bvh_depth=depth)
+    want_nodes, want_idx = ref.nodes, ref.indices
+    for order in orders:
+        nodes, idx = device_build(emu, rt, shapes, depth, order)
+        assert len(nodes) == len(want_nodes), (order, len(nodes), len(want_nodes))
+        assert nodes.tobytes() == want_nodes.tobytes(), "node bytes differ (thread order %d)" % order
+        assert idx.tobytes() == want_idx.tobytes(), "bvhIndices differ (thread order %d)" % order
+    return ref
+
+
+@pytest.mark.parametrize("name,n,depth", [("toy", 0, 0), ("triangle", 0, 0), ("monkey", 0, 0), ("car", 0, 0),
+                                          ("soup", 20000, 0), ("monkey", 0, 3), ("car", 0, 40), ("monkey", 0, 1)])
+def test_scene_trees_are_byte_identical(rt, emu, name, n, depth):
+    sc = rt.Scene(name, 160, 120, n_override=n, bvh_depth=depth)
+    d = depth if depth > 0 else {"toy": None, "triangle": None, "monkey": 15, "car": 25, "soup": 40}[name]
+    if d is None:                      # the scene's own default: recover it from a rebuild with a known depth below
+        d = 15
+        ref = check(emu, rt, sc.shapes, d)
+        return
+    ref = check(emu, rt, sc.shapes, d)
+    assert ref.nodes.tobytes() == sc.nodes.tobytes() and ref.indices.tobytes() == sc.indices.tobytes()
+
+
+def test_rebuild_follows_the_animation(rt, emu):
+    """C5's rebuild mode: after every animated frame the tree built from the moved shapes equals the host's rebuild."""
+    for name, depth in (("monkey", 15), ("car", 25)):
+        sc = rt.Scene(name, 160, 120)
+        for f in range(1, 6):
+            sc.animate(f / 60.0, 1 / 60.0, 1)
+            nodes, idx = device_build(emu, rt, sc.shapes, depth, order=f)
+            assert nodes.tobytes() == sc.nodes.tobytes() and idx.tobytes() == sc.indices.tobytes(), (name, f)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_shapes_all_types(rt, emu, seed):
+    rng = np.random.default_rng(100 + seed)
+    n = int(rng.integers(1, 400))
+    sh = random_shapes(rt, rng, n, types=(0, 1, 2, 3), extent=float(rng.choice([0.5, 10.0, 1e3])))
+    check(emu, rt, sh, int(rng.integers(1, 20)))
+
+
+def test_edge_cases(rt, emu):
+    rng = np.random.default_rng(5)
+    # one and two shapes, depth budgets 0 / 1
+    for n in (1, 2, 3):
+        sh = random_shapes(rt, rng, n, types=(0, 3))
+        for depth in (1, 2, 64):
+            check(emu, rt, sh, depth)
+        nodes, idx = device_build(emu, rt, sh, 0)          # no depth budget: the root is the only node (split, :1113-1118)
+        assert len(nodes) == 1 and nodes["leftChild"][0] == -1 and nodes["numShapes"][0] == n and idx.tolist() == list(range(n))
+    # coincident centres: one side of the split stays empty, the node is a (fat) leaf
+    sh = random_shapes(rt, rng, 40, types=(0,))
+    sh["sphereCenter"][:] = sh["sphereCenter"][0]
+    check(emu, rt, sh, 10)
+    # signed zeros: bounds that are +0 in one shape and -0 in another keep the sign of the first in list order
+    sh = random_shapes(rt, rng, 64, types=(3,))
+    for k, f in enumerate(("triP1", "triP2", "triP3")):
+        v = sh[f].copy()
+        v[rng.uniform(size=v.shape) < 0.3] = 0.0
+        v[rng.uniform(size=v.shape) < 0.15] = -0.0
+        v = np.minimum(v, 0.0) if k == 0 else v
+        sh[f] = v
+    check(emu, rt, sh, 12)
+    sh2 = sh.copy()
+    sh2["triP1"] = np.abs(sh2["triP1"]) * 0.0 - np.where(rng.uniform(size=sh2["triP1"].shape) < 0.5, 0.0, -0.0)
+    check(emu, rt, sh2, 12)
+    # non-finite coordinates: a triangle with a non-finite x is skipped as a whole, NaN in y / z is ignored per
+    # component, infinities are kept; a NaN wall basis (normal parallel to no axis test) gives NaN corners
+    sh = random_shapes(rt, rng, 80, types=(0, 2, 3))
+    tri = np.nonzero(sh["type"] == 3)[0]
+    sh["triP1"][tri[0], 0] = np.nan
+    sh["triP2"][tri[1], 0] = np.inf
+    sh["triP3"][tri[2], 1] = np.nan
+    sh["triP1"][tri[3], 2] = np.inf
+    sh["triP2"][tri[4], 1] = -np.inf
+    wall = np.nonzero(sh["type"] == 2)[0]
+    sh["planeNormal"][wall[0]] = (0.0, 0.0, 0.0)
+    sph = np.nonzero(sh["type"] == 0)[0]
+    sh["sphereRadius"][sph[0]] = np.nan
+    sh["sphereCenter"][sph[1], 1] = np.inf
+    check(emu, rt, sh, 12)
+    # infinite planes only: nothing bounds the root, nothing splits
+    check(emu, rt, random_shapes(rt, rng, 5, types=(1,)), 8)
