@@ -359,13 +359,13 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
     import ctypes as C
     out = {}
     L, Hl = rt.lib(), rt.hostlib()
-    for mode, label in ((0, "refit"), (1, "rebuild"), (2, "device_animation")):
+    for mode, label in ((0, "refit"), (1, "rebuild"), (2, "device_animation"), (3, "device_rebuild")):
         sc = rt.Scene("monkey", W, H)
         params = rt.make_params(W, H)
         tr = rt.RayTracer(W, H, device=torch.cuda.current_device(), flags=0)
         tr.set_stream(stream.cuda_stream)
         tr.upload(sc)
-        if mode == 2:
+        if mode >= 2:
             tr.register_animations(sc)
         bufs = [torch.empty((H * W, 4), dtype=torch.float32, pin_memory=True).numpy() for _ in range(2)]
         n = C.c_int(0)
@@ -376,6 +376,12 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
             if mode == 2:                         # K6 + K7 on the device copies: nothing to upload
                 tr.wait_frames(1)
                 tr.animate(i / 60.0, 1.0 / 60.0)
+                tr.render_async(params, bufs[i & 1])
+                return
+            if mode == 3:                         # K6 moves the shapes, K8 rebuilds the reference tree on the device
+                tr.wait_frames(1)
+                tr.animate(i / 60.0, 1.0 / 60.0)
+                tr.build_bvh(15, fetch=False)
                 tr.render_async(params, bufs[i & 1])
                 return
             sc.animate(i / 60.0, 1.0 / 60.0, mode)
@@ -390,18 +396,55 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
             tr.wait_frames(1)                     # frame i-2 is complete: its buffer (this one) may be consumed / reused
             tr.render_async(params, bufs[i & 1])
 
-        for i in range(10):
-            frame(i)
-        tr.synchronize()
-        t0 = time.perf_counter()
-        for i in range(10, 10 + frames):
-            frame(i)
-        tr.synchronize()
-        dt = time.perf_counter() - t0
-        out[label] = {"fps": frames / dt, "ms_per_frame": dt * 1e3 / frames}
+        try:
+            for i in range(10):
+                frame(i)
+            tr.synchronize()
+            t0 = time.perf_counter()
+            for i in range(10, 10 + frames):
+                frame(i)
+            tr.synchronize()
+            dt = time.perf_counter() - t0
+            out[label] = {"fps": frames / dt, "ms_per_frame": dt * 1e3 / frames}
+        except Exception as e:                    # a diagnostic mode must not cost the bench line
+            out[label] = {"error": repr(e)}
         tr.close()
     out["workload"] = "BASELINE.json configs[4]: monkey-1240 %dx%d, %d frames, CPU animation + BVH %s, pinned async upload, D2H of every frame" % (
-        W, H, frames, "refit | rebuild; device_animation = rt_animate (shapes and node boxes move on the device, no upload)")
+        W, H, frames, "refit | rebuild; device_animation = rt_animate (shapes and node boxes move on the device, no upload); "
+                      "device_rebuild = rt_animate + rt_build_bvh (K8: the reference tree rebuilt on the device every frame)")
+    return out
+
+
+def time_device_build(torch, rt, stream):
+    """K8 (rt_build_bvh): the reference's buildBVH + serializeBVH on the device against the host builder
+    (host/rt_host.cpp restating src/main.cpp:955-979, 1111-1193), same shapes: device time by CUDA events (best of 3),
+    the call's wall time incl. the D2H of the tree, the host builder's wall time, and whether the bytes agree."""
+    out = {}
+    for name, n, depth in (("monkey", 0, 15), ("car", 0, 25), ("soup", 1000000, 40)):
+        try:
+            t0 = time.perf_counter()
+            sc = rt.Scene(name, 800, 600, n_override=n)
+            t_scene = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            sc.animate(0.0, 0.0, 1)                                   # mode 1 = buildBVH + serializeBVH on the host
+            t_host = time.perf_counter() - t0
+            tr = rt.RayTracer(64, 48, device=torch.cuda.current_device(), flags=0)
+            tr.set_stream(stream.cuda_stream)
+            tr.upload_scene(sc.light, sc.camera, sc.shapes)
+            dev, wall = [], []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                nn, ni = tr.build_bvh(depth, fetch=False)
+                wall.append(time.perf_counter() - t0)
+                dev.append(tr.last_build_ms())
+            nodes, idx = tr.build_bvh(depth)
+            same = nodes.tobytes() == sc.nodes.tobytes() and idx.tobytes() == sc.indices.tobytes()
+            tr.close()
+            out["%s_%d" % (name, len(sc.shapes))] = {"shapes": len(sc.shapes), "nodes": int(nn), "maxDepth": depth,
+                "device_ms": min(dev), "call_wall_ms": min(wall) * 1e3, "host_builder_ms": t_host * 1e3,
+                "bytes_equal_host_builder": bool(same), "algorithmic_bytes": 192 * len(sc.shapes) + 48 * int(nn) + 4 * int(ni)}
+        except Exception as e:
+            out[name] = {"error": repr(e)}
     return out
 
 
@@ -519,6 +562,7 @@ def main():
                 extra["car_800x600"]["alg_GBps"] = c2["alg_bytes"] / ren2 / 1e6
             tr2.close()
             extra["monkey_animated_300f"] = time_animated(torch, rt, stream)
+            extra["device_bvh_build"] = time_device_build(torch, rt, stream)
 
     if rank == 0:
         peaks = {}

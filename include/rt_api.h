@@ -194,6 +194,23 @@ int rt_anim_rotate_z(rt_ctx* ctx, const int32_t* shapes, int count, const float 
 int rt_animate(rt_ctx* ctx, float t, float dt);
 int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
 
+/* ---- device-side BVH build (K8; opt-in, the host-built tree stays the default) ----
+ * Replaces buildBVH / split (src/main.cpp:1111-1193) + serializeBVH (:955-979) + the node / index upload
+ * (:258-275, :342-344) for callers that only keep the shapes current: the reference's midpoint-split tree
+ * over the shapes the context holds (the device copy, i.e. including what rt_animate moved) is built on the
+ * GPU level by level and emitted in the reference's own numbering — FlatNode[] and bvhIndices[] are BYTE
+ * IDENTICAL to the host builder's, so every traversal decision and tie-break stays what it was.  The tree
+ * becomes the context's BVH as if it had been passed to rt_upload_scene (the threaded layout follows at the
+ * next render; an unchanged topology keeps it and only refits).  maxDepth = buildBVH's argument (15 / 25 in
+ * the reference scenes), at most 64 (the shader's stack).  Shapes of unknown type and infinite planes get no
+ * bounds, as upstream.  rt_get_bvh copies the context's current nodes / indices out (either may be NULL);
+ * rt_last_build_ms = device time of the last build. */
+enum { RT_BUILD_DEFAULT = 0u,
+       RT_BUILD_NO_WARP_AGGREGATION = 1u << 0   /* one atomic per shape and bound instead of per warp (diagnostic) */ };
+int rt_build_bvh(rt_ctx* ctx, int maxDepth, unsigned build_flags, int* nNodes_out, int* nIndices_out);
+int rt_get_bvh(rt_ctx* ctx, void* nodes_or_NULL, int nodeCapacity, int32_t* indices_or_NULL, int indexCapacity);
+float rt_last_build_ms(const rt_ctx* ctx);
+
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in
  * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one
  * row-major W*H image. */

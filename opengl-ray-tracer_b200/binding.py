@@ -56,7 +56,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -99,6 +99,9 @@ def lib():
     L.rt_anim_rotate_z.argtypes = [vp, vp, ip, vp, C.c_float]; L.rt_anim_rotate_z.restype = ip
     L.rt_animate.argtypes = [vp, C.c_float, C.c_float]; L.rt_animate.restype = ip
     L.rt_download_scene.argtypes = [vp, vp, vp]; L.rt_download_scene.restype = ip
+    L.rt_build_bvh.argtypes = [vp, ip, C.c_uint, C.POINTER(C.c_int), C.POINTER(C.c_int)]; L.rt_build_bvh.restype = ip
+    L.rt_get_bvh.argtypes = [vp, vp, ip, vp, ip]; L.rt_get_bvh.restype = ip
+    L.rt_last_build_ms.argtypes = [vp]; L.rt_last_build_ms.restype = C.c_float
     L.rt_item_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_item_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
@@ -358,6 +361,19 @@ class RayTracer:
         shapes = np.zeros(n_shapes, dtype=SHAPE_DTYPE); nodes = np.zeros(n_nodes, dtype=NODE_DTYPE)
         self._chk(self._L.rt_download_scene(self._c, _ptr(shapes), _ptr(nodes)))
         return shapes, nodes
+
+    def build_bvh(self, max_depth, build_flags=0, fetch=True):
+        """K8: build the reference's BVH on the device from the context's shapes; returns (nodes, indices) when `fetch`."""
+        nn, ni = C.c_int(0), C.c_int(0)
+        self._chk(self._L.rt_build_bvh(self._c, int(max_depth), int(build_flags), C.byref(nn), C.byref(ni)))
+        if not fetch:
+            return nn.value, ni.value
+        nodes = np.zeros(nn.value, dtype=NODE_DTYPE); idx = np.zeros(ni.value, dtype=np.int32)
+        self._chk(self._L.rt_get_bvh(self._c, _ptr(nodes), nn.value, _ptr(idx), ni.value))
+        return nodes, idx
+
+    def last_build_ms(self):
+        return float(self._L.rt_last_build_ms(self._c))
 
     def host_frame_unregister(self, host):
         self._chk(self._L.rt_host_frame_unregister(self._c, _ptr(host)))

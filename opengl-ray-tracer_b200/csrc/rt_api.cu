@@ -5,6 +5,7 @@
 #include "rt_layout.h"
 #include "rt_refit.cuh"
 #include "rt_anim.cuh"
+#include "rt_build.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -98,6 +99,13 @@ struct rt_ctx {
     PinBuf<AnimEntry> hAnimEntries; DevBuf<AnimEntry> dAnimEntries; DevBuf<AnimItem> dAnimItems;
     DevBuf<unsigned char> dAnimFlag; DevBuf<int> dIndices, dNodeAux; DevBuf<unsigned> dGrowArrived;   // dNodeAux: [parent nNodes | leaves nLeaves]
     int nLeavesRaw = 0;
+    // device-side BVH build (rt_build.cuh, K8): scratch tables and the emitted FlatNode[] / bvhIndices[]
+    DevBuf<int> bInt; DevBuf<bld::u64> bKey; DevBuf<float> bBox; DevBuf<unsigned char> bFlag; DevBuf<bld::Ctl> bCtl;
+    DevBuf<rt_flat_node> bNodes; DevBuf<int32_t> bIdx;
+    std::vector<rt_flat_node> bHostNodes; std::vector<int32_t> bHostIdx;
+    bool shapesOnDevice = false;      // the pending host range [shapeLo, shapeHi) has already been copied (rt_build_bvh)
+    float lastBuildMs = 0.f;
+    cudaEvent_t evBuild[2] = {nullptr, nullptr};
     bool animDirty = true;            // registrations changed: item list / flags / tree maps must go up again
     bool devShapesDirty = false, devNodesDirty = false;   // the device copies were changed by K6 / K7: repack without an upload
     bool hostStale = false;           // the host shadows no longer describe the device scene (shapes and / or node boxes)
@@ -262,7 +270,7 @@ int flush_scene(rt_ctx* c) {
     const bool shapesChanged = c->shapeHi > c->shapeLo;
     if ((shapesChanged || c->devShapesDirty) && c->nSub > 0) c->subDirty = true;
     cudaEventRecord(c->ev[0], c->stream);
-    if (shapesChanged) {
+    if (shapesChanged && !c->shapesOnDevice) {
         CU(c, c->dShapes.reserve((size_t)c->nShapes));
         CU(c, cudaMemcpyAsync(c->dShapes.p + c->shapeLo, c->hShapes.p + c->shapeLo,
                               (size_t)(c->shapeHi - c->shapeLo) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
@@ -353,6 +361,7 @@ int flush_scene(rt_ctx* c) {
     CU(c, cudaGetLastError());
     c->shapeLo = c->shapeHi = 0; c->nodesDirty = c->topoDirty = false;
     c->devShapesDirty = c->devNodesDirty = false;
+    c->shapesOnDevice = false;
     return RT_OK;
 }
 
@@ -431,6 +440,8 @@ void rt_destroy(rt_ctx* c) {
     c->hRf.release(); c->dRf.release(); c->dRfArrived.release();
     c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
     c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
+    for (auto& e : c->evBuild) if (e) cudaEventDestroy(e);
+    c->bInt.release(); c->bKey.release(); c->bBox.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     for (auto& e : c->evFrame) if (e) cudaEventDestroy(e);
     c->image2.release(); c->ids2.release();
@@ -460,7 +471,7 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
         CU(c, c->hShapes.reserve((size_t)nShapes, 0));
         if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
         c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes;
-        c->hostShapesStale = false;
+        c->hostShapesStale = false; c->shapesOnDevice = false;
         if (!sameTypes) c->topoDirty = true;
     }
     if (indices) {
@@ -493,6 +504,7 @@ int rt_update_shapes(rt_ctx* c, int first, int count, const void* shapes) {
         for (int i = 0; i < count; ++i) if (in[i].type != c->hShapes.p[first + i].type) { c->topoDirty = true; break; }
     }
     std::memcpy(c->hShapes.p + first, shapes, (size_t)count * sizeof(rt_flat_shape));
+    c->shapesOnDevice = false;
     if (c->shapeHi <= c->shapeLo) { c->shapeLo = first; c->shapeHi = first + count; }
     else { if (first < c->shapeLo) c->shapeLo = first; if (first + count > c->shapeHi) c->shapeHi = first + count; }
     return RT_OK;
@@ -897,6 +909,110 @@ int rt_download_scene(rt_ctx* c, void* shapes, void* nodes) {
     if (nodes && c->nNodes > 0) CU(c, cudaMemcpy(nodes, c->dNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost));
     return RT_OK;
 }
+
+// K8 (rt_build.cuh): buildBVH + serializeBVH of the reference on the device copy of the shapes.
+int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* nIndices_out) {
+    if (!c) return RT_ERR_ARG;
+    if (maxDepth > 64) return fail(c, RT_ERR_ARG, "rt_build_bvh: the shader's traversal stack holds 64 entries, maxDepth must be <= 64");
+    if (!c->haveScene || c->hShapes.p == nullptr) return fail(c, RT_ERR_STATE, "rt_build_bvh before the shapes were uploaded");
+    if ((size_t)c->nShapes >= (1u << 29)) return fail(c, RT_ERR_ARG, "rt_build_bvh: more than 2^29 shapes");
+    CU(c, cudaSetDevice(c->device));
+    const int n = c->nShapes;
+    if (n == 0) {                                   // buildBVH over nothing: one empty leaf (main.cpp:1175-1193)
+        c->bHostNodes.assign(1, rt_flat_node{});
+        rt_flat_node& r = c->bHostNodes[0];
+        for (int k = 0; k < 3; ++k) { r.boundsMin[k] = INFINITY; r.boundsMax[k] = -INFINITY; }
+        r.leftChild = r.rightChild = -1;
+        c->bHostIdx.clear();
+    } else {
+        // the device copy of the shapes must be current: push the pending host range now (flush_scene will not repeat it)
+        if (c->shapeHi > c->shapeLo && !c->shapesOnDevice) {
+            CU(c, c->dShapes.reserve((size_t)n));
+            CU(c, cudaMemcpyAsync(c->dShapes.p + c->shapeLo, c->hShapes.p + c->shapeLo,
+                                  (size_t)(c->shapeHi - c->shapeLo) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+            cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
+            c->shapesOnDevice = true;
+        }
+        const size_t maxNodes = 2 * (size_t)n;
+        const int nBlocks = (n + RT_BLD_THREADS - 1) / RT_BLD_THREADS;
+        // int tables: 8 per node + arrived, 2 orders + 2 node maps + scan (n + 1), block sums
+        const size_t nInt = 9 * maxNodes + 4 * (size_t)n + ((size_t)n + 1) + (size_t)nBlocks + 1;
+        CU(c, c->bInt.reserve(nInt)); CU(c, c->bKey.reserve(6 * maxNodes)); CU(c, c->bBox.reserve(6 * maxNodes));
+        CU(c, c->bFlag.reserve((size_t)n)); CU(c, c->bCtl.reserve(1));
+        CU(c, c->bNodes.reserve(maxNodes)); CU(c, c->bIdx.reserve((size_t)n));
+        BuildBufs B;
+        int* q = c->bInt.p;
+        B.N.start = q; q += maxNodes; B.N.count = q; q += maxNodes; B.N.left = q; q += maxNodes; B.N.parent = q; q += maxNodes;
+        B.N.depth = q; q += maxNodes; B.N.desc = q; q += maxNodes; B.N.idx = q; q += maxNodes; B.N.first = q; q += maxNodes;
+        B.N.arrived = reinterpret_cast<unsigned*>(q); q += maxNodes;
+        B.ord[0] = q; q += n; B.ord[1] = q; q += n; B.pnode[0] = q; q += n; B.pnode[1] = q; q += n;
+        B.scanL = q; q += (size_t)n + 1; B.bsum = q;
+        B.N.key = c->bKey.p; B.N.box = c->bBox.p; B.flag = c->bFlag.p; B.ctl = c->bCtl.p;
+        const int agg = (flags & RT_BUILD_NO_WARP_AGGREGATION) ? 0 : 1;
+        cudaStream_t st = c->stream;
+        for (auto& e : c->evBuild) if (!e) CU(c, cudaEventCreate(&e));
+        cudaEventRecord(c->evBuild[0], st);
+        bld_setup_kernel<<<1, 32, 0, st>>>(B, n, maxDepth);
+        bld_init_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, agg);
+        bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, -1);
+        c->launches += 3;
+        for (int level = 0; level < maxDepth; ++level) {
+            bld_classify_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, level);
+            bld_scan_blocks_kernel<<<1, 1024, 0, st>>>(B, n, nBlocks, level);
+            bld_scan_apply_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
+            bld_heads_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
+            bld_scatter_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, level, agg);
+            bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
+            c->launches += 6;
+        }
+        CU(c, cudaGetLastError());
+        int nNodes = 0;                              // the one host round trip: how many nodes there are
+        CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CU(c, cudaStreamSynchronize(st));
+        if (nNodes < 1 || (size_t)nNodes > maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
+        const int nb = (nNodes + RT_BLD_THREADS - 1) / RT_BLD_THREADS;
+        CU(c, cudaMemsetAsync(B.N.arrived, 0, (size_t)nNodes * sizeof(unsigned), st));
+        bld_desc_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
+        bld_number_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
+        bld_emit_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes, c->bNodes.p, c->bIdx.p);
+        c->launches += 3;
+        cudaEventRecord(c->evBuild[1], st);
+        CU(c, cudaGetLastError());
+        c->bHostNodes.resize((size_t)nNodes); c->bHostIdx.resize((size_t)n);
+        CU(c, cudaMemcpyAsync(c->bHostNodes.data(), c->bNodes.p, (size_t)nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost, st));
+        CU(c, cudaMemcpyAsync(c->bHostIdx.data(), c->bIdx.p, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CU(c, cudaStreamSynchronize(st));
+        cudaEventElapsedTime(&c->lastBuildMs, c->evBuild[0], c->evBuild[1]);
+    }
+    // hand the tree to the context exactly as an upload of these nodes and indices would
+    const bool sameIdx = c->bHostIdx.size() == c->indices.size() &&
+                         (c->bHostIdx.empty() || std::memcmp(c->bHostIdx.data(), c->indices.data(), c->bHostIdx.size() * sizeof(int32_t)) == 0);
+    if (!sameIdx) { c->indices = c->bHostIdx; c->topoDirty = true; }
+    int rc = set_nodes(c, c->bHostNodes.data(), (int)c->bHostNodes.size());
+    if (rc != RT_OK) return rc;
+    if (nNodes_out) *nNodes_out = (int)c->bHostNodes.size();
+    if (nIndices_out) *nIndices_out = (int)c->bHostIdx.size();
+    return RT_OK;
+}
+
+int rt_get_bvh(rt_ctx* c, void* nodes, int nodeCap, int32_t* indices, int indexCap) {
+    if (!c) return RT_ERR_ARG;
+    if (!c->haveScene) return fail(c, RT_ERR_STATE, "no scene");
+    if ((nodes && nodeCap < c->nNodes) || (indices && (size_t)indexCap < c->indices.size())) return fail(c, RT_ERR_ARG, "rt_get_bvh: buffer too small");
+    if (c->hostNodesStale) {                        // K7 grew the boxes on the device
+        CU(c, cudaSetDevice(c->device));
+        int rc = flush_scene(c);
+        if (rc != RT_OK) return rc;
+        CU(c, cudaStreamSynchronize(c->stream));
+        if (nodes && c->nNodes > 0) CU(c, cudaMemcpy(nodes, c->dNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost));
+    } else if (nodes && c->nNodes > 0) {
+        wait_copies(c);
+        std::memcpy(nodes, c->hNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node));
+    }
+    if (indices && !c->indices.empty()) std::memcpy(indices, c->indices.data(), c->indices.size() * sizeof(int32_t));
+    return RT_OK;
+}
+float rt_last_build_ms(const rt_ctx* c) { return c ? c->lastBuildMs : 0.f; }
 
 int rt_untile(rt_ctx* c, const float* dev_shards, int world, float* dev_rgba_out) {
     if (!c || !dev_shards || !dev_rgba_out || world < 1) return RT_ERR_ARG;

@@ -1,0 +1,97 @@
+"""GPU: K8, the reference's BVH builder on the device (rt_build_bvh, opengl-ray-tracer_b200/csrc/rt_build.cuh), through
+the C ABI.  The emitted FlatNode[] / bvhIndices[] must equal the host builder's (buildBVH / split / serializeBVH,
+src/main.cpp:955-979, 1111-1193, restated in host/rt_host.cpp) BYTE FOR BYTE, and a frame rendered over the
+device-built tree must be bit-identical to one rendered over the uploaded host tree."""
+import numpy as np
+import pytest
+
+from util import random_shapes
+
+pytestmark = pytest.mark.gpu
+
+NO_AGG = 1      # RT_BUILD_NO_WARP_AGGREGATION
+
+
+def _same_frame(a, b):
+    return np.array_equal(a[1], b[1]) and np.array_equal(a[0].view(np.uint32), b[0].view(np.uint32))
+
+
+@pytest.mark.parametrize("name,n,depth", [("toy", 0, 15), ("monkey", 0, 15), ("car", 0, 25), ("soup", 60000, 40), ("monkey", 0, 2)])
+@pytest.mark.parametrize("flags", [0, NO_AGG])
+def test_device_tree_is_the_host_tree(rt, name, n, depth, flags):
+    W, H = 200, 150
+    sc = rt.Scene(name, W, H, n_override=n, bvh_depth=depth)
+    p = rt.make_params(W, H)
+    a = rt.RayTracer(W, H); a.upload(sc)
+    want = a.render(p)
+    b = rt.RayTracer(W, H)
+    b.upload_scene(sc.light, sc.camera, sc.shapes)                # shapes only: no host tree ever reaches this context
+    nodes, idx = b.build_bvh(depth, flags)
+    assert len(nodes) == len(sc.nodes) and nodes.tobytes() == np.ascontiguousarray(sc.nodes).tobytes(), "FlatNode[] differs"
+    assert idx.tobytes() == np.ascontiguousarray(sc.indices).tobytes(), "bvhIndices[] differs"
+    assert _same_frame(b.render(p), want)
+    # rebuilding over an uploaded tree of the same topology keeps the layout and the frame
+    nodes2, idx2 = a.build_bvh(depth, flags)
+    assert nodes2.tobytes() == nodes.tobytes() and idx2.tobytes() == idx.tobytes()
+    assert _same_frame(a.render(p), want)
+    a.close(); b.close()
+
+
+@pytest.mark.parametrize("name,depth", [("monkey", 15), ("car", 25)])
+def test_rebuild_per_frame_equals_host_rebuild(rt, name, depth):
+    """BASELINE configs[4] in rebuild mode with nothing but a few scalars crossing PCIe: rt_animate moves the shapes on
+    the device (K6), rt_build_bvh rebuilds the tree there (K8); the host animates and rebuilds (buildBVH) beside it."""
+    W, H = 200, 150
+    sc = rt.Scene(name, W, H)
+    p = rt.make_params(W, H)
+    a = rt.RayTracer(W, H); b = rt.RayTracer(W, H)
+    a.upload(sc); b.upload(sc)
+    b.register_animations(sc)
+    for frame in range(1, 5):
+        t, dt = frame * 0.21, 0.21
+        sc.animate(t, dt, mode=1)
+        a.upload_scene(None, None, sc.shapes, sc.nodes, sc.indices)
+        b.animate(t, dt)
+        nodes, idx = b.build_bvh(depth)
+        assert nodes.tobytes() == np.ascontiguousarray(sc.nodes).tobytes(), "nodes, frame %d" % frame
+        assert idx.tobytes() == np.ascontiguousarray(sc.indices).tobytes(), "indices, frame %d" % frame
+        assert _same_frame(a.render(p), b.render(p)), "frame %d" % frame
+    a.close(); b.close()
+
+
+def test_device_build_edge_cases(rt):
+    """Every shape type incl. infinite planes, coincident centres, signed zeros, non-finite coordinates, depth budgets."""
+    rng = np.random.default_rng(11)
+    light = np.zeros(1, rt.LIGHT_DTYPE); cam = np.zeros(1, rt.CAMERA_DTYPE)
+    cases = []
+    for n in (1, 2, 3, 33, 700):
+        cases.append((random_shapes(rt, rng, n, types=(0, 1, 2, 3)), int(rng.integers(1, 20))))
+    sh = random_shapes(rt, rng, 40, types=(0,)); sh["sphereCenter"][:] = sh["sphereCenter"][0]
+    cases.append((sh, 10))
+    sh = random_shapes(rt, rng, 300, types=(3,))
+    for f in ("triP1", "triP2", "triP3"):
+        v = sh[f].copy()
+        v[rng.uniform(size=v.shape) < 0.3] = 0.0
+        v[rng.uniform(size=v.shape) < 0.15] = -0.0
+        sh[f] = v
+    cases.append((sh, 12))
+    sh = random_shapes(rt, rng, 200, types=(0, 2, 3))
+    tri = np.nonzero(sh["type"] == 3)[0]
+    sh["triP1"][tri[0], 0] = np.nan; sh["triP2"][tri[1], 0] = np.inf; sh["triP3"][tri[2], 1] = np.nan
+    sh["triP1"][tri[3], 2] = np.inf; sh["triP2"][tri[4], 1] = -np.inf
+    sh["planeNormal"][np.nonzero(sh["type"] == 2)[0][0]] = (0.0, 0.0, 0.0)
+    sph = np.nonzero(sh["type"] == 0)[0]
+    sh["sphereRadius"][sph[0]] = np.nan; sh["sphereCenter"][sph[1], 1] = np.inf
+    cases.append((sh, 12))
+    tr = rt.RayTracer(64, 48)
+    for shapes, depth in cases:
+        ref = rt.Scene.from_shapes(shapes, light, cam, bvh_depth=depth)
+        for flags in (0, NO_AGG):
+            tr.upload_scene(light, cam, shapes)
+            nodes, idx = tr.build_bvh(depth, flags)
+            assert nodes.tobytes() == np.ascontiguousarray(ref.nodes).tobytes(), (len(shapes), depth, flags)
+            assert idx.tobytes() == np.ascontiguousarray(ref.indices).tobytes(), (len(shapes), depth, flags)
+    # no depth budget: the root is the only node
+    nodes, idx = tr.build_bvh(0)
+    assert len(nodes) == 1 and nodes["leftChild"][0] == -1 and nodes["numShapes"][0] == len(cases[-1][0])
+    tr.close()
