@@ -93,7 +93,10 @@ const char* rt_last_error(const rt_ctx* ctx);
  * be NULL = keep what is resident.  shapes/nodes/indices are the reference's
  * FlatShape[]/FlatNode[]/int[] bytes; the root is nodes[nNodes-1]
  * (gpu_shader.comp:386).  The buffers are staged through pinned memory with
- * cudaMemcpyAsync and repacked on the device into float4 SoA. */
+ * cudaMemcpyAsync and repacked on the device into float4 SoA.
+ * A SHORTER shape buffer passed on its own (nodes and indices NULL) drops the
+ * tree the context holds — its indices would point past the end; useBVH frames
+ * then hit nothing until nodes / indices are supplied or rt_build_bvh is called. */
 int rt_upload_scene(rt_ctx* ctx,
                     const void* light32, const void* camera80,
                     const void* shapes, int nShapes,

@@ -468,6 +468,11 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
         bool sameTypes = c->haveScene && nShapes == c->nShapes && !c->topoDirty;
         const rt_flat_shape* in = static_cast<const rt_flat_shape*>(shapes);
         for (int i = 0; sameTypes && i < nShapes; ++i) sameTypes = in[i].type == c->hShapes.p[i].type;
+        if (!nodes && !indices && c->haveScene && nShapes < c->nShapes && c->nNodes > 0) {
+            // a shorter shape buffer on its own: the tree the context holds would index past its end.  It is dropped
+            // (useBVH frames hit nothing) until nodes / indices are supplied or rt_build_bvh builds a new one.
+            c->nNodes = 0; c->indices.clear(); c->topoDirty = true; c->nodesDirty = true; c->hostNodesStale = false;
+        }
         CU(c, c->hShapes.reserve((size_t)nShapes, 0));
         if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
         c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes;

@@ -1,5 +1,5 @@
 """Times K8 (rt_build_bvh) against the host builder on the same shapes (no torch needed): device time by CUDA
-events, wall time of the call, host builder wall time, byte equality.  Usage: python tools/build_probe.py [soup_n]"""
+events, wall time of the call, host builder wall time, byte equality.  Usage: python tools/build_probe.py [soup_n [scene,scene...]]"""
 import json
 import os
 import sys
@@ -10,8 +10,11 @@ import rtload  # noqa: E402
 
 rt = rtload.load()
 soup_n = int(sys.argv[1]) if len(sys.argv) > 1 else 1000000
+only = sys.argv[2].split(",") if len(sys.argv) > 2 else None
 out = {}
 for name, n, depth in (("monkey", 0, 15), ("car", 0, 25), ("soup", soup_n, 40)):
+    if only and name not in only:
+        continue
     sc = rt.Scene(name, 800, 600, n_override=n)
     t0 = time.perf_counter()
     sc.animate(0.0, 0.0, 1)                       # buildBVH + serializeBVH on the host
