@@ -101,7 +101,7 @@ struct rt_ctx {
     int nLeavesRaw = 0;
     // device-side BVH build (rt_build.cuh, K8): scratch tables and the emitted FlatNode[] / bvhIndices[]
     DevBuf<int> bInt; DevBuf<bld::u64> bKey; DevBuf<float> bBox; DevBuf<unsigned char> bFlag; DevBuf<bld::Ctl> bCtl;
-    DevBuf<rt_flat_node> bNodes; DevBuf<int32_t> bIdx;
+    DevBuf<rt_flat_node> bNodes; DevBuf<int32_t> bIdx; DevBuf<float4> bRec;
     std::vector<rt_flat_node> bHostNodes; std::vector<int32_t> bHostIdx;
     bool shapesOnDevice = false;      // the pending host range [shapeLo, shapeHi) has already been copied (rt_build_bvh)
     float lastBuildMs = 0.f;
@@ -441,7 +441,7 @@ void rt_destroy(rt_ctx* c) {
     c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
     c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
     for (auto& e : c->evBuild) if (e) cudaEventDestroy(e);
-    c->bInt.release(); c->bKey.release(); c->bBox.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release();
+    c->bInt.release(); c->bKey.release(); c->bBox.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release(); c->bRec.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     for (auto& e : c->evFrame) if (e) cudaEventDestroy(e);
     c->image2.release(); c->ids2.release();
@@ -944,7 +944,7 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         const size_t nInt = 9 * maxNodes + 4 * (size_t)n + ((size_t)n + 1) + (size_t)nBlocks + 1;
         CU(c, c->bInt.reserve(nInt)); CU(c, c->bKey.reserve(6 * maxNodes)); CU(c, c->bBox.reserve(6 * maxNodes));
         CU(c, c->bFlag.reserve((size_t)n)); CU(c, c->bCtl.reserve(1));
-        CU(c, c->bNodes.reserve(maxNodes)); CU(c, c->bIdx.reserve((size_t)n));
+        CU(c, c->bNodes.reserve(maxNodes)); CU(c, c->bIdx.reserve((size_t)n)); CU(c, c->bRec.reserve(3 * (size_t)n));
         BuildBufs B;
         int* q = c->bInt.p;
         B.N.start = q; q += maxNodes; B.N.count = q; q += maxNodes; B.N.left = q; q += maxNodes; B.N.parent = q; q += maxNodes;
@@ -953,6 +953,7 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         B.ord[0] = q; q += n; B.ord[1] = q; q += n; B.pnode[0] = q; q += n; B.pnode[1] = q; q += n;
         B.scanL = q; q += (size_t)n + 1; B.bsum = q;
         B.N.key = c->bKey.p; B.N.box = c->bBox.p; B.flag = c->bFlag.p; B.ctl = c->bCtl.p;
+        B.R.cen = c->bRec.p; B.R.mn = c->bRec.p + n; B.R.mx = c->bRec.p + 2 * (size_t)n;
         const int agg = (flags & RT_BUILD_NO_WARP_AGGREGATION) ? 0 : 1;
         cudaStream_t st = c->stream;
         for (auto& e : c->evBuild) if (!e) CU(c, cudaEventCreate(&e));
@@ -962,11 +963,11 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, -1);
         c->launches += 3;
         for (int level = 0; level < maxDepth; ++level) {
-            bld_classify_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, level);
+            bld_classify_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
             bld_scan_blocks_kernel<<<1, 1024, 0, st>>>(B, n, nBlocks, level);
             bld_scan_apply_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
             bld_heads_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
-            bld_scatter_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, level, agg);
+            bld_scatter_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level, agg);
             bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
             c->launches += 6;
         }

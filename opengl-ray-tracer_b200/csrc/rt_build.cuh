@@ -129,37 +129,61 @@ RT_DEV int shape_points(const rt_flat_shape* __restrict__ s, V3 pt[3]) {
 }
 RT_DEV float comp(V3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; }
 
-// The six keys of the shape at position `pos` (sequence = pos * 4 + point number); identity where it has none.
-RT_DEV void shape_keys(const rt_flat_shape* __restrict__ s, unsigned pos, u64 k[6]) {
+// Per-shape record, computed once per build (the level loop never reads the 192-byte shapes again):
+//   cen = split's centre of the shape (main.cpp:1128-1142)
+//   mn / mx = per axis the value the shape contributes to a box minimum / maximum — the first of its points, in the
+//   host's growing order, among those that compare equal — and in .w which point that was (2 bits per axis) and
+//   whether the axis has a value at all (bit 6 + axis): NaN coordinates never change a bound (`NaN < mn` is false).
+struct Records { float4* cen; float4* mn; float4* mx; };
+
+RT_DEV void shape_record(const rt_flat_shape* __restrict__ s, float4& cen, float4& mn, float4& mx) {
     V3 pt[3];
     const int np = shape_points(s, pt);
+    float lo[3] = {0.f, 0.f, 0.f}, hi[3] = {0.f, 0.f, 0.f};
+    unsigned metaLo = 0u, metaHi = 0u;
 #pragma unroll
-    for (int a = 0; a < 3; ++a) { k[a] = RT_BLD_KEY_MIN_ID; k[3 + a] = RT_BLD_KEY_MAX_ID; }
-    for (int j = 0; j < np; ++j) {
-        const unsigned seq = pos * 4u + (unsigned)j;
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
+    for (int a = 0; a < 3; ++a) {
+        bool have = false;
+        for (int j = 0; j < np; ++j) {
             const float v = comp(pt[j], a);
-            if (v != v) continue;                       // `NaN < mn` and `mx < NaN` are false: the host keeps the old bound
-            const u64 lo = key_min(v, seq), hi = key_max(v, seq);
-            if (lo < k[a]) k[a] = lo;
-            if (hi > k[3 + a]) k[3 + a] = hi;
+            if (v != v) continue;
+            if (!have) { lo[a] = v; hi[a] = v; metaLo |= ((unsigned)j << (2 * a)) | (1u << (6 + a)); metaHi |= ((unsigned)j << (2 * a)) | (1u << (6 + a)); have = true; continue; }
+            if (v < lo[a]) { lo[a] = v; metaLo = (metaLo & ~(3u << (2 * a))) | ((unsigned)j << (2 * a)); }
+            if (hi[a] < v) { hi[a] = v; metaHi = (metaHi & ~(3u << (2 * a))) | ((unsigned)j << (2 * a)); }
         }
+    }
+    V3 c = mk(0.f, 0.f, 0.f);                            // upstream leaves a plane's centre uninitialised; 0 as in rt_host.cpp
+    const int type = s->type;
+    if (type == RT_SHAPE_SPHERE) c = mk(s->sphereCenter);
+    else if (type == RT_SHAPE_WALL) c = (mk(s->wallStart) + wall_end(s)) * 0.5f;
+    else if (type == RT_SHAPE_TRIANGLE) c = ((mk(s->triP1) + mk(s->triP2)) + mk(s->triP3)) / 3.0f;
+    cen = make_float4(c.x, c.y, c.z, 0.f);
+    mn = make_float4(lo[0], lo[1], lo[2], u2f(metaLo));
+    mx = make_float4(hi[0], hi[1], hi[2], u2f(metaHi));
+}
+
+// The six keys of a shape standing at position `pos` (sequence = pos * 4 + point number); identity where it has none.
+RT_DEV void record_keys(float4 mn, float4 mx, unsigned pos, u64 k[6]) {
+    const unsigned mLo = f2u(mn.w), mHi = f2u(mx.w);
+    const float lo[3] = {mn.x, mn.y, mn.z}, hi[3] = {mx.x, mx.y, mx.z};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        k[a]     = (mLo >> (6 + a)) & 1u ? key_min(lo[a], pos * 4u + ((mLo >> (2 * a)) & 3u)) : RT_BLD_KEY_MIN_ID;
+        k[3 + a] = (mHi >> (6 + a)) & 1u ? key_max(hi[a], pos * 4u + ((mHi >> (2 * a)) & 3u)) : RT_BLD_KEY_MAX_ID;
     }
 }
 
-// split's centre test (main.cpp:1119-1142): does the shape go to the left child of a node with this box?
-RT_DEV bool goes_left(const rt_flat_shape* __restrict__ s, const float* __restrict__ box) {
+// split's side test (main.cpp:1119-1145): does a shape with this centre go to the left child of a node with this box?
+RT_DEV bool goes_left(float4 cen, const float* __restrict__ box) {
     const float sx = box[3] - box[0], sy = box[4] - box[1], sz = box[5] - box[2];
     const int axis = sx > (sy < sz ? sz : sy) ? 0 : sy > sz ? 1 : 2;
     const float pos = (box[axis] + box[3 + axis]) * 0.5f;
-    float c = 0.f;                                       // upstream leaves a plane's centre uninitialised; 0 as in rt_host.cpp
-    const int type = s->type;
-    if (type == RT_SHAPE_SPHERE) c = s->sphereCenter[axis];
-    else if (type == RT_SHAPE_WALL) c = comp((mk(s->wallStart) + wall_end(s)) * 0.5f, axis);
-    else if (type == RT_SHAPE_TRIANGLE) c = ((s->triP1[axis] + s->triP2[axis]) + s->triP3[axis]) / 3.0f;
+    const float c = axis == 0 ? cen.x : axis == 1 ? cen.y : cen.z;
     return c < pos;
 }
+
+// A node's positions are contiguous: p is the first of its node iff its left neighbour belongs to another node.
+RT_DEV bool is_head(int p, const int* __restrict__ pnode) { return p == 0 || pnode[p - 1] != pnode[p]; }
 
 // ---- per-thread bodies of the level loop -------------------------------------------------------------------
 RT_DEV void setup_root(const Nodes& N, Ctl* ctl, int n, int maxDepth) {
@@ -171,20 +195,27 @@ RT_DEV void setup_root(const Nodes& N, Ctl* ctl, int n, int maxDepth) {
     ctl->active[0] = maxDepth > 0 ? 1 : 0;
 }
 
-// position p of level 0: the identity order, everything in the root; returns the shape's keys
-RT_DEV void init_position(int p, int* __restrict__ ord, int* __restrict__ pnode) { ord[p] = p; pnode[p] = 0; }
+// position p of level 0: the identity order, everything in the root; the shape's record; its keys for the root box
+RT_DEV void init_position(int p, const rt_flat_shape* __restrict__ shapes, const Records& R, int* __restrict__ ord,
+                          int* __restrict__ pnode, u64 k[6]) {
+    ord[p] = p; pnode[p] = 0;
+    float4 cen, mn, mx;
+    shape_record(shapes + p, cen, mn, mx);
+    R.cen[p] = cen; R.mn[p] = mn; R.mx[p] = mx;
+    record_keys(mn, mx, (unsigned)p, k);
+}
 
-RT_DEV int classify(int p, const rt_flat_shape* __restrict__ shapes, const int* __restrict__ ord,
-                    const int* __restrict__ pnode, const Nodes& N) {
+RT_DEV int classify(int p, const Records& R, const int* __restrict__ ord, const int* __restrict__ pnode, const Nodes& N) {
     const int node = pnode[p];
     if (N.left[node] != RT_BLD_PENDING) return 0;
-    return goes_left(shapes + ord[p], N.box + 6 * (size_t)node) ? 1 : 0;
+    return goes_left(R.cen[ord[p]], N.box + 6 * (size_t)node) ? 1 : 0;
 }
 
 // scanL: exclusive prefix sums of the flags, n + 1 entries
 RT_DEV void head(int p, int level, const int* __restrict__ pnode, const int* __restrict__ scanL, const Nodes& N, Ctl* ctl) {
+    if (!is_head(p, pnode)) return;
     const int node = pnode[p];
-    if (N.left[node] != RT_BLD_PENDING || p != N.start[node]) return;
+    if (N.left[node] != RT_BLD_PENDING) return;
     const int cnt = N.count[node];
     const int nL = scanL[p + cnt] - scanL[p];
     if (nL == 0 || nL == cnt) { N.left[node] = RT_BLD_LEAF; return; }      // "no reason to split anymore" (:1156-1161)
@@ -226,8 +257,8 @@ RT_DEV void fold_keys(u64* __restrict__ nodeKeys, const u64 k[6]) {
 }
 
 RT_DEV void box_from_keys(int p, const int* __restrict__ pnode, const Nodes& N) {
+    if (!is_head(p, pnode)) return;
     const int node = pnode[p];
-    if (p != N.start[node]) return;
 #pragma unroll
     for (int a = 0; a < 6; ++a) N.box[6 * (size_t)node + a] = key_value(N.key[6 * (size_t)node + a]);
 }
@@ -290,6 +321,7 @@ RT_DEV void emit_node(int id, const Nodes& N, const int* __restrict__ ord, rt_fl
 
 struct BuildBufs {
     bld::Nodes N;
+    bld::Records R;
     bld::Ctl* ctl;
     int* ord[2];
     int* pnode[2];
@@ -302,40 +334,79 @@ __global__ void bld_setup_kernel(BuildBufs B, int n, int maxDepth) {
     if (blockIdx.x == 0 && threadIdx.x == 0) bld::setup_root(B.N, B.ctl, n, maxDepth);
 }
 
-// Fold the keys of this thread's shape into `keys` of node `node` (node < 0: nothing to fold).  When every
-// lane of the warp that has something to fold aims at the same pair of siblings (the common case while the
-// segments are longer than a warp), the warp reduces first and issues one atomic per key and side.
-__device__ __forceinline__ void bld_fold_warp(bld::u64* __restrict__ keyBase, int node, const bld::u64 k[6], bool agg) {
+// Warp-wide minimum (isMin) or maximum of 64-bit keys, two 32-bit REDUX steps: the high words, then the low words
+// of the lanes that hold the winning high word.
+__device__ __forceinline__ bld::u64 bld_warp_best(bld::u64 v, bool isMin) {
     const unsigned full = 0xffffffffu;
-    const int pair = node < 0 ? -1 : (node + 1) >> 1;                 // siblings (l, l + 1) with l odd share (l + 1) / 2
-    const unsigned have = __ballot_sync(full, node >= 0);
-    if (have == 0u) return;
-    const int lead = __ffs(have) - 1;
-    const int pair0 = __shfl_sync(full, pair, lead);
-    const bool uniform = agg && __all_sync(full, node < 0 || pair == pair0);
-    if (!uniform) {
-        if (node >= 0) bld::fold_keys(keyBase + 6 * (size_t)node, k);
+    const unsigned hi = (unsigned)(v >> 32), lo = (unsigned)v;
+    const unsigned bestHi = isMin ? __reduce_min_sync(full, hi) : __reduce_max_sync(full, hi);
+    const unsigned cand = hi == bestHi ? lo : (isMin ? 0xffffffffu : 0u);
+    const unsigned bestLo = isMin ? __reduce_min_sync(full, cand) : __reduce_max_sync(full, cand);
+    return ((bld::u64)bestHi << 32) | bestLo;
+}
+
+// Fold the keys k of this thread's shape into node `node` (node < 0: nothing to fold).  Called by every thread of
+// the block.  While the segments are long, all the shapes of a warp — of the whole block — go to the same pair of
+// siblings: then the warp reduces each key first (REDUX), the block combines its warps in shared memory, and one
+// global atomic per key and side leaves the block (warp, when only the warp is uniform).  Mixed warps fall back to
+// one atomic per shape and key.  agg == 0 forces that fallback everywhere (diagnostic).
+__device__ __forceinline__ void bld_fold_block(bld::u64* __restrict__ keyBase, int node, const bld::u64 k[6], bool agg) {
+    __shared__ bld::u64 sk[12];
+    __shared__ int sPair;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int pair = node < 0 ? -1 : (node + 1) >> 1;                 // siblings (l, l + 1), l odd, share (l + 1) / 2; the root is pair 0
+    if (!agg) { if (node >= 0) bld::fold_keys(keyBase + 6 * (size_t)node, k); return; }
+    if (threadIdx.x == 0) sPair = -1;
+    if (threadIdx.x < 12) sk[threadIdx.x] = threadIdx.x % 6 < 3 ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
+    __syncthreads();
+    if (node >= 0) sPair = pair;                                      // any one of them
+    __syncthreads();
+    const int pair0 = sPair;
+    if (pair0 < 0) return;                                            // nothing to fold in this block (uniform)
+    const bool blockUniform = __syncthreads_and(node < 0 || pair == pair0) != 0;
+    const int left0 = pair0 == 0 ? 0 : 2 * pair0 - 1;                  // the pair's first node (the root stands alone)
+    if (blockUniform) {
+#pragma unroll
+        for (int side = 0; side < 2; ++side) {
+            const bool mine = node == left0 + side;
+            if (__ballot_sync(full, mine) == 0u) continue;
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                const bool isMin = a < 3;
+                const bld::u64 id = isMin ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
+                const bld::u64 best = bld_warp_best(mine ? k[a] : id, isMin);
+                if (lane == 0 && best != id) { if (isMin) atomicMin(&sk[side * 6 + a], best); else atomicMax(&sk[side * 6 + a], best); }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < 12) {
+            const int side = threadIdx.x / 6, a = threadIdx.x % 6;
+            const bld::u64 v = sk[threadIdx.x];
+            if (a < 3) { if (v != RT_BLD_KEY_MIN_ID) bld::amin64(keyBase + 6 * (size_t)(left0 + side) + a, v); }
+            else       { if (v != RT_BLD_KEY_MAX_ID) bld::amax64(keyBase + 6 * (size_t)(left0 + side) + a, v); }
+        }
         return;
     }
-    const int lane = threadIdx.x & 31;
+    // per warp
+    const unsigned have = __ballot_sync(full, node >= 0);
+    if (have == 0u) return;
+    const int wpair = __shfl_sync(full, pair, __ffs(have) - 1);
+    const bool warpUniform = __all_sync(full, node < 0 || pair == wpair);
+    if (!warpUniform) { if (node >= 0) bld::fold_keys(keyBase + 6 * (size_t)node, k); return; }
+    const int wleft = wpair == 0 ? 0 : 2 * wpair - 1;
 #pragma unroll
     for (int side = 0; side < 2; ++side) {
-        const int target = 2 * pair0 - 1 + side;                       // pair0 = (l + 1) / 2, l odd  =>  l = 2 * pair0 - 1
-        const bool mine = node == target;
+        const bool mine = node == wleft + side;
         if (__ballot_sync(full, mine) == 0u) continue;
 #pragma unroll
         for (int a = 0; a < 6; ++a) {
             const bool isMin = a < 3;
             const bld::u64 id = isMin ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
-            const bld::u64 v = mine ? k[a] : id;
-            const unsigned hi = (unsigned)(v >> 32), lo = (unsigned)v;
-            const unsigned bestHi = isMin ? __reduce_min_sync(full, hi) : __reduce_max_sync(full, hi);
-            const unsigned cand = hi == bestHi ? lo : (isMin ? 0xffffffffu : 0u);
-            const unsigned bestLo = isMin ? __reduce_min_sync(full, cand) : __reduce_max_sync(full, cand);
-            const bld::u64 best = ((bld::u64)bestHi << 32) | bestLo;
+            const bld::u64 best = bld_warp_best(mine ? k[a] : id, isMin);
             if (lane == 0 && best != id) {
-                if (isMin) bld::amin64(keyBase + 6 * (size_t)target + a, best);
-                else bld::amax64(keyBase + 6 * (size_t)target + a, best);
+                if (isMin) bld::amin64(keyBase + 6 * (size_t)(wleft + side) + a, best);
+                else bld::amax64(keyBase + 6 * (size_t)(wleft + side) + a, best);
             }
         }
     }
@@ -345,28 +416,8 @@ __global__ void bld_init_kernel(BuildBufs B, const rt_flat_shape* __restrict__ s
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     bld::u64 k[6];
     int node = -1;
-    if (p < n) {
-        bld::init_position(p, B.ord[0], B.pnode[0]);
-        bld::shape_keys(shapes + p, (unsigned)p, k);
-        node = 0;
-    }
-    // the root has no sibling: the pair test of bld_fold_warp works on (node + 1) >> 1 = 0 for it, target would be -1;
-    // fold directly, one warp-reduced atomic per key
-    const unsigned full = 0xffffffffu;
-    if (!agg) { if (node == 0) bld::fold_keys(B.N.key, k); return; }
-    const int lane = threadIdx.x & 31;
-#pragma unroll
-    for (int a = 0; a < 6; ++a) {
-        const bool isMin = a < 3;
-        const bld::u64 id = isMin ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
-        const bld::u64 v = node == 0 ? k[a] : id;
-        const unsigned hi = (unsigned)(v >> 32), lo = (unsigned)v;
-        const unsigned bestHi = isMin ? __reduce_min_sync(full, hi) : __reduce_max_sync(full, hi);
-        const unsigned cand = hi == bestHi ? lo : (isMin ? 0xffffffffu : 0u);
-        const unsigned bestLo = isMin ? __reduce_min_sync(full, cand) : __reduce_max_sync(full, cand);
-        const bld::u64 best = ((bld::u64)bestHi << 32) | bestLo;
-        if (lane == 0 && best != id) { if (isMin) bld::amin64(B.N.key + a, best); else bld::amax64(B.N.key + a, best); }
-    }
+    if (p < n) { bld::init_position(p, shapes, B.R, B.ord[0], B.pnode[0], k); node = 0; }
+    bld_fold_block(B.N.key, node, k, agg != 0);
 }
 
 __global__ void bld_boxes_kernel(BuildBufs B, int n, int level) {      // level < 0: unconditional (the root)
@@ -378,12 +429,12 @@ __global__ void bld_boxes_kernel(BuildBufs B, int n, int level) {      // level 
 }
 
 // classify + block totals of the flags
-__global__ void bld_classify_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int level) {
+__global__ void bld_classify_kernel(BuildBufs B, int n, int level) {
     if (!B.ctl->active[level]) return;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     const int cur = level & 1;
     int f = 0;
-    if (p < n) { f = bld::classify(p, shapes, B.ord[cur], B.pnode[cur], B.N); B.flag[p] = (unsigned char)f; }
+    if (p < n) { f = bld::classify(p, B.R, B.ord[cur], B.pnode[cur], B.N); B.flag[p] = (unsigned char)f; }
     const int total = __syncthreads_count(f);
     if (threadIdx.x == 0) B.bsum[blockIdx.x] = total;
 }
@@ -438,7 +489,7 @@ __global__ void bld_heads_kernel(BuildBufs B, int n, int level) {
     bld::head(p, level, B.pnode[level & 1], B.scanL, B.N, B.ctl);
 }
 
-__global__ void bld_scatter_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int level, int agg) {
+__global__ void bld_scatter_kernel(BuildBufs B, int n, int level, int agg) {
     if (!B.ctl->active[level]) return;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     const int cur = level & 1, nxt = cur ^ 1;
@@ -450,9 +501,9 @@ __global__ void bld_scatter_kernel(BuildBufs B, const rt_flat_shape* __restrict_
         const int shape = B.ord[cur][p];
         B.ord[nxt][newPos] = shape;
         B.pnode[nxt][newPos] = newNode;
-        if (moved) { bld::shape_keys(shapes + shape, (unsigned)newPos, k); node = newNode; }
+        if (moved) { bld::record_keys(B.R.mn[shape], B.R.mx[shape], (unsigned)newPos, k); node = newNode; }
     }
-    bld_fold_warp(B.N.key, node, k, agg != 0);
+    bld_fold_block(B.N.key, node, k, agg != 0);
     if (p == 0) B.ctl->parity = nxt;
 }
 

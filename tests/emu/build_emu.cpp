@@ -28,6 +28,8 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
     std::vector<int> ord[2] = {std::vector<int>((size_t)n), std::vector<int>((size_t)n)};
     std::vector<int> pnode[2] = {std::vector<int>((size_t)n), std::vector<int>((size_t)n)};
     std::vector<int> flag((size_t)n), scanL((size_t)n + 1);
+    std::vector<float4> cen((size_t)n), rmn((size_t)n), rmx((size_t)n);
+    bld::Records R{cen.data(), rmn.data(), rmx.data()};
 
     std::mt19937 rng(threadOrder);
     auto threads = [&](int m) {
@@ -39,9 +41,8 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
 
     bld::setup_root(N, &ctl, n, maxDepth);
     for (int p : threads(n)) {
-        bld::init_position(p, ord[0].data(), pnode[0].data());
         bld::u64 k[6];
-        bld::shape_keys(shapes + p, (unsigned)p, k);
+        bld::init_position(p, shapes, R, ord[0].data(), pnode[0].data(), k);
         bld::fold_keys(N.key, k);
     }
     for (int p : threads(n)) bld::box_from_keys(p, pnode[0].data(), N);
@@ -49,7 +50,7 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
     for (int level = 0; level < maxDepth; ++level) {
         if (!ctl.active[level]) continue;
         const int cur = level & 1, nxt = cur ^ 1;
-        for (int p : threads(n)) flag[(size_t)p] = bld::classify(p, shapes, ord[cur].data(), pnode[cur].data(), N);
+        for (int p : threads(n)) flag[(size_t)p] = bld::classify(p, R, ord[cur].data(), pnode[cur].data(), N);
         int run = 0;
         for (int p = 0; p < n; ++p) { scanL[(size_t)p] = run; run += flag[(size_t)p]; }
         scanL[(size_t)n] = run;
@@ -62,7 +63,7 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
             pnode[nxt][(size_t)newPos] = newNode;
             if (moved) {
                 bld::u64 k[6];
-                bld::shape_keys(shapes + shape, (unsigned)newPos, k);
+                bld::record_keys(rmn[(size_t)shape], rmx[(size_t)shape], (unsigned)newPos, k);
                 bld::fold_keys(N.key + 6 * (size_t)newNode, k);
             }
         }
