@@ -209,7 +209,8 @@ int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
  * bounds, as upstream.  rt_get_bvh copies the context's current nodes / indices out (either may be NULL);
  * rt_last_build_ms = device time of the last build. */
 enum { RT_BUILD_DEFAULT = 0u,
-       RT_BUILD_NO_WARP_AGGREGATION = 1u << 0   /* one atomic per shape and bound instead of per warp (diagnostic) */ };
+       RT_BUILD_NO_WARP_AGGREGATION = 1u << 0,  /* one atomic per shape and bound instead of per warp / block (diagnostic) */
+       RT_BUILD_NO_SINGLE_BLOCK = 1u << 1       /* scenes of <= 2048 shapes also take the one-launch-per-phase path (diagnostic) */ };
 int rt_build_bvh(rt_ctx* ctx, int maxDepth, unsigned build_flags, int* nNodes_out, int* nIndices_out);
 int rt_get_bvh(rt_ctx* ctx, void* nodes_or_NULL, int nodeCapacity, int32_t* indices_or_NULL, int indexCapacity);
 float rt_last_build_ms(const rt_ctx* ctx);

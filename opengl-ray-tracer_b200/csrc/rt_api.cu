@@ -102,7 +102,7 @@ struct rt_ctx {
     // device-side BVH build (rt_build.cuh, K8): scratch tables and the emitted FlatNode[] / bvhIndices[]
     DevBuf<int> bInt; DevBuf<bld::u64> bKey; DevBuf<float> bBox; DevBuf<unsigned char> bFlag; DevBuf<bld::Ctl> bCtl;
     DevBuf<rt_flat_node> bNodes; DevBuf<int32_t> bIdx; DevBuf<float4> bRec;
-    std::vector<rt_flat_node> bHostNodes; std::vector<int32_t> bHostIdx;
+    PinBuf<rt_flat_node> bHostNodes; PinBuf<int32_t> bHostIdx; int bNodeCount = 0, bIdxCount = 0;   // pinned: the tree comes back at PCIe speed
     bool shapesOnDevice = false;      // the pending host range [shapeLo, shapeHi) has already been copied (rt_build_bvh)
     float lastBuildMs = 0.f;
     cudaEvent_t evBuild[2] = {nullptr, nullptr};
@@ -441,7 +441,7 @@ void rt_destroy(rt_ctx* c) {
     c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
     c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
     for (auto& e : c->evBuild) if (e) cudaEventDestroy(e);
-    c->bInt.release(); c->bKey.release(); c->bBox.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release(); c->bRec.release();
+    c->bInt.release(); c->bKey.release(); c->bBox.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release(); c->bRec.release(); c->bHostNodes.release(); c->bHostIdx.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     for (auto& e : c->evFrame) if (e) cudaEventDestroy(e);
     c->image2.release(); c->ids2.release();
@@ -924,11 +924,12 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
     CU(c, cudaSetDevice(c->device));
     const int n = c->nShapes;
     if (n == 0) {                                   // buildBVH over nothing: one empty leaf (main.cpp:1175-1193)
-        c->bHostNodes.assign(1, rt_flat_node{});
-        rt_flat_node& r = c->bHostNodes[0];
+        CU(c, c->bHostNodes.reserve(1, 0));
+        c->bNodeCount = 1; c->bIdxCount = 0;
+        rt_flat_node& r = c->bHostNodes.p[0];
+        std::memset(&r, 0, sizeof r);
         for (int k = 0; k < 3; ++k) { r.boundsMin[k] = INFINITY; r.boundsMax[k] = -INFINITY; }
         r.leftChild = r.rightChild = -1;
-        c->bHostIdx.clear();
     } else {
         // the device copy of the shapes must be current: push the pending host range now (flush_scene will not repeat it)
         if (c->shapeHi > c->shapeLo && !c->shapesOnDevice) {
@@ -958,46 +959,70 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         cudaStream_t st = c->stream;
         for (auto& e : c->evBuild) if (!e) CU(c, cudaEventCreate(&e));
         cudaEventRecord(c->evBuild[0], st);
-        bld_setup_kernel<<<1, 32, 0, st>>>(B, n, maxDepth);
-        bld_init_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, agg);
-        bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, -1);
-        c->launches += 3;
-        for (int level = 0; level < maxDepth; ++level) {
-            bld_classify_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
-            bld_scan_blocks_kernel<<<1, 1024, 0, st>>>(B, n, nBlocks, level);
-            bld_scan_apply_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
-            bld_heads_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
-            bld_scatter_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level, agg);
-            bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
-            c->launches += 6;
+        int nNodes = 0;
+        if (n <= RT_BLD_SMALL_MAX && !(flags & RT_BUILD_NO_SINGLE_BLOCK)) {
+            // launch-bound sizes: one block runs the whole build and stops at the first level with nothing pending
+            bld_small_kernel<<<1, RT_BLD_SMALL_THREADS, 0, st>>>(B, c->dShapes.p, n, maxDepth, c->bNodes.p, c->bIdx.p);
+            c->launches += 1;
+            cudaEventRecord(c->evBuild[1], st);
+            CU(c, cudaGetLastError());
+            CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CU(c, cudaStreamSynchronize(st));
+            if (nNodes < 1 || (size_t)nNodes > maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
+        } else {
+            bld_setup_kernel<<<1, 32, 0, st>>>(B, n, maxDepth);
+            bld_init_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, agg);
+            bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, -1, maxDepth);
+            c->launches += 3;
+            // Every shape alone is reached after about log2(n) levels of a balanced tree; from a few levels past that
+            // on, every 8th level first asks the device whether anything is still pending (a level with nothing
+            // pending costs six empty launches, the question one small round trip).
+            int firstAsk = 4;
+            while ((1 << (firstAsk - 4)) < n && firstAsk < 36) ++firstAsk;
+            for (int level = 0; level < maxDepth; ++level) {
+                if (level >= firstAsk && (level - firstAsk) % 8 == 0) {
+                    int active = 1;
+                    CU(c, cudaMemcpyAsync(&active, &c->bCtl.p->active[level], sizeof(int), cudaMemcpyDeviceToHost, st));
+                    CU(c, cudaStreamSynchronize(st));
+                    if (!active) break;
+                }
+                bld_classify_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
+                bld_scan_blocks_kernel<<<1, 1024, 0, st>>>(B, n, nBlocks, level);
+                bld_scan_apply_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
+                bld_heads_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
+                bld_scatter_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level, agg);
+                bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level, maxDepth);
+                c->launches += 6;
+            }
+            CU(c, cudaGetLastError());
+            // the one host round trip: how many nodes there are
+            CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CU(c, cudaStreamSynchronize(st));
+            if (nNodes < 1 || (size_t)nNodes > maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
+            const int nb = (nNodes + RT_BLD_THREADS - 1) / RT_BLD_THREADS;
+            CU(c, cudaMemsetAsync(B.N.arrived, 0, (size_t)nNodes * sizeof(unsigned), st));
+            bld_desc_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
+            bld_number_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
+            bld_emit_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes, c->bNodes.p, c->bIdx.p);
+            c->launches += 3;
+            cudaEventRecord(c->evBuild[1], st);
+            CU(c, cudaGetLastError());
         }
-        CU(c, cudaGetLastError());
-        int nNodes = 0;                              // the one host round trip: how many nodes there are
-        CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
-        CU(c, cudaStreamSynchronize(st));
-        if (nNodes < 1 || (size_t)nNodes > maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
-        const int nb = (nNodes + RT_BLD_THREADS - 1) / RT_BLD_THREADS;
-        CU(c, cudaMemsetAsync(B.N.arrived, 0, (size_t)nNodes * sizeof(unsigned), st));
-        bld_desc_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
-        bld_number_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
-        bld_emit_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes, c->bNodes.p, c->bIdx.p);
-        c->launches += 3;
-        cudaEventRecord(c->evBuild[1], st);
-        CU(c, cudaGetLastError());
-        c->bHostNodes.resize((size_t)nNodes); c->bHostIdx.resize((size_t)n);
-        CU(c, cudaMemcpyAsync(c->bHostNodes.data(), c->bNodes.p, (size_t)nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost, st));
-        CU(c, cudaMemcpyAsync(c->bHostIdx.data(), c->bIdx.p, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CU(c, c->bHostNodes.reserve((size_t)nNodes, 0)); CU(c, c->bHostIdx.reserve((size_t)n, 0));
+        c->bNodeCount = nNodes; c->bIdxCount = n;
+        CU(c, cudaMemcpyAsync(c->bHostNodes.p, c->bNodes.p, (size_t)nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost, st));
+        CU(c, cudaMemcpyAsync(c->bHostIdx.p, c->bIdx.p, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         CU(c, cudaStreamSynchronize(st));
         cudaEventElapsedTime(&c->lastBuildMs, c->evBuild[0], c->evBuild[1]);
     }
     // hand the tree to the context exactly as an upload of these nodes and indices would
-    const bool sameIdx = c->bHostIdx.size() == c->indices.size() &&
-                         (c->bHostIdx.empty() || std::memcmp(c->bHostIdx.data(), c->indices.data(), c->bHostIdx.size() * sizeof(int32_t)) == 0);
-    if (!sameIdx) { c->indices = c->bHostIdx; c->topoDirty = true; }
-    int rc = set_nodes(c, c->bHostNodes.data(), (int)c->bHostNodes.size());
+    const bool sameIdx = (size_t)c->bIdxCount == c->indices.size() &&
+                         (c->bIdxCount == 0 || std::memcmp(c->bHostIdx.p, c->indices.data(), (size_t)c->bIdxCount * sizeof(int32_t)) == 0);
+    if (!sameIdx) { c->indices.assign(c->bHostIdx.p, c->bHostIdx.p + c->bIdxCount); c->topoDirty = true; }
+    int rc = set_nodes(c, c->bHostNodes.p, c->bNodeCount);
     if (rc != RT_OK) return rc;
-    if (nNodes_out) *nNodes_out = (int)c->bHostNodes.size();
-    if (nIndices_out) *nIndices_out = (int)c->bHostIdx.size();
+    if (nNodes_out) *nNodes_out = c->bNodeCount;
+    if (nIndices_out) *nIndices_out = c->bIdxCount;
     return RT_OK;
 }
 

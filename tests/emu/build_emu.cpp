@@ -45,7 +45,7 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
         bld::init_position(p, shapes, R, ord[0].data(), pnode[0].data(), k);
         bld::fold_keys(N.key, k);
     }
-    for (int p : threads(n)) bld::box_from_keys(p, pnode[0].data(), N);
+    for (int p : threads(n)) bld::box_from_keys(p, pnode[0].data(), N, maxDepth);
 
     for (int level = 0; level < maxDepth; ++level) {
         if (!ctl.active[level]) continue;
@@ -68,7 +68,7 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
             }
         }
         ctl.parity = nxt;
-        for (int p : threads(n)) bld::box_from_keys(p, pnode[nxt].data(), N);
+        for (int p : threads(n)) bld::box_from_keys(p, pnode[nxt].data(), N, maxDepth - (level + 1));
     }
     const int nNodes = ctl.nNodes;
     for (int id : threads(nNodes)) bld::count_descendants(id, N);

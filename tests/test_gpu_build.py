@@ -10,6 +10,8 @@ from util import random_shapes
 pytestmark = pytest.mark.gpu
 
 NO_AGG = 1      # RT_BUILD_NO_WARP_AGGREGATION
+NO_SINGLE = 2   # RT_BUILD_NO_SINGLE_BLOCK: small scenes also take the one-launch-per-phase path
+PATHS = [0, NO_SINGLE, NO_SINGLE | NO_AGG]
 
 
 def _same_frame(a, b):
@@ -17,7 +19,7 @@ def _same_frame(a, b):
 
 
 @pytest.mark.parametrize("name,n,depth", [("toy", 0, 15), ("monkey", 0, 15), ("car", 0, 25), ("soup", 60000, 40), ("monkey", 0, 2)])
-@pytest.mark.parametrize("flags", [0, NO_AGG])
+@pytest.mark.parametrize("flags", PATHS)
 def test_device_tree_is_the_host_tree(rt, name, n, depth, flags):
     W, H = 200, 150
     sc = rt.Scene(name, W, H, n_override=n, bvh_depth=depth)
@@ -52,7 +54,7 @@ def test_rebuild_per_frame_equals_host_rebuild(rt, name, depth):
         sc.animate(t, dt, mode=1)
         a.upload_scene(None, None, sc.shapes, sc.nodes, sc.indices)
         b.animate(t, dt)
-        nodes, idx = b.build_bvh(depth)
+        nodes, idx = b.build_bvh(depth, PATHS[frame % 3])
         assert nodes.tobytes() == np.ascontiguousarray(sc.nodes).tobytes(), "nodes, frame %d" % frame
         assert idx.tobytes() == np.ascontiguousarray(sc.indices).tobytes(), "indices, frame %d" % frame
         assert _same_frame(a.render(p), b.render(p)), "frame %d" % frame
@@ -86,7 +88,7 @@ def test_device_build_edge_cases(rt):
     tr = rt.RayTracer(64, 48)
     for shapes, depth in cases:
         ref = rt.Scene.from_shapes(shapes, light, cam, bvh_depth=depth)
-        for flags in (0, NO_AGG):
+        for flags in PATHS:
             tr.upload_scene(light, cam, shapes)
             nodes, idx = tr.build_bvh(depth, flags)
             assert nodes.tobytes() == np.ascontiguousarray(ref.nodes).tobytes(), (len(shapes), depth, flags)

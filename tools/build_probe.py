@@ -22,7 +22,7 @@ for name, n, depth in (("monkey", 0, 15), ("car", 0, 25), ("soup", soup_n, 40)):
     tr = rt.RayTracer(64, 48)
     tr.upload_scene(sc.light, sc.camera, sc.shapes)
     res = {}
-    for flags, label in ((0, "warp_aggregated"), (1, "plain_atomics")):
+    for flags, label in ((0, "default"), (2, "per_phase_launches"), (3, "per_phase_launches_plain_atomics")):
         dev, wall = [], []
         for _ in range(3):
             t0 = time.perf_counter()
