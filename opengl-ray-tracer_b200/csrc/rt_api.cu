@@ -100,7 +100,7 @@ struct rt_ctx {
     DevBuf<unsigned char> dAnimFlag; DevBuf<int> dIndices, dNodeAux; DevBuf<unsigned> dGrowArrived;   // dNodeAux: [parent nNodes | leaves nLeaves]
     int nLeavesRaw = 0;
     // device-side BVH build (rt_build.cuh, K8): scratch tables and the emitted FlatNode[] / bvhIndices[]
-    DevBuf<int> bInt; DevBuf<bld::u64> bKey; DevBuf<float> bBox; DevBuf<unsigned char> bFlag; DevBuf<bld::Ctl> bCtl;
+    DevBuf<int> bInt; DevBuf<bld::u64> bKey; DevBuf<unsigned char> bFlag; DevBuf<bld::Ctl> bCtl;
     DevBuf<rt_flat_node> bNodes; DevBuf<int32_t> bIdx; DevBuf<float4> bRec;
     PinBuf<rt_flat_node> bHostNodes; PinBuf<int32_t> bHostIdx; int bNodeCount = 0, bIdxCount = 0;   // pinned: the tree comes back at PCIe speed
     bool shapesOnDevice = false;      // the pending host range [shapeLo, shapeHi) has already been copied (rt_build_bvh)
@@ -441,7 +441,7 @@ void rt_destroy(rt_ctx* c) {
     c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
     c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
     for (auto& e : c->evBuild) if (e) cudaEventDestroy(e);
-    c->bInt.release(); c->bKey.release(); c->bBox.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release(); c->bRec.release(); c->bHostNodes.release(); c->bHostIdx.release();
+    c->bInt.release(); c->bKey.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release(); c->bRec.release(); c->bHostNodes.release(); c->bHostIdx.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     for (auto& e : c->evFrame) if (e) cudaEventDestroy(e);
     c->image2.release(); c->ids2.release();
@@ -939,11 +939,12 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
             cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
             c->shapesOnDevice = true;
         }
-        const size_t maxNodes = 2 * (size_t)n;
+        const size_t maxNodes = 2 * (size_t)n;     // build ids 0 .. 2n - 2
         const int nBlocks = (n + RT_BLD_THREADS - 1) / RT_BLD_THREADS;
-        // int tables: 8 per node + arrived, 2 orders + 2 node maps + scan (n + 1), block sums
+        const int nIds = 2 * n, idBlocks = (nIds + RT_BLD_THREADS - 1) / RT_BLD_THREADS;
+        // int tables: 8 per id + arrived, 2 orders + 2 node maps + scan (n + 1), block sums
         const size_t nInt = 9 * maxNodes + 4 * (size_t)n + ((size_t)n + 1) + (size_t)nBlocks + 1;
-        CU(c, c->bInt.reserve(nInt)); CU(c, c->bKey.reserve(6 * maxNodes)); CU(c, c->bBox.reserve(6 * maxNodes));
+        CU(c, c->bInt.reserve(nInt)); CU(c, c->bKey.reserve(6 * maxNodes));
         CU(c, c->bFlag.reserve((size_t)n)); CU(c, c->bCtl.reserve(1));
         CU(c, c->bNodes.reserve(maxNodes)); CU(c, c->bIdx.reserve((size_t)n)); CU(c, c->bRec.reserve(3 * (size_t)n));
         BuildBufs B;
@@ -953,30 +954,23 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         B.N.arrived = reinterpret_cast<unsigned*>(q); q += maxNodes;
         B.ord[0] = q; q += n; B.ord[1] = q; q += n; B.pnode[0] = q; q += n; B.pnode[1] = q; q += n;
         B.scanL = q; q += (size_t)n + 1; B.bsum = q;
-        B.N.key = c->bKey.p; B.N.box = c->bBox.p; B.flag = c->bFlag.p; B.ctl = c->bCtl.p;
+        B.N.key = c->bKey.p; B.flag = c->bFlag.p; B.ctl = c->bCtl.p;
         B.R.cen = c->bRec.p; B.R.mn = c->bRec.p + n; B.R.mx = c->bRec.p + 2 * (size_t)n;
         const int agg = (flags & RT_BUILD_NO_WARP_AGGREGATION) ? 0 : 1;
         cudaStream_t st = c->stream;
         for (auto& e : c->evBuild) if (!e) CU(c, cudaEventCreate(&e));
         cudaEventRecord(c->evBuild[0], st);
-        int nNodes = 0;
         if (n <= RT_BLD_SMALL_MAX && !(flags & RT_BUILD_NO_SINGLE_BLOCK)) {
             // launch-bound sizes: one block runs the whole build and stops at the first level with nothing pending
             bld_small_kernel<<<1, RT_BLD_SMALL_THREADS, 0, st>>>(B, c->dShapes.p, n, maxDepth, c->bNodes.p, c->bIdx.p);
             c->launches += 1;
-            cudaEventRecord(c->evBuild[1], st);
-            CU(c, cudaGetLastError());
-            CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
-            CU(c, cudaStreamSynchronize(st));
-            if (nNodes < 1 || (size_t)nNodes > maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
         } else {
-            bld_setup_kernel<<<1, 32, 0, st>>>(B, n, maxDepth);
+            bld_setup_kernel<<<idBlocks, RT_BLD_THREADS, 0, st>>>(B, n, maxDepth);
             bld_init_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, agg);
-            bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, -1, maxDepth);
-            c->launches += 3;
+            c->launches += 2;
             // Every shape alone is reached after about log2(n) levels of a balanced tree; from a few levels past that
             // on, every 8th level first asks the device whether anything is still pending (a level with nothing
-            // pending costs six empty launches, the question one small round trip).
+            // pending costs four empty launches, the question one small round trip).
             int firstAsk = 4;
             while ((1 << (firstAsk - 4)) < n && firstAsk < 36) ++firstAsk;
             for (int level = 0; level < maxDepth; ++level) {
@@ -989,25 +983,20 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
                 bld_classify_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
                 bld_scan_blocks_kernel<<<1, 1024, 0, st>>>(B, n, nBlocks, level);
                 bld_scan_apply_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
-                bld_heads_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level);
-                bld_scatter_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level, agg);
-                bld_boxes_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level, maxDepth);
-                c->launches += 6;
+                bld_split_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, n, level, agg);
+                c->launches += 4;
             }
-            CU(c, cudaGetLastError());
-            // the one host round trip: how many nodes there are
-            CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
-            CU(c, cudaStreamSynchronize(st));
-            if (nNodes < 1 || (size_t)nNodes > maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
-            const int nb = (nNodes + RT_BLD_THREADS - 1) / RT_BLD_THREADS;
-            CU(c, cudaMemsetAsync(B.N.arrived, 0, (size_t)nNodes * sizeof(unsigned), st));
-            bld_desc_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
-            bld_number_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes);
-            bld_emit_kernel<<<nb, RT_BLD_THREADS, 0, st>>>(B, nNodes, c->bNodes.p, c->bIdx.p);
+            bld_desc_kernel<<<idBlocks, RT_BLD_THREADS, 0, st>>>(B, nIds);
+            bld_number_kernel<<<idBlocks, RT_BLD_THREADS, 0, st>>>(B, nIds);
+            bld_emit_kernel<<<idBlocks, RT_BLD_THREADS, 0, st>>>(B, nIds, c->bNodes.p, c->bIdx.p);
             c->launches += 3;
-            cudaEventRecord(c->evBuild[1], st);
-            CU(c, cudaGetLastError());
         }
+        cudaEventRecord(c->evBuild[1], st);
+        CU(c, cudaGetLastError());
+        int nNodes = 0;                                // the numbering pass knows how many nodes there are
+        CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CU(c, cudaStreamSynchronize(st));
+        if (nNodes < 1 || (size_t)nNodes >= maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
         CU(c, c->bHostNodes.reserve((size_t)nNodes, 0)); CU(c, c->bHostIdx.reserve((size_t)n, 0));
         c->bNodeCount = nNodes; c->bIdxCount = n;
         CU(c, cudaMemcpyAsync(c->bHostNodes.p, c->bNodes.p, (size_t)nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost, st));

@@ -11,13 +11,13 @@
 //
 //   per level   classify  every shape of a pending node: centre[axis] < splitPos (the host's fp32 operations)
 //               scan      exclusive prefix sum of the "left" flags over the whole position array
-//               heads     the first position of each pending node decides (both sides non-empty, depth left)
-//                         and allocates the two children
-//               scatter   stable partition inside each node's segment; every shape folds its points into
-//                         its child's box with 64-bit atomicMin / atomicMax on (ordered value, sequence) keys:
-//                         min / max are exact and the key's low word keeps "first in list order wins among
-//                         equal values", i.e. the sign of a zero the host's `x < mn ? x : mn` would keep
-//               boxes     the keys become floats
+//               split     every position works out from the scan whether its node splits (both sides non-empty),
+//                         where the stable partition puts it and which child (ids follow from the boundary
+//                         position, no counter) owns it; the node's first position records the decision; every
+//                         shape folds its points into its child's box with 64-bit atomicMin / atomicMax on
+//                         (ordered value, sequence) keys: min / max are exact and the key's low word keeps "first
+//                         in list order wins among equal values", i.e. the sign of a zero the host's
+//                         `x < mn ? x : mn` would keep.  The keys ARE the boxes: readers decode them.
 //   then        desc      descendants per node, leaves upwards (second arrival at a parent adds its children)
 //               number    the reference's node index and startShapeIdx of every node from the sums along
 //                         its path to the root
@@ -38,6 +38,7 @@ typedef unsigned long long u64;
 
 #define RT_BLD_PENDING (-2)
 #define RT_BLD_LEAF (-1)
+#define RT_BLD_ABSENT (-3)
 
 #ifdef __CUDACC__
 RT_DEV void amin64(u64* p, u64 v) { atomicMin(p, v); }
@@ -60,15 +61,14 @@ inline unsigned f2u(float f) { unsigned u; memcpy(&u, &f, 4); return u; }
 inline float u2f(unsigned u) { float f; memcpy(&f, &u, 4); return f; }
 #endif
 
-// Build-time node table, indexed by build id: root = 0, the children of one node are (id, id + 1).
+// Build-time node table, indexed by build id (see setup_id): root = 0, the children of one node are (id, id + 1).
 struct Nodes {
     int* start;        // first position of the node's segment in the position array
     int* count;        // shapes in the segment (= numShapes of the flat node, inner nodes too)
-    int* left;         // RT_BLD_PENDING, RT_BLD_LEAF or the build id of the left child
+    int* left;         // RT_BLD_ABSENT, RT_BLD_PENDING, RT_BLD_LEAF or the build id of the left child
     int* parent;       // build id, -1 at the root
     int* depth;        // depth budget left (split's `depth` argument)
     u64* key;          // 6 per node: min x y z, max x y z as (ordered value << 32 | sequence)
-    float* box;        // 6 per node
     int* desc;         // number of descendants
     unsigned* arrived; // counters of the upward pass
     int* idx;          // index in the reference's node array
@@ -77,7 +77,7 @@ struct Nodes {
 
 // Control words on the device.
 struct Ctl {
-    int nNodes;        // build ids handed out so far
+    int nNodes;        // number of nodes of the finished tree (written by the numbering pass)
     int parity;        // which of the two position arrays holds the final order
     int active[66];    // active[L]: some node is pending at level L
 };
@@ -186,10 +186,16 @@ RT_DEV bool goes_left(float4 cen, const float* box) {
 RT_DEV bool is_head(int p, const int* pnode) { return p == 0 || pnode[p - 1] != pnode[p]; }
 
 // ---- per-thread bodies of the level loop -------------------------------------------------------------------
-RT_DEV void setup_root(const Nodes& N, Ctl* ctl, int n, int maxDepth) {
+// Build ids.  The root is 0.  A node whose segment [start, start + count) splits after nL shapes gets the children
+// (2q - 1, 2q) with q = start + nL, the first position of the right child: a boundary between two positions is created
+// at most once in a build, so the ids are unique without a counter, lie in [1, 2n - 2], siblings are neighbours, and
+// every position of the node can compute its child's id on its own.  Ids nobody created stay RT_BLD_ABSENT.
+RT_DEV void setup_id(int id, const Nodes& N, Ctl* ctl, int n, int maxDepth) {
+    for (int a = 0; a < 3; ++a) { N.key[6 * (size_t)id + a] = RT_BLD_KEY_MIN_ID; N.key[6 * (size_t)id + 3 + a] = RT_BLD_KEY_MAX_ID; }
+    N.arrived[id] = 0u;
+    if (id != 0) { N.left[id] = RT_BLD_ABSENT; return; }
     N.start[0] = 0; N.count[0] = n; N.parent[0] = -1; N.depth[0] = maxDepth;
     N.left[0] = maxDepth > 0 ? RT_BLD_PENDING : RT_BLD_LEAF;
-    for (int a = 0; a < 3; ++a) { N.key[a] = RT_BLD_KEY_MIN_ID; N.key[3 + a] = RT_BLD_KEY_MAX_ID; }
     ctl->nNodes = 1; ctl->parity = 0;
     for (int l = 0; l < 66; ++l) ctl->active[l] = 0;
     ctl->active[0] = maxDepth > 0 ? 1 : 0;
@@ -205,56 +211,49 @@ RT_DEV void init_position(int p, const rt_flat_shape* __restrict__ shapes, const
     record_keys(mn, mx, (unsigned)p, k);
 }
 
+RT_DEV void node_box(const Nodes& N, int node, float box[6]) {
+#pragma unroll
+    for (int a = 0; a < 6; ++a) box[a] = key_value(N.key[6 * (size_t)node + a]);
+}
+
 RT_DEV int classify(int p, const Records& R, const int* ord, const int* pnode, const Nodes& N) {
     const int node = pnode[p];
     if (N.left[node] != RT_BLD_PENDING) return 0;
-    return goes_left(R.cen[ord[p]], N.box + 6 * (size_t)node) ? 1 : 0;
+    float box[6];
+    node_box(N, node, box);
+    return goes_left(R.cen[ord[p]], box) ? 1 : 0;
 }
 
-// scanL: exclusive prefix sums of the flags, n + 1 entries.  head_decide: is p the first position of a pending node
-// that splits (both sides non-empty)?  A pending node that does not becomes a leaf here.
-RT_DEV bool head_decide(int p, const int* pnode, const int* scanL, const Nodes& N, int& node, int& nL, int& cnt) {
-    if (!is_head(p, pnode)) return false;
-    node = pnode[p];
-    if (N.left[node] != RT_BLD_PENDING) return false;
-    cnt = N.count[node];
-    nL = scanL[p + cnt] - scanL[p];
-    if (nL == 0 || nL == cnt) { N.left[node] = RT_BLD_LEAF; return false; }  // "no reason to split anymore" (:1156-1161)
-    return true;
-}
-// the two children (l, l + 1) of `node`, whose segment starts at p
-RT_DEV void head_split(int p, int level, int node, int nL, int cnt, int l, const Nodes& N, Ctl* ctl) {
+// scanL: exclusive prefix sums of the flags, n + 1 entries.  Position p of a pending node: does the node split (both
+// sides non-empty, :1156-1161), where does p go, which node owns it then.  The node's first position also records
+// the decision: a leaf, or the two children (whose keys are still the identity from setup_id; the shapes fold
+// their bounds in during this very sweep).
+RT_DEV void split_position(int p, int flag, int level, const int* pnode, const int* scanL, const Nodes& N, Ctl* ctl,
+                           int& newPos, int& newNode, bool& moved) {
+    const int node = pnode[p];
+    newPos = p; newNode = node; moved = false;
+    if (N.left[node] == RT_BLD_LEAF) return;             // decided at an earlier level (or by its first position just now)
+    const int st = N.start[node], cnt = N.count[node];
+    const int nL = scanL[st + cnt] - scanL[st];
+    const bool first = p == st;
+    if (nL == 0 || nL == cnt) { if (first) N.left[node] = RT_BLD_LEAF; return; }
+    const int q = st + nL, l = 2 * q - 1;
+    const int rankL = scanL[p] - scanL[st];
+    if (flag) { newPos = st + rankL; newNode = l; }
+    else { newPos = q + ((p - st) - rankL); newNode = l + 1; }
+    moved = true;
+    if (!first) return;
     const int d = N.depth[node] - 1;
     for (int s = 0; s < 2; ++s) {
         const int id = l + s;
-        N.start[id] = s == 0 ? p : p + nL;
+        N.start[id] = s == 0 ? st : q;
         N.count[id] = s == 0 ? nL : cnt - nL;
         N.parent[id] = node;
         N.depth[id] = d;
         N.left[id] = d > 0 ? RT_BLD_PENDING : RT_BLD_LEAF;                 // split(child, 0) makes a leaf (:1113-1118)
-        for (int a = 0; a < 3; ++a) { N.key[6 * (size_t)id + a] = RT_BLD_KEY_MIN_ID; N.key[6 * (size_t)id + 3 + a] = RT_BLD_KEY_MAX_ID; }
     }
     N.left[node] = l;
     if (d > 0) ctl->active[level + 1] = 1;
-}
-RT_DEV void head(int p, int level, const int* pnode, const int* scanL, const Nodes& N, Ctl* ctl) {
-    int node, nL, cnt;
-    if (!head_decide(p, pnode, scanL, N, node, nL, cnt)) return;
-    head_split(p, level, node, nL, cnt, aadd(&ctl->nNodes, 2), N, ctl);
-}
-
-// Where position p goes and which node it then belongs to; child < 0: it stays where it is.
-RT_DEV void scatter_target(int p, int flag, const int* pnode, const int* scanL, const Nodes& N,
-                           int& newPos, int& newNode, bool& moved) {
-    const int node = pnode[p];
-    const int l = N.left[node];
-    if (l < 0) { newPos = p; newNode = node; moved = false; return; }
-    const int st = N.start[node];
-    const int nL = scanL[st + N.count[node]] - scanL[st];
-    const int rankL = scanL[p] - scanL[st];
-    if (flag) { newPos = st + rankL; newNode = l; }
-    else { newPos = st + nL + ((p - st) - rankL); newNode = l + 1; }
-    moved = true;
 }
 
 RT_DEV void fold_keys(u64* nodeKeys, const u64 k[6]) {
@@ -265,17 +264,9 @@ RT_DEV void fold_keys(u64* nodeKeys, const u64 k[6]) {
     }
 }
 
-RT_DEV void box_from_keys(int p, const int* pnode, const Nodes& N, int depthOfNew) {
-    if (!is_head(p, pnode)) return;
-    const int node = pnode[p];
-    if (N.depth[node] != depthOfNew) return;             // older nodes have their boxes already
-#pragma unroll
-    for (int a = 0; a < 6; ++a) N.box[6 * (size_t)node + a] = key_value(N.key[6 * (size_t)node + a]);
-}
-
-// ---- numbering ---------------------------------------------------------------------------------------------
+// ---- numbering (over all 2n ids; absent ones do nothing) -------------------------------------------------------
 RT_DEV void count_descendants(int id, const Nodes& N) {
-    if (N.left[id] >= 0) return;                  // leaves start
+    if (N.left[id] != RT_BLD_LEAF) return;        // leaves start
     N.desc[id] = 0;
     for (int j = N.parent[id]; j >= 0; j = N.parent[j]) {
         fence();
@@ -291,8 +282,9 @@ RT_DEV int leaf_shapes_below(const Nodes& N, int id) { return N.left[id] >= 0 ? 
 // The reference pushes, for a node P whose descendants start at node index b and whose indices start at e:
 // [descendants of L] [descendants of R] L R.  Hence for a child: index and first bvhIndices entry follow from
 // b(P), e(P), and b / e of a node follow from its ancestors: a right child starts after its left sibling's block.
-RT_DEV void number_node(int id, const Nodes& N) {
-    if (id == 0) { N.idx[0] = N.desc[0]; N.first[0] = leaf_shapes_below(N, 0); return; }
+RT_DEV void number_node(int id, const Nodes& N, Ctl* ctl) {
+    if (N.left[id] == RT_BLD_ABSENT) return;
+    if (id == 0) { N.idx[0] = N.desc[0]; N.first[0] = leaf_shapes_below(N, 0); ctl->nNodes = N.desc[0] + 1; return; }
     const int par = N.parent[id];
     int b = 0, e = 0;
     for (int a = par; a != 0; a = N.parent[a]) {
@@ -307,8 +299,10 @@ RT_DEV void number_node(int id, const Nodes& N) {
 }
 
 RT_DEV void emit_node(int id, const Nodes& N, const int* ord, rt_flat_node* out, int32_t* indices) {
+    if (N.left[id] == RT_BLD_ABSENT) return;
     rt_flat_node f;
-    const float* b = N.box + 6 * (size_t)id;
+    float b[6];
+    node_box(N, id, b);
     f.boundsMin[0] = b[0]; f.boundsMin[1] = b[1]; f.boundsMin[2] = b[2]; f.padding1 = 0.f;
     f.boundsMax[0] = b[3]; f.boundsMax[1] = b[4]; f.boundsMax[2] = b[5]; f.padding2 = 0.f;
     const int l = N.left[id];
@@ -340,8 +334,9 @@ struct BuildBufs {
     int* bsum;           // one per block of RT_BLD_THREADS positions (+1)
 };
 
-__global__ void bld_setup_kernel(BuildBufs B, int n, int maxDepth) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) bld::setup_root(B.N, B.ctl, n, maxDepth);
+__global__ void bld_setup_kernel(BuildBufs B, int n, int maxDepth) {      // one thread per build id, 2n of them
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id < 2 * n) bld::setup_id(id, B.N, B.ctl, n, maxDepth);
 }
 
 // Warp-wide minimum (isMin) or maximum of 64-bit keys, two 32-bit REDUX steps: the high words, then the low words
@@ -430,14 +425,6 @@ __global__ void bld_init_kernel(BuildBufs B, const rt_flat_shape* __restrict__ s
     bld_fold_block(B.N.key, node, k, agg != 0);
 }
 
-__global__ void bld_boxes_kernel(BuildBufs B, int n, int level, int maxDepth) {      // level < 0: the root
-    if (level >= 0 && !B.ctl->active[level]) return;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
-    const int cur = level < 0 ? 0 : ((level + 1) & 1);
-    bld::box_from_keys(p, B.pnode[cur], B.N, maxDepth - (level + 1));
-}
-
 // classify + block totals of the flags
 __global__ void bld_classify_kernel(BuildBufs B, int n, int level) {
     if (!B.ctl->active[level]) return;
@@ -492,22 +479,8 @@ __global__ void bld_scan_apply_kernel(BuildBufs B, int n, int level) {
     if (p < n) B.scanL[p] = B.bsum[blockIdx.x] + before + __popc(bal & ((1u << lane) - 1u));
 }
 
-__global__ void bld_heads_kernel(BuildBufs B, int n, int level) {
-    if (!B.ctl->active[level]) return;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    // one atomicAdd per warp hands out the build ids of all the nodes its lanes split
-    int node = 0, nL = 0, cnt = 0;
-    const bool split = p < n && bld::head_decide(p, B.pnode[level & 1], B.scanL, B.N, node, nL, cnt);
-    const unsigned who = __ballot_sync(0xffffffffu, split);
-    if (who == 0u) return;
-    const int lane = threadIdx.x & 31, leader = __ffs(who) - 1;
-    int base = 0;
-    if (lane == leader) base = bld::aadd(&B.ctl->nNodes, 2 * __popc(who));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (split) bld::head_split(p, level, node, nL, cnt, base + 2 * __popc(who & ((1u << lane) - 1u)), B.N, B.ctl);
-}
-
-__global__ void bld_scatter_kernel(BuildBufs B, int n, int level, int agg) {
+// stable partition of every splitting node's segment + the node's decision (first position) + the children's boxes
+__global__ void bld_split_kernel(BuildBufs B, int n, int level, int agg) {
     if (!B.ctl->active[level]) return;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     const int cur = level & 1, nxt = cur ^ 1;
@@ -515,7 +488,7 @@ __global__ void bld_scatter_kernel(BuildBufs B, int n, int level, int agg) {
     int node = -1;
     if (p < n) {
         int newPos, newNode; bool moved;
-        bld::scatter_target(p, (int)B.flag[p], B.pnode[cur], B.scanL, B.N, newPos, newNode, moved);
+        bld::split_position(p, (int)B.flag[p], level, B.pnode[cur], B.scanL, B.N, B.ctl, newPos, newNode, moved);
         const int shape = B.ord[cur][p];
         B.ord[nxt][newPos] = shape;
         B.pnode[nxt][newPos] = newNode;
@@ -525,17 +498,17 @@ __global__ void bld_scatter_kernel(BuildBufs B, int n, int level, int agg) {
     if (p == 0) B.ctl->parity = nxt;
 }
 
-__global__ void bld_desc_kernel(BuildBufs B, int nNodes) {
+__global__ void bld_desc_kernel(BuildBufs B, int nIds) {
     const int id = blockIdx.x * blockDim.x + threadIdx.x;
-    if (id < nNodes) bld::count_descendants(id, B.N);
+    if (id < nIds) bld::count_descendants(id, B.N);
 }
-__global__ void bld_number_kernel(BuildBufs B, int nNodes) {
+__global__ void bld_number_kernel(BuildBufs B, int nIds) {
     const int id = blockIdx.x * blockDim.x + threadIdx.x;
-    if (id < nNodes) bld::number_node(id, B.N);
+    if (id < nIds) bld::number_node(id, B.N, B.ctl);
 }
-__global__ void bld_emit_kernel(BuildBufs B, int nNodes, rt_flat_node* __restrict__ out, int32_t* __restrict__ indices) {
+__global__ void bld_emit_kernel(BuildBufs B, int nIds, rt_flat_node* __restrict__ out, int32_t* __restrict__ indices) {
     const int id = blockIdx.x * blockDim.x + threadIdx.x;
-    if (id < nNodes) bld::emit_node(id, B.N, B.ord[B.ctl->parity], out, indices);
+    if (id < nIds) bld::emit_node(id, B.N, B.ord[B.ctl->parity], out, indices);
 }
 // ---- small scenes: the whole build in ONE block -----------------------------------------------------------
 // Up to RT_BLD_SMALL_MAX shapes (measured: 1240 shapes 0.28 vs 0.49 ms, 4122 shapes 0.80 vs 0.73 ms) the level loop is launch-bound (6 launches of a few microseconds per level), so one
@@ -549,7 +522,8 @@ bld_small_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, i
                  rt_flat_node* out, int32_t* indices) {
     __shared__ int warpSum[RT_BLD_SMALL_THREADS / 32];
     const int t = threadIdx.x, T = blockDim.x, lane = t & 31, w = t >> 5;
-    if (t == 0) bld::setup_root(B.N, B.ctl, n, maxDepth);
+    const int nIds = 2 * n;
+    for (int id = t; id < nIds; id += T) bld::setup_id(id, B.N, B.ctl, n, maxDepth);
     __syncthreads();
     for (int base = 0; base < n; base += T) {                          // whole warps stay together for the REDUX
         const int p = base + t;
@@ -563,8 +537,6 @@ bld_small_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, i
             if (lane == 0 && best != id) { if (isMin) bld::amin64(B.N.key + a, best); else bld::amax64(B.N.key + a, best); }
         }
     }
-    __syncthreads();
-    for (int p = t; p < n; p += T) bld::box_from_keys(p, B.pnode[0], B.N, maxDepth);
     __syncthreads();
     const int chunk = (n + T - 1) / T, lo = min(n, t * chunk), hi = min(n, lo + chunk);
     for (int level = 0; level < maxDepth; ++level) {
@@ -589,11 +561,9 @@ bld_small_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, i
         for (int p = lo; p < hi; ++p) { B.scanL[p] = run; run += (int)B.flag[p]; }
         if (t == T - 1) B.scanL[n] = warpSum[31];
         __syncthreads();
-        for (int p = t; p < n; p += T) bld::head(p, level, B.pnode[cur], B.scanL, B.N, B.ctl);
-        __syncthreads();
         for (int p = t; p < n; p += T) {
             int newPos, newNode; bool moved;
-            bld::scatter_target(p, (int)B.flag[p], B.pnode[cur], B.scanL, B.N, newPos, newNode, moved);
+            bld::split_position(p, (int)B.flag[p], level, B.pnode[cur], B.scanL, B.N, B.ctl, newPos, newNode, moved);
             const int shape = B.ord[cur][p];
             B.ord[nxt][newPos] = shape;
             B.pnode[nxt][newPos] = newNode;
@@ -605,18 +575,13 @@ bld_small_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, i
         }
         if (t == 0) B.ctl->parity = nxt;
         __syncthreads();
-        for (int p = t; p < n; p += T) bld::box_from_keys(p, B.pnode[nxt], B.N, maxDepth - (level + 1));
-        __syncthreads();
     }
-    const int nNodes = B.ctl->nNodes;
     const int* ord = B.ord[B.ctl->parity];
-    for (int id = t; id < nNodes; id += T) B.N.arrived[id] = 0u;
+    for (int id = t; id < nIds; id += T) bld::count_descendants(id, B.N);
     __syncthreads();
-    for (int id = t; id < nNodes; id += T) bld::count_descendants(id, B.N);
+    for (int id = t; id < nIds; id += T) bld::number_node(id, B.N, B.ctl);
     __syncthreads();
-    for (int id = t; id < nNodes; id += T) bld::number_node(id, B.N);
-    __syncthreads();
-    for (int id = t; id < nNodes; id += T) bld::emit_node(id, B.N, ord, out, indices);
+    for (int id = t; id < nIds; id += T) bld::emit_node(id, B.N, ord, out, indices);
 }
 #endif  // __CUDACC__
 

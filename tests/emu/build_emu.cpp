@@ -21,9 +21,8 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
     const size_t maxNodes = 2 * (size_t)n;
     std::vector<int> start(maxNodes), count(maxNodes), left(maxNodes), parent(maxNodes), depth(maxNodes), desc(maxNodes), idx(maxNodes), first(maxNodes);
     std::vector<bld::u64> key(6 * maxNodes);
-    std::vector<float> box(6 * maxNodes);
-    std::vector<unsigned> arrived(maxNodes, 0u);
-    bld::Nodes N{start.data(), count.data(), left.data(), parent.data(), depth.data(), key.data(), box.data(), desc.data(), arrived.data(), idx.data(), first.data()};
+        std::vector<unsigned> arrived(maxNodes, 0u);
+    bld::Nodes N{start.data(), count.data(), left.data(), parent.data(), depth.data(), key.data(), desc.data(), arrived.data(), idx.data(), first.data()};
     bld::Ctl ctl;
     std::vector<int> ord[2] = {std::vector<int>((size_t)n), std::vector<int>((size_t)n)};
     std::vector<int> pnode[2] = {std::vector<int>((size_t)n), std::vector<int>((size_t)n)};
@@ -39,14 +38,13 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
         return t;
     };
 
-    bld::setup_root(N, &ctl, n, maxDepth);
+    const int nIds = 2 * n;
+    for (int id : threads(nIds)) bld::setup_id(id, N, &ctl, n, maxDepth);
     for (int p : threads(n)) {
         bld::u64 k[6];
         bld::init_position(p, shapes, R, ord[0].data(), pnode[0].data(), k);
         bld::fold_keys(N.key, k);
     }
-    for (int p : threads(n)) bld::box_from_keys(p, pnode[0].data(), N, maxDepth);
-
     for (int level = 0; level < maxDepth; ++level) {
         if (!ctl.active[level]) continue;
         const int cur = level & 1, nxt = cur ^ 1;
@@ -54,10 +52,9 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
         int run = 0;
         for (int p = 0; p < n; ++p) { scanL[(size_t)p] = run; run += flag[(size_t)p]; }
         scanL[(size_t)n] = run;
-        for (int p : threads(n)) bld::head(p, level, pnode[cur].data(), scanL.data(), N, &ctl);
         for (int p : threads(n)) {
             int newPos, newNode; bool moved;
-            bld::scatter_target(p, flag[(size_t)p], pnode[cur].data(), scanL.data(), N, newPos, newNode, moved);
+            bld::split_position(p, flag[(size_t)p], level, pnode[cur].data(), scanL.data(), N, &ctl, newPos, newNode, moved);
             const int shape = ord[cur][(size_t)p];
             ord[nxt][(size_t)newPos] = shape;
             pnode[nxt][(size_t)newPos] = newNode;
@@ -68,11 +65,10 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
             }
         }
         ctl.parity = nxt;
-        for (int p : threads(n)) bld::box_from_keys(p, pnode[nxt].data(), N, maxDepth - (level + 1));
     }
+    for (int id : threads(nIds)) bld::count_descendants(id, N);
+    for (int id : threads(nIds)) bld::number_node(id, N, &ctl);
+    for (int id : threads(nIds)) bld::emit_node(id, N, ord[ctl.parity].data(), outNodes, outIdx);
     const int nNodes = ctl.nNodes;
-    for (int id : threads(nNodes)) bld::count_descendants(id, N);
-    for (int id : threads(nNodes)) bld::number_node(id, N);
-    for (int id : threads(nNodes)) bld::emit_node(id, N, ord[ctl.parity].data(), outNodes, outIdx);
     return nNodes;
 }
