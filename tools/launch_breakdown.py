@@ -19,5 +19,5 @@ T = sum(tot.values())
 for n in sorted(tot, key=lambda q: -tot[q]):
     print("%-28s %4d launches %9.1f us %5.1f%%" % (n, cnt[n], tot[n], 100 * tot[n] / T))
 print("total %.1f us over %d launches" % (T, len(one)))
-for key in ("scatter", "classify", "heads", "boxes"):
+for key in ("split", "scatter", "classify", "heads", "boxes"):
     print(key, [round(v, 1) for n, v in one if key in n])
