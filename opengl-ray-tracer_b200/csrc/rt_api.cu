@@ -13,6 +13,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <utility>
 #include <vector>
 
 using namespace rt;
@@ -373,12 +374,18 @@ bool same_topology(const rt_flat_node* a, const rt_flat_node* b, int n) {
     return true;
 }
 
-int set_nodes(rt_ctx* c, const void* nodes, int nNodes) {
+// adopt != NULL: `nodes` is adopt->p, a pinned buffer of this context (the device builder's staging): it BECOMES the
+// shadow by a pointer swap instead of being copied into it.
+int set_nodes(rt_ctx* c, const void* nodes, int nNodes, PinBuf<rt_flat_node>* adopt = nullptr) {
     const rt_flat_node* in = static_cast<const rt_flat_node*>(nodes);
     const bool sameTopo = c->haveScene && nNodes == c->nNodes && !c->topoDirty && same_topology(in, c->hNodes.p, nNodes);
     wait_copies(c);
-    CU(c, c->hNodes.reserve((size_t)nNodes, 0));
-    if (nNodes > 0) std::memcpy(c->hNodes.p, in, (size_t)nNodes * sizeof(rt_flat_node));
+    if (adopt) {
+        std::swap(c->hNodes, *adopt);
+    } else {
+        CU(c, c->hNodes.reserve((size_t)nNodes, 0));
+        if (nNodes > 0) std::memcpy(c->hNodes.p, in, (size_t)nNodes * sizeof(rt_flat_node));
+    }
     c->nNodes = nNodes;
     c->boxesFinite = true;            // NaN-free slab fast path needs |bound| <= 1e37 everywhere
     for (int i = 0; i < nNodes && c->boxesFinite; ++i)
@@ -1008,7 +1015,7 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
     const bool sameIdx = (size_t)c->bIdxCount == c->indices.size() &&
                          (c->bIdxCount == 0 || std::memcmp(c->bHostIdx.p, c->indices.data(), (size_t)c->bIdxCount * sizeof(int32_t)) == 0);
     if (!sameIdx) { c->indices.assign(c->bHostIdx.p, c->bHostIdx.p + c->bIdxCount); c->topoDirty = true; }
-    int rc = set_nodes(c, c->bHostNodes.p, c->bNodeCount);
+    int rc = set_nodes(c, c->bHostNodes.p, c->bNodeCount, &c->bHostNodes);
     if (rc != RT_OK) return rc;
     if (nNodes_out) *nNodes_out = c->bNodeCount;
     if (nIndices_out) *nIndices_out = c->bIdxCount;
