@@ -19,9 +19,11 @@
 //     order the sub-tree presents them in.
 #pragma once
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "../../include/rt_flat.h"
@@ -204,65 +206,142 @@ struct SubBuilder {
     int maxLeaf = RT_SUB_LEAF;
     SubBuilder(const std::vector<Box>& b, std::vector<int>& it) : pb(b), items(it) {}
 
-    int build(int first, int count) {
-        const int id = (int)nodes.size();
-        nodes.emplace_back();
+    // The builder works on records (item, bound) that travel with the permutation, so that every sweep over a node's
+    // items is a sequential read; the centroid of a bound is recomputed where it is needed (same expression, same value).
+    struct Rec { int item; Box b; };
+    static constexpr int NB = 16;
+    static int bin_of(double c, double lo, double ext) {
+        int k = (int)((c - lo) / ext * NB);
+        return k < 0 ? 0 : k >= NB ? NB - 1 : k;
+    }
+    static double centroid(const Box& b, int a) { return 0.5 * ((double)b.mn[a] + b.mx[a]); }
+
+    struct Task { int node, first, count; };          // a node whose subtree another thread builds
+
+    // One node over recs[first, first + count): bounds, binned-SAH split, stable partition.  Returns the split
+    // position, or -1 for a leaf.  `out` receives the node's fields.
+    int split_node(Rec* recs, Rec* scratch, int first, int count, SubNode& out) const {
         Box bb; bb.reset();
         Box cb; cb.reset();
         for (int i = first; i < first + count; ++i) {
-            const Box& b = pb[(size_t)items[(size_t)i]];
+            const Box& b = recs[i].b;
             bb.grow(b);
-            double c[3] = {0.5 * ((double)b.mn[0] + b.mx[0]), 0.5 * ((double)b.mn[1] + b.mx[1]), 0.5 * ((double)b.mn[2] + b.mx[2])};
+            const double c[3] = {centroid(b, 0), centroid(b, 1), centroid(b, 2)};
             cb.grow(c);
         }
-        nodes[(size_t)id].box = bb; nodes[(size_t)id].first = first; nodes[(size_t)id].count = count;
-        if (count <= maxLeaf) return id;
-        // binned SAH over the centroid bounds
-        const int NB = 16;
+        out.box = bb; out.first = first; out.count = count; out.left = out.right = -1;
+        if (count <= maxLeaf) return -1;
+        // binned SAH over the centroid bounds: one sweep over the items fills the bins of all three axes.  Only the
+        // bins that received something are reset, accumulated and evaluated: an empty bin changes neither side of a
+        // split, and of the candidates between two occupied bins the first one (the lower bin itself) is the one a
+        // scan over all NB - 1 candidates would keep — most nodes of a deep tree hold a handful of items.
+        Box bins[3][NB]; int cnt[3][NB];
+        double lo[3], ext[3]; unsigned occ[3] = {0u, 0u, 0u};
+        for (int a = 0; a < 3; ++a) { lo[a] = cb.mn[a]; ext[a] = (double)cb.mx[a] - lo[a]; }
+        for (int i = first; i < first + count; ++i) {
+            const Box& b = recs[i].b;
+            for (int a = 0; a < 3; ++a) {
+                if (!(ext[a] > 0)) continue;
+                const int k = bin_of(centroid(b, a), lo[a], ext[a]);
+                if (!((occ[a] >> k) & 1u)) { bins[a][k].reset(); cnt[a][k] = 0; occ[a] |= 1u << k; }
+                bins[a][k].grow(b); cnt[a][k]++;
+            }
+        }
         int bestAxis = -1, bestSplit = -1; double bestCost = INFINITY;
         for (int a = 0; a < 3; ++a) {
-            const double lo = cb.mn[a], ext = (double)cb.mx[a] - lo;
-            if (!(ext > 0)) continue;
-            Box bins[NB]; int cnt[NB];
-            for (int b = 0; b < NB; ++b) { bins[b].reset(); cnt[b] = 0; }
-            for (int i = first; i < first + count; ++i) {
-                const Box& b = pb[(size_t)items[(size_t)i]];
-                int k = (int)((0.5 * ((double)b.mn[a] + b.mx[a]) - lo) / ext * NB);
-                k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
-                bins[k].grow(b); cnt[k]++;
-            }
-            double rightArea[NB]; int rightCnt[NB];
+            if (!(ext[a] > 0)) continue;
+            int ks[NB], m = 0;
+            for (int k = 0; k < NB; ++k) if ((occ[a] >> k) & 1u) ks[m++] = k;
+            double rightArea[NB]; int rightCnt[NB];                  // of the occupied bins i .. m-1
             Box acc; acc.reset(); int n = 0;
-            for (int b = NB - 1; b > 0; --b) { acc.grow(bins[b]); n += cnt[b]; rightArea[b] = acc.area(); rightCnt[b] = n; }
+            for (int i = m - 1; i > 0; --i) { acc.grow(bins[a][ks[i]]); n += cnt[a][ks[i]]; rightArea[i] = acc.area(); rightCnt[i] = n; }
             acc.reset(); n = 0;
-            for (int b = 0; b < NB - 1; ++b) {
-                acc.grow(bins[b]); n += cnt[b];
-                if (n == 0 || rightCnt[b + 1] == 0) continue;
-                const double cost = acc.area() * n + rightArea[b + 1] * rightCnt[b + 1];
-                if (cost < bestCost) { bestCost = cost; bestAxis = a; bestSplit = b; }
+            for (int i = 0; i + 1 < m; ++i) {
+                acc.grow(bins[a][ks[i]]); n += cnt[a][ks[i]];
+                const double cost = acc.area() * n + rightArea[i + 1] * rightCnt[i + 1];
+                if (cost < bestCost) { bestCost = cost; bestAxis = a; bestSplit = ks[i]; }
             }
         }
         int mid;
         if (bestAxis < 0) {
             mid = first + count / 2;                                        // identical centroids: split by count
         } else {
+            // stable partition: bins <= bestSplit first, both sides in their old order
             const int a = bestAxis;
-            const double lo = cb.mn[a], ext = (double)cb.mx[a] - lo;
-            auto binOf = [&](int item) {
-                const Box& b = pb[(size_t)item];
-                int k = (int)((0.5 * ((double)b.mn[a] + b.mx[a]) - lo) / ext * NB);
-                return k < 0 ? 0 : k >= NB ? NB - 1 : k;
-            };
-            auto it = std::stable_partition(items.begin() + first, items.begin() + first + count, [&](int item) { return binOf(item) <= bestSplit; });
-            mid = (int)(it - items.begin());
+            int w = first, r = first;
+            for (int i = first; i < first + count; ++i) {
+                if (bin_of(centroid(recs[i].b, a), lo[a], ext[a]) <= bestSplit) recs[w++] = recs[i];
+                else scratch[r++] = recs[i];
+            }
+            mid = w;
+            std::copy(scratch + first, scratch + r, recs + w);
             if (mid == first || mid == first + count) mid = first + count / 2;
         }
-        const int l = build(first, mid - first);
-        const int r = build(mid, first + count - mid);
-        nodes[(size_t)id].left = l; nodes[(size_t)id].right = r;
+        return mid;
+    }
+
+    // Subtree over recs[first, first + count) into `out` (ids local to `out`); ranges of more than `defer` items below
+    // the root of this call are not descended into but listed in `tasks` (defer <= 0: never).
+    int build_rec(Rec* recs, Rec* scratch, int first, int count, std::vector<SubNode>& out, int defer, std::vector<Task>* tasks, bool root) const {
+        const int id = (int)out.size();
+        out.emplace_back();
+        if (!root && tasks && count > maxLeaf && count <= defer) { tasks->push_back({id, first, count}); return id; }
+        SubNode nd;
+        const int mid = split_node(recs, scratch, first, count, nd);
+        out[(size_t)id] = nd;
+        if (mid < 0) return id;
+        const int l = build_rec(recs, scratch, first, mid - first, out, defer, tasks, false);
+        const int r = build_rec(recs, scratch, mid, first + count - mid, out, defer, tasks, false);
+        out[(size_t)id].left = l; out[(size_t)id].right = r;
         return id;
     }
+
+    int build(int first, int count);
 };
+
+// Large ranges (the tree over a million reference leaves) are split among the host's cores: the top of the tree is
+// built here until the ranges are small, the subtrees below are independent (disjoint record ranges) and are built by
+// worker threads into their own node lists, which are appended afterwards.  Node ids differ from a sequential build,
+// the TREE (boxes, children, item order) is the same, and only that reaches the layout.
+inline int SubBuilder::build(int first, int count) {
+    if (count <= 0) return -1;
+    std::vector<Rec> recs((size_t)count), scratch((size_t)count);
+    for (int i = 0; i < count; ++i) { recs[(size_t)i].item = items[(size_t)(first + i)]; recs[(size_t)i].b = pb[(size_t)recs[(size_t)i].item]; }
+    const int base = (int)nodes.size();
+    std::vector<Task> tasks;
+    unsigned hw = std::thread::hardware_concurrency();
+    const int nThreads = count >= (1 << 16) ? (int)(hw == 0 ? 1 : hw > 16 ? 16 : hw) : 1;
+    const int root = build_rec(recs.data(), scratch.data(), 0, count, nodes, nThreads > 1 ? count / (4 * nThreads) : 0, nThreads > 1 ? &tasks : nullptr, true);
+    if (!tasks.empty()) {
+        std::vector<std::vector<SubNode>> local(tasks.size());
+        std::atomic<size_t> next{0};
+        auto work = [&]() {
+            for (size_t t = next.fetch_add(1); t < tasks.size(); t = next.fetch_add(1))
+                build_rec(recs.data(), scratch.data(), tasks[t].first, tasks[t].count, local[t], 0, nullptr, true);
+        };
+        std::vector<std::thread> pool;
+        try { for (int t = 1; t < nThreads; ++t) pool.emplace_back(work); }
+        catch (...) {}                                       // no more threads to be had: the ones we got (and this one) do it
+        work();
+        for (auto& th : pool) th.join();
+        for (size_t t = 0; t < tasks.size(); ++t) {
+            // local[t][0] is the subtree's root: it takes the place of the placeholder node, the rest is appended
+            const int off = (int)nodes.size() - 1;               // local id j >= 1  ->  off + j
+            SubNode r = local[t][0];
+            if (r.left >= 0) { r.left += off; r.right += off; }
+            nodes[(size_t)tasks[t].node] = r;
+            for (size_t j = 1; j < local[t].size(); ++j) {
+                SubNode x = local[t][j];
+                if (x.left >= 0) { x.left += off; x.right += off; }
+                nodes.push_back(x);
+            }
+        }
+    }
+    // node ranges are relative to `first`; the permutation goes back into items
+    if (first != 0) for (size_t j = (size_t)base; j < nodes.size(); ++j) nodes[j].first += first;
+    for (int i = 0; i < count; ++i) items[(size_t)(first + i)] = recs[(size_t)i].item;
+    return root;
+}
 
 // ---------------------------------------------------------------------------
 // The layout.
@@ -323,6 +402,9 @@ inline bool build_layout(const rt_flat_node* nd, int nNodes, const int32_t* indi
     std::vector<int> treeSlot0;                           // first slot of the tree's bounded primitives
     std::vector<Item> st; st.push_back({nNodes - 1, 1, -1, -1});
     std::vector<int> parent;                              // emitted position of each emitted node's parent
+    L.src.reserve((size_t)nNodes); L.link.reserve((size_t)nNodes); L.cw.reserve((size_t)nNodes); parent.reserve((size_t)nNodes);
+    L.pshape.reserve(nIndices); L.prank.reserve(nIndices);
+    L.entryPos.reserve((size_t)nNodes / 2 + 1); L.entryRaw.reserve((size_t)nNodes / 2 + 1);
     const size_t limit = (size_t)nNodes * 4 + 64;
     size_t refEmitted = 0;
     int rank = 0;
