@@ -105,6 +105,23 @@ void* emu_create(const rt_flat_shape* shapes, int nShapes, const rt_flat_node* n
 }
 void emu_destroy(void* e) { delete static_cast<Emu*>(e); }
 
+// FNV-1a over every array of the layout (lists A and B, slots, boxes, refit graph): a regression handle on the
+// host-side builder — the render kernel's behaviour on the GPU was validated against exactly these layouts.
+unsigned long long emu_layout_hash(void* e) {
+    Emu* E = static_cast<Emu*>(e);
+    rtl::Layout& L = E->L;
+    rtl::build_refit_graph(L);
+    unsigned long long h = 1469598103934665603ull;
+    auto mix = [&](const void* p, size_t bytes) { const unsigned char* c = (const unsigned char*)p; for (size_t i = 0; i < bytes; ++i) { h ^= c[i]; h *= 1099511628211ull; } };
+    mix(L.src.data(), L.src.size() * 4); mix(L.link.data(), L.link.size() * 4); mix(L.cw.data(), L.cw.size() * 4);
+    mix(L.pshape.data(), L.pshape.size() * 4); mix(L.prank.data(), L.prank.size() * 4);
+    mix(L.subBox.data(), L.subBox.size() * sizeof(rtl::Box));
+    mix(L.srcB.data(), L.srcB.size() * 4); mix(L.linkB.data(), L.linkB.size() * 4); mix(L.cwB.data(), L.cwB.size() * 4);
+    mix(L.rfParent.data(), L.rfParent.size() * 4); mix(L.rfChild.data(), L.rfChild.size() * 4);
+    mix(L.rfLeaf.data(), L.rfLeaf.size() * 4); mix(L.rfStart.data(), L.rfStart.size() * 4);
+    return h;
+}
+
 // info: [0] emitted nodes [1] sub nodes [2] prims [3] fat leaves [4] max leaf size [5] nodes of list B (0 = unused)
 void emu_info(void* e, int out[6]) {
     out[5] = static_cast<Emu*>(e)->L.useB ? (int)static_cast<Emu*>(e)->L.srcB.size() : 0;

@@ -31,6 +31,7 @@ def emu():
     L.emu_refit.argtypes = [vp, vp, vp]; L.emu_refit.restype = ip
     L.emu_refit_graph_check.argtypes = [vp, vp, vp]; L.emu_refit_graph_check.restype = ip
     L.emu_query.argtypes = [vp, ip, vp, vp, ip, ip, vp, vp, vp, vp, vp]; L.emu_query.restype = None
+    L.emu_layout_hash.argtypes = [vp]; L.emu_layout_hash.restype = C.c_uint64
     return L
 
 
@@ -294,3 +295,18 @@ def test_axis_parallel_and_degenerate_rays(rt, oracle, emu):
             assert np.array_equal(gid, rid), "%s mt=%s: %d ids differ" % (name, mt, int((gid != rid).sum()))
             assert np.array_equal(gdist.view(np.uint32), rdist.view(np.uint32))
         e.close()
+
+
+# FNV-1a of every layout array (lists A / B, slots, boxes, refit graph), omax = 200, sub-trees and list B on.  These are
+# the layouts the render kernel was validated with on the B200; the values were produced by the builder as it was then
+# (commit 79331da) and by the record-based / multi-threaded SAH builder that replaced it — any change to rt_layout.h
+# that moves a single word shows up here.  soup 80 000 (> 65 536 reference leaves) takes the multi-threaded path.
+LAYOUT_HASHES = [("toy", 0, 0x0a6055fbc85e3700), ("triangle", 0, 0xcd9ed5b4917cac12), ("monkey", 0, 0x49a569ec8332fdfe),
+                 ("car", 0, 0xac2e7573db02538d), ("soup", 80000, 0xaee99b7a581aefff)]
+
+
+@pytest.mark.parametrize("name,n,want", LAYOUT_HASHES)
+def test_layout_is_the_validated_one(rt, emu, name, n, want):
+    sc = rt.Scene(name, 800, 600, n_override=n)
+    e = Emu(emu, sc.shapes, sc.nodes, sc.indices, omax=200.0)
+    assert emu.emu_layout_hash(e.h) == want, "%s: layout hash %016x" % (name, emu.emu_layout_hash(e.h))
