@@ -23,11 +23,12 @@
 //                         its path to the root
 //               emit      FlatNode[] and bvhIndices[]
 //
-// No host round trip inside the level loop: every launch covers all n positions, a level at which nothing
-// is pending exits at once.  Everything that decides a byte of the output lives in the RT_DEV functions
+// No host round trip per level: every launch covers all n positions and a level at which nothing is pending
+// exits at once (past log2(n) + 4 levels the host asks every 8th level whether anything is still pending).
+// Scenes of up to RT_BLD_SMALL_MAX shapes run the whole build in one block (bld_small_kernel).  Everything that decides a byte of the output lives in the RT_DEV functions
 // below; tests/emu/build_emu.cpp compiles exactly those with g++ and tests/test_build_emu.py compares
 // their output with the host builder's on the CPU.  The __global__ wrappers add only indexing, the block
-// scan and the warp-aggregated form of the box atomics.
+// scans and the warp- / block-aggregated form of the box atomics.
 #pragma once
 #include "rt_device.cuh"
 
@@ -43,7 +44,6 @@ typedef unsigned long long u64;
 #ifdef __CUDACC__
 RT_DEV void amin64(u64* p, u64 v) { atomicMin(p, v); }
 RT_DEV void amax64(u64* p, u64 v) { atomicMax(p, v); }
-RT_DEV int  aadd(int* p, int v) { return atomicAdd(p, v); }
 RT_DEV unsigned aaddu(unsigned* p, unsigned v) { return atomicAdd(p, v); }
 RT_DEV void fence() { __threadfence(); }
 RT_DEV int  ld_int(const int* p) { return __ldcg(p); }
@@ -53,7 +53,6 @@ RT_DEV float u2f(unsigned u) { return __uint_as_float(u); }
 // host emulation (tests only): one thread at a time
 inline void amin64(u64* p, u64 v) { if (v < *p) *p = v; }
 inline void amax64(u64* p, u64 v) { if (v > *p) *p = v; }
-inline int  aadd(int* p, int v) { int o = *p; *p += v; return o; }
 inline unsigned aaddu(unsigned* p, unsigned v) { unsigned o = *p; *p += v; return o; }
 inline void fence() {}
 inline int  ld_int(const int* p) { return *p; }
@@ -181,9 +180,6 @@ RT_DEV bool goes_left(float4 cen, const float* box) {
     const float c = axis == 0 ? cen.x : axis == 1 ? cen.y : cen.z;
     return c < pos;
 }
-
-// A node's positions are contiguous: p is the first of its node iff its left neighbour belongs to another node.
-RT_DEV bool is_head(int p, const int* pnode) { return p == 0 || pnode[p - 1] != pnode[p]; }
 
 // ---- per-thread bodies of the level loop -------------------------------------------------------------------
 // Build ids.  The root is 0.  A node whose segment [start, start + count) splits after nL shapes gets the children
