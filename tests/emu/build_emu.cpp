@@ -12,11 +12,14 @@
 #include <vector>
 
 #include "../../opengl-ray-tracer_b200/csrc/rt_build.cuh"
+#include "../../opengl-ray-tracer_b200/csrc/rt_build_list.cuh"
+#include "../../opengl-ray-tracer_b200/csrc/rt_layout.h"
 
 using namespace rt;
 
-extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, rt_flat_node* outNodes, int32_t* outIdx,
-                             unsigned threadOrder) {
+// listSrc .. listPrank (optional, 2n / 2n*2 / n / n ints): K9's list A from the same tables (rt_build_list.cuh)
+extern "C" int emu_build_bvh_list(const rt_flat_shape* shapes, int n, int maxDepth, rt_flat_node* outNodes, int32_t* outIdx,
+                                  unsigned threadOrder, int* listSrc, int* listLinkCw, int* listPshape, int* listPrank) {
     if (n <= 0) return -1;
     const size_t maxNodes = 2 * (size_t)n;
     std::vector<int> start(maxNodes), count(maxNodes), left(maxNodes), parent(maxNodes), depth(maxNodes), desc(maxNodes), idx(maxNodes), first(maxNodes);
@@ -70,5 +73,23 @@ extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, r
     for (int id : threads(nIds)) bld::number_node(id, N, &ctl);
     for (int id : threads(nIds)) bld::emit_node(id, N, ord[ctl.parity].data(), outNodes, outIdx);
     const int nNodes = ctl.nNodes;
+    if (listSrc)
+        for (int id : threads(nIds))
+            bld::thread_node(id, N, ord[ctl.parity].data(), shapes, listSrc, reinterpret_cast<int2*>(listLinkCw), listPshape, listPrank);
     return nNodes;
+}
+
+extern "C" int emu_build_bvh(const rt_flat_shape* shapes, int n, int maxDepth, rt_flat_node* outNodes, int32_t* outIdx,
+                             unsigned threadOrder) {
+    return emu_build_bvh_list(shapes, n, maxDepth, outNodes, outIdx, threadOrder, nullptr, nullptr, nullptr, nullptr);
+}
+
+// The host layout builder's list A without sub-trees (the plain reference walk), for comparison with K9.
+extern "C" int emu_host_list(const rt_flat_shape* shapes, int n, const rt_flat_node* nodes, int nNodes, const int32_t* idx, int nIdx,
+                             int* src, int* linkCw, int* pshape, int* prank) {
+    rtl::Layout L;
+    if (!rtl::build_layout(nodes, nNodes, idx, (size_t)nIdx, shapes, n, false, 1.0, L)) return -1;
+    for (int k = 0; k < L.nodes(); ++k) { src[k] = L.src[(size_t)k]; linkCw[2 * k] = L.link[(size_t)k]; linkCw[2 * k + 1] = L.cw[(size_t)k]; }
+    for (int s = 0; s < L.prims(); ++s) { pshape[s] = L.pshape[(size_t)s]; prank[s] = L.prank[(size_t)s]; }
+    return L.nodes();
 }

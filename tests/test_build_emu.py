@@ -20,13 +20,17 @@ CSRC = os.path.join(os.path.dirname(HERE), "opengl-ray-tracer_b200", "csrc")
 
 @pytest.fixture(scope="module")
 def emu():
-    deps = [EMU_SRC, os.path.join(CSRC, "rt_build.cuh"), os.path.join(CSRC, "rt_device.cuh")]
+    deps = [EMU_SRC, os.path.join(CSRC, "rt_build.cuh"), os.path.join(CSRC, "rt_build_list.cuh"), os.path.join(CSRC, "rt_device.cuh"),
+            os.path.join(CSRC, "rt_layout.h")]
     if not os.path.exists(EMU_SO) or any(os.path.getmtime(d) > os.path.getmtime(EMU_SO) for d in deps):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared",
                                "-I/usr/local/cuda/include", "-o", EMU_SO, EMU_SRC])
     L = C.CDLL(EMU_SO)
     L.emu_build_bvh.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint]
     L.emu_build_bvh.restype = C.c_int
+    vp = C.c_void_p
+    L.emu_build_bvh_list.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_uint, vp, vp, vp, vp]; L.emu_build_bvh_list.restype = C.c_int
+    L.emu_host_list.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, vp]; L.emu_host_list.restype = C.c_int
     return L
 
 
@@ -124,3 +128,26 @@ def test_edge_cases(rt, emu):
     check(emu, rt, sh, 12)
     # infinite planes only: nothing bounds the root, nothing splits
     check(emu, rt, random_shapes(rt, rng, 5, types=(1,)), 8)
+
+
+@pytest.mark.parametrize("name,n,depth,order", [("toy", 0, 15, 0), ("monkey", 0, 15, 3), ("car", 0, 25, 0), ("soup", 20000, 40, 5), ("monkey", 0, 2, 1)])
+def test_list_a_from_the_build_tables(rt, emu, name, n, depth, order):
+    """K9 (rt_build_list.cuh, prepared for the next round): the threaded node list and the primitive slots that
+    rtl::build_layout derives on the host from FlatNode[] / bvhIndices[] (plain reference walk, no sub-trees) follow
+    word for word from K8's own tables, node by node, in any thread order."""
+    sc = rt.Scene(name, 160, 120, n_override=n, bvh_depth=depth)
+    shapes = np.ascontiguousarray(sc.shapes)
+    ns = len(shapes)
+    nodes = np.zeros(2 * ns, dtype=rt.NODE_DTYPE); idx = np.zeros(ns, np.int32)
+    src = np.full(2 * ns, -9, np.int32); lc = np.full((2 * ns, 2), -9, np.int32)
+    psh = np.full(ns, -9, np.int32); prk = np.full(ns, -9, np.int32)
+    nn = emu.emu_build_bvh_list(shapes.ctypes.data, ns, depth, nodes.ctypes.data, idx.ctypes.data, order,
+                                src.ctypes.data, lc.ctypes.data, psh.ctypes.data, prk.ctypes.data)
+    assert nodes[:nn].tobytes() == np.ascontiguousarray(sc.nodes).tobytes()
+    hsrc = np.zeros(nn, np.int32); hlc = np.zeros((nn, 2), np.int32); hpsh = np.zeros(ns, np.int32); hprk = np.zeros(ns, np.int32)
+    hn = np.ascontiguousarray(sc.nodes); hi = np.ascontiguousarray(sc.indices)
+    m = emu.emu_host_list(shapes.ctypes.data, ns, hn.ctypes.data, len(hn), hi.ctypes.data, len(hi),
+                          hsrc.ctypes.data, hlc.ctypes.data, hpsh.ctypes.data, hprk.ctypes.data)
+    assert m == nn
+    assert np.array_equal(src[:nn], hsrc) and np.array_equal(lc[:nn], hlc)
+    assert np.array_equal(psh, hpsh) and np.array_equal(prk, hprk)
