@@ -151,3 +151,30 @@ def test_list_a_from_the_build_tables(rt, emu, name, n, depth, order):
     assert m == nn
     assert np.array_equal(src[:nn], hsrc) and np.array_equal(lc[:nn], hlc)
     assert np.array_equal(psh, hpsh) and np.array_equal(prk, hprk)
+
+
+def test_property_random_bit_patterns(rt, emu):
+    """Property test (hypothesis): shapes whose coordinates are arbitrary fp32 BIT PATTERNS — denormals, huge values,
+    infinities, NaNs with payloads, both zeros — in any mix of the four types (and an unknown one): the emulated device
+    build still equals the host builder byte for byte."""
+    hyp = pytest.importorskip("hypothesis")
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    special = [0x00000000, 0x80000000, 0x7f800000, 0xff800000, 0x7fc00000, 0xffc00001, 0x00000001, 0x80000001,
+               0x7f7fffff, 0xff7fffff, 0x3f800000, 0xbf800000]
+    word = st.one_of(st.sampled_from(special), st.integers(0, 2 ** 32 - 1),
+                     st.floats(-50, 50, width=32).map(lambda f: int(np.float32(f).view(np.uint32))))
+
+    @settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+    @given(n=st.integers(1, 40), depth=st.integers(1, 12), data=st.data())
+    def run(n, depth, data):
+        sh = np.zeros(n, dtype=rt.SHAPE_DTYPE)
+        raw = sh.view(np.uint32).reshape(n, 48)
+        for i in range(n):
+            sh["type"][i] = data.draw(st.sampled_from([0, 0, 1, 2, 3, 3, 3, 7]))
+            for w in (16, 17, 18, 19, 20, 21, 22, 23, 24, 25, 26, 27, 28, 36, 37, 38, 40, 41, 42, 44, 45, 46):
+                raw[i, w] = data.draw(word)      # centre, radius, normal, D, wall start / width / height, the three vertices
+        check(emu, rt, sh, depth, orders=(0, 5))
+
+    with np.errstate(all="ignore"):
+        run()
