@@ -208,6 +208,27 @@ def run_reference_arm(args):
     }))
 
 
+def fetch_bandwidth(prof, kernel_ms):
+    """The render kernel's REAL node + primitive fetch traffic per launch (one ncu --set full capture, profiles/traffic.json)
+    over the live kernel time, level by level, beside the read-bandwidth peaks of tools/l2_probe.cu when that has been run on
+    the box (profiles/l2_peak.json; SURVEY.md par. 8d asks for the L2 figure next to the HBM peak of MEASURED_PEAKS.json)."""
+    try:
+        out = {"l1_global_load_GBps": prof["render_kernel_l1_global_load_bytes"] / kernel_ms / 1e6,
+               "l2_read_from_sm_GBps": prof["render_kernel_l2_read_bytes_from_sm"] / kernel_ms / 1e6,
+               "dram_read_GBps": prof["render_kernel_dram_read_bytes"] / kernel_ms / 1e6,
+               "source": prof.get("source")}
+    except (KeyError, TypeError, ZeroDivisionError):
+        return None
+    try:
+        pk = json.load(open(os.path.join(ROOT, "profiles", "l2_peak.json")))
+        out["l1_peak_GBps"], out["l2_peak_GBps"] = pk.get("l1_gbs"), pk.get("l2_gbs")
+        if pk.get("l2_gbs"):
+            out["l2_frac"] = out["l2_read_from_sm_GBps"] / pk["l2_gbs"]
+    except (OSError, ValueError):
+        out["l1_peak_GBps"] = out["l2_peak_GBps"] = None      # tools/l2_probe has not been run on this box yet
+    return out
+
+
 def workload_config(args, **more):
     cfg = {"workload": "%s scene %dx%d, maxBounces=%d useBVH=1 useFresnel=%d useMollerTrumbore=%d "
                        "(BASELINE.json configs[2]; synthetic stand-in mesh, same primitive counts)" %
@@ -608,6 +629,7 @@ def main():
                                  "(~1 MB) is L1/L2-resident and our walk skips most of that traffic, so HBM is not the limiter and "
                                  "frac can exceed 1: DRAM sees the image write only (traffic).  The binding resource is "
                                  "instruction issue: see issue_roofline"},
+            "fetch_bandwidth": fetch_bandwidth(prof, ren) if traffic is not None else None,
             "issue_roofline": {"bound": "warp-instruction issue (4 schedulers x 148 SMs x SM clock)",
                                "warp_instructions_per_launch": winst, "source": "profiles/traffic.json (ncu smsp__inst_executed.sum)",
                                "achieved_Ginst_s": (winst / ren / 1e6) if winst else None, "peak_Ginst_s": issue_peak / 1e9,
