@@ -49,3 +49,17 @@ def test_layout_builder_under_sanitizers(rt, flags, tag):
         r = _run([exe, name, str(n)])
         assert r.returncode == 0, r.stderr[-3000:]
         assert "layout hash %016x" % want[(name, n)] in r.stdout, r.stdout
+
+
+def test_walk_emulation_under_asan_ubsan(rt):
+    """The kernel's primitive / box tests (rt_device.cuh) walking the layouts of rt_layout.h (reference walk, sub-trees,
+    list B): every node, link and slot access checked; the number of hits must not depend on the layout."""
+    exe = _build(rt, "sanitize_walk_main.cpp", "sanitize_walk_asan", ["-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"])
+    for args in (["car", "0"], ["monkey", "0"], ["toy", "0"]):
+        r = _run([exe] + args)
+        assert r.returncode == 0, r.stderr[-3000:]
+        hits = {}
+        for line in r.stdout.splitlines():
+            w = line.replace(":", "").replace(",", "").split()
+            hits.setdefault((w[4], w[6]), set()).add(int(w[9]))            # (mt, any) -> hit counts over the three layouts
+        assert len(hits) == 4 and all(len(v) == 1 for v in hits.values()), r.stdout
