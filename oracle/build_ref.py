@@ -73,7 +73,7 @@ def main() -> int:
         return rc
     # the reference's own C++ shape classes, for the primitive-level cross-check
     cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared",
-           "-I", os.path.join(ref, "src"), "-I", glm, "-I", os.path.join(HERE, "stubs"),
+           "-I", os.path.join(ref, "src"), "-I", ref, "-I", glm, "-I", os.path.join(HERE, "stubs"),
            os.path.join(HERE, "ref_shapes_glue.cpp"), "-o", os.path.join(outdir, "libref_shapes.so")]
     print(" ".join(cmd))
     return subprocess.call(cmd)

@@ -30,3 +30,45 @@ extern "C" int refshape_intersect(int type, const float* a, const float* b, cons
     hit[0] = r.hit_point.x; hit[1] = r.hit_point.y; hit[2] = r.hit_point.z;
     return (int)r.intersect_type;
 }
+
+/*
+ * The reference's own BoundingBox (src/BoundingBox.hpp:34-95), Wall::end (shapes/wall.hpp:16-31) and Triangle::center
+ * (shapes/triangle.hpp:27-29) — the arithmetic buildBVH / split (src/main.cpp:1111-1193) is made of — for pinning the host
+ * restatement and the device builder K8 (rt_build.cuh) against the reference's code itself.  mesh.hpp drags in OpenGL;
+ * BoundingBox only needs Mesh::mesh2triangles to exist, so the header's include guard is taken and a stand-in declared.
+ */
+#define MESH_H
+class Mesh { public: std::vector<Triangle> mesh2triangles() { return {}; } };
+#include "BoundingBox.hpp"
+
+// Shapes i = 0..n-1, types 0 sphere / 2 wall / 3 triangle (1 = infinite plane: a = normal, b = point), parameters as for
+// refshape_intersect (12 floats per shape: a, b, c, s0, s1, unused).  Grows ONE reference BoundingBox by all of them in
+// order through growToInclude(std::unique_ptr<Shape>&), the overload buildBVH uses.  Per shape also returns what
+// serializeShape would put into the flat structure (normal, d: 4 floats) and split's centre (3 floats; planes: untouched).
+extern "C" void refbbox_grow(int n, const int* type, const float* par, float box[6], float* normal_d, float* center) {
+    BoundingBox bb;
+    for (int i = 0; i < n; ++i) {
+        const float* p = par + 12 * (size_t)i;
+        glm::vec3 A(p[0], p[1], p[2]), B(p[3], p[4], p[5]), Cc(p[6], p[7], p[8]);
+        std::unique_ptr<Shape> s;
+        if (type[i] == 0) s = std::make_unique<Sphere>(A, p[9]);
+        else if (type[i] == 1) s = std::make_unique<Plane>(A, B);
+        else if (type[i] == 2) s = std::make_unique<Wall>(A, p[9], p[10], B);
+        else s = std::make_unique<Triangle>(A, B, Cc);
+        bb.growToInclude(s);
+        float* nd = normal_d + 4 * (size_t)i; float* c = center + 3 * (size_t)i;
+        if (auto sp = dynamic_cast<Sphere*>(s.get())) { c[0] = sp->m_center.x; c[1] = sp->m_center.y; c[2] = sp->m_center.z; }
+        else if (auto w = dynamic_cast<Wall*>(s.get())) {
+            const glm::vec3 m = (w->start + w->end()) * 0.5f;                      // main.cpp:1131-1134
+            c[0] = m.x; c[1] = m.y; c[2] = m.z;
+            nd[0] = w->m_normal.x; nd[1] = w->m_normal.y; nd[2] = w->m_normal.z; nd[3] = w->d;
+        } else if (auto t = dynamic_cast<Triangle*>(s.get())) {
+            const glm::vec3 m = t->center();
+            c[0] = m.x; c[1] = m.y; c[2] = m.z;
+            nd[0] = t->m_normal.x; nd[1] = t->m_normal.y; nd[2] = t->m_normal.z; nd[3] = t->d;
+        } else if (auto pl = dynamic_cast<Plane*>(s.get())) {
+            nd[0] = pl->m_normal.x; nd[1] = pl->m_normal.y; nd[2] = pl->m_normal.z; nd[3] = pl->d;
+        }
+    }
+    box[0] = bb.Min.x; box[1] = bb.Min.y; box[2] = bb.Min.z; box[3] = bb.Max.x; box[4] = bb.Max.y; box[5] = bb.Max.z;
+}

@@ -93,3 +93,12 @@ extern "C" int emu_host_list(const rt_flat_shape* shapes, int n, const rt_flat_n
     for (int s = 0; s < L.prims(); ++s) { pshape[s] = L.pshape[(size_t)s]; prank[s] = L.prank[(size_t)s]; }
     return L.nodes();
 }
+
+// split's centre of every shape as K8 computes it (rt_build.cuh: shape_record), for pinning against the reference's classes
+extern "C" void emu_shape_centres(const rt_flat_shape* shapes, int n, float* cen) {
+    for (int i = 0; i < n; ++i) {
+        float4 c, mn, mx;
+        bld::shape_record(shapes + i, c, mn, mx);
+        cen[3 * i] = c.x; cen[3 * i + 1] = c.y; cen[3 * i + 2] = c.z;
+    }
+}

@@ -30,6 +30,7 @@ def emu():
     L.emu_build_bvh.restype = C.c_int
     vp = C.c_void_p
     L.emu_build_bvh_list.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_uint, vp, vp, vp, vp]; L.emu_build_bvh_list.restype = C.c_int
+    L.emu_shape_centres.argtypes = [vp, C.c_int, vp]; L.emu_shape_centres.restype = None
     L.emu_host_list.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int, vp, vp, vp, vp]; L.emu_host_list.restype = C.c_int
     return L
 
@@ -178,3 +179,53 @@ def test_property_random_bit_patterns(rt, emu):
 
     with np.errstate(all="ignore"):
         run()
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_boxes_and_centres_are_the_reference_classes(rt, emu, seed):
+    """Pins the arithmetic the builder is made of to the REFERENCE'S OWN CODE (oracle/_ref/libref_shapes.so compiles
+    src/BoundingBox.hpp, shapes/wall.hpp, shapes/triangle.hpp, shapes/sphere.hpp in place): one reference BoundingBox grown
+    by random spheres / walls / triangles in list order through growToInclude(unique_ptr<Shape>&) — the call buildBVH
+    makes — must equal, bit for bit, the root box of the host builder and of the emulated device build; split's centres
+    (sphere centre, (start + Wall::end()) / 2, Triangle::center()) must equal K8's per-shape records."""
+    ref = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "libref_shapes.so")
+    if not os.path.exists(ref):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    R = C.CDLL(ref)
+    R.refbbox_grow.argtypes = [C.c_int] + [C.c_void_p] * 5; R.refbbox_grow.restype = None
+    rng = np.random.default_rng(4000 + seed)
+    n = int(rng.integers(1, 200))
+    types = rng.choice([0, 2, 3], size=n).astype(np.int32)
+    par = np.zeros((n, 12), np.float32)
+    scale = float(rng.choice([1.0, 30.0, 1e-3]))
+    par[:, 0:9] = rng.uniform(-scale, scale, (n, 9))
+    par[:, 9:11] = rng.uniform(0.1, 5.0, (n, 2)) * scale
+    if seed % 2:                                   # signed zeros and axis-aligned walls
+        par[rng.uniform(size=par.shape) < 0.15] = 0.0
+        par[rng.uniform(size=par.shape) < 0.08] = -0.0
+        par[:, 9:11] = np.abs(par[:, 9:11]) + 0.5
+        w = types == 2
+        par[w, 3:6] = np.where(np.abs(par[w, 3:6]).sum(axis=1, keepdims=True) == 0, 1.0, par[w, 3:6])   # a wall needs a normal
+    box = np.zeros(6, np.float32); nd = np.zeros((n, 4), np.float32); cen = np.zeros((n, 3), np.float32)
+    R.refbbox_grow(n, types.ctypes.data, par.ctypes.data, box.ctypes.data, nd.ctypes.data, cen.ctypes.data)
+    sh = np.zeros(n, dtype=rt.SHAPE_DTYPE)
+    sh["type"] = types
+    for i in range(n):                              # what serializeShape writes (src/main.cpp:994-1066)
+        if types[i] == 0:
+            sh["sphereCenter"][i] = par[i, 0:3]; sh["sphereRadius"][i] = par[i, 9]
+        elif types[i] == 2:
+            sh["wallStart"][i] = par[i, 0:3]; sh["wallWidth"][i] = par[i, 9]; sh["wallHeight"][i] = par[i, 10]
+            sh["planeNormal"][i] = nd[i, 0:3]; sh["planeD"][i] = nd[i, 3]
+        else:
+            sh["triP1"][i], sh["triP2"][i], sh["triP3"][i] = par[i, 0:3], par[i, 3:6], par[i, 6:9]
+            sh["planeNormal"][i] = nd[i, 0:3]; sh["planeD"][i] = nd[i, 3]
+    host = rt.Scene.from_shapes(sh, np.zeros(1, rt.LIGHT_DTYPE), np.zeros(1, rt.CAMERA_DTYPE), bvh_depth=6)
+    root = host.nodes[-1]
+    got = np.concatenate([root["boundsMin"], root["boundsMax"]]).astype(np.float32)
+    assert got.view(np.uint32).tolist() == box.view(np.uint32).tolist(), "host builder's root box vs the reference BoundingBox"
+    nodes, _ = device_build(emu, rt, sh, 6, order=seed)
+    got = np.concatenate([nodes[-1]["boundsMin"], nodes[-1]["boundsMax"]]).astype(np.float32)
+    assert got.view(np.uint32).tolist() == box.view(np.uint32).tolist(), "emulated device build's root box vs the reference BoundingBox"
+    k8 = np.zeros((n, 3), np.float32)
+    emu.emu_shape_centres(np.ascontiguousarray(sh).ctypes.data, n, k8.ctypes.data)
+    assert np.array_equal(k8.view(np.uint32), cen.view(np.uint32)), "K8's split centres vs sphere centre / Wall::end / Triangle::center"
