@@ -76,6 +76,13 @@ def main() -> int:
            "-I", os.path.join(ref, "src"), "-I", ref, "-I", glm, "-I", os.path.join(HERE, "stubs"),
            os.path.join(HERE, "ref_shapes_glue.cpp"), "-o", os.path.join(outdir, "libref_shapes.so")]
     print(" ".join(cmd))
+    rc = subprocess.call(cmd)
+    if rc != 0:
+        return rc
+    # the reference's wheel-animation expression on its vendored GLM (pins host/rt_anim_math.h)
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared", "-I", glm,
+           os.path.join(HERE, "ref_anim_glue.cpp"), "-o", os.path.join(outdir, "libref_anim.so")]
+    print(" ".join(cmd))
     return subprocess.call(cmd)
 
 

@@ -165,3 +165,36 @@ def test_leaf_growth_plus_child_union_equals_updateBVH(rt, name):
         assert mn.tobytes() == want["boundsMin"].astype(f32).tobytes(), "frame %d" % frame
         assert mx.tobytes() == want["boundsMax"].astype(f32).tobytes(), "frame %d" % frame
         nodes0 = want.copy()
+
+
+def test_wheel_transform_restatement_equals_glm():
+    """host/rt_anim_math.h (prepared for K6: the reference's translate * rotate * translate matrix and the matrix-vector
+    product, operation by operation in GLM's order) against the reference's vendored GLM evaluating the very expression of
+    updateWheelAnimations (src/main.cpp:1091-1105): matrix and transformed points bit for bit, any axis."""
+    import ctypes as C
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = os.path.join(root, "oracle", "_ref", "libref_anim.so")
+    if not os.path.exists(ref):
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    src = os.path.join(root, "tests", "emu", "anim_math_emu.cpp")
+    so = os.path.join(root, "tests", "emu", "libanim_math_emu.so")
+    hdr = os.path.join(root, "opengl-ray-tracer_b200", "host", "rt_anim_math.h")
+    if not os.path.exists(so) or max(os.path.getmtime(src), os.path.getmtime(hdr)) > os.path.getmtime(so):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", so, src])
+    R, E = C.CDLL(ref), C.CDLL(so)
+    sig = [C.c_void_p, C.c_float, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    R.refanim_wheel.argtypes = sig; E.rta_wheel.argtypes = sig
+    rng = np.random.default_rng(77)
+    for trial in range(200):
+        center = rng.uniform(-15, 15, 3).astype(np.float32)
+        axis = np.array([0, 0, 1], np.float32) if trial % 2 == 0 else rng.normal(size=3).astype(np.float32)
+        angle = np.float32(rng.uniform(-0.2, 0.2) if trial % 3 else (trial + 1) / 60.0)
+        pts = rng.uniform(-20, 20, (64, 3)).astype(np.float32)
+        a, b = np.zeros_like(pts), np.zeros_like(pts)
+        ma, mb = np.zeros(16, np.float32), np.zeros(16, np.float32)
+        R.refanim_wheel(center.ctypes.data, angle, axis.ctypes.data, len(pts), pts.ctypes.data, a.ctypes.data, ma.ctypes.data)
+        E.rta_wheel(center.ctypes.data, angle, axis.ctypes.data, len(pts), pts.ctypes.data, b.ctypes.data, mb.ctypes.data)
+        assert np.array_equal(ma.view(np.uint32), mb.view(np.uint32)), "transform matrix, trial %d" % trial
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), "transformed points, trial %d" % trial
