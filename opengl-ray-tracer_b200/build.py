@@ -31,7 +31,7 @@ def _run(cmd):
 
 def cuda_sources():
     return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh", ".h"))] + \
-           [os.path.join(ROOT, "include", "rt_api.h"), os.path.join(ROOT, "include", "rt_flat.h")]
+           [os.path.join(ROOT, "include", "rt_api.h"), os.path.join(ROOT, "include", "rt_flat.h"), os.path.join(HOST, "rt_anim_math.h")]
 
 
 def build_cuda(force=False):
@@ -49,7 +49,7 @@ def build_cuda(force=False):
 
 def build_host(force=False):
     out = os.path.join(HOST, "librt_host.so")
-    srcs = [os.path.join(HOST, "rt_host.cpp"), os.path.join(HOST, "rt_host.h")]
+    srcs = [os.path.join(HOST, "rt_host.cpp"), os.path.join(HOST, "rt_host.h"), os.path.join(HOST, "rt_anim_math.h")]
     if not force and _newer(out, srcs):
         return out
     _run(["g++"] + CXX_FLAGS + ["-o", out, srcs[0]])

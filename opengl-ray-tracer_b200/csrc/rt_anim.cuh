@@ -5,10 +5,11 @@
 // glBufferSubData (:981-992), grow the boxes of every BVH node that holds an animated shape
 // (updateBVH :1068-1077, grow-only) and re-upload all nodes (:342-344).  Here the shapes and nodes stay
 // on the device:
-//   K6 anim_kernel   one thread per animated shape; the per-entry scalars (the bounced y, cos/sin of the
-//                    frame's wheel angle) are computed on the host with the host's libm and passed in,
-//                    the per-vertex arithmetic runs here with the reference's operation order — the
-//                    result is bit-identical to the host path (checked by tests/test_gpu_parity.py).
+//   K6 anim_kernel   one thread per animated shape; the per-entry scalars (the bounced y; the 12 entries of the
+//                    frame's GLM wheel transform, from cos/sin of the host's libm) are computed on the host
+//                    and passed in, the per-vertex mat4 * vec4 runs here in GLM's operation order — the
+//                    result is bit-identical to the reference's own updateWheelAnimations compiled in place
+//                    (oracle/_ref/libref_bvh.so; tests/test_gpu_parity.py, tests/test_ref_builder.py).
 //                    Wheels keep their stale planeNormal / planeD, as upstream does (:1101-1106).
 //   K7 grow_kernel   grow-only refit of the raw reference nodes: one thread per leaf grows its box by the
 //                    leaf's animated shapes (BoundingBox::growToInclude, BoundingBox.hpp:60-95) and walks
@@ -22,7 +23,9 @@
 namespace rt {
 
 enum { RT_ANIM_BOUNCE = 0, RT_ANIM_ROTATE_Z = 1 };
-struct AnimEntry { int kind; float a, b, cx, cy; };           // bounce: a = new centre y; rotate: a = cos, b = sin, (cx, cy) = wheel centre
+// bounce: m[0] = new centre y; rotate: m[0..11] = rows 0..2 of the frame's GLM wheel transform, column-major m[3 * col + row]
+// (translate(center) * rotate(angle, axis) * translate(-center), computed on the host by host/rt_anim_math.h)
+struct AnimEntry { int kind; float m[12]; };
 struct AnimItem  { int shape; int entry; };
 
 __global__ void anim_kernel(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
@@ -33,14 +36,16 @@ __global__ void anim_kernel(rt_flat_shape* __restrict__ shapes, const AnimItem* 
     const AnimEntry e = entries[it.entry];
     rt_flat_shape* s = shapes + it.shape;
     if (e.kind == RT_ANIM_BOUNCE) {
-        s->sphereCenter[1] = e.a;
+        s->sphereCenter[1] = e.m[0];
     } else {
+        // vec3(transform * vec4(p, 1)) in GLM's operation order (type_mat4x4.inl:595-613; rta_apply in host/rt_anim_math.h):
+        // (m[0] * x + m[1] * y) + (m[2] * z + m[3] * 1); compiled with -fmad=false, so bit-identical to the host's GLM path
         float* P[3] = {s->triP1, s->triP2, s->triP3};
 #pragma unroll
         for (int v = 0; v < 3; ++v) {
-            const float x = P[v][0] - e.cx, y = P[v][1] - e.cy;
-            P[v][0] = (e.a * x - e.b * y) + e.cx;
-            P[v][1] = (e.b * x + e.a * y) + e.cy;
+            const float x = P[v][0], y = P[v][1], z = P[v][2];
+#pragma unroll
+            for (int r = 0; r < 3; ++r) P[v][r] = (e.m[r] * x + e.m[3 + r] * y) + (e.m[6 + r] * z + e.m[9 + r] * 1.0f);
         }
     }
 }

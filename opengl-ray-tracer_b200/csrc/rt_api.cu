@@ -6,6 +6,7 @@
 #include "rt_refit.cuh"
 #include "rt_anim.cuh"
 #include "rt_build.cuh"
+#include "../host/rt_anim_math.h"
 
 #include <cmath>
 #include <cstdio>
@@ -95,7 +96,7 @@ struct rt_ctx {
     int nRfStart = 0;
     int* hRfDegraded = nullptr;                 // pinned: lazily read back flag of the last refit
     // device-side animation (rt_anim.cuh)
-    struct AnimDef { int kind; float originY, amp, freq, cx, cy, speed; };
+    struct AnimDef { int kind; float originY, amp, freq, cx, cy, cz, speed; };
     std::vector<AnimDef> animDefs; std::vector<AnimItem> animItems;
     PinBuf<AnimEntry> hAnimEntries; DevBuf<AnimEntry> dAnimEntries; DevBuf<AnimItem> dAnimItems;
     DevBuf<unsigned char> dAnimFlag; DevBuf<int> dIndices, dNodeAux; DevBuf<unsigned> dGrowArrived;   // dNodeAux: [parent nNodes | leaves nLeaves]
@@ -818,7 +819,7 @@ int rt_anim_bounce(rt_ctx* c, int shape, float origin_y, float amplitude, float 
     if (shape < 0 || shape >= c->nShapes) return fail(c, RT_ERR_ARG, "animated shape outside the uploaded buffer");
     if (c->hShapes.p[shape].type != RT_SHAPE_SPHERE) return fail(c, RT_ERR_ARG, "rt_anim_bounce wants a sphere");
     c->animItems.push_back(AnimItem{shape, (int)c->animDefs.size()});
-    c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_BOUNCE, origin_y, amplitude, frequency, 0.f, 0.f, 0.f});
+    c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_BOUNCE, origin_y, amplitude, frequency, 0.f, 0.f, 0.f, 0.f});
     c->animDirty = true;
     return RT_OK;
 }
@@ -830,7 +831,7 @@ int rt_anim_rotate_z(rt_ctx* c, const int32_t* shapes, int count, const float ce
         if (c->hShapes.p[shapes[i]].type != RT_SHAPE_TRIANGLE) return fail(c, RT_ERR_ARG, "rt_anim_rotate_z wants triangles");
     }
     for (int i = 0; i < count; ++i) c->animItems.push_back(AnimItem{shapes[i], (int)c->animDefs.size()});
-    c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_ROTATE_Z, 0.f, 0.f, 0.f, center[0], center[1], speed});
+    c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_ROTATE_Z, 0.f, 0.f, 0.f, center[0], center[1], center[2], speed});
     c->animDirty = true;
     return RT_OK;
 }
@@ -888,9 +889,15 @@ int rt_animate(rt_ctx* c, float t, float dt) {
     for (size_t e = 0; e < c->animDefs.size(); ++e) {
         const rt_ctx::AnimDef& d = c->animDefs[e];
         AnimEntry& o = c->hAnimEntries.p[e];
-        o.kind = d.kind; o.cx = d.cx; o.cy = d.cy;
-        if (d.kind == RT_ANIM_BOUNCE) { o.a = d.originY + d.amp * std::sin(d.freq * t); o.b = 0.f; }     // main.cpp:1079-1082
-        else { const float ang = d.speed * dt; o.a = std::cos(ang); o.b = std::sin(ang); }                 // main.cpp:1084-1109
+        o.kind = d.kind;
+        for (float& x : o.m) x = 0.f;
+        if (d.kind == RT_ANIM_BOUNCE) { o.m[0] = d.originY + d.amp * std::sin(d.freq * t); }              // main.cpp:1079-1082
+        else {                                                                                             // main.cpp:1084-1109
+            const float ang = d.speed * dt, center[3] = {d.cx, d.cy, d.cz}, axis[3] = {0.f, 0.f, 1.f};
+            float m[16];
+            rta_wheel_transform(center, std::cos(ang), std::sin(ang), axis, m);
+            for (int col = 0; col < 4; ++col) for (int r = 0; r < 3; ++r) o.m[3 * col + r] = m[4 * col + r];
+        }
     }
     CU(c, cudaMemcpyAsync(c->dAnimEntries.p, c->hAnimEntries.p, c->animDefs.size() * sizeof(AnimEntry), cudaMemcpyHostToDevice, c->stream));
     cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;

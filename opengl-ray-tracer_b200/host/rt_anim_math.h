@@ -5,10 +5,9 @@
  * :526-537 and :595-613), so that it can be evaluated without GLM and — the 4x4 matrix once per wheel on the host, the
  * matrix-vector product per vertex in a kernel — on the device, bit for bit.
  *
- * PREPARED, NOT YET USED: the headless host (rt_host.cpp: rotate_wheels) and K6 (rt_anim.cuh) rotate with the direct form
- * (c x - s y) + cx, which differs from the matrix path by a few ulp per frame (and keeps z, which the matrix path moves by
- * c + (1 - c) != 1); they agree with each other bit for bit, not with upstream.  tests/test_host.py pins this header to
- * GLM itself; wiring it into K6 needs a GPU run to validate and is on the list for the next round (DESIGN.md par. 6c).
+ * USED BY the headless host (rt_host.cpp: rotate_wheels) and by rt_animate (rt_api.cu: the 12 matrix entries per wheel that K6,
+ * rt_anim.cuh, applies per vertex).  tests/test_host.py pins this header to GLM itself; tests/test_ref_builder.py pins the
+ * animated scene to the reference's own updateWheelAnimations compiled in place (oracle/_ref/libref_bvh.so).
  * Column-major float[16] as in GLM: m[4 * col + row].  Pure C++ (host and device).
  */
 #ifndef RT_ANIM_MATH_H

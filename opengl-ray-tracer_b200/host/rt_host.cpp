@@ -2,6 +2,7 @@
 // See rt_host.h for what it restates.  Plain fp32, built with -ffp-contract=off
 // so the produced bytes are reproducible.
 #include "rt_host.h"
+#include "rt_anim_math.h"
 
 #include <cmath>
 #include <cstring>
@@ -386,19 +387,26 @@ void finish(rh_scene& sc, int depth) {
     serialize_all(sc);
 }
 
-// updateWheelAnimations main.cpp:1084-1109: rotate by rotationSpeed*deltaTime about z through
-// the wheel centre; m_normal/d are NOT refreshed upstream (stale planes), reproduced.
+// updateWheelAnimations main.cpp:1084-1109: transform = translate(center) * rotate(rotationSpeed * deltaTime, (0,0,1)) *
+// translate(-center) as a GLM mat4, every vertex through mat4 * vec4 (rt_anim_math.h restates GLM's operation order and is
+// pinned to the vendored GLM bit for bit); m_normal / d are NOT refreshed upstream (stale planes), reproduced.
 void rotate_wheels(rh_scene& sc, float dt) {
-    float ang = 1.0f * dt, cs = std::cos(ang), sn = std::sin(ang);
-    for (Wheel& w : sc.wheels)
+    const float ang = 1.0f * dt, cs = std::cos(ang), sn = std::sin(ang);
+    const float axis[3] = {0.f, 0.f, 1.f};                        // main.cpp:779
+    for (Wheel& w : sc.wheels) {
+        const float center[3] = {w.center.x, w.center.y, w.center.z};
+        float m[16];
+        rta_wheel_transform(center, cs, sn, axis, m);
         for (int i : w.idx) {
             Shape& t = sc.shapes[(size_t)i];
             for (V3* p : {&t.a, &t.b, &t.c}) {
-                float x = p->x - w.center.x, y = p->y - w.center.y;
-                p->x = (cs * x - sn * y) + w.center.x;
-                p->y = (sn * x + cs * y) + w.center.y;
+                const float in[3] = {p->x, p->y, p->z};
+                float out[3];
+                rta_apply(m, in, out);
+                p->x = out[0]; p->y = out[1]; p->z = out[2];
             }
         }
+    }
 }
 
 }  // namespace

@@ -51,6 +51,46 @@ def transform(src: str) -> str:
     return body
 
 
+def cut(src: str, head_re: str) -> str:
+    """The definition that starts at the line matching head_re, through its matching closing brace (plus a trailing
+    declarator such as `} wheels[4];`).  Text is taken verbatim."""
+    for m in re.finditer(head_re, src, re.M):
+        i = src.index("{", m.start())
+        if ";" not in src[m.start():i]:          # a prototype (ends in ';' before any brace) is not the definition
+            break
+    else:
+        raise SystemExit("build_ref: %r not found in main.cpp" % head_re)
+    depth, j = 0, i
+    while True:
+        c = src[j]
+        if c == "{":
+            depth += 1
+        elif c == "}":
+            depth -= 1
+            if depth == 0:
+                break
+        j += 1
+    k = src.index("\n", j)
+    return src[m.start():k] + "\n"
+
+
+def extract_main(ref: str, outdir: str) -> None:
+    """src/main.cpp -> oracle/_ref/ref_main_{node,wheel,funcs}.inc (verbatim definitions, see ref_bvh_glue.cpp)."""
+    with open(os.path.join(ref, "src", "main.cpp"), "r", encoding="utf-8", errors="replace") as f:
+        src = f.read()
+    with open(os.path.join(outdir, "ref_main_node.inc"), "w") as f:
+        f.write(cut(src, r"^class Node\b"))
+    with open(os.path.join(outdir, "ref_main_wheel.inc"), "w") as f:
+        f.write(cut(src, r"^struct Wheel\b"))
+    heads = [r"^void serializeBVH\(std::vector<FlatNode>& nodes, std::vector<int>& indices\) \{", r"^void updateScene\(FlatScene& flatScene, GLuint ssbo\)\s*$",
+             r"^FlatShape serializeShape\(const std::unique_ptr<Shape>& shape\)\s*$", r"^void updateBVH\(\) \{",
+             r"^void bounceSphere\(", r"^void updateWheelAnimations\(float elapsedTime\) \{",
+             r"^void split\(std::unique_ptr<Node>& parentNode, int depth\) \{", r"^int buildBVH\(int maxDepth\) \{"]
+    with open(os.path.join(outdir, "ref_main_funcs.inc"), "w") as f:
+        for h in heads:
+            f.write(cut(src, h) + "\n")
+
+
 def main() -> int:
     ref = sys.argv[1] if len(sys.argv) > 1 else os.environ.get("RT_REFERENCE_DIR", "/root/reference")
     shader = os.path.join(ref, "src", "shaders", "gpu_shader.comp")
@@ -82,6 +122,15 @@ def main() -> int:
     # the reference's wheel-animation expression on its vendored GLM (pins host/rt_anim_math.h)
     cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared", "-I", glm,
            os.path.join(HERE, "ref_anim_glue.cpp"), "-o", os.path.join(outdir, "libref_anim.so")]
+    print(" ".join(cmd))
+    rc = subprocess.call(cmd)
+    if rc != 0:
+        return rc
+    # the reference's own builder / serialiser / animation step cut out of main.cpp (pins host builder, K6, K7, K8)
+    extract_main(ref, outdir)
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared",
+           "-I", os.path.join(ref, "src"), "-I", ref, "-I", glm, "-I", os.path.join(HERE, "stubs"), "-I", HERE,
+           os.path.join(HERE, "ref_bvh_glue.cpp"), "-o", os.path.join(outdir, "libref_bvh.so")]
     print(" ".join(cmd))
     return subprocess.call(cmd)
 

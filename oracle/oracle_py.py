@@ -58,6 +58,7 @@ def lib():
         L.oracle_intersect_shape.argtypes = [vp, vp, vp, ip, vp]; L.oracle_intersect_shape.restype = ip
         L.oracle_intersect_scene.argtypes = [vp, ip, vp, ip, vp, ip, vp, vp, ip, vp, vp, vp]; L.oracle_intersect_scene.restype = ip
         L.oracle_intersect_scene_batch.argtypes = [vp, ip, vp, ip, vp, ip, ip, vp, vp, ip, vp, vp, vp]; L.oracle_intersect_scene_batch.restype = None
+        L.oracle_primary_ties.argtypes = [vp, vp, ip, vp, ip, vp, ip, vp, ip, ip, ip, ip, vp, ip]; L.oracle_primary_ties.restype = C.c_int64
         L.oracle_present.argtypes = [vp, vp, C.c_int64]; L.oracle_present.restype = None
         _lib = L
     return _lib
@@ -78,6 +79,79 @@ def ref_lib():
     return _ref
 
 
+_bvh = None
+
+
+def refbvh_lib():
+    """The reference's own builder / serialiser / animation step cut out of src/main.cpp and compiled in place
+    (oracle/_ref/libref_bvh.so, see oracle/ref_bvh_glue.cpp), or None if never built."""
+    global _bvh
+    if _bvh is None:
+        p = os.path.join(HERE, "_ref", "libref_bvh.so")
+        if not os.path.exists(p):
+            return None
+        B = C.CDLL(p)
+        vp, ip, fl = C.c_void_p, C.c_int, C.c_float
+        B.refbvh_load.argtypes = [vp, ip, vp]; B.refbvh_load.restype = ip
+        B.refbvh_build.argtypes = [ip, C.POINTER(ip), C.POINTER(ip)]; B.refbvh_build.restype = None
+        B.refbvh_get.argtypes = [vp, vp]; B.refbvh_get.restype = None
+        B.refbvh_get_shapes.argtypes = [vp]; B.refbvh_get_shapes.restype = None
+        B.refbvh_wheel.argtypes = [ip, vp, ip, vp]; B.refbvh_wheel.restype = ip
+        B.refbvh_bounce.argtypes = [ip, fl, fl, fl]; B.refbvh_bounce.restype = ip
+        B.refbvh_wheels_step.argtypes = [fl, fl]; B.refbvh_wheels_step.restype = None
+        B.refbvh_frame.argtypes = [ip, ip, C.POINTER(ip), C.POINTER(ip)]; B.refbvh_frame.restype = None
+        _bvh = B
+    return _bvh
+
+
+class RefScene:
+    """The reference's `scene` (src/main.cpp:93-101) filled from flat shapes; ONE instance at a time (upstream globals).
+    build() = buildBVH + serializeBVH; frame() = updateScene + updateBVH | buildBVH + serializeBVH (main.cpp:328-344)."""
+
+    def __init__(self, shapes, animated=(), node_dtype=None):
+        self.B = refbvh_lib()
+        if self.B is None:
+            raise RuntimeError("oracle/_ref/libref_bvh.so not built")
+        self.shapes0 = np.ascontiguousarray(shapes)
+        self.n = len(self.shapes0)
+        flag = np.zeros(max(self.n, 1), np.uint8)
+        flag[np.asarray(list(animated), dtype=np.int64)] = 1
+        if self.B.refbvh_load(_p(self.shapes0), self.n, _p(flag)) != 0:
+            raise ValueError("unknown shape type")
+        self.node_dtype = node_dtype
+
+    def _fetch(self, nn, ni):
+        nodes = np.zeros(nn.value, dtype=self.node_dtype if self.node_dtype is not None else np.dtype(("u1", 48)))
+        idx = np.zeros(ni.value, np.int32)
+        self.B.refbvh_get(_p(nodes), _p(idx))
+        return nodes, idx
+
+    def build(self, max_depth):
+        nn, ni = C.c_int(0), C.c_int(0)
+        self.B.refbvh_build(int(max_depth), C.byref(nn), C.byref(ni))
+        return self._fetch(nn, ni)
+
+    def wheel(self, k, indices, center):
+        idx = np.ascontiguousarray(indices, np.int32); c = np.ascontiguousarray(center, np.float32)
+        assert self.B.refbvh_wheel(int(k), _p(idx), len(idx), _p(c)) == 0
+
+    def bounce(self, shape, t, amplitude, frequency):
+        assert self.B.refbvh_bounce(int(shape), t, amplitude, frequency) == 0
+
+    def wheels_step(self, t, dt):
+        self.B.refbvh_wheels_step(t, dt)
+
+    def frame(self, rebuild=False, max_depth=15):
+        nn, ni = C.c_int(0), C.c_int(0)
+        self.B.refbvh_frame(int(bool(rebuild)), int(max_depth), C.byref(nn), C.byref(ni))
+        return self._fetch(nn, ni)
+
+    def shapes(self):
+        out = self.shapes0.copy()
+        self.B.refbvh_get_shapes(_p(out))
+        return out
+
+
 def render(light, camera, shapes, nodes, indices, params, W, H, threads=None, row_step=1, row_phase=0,
            want_counters=True):
     """Returns (rgba[H,W,4] f32, ids[H,W] i32, dists[H,W] f32, counters dict|None)."""
@@ -93,6 +167,19 @@ def render(light, camera, shapes, nodes, indices, params, W, H, threads=None, ro
     if rc != 0:
         raise RuntimeError("oracle_render failed")
     return rgba, ids, dists, (cnt.as_dict() if cnt is not None else None)
+
+
+def primary_ties(camera, shapes, nodes, indices, params, W, H, threads=None, row_step=1, row_phase=0, want_map=False):
+    """Number of tie pixels among the sampled rows (a candidate of another shape within 1 ulp of the winner's
+    closestDist, gpu_shader.comp:410-411); with want_map also the 0/1 map."""
+    threads = threads or os.cpu_count() or 1
+    arrs = [np.ascontiguousarray(a) for a in (camera, shapes, nodes, indices)]
+    ties = np.zeros((H, W), np.uint8) if want_map else None
+    n = lib().oracle_primary_ties(_p(arrs[0]), _p(arrs[1]), len(arrs[1]), _p(arrs[2]), len(arrs[2]), _p(arrs[3]), len(arrs[3]),
+                                  C.addressof(params), W, H, row_step, row_phase, _p(ties), threads)
+    if n < 0:
+        raise RuntimeError("oracle_primary_ties failed")
+    return (int(n), ties) if want_map else int(n)
 
 
 def ref_render(light, camera, shapes, nodes, indices, params, W, H, threads=None, row_step=1, row_phase=0):

@@ -32,6 +32,7 @@
 #include <cmath>
 #include <cstring>
 #include <thread>
+#include <utility>
 #include <vector>
 
 namespace {
@@ -468,6 +469,67 @@ void oracle_intersect_scene_batch(const rt_flat_shape* shapes, int nShapes, cons
             out_point[3 * (size_t)i] = in ? h.point.x : 0.f; out_point[3 * (size_t)i + 1] = in ? h.point.y : 0.f; out_point[3 * (size_t)i + 2] = in ? h.point.z : 0.f;
         }
     }
+}
+
+// Tie pixels (north_star: "pixels whose t-values tie within 1 ulp ... are counted and reported"): the primary
+// ray's INNER candidates in the reference's visit order (:390-427); a pixel is a tie pixel when a candidate of a
+// DIFFERENT shape lies within 1 ulp of the winning closestDist (:410-411 decides those by visit order alone).
+int64_t oracle_primary_ties(const rt_flat_camera* camera, const rt_flat_shape* shapes, int nShapes,
+                            const rt_flat_node* nodes, int nNodes, const int32_t* indices, int nIndices,
+                            const rt_params* params, int W, int H, int row_step, int row_phase,
+                            uint8_t* ties, int threads) {
+    if (!camera || !params || W <= 0 || H <= 0 || row_step <= 0) return -1;
+    Scene sc{nullptr, camera, shapes, nShapes, nodes, nNodes, indices, nIndices, params->useMollerTrumbore != 0};
+    std::vector<int> rows;
+    for (int y = 0; y < H; ++y) if (y % row_step == row_phase) rows.push_back(y);
+    if (threads < 1) threads = 1;
+    std::vector<int64_t> found((size_t)threads, 0);
+    auto ulps = [](float a, float b) {
+        int32_t ia, ib; std::memcpy(&ia, &a, 4); std::memcpy(&ib, &b, 4);
+        return ia > ib ? (int64_t)ia - ib : (int64_t)ib - ia;      // both distances are positive floats
+    };
+    auto work = [&](int tid) {
+        std::vector<std::pair<float, int>> cand;
+        for (size_t r = (size_t)tid; r < rows.size(); r += (size_t)threads) {
+            const int y = rows[r];
+            for (int x = 0; x < W; ++x) {
+                Ray ray = get_ray(*sc.cam, 2.0f * (float)x / params->screenRes[0] - 1.0f, 1.0f - 2.0f * (float)y / params->screenRes[1]);
+                cand.clear();
+                auto test = [&](int shapeIdx) {
+                    V3 hp{0, 0, 0};
+                    if (get_intersection(sc.shapes[shapeIdx], ray, sc.useMT, hp, nullptr) == INNER)
+                        cand.emplace_back(g_distance(ray.start, hp), shapeIdx);
+                };
+                if (params->useBVH) {
+                    int stack[64]; int sp = 0;
+                    if (sc.nNodes > 0) stack[sp++] = sc.nNodes - 1;
+                    while (sp > 0) {
+                        const rt_flat_node& node = sc.nodes[stack[--sp]];
+                        if (!ray_intersects_aabb(ray, v3(node.boundsMin), v3(node.boundsMax))) continue;
+                        if (node.leftChild == -1) { for (int i = 0; i < node.numShapes; ++i) test(sc.indices[node.startShapeIdx + i]); }
+                        else { stack[sp++] = node.leftChild; stack[sp++] = node.rightChild; }
+                    }
+                } else {
+                    for (int i = 0; i < sc.nShapes; ++i) test(i);
+                }
+                float best = 1e20f; int who = -1;
+                for (auto& c : cand) if (c.first < best) { best = c.first; who = c.second; }
+                bool tie = false;
+                if (who >= 0) for (auto& c : cand) if (c.second != who && c.first < 1e20f && ulps(c.first, best) <= 1) tie = true;
+                if (ties) ties[(size_t)y * (size_t)W + (size_t)x] = tie ? 1 : 0;
+                found[(size_t)tid] += tie ? 1 : 0;
+            }
+        }
+    };
+    if (threads == 1) work(0);
+    else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; ++t) pool.emplace_back(work, t);
+        for (auto& t : pool) t.join();
+    }
+    int64_t n = 0;
+    for (int64_t f : found) n += f;
+    return n;
 }
 
 void oracle_present(const float* rgba, uint8_t* rgba8, int64_t pixels) {

@@ -62,6 +62,14 @@ void oracle_intersect_scene_batch(const rt_flat_shape* shapes, int nShapes, cons
                                   const int32_t* indices, int nIndices, int n, const float* starts, const float* dirs,
                                   int useMollerTrumbore, int32_t* out_shape, float* out_dist, float* out_point);
 
+/* Tie pixels of the sampled rows: primary rays for which a candidate of a DIFFERENT shape lies within 1 ulp of the
+ * winning closestDist (gpu_shader.comp:410-411 resolves those by visit order).  ties: W*H bytes (0/1) or NULL.
+ * Returns the number of tie pixels, or -1 on bad arguments. */
+int64_t oracle_primary_ties(const rt_flat_camera* camera, const rt_flat_shape* shapes, int nShapes,
+                            const rt_flat_node* nodes, int nNodes, const int32_t* indices, int nIndices,
+                            const rt_params* params, int W, int H, int row_step, int row_phase,
+                            uint8_t* ties, int threads);
+
 /* K4 restatement: clamp [0,1], alpha=1, quantise to RGBA8 (round to nearest). */
 void oracle_present(const float* rgba, uint8_t* rgba8, int64_t pixels);
 

@@ -88,8 +88,9 @@ def test_camera_basis_is_orthonormal(rt):
 
 def test_animation_list_reproduces_the_host_animation(rt):
     """Scene.animations() (what rt_anim_bounce / rt_anim_rotate_z are fed) carries the parameters of the host's own
-    animation step: applying the reference formulas (main.cpp:1079-1109) to them with libm's sinf / cosf and fp32
-    arithmetic gives the animated shapes of Scene.animate bit for bit — the arithmetic K6 performs on the device."""
+    animation step: applying the reference formulas (main.cpp:1079-1109; the wheels through GLM's translate * rotate *
+    translate and mat4 * vec4) to them with libm's sinf / cosf and fp32 arithmetic gives the animated shapes of Scene.animate
+    bit for bit — the arithmetic rt_animate / K6 perform."""
     import ctypes as C
     m = C.CDLL("libm.so.6")
     m.sinf.restype = C.c_float; m.sinf.argtypes = [C.c_float]
@@ -113,19 +114,41 @@ def test_animation_list_reproduces_the_host_animation(rt):
     assert sorted(int(x) for _, i, _ in an for x in i) == sorted(int(x) for x in sc.animated)
     sc.animate(0.3, 0.3, mode=0)
     after = sc.shapes
+    def wheel_matrix(c, cs, sn):
+        """translate(I, c) * rotate(I, angle, (0,0,1)) * translate(I, -c) in GLM 0.9.8.5's operation order, fp32 (the
+        restatement host/rt_anim_math.h is pinned to GLM by test_wheel_transform_restatement_equals_glm)."""
+        I = np.eye(4, dtype=f32)                                  # M[row, col]
+        def translate(m, v):
+            out = m.copy()
+            out[:, 3] = ((m[:, 0] * v[0] + m[:, 1] * v[1]) + m[:, 2] * v[2]) + m[:, 3]
+            return out
+        ax = np.array([0, 0, 1], f32) * (f32(1.0) / np.sqrt(f32(1.0)))
+        omc = f32(1.0) - cs
+        tt = omc * ax
+        R = np.zeros((3, 3), f32)                                 # R[col][k] as in gtc/matrix_transform.inl
+        R[0, 0] = cs + tt[0] * ax[0]; R[0, 1] = tt[0] * ax[1] + sn * ax[2]; R[0, 2] = tt[0] * ax[2] - sn * ax[1]
+        R[1, 0] = tt[1] * ax[0] - sn * ax[2]; R[1, 1] = cs + tt[1] * ax[1]; R[1, 2] = tt[1] * ax[2] + sn * ax[0]
+        R[2, 0] = tt[2] * ax[0] + sn * ax[1]; R[2, 1] = tt[2] * ax[1] - sn * ax[0]; R[2, 2] = cs + tt[2] * ax[2]
+        rot = I.copy()
+        for col in range(3):
+            rot[:, col] = (I[:, 0] * R[col, 0] + I[:, 1] * R[col, 1]) + I[:, 2] * R[col, 2]
+        def mul(a, b):
+            out = np.zeros((4, 4), f32)
+            for col in range(4):
+                out[:, col] = ((a[:, 0] * b[0, col] + a[:, 1] * b[1, col]) + a[:, 2] * b[2, col]) + a[:, 3] * b[3, col]
+            return out
+        return mul(mul(translate(I, c), rot), translate(I, -c))
+
     for kind, idx, p in an:
         assert kind == 1
         ang = f32(p[3]) * f32(0.3)
         cs, sn = f32(m.cosf(ang)), f32(m.sinf(ang))
-        cx, cy = f32(p[0]), f32(p[1])
+        M = wheel_matrix(np.array(p[:3], f32), cs, sn)
         for key in ("triP1", "triP2", "triP3"):
             v = before[key][idx].astype(f32)
-            x, y = v[:, 0] - cx, v[:, 1] - cy
-            nx = (cs * x - sn * y) + cx
-            ny = (sn * x + cs * y) + cy
-            assert nx.astype(f32).tobytes() == after[key][idx][:, 0].astype(f32).tobytes()
-            assert ny.astype(f32).tobytes() == after[key][idx][:, 1].astype(f32).tobytes()
-            assert np.array_equal(v[:, 2], after[key][idx][:, 2])
+            for r in range(3):                                    # vec3(M * vec4(p, 1)): (m0 x + m1 y) + (m2 z + m3 1)
+                want = (M[r, 0] * v[:, 0] + M[r, 1] * v[:, 1]) + (M[r, 2] * v[:, 2] + M[r, 3] * f32(1.0))
+                assert want.astype(f32).tobytes() == after[key][idx][:, r].astype(f32).tobytes(), (key, r)
         assert np.array_equal(before["planeNormal"][idx], after["planeNormal"][idx])
 
 

@@ -13,11 +13,13 @@ def compare(rgba, ids, o_rgba, o_ids, o_dists=None):
     both_nan = np.isnan(rgba) & np.isnan(o_rgba)
     diff[both_nan] = 0.0
     diff[np.isnan(diff)] = np.inf
-    # tolerance is absolute 1e-3; radiance is unclamped (light colour 26-50), so also allow 1e-4 relative
-    tol = COLOR_TOL + 1e-4 * np.abs(o_rgba)
-    ok = (diff <= tol).all(axis=-1)
+    # THE BAR is north_star's: max-abs 1e-3 per channel on >= 99.9 % of pixels (frac_ok, asserted).  Two more counts are
+    # reported beside it: a 10x stricter one (1e-4) and the round-1 looser one (1e-3 + 1e-4 relative; radiance is unclamped).
+    ok = (diff <= COLOR_TOL).all(axis=-1)
     out = dict(frac_ok=float(ok.mean()), max_abs=float(diff[np.isfinite(diff)].max() if np.isfinite(diff).any() else 0.0),
-               n_bad=int((~ok).sum()))
+               n_bad=int((~ok).sum()), frac_within_1e_4=float((diff <= 1e-4).all(axis=-1).mean()),
+               frac_within_1e_3_plus_rel=float((diff <= COLOR_TOL + 1e-4 * np.abs(o_rgba)).all(axis=-1).mean()),
+               pixels=int(ok.size))
     if ids is not None:
         ids = np.asarray(ids).reshape(o_ids.shape)
         out["id_mismatch"] = int((ids != o_ids).sum())
@@ -26,7 +28,10 @@ def compare(rgba, ids, o_rgba, o_ids, o_dists=None):
 
 def assert_parity(stats, what=""):
     assert stats.get("id_mismatch", 0) == 0, "%s: %d primary-hit ids differ from the oracle" % (what, stats["id_mismatch"])
-    assert stats["frac_ok"] >= COLOR_FRAC, "%s: only %.5f of pixels within tolerance (max abs %.3g)" % (what, stats["frac_ok"], stats["max_abs"])
+    assert stats["frac_ok"] >= COLOR_FRAC, "%s: only %.5f of pixels within max-abs 1e-3 (max abs %.3g)" % (what, stats["frac_ok"], stats["max_abs"])
+    print("parity %s: ids differ %s, within 1e-3 %.6f, within 1e-4 %.6f, within 1e-3+1e-4|v| %.6f, max abs %.3g, tie pixels %s" %
+          (what, stats.get("id_mismatch"), stats["frac_ok"], stats["frac_within_1e_4"], stats["frac_within_1e_3_plus_rel"],
+           stats["max_abs"], stats.get("tie_pixels", "n/a")))
 
 
 def random_shapes(rt, rng, n, types=(0, 2, 3), extent=10.0):
