@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <new>
 #include <string>
 #include <utility>
@@ -122,6 +123,9 @@ struct rt_ctx {
 
     // pending work, flushed at render time so per-shape updates coalesce (main.cpp:981-992)
     int shapeLo = 0, shapeHi = 0;     // dirty raw-shape range [lo,hi)
+    // the same updates as disjoint intervals: while the shadow is stale (rt_animate moved shapes on the device) only what
+    // the host actually rewrote may go up — the gap between two updates holds pre-animation values
+    std::vector<std::pair<int, int>> shapeRanges;
     bool nodesDirty = false, topoDirty = false;
     bool boxesFinite = false;
 
@@ -193,6 +197,18 @@ double pick_omax(const rt_ctx* c) {
     return 4.0 * m;
 }
 
+// sort + merge overlapping / adjacent intervals
+void merge_ranges(std::vector<std::pair<int, int>>& v) {
+    if (v.size() < 2) return;
+    std::sort(v.begin(), v.end());
+    size_t w = 0;
+    for (size_t i = 1; i < v.size(); ++i) {
+        if (v[i].first <= v[w].second) { if (v[i].second > v[w].second) v[w].second = v[i].second; }
+        else v[++w] = v[i];
+    }
+    v.resize(w + 1);
+}
+
 void stage_subboxes(rt_ctx* c) {
     const rtl::Layout& L = c->layout;
     for (size_t j = 0; j < L.subBox.size(); ++j) {
@@ -260,10 +276,15 @@ int flush_scene(rt_ctx* c) {
         // the layout is rebuilt from the host shadows: bring them up to date with what the device animated
         CU(c, cudaStreamSynchronize(c->stream));
         wait_copies(c);
-        if (c->hostShapesStale && c->nShapes > 0) {        // everything but the range the host has just rewritten
-            const int lo = c->shapeHi > c->shapeLo ? c->shapeLo : c->nShapes, hi = c->shapeHi > c->shapeLo ? c->shapeHi : c->nShapes;
-            if (lo > 0) CU(c, cudaMemcpy(c->hShapes.p, c->dShapes.p, (size_t)lo * sizeof(rt_flat_shape), cudaMemcpyDeviceToHost));
-            if (hi < c->nShapes) CU(c, cudaMemcpy(c->hShapes.p + hi, c->dShapes.p + hi, (size_t)(c->nShapes - hi) * sizeof(rt_flat_shape), cudaMemcpyDeviceToHost));
+        if (c->hostShapesStale && c->nShapes > 0) {        // everything but the intervals the host has just rewritten
+            merge_ranges(c->shapeRanges);
+            int at = 0;
+            for (size_t i = 0; i <= c->shapeRanges.size(); ++i) {
+                const int lo = i < c->shapeRanges.size() ? c->shapeRanges[i].first : c->nShapes;
+                if (lo > at) CU(c, cudaMemcpy(c->hShapes.p + at, c->dShapes.p + at, (size_t)(lo - at) * sizeof(rt_flat_shape), cudaMemcpyDeviceToHost));
+                if (i < c->shapeRanges.size()) at = c->shapeRanges[i].second;
+            }
+            c->shapeRanges.clear();                        // the shadow is whole again: one coalesced copy below is right
         }
         if (c->hostNodesStale && !c->nodesDirty && c->nNodes > 0)
             CU(c, cudaMemcpy(c->hNodes.p, c->dNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost));
@@ -274,8 +295,16 @@ int flush_scene(rt_ctx* c) {
     cudaEventRecord(c->ev[0], c->stream);
     if (shapesChanged && !c->shapesOnDevice) {
         CU(c, c->dShapes.reserve((size_t)c->nShapes));
-        CU(c, cudaMemcpyAsync(c->dShapes.p + c->shapeLo, c->hShapes.p + c->shapeLo,
-                              (size_t)(c->shapeHi - c->shapeLo) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+        if (c->hostShapesStale && !c->shapeRanges.empty()) {
+            // the shadow between the updated intervals is older than the device copy (K6 animated it): one copy per interval
+            merge_ranges(c->shapeRanges);
+            for (const auto& r : c->shapeRanges)
+                CU(c, cudaMemcpyAsync(c->dShapes.p + r.first, c->hShapes.p + r.first,
+                                      (size_t)(r.second - r.first) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+        } else {
+            CU(c, cudaMemcpyAsync(c->dShapes.p + c->shapeLo, c->hShapes.p + c->shapeLo,
+                                  (size_t)(c->shapeHi - c->shapeLo) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+        }
     }
     if (c->nodesDirty && c->nNodes > 0) {
         CU(c, c->dNodes.reserve((size_t)c->nNodes));
@@ -362,6 +391,7 @@ int flush_scene(rt_ctx* c) {
     cudaEventRecord(c->ev[3], c->stream); c->timed[1] = true;
     CU(c, cudaGetLastError());
     c->shapeLo = c->shapeHi = 0; c->nodesDirty = c->topoDirty = false;
+    c->shapeRanges.clear();
     c->devShapesDirty = c->devNodesDirty = false;
     c->shapesOnDevice = false;
     return RT_OK;
@@ -484,7 +514,7 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
         CU(c, c->hShapes.reserve((size_t)nShapes, 0));
         if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
         c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes;
-        c->hostShapesStale = false; c->shapesOnDevice = false;
+        c->hostShapesStale = false; c->shapesOnDevice = false; c->shapeRanges.clear();
         if (!sameTypes) c->topoDirty = true;
     }
     if (indices) {
@@ -520,6 +550,10 @@ int rt_update_shapes(rt_ctx* c, int first, int count, const void* shapes) {
     c->shapesOnDevice = false;
     if (c->shapeHi <= c->shapeLo) { c->shapeLo = first; c->shapeHi = first + count; }
     else { if (first < c->shapeLo) c->shapeLo = first; if (first + count > c->shapeHi) c->shapeHi = first + count; }
+    if (c->hostShapesStale) {
+        if (c->shapeRanges.size() >= 256) merge_ranges(c->shapeRanges);
+        c->shapeRanges.emplace_back(first, first + count);
+    }
     return RT_OK;
 }
 int rt_update_nodes(rt_ctx* c, const void* nodes, int nNodes) {
@@ -948,8 +982,15 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         // the device copy of the shapes must be current: push the pending host range now (flush_scene will not repeat it)
         if (c->shapeHi > c->shapeLo && !c->shapesOnDevice) {
             CU(c, c->dShapes.reserve((size_t)n));
-            CU(c, cudaMemcpyAsync(c->dShapes.p + c->shapeLo, c->hShapes.p + c->shapeLo,
-                                  (size_t)(c->shapeHi - c->shapeLo) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+            if (c->hostShapesStale && !c->shapeRanges.empty()) {      // see flush_scene: only what the host rewrote
+                merge_ranges(c->shapeRanges);
+                for (const auto& r : c->shapeRanges)
+                    CU(c, cudaMemcpyAsync(c->dShapes.p + r.first, c->hShapes.p + r.first,
+                                          (size_t)(r.second - r.first) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+            } else {
+                CU(c, cudaMemcpyAsync(c->dShapes.p + c->shapeLo, c->hShapes.p + c->shapeLo,
+                                      (size_t)(c->shapeHi - c->shapeLo) * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+            }
             cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
             c->shapesOnDevice = true;
         }

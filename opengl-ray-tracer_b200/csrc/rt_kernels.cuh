@@ -300,7 +300,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
     // follows from the hit and the incoming direction alone (:495-497) — so the idle partner lane walks the
     // reflection while the pixel's own lane walks the shadow ray: the pixel's chain of dependent walks shrinks
     // from 2 * maxBounces to maxBounces + 1.  Same queries, same arithmetic, same pixel.
-    paired = paired && P.useBVH && !COUNT;
+    paired = paired && P.useBVH && !COUNT && P.maxBounces > 0;   // maxBounces == 0: the bounce loop never runs (:450), no step at all
     const int nSteps = paired ? P.maxBounces + 1 : 2 * P.maxBounces;
     for (int step = 0; step < nSteps; ++step) {
         if (!__any_sync(RT_FULL, alive)) break;

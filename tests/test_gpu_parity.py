@@ -544,3 +544,46 @@ def test_top_tree_flag_matches(rt, oracle):
     o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
     assert_parity(compare(ra, ia, o_rgba, o_ids), "top tree, animated")
     a.close(); b.close()
+
+
+def test_disjoint_host_updates_after_device_animation(rt, oracle):
+    """rt_animate moves shapes on the device (the host shadow goes stale); two DISJOINT rt_update_shapes calls afterwards
+    must not drag the pre-animation values of the shapes between them back onto the device (one copy per interval),
+    also when the update changes the topology (the layout is rebuilt from the read-back device state + the host's writes)."""
+    W, H = 320, 240
+    sc = rt.Scene("car", W, H)
+    p = rt.make_params(W, H)
+    tr = rt.RayTracer(W, H); tr.upload(sc); tr.register_animations(sc)
+    for frame in range(1, 4):
+        sc.animate(frame * 0.25, 0.25, mode=0)
+        tr.animate(frame * 0.25, 0.25)
+    shapes = sc.shapes.copy()                                       # == the device state (test_device_animation_equals_host_path)
+    an = sc.animated
+    a, b = int(an.min()) - 5, int(an.max()) + 5                     # two static shapes either side of the animated wheels
+    for k, topo in ((0, False), (1, True)):
+        for i in (a, b):
+            shapes["color"][i] = (0.9, 0.1 * k, 0.2)
+            if topo:
+                shapes["type"][i] = 0; shapes["sphereCenter"][i] = shapes["triP1"][i]; shapes["sphereRadius"][i] = 0.7
+            tr.update_shapes(i, shapes[i:i + 1])
+        rgba, ids = tr.render(p)
+        got, _ = tr.download_scene(len(shapes), len(sc.nodes))
+        assert got.tobytes() == shapes.tobytes(), "device shapes after disjoint updates (topology change: %s)" % topo
+        o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
+        assert_parity(compare(rgba, ids, o_rgba, o_ids), "disjoint updates after rt_animate, topo=%s" % topo)
+    tr.close()
+
+
+def test_zero_bounces_after_a_warmed_up_heavy_list(rt, oracle):
+    """maxBounces = 0: the shader's bounce loop never runs and the pixel is (0,0,0,1) (gpu_shader.comp:450); also when the
+    previous frames left a heavy list whose blocks are split into paired row groups."""
+    W, H = 800, 600
+    sc = rt.Scene("car", W, H)
+    tr = rt.RayTracer(W, H); tr.upload(sc)
+    p3 = rt.make_params(W, H, maxBounces=3)
+    for _ in range(3):
+        tr.render(p3)
+    p0 = rt.make_params(W, H, maxBounces=0)
+    rgba, ids = tr.render(p0)
+    assert np.array_equal(rgba[..., :3], np.zeros_like(rgba[..., :3])) and (rgba[..., 3] == 1).all()
+    tr.close()
