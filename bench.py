@@ -17,8 +17,12 @@ frame of configs[1] is measured too and reported under "extra".
             max over ranks, L2 flushed between steps.
   e2e       same metric through the C ABI with HOST buffers: rt_upload_scene (pinned staging, H2D,
             repack) + render + D2H of the rgba32f frame inside the timed region.
-  roofline  algorithmic bytes of the reference traversal per launch / render-kernel time vs the
-            measured HBM peak (the scene is L1/L2 resident, so this is a normalising figure).
+  roofline  the render kernel is bound by warp-instruction ISSUE (the scene is L1/L2 resident): achieved = warp
+            instructions per launch (ncu capture of this kernel, profiles/traffic.json) / live kernel time, peak = 4
+            schedulers x 148 SMs x the SM clock sampled during the run; beside it the MEASURED traffic of every memory level
+            over the live kernel time against MEASURED peaks (HBM: MEASURED_PEAKS.json, L1 / L2: tools/l2_probe.cu ->
+            profiles/l2_peak.json) and, under alg_normalised, SURVEY 8d's algorithmic bytes of the reference traversal.
+  parity    the timed frame against the oracle: ids differing, fraction of pixels within max-abs 1e-3, tie pixels.
   cpu_baseline  the reference shader compiled as C++ (oracle/_ref) or the oracle port, on the host
             cores, on a bounded row sample of the same frame (N=1, rank 0 only).
 """
@@ -52,6 +56,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (core-seconds are bounded by a row sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed frame")
     ap.add_argument("--gather", default="fused", choices=["fused", "nccl"],
                     help="N>1: fused = every rank's render kernel stores its tiles into rank 0's frame over NVLink peer memory "
                          "(one tiny all-reduce as completion barrier); nccl = compact shards + dist.gather + untile kernel")
@@ -208,31 +213,61 @@ def run_reference_arm(args):
     }))
 
 
-def fetch_bandwidth(prof, kernel_ms):
-    """The render kernel's REAL node + primitive fetch traffic per launch (one ncu --set full capture, profiles/traffic.json)
-    over the live kernel time, level by level, beside the read-bandwidth peaks of tools/l2_probe.cu when that has been run on
-    the box (profiles/l2_peak.json; SURVEY.md par. 8d asks for the L2 figure next to the HBM peak of MEASURED_PEAKS.json)."""
+def memory_levels(prof, kernel_ms, hbm_peak):
+    """The render kernel's MEASURED traffic per launch (one ncu --set full capture of this kernel on this workload,
+    profiles/traffic.json) over the LIVE kernel time, level by level, against measured peaks: HBM from
+    MEASURED_PEAKS.json, L1 / L2 read bandwidth from tools/l2_probe.cu (profiles/l2_peak.json)."""
     try:
-        out = {"l1_global_load_GBps": prof["render_kernel_l1_global_load_bytes"] / kernel_ms / 1e6,
-               "l2_read_from_sm_GBps": prof["render_kernel_l2_read_bytes_from_sm"] / kernel_ms / 1e6,
-               "dram_read_GBps": prof["render_kernel_dram_read_bytes"] / kernel_ms / 1e6,
-               "source": prof.get("source")}
+        l1 = prof["l1_global_load_bytes"] + prof["l1_local_load_bytes"]
+        out = {"l1_load_GBps": l1 / kernel_ms / 1e6, "l1_global_load_GBps": prof["l1_global_load_bytes"] / kernel_ms / 1e6,
+               "l1_local_load_GBps (register spills)": prof["l1_local_load_bytes"] / kernel_ms / 1e6,
+               "l2_read_from_sm_GBps": prof["l2_read_bytes_from_sm"] / kernel_ms / 1e6,
+               "dram_GBps": prof["dram_bytes"] / kernel_ms / 1e6, "dram_read_GBps": prof["dram_read_bytes"] / kernel_ms / 1e6,
+               "hbm_peak_GBps": hbm_peak, "hbm_frac": prof["dram_bytes"] / kernel_ms / 1e6 / hbm_peak,
+               "l1_hit_pct": prof.get("l1_hit_pct"), "source": prof.get("source"), "capture_commit": prof.get("commit")}
     except (KeyError, TypeError, ZeroDivisionError):
         return None
     try:
         pk = json.load(open(os.path.join(ROOT, "profiles", "l2_peak.json")))
         out["l1_peak_GBps"], out["l2_peak_GBps"] = pk.get("l1_gbs"), pk.get("l2_gbs")
+        out["peaks_source"] = "measured: tools/l2_probe.cu on this pool's B200 (profiles/l2_peak.json); HBM: MEASURED_PEAKS.json"
         if pk.get("l2_gbs"):
             out["l2_frac"] = out["l2_read_from_sm_GBps"] / pk["l2_gbs"]
+        if pk.get("l1_gbs"):
+            out["l1_frac"] = out["l1_load_GBps"] / pk["l1_gbs"]
     except (OSError, ValueError):
-        out["l1_peak_GBps"] = out["l2_peak_GBps"] = None      # tools/l2_probe has not been run on this box yet
+        out["l1_peak_GBps"] = out["l2_peak_GBps"] = None
+    return out
+
+
+def parity_block(rt, sc, params, W, H, rgba, ids):
+    """The timed frame against the oracle (the checker, never the thing measured): north_star's bar."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py as O
+    O.build()
+    o_rgba, o_ids, _, _ = O.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H, want_counters=False)
+    diff = np.abs(np.asarray(rgba, np.float64).reshape(o_rgba.shape) - o_rgba.astype(np.float64))
+    diff[np.isnan(diff)] = np.inf
+    out = {"ids_mismatch": int((np.asarray(ids).reshape(o_ids.shape) != o_ids).sum()) if ids is not None else None,
+           "frac_within_1e-3": float((diff <= 1e-3).all(axis=-1).mean()), "frac_within_1e-4": float((diff <= 1e-4).all(axis=-1).mean()),
+           "max_abs": float(diff[np.isfinite(diff)].max()) if np.isfinite(diff).any() else None,
+           "tie_pixels": O.primary_ties(sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H),
+           "pixels": int(W * H), "against": "oracle/oracle_rt.cpp (pinned to the reference shader compiled as C++, tests/test_oracle_golden.py)"}
+    if O.ref_lib() is not None:                     # the reference shader file itself, when oracle/_ref travelled
+        r = O.ref_render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H)
+        d2 = np.abs(np.asarray(rgba, np.float64).reshape(r.shape) - r.astype(np.float64))
+        d2[np.isnan(d2)] = np.inf
+        out["frac_within_1e-3_vs_reference_build"] = float((d2 <= 1e-3).all(axis=-1).mean())
     return out
 
 
 def workload_config(args, **more):
+    which = {("car", 3840, 2160): "BASELINE.json configs[2]", ("car", 800, 600): "BASELINE.json configs[1]",
+             ("monkey", 800, 600): "BASELINE.json configs[0]", ("soup", 7680, 4320): "BASELINE.json configs[3]"}.get(
+                 (args.scene, args.width, args.height), "not a BASELINE.json configuration")
     cfg = {"workload": "%s scene %dx%d, maxBounces=%d useBVH=1 useFresnel=%d useMollerTrumbore=%d "
-                       "(BASELINE.json configs[2]; synthetic stand-in mesh, same primitive counts)" %
-                       (args.scene, args.width, args.height, args.bounces, args.fresnel, args.mt),
+                       "(%s; synthetic stand-in mesh, same primitive counts)" %
+                       (args.scene, args.width, args.height, args.bounces, args.fresnel, args.mt, which),
            "scene": args.scene, "width": args.width, "height": args.height,
            "parallelism": "tiles%d" % args.gpus, "tile": "32x8 interleaved",
            "l2": "NOT flushed (diagnostic run)" if args.no_flush else "flushed between steps (256 MiB write)"}
@@ -335,15 +370,20 @@ def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup, 
         if host_alias is not None:
             tr.render_device(params)
             if world > 1:
-                dist.all_reduce(token)
+                dist.all_reduce(token)              # completion: every rank's tiles are in the host frame
             torch.cuda.synchronize()
+            if world > 1:
+                dist.all_reduce(token)              # release: the consumer is done with the frame, the next step may overwrite it
+                torch.cuda.synchronize()
         elif world == 1:
             tr.render(params, want_ids=False, out=host)
         elif fused:
             tr.render_device(params)
-            dist.all_reduce(token)
+            dist.all_reduce(token)                  # completion barrier
             if rank == 0:
                 tr.frame_download(host.data_ptr())
+            torch.cuda.synchronize()
+            dist.all_reduce(token)                  # release barrier: rank 0 has read its frame (rt_api.h: rt_frame_export)
             torch.cuda.synchronize()
         else:
             tr.render_device(params, shard.data_ptr())
@@ -469,6 +509,110 @@ def time_device_build(torch, rt, stream):
     return out
 
 
+def soup_extra(torch, dist, rt, stream, local, rank, world, W, H, flush, steps, warmup):
+    """BASELINE.json configs[3]: the 1M-triangle soup + 10k spheres (deep BVH, traversal-bound), tile-sharded over the ranks
+    like the headline frame.  The scene is uploaded ONCE; an end-to-end step updates the camera, renders and brings the frame
+    to the host.  Rays are counted by the kernel's own counter (no oracle constant exists at this size); parity is
+    checked on a row sample against the oracle."""
+    out = {"workload": "BASELINE.json configs[3]: soup of 1,000,000 triangles + 10,000 spheres, %dx%d, %d GPU(s), maxBounces=3" % (W, H, world)}
+    t0 = time.perf_counter()
+    sc = rt.Scene("soup", W, H, n_override=1000000)
+    params = rt.make_params(W, H)
+    out["scene_build_s"] = time.perf_counter() - t0
+    tr = rt.RayTracer(W, H, device=local, flags=0)
+    tr.set_stream(stream.cuda_stream)
+    tr.set_shard(rank, world)
+    t0 = time.perf_counter()
+    tr.upload(sc); tr.synchronize()
+    out["first_upload_s (290 MB H2D + host layout build)"] = time.perf_counter() - t0
+    st = tr.render_stats(params)
+    cnt = torch.tensor([st["rays"], st["node_visits"], st["prim_tests"]], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(cnt)
+    rays = int(cnt[0])
+    fused = world > 1
+    if fused:
+        setup_fused(torch, dist, tr, rank, world)
+    tot, ren, gat, frame = time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, flush, fused=fused)
+    t = torch.tensor([tot, ren, gat], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tot, ren, gat = t.tolist()
+    # end to end: camera update + render (+ gather) + the frame on the host
+    host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
+    token = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+    def step():
+        tr.update_camera(sc.camera)
+        if world == 1:
+            tr.render(params, want_ids=False, out=host.numpy().reshape(-1, 4))
+        else:
+            tr.render_device(params)
+            dist.all_reduce(token)                      # every rank's tiles are in rank 0's frame
+            if rank == 0:
+                tr.frame_download(host.data_ptr())
+            torch.cuda.synchronize()
+            dist.all_reduce(token)                      # rank 0 has read the frame: the next step may overwrite it
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    n = max(3, steps // 2)
+    for _ in range(n):
+        step()
+    torch.cuda.synchronize()
+    e2e = torch.tensor([(time.perf_counter() - t0) * 1e3 / n], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
+    e2e = float(e2e[0])
+    out.update({"ms_per_frame": tot, "render_ms": ren, "gather_untile_ms": gat, "fps": 1e3 / tot, "rays_counted_by_kernel": rays,
+                "Mrays_per_s": rays / tot / 1e3, "node_visits": int(cnt[1]), "prim_tests": int(cnt[2]),
+                "e2e_ms": e2e, "e2e_fps": 1e3 / e2e, "e2e_Mrays_per_s": rays / e2e / 1e3,
+                "e2e_h2d_bytes_per_step": 80, "e2e_d2h_bytes_per_step": int(W * H * 16)})
+    if rank == 0:       # parity on a row sample (the oracle needs ~1 us per node visit: the whole frame would take minutes)
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import oracle_py as O
+            O.build()
+            rs, ph = max(1, H // 24), max(1, H // 48)
+            o_rgba, _, _, _ = O.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H, row_step=rs, row_phase=ph, want_counters=False)
+            rows = np.arange(ph, H, rs)
+            got = host.numpy()[rows]
+            d = np.abs(got.astype(np.float64) - o_rgba[rows].astype(np.float64))
+            out["parity"] = {"rows_checked": int(len(rows)), "pixels": int(len(rows) * W), "frac_within_1e-3": float((d <= 1e-3).all(axis=-1).mean()),
+                             "max_abs": float(d.max()), "tie_pixels": O.primary_ties(sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H, row_step=rs, row_phase=ph)}
+        except Exception as e:
+            out["parity"] = {"error": repr(e)}
+    tr.close()
+    return out
+
+
+def fast_build_block(torch, dist, rt, stream, local, sc, params, W, H, flush, steps, warmup, parity_ms):
+    """SURVEY par. 7's "fast build": librt_b200_fast.so = the same source compiled with FMA contraction allowed.  Its speed next
+    to the parity build's, and how far its frame is from the parity build's (ids and colours) — reported, never the default."""
+    out = {"library": "librt_b200_fast.so (-fmad=true; everything else as the parity build)"}
+    Lf = rt.lib_fast()
+    out["build_info"] = Lf.rt_build_info().decode()
+    a = rt.RayTracer(W, H, device=local)                      # parity build, with ids
+    b = rt.RayTracer(W, H, device=local, library=Lf)
+    for t in (a, b):
+        t.set_stream(stream.cuda_stream); t.upload(sc)
+    ra, ia = a.render(params); rb, ib = b.render(params)
+    d = np.abs(ra.astype(np.float64) - rb.astype(np.float64))
+    d[np.isnan(d)] = np.inf
+    out.update({"ids_mismatch_vs_parity_build": int((ia != ib).sum()), "pixels": int(W * H),
+                "frac_bit_identical_vs_parity_build": float((ra.view(np.uint32) == rb.view(np.uint32)).all(axis=-1).mean()),
+                "frac_within_1e-3_vs_parity_build": float((d <= 1e-3).all(axis=-1).mean()),
+                "max_abs_vs_parity_build": float(d[np.isfinite(d)].max())})
+    a.close()
+    f = rt.RayTracer(W, H, device=local, flags=0, library=Lf)
+    f.set_stream(stream.cuda_stream); f.upload(sc)
+    tot, ren, _, _ = time_frames(torch, dist, rt, f, params, W, H, 0, 1, steps, warmup, flush)
+    f.close(); b.close()
+    out.update({"ms_per_frame": tot, "render_ms": ren, "parity_build_ms_per_frame": parity_ms, "speedup_vs_parity_build": parity_ms / tot})
+    return out
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -515,7 +659,7 @@ def main():
             clocks.start()
         fused = world > 1 and args.gather == "fused"
         frame_ptr = setup_fused(torch, dist, tr, rank, world) if fused else None
-        tot, ren, gat, _ = time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush, fused=fused)
+        tot, ren, gat, last_frame = time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush, fused=fused)
         launches = (tr.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
         nccl_ms = None
         if fused:                               # the NCCL-gather path beside it (north_star: gather timed separately)
@@ -529,6 +673,7 @@ def main():
             tr.render_device(params)
             dist.all_reduce(torch.zeros(1, dtype=torch.int32, device="cuda"))
             torch.cuda.synchronize()
+            got = None
             if rank == 0:
                 got = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
                 tr.frame_download(got.data_ptr()); tr.synchronize()
@@ -564,6 +709,38 @@ def main():
         e2e_ms = min(e2e_copy, e2e_host)
         e2e_path = "host_frame" if e2e_host <= e2e_copy else "device_frame_copy"
 
+        # a step whose upload CHANGES the topology (two trees of the same shapes, alternating): the host-side layout build is in
+        cold_ms = None
+        if world == 1 and args.scene != "soup":
+            try:
+                alt = [sc, rt.Scene(args.scene, W, H, bvh_depth=12)]
+                host = torch.empty((H * W, 4), dtype=torch.float32, pin_memory=True).numpy()
+                for i in range(2):
+                    tr.upload(alt[i & 1]); tr.render(params, want_ids=False, out=host)
+                t0 = time.perf_counter()
+                for i in range(6):
+                    tr.upload(alt[i & 1]); tr.render(params, want_ids=False, out=host)
+                cold_ms = (time.perf_counter() - t0) * 1e3 / 6
+                tr.upload(sc)
+            except Exception as e:
+                cold_ms = repr(e)
+
+        # parity of the timed frame (rank 0): the frame the timed loop produces against the oracle
+        parity = None
+        if rank == 0 and not args.no_parity and args.scene != "soup":
+            try:
+                if world == 1:
+                    chk = rt.RayTracer(W, H, device=local)          # RT_FLAG_HIT_IDS
+                    chk.upload(sc)
+                    chk.render(params)                               # the second frame runs in the heavy-first order, as the timed ones
+                    f_rgba, f_ids = chk.render(params)
+                    chk.close()
+                else:
+                    f_rgba, f_ids = (got.numpy() if fused else last_frame.cpu().numpy()), None
+                parity = parity_block(rt, sc, params, W, H, f_rgba, f_ids)
+            except Exception as e:
+                parity = {"error": repr(e)}
+
         extra = {}
         if world == 1 and not args.no_extra and (W, H) != (800, 600):
             # BASELINE.json configs[1]: the same scene at the reference's own 800x600
@@ -584,6 +761,19 @@ def main():
             tr2.close()
             extra["monkey_animated_300f"] = time_animated(torch, rt, stream)
             extra["device_bvh_build"] = time_device_build(torch, rt, stream)
+            try:
+                extra["fast_build"] = fast_build_block(torch, dist, rt, stream, local, sc, params, W, H, flush, args.steps, args.warmup, tot)
+            except Exception as e:
+                extra["fast_build"] = {"error": repr(e)}
+            try:
+                extra["soup_1M_3840x2160"] = soup_extra(torch, dist, rt, stream, local, rank, world, 3840, 2160, flush, 6, 3)
+            except Exception as e:
+                extra["soup_1M_3840x2160"] = {"error": repr(e)}
+        if world == 8 and not args.no_extra and args.scene == "car":
+            try:        # every rank takes part; rank 0 keeps the result
+                extra["soup_1M_7680x4320"] = soup_extra(torch, dist, rt, stream, local, rank, world, 7680, 4320, flush, 6, 3)
+            except Exception as e:
+                extra["soup_1M_7680x4320"] = {"error": repr(e)}
 
     if rank == 0:
         peaks = {}
@@ -593,17 +783,15 @@ def main():
             pass
         peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
         alg = (consts["alg_bytes"] / world) if consts else None        # per launch: one rank's share of the frame
-        traffic, prof = None, {}
-        try:
-            prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-            if world == 1 and (W, H, args.scene) == (3840, 2160, "car"):
-                traffic = prof.get("render_kernel_dram_bytes_per_launch")
+        prof = {}
+        try:        # the ncu capture of THIS kernel on THIS workload (one rank's launch when world > 1)
+            prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(
+                "%s_%dx%d_w%d" % (args.scene, W, H, world) if not (args.mt or args.fresnel or args.bounces != 3) else "-", {})
         except (OSError, ValueError):
             pass
         sm_clk = (clk or {}).get("sm_mhz") or 1965.0
         issue_peak = 148 * 4 * sm_clk * 1e6                      # warp instructions / s: one per SM sub-partition per cycle
-        winst = prof.get("render_kernel_warp_instructions_per_launch") if traffic is not None else None
-        achieved = alg / ren / 1e6 if alg else None
+        winst = prof.get("warp_instructions")
         line = {
             "metric": "Mrays/s (%s scene)" % args.scene, "value": rays / tot / 1e3, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": tot, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -615,25 +803,33 @@ def main():
             "kernel_work": {"node_visits": nodes_gpu, "prim_tests": tests_gpu,
                             "reference_node_visits": consts["node_visits"] if consts else None,
                             "reference_prim_tests": sum(consts["tests"]) if consts else None},
+            "parity": parity,
             "e2e": {"value": rays / e2e_ms / 1e3, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms, "fps": 1e3 / e2e_ms, "path": e2e_path,
                     "paths_ms": {"host_frame: kernels store into mapped (shared) host memory, every GPU over its own PCIe link": e2e_host,
                                  "device_frame_copy: render (+ gather) on the device, D2H copy of the frame from rank 0": e2e_copy},
-                    "host_frame_equals_single_gpu": host_ok},
+                    "host_frame_equals_single_gpu": host_ok,
+                    "note": "every step re-uploads the whole scene from host buffers; the topology is unchanged from step to step, so the "
+                            "library keeps its threaded layout and only refits (K4) + repacks (K2).  A step whose upload CHANGES the "
+                            "topology also pays the host-side layout build: cold_topology_ms",
+                    "cold_topology_ms": cold_ms},
             "gpu_launches": int(launches),
             "clocks": clk,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "rt::render_kernel", "kernel_ms": ren,
-                         "note": "algorithmic bytes of the REFERENCE's unculled traversal (oracle-counted) / render time; the scene "
-                                 "(~1 MB) is L1/L2-resident and our walk skips most of that traffic, so HBM is not the limiter and "
-                                 "frac can exceed 1: DRAM sees the image write only (traffic).  The binding resource is "
-                                 "instruction issue: see issue_roofline"},
-            "fetch_bandwidth": fetch_bandwidth(prof, ren) if traffic is not None else None,
-            "issue_roofline": {"bound": "warp-instruction issue (4 schedulers x 148 SMs x SM clock)",
-                               "warp_instructions_per_launch": winst, "source": "profiles/traffic.json (ncu smsp__inst_executed.sum)",
-                               "achieved_Ginst_s": (winst / ren / 1e6) if winst else None, "peak_Ginst_s": issue_peak / 1e9,
-                               "frac": (winst / (ren * 1e-3) / issue_peak) if winst else None},
+            "roofline": {"bound": "issue", "achieved": (winst / ren / 1e6) if winst else None, "peak": issue_peak / 1e9,
+                         "unit": "Gwarp-inst/s", "frac": (winst / (ren * 1e-3) / issue_peak) if winst else None,
+                         "traffic": prof.get("dram_bytes"), "kernel": "rt::render_kernel", "kernel_ms": ren,
+                         "peak_source": "4 warp schedulers x 148 SMs x %.0f MHz (SM clock sampled during the timed region)" % sm_clk,
+                         "warp_instructions_per_launch": winst, "ncu_issue_active_pct": prof.get("issue_active_pct"),
+                         "ncu_duration_ms": prof.get("ncu_duration_ms"), "active_lanes_per_instruction": prof.get("active_lanes_per_instruction"),
+                         "memory": memory_levels(prof, ren, peak) if prof else None,
+                         "hbm_frac": (prof["dram_bytes"] / ren / 1e6 / peak) if prof else None,
+                         "alg_normalised": {"what": "SURVEY 8d: algorithmic bytes of the REFERENCE's unculled traversal (oracle-counted) per launch / "
+                                                    "kernel time / HBM peak.  Not a fraction of anything physical: the scene is cache-resident and "
+                                                    "the walk skips most of that traffic (DRAM sees the image write: traffic)",
+                                            "alg_bytes_per_launch": alg, "GBps": (alg / ren / 1e6) if alg else None,
+                                            "over_hbm_peak": (alg / ren / 1e6 / peak) if alg else None, "hbm_peak_GBps": peak, "hbm_peak_source": peak_src},
+                         "note": "instruction-issue bound: the kernel issues on %.0f %% of the scheduler cycles in the ncu capture; frac = the same "
+                                 "ratio from the LIVE kernel time" % (prof.get("issue_active_pct") or 0)},
             "extra": extra,
         }
         if world == 1 and not args.no_cpu_baseline:

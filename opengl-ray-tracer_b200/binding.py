@@ -64,13 +64,28 @@ def lib_path():
     return os.path.join(_build.CSRC, "librt_b200.so")
 
 
+_lib_fast = None
+
+
+def lib_fast():
+    """librt_b200_fast.so: the same source with FMA contraction allowed (bench.py's fast_build block only)."""
+    global _lib_fast
+    if _lib_fast is None:
+        _lib_fast = _declare(C.CDLL(_build.build_cuda(fast=True)))
+    return _lib_fast
+
+
 def lib():
     """Load librt_b200.so (building it if nvcc is here).  Raises if unavailable."""
     global _lib
     if _lib is not None:
         return _lib
     path = os.environ.get("RT_B200_LIB") or _build.build_cuda()      # RT_B200_LIB: kernel-variant experiments (tools/)
-    L = C.CDLL(path)
+    _lib = _declare(C.CDLL(path))
+    return _lib
+
+
+def _declare(L):
     vp, ip, fp = C.c_void_p, C.c_int, C.POINTER(C.c_float)
     L.rt_create.argtypes = [C.POINTER(vp), ip, ip, ip, C.c_uint]; L.rt_create.restype = ip
     L.rt_destroy.argtypes = [vp]; L.rt_destroy.restype = None
@@ -112,7 +127,6 @@ def lib():
     L.rt_last_timings.argtypes = [vp, fp]; L.rt_last_timings.restype = ip
     L.rt_launch_count.argtypes = [vp]; L.rt_launch_count.restype = C.c_int64
     L.rt_build_info.argtypes = []; L.rt_build_info.restype = C.c_char_p
-    _lib = L
     return L
 
 
@@ -242,8 +256,8 @@ class Scene:
 class RayTracer:
     """Thin object wrapper over rt_create/rt_upload_scene/rt_render/rt_destroy."""
 
-    def __init__(self, width, height, device=0, flags=RT_FLAG_HIT_IDS):
-        self._L = lib()
+    def __init__(self, width, height, device=0, flags=RT_FLAG_HIT_IDS, library=None):
+        self._L = library if library is not None else lib()
         self._c = C.c_void_p()
         rc = self._L.rt_create(C.byref(self._c), width, height, device, flags)
         if rc != 0:

@@ -34,16 +34,20 @@ def cuda_sources():
            [os.path.join(ROOT, "include", "rt_api.h"), os.path.join(ROOT, "include", "rt_flat.h"), os.path.join(HOST, "rt_anim_math.h")]
 
 
-def build_cuda(force=False):
-    out = os.path.join(CSRC, "librt_b200.so")
+def build_cuda(force=False, fast=False):
+    """librt_b200.so: the PARITY build (-fmad=false: every hit / miss decision in the shader's own IEEE operations).
+    fast=True: librt_b200_fast.so, the same source with FMA contraction allowed (SURVEY par. 7's "fast build"); bench.py
+    reports its speed and how many ids / colours differ from the parity build.  Never the default."""
+    out = os.path.join(CSRC, "librt_b200_fast.so" if fast else "librt_b200.so")
     if not force and _newer(out, cuda_sources()):
         return out
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         if os.path.exists(out):
             return out
-        raise RuntimeError("nvcc not found and no prebuilt librt_b200.so")
-    _run([nvcc] + NVCC_FLAGS + ["-o", out, os.path.join(CSRC, "rt_api.cu")])
+        raise RuntimeError("nvcc not found and no prebuilt " + os.path.basename(out))
+    flags = [f for f in NVCC_FLAGS if f != "-fmad=false"] + ["-fmad=true", "-DRT_FAST_BUILD=1"] if fast else NVCC_FLAGS
+    _run([nvcc] + flags + ["-o", out, os.path.join(CSRC, "rt_api.cu")])
     return out
 
 
@@ -57,7 +61,7 @@ def build_host(force=False):
 
 
 def build_all(force=False):
-    return build_cuda(force), build_host(force)
+    return build_cuda(force), build_host(force), build_cuda(force, fast=True)
 
 
 if __name__ == "__main__":

@@ -1145,6 +1145,10 @@ int rt_last_timings(rt_ctx* c, float out_ms[4]) {
     return RT_OK;
 }
 int64_t rt_launch_count(const rt_ctx* c) { return c ? c->launches : 0; }
+#ifdef RT_FAST_BUILD
+const char* rt_build_info(void) { return "librt_b200_fast sm_100a fmad=ON (fast build: ids / colours may differ from the parity build) prec-div prec-sqrt tile=32x8 persistent-warps"; }
+#else
 const char* rt_build_info(void) { return "librt_b200 sm_100a fmad=off prec-div prec-sqrt tile=32x8 persistent-warps"; }
+#endif
 
 }  // extern "C"

@@ -130,6 +130,17 @@ void emu_info(void* e, int out[6]) {
     for (int k = 0; k < E->L.nodes(); ++k) if (E->L.cw[(size_t)k] >= 0 && (E->L.cw[(size_t)k] & RT_LEAF_COUNT_MASK) > out[4]) out[4] = E->L.cw[(size_t)k] & RT_LEAF_COUNT_MASK;
 }
 
+// The boxes of the fat-leaf sub-tree nodes (conservative bounds, rtl::prim_bound): 6 floats each; returns their number.
+int emu_subboxes(void* e, float* out, int cap) {
+    const Emu* E = static_cast<Emu*>(e);
+    const int n = E->L.nSubA;
+    for (int j = 0; j < n && j < cap; ++j) {
+        const rtl::Box& b = E->L.subBox[(size_t)j];
+        for (int a = 0; a < 3; ++a) { out[6 * j + a] = b.mn[a]; out[6 * j + 3 + a] = b.mx[a]; }
+    }
+    return n;
+}
+
 // Refit after the caller changed shapes in place (same pointer semantics as rt_update_shapes): returns 1 ok, 0 = rebuild needed.
 int emu_refit(void* e, const rt_flat_shape* shapes, const rt_flat_node* nodes) {
     Emu* E = static_cast<Emu*>(e);

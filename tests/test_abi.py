@@ -65,3 +65,16 @@ def test_product_does_not_reference_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "oracle_py" not in text and "liboracle" not in text and "oracle_rt" not in text, f
+
+
+def test_wire_format_equals_the_references_own_header():
+    """include/rt_flat.h against src/flatStructures.hpp in ONE translation unit: static_asserts on every size and field
+    offset (tests/emu/flat_layout_check.cpp).  Needs the reference tree (this container); skipped on the GPU box."""
+    import pytest
+    ref = os.environ.get("RT_REFERENCE_DIR", "/root/reference")
+    if not os.path.isfile(os.path.join(ref, "src", "flatStructures.hpp")):
+        pytest.skip("reference tree not present")
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-Wno-invalid-offsetof", "-I", os.path.join(ref, "src"), "-I", os.path.join(ref, "glm"),
+                        "-I", ref, "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "emu", "flat_layout_check.cpp")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]

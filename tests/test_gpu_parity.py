@@ -557,7 +557,8 @@ def test_disjoint_host_updates_after_device_animation(rt, oracle):
     for frame in range(1, 4):
         sc.animate(frame * 0.25, 0.25, mode=0)
         tr.animate(frame * 0.25, 0.25)
-    shapes = sc.shapes.copy()                                       # == the device state (test_device_animation_equals_host_path)
+    shapes = sc.shapes                                              # a fresh byte copy (ndarray.copy() would not keep the std430 padding)
+                                                                    # == the device state (test_device_animation_equals_host_path)
     an = sc.animated
     a, b = int(an.min()) - 5, int(an.max()) + 5                     # two static shapes either side of the animated wheels
     for k, topo in ((0, False), (1, True)):

@@ -32,6 +32,7 @@ def emu():
     L.emu_refit_graph_check.argtypes = [vp, vp, vp]; L.emu_refit_graph_check.restype = ip
     L.emu_query.argtypes = [vp, ip, vp, vp, ip, ip, vp, vp, vp, vp, vp]; L.emu_query.restype = None
     L.emu_layout_hash.argtypes = [vp]; L.emu_layout_hash.restype = C.c_uint64
+    L.emu_subboxes.argtypes = [vp, vp, ip]; L.emu_subboxes.restype = ip
     return L
 
 
@@ -295,6 +296,63 @@ def test_axis_parallel_and_degenerate_rays(rt, oracle, emu):
             assert np.array_equal(gid, rid), "%s mt=%s: %d ids differ" % (name, mt, int((gid != rid).sum()))
             assert np.array_equal(gdist.view(np.uint32), rdist.view(np.uint32))
         e.close()
+
+
+@pytest.mark.parametrize("name,mt", [("car", False), ("car", True), ("monkey", False)])
+def test_grazing_rays_at_the_inflated_box_faces(rt, oracle, emu, name, mt):
+    """Adversarial check of the conservative margins (rtl::prim_bound: 64 E S, 128 E ... / sqrt(sin2) / |cos|): rays aimed AT
+    the faces, edges and corners of every sub-tree box — tangent to a face, or crossing it at a grazing angle a few ulp
+    inside / outside — from nearby, from far away and from the edge of the origin range the margins were computed for
+    (|o| = omax).  A ray that misses such a box must not be accepted by anything below it: ids and distances must equal the
+    walk WITHOUT sub-trees (the reference's own leaves) and the oracle."""
+    rng = np.random.default_rng(77)
+    sc = rt.Scene(name, 800, 600)
+    shapes, nodes, idx = sc.shapes, sc.nodes, sc.indices
+    a = Emu(emu, shapes, nodes, idx, subtrees=False)
+    b = Emu(emu, shapes, nodes, idx, subtrees=True)
+    nsub = b.info()["sub"]
+    if nsub == 0:
+        a.close(); b.close(); pytest.skip("no sub-trees in this scene")
+    boxes = np.zeros((nsub, 6), np.float32)
+    assert emu.emu_subboxes(b.h, _p(boxes), nsub) == nsub
+    pick = boxes[rng.permutation(nsub)[:600]].astype(np.float64)
+    O, D = [], []
+    omax = float(b.omax)
+    for bx in pick:
+        lo, hi = bx[:3], bx[3:]
+        for _ in range(6):
+            ax = int(rng.integers(0, 3)); side = int(rng.integers(0, 2))
+            # a point of the face: interior, on an edge or at a corner
+            u = rng.choice([0.0, 1.0, rng.uniform()], 3)
+            p = lo + u * (hi - lo)
+            p[ax] = hi[ax] if side else lo[ax]
+            # direction: in the face plane, plus a grazing component through the face of 0, +-1e-7, +-1e-5, +-1e-3
+            t = rng.normal(0, 1, 3); t[ax] = 0.0
+            t /= np.linalg.norm(t) + 1e-30
+            t[ax] = rng.choice([0.0, 1e-7, -1e-7, 1e-5, -1e-5, 1e-3, -1e-3])
+            # nudge the target a few fp32 ulp in / out of the box along the face normal
+            q = p.copy()
+            q[ax] = np.nextafter(np.float32(q[ax]), np.float32(np.inf if rng.uniform() < 0.5 else -np.inf), dtype=np.float32) if rng.uniform() < 0.7 else q[ax]
+            for dist in (0.5, 30.0, None):
+                if dist is None:                                   # origin on the boundary of the margins' origin range
+                    s = np.abs(t).max()
+                    far = (0.999 * omax - np.abs(q).max()) / max(s, 1e-9)
+                    o = q - t * far
+                    o = np.clip(o, -0.999 * omax, 0.999 * omax)
+                else:
+                    o = q - t * dist
+                O.append(o); D.append(q - o)
+    o = np.asarray(O, np.float32); d = normalize(np.asarray(D, np.float64))
+    ok = np.isfinite(d).all(axis=1)
+    o, d = o[ok], d[ok]
+    ia, da, _, _ = a.query(o, d, mt)
+    ib, db, _, _ = b.query(o, d, mt)
+    assert np.array_equal(ia, ib), "%d of %d grazing rays change their hit under the sub-tree boxes" % (int((ia != ib).sum()), len(o))
+    assert np.array_equal(da.view(np.uint32), db.view(np.uint32))
+    rid, rdist, _ = oracle.intersect_scene_batch(shapes, nodes, idx, o, d, mt)
+    assert np.array_equal(ib, rid) and np.array_equal(db.view(np.uint32), rdist.view(np.uint32))
+    assert (ib >= 0).mean() > 0.05, "the rays do hit the geometry under the boxes"
+    a.close(); b.close()
 
 
 # FNV-1a of every layout array (lists A / B, slots, boxes, refit graph), omax = 200, sub-trees and list B on.  These are
