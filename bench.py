@@ -500,10 +500,30 @@ def time_device_build(torch, rt, stream):
                 dev.append(tr.last_build_ms())
             nodes, idx = tr.build_bvh(depth)
             same = nodes.tobytes() == sc.nodes.tobytes() and idx.tobytes() == sc.indices.tobytes()
+            # K9: the layout on the device too (no host layout, no copy of the tree): build + first frame, wall clock
+            k9 = None
+            try:
+                p64 = rt.make_params(64, 48)
+                tr.upload_scene(sc.light, sc.camera, sc.shapes)          # a fresh scene state: nothing cached
+                tr.synchronize()
+                t0 = time.perf_counter()
+                tr.build_bvh(depth, rt.RT_BUILD_DEVICE_LAYOUT, fetch=False)
+                tr.render_device(p64); tr.synchronize()
+                k9 = {"build_plus_first_frame_wall_ms": (time.perf_counter() - t0) * 1e3, "device_ms": tr.last_build_ms(),
+                      "layout_on_device": tr.layout_info()["on_device"]}
+                tr.upload_scene(sc.light, sc.camera, sc.shapes)
+                tr.synchronize()
+                t0 = time.perf_counter()
+                tr.build_bvh(depth, fetch=False)
+                tr.render_device(p64); tr.synchronize()
+                k9["host_layout_build_plus_first_frame_wall_ms"] = (time.perf_counter() - t0) * 1e3
+            except Exception as e:
+                k9 = {"error": repr(e)}
             tr.close()
             out["%s_%d" % (name, len(sc.shapes))] = {"shapes": len(sc.shapes), "nodes": int(nn), "maxDepth": depth,
                 "device_ms": min(dev), "call_wall_ms": min(wall) * 1e3, "host_builder_ms": t_host * 1e3,
-                "bytes_equal_host_builder": bool(same), "algorithmic_bytes": 192 * len(sc.shapes) + 48 * int(nn) + 4 * int(ni)}
+                "bytes_equal_host_builder": bool(same), "algorithmic_bytes": 192 * len(sc.shapes) + 48 * int(nn) + 4 * int(ni),
+                "device_layout_k9": k9}
         except Exception as e:
             out[name] = {"error": repr(e)}
     return out

@@ -210,9 +210,18 @@ int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
  * rt_last_build_ms = device time of the last build. */
 enum { RT_BUILD_DEFAULT = 0u,
        RT_BUILD_NO_WARP_AGGREGATION = 1u << 0,  /* one atomic per shape and bound instead of per warp / block (diagnostic) */
-       RT_BUILD_NO_SINGLE_BLOCK = 1u << 1       /* scenes of <= 2048 shapes also take the one-launch-per-phase path (diagnostic) */ };
+       RT_BUILD_NO_SINGLE_BLOCK = 1u << 1,      /* scenes of <= 2048 shapes also take the one-launch-per-phase path (diagnostic) */
+       /* K9: lay the built tree out ON THE DEVICE (threaded list A, primitive slots, ranks straight from the builder's
+        * tables): no host layout build and no copy of the tree to the host (rt_get_bvh fetches it on demand).  Applies
+        * when the tree has no leaf of more than 8 shapes (nothing to expand into a sub-tree) or the context walks the
+        * reference's own sequence (RT_FLAG_REFERENCE_WALK); otherwise the call behaves as without the flag.  The own
+        * tree over the reference leaves (list B) is not built for a device-laid-out tree. */
+       RT_BUILD_DEVICE_LAYOUT = 1u << 2 };
 int rt_build_bvh(rt_ctx* ctx, int maxDepth, unsigned build_flags, int* nNodes_out, int* nIndices_out);
 int rt_get_bvh(rt_ctx* ctx, void* nodes_or_NULL, int nodeCapacity, int32_t* indices_or_NULL, int indexCapacity);
+/* Layout of the scene the next render walks: out[0] nodes of list A, out[1] nodes of list B (0 = unused), out[2] nodes of
+ * fat-leaf sub-trees, out[3] = 1 if the layout was produced on the device (K9), 0 if by the host layout builder. */
+int rt_layout_info(rt_ctx* ctx, int out[4]);
 float rt_last_build_ms(const rt_ctx* ctx);
 
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in

@@ -33,6 +33,7 @@ RT_FLAG_REFERENCE_WALK = 1
 RT_FLAG_HIT_IDS = 2
 RT_FLAG_NO_TOP_TREE = 4
 RT_FLAG_NO_HEAVY_FIRST = 8
+RT_BUILD_DEVICE_LAYOUT = 4
 TILE_W, TILE_H = 32, 8
 
 
@@ -56,7 +57,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -117,6 +118,7 @@ def _declare(L):
     L.rt_build_bvh.argtypes = [vp, ip, C.c_uint, C.POINTER(C.c_int), C.POINTER(C.c_int)]; L.rt_build_bvh.restype = ip
     L.rt_get_bvh.argtypes = [vp, vp, ip, vp, ip]; L.rt_get_bvh.restype = ip
     L.rt_last_build_ms.argtypes = [vp]; L.rt_last_build_ms.restype = C.c_float
+    L.rt_layout_info.argtypes = [vp, C.POINTER(C.c_int * 4)]; L.rt_layout_info.restype = ip
     L.rt_item_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_item_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip
@@ -385,6 +387,11 @@ class RayTracer:
         nodes = np.zeros(nn.value, dtype=NODE_DTYPE); idx = np.zeros(ni.value, dtype=np.int32)
         self._chk(self._L.rt_get_bvh(self._c, _ptr(nodes), nn.value, _ptr(idx), ni.value))
         return nodes, idx
+
+    def layout_info(self):
+        out = (C.c_int * 4)()
+        self._chk(self._L.rt_layout_info(self._c, C.byref(out)))
+        return dict(nodes=out[0], nodes_b=out[1], sub=out[2], on_device=bool(out[3]))
 
     def last_build_ms(self):
         return float(self._L.rt_last_build_ms(self._c))

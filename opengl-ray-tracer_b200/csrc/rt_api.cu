@@ -6,6 +6,7 @@
 #include "rt_refit.cuh"
 #include "rt_anim.cuh"
 #include "rt_build.cuh"
+#include "rt_build_list.cuh"
 #include "../host/rt_anim_math.h"
 
 #include <cmath>
@@ -113,6 +114,13 @@ struct rt_ctx {
     bool devShapesDirty = false, devNodesDirty = false;   // the device copies were changed by K6 / K7: repack without an upload
     bool hostStale = false;           // the host shadows no longer describe the device scene (shapes and / or node boxes)
     bool hostShapesStale = false, hostNodesStale = false;
+    // K9 laid the tree out on the device: the host's node shadow still holds an OLDER tree (boxes AND topology) and the
+    // host's index list is stale too; both are fetched on demand (ensure_host_tree)
+    bool hostTreeStale = false;
+    bool layoutOnDevice = false;
+    float rootBox[6] = {0, 0, 0, 0, 0, 0};   // the root's box of the current tree (omax)
+    PinBuf<bld::Ctl> hCtl;
+    DevBuf<int> kOrder, kPshape, kPrank; DevBuf<int2> kLinkCnt;   // K9 writes here; adopted by a swap when the list can be used
     cudaEvent_t rfDone = nullptr; bool rfPending = false;
     int nSub = 0;
     bool subDirty = false;            // sub-tree boxes must be recomputed (shapes moved / omax grew)
@@ -185,11 +193,9 @@ inline void wait_copies(rt_ctx* c) {
 double pick_omax(const rt_ctx* c) {
     double m = 1.0;
     if (c->nNodes > 0) {
-        const rt_flat_node& root = c->hNodes.p[c->nNodes - 1];
-        for (int k = 0; k < 3; ++k) {
-            const double a = std::fabs((double)root.boundsMin[k]), b = std::fabs((double)root.boundsMax[k]);
+        for (int k = 0; k < 6; ++k) {
+            const double a = std::fabs((double)c->rootBox[k]);
             if (std::isfinite(a) && a > m) m = a;
-            if (std::isfinite(b) && b > m) m = b;
         }
     }
     if (c->haveCam) for (int k = 0; k < 3; ++k) { const double a = std::fabs((double)c->cam.Position[k]); if (std::isfinite(a) && a > m) m = a; }
@@ -197,7 +203,21 @@ double pick_omax(const rt_ctx* c) {
     return 4.0 * m;
 }
 
-// sort + merge overlapping / adjacent intervals
+// After a device-side layout (K9) the host never saw the tree: bring FlatNode[] / bvhIndices[] into the host shadows for
+// the callers that need them there (a host layout build, the animation tables, rt_get_bvh, topology comparisons).
+int ensure_host_tree(rt_ctx* c) {
+    if (!c->hostTreeStale) return RT_OK;
+    CU(c, cudaStreamSynchronize(c->stream));
+    wait_copies(c);
+    CU(c, c->hNodes.reserve((size_t)c->nNodes, 0));
+    if (c->nNodes > 0) CU(c, cudaMemcpy(c->hNodes.p, c->dNodes.p, (size_t)c->nNodes * sizeof(rt_flat_node), cudaMemcpyDeviceToHost));
+    c->indices.resize((size_t)c->bIdxCount);
+    if (c->bIdxCount > 0) CU(c, cudaMemcpy(c->indices.data(), c->bIdx.p, (size_t)c->bIdxCount * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    c->hostTreeStale = false; c->hostNodesStale = false;
+    c->hostStale = c->hostShapesStale;
+    return RT_OK;
+}
+
 void merge_ranges(std::vector<std::pair<int, int>>& v) {
     if (v.size() < 2) return;
     std::sort(v.begin(), v.end());
@@ -272,6 +292,7 @@ int flush_scene(rt_ctx* c) {
     }
     const bool anyCopy = c->shapeHi > c->shapeLo || c->nodesDirty || c->topoDirty || c->subDirty || c->devShapesDirty || c->devNodesDirty;
     if (!anyCopy) return RT_OK;
+    if (c->topoDirty && c->hostTreeStale) { int rc = ensure_host_tree(c); if (rc != RT_OK) return rc; }
     if (c->topoDirty && c->hostStale) {
         // the layout is rebuilt from the host shadows: bring them up to date with what the device animated
         CU(c, cudaStreamSynchronize(c->stream));
@@ -325,6 +346,7 @@ int flush_scene(rt_ctx* c) {
     }
     if (c->topoDirty) {
         wait_copies(c);
+        c->layoutOnDevice = false;
         int rc = build_visit_order(c);
         if (rc != RT_OK) return rc;
         CU(c, c->dOrder.reserve((size_t)c->nDfs)); CU(c, c->dLinkCnt.reserve((size_t)c->nDfs));
@@ -409,7 +431,9 @@ bool same_topology(const rt_flat_node* a, const rt_flat_node* b, int n) {
 // shadow by a pointer swap instead of being copied into it.
 int set_nodes(rt_ctx* c, const void* nodes, int nNodes, PinBuf<rt_flat_node>* adopt = nullptr) {
     const rt_flat_node* in = static_cast<const rt_flat_node*>(nodes);
-    const bool sameTopo = c->haveScene && nNodes == c->nNodes && !c->topoDirty && same_topology(in, c->hNodes.p, nNodes);
+    // (after a device-side layout the shadow holds an older tree: nothing to compare with)
+    const bool sameTopo = c->haveScene && !c->hostTreeStale && nNodes == c->nNodes && !c->topoDirty && same_topology(in, c->hNodes.p, nNodes);
+    c->hostTreeStale = false; c->layoutOnDevice = false;
     wait_copies(c);
     if (adopt) {
         std::swap(c->hNodes, *adopt);
@@ -418,6 +442,7 @@ int set_nodes(rt_ctx* c, const void* nodes, int nNodes, PinBuf<rt_flat_node>* ad
         if (nNodes > 0) std::memcpy(c->hNodes.p, in, (size_t)nNodes * sizeof(rt_flat_node));
     }
     c->nNodes = nNodes;
+    if (nNodes > 0) for (int k = 0; k < 3; ++k) { c->rootBox[k] = in[nNodes - 1].boundsMin[k]; c->rootBox[3 + k] = in[nNodes - 1].boundsMax[k]; }
     c->boxesFinite = true;            // NaN-free slab fast path needs |bound| <= 1e37 everywhere
     for (int i = 0; i < nNodes && c->boxesFinite; ++i)
         for (int k = 0; k < 3; ++k)
@@ -475,7 +500,8 @@ void rt_destroy(rt_ctx* c) {
     if (c->copyDone) cudaEventDestroy(c->copyDone);
     if (c->rfDone) cudaEventDestroy(c->rfDone);
     if (c->hRfDegraded) cudaFreeHost(c->hRfDegraded);
-    c->hRf.release(); c->dRf.release(); c->dRfArrived.release();
+    c->hRf.release(); c->dRf.release(); c->dRfArrived.release(); c->hCtl.release();
+    c->kOrder.release(); c->kLinkCnt.release(); c->kPshape.release(); c->kPrank.release();
     c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
     c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
     for (auto& e : c->evBuild) if (e) cudaEventDestroy(e);
@@ -510,6 +536,7 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
             // a shorter shape buffer on its own: the tree the context holds would index past its end.  It is dropped
             // (useBVH frames hit nothing) until nodes / indices are supplied or rt_build_bvh builds a new one.
             c->nNodes = 0; c->indices.clear(); c->topoDirty = true; c->nodesDirty = true; c->hostNodesStale = false;
+            c->hostTreeStale = false; c->layoutOnDevice = false; c->bIdxCount = 0;
         }
         CU(c, c->hShapes.reserve((size_t)nShapes, 0));
         if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
@@ -517,6 +544,7 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
         c->hostShapesStale = false; c->shapesOnDevice = false; c->shapeRanges.clear();
         if (!sameTypes) c->topoDirty = true;
     }
+    if ((indices || nodes) && c->hostTreeStale) { int rc = ensure_host_tree(c); if (rc != RT_OK) return rc; }
     if (indices) {
         const bool same = c->haveScene && (size_t)nIndices == c->indices.size() &&
                           (nIndices == 0 || std::memcmp(indices, c->indices.data(), (size_t)nIndices * sizeof(int32_t)) == 0);
@@ -559,6 +587,7 @@ int rt_update_shapes(rt_ctx* c, int first, int count, const void* shapes) {
 int rt_update_nodes(rt_ctx* c, const void* nodes, int nNodes) {
     if (!c || !nodes || nNodes < 0) return RT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
+    if (c->hostTreeStale) { int rc = ensure_host_tree(c); if (rc != RT_OK) return rc; }
     return set_nodes(c, nodes, nNodes);
 }
 
@@ -873,6 +902,7 @@ int rt_anim_rotate_z(rt_ctx* c, const int32_t* shapes, int count, const float ce
 namespace {
 // Tables of the device animation: items, per-shape flags, bvhIndices and the raw tree's parent / leaf lists.
 int upload_anim_tables(rt_ctx* c) {
+    if (c->hostTreeStale) { int rc = ensure_host_tree(c); if (rc != RT_OK) return rc; }
     const int nN = c->nNodes, nS = c->nShapes;
     std::vector<int> aux((size_t)nN, -1);            // parent per raw node, then the leaf list
     std::vector<int> leaves;
@@ -1048,6 +1078,47 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         }
         cudaEventRecord(c->evBuild[1], st);
         CU(c, cudaGetLastError());
+        if (flags & RT_BUILD_DEVICE_LAYOUT) {
+            // K9: list A, the primitive slots and their ranks straight from the builder's tables, where they are
+            CU(c, c->kOrder.reserve(maxNodes)); CU(c, c->kLinkCnt.reserve(maxNodes));
+            CU(c, c->kPshape.reserve((size_t)n)); CU(c, c->kPrank.reserve((size_t)n));
+            CU(c, c->hCtl.reserve(1, 0));
+            bld_list_kernel<<<idBlocks, RT_BLD_THREADS, 0, st>>>(B, nIds, c->dShapes.p, c->bNodes.p, c->kOrder.p, c->kLinkCnt.p, c->kPshape.p, c->kPrank.p);
+            c->launches += 1;
+            cudaEventRecord(c->evBuild[1], st);
+            CU(c, cudaMemcpyAsync(c->hCtl.p, c->bCtl.p, sizeof(bld::Ctl), cudaMemcpyDeviceToHost, st));
+            CU(c, cudaStreamSynchronize(st));
+            const bld::Ctl& ctl = *c->hCtl.p;
+            if (ctl.nNodes < 1 || (size_t)ctl.nNodes >= maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
+            cudaEventElapsedTime(&c->lastBuildMs, c->evBuild[0], c->evBuild[1]);
+            const bool plain = (c->flags & RT_FLAG_REFERENCE_WALK) != 0 || ctl.notFinite != 0;   // the host builds no sub-trees then either
+            if (plain || ctl.maxLeaf <= RT_FAT_LEAF) {
+                const int nN = ctl.nNodes;
+                wait_copies(c);
+                std::swap(c->dOrder, c->kOrder); std::swap(c->dLinkCnt, c->kLinkCnt);
+                std::swap(c->dPshape, c->kPshape); std::swap(c->dPrank, c->kPrank);
+                CU(c, c->dNodes.reserve((size_t)nN));
+                CU(c, cudaMemcpyAsync(c->dNodes.p, c->bNodes.p, (size_t)nN * sizeof(rt_flat_node), cudaMemcpyDeviceToDevice, st));
+                CU(c, c->dNodesT.reserve((size_t)nN * 2));
+                CU(c, c->q0.reserve((size_t)n + 4)); CU(c, c->q1.reserve((size_t)n + 4));
+                CU(c, c->q2.reserve((size_t)n + 4)); CU(c, c->q3.reserve((size_t)n + 4));
+                CU(c, c->ptype.reserve((size_t)n));
+                c->nNodes = nN; c->nDfs = nN; c->nPrims = n; c->nSub = 0; c->nDfsB = 0; c->nRfStart = 0;
+                c->bNodeCount = nN; c->bIdxCount = n;
+                c->layout = rtl::Layout();
+                c->boxesFinite = ctl.notFinite == 0;
+                for (int k = 0; k < 6; ++k) c->rootBox[k] = ctl.rootBox[k];
+                c->omax = (float)pick_omax(c);
+                c->hostTreeStale = true; c->hostNodesStale = true; c->hostStale = true; c->layoutOnDevice = true;
+                c->topoDirty = false; c->nodesDirty = false; c->subDirty = false;
+                c->devNodesDirty = true; c->devShapesDirty = true;      // flush_scene: repack the lists and the slots, nothing to upload
+                c->animDirty = true;
+                if (nNodes_out) *nNodes_out = nN;
+                if (nIndices_out) *nIndices_out = n;
+                return RT_OK;
+            }
+            // a fat leaf: its sub-tree is built by the host layout builder — continue as without the flag
+        }
         int nNodes = 0;                                // the numbering pass knows how many nodes there are
         CU(c, cudaMemcpyAsync(&nNodes, &c->bCtl.p->nNodes, sizeof(int), cudaMemcpyDeviceToHost, st));
         CU(c, cudaStreamSynchronize(st));
@@ -1060,6 +1131,7 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         cudaEventElapsedTime(&c->lastBuildMs, c->evBuild[0], c->evBuild[1]);
     }
     // hand the tree to the context exactly as an upload of these nodes and indices would
+    if (c->hostTreeStale) { c->indices.clear(); }     // the host list belongs to an older tree
     const bool sameIdx = (size_t)c->bIdxCount == c->indices.size() &&
                          (c->bIdxCount == 0 || std::memcmp(c->bHostIdx.p, c->indices.data(), (size_t)c->bIdxCount * sizeof(int32_t)) == 0);
     if (!sameIdx) { c->indices.assign(c->bHostIdx.p, c->bHostIdx.p + c->bIdxCount); c->topoDirty = true; }
@@ -1073,6 +1145,7 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
 int rt_get_bvh(rt_ctx* c, void* nodes, int nodeCap, int32_t* indices, int indexCap) {
     if (!c) return RT_ERR_ARG;
     if (!c->haveScene) return fail(c, RT_ERR_STATE, "no scene");
+    if (c->hostTreeStale) { CU(c, cudaSetDevice(c->device)); int rc = flush_scene(c); if (rc != RT_OK) return rc; rc = ensure_host_tree(c); if (rc != RT_OK) return rc; }
     if ((nodes && nodeCap < c->nNodes) || (indices && (size_t)indexCap < c->indices.size())) return fail(c, RT_ERR_ARG, "rt_get_bvh: buffer too small");
     if (c->hostNodesStale) {                        // K7 grew the boxes on the device
         CU(c, cudaSetDevice(c->device));
@@ -1088,6 +1161,14 @@ int rt_get_bvh(rt_ctx* c, void* nodes, int nodeCap, int32_t* indices, int indexC
     return RT_OK;
 }
 float rt_last_build_ms(const rt_ctx* c) { return c ? c->lastBuildMs : 0.f; }
+int rt_layout_info(rt_ctx* c, int out[4]) {
+    if (!c || !out) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    int rc = flush_scene(c);
+    if (rc != RT_OK) return rc;
+    out[0] = c->nDfs; out[1] = c->nDfsB; out[2] = c->nSub; out[3] = c->layoutOnDevice ? 1 : 0;
+    return RT_OK;
+}
 
 int rt_untile(rt_ctx* c, const float* dev_shards, int world, float* dev_rgba_out) {
     if (!c || !dev_shards || !dev_rgba_out || world < 1) return RT_ERR_ARG;

@@ -79,6 +79,10 @@ struct Ctl {
     int nNodes;        // number of nodes of the finished tree (written by the numbering pass)
     int parity;        // which of the two position arrays holds the final order
     int active[66];    // active[L]: some node is pending at level L
+    // written by K9 (rt_build_list.cuh) for the host's decision whether the device-built list can be used as it is
+    int maxLeaf;       // shapes in the largest leaf
+    int notFinite;     // some node bound is NaN / inf / beyond RT_SAFE_COORD
+    float rootBox[6];  // the root's box (min xyz, max xyz)
 };
 
 // ---- ordered keys -------------------------------------------------------------------------------------
@@ -192,7 +196,7 @@ RT_DEV void setup_id(int id, const Nodes& N, Ctl* ctl, int n, int maxDepth) {
     if (id != 0) { N.left[id] = RT_BLD_ABSENT; return; }
     N.start[0] = 0; N.count[0] = n; N.parent[0] = -1; N.depth[0] = maxDepth;
     N.left[0] = maxDepth > 0 ? RT_BLD_PENDING : RT_BLD_LEAF;
-    ctl->nNodes = 1; ctl->parity = 0;
+    ctl->nNodes = 1; ctl->parity = 0; ctl->maxLeaf = 0; ctl->notFinite = 0;
     for (int l = 0; l < 66; ++l) ctl->active[l] = 0;
     ctl->active[0] = maxDepth > 0 ? 1 : 0;
 }

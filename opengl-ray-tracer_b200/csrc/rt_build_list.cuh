@@ -1,6 +1,7 @@
-// rt_build_list.cuh — K9 (PREPARED, NOT WIRED: no kernel launches this yet): list A of the device scene layout
-// straight from K8's node table, for reference trees whose leaves are all small (no fat-leaf sub-trees), or for the
-// plain reference walk (RT_FLAG_REFERENCE_WALK) of any tree.
+// rt_build_list.cuh — K9: list A of the device scene layout straight from K8's node table, for reference trees whose
+// leaves are all small (no fat-leaf sub-trees), or for the plain reference walk (RT_FLAG_REFERENCE_WALK) of any tree.
+// Launched by rt_build_bvh(..., RT_BUILD_DEVICE_LAYOUT): the tree K8 has just built is laid out where it is, no host
+// layout call and no copy of the tree to the host (a tree with a fat leaf falls back to the host layout builder).
 //
 // rt_layout.h builds the threaded node list on the host: the reference nodes in the reference's visit order (root
 // first, right child before left, gpu_shader.comp:386, 424-425), a skip link per inner node, and the leaves' shapes in
@@ -45,4 +46,22 @@ RT_DEV void thread_node(int id, const Nodes& N, const int* ord, const rt_flat_sh
 }
 
 }  // namespace bld
+
+#ifdef __CUDACC__
+// One thread per build id.  Besides the list it gathers what the host needs to decide whether the list can be used as
+// it is: the largest leaf, whether every bound is finite (the NaN-free slab test), the root's box (omax).
+__global__ void bld_list_kernel(BuildBufs B, int nIds, const rt_flat_shape* __restrict__ shapes, const rt_flat_node* __restrict__ flat,
+                                int* __restrict__ outSrc, int2* __restrict__ outLinkCw, int* __restrict__ pshape, int* __restrict__ prank) {
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= nIds || B.N.left[id] == RT_BLD_ABSENT) return;
+    bld::thread_node(id, B.N, B.ord[B.ctl->parity], shapes, outSrc, outLinkCw, pshape, prank);
+    if (B.N.left[id] < 0) atomicMax(&B.ctl->maxLeaf, B.N.count[id]);
+    const rt_flat_node& f = flat[B.N.idx[id]];
+    bool fin = true;
+    for (int k = 0; k < 3; ++k) fin = fin && fabsf(f.boundsMin[k]) <= RT_SAFE_COORD && fabsf(f.boundsMax[k]) <= RT_SAFE_COORD;
+    if (!fin) atomicOr(&B.ctl->notFinite, 1);
+    if (id == 0) for (int k = 0; k < 3; ++k) { B.ctl->rootBox[k] = f.boundsMin[k]; B.ctl->rootBox[3 + k] = f.boundsMax[k]; }
+}
+#endif
+
 }  // namespace rt

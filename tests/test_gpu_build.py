@@ -97,3 +97,68 @@ def test_device_build_edge_cases(rt):
     nodes, idx = tr.build_bvh(0)
     assert len(nodes) == 1 and nodes["leftChild"][0] == -1 and nodes["numShapes"][0] == len(cases[-1][0])
     tr.close()
+
+
+DEVICE_LAYOUT = 4   # RT_BUILD_DEVICE_LAYOUT
+
+
+@pytest.mark.parametrize("name,n,depth,on_device", [("toy", 0, 8, True), ("soup", 60000, 40, True), ("soup", 300000, 40, True),
+                                                     ("monkey", 0, 15, False), ("car", 0, 25, False)])
+def test_device_layout_k9(rt, oracle, name, n, depth, on_device):
+    """K9 (rt_build_bvh with RT_BUILD_DEVICE_LAYOUT): list A, the primitive slots and the ranks laid out on the device
+    from K8's tables, no host layout call, no copy of the tree to the host.  The frame is bit-identical to the one a
+    context renders over the host builder's tree and the host layout builder's lists; the tree comes back on demand
+    (rt_get_bvh) byte for byte; a tree with fat leaves (monkey, car) falls back to the host layout; later host-side
+    updates (shape moves, a type change, a fresh upload) work on from the device-laid-out state."""
+    W, H = 200, 150
+    sc = rt.Scene(name, W, H, n_override=n, bvh_depth=depth)
+    p = rt.make_params(W, H, useFresnel=True)
+    a = rt.RayTracer(W, H, flags=rt.RT_FLAG_HIT_IDS | rt.RT_FLAG_NO_TOP_TREE); a.upload(sc)
+    want = a.render(p)
+    b = rt.RayTracer(W, H, flags=rt.RT_FLAG_HIT_IDS | rt.RT_FLAG_NO_TOP_TREE)
+    b.upload_scene(sc.light, sc.camera, sc.shapes)
+    nn, ni = b.build_bvh(depth, DEVICE_LAYOUT, fetch=False)
+    info = b.layout_info()
+    assert info["on_device"] == on_device, info
+    assert nn == len(sc.nodes) and ni == len(sc.indices)
+    assert info["nodes"] == a.layout_info()["nodes"]
+    assert _same_frame(b.render(p), want)
+    o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
+    from util import assert_parity, compare
+    got = b.render(p)
+    assert_parity(compare(got[0], got[1], o_rgba, o_ids), "%s over the device-laid-out tree" % name)
+    nodes = np.zeros(nn, dtype=rt.NODE_DTYPE); idx = np.zeros(ni, dtype=np.int32)
+    b._chk(b._L.rt_get_bvh(b._c, nodes.ctypes.data, nn, idx.ctypes.data, ni))
+    assert nodes.tobytes() == np.ascontiguousarray(sc.nodes).tobytes() and idx.tobytes() == np.ascontiguousarray(sc.indices).tobytes()
+    # a second device build of the same scene, then a moved shape, a type change, and a fresh upload
+    b.build_bvh(depth, DEVICE_LAYOUT, fetch=False)
+    assert _same_frame(b.render(p), want)
+    shapes = sc.shapes
+    k = int(np.flatnonzero(shapes["type"] == 0)[0])
+    shapes["sphereCenter"][k] += np.float32(0.25)
+    for t in (a, b):
+        t.update_shapes(k, shapes[k:k + 1])
+    assert _same_frame(b.render(p), a.render(p))
+    shapes["type"][k] = 3                                          # topology change: the layout goes back to the host builder
+    for t in (a, b):
+        t.update_shapes(k, shapes[k:k + 1])
+    assert _same_frame(b.render(p), a.render(p))
+    assert not b.layout_info()["on_device"]
+    b.upload(sc)
+    assert _same_frame(b.render(p), want)
+    a.close(); b.close()
+
+
+def test_device_layout_then_device_animation(rt):
+    """rt_animate (K6 + K7 need the tree's parent / leaf tables, built from the host copy) after a device-side layout."""
+    W, H = 200, 150
+    sc = rt.Scene("toy", W, H)
+    p = rt.make_params(W, H)
+    a = rt.RayTracer(W, H); a.upload(sc); a.register_animations(sc)
+    b = rt.RayTracer(W, H); b.upload_scene(sc.light, sc.camera, sc.shapes)
+    b.build_bvh(8, DEVICE_LAYOUT, fetch=False)
+    b.register_animations(sc)
+    for frame in range(1, 4):
+        a.animate(frame * 0.3, 0.3); b.animate(frame * 0.3, 0.3)
+        assert _same_frame(a.render(p), b.render(p)), "frame %d" % frame
+    a.close(); b.close()
