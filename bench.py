@@ -57,9 +57,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed frame")
-    ap.add_argument("--gather", default="fused", choices=["fused", "nccl"],
-                    help="N>1: fused = every rank's render kernel stores its tiles into rank 0's frame over NVLink peer memory "
-                         "(one tiny all-reduce as completion barrier); nccl = compact shards + dist.gather + untile kernel")
+    ap.add_argument("--gather", default="fused", choices=["fused", "barrier", "nccl"],
+                    help="N>1: fused = every rank's render kernel stores its tiles into rank 0's frame over NVLink peer memory and its "
+                         "last block signals completion (no collective per frame); barrier = the same stores with one tiny all-reduce "
+                         "as completion barrier; nccl = compact shards + dist.gather + untile kernel")
     ap.add_argument("--no-flush", action="store_true", help="diagnostic only: keep L2 warm between steps (not a valid bench line)")
     return ap.parse_args()
 
@@ -278,14 +279,34 @@ def workload_config(args, **more):
 # ---------------------------------------------------------------------------------------------
 # The B200 arm
 # ---------------------------------------------------------------------------------------------
-def setup_fused(torch, dist, tr, rank, world):
-    """Rank 0 exports its full frame over CUDA IPC, the others map it (peer access over NVLink)."""
+def setup_fused(torch, dist, tr, rank, world, signalled=True):
+    """Rank 0 exports its (double-buffered) frame over CUDA IPC, the others map it (peer access over NVLink).  Signalled
+    mode on top: every other rank exports its release word to rank 0 — from then on a frame needs no collective at all
+    (completion words written by the render kernels' last blocks, stream memory operations on the waiting side)."""
     box = [tr.frame_export() if rank == 0 else None]
     handle = [box[0][0] if rank == 0 else None]
     dist.broadcast_object_list(handle, src=0)
     if rank != 0:
         tr.frame_open(handle[0])
-    return box[0][1] if rank == 0 else None
+    mode = "nccl_barrier"
+    if signalled:
+        try:
+            mine = tr.sync_export() if rank != 0 else None
+            words = [None] * world
+            dist.all_gather_object(words, mine)
+            if rank == 0:
+                for r in range(1, world):
+                    tr.sync_peer(r, handle=words[r])
+            tr.sync_enable(world)
+            ok = torch.ones(1, dtype=torch.int32, device="cuda")
+        except Exception:
+            ok = torch.zeros(1, dtype=torch.int32, device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)          # all ranks or none (also the barrier after the words were zeroed)
+        if int(ok[0]) == 1:
+            mode = "signalled"
+        else:
+            tr.sync_enable(0)
+    return (box[0][1] if rank == 0 else None), mode
 
 
 def setup_host_frame(dist, tr, rank, world, W, H):
@@ -307,9 +328,12 @@ def setup_host_frame(dist, tr, rank, world, W, H):
 
 
 def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, flush, fused=False):
-    """Device-timed frames with the scene resident.  Returns per-rank mean ms (total, render, gather)."""
+    """Device-timed frames with the scene resident.  Returns per-rank mean ms (total, render, gather).
+    fused: False = NCCL gather + untile; "nccl_barrier" = peer stores + one all-reduce; "signalled" = peer stores + completion
+    words (rank 0 acquires and releases the frame in its stream; nothing collective)."""
     px = tr.shard_pixels()
-    token = torch.zeros(1, dtype=torch.int32, device="cuda") if (fused and world > 1) else None
+    signalled = fused == "signalled"
+    token = torch.zeros(1, dtype=torch.int32, device="cuda") if (fused and world > 1 and not signalled) else None
     shard = torch.empty((px, 4), dtype=torch.float32, device="cuda")
     full = torch.empty((H, W, 4), dtype=torch.float32, device="cuda") if (rank == 0 and world > 1) else None
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
@@ -319,7 +343,13 @@ def time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, f
         if flush is not None:
             flush.zero_()                       # evict the scene and the image from L2 (untimed)
         e0.record()
-        if token is not None:
+        if signalled:
+            tr.render_device(params)            # tiles go straight into rank 0's frame; the last block signals
+            e1.record()
+            if rank == 0:
+                tr.frame_acquire()              # the stream waits for every rank's completion word
+                tr.frame_release()              # ... and tells them the buffer may be reused two frames on
+        elif token is not None:
             tr.render_device(params)            # tiles go straight into rank 0's frame (peer stores)
             e1.record()
             dist.all_reduce(token)              # completion barrier: the only collective left
@@ -377,6 +407,11 @@ def time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, steps, warmup, 
                 torch.cuda.synchronize()
         elif world == 1:
             tr.render(params, want_ids=False, out=host)
+        elif fused == "signalled":
+            tr.render_device(params)
+            if rank == 0:
+                tr.frame_download(host.data_ptr())  # acquire (completion words) + copy + release: no collective, no host barrier
+            torch.cuda.synchronize()
         elif fused:
             tr.render_device(params)
             dist.all_reduce(token)                  # completion barrier
@@ -550,9 +585,9 @@ def soup_extra(torch, dist, rt, stream, local, rank, world, W, H, flush, steps, 
     if world > 1:
         dist.all_reduce(cnt)
     rays = int(cnt[0])
-    fused = world > 1
-    if fused:
-        setup_fused(torch, dist, tr, rank, world)
+    fused = False
+    if world > 1:
+        _, fused = setup_fused(torch, dist, tr, rank, world)
     tot, ren, gat, frame = time_frames(torch, dist, rt, tr, params, W, H, rank, world, steps, warmup, flush, fused=fused)
     t = torch.tensor([tot, ren, gat], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -566,6 +601,11 @@ def soup_extra(torch, dist, rt, stream, local, rank, world, W, H, flush, steps, 
         tr.update_camera(sc.camera)
         if world == 1:
             tr.render(params, want_ids=False, out=host.numpy().reshape(-1, 4))
+        elif fused == "signalled":
+            tr.render_device(params)
+            if rank == 0:
+                tr.frame_download(host.data_ptr())      # acquire (completion words) + copy + release
+            torch.cuda.synchronize()
         else:
             tr.render_device(params)
             dist.all_reduce(token)                      # every rank's tiles are in rank 0's frame
@@ -677,12 +717,24 @@ def main():
         launches0 = tr.launch_count()
         if rank == 0:
             clocks.start()
-        fused = world > 1 and args.gather == "fused"
-        frame_ptr = setup_fused(torch, dist, tr, rank, world) if fused else None
+        fused = False
+        frame_ptr = None
+        if world > 1 and args.gather != "nccl":
+            frame_ptr, fused = setup_fused(torch, dist, tr, rank, world, signalled=args.gather == "fused")
         tot, ren, gat, last_frame = time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush, fused=fused)
         launches = (tr.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
-        nccl_ms = None
-        if fused:                               # the NCCL-gather path beside it (north_star: gather timed separately)
+        nccl_ms, barrier_ms = None, None
+        if fused:                               # the other exchange paths beside it (north_star: gather timed separately)
+            if fused == "signalled":            # the same peer stores with an all-reduce as completion barrier
+                tr.sync_enable(0)
+                dist.barrier()
+                t2 = torch.tensor(list(time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush, fused="nccl_barrier")[:3]),
+                                  dtype=torch.float64, device="cuda")
+                dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+                barrier_ms = dict(zip(["total_ms", "render_ms", "gather_untile_ms"], t2.tolist()))
+                torch.cuda.synchronize(); dist.barrier()
+                tr.sync_enable(world)
+                torch.cuda.synchronize(); dist.barrier()
             t2 = torch.tensor(list(time_frames(torch, dist, rt, tr, params, W, H, rank, world, args.steps, args.warmup, flush)[:3]),
                               dtype=torch.float64, device="cuda")
             dist.all_reduce(t2, op=dist.ReduceOp.MAX)
@@ -691,12 +743,13 @@ def main():
         frame_ok = None
         if fused:                               # the gathered frame must equal a single-GPU render bit for bit
             tr.render_device(params)
-            dist.all_reduce(torch.zeros(1, dtype=torch.int32, device="cuda"))
+            if fused != "signalled":
+                dist.all_reduce(torch.zeros(1, dtype=torch.int32, device="cuda"))
             torch.cuda.synchronize()
             got = None
             if rank == 0:
                 got = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
-                tr.frame_download(got.data_ptr()); tr.synchronize()
+                tr.frame_download(got.data_ptr()); tr.synchronize()      # signalled: acquire + copy + release
                 solo = rt.RayTracer(W, H, device=local, flags=0)
                 solo.upload(sc)
                 want, _ = solo.render(params, want_ids=False)
@@ -711,7 +764,7 @@ def main():
                                       frame_ptr=frame_ptr, fused=fused)
         # the same step with the frame target in mapped host memory: the kernels' own stores are the D2H
         hostf, alias = setup_host_frame(dist, tr, rank, world, W, H)
-        tr.set_frame_target(alias)
+        tr.set_frame_target(alias)                               # (leaves signalled mode: this target is one host frame)
         e2e_host, _, _ = time_e2e(torch, dist, rt, tr, sc, params, W, H, rank, world, max(3, args.steps // 3), 3, host_alias=alias)
         host_ok = None
         if rank == 0:                           # the host frame must equal a single-GPU rt_render bit for bit
@@ -817,8 +870,10 @@ def main():
             "warmup": args.warmup, "ms_per_step": tot, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "fps": 1e3 / tot, "render_ms": ren, "gather_untile_ms": gat,
-            "gather": ("fused: peer stores from the render kernel + 1 all-reduce barrier" if fused else "nccl gather + untile") if world > 1 else None,
-            "nccl_gather_path": nccl_ms, "gathered_frame_equals_single_gpu": frame_ok,
+            "gather": ({"signalled": "fused + signalled: peer stores from the render kernel, its last block publishes a completion word on rank 0, "
+                                     "rank 0's stream waits on the words (stream memory operation) and releases the buffer: no collective per frame",
+                        "nccl_barrier": "fused: peer stores from the render kernel + 1 all-reduce barrier"}.get(fused, "nccl gather + untile")) if world > 1 else None,
+            "barrier_path": barrier_ms, "nccl_gather_path": nccl_ms, "gathered_frame_equals_single_gpu": frame_ok,
             "rays_per_frame": rays, "rays_counted_by_kernel": rays_gpu, "rays_match_oracle": rays_match,
             "kernel_work": {"node_visits": nodes_gpu, "prim_tests": tests_gpu,
                             "reference_node_visits": consts["node_visits"] if consts else None,

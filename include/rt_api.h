@@ -164,12 +164,36 @@ int rt_item_stats(rt_ctx* ctx, uint64_t out[3]);
  * rt_frame_open.  A single-process driver can hand any device pointer to rt_set_frame_target
  * (NULL switches the mode off).  While a frame target is set,
  * rt_render_device(ctx, params, NULL, NULL) writes there; the frame is complete once every rank
- * has synchronised (a barrier is the only collective left). */
+ * has synchronised (a barrier is the only collective left).  RULE for this plain mode: a rank may render the NEXT
+ * frame into the same target only after the consumer has finished with the current one — a second barrier after the
+ * consumer's read, before any rank renders again (bench.py: "release barrier").  The signalled mode below needs neither. */
 int rt_set_frame_target(rt_ctx* ctx, float* dev_frame);
 int rt_frame_export(rt_ctx* ctx, unsigned char handle[64], float** dev_frame);
 int rt_frame_open(rt_ctx* ctx, const unsigned char handle[64]);
-/* Rank 0: asynchronous copy of the exported frame to the host (ordered on rt_stream). */
+/* Rank 0: asynchronous copy of the exported frame to the host (ordered on rt_stream).  In signalled mode:
+ * rt_frame_acquire + the copy + rt_frame_release. */
 int rt_frame_download(rt_ctx* ctx, float* host_rgba);
+
+/* ---- signalled fused gather: compute + signal, no collective ------------------------------------------------
+ * The exported frame is DOUBLE-BUFFERED (frame f goes to buffer f & 1) and carries one completion word per rank; every
+ * other rank owns one release word.  In signalled mode
+ *   - a rank's render kernel stores its tiles into rank 0's buffer over NVLink and its LAST thread block, after a
+ *     system-scope fence, stores the frame number into this rank's completion word on rank 0;
+ *   - rank 0's rt_frame_acquire makes its stream wait (stream memory operation on local words, no kernel spins) until
+ *     every rank's completion word has reached the frame number, and returns the buffer: work enqueued afterwards sees
+ *     the whole frame;
+ *   - rank 0's rt_frame_release stores the frame number into every other rank's release word; a rank's render of frame
+ *     f + 2 (same buffer) waits in ITS stream for the release of frame f.  Ranks therefore run at most one frame ahead of
+ *     the consumer and never overwrite a frame that is being read: no barrier, no NCCL call per frame.
+ * Set-up (once): rank 0 rt_frame_export, others rt_frame_open (or rt_set_frame_target in one process); every rank r > 0
+ * rt_sync_local (+ rt_sync_export for another process) and rank 0 rt_sync_peer(r, ...) for each of them; then every rank
+ * rt_sync_enable(ctx, world).  Every rank must render the same sequence of frames. */
+int rt_sync_local(rt_ctx* ctx, unsigned** dev_release_word);
+int rt_sync_export(rt_ctx* ctx, unsigned char handle[64]);
+int rt_sync_peer(rt_ctx* ctx, int rank, unsigned* dev_release_word_or_null, const unsigned char handle_or_null[64]);
+int rt_sync_enable(rt_ctx* ctx, int world_or_0);
+int rt_frame_acquire(rt_ctx* ctx, float** dev_frame);
+int rt_frame_release(rt_ctx* ctx);
 /* Host frame: pin and map a caller-owned host buffer of W*H float4 (for several ranks: one POSIX
  * shared-memory segment that every process maps) and return its device alias.  Passed to
  * rt_set_frame_target, the render kernel stores its pixels straight into host memory over this

@@ -57,7 +57,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_sync_local", "rt_sync_export", "rt_sync_peer", "rt_sync_enable", "rt_frame_acquire", "rt_frame_release", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -107,6 +107,12 @@ def _declare(L):
     L.rt_frame_export.argtypes = [vp, C.c_char_p, C.POINTER(vp)]; L.rt_frame_export.restype = ip
     L.rt_frame_open.argtypes = [vp, C.c_char_p]; L.rt_frame_open.restype = ip
     L.rt_frame_download.argtypes = [vp, vp]; L.rt_frame_download.restype = ip
+    L.rt_sync_local.argtypes = [vp, C.POINTER(vp)]; L.rt_sync_local.restype = ip
+    L.rt_sync_export.argtypes = [vp, C.c_char_p]; L.rt_sync_export.restype = ip
+    L.rt_sync_peer.argtypes = [vp, ip, vp, C.c_char_p]; L.rt_sync_peer.restype = ip
+    L.rt_sync_enable.argtypes = [vp, ip]; L.rt_sync_enable.restype = ip
+    L.rt_frame_acquire.argtypes = [vp, C.POINTER(vp)]; L.rt_frame_acquire.restype = ip
+    L.rt_frame_release.argtypes = [vp]; L.rt_frame_release.restype = ip
     L.rt_host_frame_register.argtypes = [vp, vp, C.c_size_t, C.POINTER(vp)]; L.rt_host_frame_register.restype = ip
     L.rt_host_frame_unregister.argtypes = [vp, vp]; L.rt_host_frame_unregister.restype = ip
     L.rt_wait_frames.argtypes = [vp, ip]; L.rt_wait_frames.restype = ip
@@ -353,6 +359,32 @@ class RayTracer:
 
     def frame_download(self, host):
         self._chk(self._L.rt_frame_download(self._c, _ptr(host)))
+
+    def sync_local(self):
+        """This rank's release word (device pointer) for the signalled fused gather."""
+        p = C.c_void_p()
+        self._chk(self._L.rt_sync_local(self._c, C.byref(p)))
+        return p.value
+
+    def sync_export(self):
+        h = C.create_string_buffer(64)
+        self._chk(self._L.rt_sync_export(self._c, h))
+        return h.raw
+
+    def sync_peer(self, rank, dev_word=None, handle=None):
+        self._chk(self._L.rt_sync_peer(self._c, int(rank), C.c_void_p(dev_word) if dev_word else None,
+                                       C.create_string_buffer(handle, 64) if handle else None))
+
+    def sync_enable(self, world):
+        self._chk(self._L.rt_sync_enable(self._c, int(world)))
+
+    def frame_acquire(self):
+        p = C.c_void_p()
+        self._chk(self._L.rt_frame_acquire(self._c, C.byref(p)))
+        return p.value
+
+    def frame_release(self):
+        self._chk(self._L.rt_frame_release(self._c))
 
     def host_frame_register(self, host):
         """host: a C-contiguous numpy float32 array of W*H*4 (may live in shared memory); returns the device alias."""

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <cstdint>
 #include <algorithm>
 #include <new>
 #include <string>
@@ -149,6 +150,14 @@ struct rt_ctx {
     DevBuf<float4> frame;             // full W*H frame other ranks write into (rt_frame_export)
     float* frameTarget = nullptr;     // where this rank's tiles go row-major (local frame, peer mapping, or caller's)
     void* ipcOpened = nullptr;        // mapping obtained from cudaIpcOpenMemHandle
+    // signalled fused gather (rt_api.h): double-buffered frame + completion words on rank 0, one release word per other rank
+    bool syncOn = false;
+    unsigned frameSeq = 0;            // frames rendered in signalled mode (frame f -> buffer f & 1)
+    DevBuf<unsigned> releaseLocal, ctaDone;
+    unsigned* peerRelease[64] = {};   // rank 0: the other ranks' release words (same-process pointers or IPC mappings)
+    void* peerIpc[64] = {};
+    DevBuf<unsigned*> dPeerRelease;
+    int (*waitValue32)(cudaStream_t, unsigned long long, unsigned, unsigned) = nullptr;   // cuStreamWaitValue32 (driver entry point)
     DevBuf<unsigned long long> tally;
     DevBuf<unsigned int> queue;       // work-stealing counter of K1
     DevBuf<unsigned> itemCost, heavyList, lptCtl;   // heavy-first scheduling from the previous frame's item costs
@@ -493,6 +502,8 @@ void rt_destroy(rt_ctx* c) {
     c->hOrderB.release(); c->dOrderB.release(); c->hLinkCntB.release(); c->dLinkCntB.release(); c->dNodesB.release();
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
     if (c->ipcOpened) cudaIpcCloseMemHandle(c->ipcOpened);
+    for (auto& p : c->peerIpc) if (p) cudaIpcCloseMemHandle(p);
+    c->releaseLocal.release(); c->ctaDone.release(); c->dPeerRelease.release();
     c->frame.release();
     c->itemCost.release(); c->heavyList.release(); c->lptCtl.release(); c->heavyFlag.release();
     c->image.release(); c->ids.release(); c->tally.release(); c->queue.release();
@@ -684,8 +695,21 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     F.W = c->W; F.H = c->H; F.tilesX = tiles_x(c); F.tilesY = tiles_y(c);
     F.shardRank = c->shardRank; F.shardWorld = c->shardWorld; F.nTilesMine = tiles_mine(c);
     F.writeIds = (count && dev_ids) ? 2 : wantIds ? 1 : 0;
-    F.frameTarget = 0;
+    F.frameTarget = 0; F.doneWord = nullptr; F.ctaDone = nullptr; F.doneSeq = 0;
     if (useFrame) { F.frameTarget = 1; dev_rgba = c->frameTarget; }
+    if (useFrame && c->syncOn) {
+        const size_t frameFloats = 4 * (size_t)c->W * (size_t)c->H;
+        const unsigned seq = ++c->frameSeq;
+        dev_rgba = c->frameTarget + (seq & 1u) * frameFloats;
+        if (c->shardRank != 0) {
+            // buffer seq & 1 held frame seq - 2: wait (in the stream, no kernel spins) until rank 0 has released it
+            if (seq > 2 && c->waitValue32(c->stream, (unsigned long long)(uintptr_t)c->releaseLocal.p, seq - 2, 0u /* GEQ */) != 0)
+                return fail(c, RT_ERR_CUDA, "cuStreamWaitValue32 (release word)");
+            CU(c, cudaMemsetAsync(c->ctaDone.p, 0, sizeof(unsigned), c->stream));
+            F.doneWord = reinterpret_cast<unsigned*>(c->frameTarget + 2 * frameFloats) + c->shardRank;
+            F.ctaDone = c->ctaDone.p; F.doneSeq = seq;
+        }
+    }
 
     const int tilesMine = tiles_mine(c);
     const bool toHost = host_rgba || host_ids;
@@ -814,13 +838,17 @@ int rt_wait_frames(rt_ctx* c, int max_in_flight) {
 int rt_set_frame_target(rt_ctx* c, float* dev_frame) {
     if (!c) return RT_ERR_ARG;
     c->frameTarget = dev_frame;
+    c->syncOn = false;                 // a new target: signalled mode is switched on again by rt_sync_enable
     return RT_OK;
 }
 
 int rt_frame_export(rt_ctx* c, unsigned char handle[64], float** dev_frame) {
     if (!c || !handle) return RT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
-    CU(c, c->frame.reserve((size_t)c->W * (size_t)c->H));
+    // two frames (signalled mode alternates them) + 64 completion words
+    const size_t want = 2 * (size_t)c->W * (size_t)c->H + 16;
+    if (c->frame.cap < want) { c->frame.release(); CU(c, cudaMalloc(&c->frame.p, want * sizeof(float4))); c->frame.cap = want; }
+    CU(c, cudaMemset(c->frame.p + 2 * (size_t)c->W * (size_t)c->H, 0, 16 * sizeof(float4)));
     cudaIpcMemHandle_t h;
     CU(c, cudaIpcGetMemHandle(&h, c->frame.p));
     static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
@@ -843,11 +871,101 @@ int rt_frame_open(rt_ctx* c, const unsigned char handle[64]) {
     return RT_OK;
 }
 
+int rt_frame_acquire(rt_ctx* c, float** dev_frame) {
+    if (!c) return RT_ERR_ARG;
+    if (!c->syncOn || c->shardRank != 0 || !c->frame.p) return fail(c, RT_ERR_STATE, "rt_frame_acquire: rank 0 in signalled mode only");
+    CU(c, cudaSetDevice(c->device));
+    unsigned* words = reinterpret_cast<unsigned*>(c->frame.p + 2 * (size_t)c->W * (size_t)c->H);
+    for (int r = 1; r < c->shardWorld; ++r)
+        if (c->waitValue32(c->stream, (unsigned long long)(uintptr_t)(words + r), c->frameSeq, 0u /* GEQ */) != 0)
+            return fail(c, RT_ERR_CUDA, "cuStreamWaitValue32 (completion word)");
+    if (dev_frame) *dev_frame = reinterpret_cast<float*>(c->frame.p) + (c->frameSeq & 1u) * 4 * (size_t)c->W * (size_t)c->H;
+    return RT_OK;
+}
+
+int rt_frame_release(rt_ctx* c) {
+    if (!c) return RT_ERR_ARG;
+    if (!c->syncOn || c->shardRank != 0) return fail(c, RT_ERR_STATE, "rt_frame_release: rank 0 in signalled mode only");
+    CU(c, cudaSetDevice(c->device));
+    if (c->shardWorld > 1) {
+        release_kernel<<<1, 64, 0, c->stream>>>(c->dPeerRelease.p, c->shardWorld, c->frameSeq);
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
+    return RT_OK;
+}
+
 int rt_frame_download(rt_ctx* c, float* host_rgba) {
     if (!c || !host_rgba) return RT_ERR_ARG;
     if (!c->frame.p) return fail(c, RT_ERR_STATE, "no exported frame on this context");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemcpyAsync(host_rgba, c->frame.p, (size_t)c->W * (size_t)c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    const float* src = reinterpret_cast<const float*>(c->frame.p);
+    if (c->syncOn) { float* f = nullptr; int rc = rt_frame_acquire(c, &f); if (rc != RT_OK) return rc; src = f; }
+    CU(c, cudaMemcpyAsync(host_rgba, src, (size_t)c->W * (size_t)c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    if (c->syncOn) return rt_frame_release(c);
+    return RT_OK;
+}
+
+int rt_sync_local(rt_ctx* c, unsigned** dev_release_word) {
+    if (!c) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->releaseLocal.reserve(1));
+    CU(c, cudaMemset(c->releaseLocal.p, 0, sizeof(unsigned)));
+    if (dev_release_word) *dev_release_word = c->releaseLocal.p;
+    return RT_OK;
+}
+
+int rt_sync_export(rt_ctx* c, unsigned char handle[64]) {
+    if (!c || !handle) return RT_ERR_ARG;
+    int rc = rt_sync_local(c, nullptr);
+    if (rc != RT_OK) return rc;
+    cudaIpcMemHandle_t h;
+    CU(c, cudaIpcGetMemHandle(&h, c->releaseLocal.p));
+    std::memcpy(handle, &h, 64);
+    return RT_OK;
+}
+
+int rt_sync_peer(rt_ctx* c, int rank, unsigned* dev_word, const unsigned char handle[64]) {
+    if (!c || rank < 1 || rank >= 64 || (!dev_word && !handle)) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    if (c->peerIpc[rank]) { cudaIpcCloseMemHandle(c->peerIpc[rank]); c->peerIpc[rank] = nullptr; }
+    if (!dev_word) {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handle, 64);
+        void* p = nullptr;
+        CU(c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        c->peerIpc[rank] = p; dev_word = static_cast<unsigned*>(p);
+    }
+    c->peerRelease[rank] = dev_word;
+    return RT_OK;
+}
+
+int rt_sync_enable(rt_ctx* c, int world) {
+    if (!c || world < 0 || world > 64) return RT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    if (world == 0) { c->syncOn = false; return RT_OK; }
+    if (world != c->shardWorld) return fail(c, RT_ERR_ARG, "rt_sync_enable: world differs from rt_set_shard's");
+    if (!c->frameTarget) return fail(c, RT_ERR_STATE, "rt_sync_enable needs the exported frame (rt_frame_export / rt_frame_open / rt_set_frame_target)");
+    if (!c->waitValue32) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn || q != cudaDriverEntryPointSuccess)
+            return fail(c, RT_ERR_CUDA, "stream memory operations (cuStreamWaitValue32) are not available");
+        c->waitValue32 = reinterpret_cast<int (*)(cudaStream_t, unsigned long long, unsigned, unsigned)>(fn);
+    }
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (c->shardRank == 0) {
+        if (!c->frame.p) return fail(c, RT_ERR_STATE, "rt_sync_enable on rank 0 needs rt_frame_export");
+        for (int r = 1; r < world; ++r) if (!c->peerRelease[r]) return fail(c, RT_ERR_STATE, "rt_sync_enable: a rank's release word is missing (rt_sync_peer)");
+        CU(c, c->dPeerRelease.reserve(64));
+        CU(c, cudaMemcpy(c->dPeerRelease.p, c->peerRelease, 64 * sizeof(unsigned*), cudaMemcpyHostToDevice));
+        CU(c, cudaMemset(c->frame.p + 2 * (size_t)c->W * (size_t)c->H, 0, 16 * sizeof(float4)));
+    } else {
+        if (!c->releaseLocal.p) return fail(c, RT_ERR_STATE, "rt_sync_enable: rt_sync_local / rt_sync_export first");
+        CU(c, cudaMemset(c->releaseLocal.p, 0, sizeof(unsigned)));
+        CU(c, c->ctaDone.reserve(1));
+    }
+    c->frameSeq = 0; c->syncOn = true;
     return RT_OK;
 }
 

@@ -92,6 +92,10 @@ struct FrameParams {
     const unsigned char* heavyFlag;
     unsigned* lptCtl;          // [0] number of heavy items, [1] claim counter of the heavy list
     int   frameTarget;         // world > 1: colours go row-major into a full W*H frame (rank 0's, possibly peer memory)
+    // signalled fused gather: the last thread block of the launch stores doneSeq into *doneWord (rank 0's memory)
+    unsigned* doneWord;        // NULL = off
+    unsigned* ctaDone;         // local counter of finished thread blocks (zeroed before the launch)
+    unsigned  doneSeq;
 };
 
 // ---------------------------------------------------------------------------

@@ -502,6 +502,18 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             if (lane == 0 && v && i != 16 && i != 19) atomicAdd(tally + i, v);
         }
+    }    if (P.doneWord) {
+        // compute + signal: every thread makes its pixel stores (peer memory over NVLink) visible system-wide, the last
+        // thread block of the launch then publishes the frame number in this rank's completion word on rank 0
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(P.ctaDone, 1u) == gridDim.x - 1) {
+                __threadfence_system();
+                *reinterpret_cast<volatile unsigned*>(P.doneWord) = P.doneSeq;
+            }
+        }
     }
 }
 
@@ -576,6 +588,12 @@ __global__ void repack_prims_kernel(const rt_flat_shape* __restrict__ shapes, co
 // K3: untile.  shards = `world` compact buffers of shardPixels float4 each, rank
 // after rank (the NCCL gather's landing layout) -> row-major W*H.
 // ---------------------------------------------------------------------------
+// signalled fused gather: rank 0 tells the other ranks that it has finished reading frame `seq`
+__global__ void release_kernel(unsigned* const* __restrict__ words, int n, unsigned seq) {
+    const int i = threadIdx.x;
+    if (i < n && words[i]) { __threadfence_system(); *reinterpret_cast<volatile unsigned*>(words[i]) = seq; }
+}
+
 __global__ void untile_kernel(const float4* __restrict__ shards, float4* __restrict__ out, int W, int H,
                               int tilesX, int world, long long shardPixels) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

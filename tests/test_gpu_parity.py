@@ -588,3 +588,51 @@ def test_zero_bounces_after_a_warmed_up_heavy_list(rt, oracle):
     rgba, ids = tr.render(p0)
     assert np.array_equal(rgba[..., :3], np.zeros_like(rgba[..., :3])) and (rgba[..., 3] == 1).all()
     tr.close()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_signalled_fused_gather_animated(rt, world):
+    """Compute + signal, no collective (rt_api.h "signalled fused gather"), emulated on one device with one context per
+    rank: the other ranks run one frame ahead, rank 0 renders, acquires, downloads and releases frame after frame.  The camera moves every frame, so a frame torn by a rank that ran ahead (overwriting a
+    buffer still being read), or one acquired before a rank's tiles landed, differs from the single-GPU render."""
+    import torch
+    W, H, frames = 333, 201, 7
+    sc = rt.Scene("monkey", W, H)
+    p = rt.make_params(W, H)
+    cams = []
+    for f in range(frames):
+        sc.set_camera((30.0 - 3.0 * f, -5.0, 40.0), (0.0, 10.0, -8.0))
+        cams.append(sc.camera)
+    solo = rt.RayTracer(W, H, flags=0); solo.upload(sc)
+    want = []
+    for f in range(frames):
+        solo.update_camera(cams[f])
+        want.append(solo.render(p, want_ids=False)[0].copy())
+    solo.close()
+    ranks = [rt.RayTracer(W, H, flags=0) for _ in range(world)]
+    for r, t in enumerate(ranks):
+        t.upload(sc); t.set_shard(r, world)
+    _, base = ranks[0].frame_export()
+    for r in range(1, world):
+        ranks[r].set_frame_target(base)
+        ranks[0].sync_peer(r, dev_word=ranks[r].sync_local())
+    for t in ranks:
+        t.sync_enable(world)
+    def others(f):                                # the other ranks enqueue frame f
+        for r in range(1, world):
+            ranks[r].update_camera(cams[f]); ranks[r].render_device(p)
+    host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+    others(0)
+    for f in range(frames):
+        # the other ranks run ONE frame ahead (into the other buffer) while rank 0 renders and reads frame f.  (On ONE
+        # device nothing may be enqueued whose wait is not already satisfied: streams of one process can share a hardware
+        # queue, and a pending wait would block the very work it waits for.  Across GPUs the waits gate real run-ahead.)
+        if f + 1 < frames:
+            others(f + 1)
+        ranks[0].update_camera(cams[f]); ranks[0].render_device(p)
+        host.fill_(-1.0)
+        ranks[0].frame_download(host.data_ptr())
+        ranks[0].synchronize()
+        assert np.array_equal(host.numpy().view(np.uint32), want[f].view(np.uint32)), "frame %d, world %d" % (f, world)
+    for t in ranks:
+        t.synchronize(); t.close()
