@@ -744,8 +744,9 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         CU(c, cudaMemsetAsync(c->lptCtl.p, 0, 4 * sizeof(unsigned), c->stream));
         if (c->lptItems == items) {
             lpt_sum_kernel<<<64, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p);
+            const int gridWarps = c->gridBlocks[variant] * (RT_BLOCK_THREADS / 32);
             lpt_mark_kernel<<<(items + 255) / 256, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p, c->heavyList.p, c->heavyFlag.p,
-                                                                         c->gridBlocks[variant] * (RT_BLOCK_THREADS / 32));
+                                                                         gridWarps, items < 5 * gridWarps ? RT_HEAVY_FACTOR_FEW : RT_HEAVY_FACTOR);
             c->launches += 2;
         }
         c->lptItems = items;

@@ -521,8 +521,14 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
 // Heavy-first list for the next launch from this launch's item costs.  ctl[0] = number of heavy
 // items (out), ctl[2..3] = 64-bit sum of costs (scratch).  Two tiny launches per frame.
 // ---------------------------------------------------------------------------
+// A block is HEAVY when its cost exceeds heavyFactor x the mean.  Measured on the car frame at 4K over 1 / 2 / 4 / 8 ranks
+// (profiles/r2/heavy_first_sweep.txt): 4 x is as good as 3 x on a whole frame and 6 - 8 % faster on a half or a quarter
+// of it; with fewer than five blocks per warp (an eighth of the frame, 800x600) 3 x is better.
 #ifndef RT_HEAVY_FACTOR
-#define RT_HEAVY_FACTOR 3
+#define RT_HEAVY_FACTOR 4
+#endif
+#ifndef RT_HEAVY_FACTOR_FEW
+#define RT_HEAVY_FACTOR_FEW 3
 #endif
 __global__ void lpt_sum_kernel(const unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl) {
     unsigned long long s = 0;
@@ -541,12 +547,12 @@ __global__ void lpt_sum_kernel(const unsigned* __restrict__ cost, int n, unsigne
 #define RT_SPLIT_K 2           // parts ~ K * cost / share, rounded down to a power of two (two parts from cost > share on)
 #endif
 __global__ void lpt_mark_kernel(unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl,
-                                unsigned* __restrict__ heavyList, unsigned char* __restrict__ heavyFlag, int gridWarps) {
+                                unsigned* __restrict__ heavyList, unsigned char* __restrict__ heavyFlag, int gridWarps, int heavyFactor) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const unsigned long long sum = *reinterpret_cast<const unsigned long long*>(ctl + 2);
     const unsigned long long ci = cost[i];
-    const bool heavy = ci * (unsigned long long)n > (unsigned long long)RT_HEAVY_FACTOR * sum;
+    const bool heavy = ci * (unsigned long long)n > (unsigned long long)heavyFactor * sum;
     heavyFlag[i] = heavy ? 1 : 0;
     if (!heavy) return;
     const unsigned long long want = sum > 0 ? ci * (unsigned long long)gridWarps * RT_SPLIT_K / sum : 0;   // ~ K * cost / share
