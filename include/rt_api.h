@@ -85,6 +85,8 @@ enum {
  * Replaces ComputeShader::ComputeShader + the output-texture creation
  * (computeShader.hpp:29-83, main.cpp:182-191).  device = CUDA ordinal. */
 int  rt_create(rt_ctx** out, int width, int height, int device, unsigned flags);
+/* Drains the context's streams, frees everything it owns, unpins host frames still registered (rt_host_frame_register)
+ * and closes IPC mappings.  The handle is invalid afterwards (NULL is accepted; a second call on the same handle is not). */
 void rt_destroy(rt_ctx* ctx);
 const char* rt_last_error(const rt_ctx* ctx);
 
@@ -261,7 +263,8 @@ int rt_present(rt_ctx* ctx, const float* dev_rgba, uint8_t* dev_rgba8_out, int64
 void* rt_stream(rt_ctx* ctx);                 /* cudaStream_t of the context     */
 /* Run all further work of this context on a caller-owned cudaStream_t (e.g. the
  * stream a framework times with its own events); NULL restores the internal one.
- * The previous stream is drained first. */
+ * The previous stream is drained first (pinned-shadow copies in flight complete with it).  A context is meant to be
+ * driven by ONE host thread at a time: the calls are not internally synchronised. */
 int   rt_set_stream(rt_ctx* ctx, void* cuda_stream);
 int   rt_synchronize(rt_ctx* ctx);
 float* rt_device_image(rt_ctx* ctx);          /* internal float4 image           */

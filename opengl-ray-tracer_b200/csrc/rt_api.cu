@@ -150,6 +150,7 @@ struct rt_ctx {
     DevBuf<float4> frame;             // full W*H frame other ranks write into (rt_frame_export)
     float* frameTarget = nullptr;     // where this rank's tiles go row-major (local frame, peer mapping, or caller's)
     void* ipcOpened = nullptr;        // mapping obtained from cudaIpcOpenMemHandle
+    std::vector<void*> hostFrames;    // host buffers pinned by rt_host_frame_register (undone by rt_destroy if the caller did not)
     // signalled fused gather (rt_api.h): double-buffered frame + completion words on rank 0, one release word per other rank
     bool syncOn = false;
     unsigned frameSeq = 0;            // frames rendered in signalled mode (frame f -> buffer f & 1)
@@ -501,6 +502,8 @@ void rt_destroy(rt_ctx* c) {
     c->hSubBox.release(); c->dSubBox.release(); c->dNodesT.release();
     c->hOrderB.release(); c->dOrderB.release(); c->hLinkCntB.release(); c->dLinkCntB.release(); c->dNodesB.release();
     c->q0.release(); c->q1.release(); c->q2.release(); c->q3.release(); c->ptype.release();
+    for (void* h : c->hostFrames) cudaHostUnregister(h);     // a registered host frame the caller never unregistered
+    c->hostFrames.clear();
     if (c->ipcOpened) cudaIpcCloseMemHandle(c->ipcOpened);
     for (auto& p : c->peerIpc) if (p) cudaIpcCloseMemHandle(p);
     c->releaseLocal.release(); c->ctaDone.release(); c->dPeerRelease.release();
@@ -979,6 +982,7 @@ int rt_host_frame_register(rt_ctx* c, void* host_frame, size_t bytes, float** de
     cudaError_t e = cudaHostGetDevicePointer(&d, host_frame, 0);
     if (e != cudaSuccess) { cudaHostUnregister(host_frame); CU(c, e); }
     *dev_alias = static_cast<float*>(d);
+    c->hostFrames.push_back(host_frame);
     return RT_OK;
 }
 
@@ -987,6 +991,7 @@ int rt_host_frame_unregister(rt_ctx* c, void* host_frame) {
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaHostUnregister(host_frame));
+    c->hostFrames.erase(std::remove(c->hostFrames.begin(), c->hostFrames.end(), host_frame), c->hostFrames.end());
     return RT_OK;
 }
 

@@ -21,6 +21,7 @@ ap.add_argument("--steps", type=int, default=20)
 ap.add_argument("--warmup", type=int, default=5)
 ap.add_argument("--cases", default="car4k,car800,monkey800")
 ap.add_argument("--world", type=int, default=1)
+ap.add_argument("--rank", type=int, default=0)
 a = ap.parse_args()
 rt = rtload.load()
 CASES = {"car4k": ("car", 3840, 2160, 0), "car800": ("car", 800, 600, 0), "monkey800": ("monkey", 800, 600, 0),
@@ -35,7 +36,7 @@ with torch.cuda.stream(stream):
         p = rt.make_params(W, H, useMollerTrumbore=case.endswith("mtfr"), useFresnel=case.endswith("mtfr"))
         tr = rt.RayTracer(W, H, device=0, flags=a.flags)
         tr.set_stream(stream.cuda_stream)
-        tr.set_shard(0, a.world)
+        tr.set_shard(a.rank, a.world)
         tr.upload(sc)
         px = tr.shard_pixels()
         img = torch.empty((px, 4), dtype=torch.float32, device="cuda")
