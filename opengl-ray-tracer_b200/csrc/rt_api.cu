@@ -680,21 +680,6 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         if (!pipeline) c->framePending[par] = false;
     }
 
-    // EXPERIMENT (DESIGN.md par. 3, profiles/r2/design_choices.json): RT_L2_WINDOW=1 pins the walked node list in L2 with an
-    // access-policy window on the render stream.  Off by default: it changes nothing on the car (the list never leaves L1 / L2)
-    // and nothing measurable on the soup.
-    static const bool l2Window = [] { const char* e = std::getenv("RT_L2_WINDOW"); return e && e[0] == '1'; }();
-    if (l2Window && c->nDfs > 0) {
-        cudaStreamAttrValue av{};
-        av.accessPolicyWindow.base_ptr = c->nDfsB > 0 ? (void*)c->dNodesB.p : (void*)c->dNodesT.p;
-        size_t bytes = (size_t)(c->nDfsB > 0 ? c->nDfsB : c->nDfs) * 2 * sizeof(float4);
-        int maxWin = 0; cudaDeviceGetAttribute(&maxWin, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
-        if (maxWin > 0 && bytes > (size_t)maxWin) bytes = (size_t)maxWin;
-        av.accessPolicyWindow.num_bytes = bytes; av.accessPolicyWindow.hitRatio = 1.0f;
-        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting; av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes);
-        cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av);
-    }
     DeviceScene S;
     S.nodes = c->dNodesT.p; S.nodesB = c->nDfsB > 0 ? c->dNodesB.p : nullptr; S.nNodesB = c->nDfsB; S.q0 = c->q0.p; S.q1 = c->q1.p; S.q2 = c->q2.p; S.q3 = c->q3.p;
     S.ptype = c->ptype.p; S.pshape = c->dPshape.p; S.prank = c->dPrank.p; S.shapes = c->dShapes.p;

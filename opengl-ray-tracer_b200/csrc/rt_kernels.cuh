@@ -137,15 +137,9 @@ __device__ __noinline__ Cand leaf_generic(const float4* __restrict__ q0, const f
 #ifndef RT_SAMPLE
 #define RT_SAMPLE 4         // power of two
 #endif
-#ifndef RT_SMEM_TOP
-#define RT_SMEM_TOP 0       // EXPERIMENT (DESIGN.md par. 3, profiles/r2/design_choices.json): the first RT_SMEM_TOP nodes of the walked list staged in shared memory; 0 = off (shipped)
-#endif
+
 template <bool MT, bool COUNT>
-__device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active, bool anyMode, Tally& tl, int tbase
-#if RT_SMEM_TOP
-                                     , const float4* __restrict__ smemTop
-#endif
-                                     ) {
+__device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active, bool anyMode, Tally& tl, int tbase) {
     const Ray& r = q.r;
     int k = active ? 0 : RT_DONE;
     // Rays that cannot use the NaN-free fast slab test (non-finite origin or 1/d) or for which the
@@ -164,11 +158,13 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
     // List B (own tree over the reference leaves) is valid for rays with finite origin and 1/d inside
     // omax; a warp with any other ray walks list A, the reference's own tree order.
     const bool useB = S.nNodesB > 0 && !anyOdd;
-    const int n = useB ? S.nNodesB : S.nNodes;
+    int n = useB ? S.nNodesB : S.nNodes;
     const char* __restrict__ nbase = reinterpret_cast<const char*>(useB ? S.nodesB : S.nodes);
-    // keep the selected base in (uniform) registers: without this barrier ptxas re-selects list A / B from the constant
-    // bank in every iteration (3 of ~58 instructions; car 4K 1.295 -> 1.273 ms, profiles/r2/design_choices.json)
+    // keep the selected list (base and length) in registers: without these barriers ptxas re-selects list A / B from the
+    // constant bank in every iteration and leaves the mode-sampling instructions predicated in the loop (~8 of ~58
+    // instructions per iteration; car 4K 1.295 -> 1.214 ms, profiles/r2/design_choices.json)
     asm volatile("" : "+l"(nbase));
+    asm volatile("" : "+r"(n));
     for (;;) {
         const int kmin = __reduce_min_sync(RT_FULL, k);
         if (kmin >= n) break;
@@ -181,14 +177,8 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
             if (low >= RT_LOW_RUNS) pm = 0;
         }
         const float4* np = reinterpret_cast<const float4*>(nbase + (unsigned)km * 32u);
-#if RT_SMEM_TOP
-        float4 a, b;
-        if (useB && km < RT_SMEM_TOP) { a = smemTop[2 * km]; b = smemTop[2 * km + 1]; }
-        else { a = __ldg(np); b = __ldg(np + 1); }
-#else
         const float4 a = __ldg(np);
         const float4 b = __ldg(np + 1);
-#endif
         const int cw = __float_as_int(b.w);
         const int lnk = __float_as_int(a.w);
         RT_TALLY(4, mine ? 1 : 0);
@@ -221,7 +211,6 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
         }
     }
 }
-
 // Brute-force twins (a14, useBVH == false): linear scan over the raw shapes.
 template <bool MT>
 __device__ __forceinline__ void scan_closest(const DeviceScene& S, const Ray& r, Hit& h) {
@@ -292,11 +281,7 @@ __device__ __forceinline__ V3 phong(V3 point, V3 normal, V3 viewDir, V3 lpos, V3
 // so that the walk is instantiated ONCE and both kinds of query share its code.
 template <bool MT, bool COUNT>
 __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameParams& P, int x, int y, bool inside,
-                                              int& idOut, Tally& tl, bool paired
-#if RT_SMEM_TOP
-                                              , const float4* __restrict__ smemTop
-#endif
-                                              ) {
+                                              int& idOut, Tally& tl, bool paired) {
     const bool bf = S.boxesFinite != 0;
     // Live state across the walks is kept small (occupancy): the view direction, the hit point, the hit
     // shape's index, and the two colour accumulators.  Normal and material are re-read after the shadow walk.
@@ -352,11 +337,7 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
         q.slot = -1; q.p = mk(0.f, 0.f, 0.f);
         int nextSlot = -1; V3 nextP = mk(0.f, 0.f, 0.f);   // paired: the partner's closest hit of the reflected ray
         if (P.useBVH) {
-#if RT_SMEM_TOP
-            walk<MT, COUNT>(S, q, alive || helper, shadowStep && !helper, tl, step < 2 ? 8 : 12, smemTop);
-#else
             walk<MT, COUNT>(S, q, alive || helper, shadowStep && !helper, tl, step < 2 ? 8 : 12);
-#endif
             if (paired && shadowStep) {
                 nextSlot = __shfl_xor_sync(RT_FULL, q.slot, 16);
                 nextP = mk(__shfl_xor_sync(RT_FULL, q.p.x, 16), __shfl_xor_sync(RT_FULL, q.p.y, 16), __shfl_xor_sync(RT_FULL, q.p.z, 16));
@@ -433,11 +414,6 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
               unsigned long long* __restrict__ tally, unsigned int* __restrict__ queue) {
     Tally tl;
     if (COUNT) { for (int i = 0; i < RT_NTALLY; ++i) tl.v[i] = 0; }
-#if RT_SMEM_TOP
-    __shared__ float4 smemTop[2 * RT_SMEM_TOP];
-    if (S.nNodesB > 0) for (int i = threadIdx.x; i < 2 * RT_SMEM_TOP && i < 2 * S.nNodesB; i += blockDim.x) smemTop[i] = __ldg(S.nodesB + i);
-    __syncthreads();
-#endif
     const int lane = threadIdx.x & 31;
     const int nItems = P.nTilesMine * RT_WARPS_PER_TILE;
     // Heavy-first order: the critical path of a frame is its slowest 8x4 block (an incoherent bounce
@@ -487,11 +463,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         long long clk0 = 0;
         unsigned long long it0[4] = {0, 0, 0, 0};
         if (COUNT) { cost0 = tl.v[4] + tl.v[5]; clk0 = clock64(); it0[0] = tl.v[8]; it0[1] = tl.v[9]; it0[2] = tl.v[12]; it0[3] = tl.v[13]; }
-#if RT_SMEM_TOP
-        c = shade_pixel<MT, COUNT>(S, P, x, y, inside, id, tl, parts >= 2, smemTop);
-#else
         c = shade_pixel<MT, COUNT>(S, P, x, y, inside, id, tl, parts >= 2);
-#endif
         if (COUNT && P.writeIds == 2) id = (int)(tl.v[4] + tl.v[5] - cost0);   // diagnostic: per-pixel work AOV
         if (COUNT) {
             const unsigned long long dt = (unsigned long long)(clock64() - clk0);
