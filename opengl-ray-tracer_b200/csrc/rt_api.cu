@@ -164,6 +164,7 @@ struct rt_ctx {
     DevBuf<unsigned> itemCost, heavyList, lptCtl;   // heavy-first scheduling from the previous frame's item costs
     DevBuf<unsigned char> heavyFlag;
     int lptItems = -1;                // item count the recorded costs belong to (-1: none yet)
+    unsigned lptFrame = 0;            // frames rendered with these costs (parity = slot of the control block)
     int gridBlocks[4] = {0, 0, 0, 0}; // persistent grid per kernel variant
     int shardRank = 0, shardWorld = 1;
 };
@@ -728,8 +729,6 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         if (nBands < 1) nBands = 1;
     }
     CU(c, c->queue.reserve(RT_MAX_BANDS));
-    CU(c, cudaMemsetAsync(c->queue.p, 0, RT_MAX_BANDS * sizeof(unsigned int), c->stream));
-    cudaEventRecord(c->ev[4], c->stream);
     const int variant = (F.useMT ? 1 : 0) + (count ? 2 : 0);
     if (tilesMine > 0 && c->gridBlocks[variant] == 0) {       // persistent grid: fill every SM once
         int perSM = 0;
@@ -738,22 +737,30 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, RT_BLOCK_THREADS, 0));
         c->gridBlocks[variant] = c->smCount * (perSM > 0 ? perSM : 1);
     }
-    // heavy-first order (single-launch renders): build the list from the previous frame's item costs
-    F.itemCost = nullptr; F.heavyList = nullptr; F.heavyFlag = nullptr; F.lptCtl = nullptr;
-    if (nBands == 1 && !count && tilesMine > 0 && tilesMine * RT_WARPS_PER_TILE < (1 << 24) && !(c->flags & RT_FLAG_NO_HEAVY_FIRST)) {
+    // heavy-first order (single-launch renders): the list is made from the previous frame's item costs
+    F.itemCost = nullptr; F.heavyList = nullptr; F.heavyFlag = nullptr; F.lptCtl = nullptr; F.lptPar = 0;
+    unsigned int* queue0 = c->queue.p;                         // claim counter of the plain queue (band 0)
+    const bool heavyFirst = nBands == 1 && !count && tilesMine > 0 && tilesMine * RT_WARPS_PER_TILE < (1 << 24) && !(c->flags & RT_FLAG_NO_HEAVY_FIRST);
+    cudaEventRecord(c->ev[4], c->stream);
+    if (heavyFirst) {
         const int items = tilesMine * RT_WARPS_PER_TILE;
         CU(c, c->itemCost.reserve((size_t)items)); CU(c, c->heavyList.reserve((size_t)items * (1u << RT_SPLIT_MAXLG)));
-        CU(c, c->heavyFlag.reserve((size_t)items)); CU(c, c->lptCtl.reserve(4));
-        CU(c, cudaMemsetAsync(c->lptCtl.p, 0, 4 * sizeof(unsigned), c->stream));
-        if (c->lptItems == items) {
-            lpt_sum_kernel<<<64, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p);
+        CU(c, c->heavyFlag.reserve((size_t)items)); CU(c, c->lptCtl.reserve(8));
+        if (c->lptItems != items) {                            // new frame geometry: no costs yet, every slot of the control block zero
+            CU(c, cudaMemsetAsync(c->lptCtl.p, 0, 8 * sizeof(unsigned), c->stream));
+            c->lptItems = items; c->lptFrame = 0;
+        } else {
             const int gridWarps = c->gridBlocks[variant] * (RT_BLOCK_THREADS / 32);
-            lpt_mark_kernel<<<(items + 255) / 256, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p, c->heavyList.p, c->heavyFlag.p,
-                                                                         gridWarps, items < 5 * gridWarps ? RT_HEAVY_FACTOR_FEW : RT_HEAVY_FACTOR);
-            c->launches += 2;
+            lpt_prepare_kernel<<<(items + 255) / 256, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p, c->heavyList.p, c->heavyFlag.p,
+                gridWarps, items < 5 * gridWarps ? RT_HEAVY_FACTOR_FEW : RT_HEAVY_FACTOR, (int)(c->lptFrame & 1u));
+            c->launches += 1;
         }
-        c->lptItems = items;
         F.itemCost = c->itemCost.p; F.heavyList = c->heavyList.p; F.heavyFlag = c->heavyFlag.p; F.lptCtl = c->lptCtl.p;
+        F.lptPar = (int)(c->lptFrame & 1u);
+        queue0 = c->lptCtl.p + 3;
+        c->lptFrame++;
+    } else {
+        CU(c, cudaMemsetAsync(c->queue.p, 0, RT_MAX_BANDS * sizeof(unsigned int), c->stream));
     }
     cudaEvent_t evFork = c->evBand[RT_MAX_BANDS], evJoin = c->evBand[RT_MAX_BANDS + 1], evCopied = c->evBand[RT_MAX_BANDS + 2];
     if (nBands > 1 || toHost) {
@@ -774,7 +781,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         const dim3 blk(RT_BLOCK_THREADS);
         float4* o4 = reinterpret_cast<float4*>(dev_rgba);
         unsigned long long* tl = c->tally.p;
-        unsigned int* q = c->queue.p + band;
+        unsigned int* q = band == 0 ? queue0 : c->queue.p + band;
         if (count) {
             if (F.useMT) render_kernel<true, true><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);
             else         render_kernel<false, true><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);

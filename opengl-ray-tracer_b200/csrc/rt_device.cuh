@@ -90,7 +90,10 @@ struct FrameParams {
     unsigned* itemCost;        // [items] SM cycles >> 4 of every warp item, written by this launch
     const unsigned* heavyList; // items whose last cost exceeded RT_HEAVY_FACTOR x mean, claimed first
     const unsigned char* heavyFlag;
-    unsigned* lptCtl;          // [0] number of heavy items, [1] claim counter of the heavy list
+    // control block of the heavy-first scheduler, 8 words: [0], [1] number of heavy items of even / odd frames, [2] claim counter
+    // of the heavy list, [3] claim counter of the plain queue, [4..5], [6..7] 64-bit sums of this launch's item costs (even / odd)
+    unsigned* lptCtl;
+    int   lptPar;              // parity of this frame: which count / sum slot it uses
     int   frameTarget;         // world > 1: colours go row-major into a full W*H frame (rank 0's, possibly peer memory)
     // signalled fused gather: the last thread block of the launch stores doneSeq into *doneWord (rank 0's memory)
     unsigned* doneWord;        // NULL = off

@@ -422,7 +422,8 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
     // The SM's warp schedulers favour the low warp slots (measured: slots 0-7 complete twice as many
     // blocks as slots 28-31, tools/timeline.py), and a slow block on a starved slot runs three times
     // longer — so only the favoured half of the slots claims from the heavy list while it lasts.
-    const int nHeavy = P.lptCtl ? (int)__ldg(P.lptCtl) : 0;
+    const int nHeavy = P.lptCtl ? (int)__ldg(P.lptCtl + P.lptPar) : 0;
+    unsigned long long costSum = 0;              // this warp's share of the frame's cost sum (one atomic per warp at the end)
     unsigned warpSlot;
     asm("mov.u32 %0, %%warpid;" : "=r"(warpSlot));
     const bool favoured = warpSlot < RT_HEAVY_SLOTS;
@@ -433,7 +434,7 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         int parts = 1, part = 0;                 // a heavy block may come as 2 or 4 row groups (see lpt_mark_kernel)
         if (heavyLeft && (favoured || !lightLeft)) {
             int hq = 0;
-            if (lane == 0) hq = (int)atomicAdd(P.lptCtl + 1, 1u);
+            if (lane == 0) hq = (int)atomicAdd(P.lptCtl + 2, 1u);
             hq = __shfl_sync(0xffffffffu, hq, 0);
             if (hq < nHeavy) {
                 const unsigned e = __ldg(P.heavyList + hq);
@@ -499,8 +500,10 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         if (P.itemCost && lane == 0) {           // parts add up (lpt_mark_kernel zeroed the entry of a split block)
             const unsigned dtc = (unsigned)((unsigned long long)(clock64() - itemClk0) >> 4);
             if (parts == 1) P.itemCost[w] = dtc; else atomicAdd(P.itemCost + w, dtc);
+            costSum += dtc;
         }
     }
+    if (P.lptCtl && lane == 0 && costSum) atomicAdd(reinterpret_cast<unsigned long long*>(P.lptCtl + 4 + 2 * P.lptPar), costSum);
     if (COUNT) {
         for (int i = 0; i < RT_NTALLY; ++i) {
             unsigned long long v = tl.v[i];
@@ -523,8 +526,11 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
 }
 
 // ---------------------------------------------------------------------------
-// Heavy-first list for the next launch from this launch's item costs.  ctl[0] = number of heavy
-// items (out), ctl[2..3] = 64-bit sum of costs (scratch).  Two tiny launches per frame.
+// Heavy-first list for this launch from the previous launch's item costs: ONE small launch per frame (round 1 used two
+// memsets and two kernels: ~10 us of a 0.3 ms frame).  The render kernel itself sums its item costs (one atomic per warp)
+// into the slot of its frame parity; this kernel reads the previous frame's sum, marks and lists the heavy items into this
+// parity's count, and resets what the coming render launch and the next prepare launch need: the two claim counters, this
+// parity's sum, the other parity's count.
 // ---------------------------------------------------------------------------
 // A block is HEAVY when its cost exceeds heavyFactor x the mean.  Measured on the car frame at 4K over 1 / 2 / 4 / 8 ranks
 // (profiles/r2/heavy_first_sweep.txt): 4 x is as good as 3 x on a whole frame and 6 - 8 % faster on a half or a quarter
@@ -535,12 +541,6 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
 #ifndef RT_HEAVY_FACTOR_FEW
 #define RT_HEAVY_FACTOR_FEW 3
 #endif
-__global__ void lpt_sum_kernel(const unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl) {
-    unsigned long long s = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) s += cost[i];
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if ((threadIdx.x & 31) == 0 && s) atomicAdd(reinterpret_cast<unsigned long long*>(ctl + 2), s);
-}
 // A block whose cost is a large share of what ONE warp would ideally do in the whole frame (sum / warps of the
 // grid) bounds the frame however early it starts — the case of small frames and of many GPUs sharing a frame.
 // Such a block is listed as 2^k lane groups (8x2, 8x1, 4x1 ... pixels each, other lanes idle) that different
@@ -551,11 +551,12 @@ __global__ void lpt_sum_kernel(const unsigned* __restrict__ cost, int n, unsigne
 #ifndef RT_SPLIT_K
 #define RT_SPLIT_K 2           // parts ~ K * cost / share, rounded down to a power of two (two parts from cost > share on)
 #endif
-__global__ void lpt_mark_kernel(unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl,
-                                unsigned* __restrict__ heavyList, unsigned char* __restrict__ heavyFlag, int gridWarps, int heavyFactor) {
+__global__ void lpt_prepare_kernel(unsigned* __restrict__ cost, int n, unsigned* __restrict__ ctl,
+                                   unsigned* __restrict__ heavyList, unsigned char* __restrict__ heavyFlag, int gridWarps, int heavyFactor, int par) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { ctl[2] = 0u; ctl[3] = 0u; ctl[4 + 2 * par] = 0u; ctl[5 + 2 * par] = 0u; ctl[par ^ 1] = 0u; }
     if (i >= n) return;
-    const unsigned long long sum = *reinterpret_cast<const unsigned long long*>(ctl + 2);
+    const unsigned long long sum = *reinterpret_cast<const unsigned long long*>(ctl + 4 + 2 * (par ^ 1));
     const unsigned long long ci = cost[i];
     const bool heavy = ci * (unsigned long long)n > (unsigned long long)heavyFactor * sum;
     heavyFlag[i] = heavy ? 1 : 0;
@@ -564,7 +565,7 @@ __global__ void lpt_mark_kernel(unsigned* __restrict__ cost, int n, unsigned* __
     unsigned lg = 0;
     while (lg < RT_SPLIT_MAXLG && (2ull << lg) <= want) ++lg;
     const unsigned parts = 1u << lg;
-    const unsigned at = atomicAdd(ctl, parts);
+    const unsigned at = atomicAdd(ctl + par, parts);
     for (unsigned p = 0; p < parts; ++p) heavyList[at + p] = (unsigned)i | (p << 24) | (lg << 29);
     if (parts > 1) cost[i] = 0;                  // the parts add their costs up
 }
