@@ -76,8 +76,10 @@ enum {
     RT_FLAG_HIT_IDS   = 1u << 1
 };
 
-/* Tile geometry used when a frame is sharded over several GPUs: tile k
- * (row-major over the tile grid) belongs to rank k % world. */
+/* Tile geometry used when a frame is sharded over several GPUs: tile k belongs to rank k % world.  Tile k sits in tile
+ * row k / tilesX; its column is k % tilesX for one GPU and (k % tilesX + row) % tilesX when sharded (every row rotated by its
+ * number, so that a rank's tiles form diagonals rather than vertical stripes).  A rank's compact shard holds its tiles in
+ * increasing k, 32x8 pixels each, row-major inside the tile; rt_untile restores the frame. */
 #define RT_TILE_W 32
 #define RT_TILE_H 8
 

@@ -454,8 +454,13 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         const int tile = P.shardRank + t * P.shardWorld;
         const int lx = ((b & 3) << 3) + (lane & 7);
         const int ly = ((b >> 2) << 2) + (lane >> 3);
-        const int x = (tile % P.tilesX) * RT_TILE_W + lx;
-        const int y = (tile / P.tilesX) * RT_TILE_H + ly;
+        // tile index -> place in the tile grid.  One GPU: row-major.  Sharded: every tile row is rotated by its row number, so
+        // that a rank's tiles (k = rank mod world) form DIAGONALS instead of the vertical stripes they would form whenever the
+        // row length is a multiple of world (4K: 120 tiles per row) — the content of a frame varies across columns
+        const int trow = tile / P.tilesX, tc0 = tile - trow * P.tilesX;
+        const int tcol = P.shardWorld == 1 ? tc0 : (tc0 + trow) % P.tilesX;
+        const int x = tcol * RT_TILE_W + lx;
+        const int y = trow * RT_TILE_H + ly;
         const bool partOK = ((lane * parts) >> 5) == part;             // the lanes (rows / row pieces of the 8x4 block) this warp renders
         const bool inside = x < P.W && y < P.H && partOK;
         float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -611,7 +616,9 @@ __global__ void untile_kernel(const float4* __restrict__ shards, float4* __restr
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (long long)W * H) return;
     const int x = (int)(i % W), y = (int)(i / W);
-    const int tile = (y / RT_TILE_H) * tilesX + (x / RT_TILE_W);
+    const int trow = y / RT_TILE_H, tcol = x / RT_TILE_W;
+    const int tc0 = world == 1 ? tcol : (tcol + tilesX - trow % tilesX) % tilesX;     // inverse of the render kernel's row rotation
+    const int tile = trow * tilesX + tc0;
     const int rank = tile % world, t = tile / world;
     const long long src = (long long)rank * shardPixels + (long long)t * (RT_TILE_W * RT_TILE_H) +
                           (y % RT_TILE_H) * RT_TILE_W + (x % RT_TILE_W);

@@ -181,7 +181,7 @@ def test_sharded_scheduled_frames(rt):
     tx = (W + 31) // 32
     for k in range(0, px // 256, 7):
         tile = k * world
-        x0, y0 = (tile % tx) * 32, (tile // tx) * 8
+        x0, y0 = rt.shard.tile_origin(W, H, tile, world)
         if y0 + 8 > H or x0 + 32 > W:
             continue
         assert np.array_equal(ids0[k * 256:(k + 1) * 256].reshape(8, 32), full_ids[y0:y0 + 8, x0:x0 + 32]), "tile %d" % tile

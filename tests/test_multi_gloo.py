@@ -70,7 +70,7 @@ def test_partition_covers_every_pixel_once(rt=None):
             total += len(tiles)
             assert len(tiles) * sh.TILE_PX <= sh.shard_pixels(W, H, world) or world == 1
             for t in tiles:
-                ys, xs = sh.tile_pixels(W, H, t)
+                ys, xs = sh.tile_pixels(W, H, t, world)
                 ok = (ys < H) & (xs < W)
                 seen[ys[ok], xs[ok]] += 1
         assert (seen == 1).all() and total == 4 * 8
