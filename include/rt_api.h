@@ -179,13 +179,13 @@ int rt_frame_open(rt_ctx* ctx, const unsigned char handle[64]);
 int rt_frame_download(rt_ctx* ctx, float* host_rgba);
 
 /* ---- signalled fused gather: compute + signal, no collective ------------------------------------------------
- * The exported frame is DOUBLE-BUFFERED (frame f goes to buffer f & 1) and carries one completion word per rank; every
+ * The exported frame is DOUBLE-BUFFERED (frame f goes to buffer f & 1) and carries one completion counter per buffer; every
  * other rank owns one release word.  In signalled mode
  *   - a rank's render kernel stores its tiles into rank 0's buffer over NVLink and its LAST thread block, after a
- *     system-scope fence, stores the frame number into this rank's completion word on rank 0;
- *   - rank 0's rt_frame_acquire makes its stream wait (stream memory operation on local words, no kernel spins) until
- *     every rank's completion word has reached the frame number, and returns the buffer: work enqueued afterwards sees
- *     the whole frame;
+ *     system-scope fence, adds 1 to that buffer's completion counter on rank 0 (a peer atomic);
+ *   - rank 0's rt_frame_acquire makes its stream wait (ONE stream memory operation on a local word, no kernel spins) until
+ *     the counter has reached (number of frames of this buffer) * (world - 1), and returns the buffer: work enqueued afterwards
+ *     sees the whole frame;
  *   - rank 0's rt_frame_release stores the frame number into every other rank's release word; a rank's render of frame
  *     f + 2 (same buffer) waits in ITS stream for the release of frame f.  Ranks therefore run at most one frame ahead of
  *     the consumer and never overwrite a frame that is being read: no barrier, no NCCL call per frame.

@@ -709,8 +709,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
             // buffer seq & 1 held frame seq - 2: wait (in the stream, no kernel spins) until rank 0 has released it
             if (seq > 2 && c->waitValue32(c->stream, (unsigned long long)(uintptr_t)c->releaseLocal.p, seq - 2, 0u /* GEQ */) != 0)
                 return fail(c, RT_ERR_CUDA, "cuStreamWaitValue32 (release word)");
-            CU(c, cudaMemsetAsync(c->ctaDone.p, 0, sizeof(unsigned), c->stream));
-            F.doneWord = reinterpret_cast<unsigned*>(c->frameTarget + 2 * frameFloats) + c->shardRank;
+            F.doneWord = reinterpret_cast<unsigned*>(c->frameTarget + 2 * frameFloats) + (seq & 1u);   // this buffer's completion counter
             F.ctaDone = c->ctaDone.p; F.doneSeq = seq;
         }
     }
@@ -886,10 +885,13 @@ int rt_frame_acquire(rt_ctx* c, float** dev_frame) {
     if (!c) return RT_ERR_ARG;
     if (!c->syncOn || c->shardRank != 0 || !c->frame.p) return fail(c, RT_ERR_STATE, "rt_frame_acquire: rank 0 in signalled mode only");
     CU(c, cudaSetDevice(c->device));
-    unsigned* words = reinterpret_cast<unsigned*>(c->frame.p + 2 * (size_t)c->W * (size_t)c->H);
-    for (int r = 1; r < c->shardWorld; ++r)
-        if (c->waitValue32(c->stream, (unsigned long long)(uintptr_t)(words + r), c->frameSeq, 0u /* GEQ */) != 0)
-            return fail(c, RT_ERR_CUDA, "cuStreamWaitValue32 (completion word)");
+    // One counter per buffer; every other rank's last thread block adds 1 per frame.  Frame f is the ceil(f / 2)-th frame of
+    // its buffer: complete at ceil(f / 2) * (world - 1) (compared modulo 2^32).  Per buffer, because a rank may already have
+    // finished frame f + 1 (the other buffer) when another has not finished f; nobody starts f + 2 before f was released.
+    unsigned* counter = reinterpret_cast<unsigned*>(c->frame.p + 2 * (size_t)c->W * (size_t)c->H) + (c->frameSeq & 1u);
+    const unsigned expect = ((c->frameSeq + 1u) / 2u) * (unsigned)(c->shardWorld - 1);
+    if (c->shardWorld > 1 && c->waitValue32(c->stream, (unsigned long long)(uintptr_t)counter, expect, 0u /* GEQ */) != 0)
+        return fail(c, RT_ERR_CUDA, "cuStreamWaitValue32 (completion counter)");
     if (dev_frame) *dev_frame = reinterpret_cast<float*>(c->frame.p) + (c->frameSeq & 1u) * 4 * (size_t)c->W * (size_t)c->H;
     return RT_OK;
 }
@@ -975,6 +977,7 @@ int rt_sync_enable(rt_ctx* c, int world) {
         if (!c->releaseLocal.p) return fail(c, RT_ERR_STATE, "rt_sync_enable: rt_sync_local / rt_sync_export first");
         CU(c, cudaMemset(c->releaseLocal.p, 0, sizeof(unsigned)));
         CU(c, c->ctaDone.reserve(1));
+        CU(c, cudaMemset(c->ctaDone.p, 0, sizeof(unsigned)));
     }
     c->frameSeq = 0; c->syncOn = true;
     return RT_OK;

@@ -95,9 +95,9 @@ struct FrameParams {
     unsigned* lptCtl;
     int   lptPar;              // parity of this frame: which count / sum slot it uses
     int   frameTarget;         // world > 1: colours go row-major into a full W*H frame (rank 0's, possibly peer memory)
-    // signalled fused gather: the last thread block of the launch stores doneSeq into *doneWord (rank 0's memory)
+    // signalled fused gather: the last thread block of the launch adds 1 to *doneWord (the completion counter in rank 0's memory)
     unsigned* doneWord;        // NULL = off
-    unsigned* ctaDone;         // local counter of finished thread blocks (zeroed before the launch)
+    unsigned* ctaDone;         // local counter of finished thread blocks (the last block resets it)
     unsigned  doneSeq;
 };
 

@@ -517,14 +517,15 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         }
     }    if (P.doneWord) {
         // compute + signal: every thread makes its pixel stores (peer memory over NVLink) visible system-wide, the last
-        // thread block of the launch then publishes the frame number in this rank's completion word on rank 0
+        // thread block of the launch then adds 1 to the completion counter on rank 0 (a peer atomic over NVLink)
         __threadfence_system();
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence();
             if (atomicAdd(P.ctaDone, 1u) == gridDim.x - 1) {
+                *P.ctaDone = 0u;                            // ready for the next launch (stream order): no memset per frame
                 __threadfence_system();
-                *reinterpret_cast<volatile unsigned*>(P.doneWord) = P.doneSeq;
+                atomicAdd_system(P.doneWord, 1u);           // ONE completion counter on rank 0: every other rank adds 1 per frame
             }
         }
     }
