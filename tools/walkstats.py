@@ -7,7 +7,8 @@ rt = rtload.load()
 name = sys.argv[1] if len(sys.argv) > 1 else "car"
 W = int(sys.argv[2]) if len(sys.argv) > 2 else 3840
 H = int(sys.argv[3]) if len(sys.argv) > 3 else 2160
-sc = rt.Scene(name, W, H)
+n = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+sc = rt.Scene(name, W, H, n_override=n)
 tr = rt.RayTracer(W, H, flags=0)
 tr.upload(sc)
 for b in (1, 3):
