@@ -455,7 +455,7 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
     import ctypes as C
     out = {}
     L, Hl = rt.lib(), rt.hostlib()
-    for mode, label in ((0, "refit"), (1, "rebuild"), (2, "device_animation"), (3, "device_rebuild")):
+    for mode, label in ((0, "refit"), (1, "rebuild"), (2, "device_animation"), (3, "device_rebuild"), (4, "device_rebuild_k9")):
         sc = rt.Scene("monkey", W, H)
         params = rt.make_params(W, H)
         tr = rt.RayTracer(W, H, device=torch.cuda.current_device(), flags=0)
@@ -478,6 +478,12 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
                 tr.wait_frames(1)
                 tr.animate(i / 60.0, 1.0 / 60.0)
                 tr.build_bvh(15, fetch=False)
+                tr.render_async(params, bufs[i & 1])
+                return
+            if mode == 4:                         # K6 only, K8 + K9: tree AND layout on the device, nothing comes back but 296 bytes
+                tr.wait_frames(1)
+                tr.animate_shapes(i / 60.0, 1.0 / 60.0)
+                tr.build_bvh(15, rt.RT_BUILD_DEVICE_LAYOUT, fetch=False)
                 tr.render_async(params, bufs[i & 1])
                 return
             sc.animate(i / 60.0, 1.0 / 60.0, mode)
@@ -507,7 +513,8 @@ def time_animated(torch, rt, stream, frames=300, W=800, H=600):
         tr.close()
     out["workload"] = "BASELINE.json configs[4]: monkey-1240 %dx%d, %d frames, CPU animation + BVH %s, pinned async upload, D2H of every frame" % (
         W, H, frames, "refit | rebuild; device_animation = rt_animate (shapes and node boxes move on the device, no upload); "
-                      "device_rebuild = rt_animate + rt_build_bvh (K8: the reference tree rebuilt on the device every frame)")
+                      "device_rebuild = rt_animate + rt_build_bvh (K8: the reference tree rebuilt on the device every frame); "
+                      "device_rebuild_k9 = rt_animate_shapes + rt_build_bvh(RT_BUILD_DEVICE_LAYOUT) (K8 + K9: tree and layout on the device)")
     return out
 
 

@@ -223,6 +223,9 @@ int rt_anim_clear(rt_ctx* ctx);
 int rt_anim_bounce(rt_ctx* ctx, int shape, float origin_y, float amplitude, float frequency);
 int rt_anim_rotate_z(rt_ctx* ctx, const int32_t* shapes, int count, const float center[3], float speed);
 int rt_animate(rt_ctx* ctx, float t, float dt);
+/* K6 only: moves the registered shapes and leaves the node boxes alone — for a caller that rebuilds the tree afterwards
+ * (rt_build_bvh) instead of growing it: per-frame rebuild loops need neither K7 nor its tables of the tree. */
+int rt_animate_shapes(rt_ctx* ctx, float t, float dt);
 int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
 
 /* ---- device-side BVH build (K8; opt-in, the host-built tree stays the default) ----
@@ -241,9 +244,11 @@ enum { RT_BUILD_DEFAULT = 0u,
        RT_BUILD_NO_SINGLE_BLOCK = 1u << 1,      /* scenes of <= 2048 shapes also take the one-launch-per-phase path (diagnostic) */
        /* K9: lay the built tree out ON THE DEVICE (threaded list A, primitive slots, ranks straight from the builder's
         * tables): no host layout build and no copy of the tree to the host (rt_get_bvh fetches it on demand).  Applies
-        * when the tree has no leaf of more than 8 shapes (nothing to expand into a sub-tree) or the context walks the
-        * reference's own sequence (RT_FLAG_REFERENCE_WALK); otherwise the call behaves as without the flag.  The own
-        * tree over the reference leaves (list B) is not built for a device-laid-out tree. */
+        * when the tree has no leaf of more than 16 shapes (such leaves are walked as they are; the host layout would expand
+        * leaves of more than 8 shapes into sub-trees, which pays off for the hundreds of shapes the reference builder can
+        * leave in a leaf) or the context walks the reference's own sequence (RT_FLAG_REFERENCE_WALK); otherwise the call
+        * behaves as without the flag.  The own tree over the reference leaves (list B) is not built for a
+        * device-laid-out tree. */
        RT_BUILD_DEVICE_LAYOUT = 1u << 2 };
 int rt_build_bvh(rt_ctx* ctx, int maxDepth, unsigned build_flags, int* nNodes_out, int* nIndices_out);
 int rt_get_bvh(rt_ctx* ctx, void* nodes_or_NULL, int nodeCapacity, int32_t* indices_or_NULL, int indexCapacity);

@@ -57,7 +57,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_sync_local", "rt_sync_export", "rt_sync_peer", "rt_sync_enable", "rt_frame_acquire", "rt_frame_release", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_sync_local", "rt_sync_export", "rt_sync_peer", "rt_sync_enable", "rt_frame_acquire", "rt_frame_release", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_animate_shapes", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -120,6 +120,7 @@ def _declare(L):
     L.rt_anim_bounce.argtypes = [vp, ip, C.c_float, C.c_float, C.c_float]; L.rt_anim_bounce.restype = ip
     L.rt_anim_rotate_z.argtypes = [vp, vp, ip, vp, C.c_float]; L.rt_anim_rotate_z.restype = ip
     L.rt_animate.argtypes = [vp, C.c_float, C.c_float]; L.rt_animate.restype = ip
+    L.rt_animate_shapes.argtypes = [vp, C.c_float, C.c_float]; L.rt_animate_shapes.restype = ip
     L.rt_download_scene.argtypes = [vp, vp, vp]; L.rt_download_scene.restype = ip
     L.rt_build_bvh.argtypes = [vp, ip, C.c_uint, C.POINTER(C.c_int), C.POINTER(C.c_int)]; L.rt_build_bvh.restype = ip
     L.rt_get_bvh.argtypes = [vp, vp, ip, vp, ip]; L.rt_get_bvh.restype = ip
@@ -404,6 +405,10 @@ class RayTracer:
 
     def animate(self, t, dt):
         self._chk(self._L.rt_animate(self._c, t, dt))
+
+    def animate_shapes(self, t, dt):
+        """K6 only (no K7): for loops that rebuild the tree afterwards."""
+        self._chk(self._L.rt_animate_shapes(self._c, t, dt))
 
     def download_scene(self, n_shapes, n_nodes):
         shapes = np.zeros(n_shapes, dtype=SHAPE_DTYPE); nodes = np.zeros(n_nodes, dtype=NODE_DTYPE)

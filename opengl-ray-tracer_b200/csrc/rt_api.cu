@@ -58,6 +58,9 @@ struct PinBuf {                       // capacity-based pinned host array (keeps
 }  // namespace
 
 #define RT_MAX_BANDS 8
+#ifndef RT_DEVICE_LAYOUT_MAX_LEAF
+#define RT_DEVICE_LAYOUT_MAX_LEAF 16
+#endif
 
 struct rt_ctx {
     int device = 0, W = 0, H = 0;
@@ -111,7 +114,8 @@ struct rt_ctx {
     bool shapesOnDevice = false;      // the pending host range [shapeLo, shapeHi) has already been copied (rt_build_bvh)
     float lastBuildMs = 0.f;
     cudaEvent_t evBuild[2] = {nullptr, nullptr};
-    bool animDirty = true;            // registrations changed: item list / flags / tree maps must go up again
+    bool animDirty = true;            // registrations or topology changed: item list / flags / tree maps must go up again
+    bool animItemsDirty = true;       // registrations changed: the item list alone (rt_animate_shapes needs no tree maps)
     bool devShapesDirty = false, devNodesDirty = false;   // the device copies were changed by K6 / K7: repack without an upload
     bool hostStale = false;           // the host shadows no longer describe the device scene (shapes and / or node boxes)
     bool hostShapesStale = false, hostNodesStale = false;
@@ -1007,7 +1011,7 @@ int rt_host_frame_unregister(rt_ctx* c, void* host_frame) {
 
 int rt_anim_clear(rt_ctx* c) {
     if (!c) return RT_ERR_ARG;
-    c->animDefs.clear(); c->animItems.clear(); c->animDirty = true;
+    c->animDefs.clear(); c->animItems.clear(); c->animDirty = true; c->animItemsDirty = true;
     return RT_OK;
 }
 
@@ -1017,7 +1021,7 @@ int rt_anim_bounce(rt_ctx* c, int shape, float origin_y, float amplitude, float 
     if (c->hShapes.p[shape].type != RT_SHAPE_SPHERE) return fail(c, RT_ERR_ARG, "rt_anim_bounce wants a sphere");
     c->animItems.push_back(AnimItem{shape, (int)c->animDefs.size()});
     c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_BOUNCE, origin_y, amplitude, frequency, 0.f, 0.f, 0.f, 0.f});
-    c->animDirty = true;
+    c->animDirty = true; c->animItemsDirty = true;
     return RT_OK;
 }
 
@@ -1029,7 +1033,7 @@ int rt_anim_rotate_z(rt_ctx* c, const int32_t* shapes, int count, const float ce
     }
     for (int i = 0; i < count; ++i) c->animItems.push_back(AnimItem{shapes[i], (int)c->animDefs.size()});
     c->animDefs.push_back(rt_ctx::AnimDef{RT_ANIM_ROTATE_Z, 0.f, 0.f, 0.f, center[0], center[1], center[2], speed});
-    c->animDirty = true;
+    c->animDirty = true; c->animItemsDirty = true;
     return RT_OK;
 }
 
@@ -1069,12 +1073,25 @@ int upload_anim_tables(rt_ctx* c) {
     if (!c->indices.empty()) CU(c, cudaMemcpyAsync(c->dIndices.p, c->indices.data(), c->indices.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     if (!c->animItems.empty()) CU(c, cudaMemcpyAsync(c->dAnimItems.p, c->animItems.data(), c->animItems.size() * sizeof(AnimItem), cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
-    c->animDirty = false;
+    c->animDirty = false; c->animItemsDirty = false;
+    return RT_OK;
+}
+// The item list alone (K6 without K7): what rt_animate_shapes needs.
+int upload_anim_items(rt_ctx* c) {
+    CU(c, c->dAnimItems.reserve(c->animItems.size())); CU(c, c->dAnimEntries.reserve(c->animDefs.size()));
+    CU(c, c->hAnimEntries.reserve(c->animDefs.size(), 0));
+    if (!c->animItems.empty()) CU(c, cudaMemcpyAsync(c->dAnimItems.p, c->animItems.data(), c->animItems.size() * sizeof(AnimItem), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->animItemsDirty = false;
     return RT_OK;
 }
 }  // namespace
 
-int rt_animate(rt_ctx* c, float t, float dt) {
+static int animate_impl(rt_ctx* c, float t, float dt, bool grow);
+int rt_animate(rt_ctx* c, float t, float dt) { return animate_impl(c, t, dt, true); }
+int rt_animate_shapes(rt_ctx* c, float t, float dt) { return animate_impl(c, t, dt, false); }
+
+static int animate_impl(rt_ctx* c, float t, float dt, bool grow) {
     if (!c) return RT_ERR_ARG;
     if (!c->haveScene) return fail(c, RT_ERR_STATE, "rt_animate before a scene upload");
     CU(c, cudaSetDevice(c->device));
@@ -1082,7 +1099,8 @@ int rt_animate(rt_ctx* c, float t, float dt) {
     if (rc != RT_OK) return rc;
     if (c->animDefs.empty() || c->animItems.empty()) return RT_OK;
     for (const AnimItem& it : c->animItems) if (it.shape >= c->nShapes) return fail(c, RT_ERR_STATE, "animation registered for a shape that is gone");
-    if (c->animDirty) { rc = upload_anim_tables(c); if (rc != RT_OK) return rc; }
+    if (grow) { if (c->animDirty) { rc = upload_anim_tables(c); if (rc != RT_OK) return rc; } }
+    else if (c->animItemsDirty) { rc = upload_anim_items(c); if (rc != RT_OK) return rc; }
     wait_copies(c);                                // the pinned entry table is the source of an async copy
     for (size_t e = 0; e < c->animDefs.size(); ++e) {
         const rt_ctx::AnimDef& d = c->animDefs[e];
@@ -1102,7 +1120,7 @@ int rt_animate(rt_ctx* c, float t, float dt) {
     const int nI = (int)c->animItems.size();
     anim_kernel<<<(nI + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, c->dAnimEntries.p);
     c->launches++;
-    if (c->nNodes > 0 && c->nLeavesRaw > 0) {
+    if (grow && c->nNodes > 0 && c->nLeavesRaw > 0) {
         CU(c, cudaMemsetAsync(c->dGrowArrived.p, 0, (size_t)c->nNodes * sizeof(unsigned), c->stream));
         grow_kernel<<<(c->nLeavesRaw + 127) / 128, 128, 0, c->stream>>>(c->dNodes.p, c->dShapes.p, c->dIndices.p, c->dAnimFlag.p,
             c->dNodeAux.p + c->nNodes, c->nLeavesRaw, c->dNodeAux.p, c->dGrowArrived.p);
@@ -1226,7 +1244,9 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
             if (ctl.nNodes < 1 || (size_t)ctl.nNodes >= maxNodes) return fail(c, RT_ERR_CUDA, "rt_build_bvh: node count out of range");
             cudaEventElapsedTime(&c->lastBuildMs, c->evBuild[0], c->evBuild[1]);
             const bool plain = (c->flags & RT_FLAG_REFERENCE_WALK) != 0 || ctl.notFinite != 0;   // the host builds no sub-trees then either
-            if (plain || ctl.maxLeaf <= RT_FAT_LEAF) {
+            // a leaf of up to RT_DEVICE_LAYOUT_MAX_LEAF shapes is walked as it is (the host layout would expand leaves of more
+            // than RT_FAT_LEAF = 8 shapes into a sub-tree; testing up to 16 shapes in a row costs less than a trip to the host)
+            if (plain || ctl.maxLeaf <= RT_DEVICE_LAYOUT_MAX_LEAF) {
                 const int nN = ctl.nNodes;
                 wait_copies(c);
                 std::swap(c->dOrder, c->kOrder); std::swap(c->dLinkCnt, c->kLinkCnt);

@@ -350,6 +350,35 @@ __device__ __forceinline__ bld::u64 bld_warp_best(bld::u64 v, bool isMin) {
     return ((bld::u64)bestHi << 32) | bestLo;
 }
 
+// The same for one warp (all 32 lanes call it): when its shapes all go to one pair of siblings the warp reduces each key
+// first (REDUX) and issues one atomic per key and side; a mixed warp issues one atomic per shape and key.
+__device__ __forceinline__ void bld_fold_warp(bld::u64* keyBase, int node, const bld::u64 k[6]) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int pair = node < 0 ? -1 : (node + 1) >> 1;
+    const unsigned have = __ballot_sync(full, node >= 0);
+    if (have == 0u) return;
+    const int wpair = __shfl_sync(full, pair, __ffs(have) - 1);
+    const bool warpUniform = __all_sync(full, node < 0 || pair == wpair);
+    if (!warpUniform) { if (node >= 0) bld::fold_keys(keyBase + 6 * (size_t)node, k); return; }
+    const int wleft = wpair == 0 ? 0 : 2 * wpair - 1;
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+        const bool mine = node == wleft + side;
+        if (__ballot_sync(full, mine) == 0u) continue;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            const bool isMin = a < 3;
+            const bld::u64 id = isMin ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
+            const bld::u64 best = bld_warp_best(mine ? k[a] : id, isMin);
+            if (lane == 0 && best != id) {
+                if (isMin) bld::amin64(keyBase + 6 * (size_t)(wleft + side) + a, best);
+                else bld::amax64(keyBase + 6 * (size_t)(wleft + side) + a, best);
+            }
+        }
+    }
+}
+
 // Fold the keys k of this thread's shape into node `node` (node < 0: nothing to fold).  Called by every thread of
 // the block.  While the segments are long, all the shapes of a warp — of the whole block — go to the same pair of
 // siblings: then the warp reduces each key first (REDUX), the block combines its warps in shared memory, and one
@@ -393,28 +422,7 @@ __device__ __forceinline__ void bld_fold_block(bld::u64* keyBase, int node, cons
         }
         return;
     }
-    // per warp
-    const unsigned have = __ballot_sync(full, node >= 0);
-    if (have == 0u) return;
-    const int wpair = __shfl_sync(full, pair, __ffs(have) - 1);
-    const bool warpUniform = __all_sync(full, node < 0 || pair == wpair);
-    if (!warpUniform) { if (node >= 0) bld::fold_keys(keyBase + 6 * (size_t)node, k); return; }
-    const int wleft = wpair == 0 ? 0 : 2 * wpair - 1;
-#pragma unroll
-    for (int side = 0; side < 2; ++side) {
-        const bool mine = node == wleft + side;
-        if (__ballot_sync(full, mine) == 0u) continue;
-#pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            const bool isMin = a < 3;
-            const bld::u64 id = isMin ? RT_BLD_KEY_MIN_ID : RT_BLD_KEY_MAX_ID;
-            const bld::u64 best = bld_warp_best(mine ? k[a] : id, isMin);
-            if (lane == 0 && best != id) {
-                if (isMin) bld::amin64(keyBase + 6 * (size_t)(wleft + side) + a, best);
-                else bld::amax64(keyBase + 6 * (size_t)(wleft + side) + a, best);
-            }
-        }
-    }
+    bld_fold_warp(keyBase, node, k);
 }
 
 __global__ void bld_init_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int agg) {
@@ -561,17 +569,19 @@ bld_small_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, i
         for (int p = lo; p < hi; ++p) { B.scanL[p] = run; run += (int)B.flag[p]; }
         if (t == T - 1) B.scanL[n] = warpSum[31];
         __syncthreads();
-        for (int p = t; p < n; p += T) {
-            int newPos, newNode; bool moved;
-            bld::split_position(p, (int)B.flag[p], level, B.pnode[cur], B.scanL, B.N, B.ctl, newPos, newNode, moved);
-            const int shape = B.ord[cur][p];
-            B.ord[nxt][newPos] = shape;
-            B.pnode[nxt][newPos] = newNode;
-            if (moved) {
-                bld::u64 k[6];
-                bld::record_keys(B.R.mn[shape], B.R.mx[shape], (unsigned)newPos, k);
-                bld::fold_keys(B.N.key + 6 * (size_t)newNode, k);
+        for (int base = 0; base < n; base += T) {                      // whole warps stay together: the fold is warp-aggregated
+            const int p = base + t;
+            bld::u64 k[6];
+            int node = -1;
+            if (p < n) {
+                int newPos, newNode; bool moved;
+                bld::split_position(p, (int)B.flag[p], level, B.pnode[cur], B.scanL, B.N, B.ctl, newPos, newNode, moved);
+                const int shape = B.ord[cur][p];
+                B.ord[nxt][newPos] = shape;
+                B.pnode[nxt][newPos] = newNode;
+                if (moved) { bld::record_keys(B.R.mn[shape], B.R.mx[shape], (unsigned)newPos, k); node = newNode; }
             }
+            bld_fold_warp(B.N.key, node, k);        // (the per-shape atomics of round 1 were 7 k same-address atomics per level at the top)
         }
         if (t == 0) B.ctl->parity = nxt;
         __syncthreads();

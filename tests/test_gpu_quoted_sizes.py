@@ -95,7 +95,7 @@ def test_soup_1m_8k_row_sample_and_shards(rt, oracle):
     tr.close()
 
 
-@pytest.mark.parametrize("mode,label", [(0, "refit"), (1, "rebuild"), (2, "device_animation"), (3, "device_rebuild")])
+@pytest.mark.parametrize("mode,label", [(0, "refit"), (1, "rebuild"), (2, "device_animation"), (3, "device_rebuild"), (4, "device_rebuild_k9")])
 def test_animated_monkey_300_frames(rt, oracle, mode, label):
     """BASELINE configs[4] exactly as bench.time_animated drives it (pipelined rt_render_async, two host buffers), every
     25th frame compared with the oracle on the host-side scene state of that frame (the reference's own frame step:
@@ -118,11 +118,13 @@ def test_animated_monkey_300_frames(rt, oracle, mode, label):
     worst = 1.0
     for i in range(frames):
         t, dt = i / 60.0, 1.0 / 60.0
-        sc.animate(t, dt, 1 if mode in (1, 3) else 0)      # the host's state of this frame = the oracle's input
+        sc.animate(t, dt, 1 if mode in (1, 3, 4) else 0)   # the host's state of this frame = the oracle's input
         if mode == 2:
             tr.wait_frames(1); tr.animate(t, dt)
         elif mode == 3:
             tr.wait_frames(1); tr.animate(t, dt); tr.build_bvh(15, fetch=False)
+        elif mode == 4:
+            tr.wait_frames(1); tr.animate_shapes(t, dt); tr.build_bvh(15, rt.RT_BUILD_DEVICE_LAYOUT, fetch=False)
         else:
             shp = Hl.rh_shapes(sc._h, C.byref(n)); ns = n.value
             nod = Hl.rh_nodes(sc._h, C.byref(n)); nn = n.value
