@@ -1,5 +1,6 @@
 #!/bin/bash
-# final evidence of the round: ncu captures of HEAD, GPU suite, bench N=1
+# evidence of a round on one B200 (run under gpurun): ncu --set full captures of the render kernel at 4K, 800x600 and as rank 0 of 8
+# (read here with tools/ncu_summary.py, tools/ncu_traffic.py, tools/sass_lines.py), the launch list, the GPU test suite
 mkdir -p gpurun_out
 for cfg in "4k:--width 3840 --height 2160" "800:--width 800 --height 600" "4k_r0of8:--width 3840 --height 2160 --world 8 --rank 0"; do
   name=${cfg%%:*}; args=${cfg#*:}
