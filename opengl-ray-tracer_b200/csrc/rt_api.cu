@@ -57,7 +57,12 @@ struct PinBuf {                       // capacity-based pinned host array (keeps
 
 }  // namespace
 
+#ifndef RT_MAX_BANDS
 #define RT_MAX_BANDS 8
+#endif
+#ifndef RT_BAND_ROWS
+#define RT_BAND_ROWS 16         // at least this many tile rows per band
+#endif
 #ifndef RT_DEVICE_LAYOUT_MAX_LEAF
 #define RT_DEVICE_LAYOUT_MAX_LEAF 16
 #endif
@@ -723,11 +728,14 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     // bands: whole tile rows (world == 1: a band is a contiguous block of image rows)
     const int rowTiles = c->shardWorld == 1 ? F.tilesX : 1;
     int nBands = 1;
-    // a small pipelined frame is one launch (heavy-first order and split blocks need the whole frame; its copy
-    // overlaps the NEXT frame's render instead of this one's)
-    if (toHost && !count && !(pipeline && px <= (int64_t)1 << 21)) {
+    // a frame of up to 2 M pixels is ONE launch (heavy-first order and split blocks need the whole frame, and a small frame's
+    // copy is short: car 800x600 end to end 0.93 -> 0.63 ms); pipelined, its copy overlaps the NEXT frame's render
+#ifndef RT_BAND_MIN_PIXELS
+#define RT_BAND_MIN_PIXELS ((int64_t)1 << 21)
+#endif
+    if (toHost && !count && px > RT_BAND_MIN_PIXELS) {
         const int rows = (tilesMine + rowTiles - 1) / rowTiles;
-        nBands = rows / 16;                              // at least 16 tile rows (128 pixel rows) per band
+        nBands = rows / RT_BAND_ROWS;                    // at least RT_BAND_ROWS tile rows per band
         if (nBands > RT_MAX_BANDS) nBands = RT_MAX_BANDS;
         if (nBands < 1) nBands = 1;
     }
