@@ -257,6 +257,31 @@ int rt_get_bvh(rt_ctx* ctx, void* nodes_or_NULL, int nodeCapacity, int32_t* indi
 int rt_layout_info(rt_ctx* ctx, int out[4]);
 float rt_last_build_ms(const rt_ctx* ctx);
 
+/* ---- K8 without any allocation ----
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The single-block form of the K8 build
+ * (the same tree: FlatNode[] / bvhIndices[] byte-identical to rt_build_bvh's and to buildBVH + serializeBVH,
+ * src/main.cpp:955-979, :1111-1193) with its working tables in a file-scope __device__ array of the library instead of
+ * buffers of a context: the call needs no rt_ctx and calls no cudaMalloc / cudaFree / allocating routine.  It only
+ * launches one kernel on `cuda_stream` (NULL = the default stream) of the CURRENT device and returns without
+ * synchronising; the first call on a device also resolves the array's device address (cudaGetSymbolAddress) — make
+ * that call outside a stream capture; with nShapes = 0 and every pointer NULL the call does only this set-up.
+ *   dev_shapes        nShapes FlatShape records (192 B each) in device memory
+ *   dev_nodes_out     room for nodeCapacity >= max(1, 2 * nShapes - 1) FlatNode records (48 B each), device memory
+ *   dev_indices_out   room for indexCapacity >= nShapes int32, device memory
+ *   dev_counts_out    2 x int32 in device memory: [0] nodes written, [1] indices written
+ *   err_or_NULL       receives the message of a failed call (errCapacity bytes, always terminated)
+ * Limit: nShapes <= RT_STATIC_BUILD_MAX_SHAPES; more is rejected with RT_ERR_ARG and a message naming the limit (use
+ * rt_build_bvh).  Every GPU that loads the library holds RT_STATIC_BUILD_SCRATCH_BYTES of device memory for the array
+ * until the process exits.  All calls share the array: it keeps the last call's contents (the kernel re-initialises
+ * what it reads), and two calls that overlap on the GPU — different streams, or two host threads — race on it:
+ * order them on one stream or with events. */
+#define RT_STATIC_BUILD_MAX_SHAPES 2048
+#define RT_STATIC_BUILD_SCRATCH_BYTES 486144
+int rt_build_bvh_static(const void* dev_shapes, int nShapes, int maxDepth,
+                        void* dev_nodes_out, int nodeCapacity, int32_t* dev_indices_out, int indexCapacity,
+                        int32_t* dev_counts_out, void* cuda_stream, char* err_or_NULL, size_t errCapacity);
+
 /* K3: scatter `world` compact tile-major shards, laid out rank after rank in
  * dev_shards (each rt_shard_pixels long, as gathered by NCCL), into one
  * row-major W*H image. */

@@ -57,8 +57,24 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_sync_local", "rt_sync_export", "rt_sync_peer", "rt_sync_enable", "rt_frame_acquire", "rt_frame_release", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_animate_shapes", "rt_download_scene", "rt_build_bvh", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_sync_local", "rt_sync_export", "rt_sync_peer", "rt_sync_enable", "rt_frame_acquire", "rt_frame_release", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_animate_shapes", "rt_download_scene", "rt_build_bvh", "rt_build_bvh_static", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
+
+
+RT_STATIC_BUILD_MAX_SHAPES = 2048
+
+
+def build_bvh_static(dev_shapes, n_shapes, max_depth, dev_nodes_out, node_capacity, dev_indices_out, index_capacity,
+                     dev_counts_out, stream=None, library=None):
+    """rt_build_bvh_static (include/rt_api.h): K8's single-block build with its tables in the library's static device
+    array; every argument is a raw device address (int) or None.  Allocates nothing, does not synchronise.  Raises
+    RuntimeError with the library's message on failure."""
+    L = library or lib()
+    err = C.create_string_buffer(512)
+    rc = L.rt_build_bvh_static(dev_shapes, int(n_shapes), int(max_depth), dev_nodes_out, int(node_capacity),
+                               dev_indices_out, int(index_capacity), dev_counts_out, stream, err, len(err))
+    if rc != 0:
+        raise RuntimeError("rt_build_bvh_static failed (%d): %s" % (rc, err.value.decode()))
 
 
 def lib_path():
@@ -126,6 +142,7 @@ def _declare(L):
     L.rt_get_bvh.argtypes = [vp, vp, ip, vp, ip]; L.rt_get_bvh.restype = ip
     L.rt_last_build_ms.argtypes = [vp]; L.rt_last_build_ms.restype = C.c_float
     L.rt_layout_info.argtypes = [vp, C.POINTER(C.c_int * 4)]; L.rt_layout_info.restype = ip
+    L.rt_build_bvh_static.argtypes = [vp, ip, ip, vp, ip, vp, ip, vp, vp, C.c_char_p, C.c_size_t]; L.rt_build_bvh_static.restype = ip
     L.rt_item_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_item_stats.restype = ip
     L.rt_untile.argtypes = [vp, vp, ip, vp]; L.rt_untile.restype = ip
     L.rt_present.argtypes = [vp, vp, vp, C.c_int64]; L.rt_present.restype = ip

@@ -10,6 +10,7 @@
 #include "../host/rt_anim_math.h"
 
 #include <cmath>
+#include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -1393,5 +1394,197 @@ const char* rt_build_info(void) { return "librt_b200_fast sm_100a fmad=ON (fast 
 #else
 const char* rt_build_info(void) { return "librt_b200 sm_100a fmad=off prec-div prec-sqrt tile=32x8 persistent-warps"; }
 #endif
+
+
+// ---- rt_build_bvh_static: K8's single-block build without any allocation -----------------------------------
+// No counterpart in the reference; added for callers that may not call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  rt_build_bvh keeps
+// its tables in DevBufs that grow on demand; this entry point keeps them in ONE file-scope __device__ array of a
+// fixed size instead, so that it calls no cudaMalloc / cudaFree / allocating library routine at all.  Every GPU
+// that loads the library holds the array (RT_STATIC_BUILD_SCRATCH_BYTES, about 0.5 MB) until the process exits.
+//
+// In host code `g_staticBuildScratch` is only the host-side stand-in of the symbol, NOT a device address: the
+// address comes from cudaGetSymbolAddress, asked once per device with that device current (static_scratch_ptr),
+// and that pointer is what the kernel gets.  All calls share the array and it keeps the last call's contents:
+// the kernel's own set-up phase re-initialises every table entry it reads before writing (bld::setup_id: the box
+// keys, the arrival counters, the child links and the control words; bld::init_position: order, node map and
+// records), so nothing has to be cleared by the host — but two calls that overlap on the GPU (different streams,
+// or two host threads) race on it.
+}  // extern "C"
+
+namespace {
+
+constexpr size_t static_align(size_t v) { return (v + 255) & ~(size_t)255; }
+constexpr size_t kSbN       = RT_STATIC_BUILD_MAX_SHAPES;
+constexpr size_t kSbIds     = 2 * kSbN;                                           // build ids 0 .. 2n - 2
+constexpr size_t kSbKeyOff  = 0;                                                  // u64  [6 * ids]
+constexpr size_t kSbRecOff  = kSbKeyOff + static_align(6 * kSbIds * sizeof(bld::u64));   // float4 [3 * n]
+constexpr size_t kSbIntOff  = kSbRecOff + static_align(3 * kSbN * sizeof(float4));       // int [9 * ids + 4 * n + n + 1 + 1]
+constexpr size_t kSbIntCnt  = 9 * kSbIds + 4 * kSbN + kSbN + 1 + 1;
+constexpr size_t kSbCtlOff  = kSbIntOff + static_align(kSbIntCnt * sizeof(int));         // bld::Ctl
+constexpr size_t kSbFlagOff = kSbCtlOff + static_align(sizeof(bld::Ctl));                // unsigned char [n]
+constexpr size_t kSbBytes   = kSbFlagOff + static_align(kSbN);
+static_assert(kSbBytes == RT_STATIC_BUILD_SCRATCH_BYTES, "include/rt_api.h states the size of the static build scratch");
+static_assert(RT_STATIC_BUILD_MAX_SHAPES <= RT_BLD_SMALL_MAX, "the single-block build covers RT_BLD_SMALL_MAX shapes");
+
+static __device__ __align__(256) unsigned char g_staticBuildScratch[kSbBytes];
+
+// the tables of one build inside the scratch array (fixed offsets: every table is sized for the maximum)
+__device__ __forceinline__ BuildBufs static_build_bufs(unsigned char* s) {
+    BuildBufs B;
+    B.N.key = reinterpret_cast<bld::u64*>(s + kSbKeyOff);
+    float4* rec = reinterpret_cast<float4*>(s + kSbRecOff);
+    B.R.cen = rec; B.R.mn = rec + kSbN; B.R.mx = rec + 2 * kSbN;
+    int* q = reinterpret_cast<int*>(s + kSbIntOff);
+    B.N.start = q; q += kSbIds; B.N.count = q; q += kSbIds; B.N.left = q; q += kSbIds; B.N.parent = q; q += kSbIds;
+    B.N.depth = q; q += kSbIds; B.N.desc = q; q += kSbIds; B.N.idx = q; q += kSbIds; B.N.first = q; q += kSbIds;
+    B.N.arrived = reinterpret_cast<unsigned*>(q); q += kSbIds;
+    B.ord[0] = q; q += kSbN; B.ord[1] = q; q += kSbN; B.pnode[0] = q; q += kSbN; B.pnode[1] = q; q += kSbN;
+    B.scanL = q; q += kSbN + 1; B.bsum = q;
+    B.ctl = reinterpret_cast<bld::Ctl*>(s + kSbCtlOff);
+    B.flag = s + kSbFlagOff;
+    return B;
+}
+
+// The variant of bld_small_kernel (rt_build.cuh): the same per-thread bodies (bld::*), phases and barriers, hence the
+// same bytes; the tables are carved out of `scratch` here on the device, an empty shape list gives buildBVH's one empty
+// leaf (main.cpp:1175-1193) and the counts land in the caller's device memory (no host round trip).
+__global__ void __launch_bounds__(RT_BLD_SMALL_THREADS)
+bld_small_static_kernel(unsigned char* __restrict__ scratch, const rt_flat_shape* __restrict__ shapes, int n, int maxDepth,
+                        rt_flat_node* __restrict__ out, int32_t* __restrict__ indices, int32_t* __restrict__ counts) {
+    __shared__ int warpSum[RT_BLD_SMALL_THREADS / 32];
+    const int t = threadIdx.x, T = blockDim.x, lane = t & 31, w = t >> 5;
+    if (n == 0) {
+        if (t == 0) {
+            rt_flat_node r;
+            memset(&r, 0, sizeof r);
+            for (int k = 0; k < 3; ++k) { r.boundsMin[k] = INFINITY; r.boundsMax[k] = -INFINITY; }
+            r.leftChild = r.rightChild = -1;
+            out[0] = r;
+            counts[0] = 1; counts[1] = 0;
+        }
+        return;
+    }
+    const BuildBufs B = static_build_bufs(scratch);
+    const int nIds = 2 * n;
+    for (int id = t; id < nIds; id += T) bld::setup_id(id, B.N, B.ctl, n, maxDepth);      // clears what must start clean
+    __syncthreads();
+    for (int base = 0; base < n; base += T) {
+        const int p = base + t;
+        bld::u64 k[6];
+        if (p < n) bld::init_position(p, shapes, B.R, B.ord[0], B.pnode[0], k);
+        bld_fold_warp(B.N.key, p < n ? 0 : -1, k);
+    }
+    __syncthreads();
+    const int chunk = (n + T - 1) / T, lo = min(n, t * chunk), hi = min(n, lo + chunk);
+    for (int level = 0; level < maxDepth; ++level) {
+        if (!B.ctl->active[level]) break;
+        const int cur = level & 1, nxt = cur ^ 1;
+        int mine = 0;
+        for (int p = lo; p < hi; ++p) { const int f = bld::classify(p, B.R, B.ord[cur], B.pnode[cur], B.N); B.flag[p] = (unsigned char)f; mine += f; }
+        int incl = mine;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+        if (lane == 31) warpSum[w] = incl;
+        __syncthreads();
+        if (w == 0) {
+            int v = warpSum[lane];
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, off); if (lane >= off) v += u; }
+            warpSum[lane] = v;
+        }
+        __syncthreads();
+        int run = (w > 0 ? warpSum[w - 1] : 0) + incl - mine;
+        for (int p = lo; p < hi; ++p) { B.scanL[p] = run; run += (int)B.flag[p]; }
+        if (t == T - 1) B.scanL[n] = warpSum[31];
+        __syncthreads();
+        for (int base = 0; base < n; base += T) {
+            const int p = base + t;
+            bld::u64 k[6];
+            int node = -1;
+            if (p < n) {
+                int newPos, newNode; bool moved;
+                bld::split_position(p, (int)B.flag[p], level, B.pnode[cur], B.scanL, B.N, B.ctl, newPos, newNode, moved);
+                const int shape = B.ord[cur][p];
+                B.ord[nxt][newPos] = shape;
+                B.pnode[nxt][newPos] = newNode;
+                if (moved) { bld::record_keys(B.R.mn[shape], B.R.mx[shape], (unsigned)newPos, k); node = newNode; }
+            }
+            bld_fold_warp(B.N.key, node, k);
+        }
+        if (t == 0) B.ctl->parity = nxt;
+        __syncthreads();
+    }
+    const int* ord = B.ord[B.ctl->parity];
+    for (int id = t; id < nIds; id += T) bld::count_descendants(id, B.N);
+    __syncthreads();
+    for (int id = t; id < nIds; id += T) bld::number_node(id, B.N, B.ctl);
+    __syncthreads();
+    for (int id = t; id < nIds; id += T) bld::emit_node(id, B.N, ord, out, indices);
+    if (t == 0) { counts[0] = B.ctl->nNodes; counts[1] = n; }
+}
+
+// The device address of g_staticBuildScratch on the CURRENT device, resolved once per device.
+constexpr int kSbMaxDevices = 64;
+unsigned char* g_staticBuildPtr[kSbMaxDevices];     // zero-initialised; written once per device (same value if two threads race)
+
+int static_fail(char* err, size_t cap, int code, const char* fmt, ...) {
+    if (err && cap > 0) {
+        va_list ap; va_start(ap, fmt);
+        vsnprintf(err, cap, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+int static_scratch_ptr(unsigned char** out, char* err, size_t cap) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return static_fail(err, cap, RT_ERR_CUDA, "rt_build_bvh_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kSbMaxDevices) return static_fail(err, cap, RT_ERR_ARG, "rt_build_bvh_static: device %d out of range", dev);
+    unsigned char* p = __atomic_load_n(&g_staticBuildPtr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_staticBuildScratch);
+        if (e != cudaSuccess || !p)
+            return static_fail(err, cap, RT_ERR_CUDA, "rt_build_bvh_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+        __atomic_store_n(&g_staticBuildPtr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_build_bvh_static(const void* dev_shapes, int nShapes, int maxDepth,
+                        void* dev_nodes_out, int nodeCapacity, int32_t* dev_indices_out, int indexCapacity,
+                        int32_t* dev_counts_out, void* cuda_stream, char* err, size_t errCapacity) {
+    if (err && errCapacity > 0) err[0] = 0;
+    if (nShapes < 0) return static_fail(err, errCapacity, RT_ERR_ARG, "rt_build_bvh_static: nShapes = %d", nShapes);
+    if (nShapes > RT_STATIC_BUILD_MAX_SHAPES)
+        return static_fail(err, errCapacity, RT_ERR_ARG,
+                           "rt_build_bvh_static: %d shapes, the static scratch holds the tables of at most %d (RT_STATIC_BUILD_MAX_SHAPES); "
+                           "use rt_build_bvh for larger scenes", nShapes, (int)RT_STATIC_BUILD_MAX_SHAPES);
+    if (maxDepth < 0 || maxDepth > 64)
+        return static_fail(err, errCapacity, RT_ERR_ARG, "rt_build_bvh_static: maxDepth = %d, the shader's traversal stack holds 64 entries", maxDepth);
+    unsigned char* scratch = nullptr;
+    const int rc = static_scratch_ptr(&scratch, err, errCapacity);
+    if (rc != RT_OK) return rc;
+    if (nShapes == 0 && !dev_shapes && !dev_nodes_out && !dev_indices_out && !dev_counts_out) return RT_OK;   // set-up only
+    const int needNodes = nShapes > 0 ? 2 * nShapes - 1 : 1;
+    if (!dev_nodes_out || !dev_counts_out || (nShapes > 0 && (!dev_shapes || !dev_indices_out)))
+        return static_fail(err, errCapacity, RT_ERR_ARG, "rt_build_bvh_static: NULL input or output pointer");
+    if (nodeCapacity < needNodes || indexCapacity < nShapes)
+        return static_fail(err, errCapacity, RT_ERR_ARG,
+                           "rt_build_bvh_static: %d shapes need room for %d nodes and %d indices (the tree's size is not known before the build), got %d and %d",
+                           nShapes, needNodes, nShapes, nodeCapacity, indexCapacity);
+    bld_small_static_kernel<<<1, RT_BLD_SMALL_THREADS, 0, static_cast<cudaStream_t>(cuda_stream)>>>(
+        scratch, static_cast<const rt_flat_shape*>(dev_shapes), nShapes, maxDepth,
+        static_cast<rt_flat_node*>(dev_nodes_out), dev_indices_out, dev_counts_out);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return static_fail(err, errCapacity, RT_ERR_CUDA, "rt_build_bvh_static: launch: %s", cudaGetErrorString(e));
+    return RT_OK;
+}
 
 }  // extern "C"
