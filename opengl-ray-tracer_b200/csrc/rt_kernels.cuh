@@ -36,6 +36,9 @@ struct Query {
     float best;      // current bound: candidates need dist < best
     int slot;        // slot of the accepted candidate, -1 = none
     V3 p;            // its hit point
+#if RT_TIMELINE
+    unsigned iters;  // diagnostic build: walk iterations of this warp so far
+#endif
 };
 struct Cand { float dist; int slot; V3 p; };
 
@@ -217,6 +220,9 @@ __device__ __forceinline__ void walk(const DeviceScene& S, Query& q, bool active
             if (stop) k = RT_DONE;
         }
     }
+#if RT_TIMELINE
+    q.iters += (unsigned)it;
+#endif
 }
 // Brute-force twins (a14, useBVH == false): linear scan over the raw shapes.
 template <bool MT>
@@ -298,6 +304,9 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
     idOut = -1;
     bool alive = inside;
     Query q;
+#if RT_TIMELINE
+    q.iters = 0;
+#endif
     {
         const float ndcX = 2.0f * (float)x / P.resW - 1.0f;
         const float ndcY = 1.0f - 2.0f * (float)y / P.resH;
@@ -399,7 +408,11 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
             }
         }
     }
+#if RT_TIMELINE
+    return make_float4(acc.x, acc.y, acc.z, __uint_as_float(q.iters));
+#else
     return make_float4(acc.x, acc.y, acc.z, 1.0f);
+#endif
 }
 
 // ---------------------------------------------------------------------------
@@ -457,6 +470,9 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
         }
         if (w < 0) { if (!heavyLeft && !lightLeft) break; continue; }
         const long long itemClk0 = P.itemCost ? clock64() : 0;
+#if RT_TIMELINE
+        const long long tlClk0 = clock64();
+#endif
         const int t = P.tileBegin + w / RT_WARPS_PER_TILE, b = w % RT_WARPS_PER_TILE;
         const int tile = P.shardRank + t * P.shardWorld;
         const int lx = ((b & 3) << 3) + (lane & 7);
@@ -494,6 +510,20 @@ render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __res
                 id = lane == 0 ? (int)(gt & 0x7fffffff) : lane == 1 ? (int)(dt >> 2) : lane == 2 ? (int)smid : (int)wid;
             }
         }
+#if RT_TIMELINE      // diagnostic build only (tools/timeline2.py): the ids plane carries when and where every part of an item ran
+        if (!COUNT && P.writeIds == 1) {
+            unsigned long long gt; unsigned smid;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            const int rel = lane - (part << 5) / parts;
+            const unsigned long long dtl = (unsigned long long)(clock64() - tlClk0);
+            if (rel == 0) id = (int)(gt & 0x7fffffffull);
+            else if (rel == 1) id = (int)(dtl >> 2);
+            else if (rel == 2) id = (int)(smid | (warpSlot << 8) | ((unsigned)parts << 16) | ((unsigned)part << 24));
+            else if (rel == 3) id = (int)__float_as_uint(c.w);
+        }
+        c.w = 1.0f;
+#endif
         __syncwarp();
         if (P.shardWorld == 1) {
             if (inside) {

@@ -22,6 +22,7 @@ ap.add_argument("--warmup", type=int, default=5)
 ap.add_argument("--cases", default="car4k,car800,monkey800")
 ap.add_argument("--world", type=int, default=1)
 ap.add_argument("--rank", type=int, default=0)
+ap.add_argument("--noflush", action="store_true", help="leave L2 as the previous frame left it (diagnostic: how much of a frame is cold misses)")
 a = ap.parse_args()
 rt = rtload.load()
 CASES = {"car4k": ("car", 3840, 2160, 0), "car800": ("car", 800, 600, 0), "monkey800": ("monkey", 800, 600, 0),
@@ -42,7 +43,8 @@ with torch.cuda.stream(stream):
         img = torch.empty((px, 4), dtype=torch.float32, device="cuda")
         evs = []
         for i in range(a.warmup + a.steps):
-            flush.zero_()
+            if not a.noflush:
+                flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(); tr.render_device(p, img.data_ptr()); e1.record()
             if i >= a.warmup:
