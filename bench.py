@@ -571,6 +571,41 @@ def time_device_build(torch, rt, stream):
     return out
 
 
+def time_k3_k5(torch, rt, stream, local, W, H, flush, steps=20, warmup=5):
+    """K3 (rt_untile: 8 tile-major shards -> one row-major frame) and K5 (rt_present: float4 -> RGBA8) are pure streaming
+    kernels: device time with L2 flushed, algorithmic GB/s (32 and 20 bytes per pixel) against the measured HBM copy peak."""
+    peak = None
+    try:
+        peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs")
+    except (OSError, ValueError):
+        pass
+    tr = rt.RayTracer(W, H, device=local)
+    tr.set_stream(stream.cuda_stream)
+    world = 8
+    tr.set_shard(0, world)
+    px = tr.shard_pixels()
+    shards = torch.rand((world * px, 4), dtype=torch.float32, device="cuda")
+    full = torch.empty((H, W, 4), dtype=torch.float32, device="cuda")
+    img8 = torch.empty((H, W, 4), dtype=torch.uint8, device="cuda")
+    out = {"workload": "%dx%d frame, 8 shards" % (W, H), "hbm_peak_GBps": peak or 6650.0,
+           "hbm_peak_source": "MEASURED_PEAKS.json hbm_gbs" if peak else "fallback (B200_PROFILING.md)"}
+    for name, fn, nbytes in (("k3_untile", lambda: tr.untile(shards.data_ptr(), world, full.data_ptr()), 32 * W * H),
+                             ("k5_present", lambda: tr.present(full.data_ptr(), img8.data_ptr(), W * H), 20 * W * H)):
+        evs = []
+        for i in range(warmup + steps):
+            if flush is not None:
+                flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            if i >= warmup:
+                evs.append((e0, e1))
+        torch.cuda.synchronize()
+        ms = sum(x.elapsed_time(y) for x, y in evs) / len(evs)
+        out[name] = {"ms": ms, "algorithmic_bytes": nbytes, "GBps": nbytes / ms / 1e6, "frac_of_hbm_peak": nbytes / ms / 1e6 / (peak or 6650.0)}
+    tr.close()
+    return out
+
+
 def soup_extra(torch, dist, rt, stream, local, rank, world, W, H, flush, steps, warmup):
     """BASELINE.json configs[3]: the 1M-triangle soup + 10k spheres (deep BVH, traversal-bound), tile-sharded over the ranks
     like the headline frame.  The scene is uploaded ONCE; an end-to-end step updates the camera, renders and brings the frame
@@ -845,6 +880,11 @@ def main():
                 extra["fast_build"] = fast_build_block(torch, dist, rt, stream, local, sc, params, W, H, flush, args.steps, args.warmup, tot)
             except Exception as e:
                 extra["fast_build"] = {"error": repr(e)}
+            try:
+                extra["k3_k5_hbm"] = {"3840x2160": time_k3_k5(torch, rt, stream, local, 3840, 2160, flush),
+                                      "7680x4320": time_k3_k5(torch, rt, stream, local, 7680, 4320, flush)}
+            except Exception as e:
+                extra["k3_k5_hbm"] = {"error": repr(e)}
             try:
                 extra["soup_1M_3840x2160"] = soup_extra(torch, dist, rt, stream, local, rank, world, 3840, 2160, flush, 6, 3)
             except Exception as e:

@@ -1338,9 +1338,9 @@ int rt_untile(rt_ctx* c, const float* dev_shards, int world, float* dev_rgba_out
     CU(c, cudaSetDevice(c->device));
     const int nT = tiles_x(c) * tiles_y(c);
     const long long shardPixels = (long long)((nT + world - 1) / world) * RT_TILE_W * RT_TILE_H;   // rank 0's (largest) shard
-    const long long n = (long long)c->W * c->H;
-    untile_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(dev_shards),
-        reinterpret_cast<float4*>(dev_rgba_out), c->W, c->H, tiles_x(c), world, shardPixels);
+    const int blocks = (nT + RT_UNTILE_UNROLL - 1) / RT_UNTILE_UNROLL;
+    untile_kernel<<<(unsigned)blocks, RT_TILE_W * RT_TILE_H, 0, c->stream>>>(reinterpret_cast<const float4*>(dev_shards),
+        reinterpret_cast<float4*>(dev_rgba_out), c->W, c->H, tiles_x(c), nT, world, shardPixels);
     c->launches++;
     CU(c, cudaGetLastError());
     return RT_OK;
@@ -1350,7 +1350,7 @@ int rt_present(rt_ctx* c, const float* dev_rgba, uint8_t* dev_rgba8_out, int64_t
     if (!c || !dev_rgba || !dev_rgba8_out || pixels < 0) return RT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
     if (pixels > 0) {
-        present_kernel<<<(unsigned)((pixels + 255) / 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(dev_rgba),
+        present_kernel<<<(unsigned)((pixels + 256 * RT_PRESENT_UNROLL - 1) / (256 * RT_PRESENT_UNROLL)), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(dev_rgba),
             reinterpret_cast<uchar4*>(dev_rgba8_out), (long long)pixels);
         c->launches++;
     }

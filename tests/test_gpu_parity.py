@@ -190,6 +190,26 @@ def test_sharded_scheduled_frames(rt):
     one.close()
 
 
+@pytest.mark.parametrize("n", [1, 255, 1023, 1025, 4097, 262147])
+def test_present_edge_values_and_ragged_sizes(rt, oracle, n):
+    """K5 on synthetic pixels: below 0, above 1, NaN, +-inf, exact quantisation boundaries; sizes around the four-pixels-per-
+    thread passes of the kernel (a pass = grid x 256 x 4 pixels)."""
+    import torch
+    rng = np.random.default_rng(n)
+    rgba = rng.uniform(-0.5, 1.5, (n, 4)).astype(np.float32)
+    special = np.array([np.nan, np.inf, -np.inf, 0.0, -0.0, 1.0, 0.5, 127.5 / 255.0, 0.5 / 255.0, 254.5 / 255.0], dtype=np.float32)
+    rgba.reshape(-1)[:: 7] = special[np.arange(len(rgba.reshape(-1)[:: 7])) % len(special)]
+    tr = rt.RayTracer(64, 48)
+    src = torch.from_numpy(rgba).cuda()
+    img8 = torch.full((n + 8, 4), 77, dtype=torch.uint8, device="cuda")
+    tr.present(src.data_ptr(), img8.data_ptr(), n)
+    tr.synchronize()
+    got = img8.cpu().numpy()
+    assert np.array_equal(got[:n], oracle.present(rgba.reshape(1, n, 4)).reshape(n, 4))
+    assert (got[n:] == 77).all(), "wrote past the end"
+    tr.close()
+
+
 def test_present_matches_oracle(rt, oracle):
     import torch
     W, H = 200, 150
