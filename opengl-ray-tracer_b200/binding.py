@@ -77,6 +77,17 @@ def build_bvh_static(dev_shapes, n_shapes, max_depth, dev_nodes_out, node_capaci
         raise RuntimeError("rt_build_bvh_static failed (%d): %s" % (rc, err.value.decode()))
 
 
+def _records(a, dtype, what):
+    """The C side strides over std430 records (192 / 48 bytes): numpy silently PACKS a padded structured dtype in some
+    operations (np.concatenate does), and such an array would be read past its end."""
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a)
+    if a.dtype.itemsize != dtype.itemsize:
+        raise ValueError("%s: records of %d bytes, the wire format has %d (a packed copy of the structured dtype?)" % (what, a.dtype.itemsize, dtype.itemsize))
+    return a
+
+
 def lib_path():
     return os.path.join(_build.CSRC, "librt_b200.so")
 
@@ -209,7 +220,7 @@ class Scene:
     @classmethod
     def from_shapes(cls, shapes, light, camera, bvh_depth=15, width=800, height=600):
         H = hostlib()
-        shapes = np.ascontiguousarray(shapes)
+        shapes = _records(shapes, SHAPE_DTYPE, "shapes")
         h = H.rh_scene_from_shapes(_ptr(shapes), len(shapes), _ptr(light), _ptr(camera), bvh_depth)
         return cls("custom", width, height, _handle=h)
 
@@ -297,6 +308,7 @@ class RayTracer:
     def upload_scene(self, light=None, camera=None, shapes=None, nodes=None, indices=None):
         keep = [np.ascontiguousarray(a) if a is not None else None for a in (light, camera, shapes, nodes, indices)]
         li, ca, sh, no, ix = keep
+        sh, no = _records(sh, SHAPE_DTYPE, "shapes"), _records(no, NODE_DTYPE, "nodes")
         self._chk(self._L.rt_upload_scene(self._c, _ptr(li), _ptr(ca), _ptr(sh), 0 if sh is None else len(sh),
                                           _ptr(no), 0 if no is None else len(no), _ptr(ix), 0 if ix is None else len(ix)))
 
@@ -310,11 +322,11 @@ class RayTracer:
         self._chk(self._L.rt_update_light(self._c, _ptr(np.ascontiguousarray(light))))
 
     def update_shapes(self, first, shapes):
-        shapes = np.ascontiguousarray(shapes)
+        shapes = _records(shapes, SHAPE_DTYPE, "shapes")
         self._chk(self._L.rt_update_shapes(self._c, int(first), len(shapes), _ptr(shapes)))
 
     def update_nodes(self, nodes):
-        nodes = np.ascontiguousarray(nodes)
+        nodes = _records(nodes, NODE_DTYPE, "nodes")
         self._chk(self._L.rt_update_nodes(self._c, _ptr(nodes), len(nodes)))
 
     def set_shard(self, rank, world):

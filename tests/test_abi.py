@@ -78,3 +78,16 @@ def test_wire_format_equals_the_references_own_header():
                         "-I", ref, "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "emu", "flat_layout_check.cpp")],
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-3000:]
+
+
+def test_binding_rejects_packed_structured_arrays(rt):
+    """np.concatenate PACKS a padded structured dtype (192-byte FlatShape records become 124 bytes): the harness must refuse
+    such an array instead of letting the C side stride past its end."""
+    import numpy as np
+    import pytest
+    sh = np.zeros(3, dtype=rt.SHAPE_DTYPE)
+    packed = np.concatenate([sh, sh])
+    if packed.dtype.itemsize == rt.SHAPE_DTYPE.itemsize:
+        pytest.skip("this numpy keeps the padding")
+    with pytest.raises(ValueError, match="192"):
+        rt.Scene.from_shapes(packed, np.zeros(1, rt.LIGHT_DTYPE), np.zeros(1, rt.CAMERA_DTYPE))

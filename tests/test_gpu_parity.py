@@ -75,6 +75,60 @@ def test_random_scenes(rt, oracle, seed):
         assert_parity(stats, "random seed=%d mt=%s" % (seed, mt))
 
 
+def _look_at(rt, pos, target, W, H, fov):
+    """Camera bytes as Camera::LookAt leaves them (camera.hpp:99-110): Front, Right = Front x worldUp, Up = Right x Front, fp32."""
+    cam = np.zeros(1, dtype=rt.CAMERA_DTYPE)
+    f32 = np.float32
+    pos, target = np.asarray(pos, f32), np.asarray(target, f32)
+    nrm = lambda v: (v * f32(1.0 / np.sqrt(f32((v * v).sum(dtype=f32))))).astype(f32)   # noqa: E731
+    front = nrm(target - pos)
+    right = nrm(np.cross(front, np.array([0, 1, 0], f32)).astype(f32))
+    up = nrm(np.cross(right, front).astype(f32))
+    cam["Position"], cam["Front"], cam["Up"], cam["Right"] = pos, front, up, right
+    cam["aspectRatio"], cam["fov"] = f32(W) / f32(H), f32(fov)
+    return cam
+
+
+@pytest.mark.parametrize("seed", list(range(100, 140)))
+def test_fuzz_scenes_cameras_and_settings(rt, oracle, seed):
+    """Random everything at once: 1 .. 500 shapes of the three boundable types with a tenth of them DUPLICATED under another
+    material (equal distances: the first in the reference's visit order must win, gpu_shader.comp:410-411), a camera somewhere
+    inside or outside the scene looking anywhere, a light anywhere, BVH depth 1 .. 20 (fat leaves of hundreds of shapes at the
+    low end), 0 .. 5 bounces, both triangle tests, Fresnel on / off, a ragged frame size."""
+    rng = np.random.default_rng(seed)
+    W, H = int(rng.integers(33, 131)), int(rng.integers(17, 97))
+    n = int(rng.choice([1, 2, 7, 40, 150, 500]))
+    shapes = random_shapes(rt, rng, n, types=(0, 2, 3), extent=float(rng.choice([3.0, 10.0, 40.0])))
+    ndup = max(1, n // 10)
+    dup = shapes[rng.integers(0, n, ndup)].copy()
+    dup["color"] = rng.uniform(0, 1, (ndup, 3))
+    dup["specularStrength"] = rng.choice([0.0, 0.5, 1.0], ndup)
+    both = np.zeros(n + ndup, dtype=rt.SHAPE_DTYPE)          # (np.concatenate would PACK the padded dtype: 124-byte records)
+    both[:n], both[n:] = shapes, dup
+    shapes = both[rng.permutation(n + ndup)]
+    assert shapes.dtype.itemsize == 192
+    base = rt.Scene("toy", W, H)
+    light = base.light.copy()
+    light["position"] = rng.uniform(-25, 25, 3)
+    light["color"] = rng.uniform(5, 40) * np.ones(3)
+    cam = _look_at(rt, rng.uniform(-20, 20, 3), rng.uniform(-5, 5, 3), W, H, float(rng.choice([30.0, 60.0, 100.0])))
+    depth = int(rng.integers(1, 21))
+    sc = rt.Scene.from_shapes(shapes, light, cam, bvh_depth=depth, width=W, height=H)
+    kw = dict(maxBounces=int(rng.integers(0, 6)), useMollerTrumbore=bool(rng.integers(0, 2)), useFresnel=bool(rng.integers(0, 2)))
+    stats, *_ = _render_both(rt, oracle, sc, W, H, **kw)
+    assert_parity(stats, "fuzz seed=%d %dx%d n=%d %r" % (seed, W, H, len(shapes), kw))
+    # the same scene through the device builder + device layout, and in the reference's own walk order
+    p = rt.make_params(W, H, **kw)
+    a = rt.RayTracer(W, H); a.upload(sc); want = a.render(p); a.close()
+    b = rt.RayTracer(W, H); b.upload_scene(sc.light, sc.camera, sc.shapes)
+    nodes, idx = b.build_bvh(depth, rt.RT_BUILD_DEVICE_LAYOUT)
+    assert nodes.tobytes() == np.ascontiguousarray(sc.nodes).tobytes() and idx.tobytes() == np.ascontiguousarray(sc.indices).tobytes()
+    got = b.render(p); b.close()
+    assert np.array_equal(got[1], want[1]) and np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)), "device build + layout differs, seed %d" % seed
+    c = rt.RayTracer(W, H, flags=rt.RT_FLAG_REFERENCE_WALK | rt.RT_FLAG_HIT_IDS); c.upload(sc); got = c.render(p); c.close()
+    assert np.array_equal(got[1], want[1]) and np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)), "reference walk differs, seed %d" % seed
+
+
 def test_planes_bruteforce(rt, oracle):
     """Infinite planes (type 1) only work in the brute-force path upstream."""
     rng = np.random.default_rng(7)
