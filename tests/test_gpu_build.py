@@ -5,7 +5,7 @@ device-built tree must be bit-identical to one rendered over the uploaded host t
 import numpy as np
 import pytest
 
-from util import random_shapes
+from util import bit_fuzzed_shapes, random_shapes
 
 pytestmark = pytest.mark.gpu
 
@@ -96,6 +96,22 @@ def test_device_build_edge_cases(rt):
     # no depth budget: the root is the only node
     nodes, idx = tr.build_bvh(0)
     assert len(nodes) == 1 and nodes["leftChild"][0] == -1 and nodes["numShapes"][0] == len(cases[-1][0])
+    tr.close()
+
+
+@pytest.mark.parametrize("seed", list(range(24)))
+def test_device_build_bit_fuzz(rt, seed):
+    """Arbitrary bit patterns in the geometry fields (NaN, inf, denormals, signed zeros): K8's tree is still the host
+    builder's byte for byte — the ordered keys and their sequence numbers reproduce what `x < mn ? x : mn` keeps."""
+    light = np.zeros(1, rt.LIGHT_DTYPE); cam = np.zeros(1, rt.CAMERA_DTYPE)
+    sh, depth = bit_fuzzed_shapes(rt, seed)
+    ref = rt.Scene.from_shapes(sh, light, cam, bvh_depth=depth)
+    tr = rt.RayTracer(64, 48)
+    for flags in PATHS:
+        tr.upload_scene(light, cam, sh)
+        nodes, idx = tr.build_bvh(depth, flags)
+        assert nodes.tobytes() == np.ascontiguousarray(ref.nodes).tobytes(), (seed, len(sh), depth, flags)
+        assert idx.tobytes() == np.ascontiguousarray(ref.indices).tobytes(), (seed, len(sh), depth, flags)
     tr.close()
 
 

@@ -71,3 +71,25 @@ def random_shapes(rt, rng, n, types=(0, 2, 3), extent=10.0):
                 s["wallWidth"] = rng.uniform(2, 12)
                 s["wallHeight"] = rng.uniform(2, 12)
     return sh
+
+
+FLOAT_FIELDS = ["sphereCenter", "sphereRadius", "planeNormal", "planeD", "wallStart", "wallWidth", "wallHeight", "triP1", "triP2", "triP3"]
+
+
+def bit_fuzzed_shapes(rt, seed):
+    """Shapes of all four types whose geometry fields carry arbitrary bit patterns in places (NaNs of both signs, infinities,
+    denormals, signed zeros, FLT_MAX): 2 % or 30 % of the words, any pattern or a list of special ones.  Returns (shapes, depth)."""
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.choice([3, 20, 200, 900]))
+    sh = random_shapes(rt, rng, n, types=(0, 1, 2, 3))
+    mode = seed % 4
+    special = np.array([0x7fc00000, 0xffc00000, 0x7f800000, 0xff800000, 0x00000001, 0x80000001, 0, 0x80000000, 0x7f7fffff], dtype=np.uint32)
+    for f in FLOAT_FIELDS:
+        v = sh[f].copy().view(np.uint32)
+        m = rng.uniform(size=v.shape) < (0.02 if mode < 2 else 0.3)
+        if mode % 2 == 0:
+            v[m] = rng.integers(0, 2 ** 32, size=int(m.sum()), dtype=np.uint64).astype(np.uint32)
+        else:
+            v[m] = rng.choice(special, size=int(m.sum()))
+        sh[f] = v.view(np.float32)
+    return sh, int(rng.integers(1, 20))
