@@ -6,7 +6,7 @@ Bar (north_star): primary-hit shape ids bit-exact; colour within max-abs 1e-3 pe
 import numpy as np
 import pytest
 
-from util import assert_parity, compare, random_shapes
+from util import assert_parity, bit_fuzzed_shapes, compare, random_shapes
 
 pytestmark = pytest.mark.gpu
 
@@ -127,6 +127,26 @@ def test_fuzz_scenes_cameras_and_settings(rt, oracle, seed):
     assert np.array_equal(got[1], want[1]) and np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)), "device build + layout differs, seed %d" % seed
     c = rt.RayTracer(W, H, flags=rt.RT_FLAG_REFERENCE_WALK | rt.RT_FLAG_HIT_IDS); c.upload(sc); got = c.render(p); c.close()
     assert np.array_equal(got[1], want[1]) and np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)), "reference walk differs, seed %d" % seed
+
+
+@pytest.mark.parametrize("seed", list(range(24)))
+def test_bit_fuzzed_scenes(rt, oracle, seed):
+    """Geometry fields with arbitrary bit patterns (NaN, inf, denormals, signed zeros; util.bit_fuzzed_shapes): the walk's
+    fast paths must hand such rays and boxes to the exact GLSL-select code (slab / Ray::fast / Ray::sub), the device layout must
+    stay conservative or fall back — ids and colours still equal the oracle's, with the BVH, both triangle tests, and brute force."""
+    sh, depth = bit_fuzzed_shapes(rt, seed)
+    if seed % 3:
+        sh = sh[sh["type"] != 1]                       # infinite planes only in every third case
+    rng = np.random.default_rng(seed)
+    W, H = 96, 64
+    base = rt.Scene("toy", W, H)
+    light = base.light.copy()
+    light["position"] = rng.uniform(-25, 25, 3)
+    cam = _look_at(rt, rng.uniform(-20, 20, 3), rng.uniform(-5, 5, 3), W, H, 60.0)
+    sc = rt.Scene.from_shapes(sh, light, cam, bvh_depth=depth, width=W, height=H)
+    for kw in (dict(), dict(useMollerTrumbore=True, useFresnel=True), dict(useBVH=False)):
+        stats, *_ = _render_both(rt, oracle, sc, W, H, **kw)
+        assert_parity(stats, "bit fuzz seed=%d n=%d depth=%d %r" % (seed, len(sh), depth, kw))
 
 
 def test_planes_bruteforce(rt, oracle):

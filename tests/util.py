@@ -9,7 +9,8 @@ COLOR_FRAC = 0.999
 def compare(rgba, ids, o_rgba, o_ids, o_dists=None):
     """Returns a dict of parity statistics between a render and the oracle's."""
     rgba = np.asarray(rgba).reshape(o_rgba.shape)
-    diff = np.abs(rgba.astype(np.float64) - o_rgba.astype(np.float64))
+    with np.errstate(invalid="ignore"):              # inf - inf: handled below
+        diff = np.abs(rgba.astype(np.float64) - o_rgba.astype(np.float64))
     both_nan = np.isnan(rgba) & np.isnan(o_rgba)
     diff[both_nan] = 0.0
     diff[np.isinf(o_rgba) & (rgba == o_rgba)] = 0.0       # the same infinity on both sides (inf - inf is NaN)
