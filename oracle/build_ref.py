@@ -111,6 +111,12 @@ def main() -> int:
     rc = subprocess.call(cmd)
     if rc != 0:
         return rc
+    # the same shader text with min / max / clamp / mix as the GLSL specification words them (NaN operands: see the glue)
+    cmd = cmd[:-2] + ["-DREF_GLSL_BUILTINS=1", "-o", os.path.join(outdir, "libref_shader_glsl.so")]
+    print(" ".join(cmd))
+    rc = subprocess.call(cmd)
+    if rc != 0:
+        return rc
     # the reference's own C++ shape classes, for the primitive-level cross-check
     cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared",
            "-I", os.path.join(ref, "src"), "-I", ref, "-I", glm, "-I", os.path.join(HERE, "stubs"),

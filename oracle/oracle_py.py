@@ -79,6 +79,25 @@ def ref_lib():
     return _ref
 
 
+_ref_glsl = None
+
+
+def ref_lib_glsl():
+    """The reference shader compiled as C++ with min / max / clamp / mix as the GLSL specification words them
+    (oracle/_ref/libref_shader_glsl.so, -DREF_GLSL_BUILTINS in ref_shader_glue.cpp), or None if never built."""
+    global _ref_glsl
+    if _ref_glsl is None:
+        p = os.path.join(HERE, "_ref", "libref_shader_glsl.so")
+        if not os.path.exists(p):
+            return None
+        R = C.CDLL(p)
+        vp, ip = C.c_void_p, C.c_int
+        R.ref_render.argtypes = [vp, vp, vp, ip, vp, ip, vp, ip, vp, ip, ip, ip, ip, vp, ip]
+        R.ref_render.restype = ip
+        _ref_glsl = R
+    return _ref_glsl
+
+
 _bvh = None
 
 
@@ -182,8 +201,8 @@ def primary_ties(camera, shapes, nodes, indices, params, W, H, threads=None, row
     return (int(n), ties) if want_map else int(n)
 
 
-def ref_render(light, camera, shapes, nodes, indices, params, W, H, threads=None, row_step=1, row_phase=0):
-    R = ref_lib()
+def ref_render(light, camera, shapes, nodes, indices, params, W, H, threads=None, row_step=1, row_phase=0, glsl_builtins=False):
+    R = ref_lib_glsl() if glsl_builtins else ref_lib()
     if R is None:
         raise RuntimeError("oracle/_ref not built")
     threads = threads or os.cpu_count() or 1

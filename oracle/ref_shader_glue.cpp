@@ -14,6 +14,9 @@
  * Known, documented deviations of this build from GLSL-spec semantics (they
  * come from GLM 0.9.8.5, glm/glm/detail/func_common.inl): mix(x,y,a) is
  * x + a*(y-x); min/max return the second operand for NaN in the first.
+ * A second build with -DREF_GLSL_BUILTINS (libref_shader_glsl.so) defines those
+ * built-ins as the GLSL specification words them; tests/test_oracle_golden.py
+ * compares the restatement with it on NaN-laden inputs.
  */
 #include <cmath>
 #include <cstdint>
@@ -31,6 +34,20 @@ typedef unsigned int uint;
 
 inline float pow(float a, int b) { return std::pow(a, (float)b); }
 inline float pow(float a, float b) { return std::pow(a, b); }
+
+#ifdef REF_GLSL_BUILTINS
+// Second build (libref_shader_glsl.so): the same shader text with the built-ins the shader calls defined as the GLSL 4.60
+// specification words them (8.3 Common Functions) instead of GLM's forms: min(x,y) = y if y < x, otherwise x; max(x,y) = y
+// if x < y, otherwise x; clamp = min(max(x, lo), hi); mix = x*(1-a) + y*a.  The two builds agree wherever no NaN or signed
+// zero reaches these functions; with a NaN operand GLM's `x < y ? x : y` / `x > y ? x : y` keep the OTHER operand than the
+// specification's selects.  Declared here they hide GLM's templates for unqualified calls from the shader body.
+inline float min(float x, float y) { return y < x ? y : x; }
+inline float max(float x, float y) { return x < y ? y : x; }
+inline vec3 min(vec3 a, vec3 b) { return vec3(min(a.x, b.x), min(a.y, b.y), min(a.z, b.z)); }
+inline vec3 max(vec3 a, vec3 b) { return vec3(max(a.x, b.x), max(a.y, b.y), max(a.z, b.z)); }
+inline float clamp(float x, float lo, float hi) { return min(max(x, lo), hi); }
+inline vec3 mix(vec3 x, vec3 y, float a) { return x * (1.0f - a) + y * a; }
+#endif
 
 template <class T>
 struct SSBO {
