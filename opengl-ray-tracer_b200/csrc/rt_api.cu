@@ -175,7 +175,7 @@ struct rt_ctx {
     DevBuf<unsigned char> heavyFlag;
     int lptItems = -1;                // item count the recorded costs belong to (-1: none yet)
     unsigned lptFrame = 0;            // frames rendered with these costs (parity = slot of the control block)
-    int gridBlocks[4] = {0, 0, 0, 0}; // persistent grid per kernel variant
+    int gridBlocks[6] = {0, 0, 0, 0, 0, 0}; // persistent grid per kernel variant
     int shardRank = 0, shardWorld = 1;
 };
 
@@ -741,11 +741,14 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         if (nBands < 1) nBands = 1;
     }
     CU(c, c->queue.reserve(RT_MAX_BANDS));
-    const int variant = (F.useMT ? 1 : 0) + (count ? 2 : 0);
+    // the walked list is far larger than L1: the instantiation with more resident warps (rt_kernels.cuh: RT_MIN_BLOCKS_BIG)
+    const bool big = !count && F.useBVH && (c->nDfsB > 0 ? c->nDfsB : c->nDfs) >= RT_BIG_SCENE_NODES;
+    const int variant = big ? 4 + (F.useMT ? 1 : 0) : (F.useMT ? 1 : 0) + (count ? 2 : 0);
     if (tilesMine > 0 && c->gridBlocks[variant] == 0) {       // persistent grid: fill every SM once
         int perSM = 0;
-        const void* fn = variant == 0 ? (const void*)render_kernel<false, false> : variant == 1 ? (const void*)render_kernel<true, false>
-                       : variant == 2 ? (const void*)render_kernel<false, true> : (const void*)render_kernel<true, true>;
+        const void* fn = variant == 0 ? (const void*)render_kernel<false, false, RT_MIN_BLOCKS> : variant == 1 ? (const void*)render_kernel<true, false, RT_MIN_BLOCKS>
+                       : variant == 2 ? (const void*)render_kernel<false, true, RT_MIN_BLOCKS> : variant == 3 ? (const void*)render_kernel<true, true, RT_MIN_BLOCKS>
+                       : variant == 4 ? (const void*)render_kernel<false, false, RT_MIN_BLOCKS_BIG> : (const void*)render_kernel<true, false, RT_MIN_BLOCKS_BIG>;
         CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, RT_BLOCK_THREADS, 0));
         c->gridBlocks[variant] = c->smCount * (perSM > 0 ? perSM : 1);
     }
@@ -795,11 +798,16 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         unsigned long long* tl = c->tally.p;
         unsigned int* q = band == 0 ? queue0 : c->queue.p + band;
         if (count) {
-            if (F.useMT) render_kernel<true, true><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);
-            else         render_kernel<false, true><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);
+            if (F.useMT) render_kernel<true, true, RT_MIN_BLOCKS><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);
+            else         render_kernel<false, true, RT_MIN_BLOCKS><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, tl, q);
         } else {
-            if (F.useMT) render_kernel<true, false><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
-            else         render_kernel<false, false><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
+            if (big) {
+                if (F.useMT) render_kernel<true, false, RT_MIN_BLOCKS_BIG><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
+                else         render_kernel<false, false, RT_MIN_BLOCKS_BIG><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
+            } else {
+                if (F.useMT) render_kernel<true, false, RT_MIN_BLOCKS><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
+                else         render_kernel<false, false, RT_MIN_BLOCKS><<<grid, blk, 0, rs>>>(S, F, o4, dev_ids, nullptr, q);
+            }
         }
         c->launches++;
         if (toHost) {

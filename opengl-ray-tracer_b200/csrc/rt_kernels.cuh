@@ -8,6 +8,16 @@
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 8          // resident CTAs per SM the register allocation aims for
 #endif
+// A scene whose walked list does not stay in L1 (the soup: 63 MB of nodes) waits for L2 / HBM, not for issue slots: there
+// 10 resident CTAs of 48 registers beat 8 of 64 in spite of their spills (soup-1M at 4K 27.5 -> 26.1 ms, 300 k shapes 10.3 ->
+// 9.9, 60 k 2.72 -> 2.67; 11 / 12 CTAs and 9: slower; the car, issue-bound, loses 5 %: profiles/r2/occupancy_sweep.txt).
+// The second instantiation is chosen at launch for lists of RT_BIG_SCENE_NODES nodes and more.
+#ifndef RT_MIN_BLOCKS_BIG
+#define RT_MIN_BLOCKS_BIG 10
+#endif
+#ifndef RT_BIG_SCENE_NODES
+#define RT_BIG_SCENE_NODES 100000
+#endif
 
 namespace rt {
 
@@ -428,8 +438,8 @@ __device__ __forceinline__ float4 shade_pixel(const DeviceScene& S, const FrameP
 #define RT_HEAVY_SLOTS 24      // warp slots (of 32 resident) that claim heavy blocks first
 #endif
 
-template <bool MT, bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK_THREADS, RT_MIN_BLOCKS)
+template <bool MT, bool COUNT, int MINB>
+__global__ void __launch_bounds__(RT_BLOCK_THREADS, MINB)
 render_kernel(DeviceScene S, FrameParams P, float4* __restrict__ out, int* __restrict__ ids,
               unsigned long long* __restrict__ tally, unsigned int* __restrict__ queue) {
     Tally tl;

@@ -26,7 +26,7 @@ ap.add_argument("--noflush", action="store_true", help="leave L2 as the previous
 a = ap.parse_args()
 rt = rtload.load()
 CASES = {"car4k": ("car", 3840, 2160, 0), "car800": ("car", 800, 600, 0), "monkey800": ("monkey", 800, 600, 0),
-         "soup4k": ("soup", 3840, 2160, 1000000), "soup800": ("soup", 800, 600, 1000000), "car4k_mtfr": ("car", 3840, 2160, 0)}
+         "soup4k": ("soup", 3840, 2160, 1000000), "soup800": ("soup", 800, 600, 1000000), "soup300k4k": ("soup", 3840, 2160, 300000), "soup60k4k": ("soup", 3840, 2160, 60000), "soup15k4k": ("soup", 3840, 2160, 15000), "car4k_mtfr": ("car", 3840, 2160, 0)}
 out = {"lib": os.environ.get("RT_B200_LIB", "in-tree"), "flags": a.flags}
 stream = torch.cuda.Stream()
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")

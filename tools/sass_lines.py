@@ -8,7 +8,7 @@ import csv, io, os, re, subprocess, sys, tempfile
 
 rep = sys.argv[1]
 lib = sys.argv[2] if len(sys.argv) > 2 else "opengl-ray-tracer_b200/csrc/librt_b200.so"
-kern = sys.argv[3] if len(sys.argv) > 3 else "render_kernelILb0ELb0"
+kern = sys.argv[3] if len(sys.argv) > 3 else "render_kernelILb0ELb0ELi8E"
 outp = sys.argv[4] if len(sys.argv) > 4 else None
 
 tmp = tempfile.mkdtemp()
