@@ -1485,7 +1485,8 @@ bld_small_static_kernel(unsigned char* __restrict__ scratch, const rt_flat_shape
     }
     __syncthreads();
     const int chunk = (n + T - 1) / T, lo = min(n, t * chunk), hi = min(n, lo + chunk);
-    for (int level = 0; level < maxDepth; ++level) {
+    int level = 0;
+    for (; level < maxDepth; ++level) {
         if (!B.ctl->active[level]) break;
         const int cur = level & 1, nxt = cur ^ 1;
         int mine = 0;
@@ -1524,8 +1525,11 @@ bld_small_static_kernel(unsigned char* __restrict__ scratch, const rt_flat_shape
         __syncthreads();
     }
     const int* ord = B.ord[B.ctl->parity];
-    for (int id = t; id < nIds; id += T) bld::count_descendants(id, B.N);
-    __syncthreads();
+    for (int lev = level; lev >= 0; --lev) {                            // descendant counts level by level, as in bld_small_kernel
+        for (int id = t; id < nIds; id += T)
+            if (B.N.left[id] != RT_BLD_ABSENT && maxDepth - B.N.depth[id] == lev) bld::desc_from_children(id, B.N);
+        __syncthreads();
+    }
     for (int id = t; id < nIds; id += T) bld::number_node(id, B.N, B.ctl);
     __syncthreads();
     for (int id = t; id < nIds; id += T) bld::emit_node(id, B.N, ord, out, indices);
