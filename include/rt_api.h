@@ -241,7 +241,8 @@ int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
  * rt_last_build_ms = device time of the last build. */
 enum { RT_BUILD_DEFAULT = 0u,
        RT_BUILD_NO_WARP_AGGREGATION = 1u << 0,  /* one atomic per shape and bound instead of per warp / block (diagnostic) */
-       RT_BUILD_NO_SINGLE_BLOCK = 1u << 1,      /* scenes of <= 2048 shapes also take the one-launch-per-phase path (diagnostic) */
+       RT_BUILD_NO_SINGLE_BLOCK = 1u << 1,      /* scenes of <= 2048 shapes do not take the single-block path (diagnostic) */
+       RT_BUILD_NO_CLUSTER = 1u << 3,           /* scenes of <= 28000 shapes do not take the single-cluster path (diagnostic) */
        /* K9: lay the built tree out ON THE DEVICE (threaded list A, primitive slots, ranks straight from the builder's
         * tables): no host layout build and no copy of the tree to the host (rt_get_bvh fetches it on demand).  Applies
         * when the tree has no leaf of more than 16 shapes (such leaves are walked as they are; the host layout would expand

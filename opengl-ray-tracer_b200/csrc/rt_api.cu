@@ -176,6 +176,7 @@ struct rt_ctx {
     int lptItems = -1;                // item count the recorded costs belong to (-1: none yet)
     unsigned lptFrame = 0;            // frames rendered with these costs (parity = slot of the control block)
     int gridBlocks[6] = {0, 0, 0, 0, 0, 0}; // persistent grid per kernel variant
+    bool noCluster = false;           // a cluster launch of the builder failed on this device once
     int shardRank = 0, shardWorld = 1;
 };
 
@@ -1214,11 +1215,31 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
         cudaStream_t st = c->stream;
         for (auto& e : c->evBuild) if (!e) CU(c, cudaEventCreate(&e));
         cudaEventRecord(c->evBuild[0], st);
+        bool built = false;
         if (n <= RT_BLD_SMALL_MAX && !(flags & RT_BUILD_NO_SINGLE_BLOCK)) {
             // launch-bound sizes: one block runs the whole build and stops at the first level with nothing pending
             bld_small_kernel<<<1, RT_BLD_SMALL_THREADS, 0, st>>>(B, c->dShapes.p, n, maxDepth, c->bNodes.p, c->bIdx.p);
             c->launches += 1;
-        } else {
+            built = true;
+        } else if (n <= RT_BLD_CLUSTER_MAX && !(flags & RT_BUILD_NO_CLUSTER) && !c->noCluster) {
+            // launch-bound still: ONE CLUSTER of 2 ... 16 blocks runs the whole build, cluster barriers in place of kernel boundaries
+            // (16 blocks: a non-portable cluster size, available on B200; a thread then owns up to two positions)
+            int blocks = 1;
+            while (blocks * RT_BLD_SMALL_THREADS < n && blocks < RT_BLD_CLUSTER_MAX_BLOCKS) blocks *= 2;
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)blocks); cfg.blockDim = dim3(RT_BLD_SMALL_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned)blocks; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            const rt_flat_shape* shp = c->dShapes.p;
+            cudaError_t e = cudaSuccess;
+            if (blocks > 8) e = cudaFuncSetAttribute(bld_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            if (e == cudaSuccess) e = cudaLaunchKernelEx(&cfg, bld_cluster_kernel, B, shp, n, maxDepth, c->bNodes.p, c->bIdx.p);
+            if (e == cudaSuccess) { c->launches += 1; built = true; }
+            else { cudaGetLastError(); c->noCluster = true; }           // this device cannot co-schedule such a cluster: per-phase launches from now on
+        }
+        if (!built) {
             bld_setup_kernel<<<idBlocks, RT_BLD_THREADS, 0, st>>>(B, n, maxDepth);
             bld_init_kernel<<<nBlocks, RT_BLD_THREADS, 0, st>>>(B, c->dShapes.p, n, agg);
             c->launches += 2;

@@ -31,6 +31,9 @@
 // scans and the warp- / block-aggregated form of the box atomics.
 #pragma once
 #include "rt_device.cuh"
+#ifdef __CUDACC__
+#include <cooperative_groups.h>
+#endif
 
 namespace rt {
 namespace bld {
@@ -605,6 +608,96 @@ bld_small_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, i
     for (int id = t; id < nIds; id += T) bld::number_node(id, B.N, B.ctl);
     __syncthreads();
     for (int id = t; id < nIds; id += T) bld::emit_node(id, B.N, ord, out, indices);
+}
+
+// ---- mid-size scenes: the whole build in ONE THREAD-BLOCK CLUSTER ----------------------------------------------
+// Between the single block (<= RT_BLD_SMALL_MAX shapes) and the one-launch-per-phase path lies the range where the latter is
+// launch-bound (car-4122: ~105 launches of 4 - 5 us = 0.52 ms for 1 MB of work).  A cluster of up to 16 blocks of 1024 threads
+// (sm_90+: the blocks of a cluster are co-scheduled and share a hardware barrier) runs the same phases with cluster.sync() —
+// MEMBAR.GPU + the cluster barrier + an L1 invalidate, so the tables in global memory written by one block are what the others
+// read after it — in place of the kernel boundaries: one or two positions per thread, the same per-thread bodies (bld::*), the block
+// scans joined through one word per block, the descendant counts level by level as in bld_small_kernel.
+// Measured on a B200 (tools/ncu_target_build.py, profiles/r2/cluster_build.txt): car-4122 0.536 -> 0.245 ms, 3 k / 6 k / 12 k / 24 k
+// shapes 0.37 / 0.55 / 0.56 / 0.60 -> 0.23 / 0.24 / 0.28 / 0.44 ms; 39 k: 0.60 against 0.49, from there on the per-phase launches win
+// (a thread would own several positions per sweep); up to 2048 shapes the single block wins (monkey 0.156 against 0.17 - 0.19).
+#ifndef RT_BLD_CLUSTER_MAX_BLOCKS
+#define RT_BLD_CLUSTER_MAX_BLOCKS 16
+#endif
+#ifndef RT_BLD_CLUSTER_MAX
+#define RT_BLD_CLUSTER_MAX 28000
+#endif
+
+__global__ void __launch_bounds__(RT_BLD_SMALL_THREADS)
+bld_cluster_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int maxDepth,
+                   rt_flat_node* out, int32_t* indices) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    __shared__ int warpSum[RT_BLD_SMALL_THREADS / 32];
+    const int t = threadIdx.x, T = blockDim.x, lane = t & 31, w = t >> 5;
+    const int rank = (int)cl.block_rank(), C = (int)cl.num_blocks();
+    const int G = C * T, g = rank * T + t;                             // the cluster is the whole grid
+    const int nIds = 2 * n;
+    for (int id = g; id < nIds; id += G) bld::setup_id(id, B.N, B.ctl, n, maxDepth);
+    cl.sync();
+    for (int base = 0; base < n; base += G) {                          // whole warps stay together for the REDUX
+        const int p = base + g;
+        bld::u64 k[6];
+        int node = -1;
+        if (p < n) { bld::init_position(p, shapes, B.R, B.ord[0], B.pnode[0], k); node = 0; }
+        bld_fold_warp(B.N.key, node, k);
+    }
+    cl.sync();
+    const int chunk = (n + G - 1) / G, lo = min(n, g * chunk), hi = min(n, lo + chunk);   // positions [lo, hi) of this thread: usually one
+    int level = 0;
+    for (; level < maxDepth; ++level) {
+        if (!B.ctl->active[level]) break;                              // written before the last cluster barrier: the same for every thread
+        const int cur = level & 1, nxt = cur ^ 1;
+        int mine = 0;
+        for (int p = lo; p < hi; ++p) { const int f = bld::classify(p, B.R, B.ord[cur], B.pnode[cur], B.N); B.flag[p] = (unsigned char)f; mine += f; }
+        int incl = mine;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+        if (lane == 31) warpSum[w] = incl;
+        __syncthreads();
+        if (w == 0) {
+            int v = warpSum[lane];
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, off); if (lane >= off) v += u; }
+            warpSum[lane] = v;                                         // inclusive over the warps of this block
+            if (lane == 31) B.bsum[rank] = v;                          // this block's total, for the blocks after it
+        }
+        cl.sync();
+        int run = (w > 0 ? warpSum[w - 1] : 0) + incl - mine;
+        for (int r = 0; r < rank; ++r) run += B.bsum[r];
+        for (int p = lo; p < hi; ++p) { B.scanL[p] = run; run += (int)B.flag[p]; }
+        if (g == G - 1) B.scanL[n] = run;                              // the last thread's running sum is the grand total
+        cl.sync();
+        for (int base = 0; base < n; base += G) {
+            const int p = base + g;
+            bld::u64 k[6];
+            int node = -1;
+            if (p < n) {
+                int newPos, newNode; bool moved;
+                bld::split_position(p, (int)B.flag[p], level, B.pnode[cur], B.scanL, B.N, B.ctl, newPos, newNode, moved);
+                const int shape = B.ord[cur][p];
+                B.ord[nxt][newPos] = shape;
+                B.pnode[nxt][newPos] = newNode;
+                if (moved) { bld::record_keys(B.R.mn[shape], B.R.mx[shape], (unsigned)newPos, k); node = newNode; }
+            }
+            bld_fold_warp(B.N.key, node, k);
+        }
+        if (g == 0) B.ctl->parity = nxt;
+        cl.sync();
+    }
+    const int* ord = B.ord[B.ctl->parity];
+    for (int lev = level; lev >= 0; --lev) {                            // descendant counts, deepest level first
+        for (int id = g; id < nIds; id += G)
+            if (B.N.left[id] != RT_BLD_ABSENT && maxDepth - B.N.depth[id] == lev) bld::desc_from_children(id, B.N);
+        cl.sync();
+    }
+    for (int id = g; id < nIds; id += G) bld::number_node(id, B.N, B.ctl);
+    cl.sync();
+    for (int id = g; id < nIds; id += G) bld::emit_node(id, B.N, ord, out, indices);
 }
 #endif  // __CUDACC__
 

@@ -10,15 +10,18 @@ from util import bit_fuzzed_shapes, random_shapes
 pytestmark = pytest.mark.gpu
 
 NO_AGG = 1      # RT_BUILD_NO_WARP_AGGREGATION
-NO_SINGLE = 2   # RT_BUILD_NO_SINGLE_BLOCK: small scenes also take the one-launch-per-phase path
-PATHS = [0, NO_SINGLE, NO_SINGLE | NO_AGG]
+NO_SINGLE = 2   # RT_BUILD_NO_SINGLE_BLOCK: scenes of <= 2048 shapes do not take the single-block path
+NO_CLUSTER = 8  # RT_BUILD_NO_CLUSTER: scenes of <= 8192 shapes do not take the single-cluster path
+# default (single block / cluster / per-phase launches by size), cluster where it fits, per-phase launches, ... without aggregation
+PATHS = [0, NO_SINGLE, NO_SINGLE | NO_CLUSTER, NO_SINGLE | NO_CLUSTER | NO_AGG]
 
 
 def _same_frame(a, b):
     return np.array_equal(a[1], b[1]) and np.array_equal(a[0].view(np.uint32), b[0].view(np.uint32))
 
 
-@pytest.mark.parametrize("name,n,depth", [("toy", 0, 15), ("monkey", 0, 15), ("car", 0, 25), ("soup", 60000, 40), ("monkey", 0, 2)])
+@pytest.mark.parametrize("name,n,depth", [("toy", 0, 15), ("monkey", 0, 15), ("car", 0, 25), ("soup", 60000, 40), ("monkey", 0, 2),
+                                          ("soup", 9000, 40), ("soup", 20000, 40), ("soup", 27000, 40)])   # clusters of 16 blocks, 1 - 2 positions per thread
 @pytest.mark.parametrize("flags", PATHS)
 def test_device_tree_is_the_host_tree(rt, name, n, depth, flags):
     W, H = 200, 150
