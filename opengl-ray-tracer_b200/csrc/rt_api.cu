@@ -23,6 +23,10 @@
 
 using namespace rt;
 
+#ifndef RT_TOP_TREE_RETRY_EVERY
+#define RT_TOP_TREE_RETRY_EVERY 64           // a rejected list B is tried again after this many topology changes
+#endif
+
 namespace {
 
 template <class T>
@@ -177,6 +181,7 @@ struct rt_ctx {
     unsigned lptFrame = 0;            // frames rendered with these costs (parity = slot of the control block)
     int gridBlocks[6] = {0, 0, 0, 0, 0, 0}; // persistent grid per kernel variant
     bool noCluster = false;           // a cluster launch of the builder failed on this device once
+    int topSkipsLeft = 0, topRejectedNodes = 0;   // list B was not worth using for a tree of that many nodes: not tried again for a while
     int shardRank = 0, shardWorld = 1;
 };
 
@@ -267,7 +272,17 @@ int build_visit_order(rt_ctx* c) {
     if (!rtl::build_layout(c->hNodes.p, c->nNodes, c->indices.data(), c->indices.size(), c->hShapes.p, c->nShapes,
                            subtrees, (double)c->omax, L))
         return fail(c, RT_ERR_SCENE, L.error ? L.error : "malformed BVH");
-    if (subtrees && !(c->flags & RT_FLAG_NO_TOP_TREE)) rtl::build_top(L, c->hNodes.p, c->nNodes);
+    // List B's tree is tried again only now and then for a context whose last tree of about this size was not worth using
+    // (monkey: 0.5 ms of host time per topology change for a list that the SAH estimate rejects every time).  Building it on a
+    // second thread beside build_layout was measured too (std::async; the tree depends on the reference leaves only): no gain on
+    // the bench box (car cold upload 2.06 -> 2.22 ms), not kept.
+    bool wantTop = subtrees && !(c->flags & RT_FLAG_NO_TOP_TREE);
+    if (wantTop && c->topSkipsLeft > 0 && std::abs(c->nNodes - c->topRejectedNodes) * 8 <= c->topRejectedNodes) { --c->topSkipsLeft; wantTop = false; }
+    if (wantTop) {
+        rtl::build_top(L, c->hNodes.p, c->nNodes);
+        if (L.useB) c->topSkipsLeft = 0;
+        else { c->topRejectedNodes = c->nNodes; c->topSkipsLeft = RT_TOP_TREE_RETRY_EVERY - 1; }
+    }
     const int m = L.nodes(), prims = L.prims();
     c->nSub = (int)L.subBox.size();
     c->nDfsB = L.useB ? (int)L.srcB.size() : 0;
