@@ -138,6 +138,31 @@ def cpu_sample_plan(rt, O, sc, params, W, H, budget_s, threads):
 _RAYS_CACHE = {}
 
 
+SCENE_BVH_DEPTH = {"monkey": 15, "car": 25, "soup": 40, "triangle": 15, "toy": 8}    # buildBVH's argument per scene (host/rt_host.cpp, main.cpp:712, :800)
+
+
+class _SceneView:
+    """The scene bytes of the reference arm / the CPU baseline: shapes, light and camera of the synthetic scene, the BVH as
+    UPSTREAM's own buildBVH + serializeBVH (cut out of src/main.cpp, oracle/_ref/libref_bvh.so) builds it when that library
+    travelled with the snapshot — checked to be the byte-identical tree the library under test is given."""
+
+    def __init__(self, rt, O, sc, name):
+        self.light, self.camera, self.shapes = sc.light, sc.camera, sc.shapes
+        self.nodes, self.indices = sc.nodes, sc.indices
+        self.bvh = {"builder": "host/rt_host.cpp (pinned to upstream by tests/test_ref_builder.py)"}
+        try:
+            if O.refbvh_lib() is not None and name in SCENE_BVH_DEPTH and len(sc.shapes) <= 200000:
+                nodes, idx = O.RefScene(sc.shapes, node_dtype=rt.NODE_DTYPE).build(SCENE_BVH_DEPTH[name])
+                mine = np.asarray(sc.nodes)
+                same = (len(nodes) == len(mine) and np.array_equal(idx, sc.indices) and
+                        all(np.array_equal(nodes[f].view(np.uint32), mine[f].view(np.uint32)) for f in rt.NODE_DTYPE.names))
+                self.nodes, self.indices = nodes, idx
+                self.bvh = {"builder": "upstream buildBVH + serializeBVH compiled in place (oracle/_ref/libref_bvh.so)",
+                            "every_field_identical_to_the_tree_given_to_the_library": bool(same)}   # (upstream leaves FlatNode's padding unset)
+        except Exception as e:      # the baseline must not depend on it
+            self.bvh["upstream_builder_error"] = repr(e)
+
+
 def cpu_render_timed(O, sc, params, W, H, threads, step, phase, use_ref):
     """Time one sample frame on the host cores; returns (seconds, rays in the sampled rows)."""
     args = (sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, params, W, H)
@@ -152,10 +177,11 @@ def cpu_render_timed(O, sc, params, W, H, threads, step, phase, use_ref):
     return time.perf_counter() - t0, _RAYS_CACHE[key]
 
 
-def cpu_baseline(rt, sc, params, W, H, budget_s, repeats=1):
+def cpu_baseline(rt, sc, params, W, H, budget_s, repeats=1, scene_name=None):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_py as O
     O.build()
+    sc = _SceneView(rt, O, sc, scene_name)
     threads = os.cpu_count() or 1
     use_ref = O.ref_lib() is not None
     step, phase = cpu_sample_plan(rt, O, sc, params, W, H, budget_s, threads)
@@ -169,7 +195,7 @@ def cpu_baseline(rt, sc, params, W, H, budget_s, repeats=1):
             "sample": "rows y%%%d==%d (%d of %d rows, %d rays) of the %dx%d frame, %.2f s, %s" %
                       (step, phase, rows, H, rays, W, H, best,
                        "reference gpu_shader.comp compiled as C++ (oracle/_ref)" if use_ref else "oracle port (oracle_rt.cpp)"),
-            "ms_per_frame_extrapolated": best * 1e3 * H / rows}, (step, phase, use_ref, threads)
+            "ms_per_frame_extrapolated": best * 1e3 * H / rows, "bvh": sc.bvh}, (step, phase, use_ref, threads)
 
 
 def run_reference_arm(args):
@@ -185,7 +211,7 @@ def run_reference_arm(args):
     import oracle_py as O
     O.build()
     W, H = args.width, args.height
-    sc = rt.Scene(args.scene, W, H)
+    sc = _SceneView(rt, O, rt.Scene(args.scene, W, H), args.scene)
     params = rt.make_params(W, H, maxBounces=args.bounces, useFresnel=bool(args.fresnel), useMollerTrumbore=bool(args.mt))
     threads = os.cpu_count() or 1
     use_ref = O.ref_lib() is not None
@@ -207,7 +233,7 @@ def run_reference_arm(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, sample=sample),
-        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample, "bvh": sc.bvh},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "fps_extrapolated": 1e3 / (ms * H / rows),
         "note": "reference GLSL through llvmpipe/GL: unavailable on this box; this is the shader's arithmetic on the host cores",
@@ -955,7 +981,7 @@ def main():
             "extra": extra,
         }
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"], _ = cpu_baseline(rt, sc, params, W, H, args.cpu_seconds)
+            line["cpu_baseline"], _ = cpu_baseline(rt, sc, params, W, H, args.cpu_seconds, scene_name=args.scene)
         print(json.dumps(line))
     tr.close()
     if world > 1:
