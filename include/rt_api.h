@@ -237,13 +237,15 @@ int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
  * becomes the context's BVH as if it had been passed to rt_upload_scene (the threaded layout follows at the
  * next render; an unchanged topology keeps it and only refits).  maxDepth = buildBVH's argument (15 / 25 in
  * the reference scenes), at most 64 (the shader's stack).  By size the build runs in one thread block (<= 2048 shapes), in one
- * thread-block cluster of up to 16 blocks (<= 28000) or as one launch per phase and level; the tree is the same on every path.
+ * thread-block cluster of up to 16 blocks (<= 28000), in one cooperative launch of a block per SM (<= 120000) or as one launch per
+ * phase and level; the tree is the same on every path.
  * Shapes of unknown type and infinite planes get no
  * bounds, as upstream.  rt_get_bvh copies the context's current nodes / indices out (either may be NULL);
  * rt_last_build_ms = device time of the last build. */
 enum { RT_BUILD_DEFAULT = 0u,
        RT_BUILD_NO_WARP_AGGREGATION = 1u << 0,  /* one atomic per shape and bound instead of per warp / block (diagnostic) */
        RT_BUILD_NO_SINGLE_BLOCK = 1u << 1,      /* scenes of <= 2048 shapes do not take the single-block path (diagnostic) */
+       RT_BUILD_NO_COOPERATIVE = 1u << 4,       /* scenes of <= 120000 shapes do not take the single cooperative launch (diagnostic) */
        RT_BUILD_NO_CLUSTER = 1u << 3,           /* scenes of <= 28000 shapes do not take the single-cluster path (diagnostic) */
        /* K9: lay the built tree out ON THE DEVICE (threaded list A, primitive slots, ranks straight from the builder's
         * tables): no host layout build and no copy of the tree to the host (rt_get_bvh fetches it on demand).  Applies

@@ -181,6 +181,8 @@ struct rt_ctx {
     unsigned lptFrame = 0;            // frames rendered with these costs (parity = slot of the control block)
     int gridBlocks[6] = {0, 0, 0, 0, 0, 0}; // persistent grid per kernel variant
     bool noCluster = false;           // a cluster launch of the builder failed on this device once
+    bool noCooperative = false;       // ... a cooperative launch
+    int bldGridBlocks = 0;            // blocks of bld_grid_kernel that are resident at once
     int topSkipsLeft = 0, topRejectedNodes = 0;   // list B was not worth using for a tree of that many nodes: not tried again for a while
     int shardRank = 0, shardWorld = 1;
 };
@@ -1253,6 +1255,27 @@ int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* 
             if (e == cudaSuccess) e = cudaLaunchKernelEx(&cfg, bld_cluster_kernel, B, shp, n, maxDepth, c->bNodes.p, c->bIdx.p);
             if (e == cudaSuccess) { c->launches += 1; built = true; }
             else { cudaGetLastError(); c->noCluster = true; }           // this device cannot co-schedule such a cluster: per-phase launches from now on
+        }
+        if (!built && !(flags & RT_BUILD_NO_COOPERATIVE) && !c->noCooperative && n > RT_BLD_SMALL_MAX && n <= RT_BLD_GRID_MAX) {
+            // up to ~120 k shapes the launches still weigh: ONE cooperative launch, a block per SM, grid barriers in place of the kernel boundaries
+            if (c->bldGridBlocks == 0) {
+                int perSM = 0, coop = 0;
+                cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
+                if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, bld_grid_kernel, RT_BLD_SMALL_THREADS, 0) == cudaSuccess && perSM > 0)
+                    c->bldGridBlocks = c->smCount * perSM;
+                else { cudaGetLastError(); c->noCooperative = true; }
+            }
+            if (!c->noCooperative) {
+                int blocks = (n + RT_BLD_SMALL_THREADS - 1) / RT_BLD_SMALL_THREADS;
+                if (blocks > c->bldGridBlocks) blocks = c->bldGridBlocks;
+                const rt_flat_shape* shp = c->dShapes.p;
+                rt_flat_node* outN = c->bNodes.p; int32_t* outI = c->bIdx.p;
+                int nn = n, md = maxDepth;
+                void* args[] = {&B, &shp, &nn, &md, &outN, &outI};
+                const cudaError_t e = cudaLaunchCooperativeKernel((const void*)bld_grid_kernel, dim3((unsigned)blocks), dim3(RT_BLD_SMALL_THREADS), args, 0, st);
+                if (e == cudaSuccess) { c->launches += 1; built = true; }
+                else { cudaGetLastError(); c->noCooperative = true; }
+            }
         }
         if (!built) {
             bld_setup_kernel<<<idBlocks, RT_BLD_THREADS, 0, st>>>(B, n, maxDepth);

@@ -699,6 +699,109 @@ bld_cluster_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n,
     cl.sync();
     for (int id = g; id < nIds; id += G) bld::emit_node(id, B.N, ord, out, indices);
 }
+
+// ---- large scenes: the whole build in ONE COOPERATIVE GRID ------------------------------------------------------
+// Beyond the cluster's reach the per-phase path pays ~100 launches too (soup-1M: 26 levels x 4 launches of 4 - 5 us = 0.5 of
+// its 2.5 ms; 100 k shapes: 0.7 ms, mostly launches).  One block of 1024 threads per SM, launched cooperatively, runs the same
+// phases with grid.sync() (block barrier + MEMBAR.GPU + an atomic barrier word + L1 invalidate) where the kernel boundaries
+// were.  Every block owns a CONTIGUOUS range of positions for the classify / scan phase and sweeps it in tiles of 1024
+// (coalesced, a block scan per tile with a running carry); the block totals are joined by one warp per block; the move / fold
+// sweep is strided over the whole grid as in the other paths.  Same per-thread bodies (bld::*), same tree.
+// Measured (profiles/r2/cluster_build.txt): 60 k shapes 0.65 -> 0.53 ms, 100 k 0.73 -> 0.59 ms; at 300 k the per-phase launches are
+// ahead again (0.93 against 1.12 ms, soup-1M 2.5 against 3.7: 1024-thread blocks, one per SM, hide less latency than the
+// per-phase kernels' 256-thread blocks at full occupancy), so the cooperative launch is taken up to RT_BLD_GRID_MAX shapes.
+#ifndef RT_BLD_GRID_MAX
+#define RT_BLD_GRID_MAX 120000
+#endif
+__global__ void __launch_bounds__(RT_BLD_SMALL_THREADS)
+bld_grid_kernel(BuildBufs B, const rt_flat_shape* __restrict__ shapes, int n, int maxDepth,
+                rt_flat_node* out, int32_t* indices) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ int warpSum[RT_BLD_SMALL_THREADS / 32];
+    __shared__ int blockBase;
+    const int t = threadIdx.x, T = blockDim.x, lane = t & 31, w = t >> 5;
+    const int rank = (int)blockIdx.x, C = (int)gridDim.x;
+    const int G = C * T, g = rank * T + t;
+    const int nIds = 2 * n;
+    for (int id = g; id < nIds; id += G) bld::setup_id(id, B.N, B.ctl, n, maxDepth);
+    grid.sync();
+    for (int base = 0; base < n; base += G) {                          // whole warps stay together for the REDUX
+        const int p = base + g;
+        bld::u64 k[6];
+        int node = -1;
+        if (p < n) { bld::init_position(p, shapes, B.R, B.ord[0], B.pnode[0], k); node = 0; }
+        bld_fold_warp(B.N.key, node, k);
+    }
+    grid.sync();
+    const int per = (((n + C - 1) / C) + T - 1) / T * T;               // positions per block, a whole number of tiles
+    const int r0 = min(n, rank * per), r1 = min(n, r0 + per);
+    int level = 0;
+    for (; level < maxDepth; ++level) {
+        if (!B.ctl->active[level]) break;                              // written before the last grid barrier: the same for every thread
+        const int cur = level & 1, nxt = cur ^ 1;
+        int carry = 0;                                                 // flags set in this block's range before the current tile
+        for (int tile = r0; tile < r1; tile += T) {
+            const int p = tile + t;
+            int f = 0;
+            if (p < r1) { f = bld::classify(p, B.R, B.ord[cur], B.pnode[cur], B.N); B.flag[p] = (unsigned char)f; }
+            int incl = f;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+            if (lane == 31) warpSum[w] = incl;
+            __syncthreads();
+            if (w == 0) {
+                int v = warpSum[lane];
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, off); if (lane >= off) v += u; }
+                warpSum[lane] = v;
+            }
+            __syncthreads();
+            if (p < r1) B.scanL[p] = carry + (w > 0 ? warpSum[w - 1] : 0) + incl - f;   // exclusive within the block's range
+            carry += warpSum[31];
+            __syncthreads();                                           // warpSum is reused by the next tile
+        }
+        if (t == 0) B.bsum[rank] = carry;
+        grid.sync();
+        if (w == 0) {                                                  // flags set in the blocks before this one
+            int s = 0;
+            for (int i = lane; i < rank; i += 32) s += B.bsum[i];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+            if (lane == 0) blockBase = s;
+        }
+        __syncthreads();
+        const int base = blockBase;
+        for (int p = r0 + t; p < r1; p += T) B.scanL[p] += base;
+        if (rank == C - 1 && t == 0) B.scanL[n] = base + carry;        // the grand total
+        grid.sync();
+        for (int b0 = 0; b0 < n; b0 += G) {
+            const int p = b0 + g;
+            bld::u64 k[6];
+            int node = -1;
+            if (p < n) {
+                int newPos, newNode; bool moved;
+                bld::split_position(p, (int)B.flag[p], level, B.pnode[cur], B.scanL, B.N, B.ctl, newPos, newNode, moved);
+                const int shape = B.ord[cur][p];
+                B.ord[nxt][newPos] = shape;
+                B.pnode[nxt][newPos] = newNode;
+                if (moved) { bld::record_keys(B.R.mn[shape], B.R.mx[shape], (unsigned)newPos, k); node = newNode; }
+            }
+            bld_fold_warp(B.N.key, node, k);
+        }
+        if (g == 0) B.ctl->parity = nxt;
+        grid.sync();
+    }
+    const int* ord = B.ord[B.ctl->parity];
+    for (int lev = level; lev >= 0; --lev) {                            // descendant counts, deepest level first
+        for (int id = g; id < nIds; id += G)
+            if (B.N.left[id] != RT_BLD_ABSENT && maxDepth - B.N.depth[id] == lev) bld::desc_from_children(id, B.N);
+        grid.sync();
+    }
+    for (int id = g; id < nIds; id += G) bld::number_node(id, B.N, B.ctl);
+    grid.sync();
+    for (int id = g; id < nIds; id += G) bld::emit_node(id, B.N, ord, out, indices);
+}
 #endif  // __CUDACC__
 
 

@@ -11,9 +11,11 @@ pytestmark = pytest.mark.gpu
 
 NO_AGG = 1      # RT_BUILD_NO_WARP_AGGREGATION
 NO_SINGLE = 2   # RT_BUILD_NO_SINGLE_BLOCK: scenes of <= 2048 shapes do not take the single-block path
-NO_CLUSTER = 8  # RT_BUILD_NO_CLUSTER: scenes of <= 8192 shapes do not take the single-cluster path
-# default (single block / cluster / per-phase launches by size), cluster where it fits, per-phase launches, ... without aggregation
-PATHS = [0, NO_SINGLE, NO_SINGLE | NO_CLUSTER, NO_SINGLE | NO_CLUSTER | NO_AGG]
+NO_CLUSTER = 8  # RT_BUILD_NO_CLUSTER: scenes of <= 28000 shapes do not take the single-cluster path
+NO_COOP = 16    # RT_BUILD_NO_COOPERATIVE: scenes of <= 120000 shapes do not take the single cooperative launch
+# default (single block / cluster / cooperative grid / per-phase by size), cluster where it fits, cooperative grid (2049 .. 120000 shapes), per-phase
+# launches, per-phase launches without aggregation
+PATHS = [0, NO_SINGLE, NO_SINGLE | NO_CLUSTER, NO_SINGLE | NO_CLUSTER | NO_COOP, NO_SINGLE | NO_CLUSTER | NO_COOP | NO_AGG]
 
 
 def _same_frame(a, b):
@@ -21,7 +23,7 @@ def _same_frame(a, b):
 
 
 @pytest.mark.parametrize("name,n,depth", [("toy", 0, 15), ("monkey", 0, 15), ("car", 0, 25), ("soup", 60000, 40), ("monkey", 0, 2),
-                                          ("soup", 9000, 40), ("soup", 20000, 40), ("soup", 27000, 40)])   # clusters of 16 blocks, 1 - 2 positions per thread
+                                          ("soup", 9000, 40), ("soup", 20000, 40), ("soup", 27000, 40), ("soup", 110000, 40)])   # clusters of 16 blocks, 1 - 2 positions per thread
 @pytest.mark.parametrize("flags", PATHS)
 def test_device_tree_is_the_host_tree(rt, name, n, depth, flags):
     W, H = 200, 150
@@ -57,7 +59,7 @@ def test_rebuild_per_frame_equals_host_rebuild(rt, name, depth):
         sc.animate(t, dt, mode=1)
         a.upload_scene(None, None, sc.shapes, sc.nodes, sc.indices)
         b.animate(t, dt)
-        nodes, idx = b.build_bvh(depth, PATHS[frame % 3])
+        nodes, idx = b.build_bvh(depth, PATHS[frame % len(PATHS)])
         assert nodes.tobytes() == np.ascontiguousarray(sc.nodes).tobytes(), "nodes, frame %d" % frame
         assert idx.tobytes() == np.ascontiguousarray(sc.indices).tobytes(), "indices, frame %d" % frame
         assert _same_frame(a.render(p), b.render(p)), "frame %d" % frame
