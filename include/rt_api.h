@@ -71,6 +71,10 @@ enum {
      * cost and the next frame claims the blocks that were slow first (frame-to-frame coherence), so
      * the long dependent walks of incoherent bounce packets overlap the bulk instead of forming the tail. */
     RT_FLAG_NO_HEAVY_FIRST = 1u << 3,
+    /* Diagnostic: start the host copy of a pipelined frame (rt_render_async) as soon as its render kernel has finished.  By
+     * default the copy of a single-launch frame starts when the NEXT frame's render kernel is launched, or when somebody waits
+     * for the frame, whichever is first: the small launches that open an animated frame run slower under a device-to-host DMA. */
+    RT_FLAG_NO_DEFERRED_COPY = 1u << 4,
     /* Record per-pixel primary-hit shape ids (an AOV the reference lacks;
      * needed by the parity criterion).  Off = the id buffer is not written. */
     RT_FLAG_HIT_IDS   = 1u << 1
@@ -135,7 +139,9 @@ int rt_render(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* h
 /* rt_render without the final wait: the frame lands in host_rgba (pinned memory for a truly
  * asynchronous copy) once rt_synchronize(ctx) returns.  Lets the host prepare the next frame's
  * scene update (main.cpp:438-457 animation step) while this one renders and copies.
- * Frames are pipelined over two device images: the copy of frame i overlaps the render of frame i+1.
+ * Frames are pipelined over two device images: the copy of frame i overlaps the render of frame i+1 (for a frame of one
+ * launch it is issued together with that render kernel, or by the first rt_wait_frames / rt_synchronize / rt_render* call
+ * that needs it, so a frame nobody follows up on or waits for stays on the device).
  * rt_wait_frames(ctx, n) blocks until at most n of the issued frames are still in flight (n = 1: the
  * older one is complete and its host buffer may be read / reused; n = 0: all of them). */
 int rt_render_async(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* host_hit_ids);

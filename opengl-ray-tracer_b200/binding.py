@@ -33,6 +33,7 @@ RT_FLAG_REFERENCE_WALK = 1
 RT_FLAG_HIT_IDS = 2
 RT_FLAG_NO_TOP_TREE = 4
 RT_FLAG_NO_HEAVY_FIRST = 8
+RT_FLAG_NO_DEFERRED_COPY = 16
 RT_BUILD_DEVICE_LAYOUT = 4
 TILE_W, TILE_H = 32, 8
 

@@ -28,8 +28,14 @@ enum { RT_ANIM_BOUNCE = 0, RT_ANIM_ROTATE_Z = 1 };
 struct AnimEntry { int kind; float m[12]; };
 struct AnimItem  { int shape; int entry; };
 
-__global__ void anim_kernel(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
-                            const AnimEntry* __restrict__ entries) {
+// Up to RT_ANIM_PACK entries travel as a kernel PARAMETER: a frame of the animated loop then issues no copy-engine
+// operation at all (a small H2D copy or memset in the render stream queues behind the previous frame's 7.7 MB D2H copy
+// on the copy engines of this box, and the whole next frame with it; see DESIGN: the pipelined monkey loop).
+#define RT_ANIM_PACK 8
+struct AnimPack { AnimEntry e[RT_ANIM_PACK]; };
+
+__device__ __forceinline__ void anim_body(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
+                                          const AnimEntry* __restrict__ entries) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nItems) return;
     const AnimItem it = items[i];
@@ -48,6 +54,14 @@ __global__ void anim_kernel(rt_flat_shape* __restrict__ shapes, const AnimItem* 
             for (int r = 0; r < 3; ++r) P[v][r] = (e.m[r] * x + e.m[3 + r] * y) + (e.m[6 + r] * z + e.m[9 + r] * 1.0f);
         }
     }
+}
+__global__ void anim_kernel(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
+                            const AnimEntry* __restrict__ entries) {
+    anim_body(shapes, items, nItems, entries);
+}
+__global__ void anim_kernel_packed(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
+                                   const __grid_constant__ AnimPack pack) {
+    anim_body(shapes, items, nItems, pack.e);
 }
 
 struct GBox { float mn[3], mx[3]; };
@@ -90,7 +104,8 @@ __device__ __forceinline__ void g_store(rt_flat_node* n, const GBox& b) {
     __stcg(p + 4, b.mx[0]); __stcg(p + 5, b.mx[1]); __stcg(p + 6, b.mx[2]);
 }
 
-// leaves[i]: raw index of leaf i; parent[n]: raw index of n's parent (-1 at the root); arrived: zeroed counters
+// leaves[i]: raw index of leaf i; parent[n]: raw index of n's parent (-1 at the root); arrived: counters that are zero at
+// launch and zero again at the end (the second arrival resets its counter: no memset per frame)
 __global__ void grow_kernel(rt_flat_node* __restrict__ nodes, const rt_flat_shape* __restrict__ shapes,
                             const int* __restrict__ indices, const unsigned char* __restrict__ animated,
                             const int* __restrict__ leaves, int nLeaves, const int* __restrict__ parent,
@@ -111,6 +126,7 @@ __global__ void grow_kernel(rt_flat_node* __restrict__ nodes, const rt_flat_shap
     for (int j = parent[n]; j >= 0; j = parent[j]) {
         __threadfence();
         if (atomicAdd(arrived + j, 1u) == 0u) return;
+        arrived[j] = 0u;                           // both children are here: nobody touches this counter again in this launch
         __threadfence();
         GBox b = g_load(nodes + j);
         const GBox l = g_load(nodes + nodes[j].leftChild), r = g_load(nodes + nodes[j].rightChild);

@@ -110,7 +110,10 @@ struct rt_ctx {
     PinBuf<int> hRf; DevBuf<int> dRf;           // [child 2nE | leaf 2nE | parent nE | start nStart]
     DevBuf<unsigned> dRfArrived;                // nE counters + 1 "degraded" flag
     int nRfStart = 0;
-    int* hRfDegraded = nullptr;                 // pinned: lazily read back flag of the last refit
+    // Flag of the device refit (a primitive could not be bounded any more), in MAPPED pinned memory: K4 stores into it directly.
+    // (It used to be a 4-byte D2H copy in the render stream: that copy queued on the D2H engine behind the previous frame's
+    // 7.7 MB copy on the copy stream and with it the whole next frame did: the pipelined monkey loop ran at 0.36 instead of 0.27 ms.)
+    int* hRfDegraded = nullptr; int* dRfDegraded = nullptr;
     // device-side animation (rt_anim.cuh)
     struct AnimDef { int kind; float originY, amp, freq, cx, cy, cz, speed; };
     std::vector<AnimDef> animDefs; std::vector<AnimItem> animItems;
@@ -160,6 +163,13 @@ struct rt_ctx {
     cudaEvent_t evFrame[2] = {nullptr, nullptr};
     bool framePending[2] = {false, false};
     int imgPar = 0;                   // image the next pipelined frame renders into
+    // The D2H copy of a pipelined single-launch frame is DEFERRED until the next frame's render kernel is about to be launched
+    // (or until somebody waits for the frame): while a 7.7 MB DMA to the host is in flight every dependent kernel launch of the
+    // stream takes ~8 us longer on this box (measured with six empty kernels per frame: 0.192 -> 0.239 ms), and an animated frame
+    // begins with five to seven small launches (K6, K7, K4, K2 ...): the copy now runs beside the long render kernel only.
+    struct DeferredCopy { bool valid = false; float* hostRgba = nullptr; const float* devRgba = nullptr; int32_t* hostIds = nullptr;
+                          const int32_t* devIds = nullptr; size_t pixels = 0; int par = 0; } deferred;
+    cudaEvent_t evDefer = nullptr;
     float4* lastImage = nullptr;
     DevBuf<float4> frame;             // full W*H frame other ranks write into (rt_frame_export)
     float* frameTarget = nullptr;     // where this rank's tiles go row-major (local frame, peer mapping, or caller's)
@@ -214,6 +224,21 @@ inline int64_t out_pixels(const rt_ctx* c) {
 // the host overwrites them (lets the next frame's update overlap the previous render).
 inline void wait_copies(rt_ctx* c) {
     if (c->copyPending) { cudaEventSynchronize(c->copyDone); c->copyPending = false; }
+}
+// Issue the deferred D2H copy of the last pipelined frame (rt_ctx::deferred).  The copy stream already waits for that frame's
+// render kernel; `afterStream` makes it wait for what the context stream holds so far as well (the small launches that open
+// the next frame), the callers that are about to wait for the frame pass false.
+int flush_deferred(rt_ctx* c, bool afterStream) {
+    if (!c->deferred.valid) return RT_OK;
+    rt_ctx::DeferredCopy& d = c->deferred;
+    d.valid = false;
+    if (afterStream) { cudaEventRecord(c->evDefer, c->stream); cudaStreamWaitEvent(c->copyStream, c->evDefer, 0); }
+    cudaEventRecord(c->ev[6], c->copyStream);
+    if (d.hostRgba) CU(c, cudaMemcpyAsync(d.hostRgba, d.devRgba, d.pixels * sizeof(float4), cudaMemcpyDeviceToHost, c->copyStream));
+    if (d.hostIds) CU(c, cudaMemcpyAsync(d.hostIds, d.devIds, d.pixels * sizeof(int), cudaMemcpyDeviceToHost, c->copyStream));
+    cudaEventRecord(c->ev[7], c->copyStream); c->timed[3] = true;
+    cudaEventRecord(c->evFrame[d.par], c->copyStream);
+    return RT_OK;
 }
 
 // Build the threaded layout (rt_layout.h): reference nodes in the reference's visit order (root =
@@ -411,6 +436,7 @@ int flush_scene(rt_ctx* c) {
         if (c->nSub > 0) {
             CU(c, c->dRf.reserve((size_t)c->nSub * 5 + (size_t)c->nRfStart));
             CU(c, c->dRfArrived.reserve((size_t)c->nSub + 1));
+            CU(c, cudaMemsetAsync(c->dRfArrived.p, 0, ((size_t)c->nSub + 1) * sizeof(unsigned), c->stream));   // once per topology: K4 leaves them zero
             CU(c, cudaMemcpyAsync(c->dRf.p, c->hRf.p, ((size_t)c->nSub * 5 + (size_t)c->nRfStart) * sizeof(int), cudaMemcpyHostToDevice, c->stream));
         }
         subUpload = true; devRefit = false;       // the layout build computed every box on the host
@@ -425,16 +451,12 @@ int flush_scene(rt_ctx* c) {
     cudaEventRecord(c->ev[2], c->stream);
     if (devRefit && c->nSub > 0 && c->nRfStart > 0) {
         const int nE = c->nSub;
-        CU(c, cudaMemsetAsync(c->dRfArrived.p, 0, ((size_t)nE + 1) * sizeof(unsigned), c->stream));
         refit_kernel<<<(c->nRfStart + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dNodes.p, c->dPshape.p,
             c->dRf.p + 5 * (size_t)nE, c->nRfStart, c->dRf.p + 4 * (size_t)nE, reinterpret_cast<const int2*>(c->dRf.p),
             reinterpret_cast<const int2*>(c->dRf.p + 2 * (size_t)nE), c->dRfArrived.p, c->dSubBox.p, (double)c->omax,
-            reinterpret_cast<int*>(c->dRfArrived.p + nE));
+            c->dRfDegraded);
         c->launches++;
-        if (!c->rfPending) {
-            CU(c, cudaMemcpyAsync(c->hRfDegraded, c->dRfArrived.p + nE, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-            cudaEventRecord(c->rfDone, c->stream); c->rfPending = true;
-        }
+        if (!c->rfPending) { cudaEventRecord(c->rfDone, c->stream); c->rfPending = true; }
         subUpload = true;                          // the node lists take the new boxes below
     }
     if ((c->nodesDirty || c->topoDirty || subUpload || c->devNodesDirty) && c->nDfs > 0) {
@@ -509,14 +531,16 @@ int rt_create(rt_ctx** out, int width, int height, int device, unsigned flags) {
     for (auto& e : c->ev) if (cudaEventCreate(&e) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     if (cudaEventCreateWithFlags(&c->copyDone, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     if (cudaEventCreateWithFlags(&c->rfDone, cudaEventDisableTiming) != cudaSuccess ||
-        cudaMallocHost(&c->hRfDegraded, sizeof(int)) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+        cudaHostAlloc(&c->hRfDegraded, sizeof(int), cudaHostAllocMapped) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     *c->hRfDegraded = 0;
+    if (cudaHostGetDevicePointer(&c->dRfDegraded, c->hRfDegraded, 0) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     cudaDeviceGetAttribute(&c->smCount, cudaDevAttrMultiProcessorCount, device);
     c->ownStream = c->stream;
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     for (auto& e : c->evBand) if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     for (auto& e : c->evFrame) if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
+    if (cudaEventCreateWithFlags(&c->evDefer, cudaEventDisableTiming) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     *out = c;
     return RT_OK;
 }
@@ -551,6 +575,7 @@ void rt_destroy(rt_ctx* c) {
     c->bInt.release(); c->bKey.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release(); c->bRec.release(); c->bHostNodes.release(); c->bHostIdx.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     for (auto& e : c->evFrame) if (e) cudaEventDestroy(e);
+    if (c->evDefer) cudaEventDestroy(c->evDefer);
     c->image2.release(); c->ids2.release();
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
@@ -636,6 +661,7 @@ int rt_update_nodes(rt_ctx* c, const void* nodes, int nNodes) {
 
 int rt_set_shard(rt_ctx* c, int rank, int world) {
     if (!c || world < 1 || rank < 0 || rank >= world) return RT_ERR_ARG;
+    { const int rc = flush_deferred(c, false); if (rc != RT_OK) return rc; }   // its source image may be reallocated for the new shard size
     c->shardRank = rank; c->shardWorld = world; c->lptItems = -1;
     return RT_OK;
 }
@@ -703,6 +729,8 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         c->lastImage = img.p;
     }
     if (ownIds) { DevBuf<int>& idb = par ? c->ids2 : c->ids; CU(c, idb.reserve((size_t)px)); dev_ids = idb.p; }
+    // a frame that is not pipelined, or one that renders into the image of the deferred copy, sends that copy off first
+    if (c->deferred.valid && (!pipeline || c->deferred.par == par)) { rc = flush_deferred(c, false); if (rc != RT_OK) return rc; }
     if ((ownImage || ownIds) && c->framePending[par]) {
         // an earlier pipelined frame's copy may still be reading this image: the kernels below wait for it
         cudaStreamWaitEvent(c->stream, c->evFrame[par], 0);
@@ -795,6 +823,8 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     } else {
         CU(c, cudaMemsetAsync(c->queue.p, 0, RT_MAX_BANDS * sizeof(unsigned int), c->stream));
     }
+    // the previous pipelined frame's copy starts here: after the small launches of this frame, beside its render kernel
+    if (c->deferred.valid) { rc = flush_deferred(c, true); if (rc != RT_OK) return rc; }
     cudaEvent_t evFork = c->evBand[RT_MAX_BANDS], evJoin = c->evBand[RT_MAX_BANDS + 1], evCopied = c->evBand[RT_MAX_BANDS + 2];
     if (nBands > 1 || toHost) {
         cudaEventRecord(evFork, c->stream);
@@ -839,6 +869,13 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
             }
             cudaEventRecord(c->evBand[band], rs);
             cudaStreamWaitEvent(c->copyStream, c->evBand[band], 0);
+            if (pipeline && nBands == 1 && !(c->flags & RT_FLAG_NO_DEFERRED_COPY)) {
+                rt_ctx::DeferredCopy& d = c->deferred;
+                d.valid = true; d.hostRgba = host_rgba ? host_rgba + 4 * p0 : nullptr; d.devRgba = dev_rgba + 4 * p0;
+                d.hostIds = host_ids ? host_ids + p0 : nullptr; d.devIds = host_ids ? dev_ids + p0 : nullptr; d.pixels = p1 - p0; d.par = par;
+                c->framePending[par] = true;             // evFrame[par] is recorded when the copy is issued (flush_deferred)
+                continue;
+            }
             if (firstCopy) { cudaEventRecord(c->ev[6], c->copyStream); firstCopy = false; }
             if (host_rgba) CU(c, cudaMemcpyAsync(host_rgba + 4 * p0, dev_rgba + 4 * p0, (p1 - p0) * sizeof(float4), cudaMemcpyDeviceToHost, c->copyStream));
             if (host_ids) CU(c, cudaMemcpyAsync(host_ids + p0, dev_ids + p0, (p1 - p0) * sizeof(int), cudaMemcpyDeviceToHost, c->copyStream));
@@ -879,6 +916,7 @@ int rt_wait_frames(rt_ctx* c, int max_in_flight) {
     CU(c, cudaSetDevice(c->device));
     // at most two frames are ever in flight (two device images); imgPar is the image of the OLDER one
     const int older = c->imgPar, newer = c->imgPar ^ 1;
+    if (c->deferred.valid && (max_in_flight == 0 || c->deferred.par == older)) { const int rc = flush_deferred(c, false); if (rc != RT_OK) return rc; }
     if (max_in_flight <= 1 && c->framePending[older]) { CU(c, cudaEventSynchronize(c->evFrame[older])); c->framePending[older] = false; }
     if (max_in_flight == 0 && c->framePending[newer]) { CU(c, cudaEventSynchronize(c->evFrame[newer])); c->framePending[newer] = false; }
     return RT_OK;
@@ -1099,6 +1137,7 @@ int upload_anim_tables(rt_ctx* c) {
     std::vector<unsigned char> flag((size_t)nS, 0);
     for (const AnimItem& it : c->animItems) if (it.shape < nS) flag[(size_t)it.shape] = 1;
     CU(c, c->dNodeAux.reserve(aux.size())); CU(c, c->dGrowArrived.reserve((size_t)nN));
+    if (nN > 0) CU(c, cudaMemsetAsync(c->dGrowArrived.p, 0, (size_t)nN * sizeof(unsigned), c->stream));   // once per table upload: K7 leaves them zero
     CU(c, c->dAnimFlag.reserve((size_t)nS)); CU(c, c->dIndices.reserve(c->indices.size()));
     CU(c, c->dAnimItems.reserve(c->animItems.size())); CU(c, c->dAnimEntries.reserve(c->animDefs.size()));
     CU(c, c->hAnimEntries.reserve(c->animDefs.size(), 0));
@@ -1136,10 +1175,12 @@ static int animate_impl(rt_ctx* c, float t, float dt, bool grow) {
     for (const AnimItem& it : c->animItems) if (it.shape >= c->nShapes) return fail(c, RT_ERR_STATE, "animation registered for a shape that is gone");
     if (grow) { if (c->animDirty) { rc = upload_anim_tables(c); if (rc != RT_OK) return rc; } }
     else if (c->animItemsDirty) { rc = upload_anim_items(c); if (rc != RT_OK) return rc; }
-    wait_copies(c);                                // the pinned entry table is the source of an async copy
+    const bool packed = c->animDefs.size() <= RT_ANIM_PACK;      // the frame's entries as a kernel parameter: no copy at all
+    AnimPack pack;
+    if (!packed) wait_copies(c);                   // the pinned entry table is the source of an async copy
     for (size_t e = 0; e < c->animDefs.size(); ++e) {
         const rt_ctx::AnimDef& d = c->animDefs[e];
-        AnimEntry& o = c->hAnimEntries.p[e];
+        AnimEntry& o = packed ? pack.e[e] : c->hAnimEntries.p[e];
         o.kind = d.kind;
         for (float& x : o.m) x = 0.f;
         if (d.kind == RT_ANIM_BOUNCE) { o.m[0] = d.originY + d.amp * std::sin(d.freq * t); }              // main.cpp:1079-1082
@@ -1150,13 +1191,17 @@ static int animate_impl(rt_ctx* c, float t, float dt, bool grow) {
             for (int col = 0; col < 4; ++col) for (int r = 0; r < 3; ++r) o.m[3 * col + r] = m[4 * col + r];
         }
     }
-    CU(c, cudaMemcpyAsync(c->dAnimEntries.p, c->hAnimEntries.p, c->animDefs.size() * sizeof(AnimEntry), cudaMemcpyHostToDevice, c->stream));
-    cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
     const int nI = (int)c->animItems.size();
-    anim_kernel<<<(nI + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, c->dAnimEntries.p);
+    if (packed) {
+        for (size_t e = c->animDefs.size(); e < RT_ANIM_PACK; ++e) { pack.e[e].kind = 0; for (float& x : pack.e[e].m) x = 0.f; }
+        anim_kernel_packed<<<(nI + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, pack);
+    } else {
+        CU(c, cudaMemcpyAsync(c->dAnimEntries.p, c->hAnimEntries.p, c->animDefs.size() * sizeof(AnimEntry), cudaMemcpyHostToDevice, c->stream));
+        cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
+        anim_kernel<<<(nI + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, c->dAnimEntries.p);
+    }
     c->launches++;
     if (grow && c->nNodes > 0 && c->nLeavesRaw > 0) {
-        CU(c, cudaMemsetAsync(c->dGrowArrived.p, 0, (size_t)c->nNodes * sizeof(unsigned), c->stream));
         grow_kernel<<<(c->nLeavesRaw + 127) / 128, 128, 0, c->stream>>>(c->dNodes.p, c->dShapes.p, c->dIndices.p, c->dAnimFlag.p,
             c->dNodeAux.p + c->nNodes, c->nLeavesRaw, c->dNodeAux.p, c->dGrowArrived.p);
         c->launches++;
@@ -1429,6 +1474,7 @@ void* rt_stream(rt_ctx* c) { return c ? (void*)c->stream : nullptr; }
 int rt_set_stream(rt_ctx* c, void* s) {
     if (!c) return RT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
+    { const int rc = flush_deferred(c, false); if (rc != RT_OK) return rc; }
     CU(c, cudaStreamSynchronize(c->stream));
     c->copyPending = false;
     c->stream = s ? static_cast<cudaStream_t>(s) : c->ownStream;
@@ -1436,6 +1482,7 @@ int rt_set_stream(rt_ctx* c, void* s) {
 }
 int rt_synchronize(rt_ctx* c) {
     if (!c) return RT_ERR_ARG;
+    { const int rc = flush_deferred(c, false); if (rc != RT_OK) return rc; }
     CU(c, cudaStreamSynchronize(c->stream));
     if (c->framePending[0] || c->framePending[1]) {       // pipelined frames finish on the copy stream
         CU(c, cudaStreamSynchronize(c->copyStream));
@@ -1447,6 +1494,7 @@ float* rt_device_image(rt_ctx* c) { return c ? reinterpret_cast<float*>(c->lastI
 
 int rt_last_timings(rt_ctx* c, float out_ms[4]) {
     if (!c || !out_ms) return RT_ERR_ARG;
+    { const int rc = flush_deferred(c, false); if (rc != RT_OK) return rc; }
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaStreamSynchronize(c->copyStream));
     for (int i = 0; i < 4; ++i) {

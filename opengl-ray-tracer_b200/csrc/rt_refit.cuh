@@ -55,6 +55,7 @@ __global__ void refit_kernel(const rt_flat_shape* __restrict__ shapes, const rt_
     while (j >= 0) {
         __threadfence();
         if (atomicAdd(arrived + j, 1u) == 0u) return;      // the sibling is not there yet: it will do the union
+        arrived[j] = 0u;                                   // zero again for the next launch (no memset per frame)
         __threadfence();
         const int2 ch = child[j];
         rtl::Box b; b.reset();

@@ -529,6 +529,47 @@ def test_pipelined_async_frames(rt, W, H):
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("flags", [0, "no_deferred"])
+def test_deferred_copy_flush_points(rt, flags):
+    """The host copy of a pipelined single-launch frame is issued with the next frame's render kernel or by whoever waits
+    first (rt_api.h: rt_render_async): every way of ending the pipeline must deliver the frame, ids included."""
+    import torch
+    W, H = 320, 200
+    sc = rt.Scene("monkey", W, H)
+    p = rt.make_params(W, H)
+    fl = rt.RT_FLAG_HIT_IDS | (rt.RT_FLAG_NO_DEFERRED_COPY if flags else 0)
+    a = rt.RayTracer(W, H, flags=fl); a.upload(sc)
+    want, want_ids = a.render(p, want_ids=True)
+    want = want.copy().view(np.uint32).reshape(-1, 4); want_ids = want_ids.copy().ravel()
+    buf = [torch.empty((H * W, 4), dtype=torch.float32, pin_memory=True).numpy() for _ in range(2)]
+    ids = [torch.empty(H * W, dtype=torch.int32, pin_memory=True).numpy() for _ in range(2)]
+    dev = torch.empty((H * W, 4), dtype=torch.float32, device="cuda")
+
+    def clear():
+        for k in range(2):
+            buf[k][:] = -7.0; ids[k][:] = -9
+
+    def check(k):
+        assert np.array_equal(buf[k].view(np.uint32), want), "colours of buffer %d" % k
+        assert np.array_equal(ids[k], want_ids), "ids of buffer %d" % k
+
+    clear(); a.render_async(p, buf[0], ids[0]); a.wait_frames(0); check(0)                       # one frame, waited for
+    clear(); a.render_async(p, buf[0], ids[0]); a.synchronize(); check(0)                        # ended by rt_synchronize
+    clear(); a.render_async(p, buf[0], ids[0]); a.timings(); check(0)                            # ended by rt_last_timings
+    clear(); a.render_async(p, buf[0], ids[0]); a.render_device(p, dev.data_ptr()); a.synchronize(); check(0)   # a device render follows
+    assert np.array_equal(dev.cpu().numpy().view(np.uint32), want)
+    clear(); a.render_async(p, buf[0], ids[0]); r, ri = a.render(p, want_ids=True); check(0)     # a synchronous render follows
+    assert np.array_equal(r.view(np.uint32).reshape(-1, 4), want) and np.array_equal(ri.ravel(), want_ids)
+    clear(); a.render_async(p, buf[0], ids[0]); a.render_async(p, buf[1], ids[1]); a.wait_frames(1); check(0)   # two in flight
+    a.wait_frames(0); check(1)
+    clear()
+    for i in range(5):                                                                           # no wait at all between frames
+        a.render_async(p, buf[i & 1], ids[i & 1])
+    a.wait_frames(0); check(0); check(1)
+    clear(); a.render_async(p, buf[0], ids[0]); a.set_shard(0, 2); a.set_shard(0, 1); a.synchronize(); check(0)  # the shard changes
+    a.close()
+
+
 @pytest.mark.parametrize("mt,fresnel,bounces", [(False, False, 3), (True, True, 3), (False, True, 6)])
 def test_scheduled_frames_identical(rt, mt, fresnel, bounces):
     """From the second frame on a context orders its blocks by last frame's costs, splits the heaviest into lane groups
