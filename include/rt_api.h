@@ -75,6 +75,10 @@ enum {
      * default the copy of a single-launch frame starts when the NEXT frame's render kernel is launched, or when somebody waits
      * for the frame, whichever is first: the small launches that open an animated frame run slower under a device-to-host DMA. */
     RT_FLAG_NO_DEFERRED_COPY = 1u << 4,
+    /* Diagnostic: rt_animate always runs K6 and the general K7 (every leaf climbs the tree) as two launches.  By default, when
+     * the animated leaves and their ancestors are at most 16384 nodes, ONE block moves the shapes and then grows exactly those
+     * nodes level by level (the only ones updateBVH can change, main.cpp:1068-1077). */
+    RT_FLAG_NO_ONE_BLOCK_UPDATE = 1u << 5,
     /* Record per-pixel primary-hit shape ids (an AOV the reference lacks;
      * needed by the parity criterion).  Off = the id buffer is not written. */
     RT_FLAG_HIT_IDS   = 1u << 1

@@ -34,6 +34,7 @@ RT_FLAG_HIT_IDS = 2
 RT_FLAG_NO_TOP_TREE = 4
 RT_FLAG_NO_HEAVY_FIRST = 8
 RT_FLAG_NO_DEFERRED_COPY = 16
+RT_FLAG_NO_ONE_BLOCK_UPDATE = 32
 RT_BUILD_DEVICE_LAYOUT = 4
 TILE_W, TILE_H = 32, 8
 

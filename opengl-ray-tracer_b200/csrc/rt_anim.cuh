@@ -34,11 +34,7 @@ struct AnimItem  { int shape; int entry; };
 #define RT_ANIM_PACK 8
 struct AnimPack { AnimEntry e[RT_ANIM_PACK]; };
 
-__device__ __forceinline__ void anim_body(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
-                                          const AnimEntry* __restrict__ entries) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nItems) return;
-    const AnimItem it = items[i];
+__device__ __forceinline__ void anim_one(rt_flat_shape* shapes, const AnimItem it, const AnimEntry* __restrict__ entries) {
     const AnimEntry e = entries[it.entry];
     rt_flat_shape* s = shapes + it.shape;
     if (e.kind == RT_ANIM_BOUNCE) {
@@ -54,6 +50,11 @@ __device__ __forceinline__ void anim_body(rt_flat_shape* __restrict__ shapes, co
             for (int r = 0; r < 3; ++r) P[v][r] = (e.m[r] * x + e.m[3 + r] * y) + (e.m[6 + r] * z + e.m[9 + r] * 1.0f);
         }
     }
+}
+__device__ __forceinline__ void anim_body(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
+                                          const AnimEntry* __restrict__ entries) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nItems) anim_one(shapes, items[i], entries);
 }
 __global__ void anim_kernel(rt_flat_shape* __restrict__ shapes, const AnimItem* __restrict__ items, int nItems,
                             const AnimEntry* __restrict__ entries) {
@@ -71,7 +72,7 @@ __device__ __forceinline__ void g_grow(GBox& b, float x, float y, float z) {    
 }
 // BoundingBox::growToInclude(Shape*) (BoundingBox.hpp:60-95): spheres by centre +- radius, walls by start and
 // the opposite corner (wall.hpp:16-31), triangles by their vertices; infinite planes are ignored.
-__device__ __forceinline__ void g_grow_shape(GBox& b, const rt_flat_shape* __restrict__ s) {
+__device__ __forceinline__ void g_grow_shape(GBox& b, const rt_flat_shape* s) {
     const int type = s->type;
     if (type == RT_SHAPE_SPHERE) {
         const float r = s->sphereRadius;
@@ -136,6 +137,58 @@ __global__ void grow_kernel(rt_flat_node* __restrict__ nodes, const rt_flat_shap
             b.mx[a] = b.mx[a] < l.mx[a] ? l.mx[a] : b.mx[a]; b.mx[a] = b.mx[a] < r.mx[a] ? r.mx[a] : b.mx[a];
         }
         g_store(nodes + j, b);
+    }
+}
+
+// K6 + K7 in ONE block for the usual case of a few animated shapes (round 2).  Only the nodes that hold an animated shape can
+// change (updateBVH grows a node by ITS animated shapes, main.cpp:1068-1077), i.e. the animated leaves and their ancestors;
+// the host lists them level by level at registration time (level 0: the animated leaves; level h: the inner nodes whose
+// longest way down to an animated leaf has h edges; upload_anim_tables) and this block walks the levels between barriers:
+// no atomics, no fences, a chain of `levels` dependent box loads.  grow_kernel (every leaf climbs, the second arrival at a
+// node joins its children) took 32 us on the monkey's 1861 nodes for three bouncing spheres; this takes ~5.
+// sched[0 .. nLevels]: entry offsets of the levels; ent[e] = {node, left child, right child, -}.
+#define RT_GROW_PATH_MAX 16384        // more listed nodes than this: grow_kernel
+#define RT_GROW_PATH_THREADS 256
+#ifndef RT_LEVELS_MAX
+#define RT_LEVELS_MAX 1023          // more levels than this: the general kernels
+#endif
+__global__ void __launch_bounds__(RT_GROW_PATH_THREADS)
+anim_grow_path_kernel(rt_flat_shape* shapes, const AnimItem* __restrict__ items, int nItems, const AnimEntry* __restrict__ entries,
+                      const __grid_constant__ AnimPack pack, rt_flat_node* nodes, const int* __restrict__ indices,
+                      const unsigned char* __restrict__ animated, const int* __restrict__ sched, const int4* __restrict__ ent, int nLevels) {
+    __shared__ int sOff[RT_LEVELS_MAX + 1];
+    for (int i = threadIdx.x; i <= nLevels; i += blockDim.x) sOff[i] = sched[i];
+    const AnimEntry* en = entries ? entries : pack.e;
+    for (int i = threadIdx.x; i < nItems; i += blockDim.x) anim_one(shapes, items[i], en);
+    __syncthreads();                                 // the block's own writes to the shapes are visible to it from here on
+    // one dependent trip to L2 per level: the entry of the NEXT level is fetched before the barrier that ends this one
+    int4 cur = make_int4(0, 0, 0, 0);
+    if (nLevels > 0 && sOff[0] + (int)threadIdx.x < sOff[1]) cur = ent[sOff[0] + threadIdx.x];
+    for (int lev = 0; lev < nLevels; ++lev) {
+        const int e0 = sOff[lev], e1 = sOff[lev + 1];
+        int4 nxt = make_int4(0, 0, 0, 0);
+        if (lev + 1 < nLevels && e1 + (int)threadIdx.x < sOff[lev + 2]) nxt = ent[e1 + threadIdx.x];
+        for (int e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
+            const int4 x = e == e0 + (int)threadIdx.x ? cur : ent[e];
+            GBox b = g_load(nodes + x.x);
+            if (lev == 0) {
+                const int s0 = nodes[x.x].startShapeIdx, cnt = nodes[x.x].numShapes;
+                for (int q = 0; q < cnt; ++q) {
+                    const int s = indices[s0 + q];
+                    if (animated[s]) g_grow_shape(b, shapes + s);
+                }
+            } else {
+                const GBox l = g_load(nodes + x.y), r = g_load(nodes + x.z);
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {        // as grow_kernel
+                    b.mn[a] = l.mn[a] < b.mn[a] ? l.mn[a] : b.mn[a]; b.mn[a] = r.mn[a] < b.mn[a] ? r.mn[a] : b.mn[a];
+                    b.mx[a] = b.mx[a] < l.mx[a] ? l.mx[a] : b.mx[a]; b.mx[a] = b.mx[a] < r.mx[a] ? r.mx[a] : b.mx[a];
+                }
+            }
+            g_store(nodes + x.x, b);
+        }
+        __syncthreads();
+        cur = nxt;
     }
 }
 

@@ -120,6 +120,7 @@ struct rt_ctx {
     PinBuf<AnimEntry> hAnimEntries; DevBuf<AnimEntry> dAnimEntries; DevBuf<AnimItem> dAnimItems;
     DevBuf<unsigned char> dAnimFlag; DevBuf<int> dIndices, dNodeAux; DevBuf<unsigned> dGrowArrived;   // dNodeAux: [parent nNodes | leaves nLeaves]
     int nLeavesRaw = 0;
+    DevBuf<int> dGrowSched; DevBuf<int4> dGrowEnt; int growLevels = 0;   // the animated leaves and their ancestors, level by level (anim_grow_path_kernel); 0: grow_kernel
     // device-side BVH build (rt_build.cuh, K8): scratch tables and the emitted FlatNode[] / bvhIndices[]
     DevBuf<int> bInt; DevBuf<bld::u64> bKey; DevBuf<unsigned char> bFlag; DevBuf<bld::Ctl> bCtl;
     DevBuf<rt_flat_node> bNodes; DevBuf<int32_t> bIdx; DevBuf<float4> bRec;
@@ -570,7 +571,7 @@ void rt_destroy(rt_ctx* c) {
     c->hRf.release(); c->dRf.release(); c->dRfArrived.release(); c->hCtl.release();
     c->kOrder.release(); c->kLinkCnt.release(); c->kPshape.release(); c->kPrank.release();
     c->hAnimEntries.release(); c->dAnimEntries.release(); c->dAnimItems.release(); c->dAnimFlag.release();
-    c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release();
+    c->dIndices.release(); c->dNodeAux.release(); c->dGrowArrived.release(); c->dGrowSched.release(); c->dGrowEnt.release();
     for (auto& e : c->evBuild) if (e) cudaEventDestroy(e);
     c->bInt.release(); c->bKey.release(); c->bFlag.release(); c->bCtl.release(); c->bNodes.release(); c->bIdx.release(); c->bRec.release(); c->bHostNodes.release(); c->bHostIdx.release();
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
@@ -1146,6 +1147,41 @@ int upload_anim_tables(rt_ctx* c) {
     if (nS > 0) CU(c, cudaMemcpyAsync(c->dAnimFlag.p, flag.data(), (size_t)nS, cudaMemcpyHostToDevice, c->stream));
     if (!c->indices.empty()) CU(c, cudaMemcpyAsync(c->dIndices.p, c->indices.data(), c->indices.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     if (!c->animItems.empty()) CU(c, cudaMemcpyAsync(c->dAnimItems.p, c->animItems.data(), c->animItems.size() * sizeof(AnimItem), cudaMemcpyHostToDevice, c->stream));
+    // the nodes that can change: the leaves that hold an animated shape and their ancestors, by height above such a leaf
+    std::vector<int> height((size_t)nN, -1);
+    int nListed = 0, maxH = -1;
+    for (int lf : leaves) {
+        const rt_flat_node& x = c->hNodes.p[lf];
+        bool any = false;
+        for (int q = 0; q < x.numShapes && !any; ++q) {
+            const int sIdx = c->indices[(size_t)x.startShapeIdx + (size_t)q];
+            any = sIdx >= 0 && sIdx < nS && flag[(size_t)sIdx];
+        }
+        if (!any) continue;
+        int h = 0;
+        for (int j = lf; j >= 0 && height[(size_t)j] < h; j = aux[(size_t)j], ++h) {   // aux[0 .. nN): parents
+            if (height[(size_t)j] < 0) ++nListed;
+            height[(size_t)j] = h;
+            if (h > maxH) maxH = h;
+            if (h > nN) return fail(c, RT_ERR_SCENE, "device animation needs a proper tree (a cycle of parents)");
+        }
+    }
+    c->growLevels = 0;
+    if (nListed > 0 && nListed <= RT_GROW_PATH_MAX && maxH + 1 <= RT_LEVELS_MAX) {
+        std::vector<int> sched((size_t)maxH + 2, 0);
+        for (int j = 0; j < nN; ++j) if (height[(size_t)j] >= 0) sched[(size_t)height[(size_t)j] + 1]++;
+        for (int h = 0; h <= maxH; ++h) sched[(size_t)h + 1] += sched[(size_t)h];
+        std::vector<int4> ent((size_t)nListed);
+        std::vector<int> fill(sched.begin(), sched.end() - 1);
+        for (int j = 0; j < nN; ++j) if (height[(size_t)j] >= 0) {
+            const rt_flat_node& x = c->hNodes.p[j];
+            ent[(size_t)fill[(size_t)height[(size_t)j]]++] = make_int4(j, x.leftChild, x.rightChild, 0);
+        }
+        CU(c, c->dGrowSched.reserve(sched.size())); CU(c, c->dGrowEnt.reserve(ent.size()));
+        CU(c, cudaMemcpyAsync(c->dGrowSched.p, sched.data(), sched.size() * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(c->dGrowEnt.p, ent.data(), ent.size() * sizeof(int4), cudaMemcpyHostToDevice, c->stream));
+        c->growLevels = maxH + 1;
+    }
     CU(c, cudaStreamSynchronize(c->stream));
     c->animDirty = false; c->animItemsDirty = false;
     return RT_OK;
@@ -1192,7 +1228,19 @@ static int animate_impl(rt_ctx* c, float t, float dt, bool grow) {
         }
     }
     const int nI = (int)c->animItems.size();
-    if (packed) {
+    const bool pathGrow = grow && c->nNodes > 0 && c->growLevels > 0 && !(c->flags & RT_FLAG_NO_ONE_BLOCK_UPDATE);
+    if (pathGrow) {                                // K6 + K7 in one block: the animated shapes, then the listed nodes level by level
+        if (packed) for (size_t e = c->animDefs.size(); e < RT_ANIM_PACK; ++e) { pack.e[e].kind = 0; for (float& x : pack.e[e].m) x = 0.f; }
+        else {
+            for (auto& pe : pack.e) { pe.kind = 0; for (float& x : pe.m) x = 0.f; }
+            CU(c, cudaMemcpyAsync(c->dAnimEntries.p, c->hAnimEntries.p, c->animDefs.size() * sizeof(AnimEntry), cudaMemcpyHostToDevice, c->stream));
+            cudaEventRecord(c->copyDone, c->stream); c->copyPending = true;
+        }
+        anim_grow_path_kernel<<<1, RT_GROW_PATH_THREADS, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, packed ? nullptr : c->dAnimEntries.p, pack,
+            c->dNodes.p, c->dIndices.p, c->dAnimFlag.p, c->dGrowSched.p, c->dGrowEnt.p, c->growLevels);
+        c->launches++;
+        c->devNodesDirty = true;
+    } else if (packed) {
         for (size_t e = c->animDefs.size(); e < RT_ANIM_PACK; ++e) { pack.e[e].kind = 0; for (float& x : pack.e[e].m) x = 0.f; }
         anim_kernel_packed<<<(nI + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, pack);
     } else {
@@ -1201,7 +1249,7 @@ static int animate_impl(rt_ctx* c, float t, float dt, bool grow) {
         anim_kernel<<<(nI + 127) / 128, 128, 0, c->stream>>>(c->dShapes.p, c->dAnimItems.p, nI, c->dAnimEntries.p);
     }
     c->launches++;
-    if (grow && c->nNodes > 0 && c->nLeavesRaw > 0) {
+    if (grow && !pathGrow && c->nNodes > 0 && c->nLeavesRaw > 0) {
         grow_kernel<<<(c->nLeavesRaw + 127) / 128, 128, 0, c->stream>>>(c->dNodes.p, c->dShapes.p, c->dIndices.p, c->dAnimFlag.p,
             c->dNodeAux.p + c->nNodes, c->nLeavesRaw, c->dNodeAux.p, c->dGrowArrived.p);
         c->launches++;

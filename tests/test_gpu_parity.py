@@ -407,15 +407,18 @@ def test_device_refit_keeps_the_boxes_tight(rt):
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("general", [False, True])
 @pytest.mark.parametrize("name", ["monkey", "car"])
-def test_device_animation_equals_host_path(rt, name):
-    """rt_animate (K6 anim_kernel + K7 grow_kernel on the device copies) against the reference's frame step done on
-    the host (animate, per-shape update, grow-only updateBVH, node re-upload): the shapes, the node boxes and the
-    rendered frames are bit-identical, frame after frame."""
+def test_device_animation_equals_host_path(rt, name, general):
+    """rt_animate (K6 + K7 on the device copies: one block that moves the shapes and grows the animated leaves and their
+    ancestors level by level, or — general, RT_FLAG_NO_ONE_BLOCK_UPDATE — anim_kernel + grow_kernel) against the
+    reference's frame step done on the host (animate, per-shape update, grow-only updateBVH, node re-upload): the
+    shapes, the node boxes and the rendered frames are bit-identical, frame after frame."""
     W, H = 320, 240
     sc = rt.Scene(name, W, H)
     p = rt.make_params(W, H)
-    a = rt.RayTracer(W, H); b = rt.RayTracer(W, H)
+    fl = rt.RT_FLAG_HIT_IDS | (rt.RT_FLAG_NO_ONE_BLOCK_UPDATE if general else 0)
+    a = rt.RayTracer(W, H); b = rt.RayTracer(W, H, flags=fl)
     a.upload(sc); b.upload(sc)
     b.register_animations(sc)
     an = sc.animated
