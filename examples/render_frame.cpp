@@ -1,14 +1,17 @@
 // render_frame.cpp — the reference's GPU frame (src/main.cpp:328-361) driven through the C ABI from
 // C++, headless: build a scene with the host library (the stand-in for generateScene*/buildBVH/
 // serializeScene), upload it, render, optionally animate a few frames the way the reference's
-// frame loop does, and write the rgba32f image as a PFM (+ an 8-bit PPM through K4's arithmetic).
+// frame loop does, and write the rgba32f image as a PFM and the displayed frame (rt_render_rgba8: K1 + the display quad's
+// arithmetic, K5) as <out>.ppm.
 //
 //   g++ -std=c++17 -O2 -Iinclude examples/render_frame.cpp -o render_frame \
 //       opengl-ray-tracer_b200/csrc/librt_b200.so opengl-ray-tracer_b200/host/librt_host.so
 //   ./render_frame car 800 600 out.pfm [frames]
 #include <cstdio>
 #include <cstdlib>
+#include <cstdint>
 #include <cstring>
+#include <string>
 #include <vector>
 
 #include "../include/rt_api.h"
@@ -60,6 +63,14 @@ int main(int argc, char** argv) {
         std::fprintf(fp, "PF\n%d %d\n-1.0\n", W, H);
         for (int y = H - 1; y >= 0; --y)
             for (int x = 0; x < W; ++x) std::fwrite(&frame[((size_t)y * W + x) * 4], sizeof(float), 3, fp);
+        std::fclose(fp);
+    }
+    // the frame as the reference shows it (renderQuad main.cpp:474-501 + shader.frag:8-12): <out>.ppm, row 0 = the +Up edge
+    std::vector<uint8_t> shown((size_t)W * H * 4);
+    if ((rc = rt_render_rgba8(rt, &p, shown.data(), nullptr)) != RT_OK) return fail(rt, "rt_render_rgba8", rc);
+    if (FILE* fp = std::fopen((std::string(out) + ".ppm").c_str(), "wb")) {
+        std::fprintf(fp, "P6\n%d %d\n255\n", W, H);
+        for (size_t i = 0; i < (size_t)W * H; ++i) std::fwrite(&shown[4 * i], 1, 3, fp);
         std::fclose(fp);
     }
     rt_destroy(rt);

@@ -149,6 +149,15 @@ int rt_render(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* h
  * rt_wait_frames(ctx, n) blocks until at most n of the issued frames are still in flight (n = 1: the
  * older one is complete and its host buffer may be read / reused; n = 0: all of them). */
 int rt_render_async(rt_ctx* ctx, const rt_params* params, float* host_rgba, int32_t* host_hit_ids);
+
+/* The frame as the reference SHOWS it: the compute dispatch followed by the display quad (renderQuad main.cpp:474-501,
+ * shader.vert:7-11, shader.frag:8-12: the rgba32f image sampled 1:1, alpha forced to 1, and the default framebuffer's
+ * conversion: clamp to [0,1], quantise to 8 bits) — K1 with K5 (rt_present's kernel) behind it band by band, then the copy of
+ * W*H*4 BYTES instead of W*H*16: a 3840x2160 frame leaves over PCIe in 0.6 ms instead of 2.4.  host_rgba8: W*H RGBA8 pixels,
+ * row-major (the compact tile-major shard with a shard set).  The rgba32f image stays on the device (rt_device_image).
+ * _async: as rt_render_async (two frames in flight, rt_wait_frames). */
+int rt_render_rgba8(rt_ctx* ctx, const rt_params* params, uint8_t* host_rgba8, int32_t* host_hit_ids);
+int rt_render_rgba8_async(rt_ctx* ctx, const rt_params* params, uint8_t* host_rgba8, int32_t* host_hit_ids);
 int rt_wait_frames(rt_ctx* ctx, int max_in_flight);
 
 /* Same, but writes into caller-provided DEVICE buffers (e.g. torch tensors)

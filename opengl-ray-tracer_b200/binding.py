@@ -59,7 +59,7 @@ _hostlib = None
 # every symbol include/rt_api.h declares
 API_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_upload_scene", "rt_update_camera", "rt_update_light",
                "rt_update_shapes", "rt_update_nodes", "rt_set_shard", "rt_shard_pixels", "rt_render",
-               "rt_render_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_sync_local", "rt_sync_export", "rt_sync_peer", "rt_sync_enable", "rt_frame_acquire", "rt_frame_release", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_animate_shapes", "rt_download_scene", "rt_build_bvh", "rt_build_bvh_static", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
+               "rt_render_async", "rt_render_rgba8", "rt_render_rgba8_async", "rt_wait_frames", "rt_render_device", "rt_render_stats", "rt_walk_stats", "rt_item_stats", "rt_set_frame_target", "rt_frame_export", "rt_frame_open", "rt_frame_download", "rt_sync_local", "rt_sync_export", "rt_sync_peer", "rt_sync_enable", "rt_frame_acquire", "rt_frame_release", "rt_host_frame_register", "rt_host_frame_unregister", "rt_anim_clear", "rt_anim_bounce", "rt_anim_rotate_z", "rt_animate", "rt_animate_shapes", "rt_download_scene", "rt_build_bvh", "rt_build_bvh_static", "rt_get_bvh", "rt_last_build_ms", "rt_layout_info", "rt_untile", "rt_present", "rt_stream", "rt_set_stream", "rt_synchronize", "rt_device_image",
                "rt_last_timings", "rt_launch_count", "rt_build_info"]
 
 
@@ -129,6 +129,8 @@ def _declare(L):
     L.rt_shard_pixels.argtypes = [vp]; L.rt_shard_pixels.restype = C.c_int64
     L.rt_render.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render.restype = ip
     L.rt_render_async.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_async.restype = ip
+    L.rt_render_rgba8.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_rgba8.restype = ip
+    L.rt_render_rgba8_async.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_rgba8_async.restype = ip
     L.rt_render_device.argtypes = [vp, C.POINTER(Params), vp, vp]; L.rt_render_device.restype = ip
     L.rt_render_stats.argtypes = [vp, C.POINTER(Params), C.POINTER(C.c_uint64), vp]; L.rt_render_stats.restype = ip
     L.rt_walk_stats.argtypes = [vp, C.POINTER(C.c_uint64)]; L.rt_walk_stats.restype = ip
@@ -354,6 +356,17 @@ class RayTracer:
     def render_async(self, params, out, out_ids=None):
         """rt_render_async: returns at once; `out` (pinned) is complete after synchronize()."""
         self._chk(self._L.rt_render_async(self._c, C.byref(params), _ptr(out), _ptr(out_ids)))
+
+    def render_rgba8(self, params, out=None, out_ids=None):
+        """rt_render_rgba8: the frame as the reference shows it (compute dispatch + display quad), W*H RGBA8 pixels on the host."""
+        if out is None:
+            out = np.empty((self.shard_pixels(), 4), dtype=np.uint8)
+        self._chk(self._L.rt_render_rgba8(self._c, C.byref(params), _ptr(out), _ptr(out_ids)))
+        return out
+
+    def render_rgba8_async(self, params, out, out_ids=None):
+        """rt_render_rgba8_async: returns at once; `out` (pinned uint8) is complete after wait_frames / synchronize()."""
+        self._chk(self._L.rt_render_rgba8_async(self._c, C.byref(params), _ptr(out), _ptr(out_ids)))
 
     def wait_frames(self, max_in_flight=1):
         self._chk(self._L.rt_wait_frames(self._c, int(max_in_flight)))

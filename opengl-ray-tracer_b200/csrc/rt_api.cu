@@ -65,6 +65,9 @@ struct PinBuf {                       // capacity-based pinned host array (keeps
 #ifndef RT_MAX_BANDS
 #define RT_MAX_BANDS 8
 #endif
+#ifndef RT_MAX_BANDS_RGBA8
+#define RT_MAX_BANDS_RGBA8 3
+#endif
 #ifndef RT_BAND_ROWS
 #define RT_BAND_ROWS 16         // at least this many tile rows per band
 #endif
@@ -161,6 +164,7 @@ struct rt_ctx {
     // rt_render_async pipelines frames: two device images alternate, so that the D2H of frame i (copy stream)
     // overlaps the render of frame i+1; evFrame[k] = the copy out of image k has finished
     DevBuf<float4> image2; DevBuf<int> ids2;
+    DevBuf<uchar4> image8[2];         // rt_render_rgba8: the display quad's RGBA8 frame (K5 behind K1), one per pipelined image
     cudaEvent_t evFrame[2] = {nullptr, nullptr};
     bool framePending[2] = {false, false};
     int imgPar = 0;                   // image the next pipelined frame renders into
@@ -169,7 +173,7 @@ struct rt_ctx {
     // stream takes ~8 us longer on this box (measured with six empty kernels per frame: 0.192 -> 0.239 ms), and an animated frame
     // begins with five to seven small launches (K6, K7, K4, K2 ...): the copy now runs beside the long render kernel only.
     struct DeferredCopy { bool valid = false; float* hostRgba = nullptr; const float* devRgba = nullptr; int32_t* hostIds = nullptr;
-                          const int32_t* devIds = nullptr; size_t pixels = 0; int par = 0; } deferred;
+                          const int32_t* devIds = nullptr; uint8_t* host8 = nullptr; const uchar4* dev8 = nullptr; size_t pixels = 0; int par = 0; } deferred;
     cudaEvent_t evDefer = nullptr;
     float4* lastImage = nullptr;
     DevBuf<float4> frame;             // full W*H frame other ranks write into (rt_frame_export)
@@ -237,6 +241,7 @@ int flush_deferred(rt_ctx* c, bool afterStream) {
     cudaEventRecord(c->ev[6], c->copyStream);
     if (d.hostRgba) CU(c, cudaMemcpyAsync(d.hostRgba, d.devRgba, d.pixels * sizeof(float4), cudaMemcpyDeviceToHost, c->copyStream));
     if (d.hostIds) CU(c, cudaMemcpyAsync(d.hostIds, d.devIds, d.pixels * sizeof(int), cudaMemcpyDeviceToHost, c->copyStream));
+    if (d.host8) CU(c, cudaMemcpyAsync(d.host8, d.dev8, d.pixels * sizeof(uchar4), cudaMemcpyDeviceToHost, c->copyStream));
     cudaEventRecord(c->ev[7], c->copyStream); c->timed[3] = true;
     cudaEventRecord(c->evFrame[d.par], c->copyStream);
     return RT_OK;
@@ -577,7 +582,7 @@ void rt_destroy(rt_ctx* c) {
     for (auto& e : c->evBand) if (e) cudaEventDestroy(e);
     for (auto& e : c->evFrame) if (e) cudaEventDestroy(e);
     if (c->evDefer) cudaEventDestroy(c->evDefer);
-    c->image2.release(); c->ids2.release();
+    c->image2.release(); c->ids2.release(); c->image8[0].release(); c->image8[1].release();
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
     if (!c->ownStream) c->ownStream = c->stream;      // rt_create failed half-way
@@ -669,7 +674,7 @@ int rt_set_shard(rt_ctx* c, int rank, int world) {
 int64_t rt_shard_pixels(const rt_ctx* c) { return c ? out_pixels(c) : 0; }
 
 static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count,
-                       float* host_rgba, int32_t* host_ids, bool pipeline);
+                       float* host_rgba, int32_t* host_ids, bool pipeline, uint8_t* host_rgba8 = nullptr);
 
 int rt_render_device(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids) {
     return render_impl(c, p, dev_rgba, dev_ids, false, nullptr, nullptr, false);
@@ -709,7 +714,7 @@ int rt_walk_stats(rt_ctx* c, uint64_t out[8]) {
 // previous band's retire), and each finished band is copied to the host on a third stream while
 // the following bands render, so the D2H of the 16 B/pixel frame overlaps the kernel.
 static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* dev_ids, bool count,
-                       float* host_rgba, int32_t* host_ids, bool pipeline) {
+                       float* host_rgba, int32_t* host_ids, bool pipeline, uint8_t* host_rgba8) {
     if (!c || !p) return RT_ERR_ARG;
     if (!c->haveScene || !c->haveCam || !c->haveLight) return fail(c, RT_ERR_STATE, "render before scene/camera/light upload");
     if (dev_ids && !count && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
@@ -718,10 +723,10 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     if (rc != RT_OK) return rc;
     const int64_t px = out_pixels(c);
     // fused gather: no explicit output buffer, a frame target set, several ranks
-    const bool useFrame = !dev_rgba && !host_rgba && !count && c->frameTarget;
+    const bool useFrame = !dev_rgba && !host_rgba && !host_rgba8 && !count && c->frameTarget;
     const bool wantIds = (c->flags & RT_FLAG_HIT_IDS) != 0;
     const bool ownImage = !dev_rgba && !useFrame, ownIds = wantIds && !dev_ids;
-    pipeline = pipeline && ownImage && (host_rgba || host_ids) && !count;
+    pipeline = pipeline && ownImage && (host_rgba || host_ids || host_rgba8) && !count;
     const int par = pipeline ? c->imgPar : 0;
     if (pipeline) c->imgPar ^= 1;
     if (ownImage) {
@@ -730,6 +735,11 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         c->lastImage = img.p;
     }
     if (ownIds) { DevBuf<int>& idb = par ? c->ids2 : c->ids; CU(c, idb.reserve((size_t)px)); dev_ids = idb.p; }
+    uchar4* dev8 = nullptr;
+    if (host_rgba8) {
+        if (!ownImage || count) return fail(c, RT_ERR_ARG, "an RGBA8 frame is rendered into the context's own image");
+        CU(c, c->image8[par].reserve((size_t)px)); dev8 = c->image8[par].p;
+    }
     // a frame that is not pipelined, or one that renders into the image of the deferred copy, sends that copy off first
     if (c->deferred.valid && (!pipeline || c->deferred.par == par)) { rc = flush_deferred(c, false); if (rc != RT_OK) return rc; }
     if ((ownImage || ownIds) && c->framePending[par]) {
@@ -772,7 +782,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
     }
 
     const int tilesMine = tiles_mine(c);
-    const bool toHost = host_rgba || host_ids;
+    const bool toHost = host_rgba || host_ids || host_rgba8;
     // bands: whole tile rows (world == 1: a band is a contiguous block of image rows)
     const int rowTiles = c->shardWorld == 1 ? F.tilesX : 1;
     int nBands = 1;
@@ -786,6 +796,8 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         nBands = rows / RT_BAND_ROWS;                    // at least RT_BAND_ROWS tile rows per band
         if (nBands > RT_MAX_BANDS) nBands = RT_MAX_BANDS;
         if (nBands < 1) nBands = 1;
+        // an RGBA8 frame's copy is a quarter as long: fewer, larger bands (4K car, upload + frame: 2.10 / 2.04 / 1.96 / 1.98 / 2.06 ms with 1 / 2 / 3 / 4 / 8 bands)
+        if (host_rgba8 && nBands > RT_MAX_BANDS_RGBA8) nBands = RT_MAX_BANDS_RGBA8;
     }
     CU(c, c->queue.reserve(RT_MAX_BANDS));
     // the walked list is far larger than L1: the instantiation with more resident warps (rt_kernels.cuh: RT_MIN_BLOCKS_BIG)
@@ -868,18 +880,26 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
             } else {
                 p0 = (size_t)tb * RT_TILE_W * RT_TILE_H; p1 = (size_t)te * RT_TILE_W * RT_TILE_H;
             }
+            if (dev8 && p1 > p0) {               // K5 behind K1 on the band's stream: the display quad's arithmetic on these pixels
+                const long long n8 = (long long)(p1 - p0);
+                present_kernel<<<(unsigned)((n8 + 256 * RT_PRESENT_UNROLL - 1) / (256 * RT_PRESENT_UNROLL)), 256, 0, rs>>>(
+                    reinterpret_cast<const float4*>(dev_rgba) + p0, dev8 + p0, n8);
+                c->launches++;
+            }
             cudaEventRecord(c->evBand[band], rs);
             cudaStreamWaitEvent(c->copyStream, c->evBand[band], 0);
             if (pipeline && nBands == 1 && !(c->flags & RT_FLAG_NO_DEFERRED_COPY)) {
                 rt_ctx::DeferredCopy& d = c->deferred;
                 d.valid = true; d.hostRgba = host_rgba ? host_rgba + 4 * p0 : nullptr; d.devRgba = dev_rgba + 4 * p0;
                 d.hostIds = host_ids ? host_ids + p0 : nullptr; d.devIds = host_ids ? dev_ids + p0 : nullptr; d.pixels = p1 - p0; d.par = par;
+                d.host8 = host_rgba8 ? host_rgba8 + 4 * p0 : nullptr; d.dev8 = host_rgba8 ? dev8 + p0 : nullptr;
                 c->framePending[par] = true;             // evFrame[par] is recorded when the copy is issued (flush_deferred)
                 continue;
             }
             if (firstCopy) { cudaEventRecord(c->ev[6], c->copyStream); firstCopy = false; }
             if (host_rgba) CU(c, cudaMemcpyAsync(host_rgba + 4 * p0, dev_rgba + 4 * p0, (p1 - p0) * sizeof(float4), cudaMemcpyDeviceToHost, c->copyStream));
             if (host_ids) CU(c, cudaMemcpyAsync(host_ids + p0, dev_ids + p0, (p1 - p0) * sizeof(int), cudaMemcpyDeviceToHost, c->copyStream));
+            if (host_rgba8) CU(c, cudaMemcpyAsync(host_rgba8 + 4 * p0, dev8 + p0, (p1 - p0) * sizeof(uchar4), cudaMemcpyDeviceToHost, c->copyStream));
         }
     }
     if (nBands > 1) { cudaEventRecord(evJoin, c->stream2); cudaStreamWaitEvent(c->stream, evJoin, 0); }
@@ -910,6 +930,21 @@ int rt_render_async(rt_ctx* c, const rt_params* p, float* host_rgba, int32_t* ho
     if (!c || !p) return RT_ERR_ARG;
     if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
     return render_impl(c, p, nullptr, nullptr, false, host_rgba, host_hit_ids, true);
+}
+
+int rt_render_rgba8(rt_ctx* c, const rt_params* p, uint8_t* host_rgba8, int32_t* host_hit_ids) {
+    if (!c || !p || !host_rgba8) return RT_ERR_ARG;
+    if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
+    int rc = render_impl(c, p, nullptr, nullptr, false, nullptr, host_hit_ids, false, host_rgba8);
+    if (rc != RT_OK) return rc;
+    CU(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_render_rgba8_async(rt_ctx* c, const rt_params* p, uint8_t* host_rgba8, int32_t* host_hit_ids) {
+    if (!c || !p || !host_rgba8) return RT_ERR_ARG;
+    if (host_hit_ids && !(c->flags & RT_FLAG_HIT_IDS)) return fail(c, RT_ERR_ARG, "hit ids need RT_FLAG_HIT_IDS");
+    return render_impl(c, p, nullptr, nullptr, false, nullptr, host_hit_ids, true, host_rgba8);
 }
 
 int rt_wait_frames(rt_ctx* c, int max_in_flight) {

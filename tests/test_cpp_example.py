@@ -52,3 +52,7 @@ def test_example_matches_oracle(rt, oracle, tmp_path):
     o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, W, H, want_counters=False)
     rgba = np.concatenate([img, np.ones((H, W, 1), np.float32)], axis=-1)
     assert_parity(compare(rgba, None, o_rgba, o_ids), "C++ example, 3 animated frames")
+    ppm = open(str(out) + ".ppm", "rb").read()              # the displayed frame: the display quad's arithmetic on that image
+    assert ppm.startswith(b"P6\n%d %d\n255\n" % (W, H))
+    shown = np.frombuffer(ppm[len(b"P6\n%d %d\n255\n" % (W, H)):], dtype=np.uint8).reshape(H, W, 3)
+    assert np.array_equal(shown, oracle.present(np.ascontiguousarray(rgba))[..., :3])

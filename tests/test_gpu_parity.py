@@ -532,6 +532,39 @@ def test_pipelined_async_frames(rt, W, H):
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("name,W,H", [("monkey", 333, 217), ("car", 1920, 1200)])
+def test_render_rgba8_is_the_presented_frame(rt, oracle, name, W, H):
+    """rt_render_rgba8 (K1 with K5 behind it band by band, RGBA8 to the host) delivers exactly the display quad's arithmetic
+    (oracle.present: shader.frag:8-12 + framebuffer conversion) on rt_render's own rgba32f frame — one launch (small frame),
+    banded (2.3 M pixels), pipelined over two images, and as a compact shard."""
+    import torch
+    sc = rt.Scene(name, W, H)
+    p = rt.make_params(W, H)
+    tr = rt.RayTracer(W, H, flags=rt.RT_FLAG_HIT_IDS); tr.upload(sc)
+    rgba, ids = tr.render(p, want_ids=True)
+    want = oracle.present(rgba.reshape(-1, 4)).reshape(-1, 4)
+    ids8 = np.full(W * H, -5, np.int32)
+    got = tr.render_rgba8(p, out_ids=ids8)
+    assert got.dtype == np.uint8 and got.shape == (W * H, 4)
+    assert np.array_equal(got, want) and np.array_equal(ids8, ids.ravel())
+    img8 = torch.empty((H * W, 4), dtype=torch.uint8, device="cuda")        # the float frame stays on the device
+    tr.present(tr.device_image(), img8.data_ptr(), W * H); tr.synchronize()
+    assert np.array_equal(img8.cpu().numpy(), want)
+    bufs = [torch.empty((H * W, 4), dtype=torch.uint8, pin_memory=True).numpy() for _ in range(2)]
+    for i in range(5):
+        tr.wait_frames(1)
+        bufs[i & 1][:] = 7
+        tr.render_rgba8_async(p, bufs[i & 1])
+    tr.wait_frames(0)
+    assert np.array_equal(bufs[0], want) and np.array_equal(bufs[1], want)
+    # a shard: the compact tile-major pixels of rank 1 of 3, presented
+    tr.set_shard(1, 3)
+    sh, _ = tr.render(p, want_ids=False)
+    got = tr.render_rgba8(p)
+    assert got.shape[0] == tr.shard_pixels() and np.array_equal(got, oracle.present(sh.reshape(-1, 4)).reshape(-1, 4))
+    tr.close()
+
+
 @pytest.mark.parametrize("flags", [0, "no_deferred"])
 def test_deferred_copy_flush_points(rt, flags):
     """The host copy of a pipelined single-launch frame is issued with the next frame's render kernel or by whoever waits
