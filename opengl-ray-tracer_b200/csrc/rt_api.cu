@@ -128,6 +128,8 @@ struct rt_ctx {
     DevBuf<int> bInt; DevBuf<bld::u64> bKey; DevBuf<unsigned char> bFlag; DevBuf<bld::Ctl> bCtl;
     DevBuf<rt_flat_node> bNodes; DevBuf<int32_t> bIdx; DevBuf<float4> bRec;
     PinBuf<rt_flat_node> bHostNodes; PinBuf<int32_t> bHostIdx; int bNodeCount = 0, bIdxCount = 0;   // pinned: the tree comes back at PCIe speed
+    bool nodesNested = false;         // the nodes of the last set_nodes: parents around their children (rtl::scan_nodes)
+    bool h2dStarted = false;          // rt_upload_scene has recorded ev[0] in front of its early shape copy
     bool shapesOnDevice = false;      // the pending host range [shapeLo, shapeHi) has already been copied (rt_build_bvh)
     float lastBuildMs = 0.f;
     cudaEvent_t evBuild[2] = {nullptr, nullptr};
@@ -383,7 +385,8 @@ int flush_scene(rt_ctx* c) {
     }
     const bool shapesChanged = c->shapeHi > c->shapeLo;
     if ((shapesChanged || c->devShapesDirty) && c->nSub > 0) c->subDirty = true;
-    cudaEventRecord(c->ev[0], c->stream);
+    if (!c->h2dStarted) cudaEventRecord(c->ev[0], c->stream);
+    c->h2dStarted = false;
     if (shapesChanged && !c->shapesOnDevice) {
         CU(c, c->dShapes.reserve((size_t)c->nShapes));
         if (c->hostShapesStale && !c->shapeRanges.empty()) {
@@ -405,7 +408,7 @@ int flush_scene(rt_ctx* c) {
     if (c->nodesDirty && !c->topoDirty && c->nDfsB > 0) {
         // reference boxes changed under an unchanged topology (grow-only refit): B's union boxes follow;
         // if the reference tree stopped being nested, B is no longer equivalent and is switched off
-        if (rtl::ref_tree_nested(c->hNodes.p, c->nNodes)) devRefit = true;
+        if (c->nodesNested) devRefit = true;     // (set_nodes' scan of exactly these nodes)
         else { c->nDfsB = 0; c->layout.useB = false; }
     }
     if (c->devNodesDirty && !c->topoDirty && c->nDfsB > 0) devRefit = true;   // K7 keeps parents around their children
@@ -486,34 +489,30 @@ int flush_scene(rt_ctx* c) {
     return RT_OK;
 }
 
-bool same_topology(const rt_flat_node* a, const rt_flat_node* b, int n) {
-    for (int i = 0; i < n; ++i)
-        if (a[i].leftChild != b[i].leftChild || a[i].rightChild != b[i].rightChild ||
-            (a[i].leftChild == -1 && (a[i].startShapeIdx != b[i].startShapeIdx || a[i].numShapes != b[i].numShapes)))
-            return false;
-    return true;
-}
 
 // adopt != NULL: `nodes` is adopt->p, a pinned buffer of this context (the device builder's staging): it BECOMES the
 // shadow by a pointer swap instead of being copied into it.
 int set_nodes(rt_ctx* c, const void* nodes, int nNodes, PinBuf<rt_flat_node>* adopt = nullptr) {
     const rt_flat_node* in = static_cast<const rt_flat_node*>(nodes);
     // (after a device-side layout the shadow holds an older tree: nothing to compare with)
-    const bool sameTopo = c->haveScene && !c->hostTreeStale && nNodes == c->nNodes && !c->topoDirty && same_topology(in, c->hNodes.p, nNodes);
+    const bool comparable = c->haveScene && !c->hostTreeStale && nNodes == c->nNodes && !c->topoDirty;
     c->hostTreeStale = false; c->layoutOnDevice = false;
     wait_copies(c);
+    // one read-only pass: the topology compare with the shadow, |bound| <= 1e37 everywhere (the NaN-free slab fast path) and
+    // parents around their children (list B stays valid under a refit; flush_scene); then the copy into the shadow
+    rtl::NodeScan sc;
+    sc = rtl::scan_nodes(in, comparable ? c->hNodes.p : nullptr, nNodes, RT_SAFE_COORD);
     if (adopt) {
         std::swap(c->hNodes, *adopt);
     } else {
         CU(c, c->hNodes.reserve((size_t)nNodes, 0));
         if (nNodes > 0) std::memcpy(c->hNodes.p, in, (size_t)nNodes * sizeof(rt_flat_node));
     }
+    const bool sameTopo = comparable && sc.sameTopo;
     c->nNodes = nNodes;
     if (nNodes > 0) for (int k = 0; k < 3; ++k) { c->rootBox[k] = in[nNodes - 1].boundsMin[k]; c->rootBox[3 + k] = in[nNodes - 1].boundsMax[k]; }
-    c->boxesFinite = true;            // NaN-free slab fast path needs |bound| <= 1e37 everywhere
-    for (int i = 0; i < nNodes && c->boxesFinite; ++i)
-        for (int k = 0; k < 3; ++k)
-            if (!(std::fabs(in[i].boundsMin[k]) <= RT_SAFE_COORD) || !(std::fabs(in[i].boundsMax[k]) <= RT_SAFE_COORD)) c->boxesFinite = false;
+    c->boxesFinite = sc.safe;
+    c->nodesNested = sc.nested;
     c->nodesDirty = true;
     c->hostNodesStale = false;
     if (!sameTopo) c->topoDirty = true;
@@ -605,18 +604,30 @@ int rt_upload_scene(rt_ctx* c, const void* light32, const void* camera80, const 
         wait_copies(c);
         bool sameTypes = c->haveScene && nShapes == c->nShapes && !c->topoDirty;
         const rt_flat_shape* in = static_cast<const rt_flat_shape*>(shapes);
-        for (int i = 0; sameTypes && i < nShapes; ++i) sameTypes = in[i].type == c->hShapes.p[i].type;
         if (!nodes && !indices && c->haveScene && nShapes < c->nShapes && c->nNodes > 0) {
             // a shorter shape buffer on its own: the tree the context holds would index past its end.  It is dropped
             // (useBVH frames hit nothing) until nodes / indices are supplied or rt_build_bvh builds a new one.
             c->nNodes = 0; c->indices.clear(); c->topoDirty = true; c->nodesDirty = true; c->hostNodesStale = false;
             c->hostTreeStale = false; c->layoutOnDevice = false; c->bIdxCount = 0;
         }
+        if (sameTypes) {                   // (without an early exit: the usual answer is "the same")
+            unsigned diff = 0u;
+            for (int i = 0; i < nShapes; ++i) diff |= (unsigned)(in[i].type != c->hShapes.p[i].type);
+            sameTypes = diff == 0u;
+        }
         CU(c, c->hShapes.reserve((size_t)nShapes, 0));
         if (nShapes > 0) std::memcpy(c->hShapes.p, shapes, (size_t)nShapes * sizeof(rt_flat_shape));
         c->nShapes = nShapes; c->shapeLo = 0; c->shapeHi = nShapes;
         c->hostShapesStale = false; c->shapesOnDevice = false; c->shapeRanges.clear();
         if (!sameTypes) c->topoDirty = true;
+        if (nShapes > 0) {
+            // the H2D copy of the shapes starts NOW and runs while the host stages and checks nodes and indices (flush_scene does
+            // not repeat it; its copyDone event, recorded behind this copy in stream order, guards the pinned source)
+            CU(c, c->dShapes.reserve((size_t)nShapes));
+            cudaEventRecord(c->ev[0], c->stream); c->h2dStarted = true;
+            CU(c, cudaMemcpyAsync(c->dShapes.p, c->hShapes.p, (size_t)nShapes * sizeof(rt_flat_shape), cudaMemcpyHostToDevice, c->stream));
+            c->shapesOnDevice = true;
+        }
     }
     if ((indices || nodes) && c->hostTreeStale) { int rc = ensure_host_tree(c); if (rc != RT_OK) return rc; }
     if (indices) {

@@ -571,6 +571,50 @@ inline bool ref_tree_nested(const rt_flat_node* nd, int nNodes) {
     return true;
 }
 
+// What a node upload has to know about the new nodes, in ONE pass without early exits (the three separate passes — the
+// topology compare, the |bound| <= 1e37 check and ref_tree_nested — were 105 of the 176 us that rt_upload_scene spent on
+// the host for the car's 3743 nodes; this pass: ~10 us):
+//   sameTopo  child links of every node, and the index range of every leaf, equal those of `old` (old == NULL: false)
+//   safe      every bound is a number with |v| <= safeCoord (the NaN-free slab test is legal)
+//   nested    ref_tree_nested(in, n)
+// Read-only on purpose: with the copy into the shadow in the same loop the loads of in[i + 1] run into the stores to
+// dst[i] (same page offsets, 4K aliasing) and the pass is slower than the three it replaces; memcpy afterwards is not.
+struct NodeScan { bool sameTopo, safe, nested; };
+inline NodeScan scan_nodes(const rt_flat_node* in, const rt_flat_node* old, int n, float safeCoord) {
+    unsigned topoBad = old ? 0u : 1u, notNested = 0u;
+    uint32_t maxAbs = 0u, safeBits;
+    std::memcpy(&safeBits, &safeCoord, 4);
+    for (int i = 0; i < n; ++i) {
+        const rt_flat_node& x = in[i];
+        if (old) {
+            const rt_flat_node& o = old[i];
+            const unsigned leaf = x.leftChild == -1;
+            topoBad |= (unsigned)(x.leftChild != o.leftChild) | (unsigned)(x.rightChild != o.rightChild) |
+                       (leaf & ((unsigned)(x.startShapeIdx != o.startShapeIdx) | (unsigned)(x.numShapes != o.numShapes)));
+        }
+        // |v| as an integer: the order of the bit patterns is the order of the magnitudes, inf and every NaN above all numbers
+        for (int a = 0; a < 3; ++a) {
+            uint32_t lo, hi;
+            std::memcpy(&lo, &x.boundsMin[a], 4); std::memcpy(&hi, &x.boundsMax[a], 4);
+            lo &= 0x7fffffffu; hi &= 0x7fffffffu;
+            maxAbs = lo > maxAbs ? lo : maxAbs; maxAbs = hi > maxAbs ? hi : maxAbs;
+        }
+        if (x.leftChild != -1) {
+            const int ch[2] = {x.leftChild, x.rightChild};
+            for (int c : ch) {
+                const bool in_range = c >= 0 && c < n;
+                notNested |= (unsigned)!in_range;
+                const rt_flat_node& y = in[in_range ? c : i];
+                for (int a = 0; a < 3; ++a)
+                    notNested |= (unsigned)!(y.boundsMin[a] >= x.boundsMin[a]) | (unsigned)!(y.boundsMax[a] <= x.boundsMax[a]);
+            }
+        }
+    }
+    NodeScan r;
+    r.sameTopo = topoBad == 0u; r.safe = maxAbs <= safeBits; r.nested = notNested == 0u && maxAbs < 0x7f800000u;
+    return r;
+}
+
 // Recompute the boxes of B's top nodes from the current raw node boxes (bottom-up) and the SAH estimates.
 inline void refit_top(Layout& L, const rt_flat_node* nd) {
     const int mB = (int)L.srcB.size();

@@ -85,6 +85,21 @@ static void fill_nodes(Emu* E, const rt_flat_node* nodes) {
 }
 
 extern "C" {
+// rtl::scan_nodes against the three separate passes it replaced (rt_api.cu: same_topology, the safe-coordinate loop, rtl::ref_tree_nested)
+int emu_scan_nodes(const rt_flat_node* in, const rt_flat_node* old, int n, int* out) {
+    const rtl::NodeScan r = rtl::scan_nodes(in, old, n, 1e37f);
+    out[0] = r.sameTopo; out[1] = r.safe; out[2] = r.nested;
+    bool same = old != nullptr;
+    for (int i = 0; same && i < n; ++i)
+        if (in[i].leftChild != old[i].leftChild || in[i].rightChild != old[i].rightChild ||
+            (in[i].leftChild == -1 && (in[i].startShapeIdx != old[i].startShapeIdx || in[i].numShapes != old[i].numShapes))) same = false;
+    bool safe = true;
+    for (int i = 0; i < n && safe; ++i)
+        for (int k = 0; k < 3; ++k)
+            if (!(std::fabs(in[i].boundsMin[k]) <= 1e37f) || !(std::fabs(in[i].boundsMax[k]) <= 1e37f)) safe = false;
+    out[3] = same; out[4] = safe; out[5] = rtl::ref_tree_nested(in, n);
+    return 1;
+}
 
 void* emu_create(const rt_flat_shape* shapes, int nShapes, const rt_flat_node* nodes, int nNodes,
                  const int32_t* indices, int nIndices, int subtrees, double omax) {

@@ -33,6 +33,7 @@ def emu():
     L.emu_query.argtypes = [vp, ip, vp, vp, ip, ip, vp, vp, vp, vp, vp]; L.emu_query.restype = None
     L.emu_layout_hash.argtypes = [vp]; L.emu_layout_hash.restype = C.c_uint64
     L.emu_subboxes.argtypes = [vp, vp, ip]; L.emu_subboxes.restype = ip
+    L.emu_scan_nodes.argtypes = [vp, vp, ip, vp]; L.emu_scan_nodes.restype = ip
     return L
 
 
@@ -368,3 +369,44 @@ def test_layout_is_the_validated_one(rt, emu, name, n, want):
     sc = rt.Scene(name, 800, 600, n_override=n)
     e = Emu(emu, sc.shapes, sc.nodes, sc.indices, omax=200.0)
     assert emu.emu_layout_hash(e.h) == want, "%s: layout hash %016x" % (name, emu.emu_layout_hash(e.h))
+
+
+def test_scan_nodes_equals_the_three_passes(emu, rt):
+    """rtl::scan_nodes (one pass over an uploaded node array: topology compare with the shadow, copy, safe coordinates,
+    nestedness) against the three separate passes it replaced, on real trees and on every kind of damage."""
+    rng = np.random.default_rng(5)
+    cases = 0
+    for name in ("toy", "monkey", "car"):
+        sc = rt.Scene(name, 64, 48)
+        base = np.ascontiguousarray(sc.nodes).copy()
+        n = len(base)
+        variants = [("same", base.copy(), base)]
+        for kind in ("grown", "shrunk", "nan", "inf", "huge", "child", "range", "leafidx", "inneridx", "empty_leaf", "no_old"):
+            for _ in range(4):
+                v = base.copy()
+                i = int(rng.integers(0, n))
+                inner = np.flatnonzero(base["leftChild"] != -1); leaves = np.flatnonzero(base["leftChild"] == -1)
+                if kind == "grown": v["boundsMax"][inner[rng.integers(0, len(inner))]] += 1.0
+                elif kind == "shrunk": v["boundsMax"][inner[rng.integers(0, len(inner))]] -= 0.5
+                elif kind == "nan": v["boundsMin"][i, rng.integers(0, 3)] = np.nan
+                elif kind == "inf": v["boundsMax"][i, rng.integers(0, 3)] = np.inf
+                elif kind == "huge": v["boundsMax"][n - 1, rng.integers(0, 3)] = 2e37
+                elif kind == "child" and len(inner) > 1:
+                    a, b = inner[rng.integers(0, len(inner), 2)]
+                    v["leftChild"][a] = base["leftChild"][b]
+                elif kind == "range": v["rightChild"][inner[rng.integers(0, len(inner))]] = n + 3
+                elif kind == "leafidx": v["numShapes"][leaves[rng.integers(0, len(leaves))]] += 1
+                elif kind == "inneridx": v["startShapeIdx"][inner[rng.integers(0, len(inner))]] += 7      # ignored for inner nodes
+                elif kind == "empty_leaf":
+                    lf = leaves[rng.integers(0, len(leaves))]
+                    v["boundsMin"][lf] = np.inf; v["boundsMax"][lf] = -np.inf
+                variants.append((kind, v, None if kind == "no_old" else base))
+        for kind, v, old in variants:
+            out = np.zeros(6, np.int32)
+            copied = emu.emu_scan_nodes(_p(v), _p(old), n, _p(out))
+            assert copied == 1, (name, kind)
+            assert out[:3].tolist() == out[3:].tolist(), (name, kind, out.tolist())
+            cases += 1
+    out = np.zeros(6, np.int32)
+    assert emu.emu_scan_nodes(None, None, 0, _p(out)) == 1 and out[1] == 1 and out[2] == 1     # no nodes: safe, nested, nothing to compare
+    assert cases > 100
