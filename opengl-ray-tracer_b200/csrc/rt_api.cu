@@ -468,17 +468,21 @@ int flush_scene(rt_ctx* c) {
         if (!c->rfPending) { cudaEventRecord(c->rfDone, c->stream); c->rfPending = true; }
         subUpload = true;                          // the node lists take the new boxes below
     }
-    if ((c->nodesDirty || c->topoDirty || subUpload || c->devNodesDirty) && c->nDfs > 0) {
-        repack_nodes_kernel<<<(c->nDfs + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dSubBox.p, c->dOrder.p, c->dLinkCnt.p, c->dNodesT.p, c->nDfs);
-        c->launches++;
-        if (c->nDfsB > 0) {
-            repack_nodes_kernel<<<(c->nDfsB + 255) / 256, 256, 0, c->stream>>>(c->dNodes.p, c->dSubBox.p, c->dOrderB.p, c->dLinkCntB.p, c->dNodesB.p, c->nDfsB);
+    {   // K2: both node lists and the primitive slots in one launch
+        const bool doNodes = (c->nodesDirty || c->topoDirty || subUpload || c->devNodesDirty) && c->nDfs > 0;
+        const bool doPrims = (shapesChanged || c->topoDirty || c->devShapesDirty) && c->nPrims > 0;
+        RepackAll R;
+        R.raw = c->dNodes.p; R.subBox = c->dSubBox.p;
+        R.orderA = c->dOrder.p; R.linkA = c->dLinkCnt.p; R.outA = c->dNodesT.p; R.nA = doNodes ? c->nDfs : 0;
+        R.orderB = c->dOrderB.p; R.linkB = c->dLinkCntB.p; R.outB = c->dNodesB.p; R.nB = doNodes ? c->nDfsB : 0;
+        R.shapes = c->dShapes.p; R.pshape = c->dPshape.p; R.q0 = c->q0.p; R.q1 = c->q1.p; R.q2 = c->q2.p; R.q3 = c->q3.p; R.ptype = c->ptype.p;
+        R.nPrims = doPrims ? c->nPrims : 0;
+        R.blocksA = (R.nA + 255) / 256; R.blocksB = (R.nB + 255) / 256;
+        const long long blocks = (long long)R.blocksA + R.blocksB + (R.nPrims + 255) / 256;
+        if (blocks > 0) {
+            repack_all_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(R);
             c->launches++;
         }
-    }
-    if ((shapesChanged || c->topoDirty || c->devShapesDirty) && c->nPrims > 0) {
-        repack_prims_kernel<<<(c->nPrims + 255) / 256, 256, 0, c->stream>>>(c->dShapes.p, c->dPshape.p, c->q0.p, c->q1.p, c->q2.p, c->q3.p, c->ptype.p, c->nPrims);
-        c->launches++;
     }
     cudaEventRecord(c->ev[3], c->stream); c->timed[1] = true;
     CU(c, cudaGetLastError());

@@ -627,26 +627,37 @@ __global__ void lpt_prepare_kernel(unsigned* __restrict__ cost, int n, unsigned*
 // K2: repack.  nodes: gather the raw 48-byte nodes into the threaded layout;
 // prims: gather the raw 192-byte shapes into float4 SoA in visit order.
 // ---------------------------------------------------------------------------
-__global__ void repack_nodes_kernel(const rt_flat_node* __restrict__ raw, const float4* __restrict__ subBox,
-                                    const int* __restrict__ order, const int2* __restrict__ linkCnt,
-                                    float4* __restrict__ out, int n) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    const int o = order[k];                 // >= 0: raw reference node; < 0: sub-tree node -1-o (host-computed box)
-    const float4* src = o >= 0 ? reinterpret_cast<const float4*>(raw + o) : subBox + 2 * (size_t)(-1 - o);
-    const float4 mn = __ldg(src), mx = __ldg(src + 1);
-    const int2 lc = linkCnt[k];
-    out[2 * k]     = make_float4(mn.x, mn.y, mn.z, __int_as_float(lc.x));
-    out[2 * k + 1] = make_float4(mx.x, mx.y, mx.z, __int_as_float(lc.y));
-}
 
-__global__ void repack_prims_kernel(const rt_flat_shape* __restrict__ shapes, const int* __restrict__ pshape,
-                                    float4* __restrict__ q0, float4* __restrict__ q1, float4* __restrict__ q2,
-                                    float4* __restrict__ q3, int* __restrict__ ptype, int n) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
-    const Prim p = prim_from_shape(shapes + pshape[s]);
-    q0[s] = p.q0; q1[s] = p.q1; q2[s] = p.q2; q3[s] = p.q3; ptype[s] = p.type;
+// K2 as ONE launch (round 2): list A, list B and the primitive slots are independent of each other; the block index selects
+// the job (blocks [0, bA): list A; [bA, bA + bB): list B; the rest: primitive slots).  A small scene's frame update paid three
+// launch gaps for 13 blocks of work.
+struct RepackAll {
+    const rt_flat_node* raw; const float4* subBox;
+    const int* orderA; const int2* linkA; float4* outA; int nA;
+    const int* orderB; const int2* linkB; float4* outB; int nB;
+    const rt_flat_shape* shapes; const int* pshape; float4 *q0, *q1, *q2, *q3; int* ptype; int nPrims;
+    int blocksA, blocksB;
+};
+__global__ void __launch_bounds__(256) repack_all_kernel(const __grid_constant__ RepackAll P) {
+    int blk = blockIdx.x;
+    if (blk < P.blocksA + P.blocksB) {
+        const bool inB = blk >= P.blocksA;
+        if (inB) blk -= P.blocksA;
+        const int k = blk * 256 + threadIdx.x, n = inB ? P.nB : P.nA;
+        if (k >= n) return;
+        const int o = (inB ? P.orderB : P.orderA)[k];
+        const float4* src = o >= 0 ? reinterpret_cast<const float4*>(P.raw + o) : P.subBox + 2 * (size_t)(-1 - o);
+        const float4 mn = __ldg(src), mx = __ldg(src + 1);
+        const int2 lc = (inB ? P.linkB : P.linkA)[k];
+        float4* out = inB ? P.outB : P.outA;
+        out[2 * k]     = make_float4(mn.x, mn.y, mn.z, __int_as_float(lc.x));
+        out[2 * k + 1] = make_float4(mx.x, mx.y, mx.z, __int_as_float(lc.y));
+    } else {
+        const int s = (blk - P.blocksA - P.blocksB) * 256 + threadIdx.x;
+        if (s >= P.nPrims) return;
+        const Prim p = prim_from_shape(P.shapes + P.pshape[s]);
+        P.q0[s] = p.q0; P.q1[s] = p.q1; P.q2[s] = p.q2; P.q3[s] = p.q3; P.ptype[s] = p.type;
+    }
 }
 
 // ---------------------------------------------------------------------------
