@@ -6,4 +6,4 @@ The directory name contains '-', so load it with `rtload.load()` at the repo roo
 """
 from . import build, shard  # noqa: F401
 from .binding import (CAMERA_DTYPE, LIGHT_DTYPE, NODE_DTYPE, SHAPE_DTYPE, RT_FLAG_REFERENCE_WALK, RT_FLAG_HIT_IDS, RT_FLAG_NO_TOP_TREE, RT_FLAG_NO_HEAVY_FIRST, RT_FLAG_NO_DEFERRED_COPY, RT_FLAG_NO_ONE_BLOCK_UPDATE, RT_BUILD_DEVICE_LAYOUT,  # noqa: F401
-                      API_SYMBOLS, RT_STATIC_BUILD_MAX_SHAPES, build_bvh_static, Params, RayTracer, RtError, Scene, hostlib, lib, lib_fast, lib_path, make_params)
+                      API_SYMBOLS, RT_STATIC_BUILD_MAX_SHAPES, build_bvh_static, obj_triangles, Params, RayTracer, RtError, Scene, hostlib, lib, lib_fast, lib_path, make_params)

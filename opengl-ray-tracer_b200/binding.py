@@ -90,6 +90,25 @@ def _records(a, dtype, what):
     return a
 
 
+def obj_triangles(path, origin=(0.0, 0.0, 0.0), material_from=None, apply_rule=False):
+    """rh_obj_triangles: a Wavefront OBJ as flat triangles (SHAPE_DTYPE) + the first triangle of every mesh (last entry: the total)."""
+    H = hostlib()
+    org = (C.c_float * 3)(*[float(x) for x in origin])
+    mat = None
+    if material_from is not None:
+        mat = np.ascontiguousarray(material_from).reshape(-1)[:1]
+        if mat.dtype.itemsize != SHAPE_DTYPE.itemsize:
+            raise ValueError("material_from: one SHAPE_DTYPE record")
+    nm = C.c_int(0)
+    n = H.rh_obj_triangles(str(path).encode(), org, _ptr(mat), int(bool(apply_rule)), None, 0, None, 0, C.byref(nm))
+    if n < 0:
+        raise RuntimeError("rh_obj_triangles(%s): %s" % (path, {-1: "bad argument", -2: "cannot open the file", -3: "malformed v / f record"}.get(n, n)))
+    out = np.zeros(n, dtype=SHAPE_DTYPE)
+    first = np.zeros(nm.value + 1, dtype=np.int32)
+    H.rh_obj_triangles(str(path).encode(), org, _ptr(mat), int(bool(apply_rule)), _ptr(out) if n else None, n, _ptr(first), len(first), C.byref(nm))
+    return out, first
+
+
 def lib_path():
     return os.path.join(_build.CSRC, "librt_b200.so")
 
@@ -180,6 +199,7 @@ def hostlib():
     H.rh_scene_create.argtypes = [C.c_char_p, ip, ip, ip, ip]; H.rh_scene_create.restype = vp
     H.rh_scene_from_shapes.argtypes = [vp, ip, vp, vp, ip]; H.rh_scene_from_shapes.restype = vp
     H.rh_scene_destroy.argtypes = [vp]; H.rh_scene_destroy.restype = None
+    H.rh_obj_triangles.argtypes = [C.c_char_p, vp, vp, ip, vp, ip, vp, ip, C.POINTER(ip)]; H.rh_obj_triangles.restype = ip
     for name in ("rh_light", "rh_camera"):
         getattr(H, name).argtypes = [vp]; getattr(H, name).restype = vp
     for name in ("rh_shapes", "rh_nodes", "rh_indices", "rh_animated"):

@@ -5,6 +5,8 @@
 #include "rt_anim_math.h"
 
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <random>
@@ -446,6 +448,91 @@ rh_scene* rh_scene_from_shapes(const rt_flat_shape* shapes, int nShapes, const r
     sc->flatShapes.assign(shapes, shapes + nShapes);      // caller's bytes pass through untouched
     serialize_bvh(*sc);
     return sc.release();
+}
+
+// ---- Wavefront OBJ -> flat triangles: the reference's model path (model.hpp:49-168 + mesh.hpp:163-189) without assimp ----
+// The reference reads its meshes through assimp with aiProcess_Triangulate and WITHOUT aiProcess_JoinIdenticalVertices:
+// the OBJ importer then hands out one vertex per face corner and one mesh per object / group / material run that has
+// faces; main.cpp offsets every vertex by mesh.origin (mesh.hpp:171-173) and builds `Triangle(a, b, c)` from the corners
+// (main.cpp:652-654, 669-671, 760-762) — the inverted normal of mesh2triangles is dropped on that way, so the plane of a
+// scene triangle is always the one its corners span (triangle.hpp:47-48, 83-92).  apply_rule != 0 keeps mesh2triangles'
+// own rule instead (a triangle whose normal has a positive dot product with Mesh::center(), mesh.hpp:51-61 =
+// (origin + sum over the face corners of (origin + p)) / corners, is inverted: mesh.hpp:178-184).
+// Polygons become fans (v0, vi, vi+1), as assimp triangulates a convex polygon; `v` and `f` records with v, v/vt, v//vn,
+// v/vt/vn and negative (relative) indices are understood, everything else is skipped.
+int rh_obj_triangles(const char* path, const float origin[3], const rt_flat_shape* material_from, int apply_rule,
+                     rt_flat_shape* out, int cap, int32_t* mesh_first, int mesh_cap, int* n_meshes) {
+    if (!path || !origin) return -1;
+    FILE* fp = std::fopen(path, "rb");
+    if (!fp) return -2;
+    Mat mat;
+    if (material_from) {
+        const rt_flat_material& m = material_from->material;
+        mat.color = v3(m.color); mat.fresnel = m.fresnelStrength; mat.ambient = m.ambientStrength; mat.diffuse = m.diffuseStrength;
+        mat.specular = m.specularStrength; mat.shininess = m.shininess;
+    }
+    const V3 org = v3(origin[0], origin[1], origin[2]);
+    std::vector<V3> verts;
+    std::vector<Shape> tris;
+    std::vector<V3> raw;                      // the face corners as read (3 per triangle): assimp's vertex array
+    std::vector<int32_t> first;               // first triangle of every mesh
+    bool meshOpen = false, bad = false;
+    char line[4096];
+    while (std::fgets(line, sizeof line, fp)) {
+        const char* q = line;
+        while (*q == ' ' || *q == '\t') ++q;
+        if (q[0] == 'v' && (q[1] == ' ' || q[1] == '\t')) {
+            float x = 0, y = 0, z = 0;
+            if (std::sscanf(q + 1, "%f %f %f", &x, &y, &z) != 3) { bad = true; break; }
+            verts.push_back(v3(x, y, z));
+        } else if (q[0] == 'f' && (q[1] == ' ' || q[1] == '\t')) {
+            std::vector<int> idx;
+            const char* r = q + 1;
+            for (;;) {
+                while (*r == ' ' || *r == '\t') ++r;
+                if (*r == 0 || *r == '\n' || *r == '\r' || *r == '#') break;
+                char* end = nullptr;
+                const long v = std::strtol(r, &end, 10);
+                if (end == r) { bad = true; break; }
+                const long at = v > 0 ? v - 1 : (long)verts.size() + v;     // negative: relative to the vertices read so far
+                if (v == 0 || at < 0 || at >= (long)verts.size()) { bad = true; break; }
+                idx.push_back((int)at);
+                r = end;
+                while (*r && *r != ' ' && *r != '\t' && *r != '\n' && *r != '\r') ++r;   // skip /vt/vn
+            }
+            if (bad) break;
+            if (idx.size() < 3) continue;
+            if (!meshOpen) { first.push_back((int32_t)tris.size()); meshOpen = true; }
+            for (size_t i = 1; i + 1 < idx.size(); ++i) {
+                Shape t = make_triangle(verts[(size_t)idx[0]] + org, verts[(size_t)idx[i]] + org, verts[(size_t)idx[i + 1]] + org);
+                t.mat = mat;
+                tris.push_back(t);
+                raw.push_back(verts[(size_t)idx[0]]); raw.push_back(verts[(size_t)idx[i]]); raw.push_back(verts[(size_t)idx[i + 1]]);
+            }
+        } else if ((q[0] == 'o' || q[0] == 'g') && (q[1] == ' ' || q[1] == '\t' || q[1] == '\n' || q[1] == '\r')) {
+            meshOpen = false;                 // the next face opens a new mesh
+        } else if (std::strncmp(q, "usemtl", 6) == 0) {
+            meshOpen = false;
+        }
+    }
+    std::fclose(fp);
+    if (bad) return -3;
+    first.push_back((int32_t)tris.size());
+    if (apply_rule) {
+        for (size_t m = 0; m + 1 < first.size(); ++m) {
+            const size_t t0 = (size_t)first[m], t1 = (size_t)first[m + 1];
+            V3 c = org;                        // Mesh::center(), vertex by vertex in assimp's order (the face corners)
+            for (size_t k = 3 * t0; k < 3 * t1; ++k) c = c + (org + raw[k]);
+            c = c / (float)((t1 - t0) * 3);
+            for (size_t t = t0; t < t1; ++t) if (dot(tris[t].normal, c) > 0.0f) invert_normal(tris[t]);
+        }
+    }
+    const int n = (int)tris.size();
+    for (int i = 0; i < n && i < cap && out; ++i) out[i] = serialize_shape(tris[(size_t)i]);
+    const int nm = (int)first.size() - 1;
+    if (n_meshes) *n_meshes = nm;
+    for (int m = 0; m <= nm && m < mesh_cap && mesh_first; ++m) mesh_first[m] = first[(size_t)m];
+    return n;
 }
 
 void rh_scene_destroy(rh_scene* s) { delete s; }

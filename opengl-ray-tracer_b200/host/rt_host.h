@@ -36,6 +36,17 @@ rh_scene* rh_scene_from_shapes(const rt_flat_shape* shapes, int nShapes,
                                const rt_flat_light* light, const rt_flat_camera* camera, int bvh_depth);
 void rh_scene_destroy(rh_scene* s);
 
+/* A Wavefront OBJ as flat triangles (type 3) with `material_from`'s material (NULL: material.hpp:23's defaults), every vertex
+ * offset by origin: the reference's model path (model.hpp:49-168 through assimp, mesh.hpp:163-189, main.cpp:645-675, 729-786)
+ * restated without assimp — one mesh per object / group / material run with faces, polygons as fans, one vertex per face
+ * corner.  apply_rule = 0 gives what main.cpp puts into its scenes (Triangle(a, b, c): the natural plane of the corners),
+ * 1 keeps mesh2triangles' normal rule (mesh.hpp:178-184).  Writes at most cap shapes to out and the first triangle of
+ * every mesh (+ the total as the last entry) to mesh_first; returns the number of triangles in the file (call again with a
+ * larger buffer if it exceeds cap), -2 if the file cannot be opened, -3 on a malformed `v` / `f` record.  Feed the result,
+ * together with spheres and walls, to rh_scene_from_shapes. */
+int rh_obj_triangles(const char* path, const float origin[3], const rt_flat_shape* material_from, int apply_rule,
+                     rt_flat_shape* out, int cap, int32_t* mesh_first, int mesh_cap, int* n_meshes);
+
 const rt_flat_light*  rh_light(const rh_scene* s);
 const rt_flat_camera* rh_camera(const rh_scene* s);
 const rt_flat_shape*  rh_shapes(const rh_scene* s, int* n);
