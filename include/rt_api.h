@@ -255,7 +255,7 @@ int rt_download_scene(rt_ctx* ctx, void* shapes_or_NULL, void* nodes_or_NULL);
  * IDENTICAL to the host builder's, so every traversal decision and tie-break stays what it was.  The tree
  * becomes the context's BVH as if it had been passed to rt_upload_scene (the threaded layout follows at the
  * next render; an unchanged topology keeps it and only refits).  maxDepth = buildBVH's argument (15 / 25 in
- * the reference scenes), at most 64 (the shader's stack).  By size the build runs in one thread block (<= 2048 shapes), in one
+ * the reference scenes), 0 ... 64 (the shader's stack; anything else is RT_ERR_ARG).  By size the build runs in one thread block (<= 2048 shapes), in one
  * thread-block cluster of up to 16 blocks (<= 28000), in one cooperative launch of a block per SM (<= 120000) or as one launch per
  * phase and level; the tree is the same on every path.
  * Shapes of unknown type and infinite planes get no

@@ -1326,7 +1326,7 @@ int rt_download_scene(rt_ctx* c, void* shapes, void* nodes) {
 // K8 (rt_build.cuh): buildBVH + serializeBVH of the reference on the device copy of the shapes.
 int rt_build_bvh(rt_ctx* c, int maxDepth, unsigned flags, int* nNodes_out, int* nIndices_out) {
     if (!c) return RT_ERR_ARG;
-    if (maxDepth > 64) return fail(c, RT_ERR_ARG, "rt_build_bvh: the shader's traversal stack holds 64 entries, maxDepth must be <= 64");
+    if (maxDepth < 0 || maxDepth > 64) return fail(c, RT_ERR_ARG, "rt_build_bvh: maxDepth must be 0 ... 64 (the shader's traversal stack holds 64 entries)");
     if (!c->haveScene || c->hShapes.p == nullptr) return fail(c, RT_ERR_STATE, "rt_build_bvh before the shapes were uploaded");
     if ((size_t)c->nShapes >= (1u << 29)) return fail(c, RT_ERR_ARG, "rt_build_bvh: more than 2^29 shapes");
     CU(c, cudaSetDevice(c->device));

@@ -241,3 +241,108 @@ def test_random_pipelined_sequences(rt, oracle, name, seed, shown):
     for i in (N - 2, N - 1):
         assert np.array_equal(bufs[i & 1], expected[i]), "%s seed %d: delivered frame %d" % (name, seed, i)
     tr.close()
+
+
+@pytest.mark.parametrize("Wx,Hx", [(1, 1), (1, 300), (4097, 1), (33, 9), (31, 7), (8, 4)])
+def test_extreme_frame_sizes(rt, oracle, Wx, Hx):
+    """Frames of one pixel, one column, one row (more than 128 tiles wide), a tile plus one pixel: every entry point against the
+    oracle, and as three compact shards untiled."""
+    sc = rt.Scene("toy", Wx, Hx)
+    p = rt.make_params(Wx, Hx, useFresnel=True)
+    tr = rt.RayTracer(Wx, Hx); tr.upload(sc)
+    rgba, ids = tr.render(p)
+    o_rgba, o_ids, _, _ = oracle.render(sc.light, sc.camera, sc.shapes, sc.nodes, sc.indices, p, Wx, Hx, want_counters=False)
+    assert_parity(compare(rgba, ids, o_rgba, o_ids), "%dx%d" % (Wx, Hx))
+    assert np.array_equal(tr.render_rgba8(p), oracle.present(rgba.reshape(-1, 4)).reshape(-1, 4))
+    shards = []
+    for r in range(3):
+        tr.set_shard(r, 3)
+        s, _ = tr.render(p)
+        shards.append(np.where(np.repeat(_valid(rt, Wx, Hx, (r, 3))[:, None], 4, 1), s.reshape(-1, 4), 0.0))
+    whole = rt.shard.untile_numpy(np.stack(shards), Wx, Hx, 3)
+    assert np.array_equal(whole.view(np.uint32), rgba.reshape(Hx, Wx, 4).view(np.uint32))
+    tr.close()
+
+
+def _valid(rt, Wx, Hx, shard):
+    rank, world = shard
+    m = np.zeros(rt.shard.shard_pixels(Wx, Hx, world), bool)
+    for j, tile in enumerate(rt.shard.shard_tiles(Wx, Hx, rank, world)):
+        ys, xs = rt.shard.tile_pixels(Wx, Hx, tile, world)
+        m[j * rt.shard.TILE_PX:(j + 1) * rt.shard.TILE_PX] = (ys < Hx) & (xs < Wx)
+    return m
+
+
+def test_two_contexts_on_two_host_threads(rt, oracle):
+    """A context is single-threaded like a GL context, but two contexts may be driven from two host threads at once (ctypes
+    drops the GIL during the calls): an animated car on one, an animated monkey with device animation on the other — every frame
+    equals the frame the same calls give when the threads run one after the other."""
+    import threading
+
+    def run(name, device_anim, out):
+        sc = rt.Scene(name, W, H)
+        p = rt.make_params(W, H, useFresnel=(name == "car"))
+        tr = rt.RayTracer(W, H); tr.upload(sc)
+        if device_anim:
+            tr.register_animations(sc)
+        an = sc.animated
+        lo, hi = int(an.min()), int(an.max()) + 1
+        for f in range(1, 25):
+            if device_anim:
+                tr.animate(f * 0.1, 0.1)
+            else:
+                sc.animate(f * 0.1, 0.1, mode=f % 2)
+                tr.update_shapes(lo, sc.shapes[lo:hi])
+                if f % 2:
+                    tr.upload_scene(nodes=sc.nodes, indices=sc.indices)
+                else:
+                    tr.update_nodes(sc.nodes)
+            rgba, ids = tr.render(p)
+            out.append((rgba.copy(), ids.copy()))
+        tr.close()
+
+    serial = ([], [])
+    run("car", False, serial[0]); run("monkey", True, serial[1])
+    both = ([], [])
+    errs = []
+
+    def guarded(*a):
+        try:
+            run(*a)
+        except Exception as e:                                  # surfaces in the main thread below
+            errs.append(e)
+    ths = [threading.Thread(target=guarded, args=("car", False, both[0])), threading.Thread(target=guarded, args=("monkey", True, both[1]))]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    assert not errs, errs
+    for k in range(2):
+        assert len(both[k]) == len(serial[k]) == 24
+        for f, ((ra, ia), (rb, ib)) in enumerate(zip(both[k], serial[k])):
+            assert np.array_equal(ia, ib) and np.array_equal(ra.view(np.uint32), rb.view(np.uint32)), "context %d frame %d" % (k, f)
+
+
+def test_argument_errors_leave_the_context_usable(rt):
+    """Bad arguments come back as negative codes with a message (never abort, never print: computeShader.hpp:48-79 prints and
+    carries on); the context renders the same frame afterwards."""
+    import ctypes as C
+    L = rt.lib()
+    h = C.c_void_p()
+    assert L.rt_create(C.byref(h), 0, 10, 0, 0) < 0 and L.rt_create(C.byref(h), 10, -1, 0, 0) < 0
+    assert L.rt_create(C.byref(h), 16, 16, 4096, 0) < 0                  # no such device
+    sc = rt.Scene("toy", 64, 48)
+    p = rt.make_params(64, 48)
+    tr = rt.RayTracer(64, 48); tr.upload(sc)
+    ref, ref_ids = tr.render(p)
+    n = len(sc.shapes)
+    for bad in (lambda: tr.update_shapes(n, sc.shapes[:1]), lambda: tr.update_shapes(-1, sc.shapes[:1]),
+                lambda: tr.update_shapes(n - 1, sc.shapes[:2]), lambda: tr.set_shard(2, 2), lambda: tr.set_shard(0, 0),
+                lambda: tr._chk(L.rt_render(tr._c, None, None, None)),
+                lambda: tr.build_bvh(65), lambda: tr.build_bvh(-1)):
+        with pytest.raises(rt.RtError) as e:
+            bad()
+        assert e.value.code < 0 and str(e.value)
+    again, again_ids = tr.render(p)
+    assert np.array_equal(again.view(np.uint32), ref.view(np.uint32)) and np.array_equal(again_ids, ref_ids)
+    tr.close()
