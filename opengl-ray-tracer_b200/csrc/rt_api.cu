@@ -90,6 +90,7 @@ struct rt_ctx {
     int64_t launches = 0;
     uint64_t lastTally[RT_NTALLY] = {};
     int smCount = 148;
+    int fewPerSm = RT_FEW_BLOCKS_PER_SM;   // resident render blocks per SM for launches with few items per warp (0: as many as fit)
 
     // raw scene, pinned shadow + device copy
     PinBuf<rt_flat_shape> hShapes; DevBuf<rt_flat_shape> dShapes; int nShapes = 0;
@@ -544,6 +545,7 @@ int rt_create(rt_ctx** out, int width, int height, int device, unsigned flags) {
     *c->hRfDegraded = 0;
     if (cudaHostGetDevicePointer(&c->dRfDegraded, c->hRfDegraded, 0) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
     cudaDeviceGetAttribute(&c->smCount, cudaDevAttrMultiProcessorCount, device);
+    if (const char* e = std::getenv("RT_B200_FEW_BLOCKS_PER_SM")) c->fewPerSm = std::atoi(e);     // kernel-variant experiments (tools/kbench.py)
     c->ownStream = c->stream;
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking) != cudaSuccess) { rt_destroy(c); return RT_ERR_CUDA; }
@@ -826,6 +828,14 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, RT_BLOCK_THREADS, 0));
         c->gridBlocks[variant] = c->smCount * (perSM > 0 ? perSM : 1);
     }
+    // Few items per warp (an eighth of a frame, 800x600): the launch is bound by its slowest block's chain of dependent walks,
+    // and an iteration of that chain waits for the issue slots of the other warps of its scheduler — fewer resident blocks per
+    // SM shorten the chain at the price of throughput the launch does not need (RT_FEW_BLOCKS_PER_SM, 0 = off).
+    int gridCap = c->gridBlocks[variant];
+    if (c->fewPerSm > 0 && nBands == 1 && !count && !big && tilesMine * RT_WARPS_PER_TILE < 8 * gridCap * (RT_BLOCK_THREADS / 32)) {
+        const int g = c->smCount * c->fewPerSm;
+        if (g < gridCap) gridCap = g;
+    }
     // heavy-first order (single-launch renders): the list is made from the previous frame's item costs
     F.itemCost = nullptr; F.heavyList = nullptr; F.heavyFlag = nullptr; F.lptCtl = nullptr; F.lptPar = 0;
     unsigned int* queue0 = c->queue.p;                         // claim counter of the plain queue (band 0)
@@ -839,7 +849,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
             CU(c, cudaMemsetAsync(c->lptCtl.p, 0, 8 * sizeof(unsigned), c->stream));
             c->lptItems = items; c->lptFrame = 0;
         } else {
-            const int gridWarps = c->gridBlocks[variant] * (RT_BLOCK_THREADS / 32);
+            const int gridWarps = gridCap * (RT_BLOCK_THREADS / 32);
             lpt_prepare_kernel<<<(items + 255) / 256, 256, 0, c->stream>>>(c->itemCost.p, items, c->lptCtl.p, c->heavyList.p, c->heavyFlag.p,
                 gridWarps, items < 5 * gridWarps ? RT_HEAVY_FACTOR_FEW : RT_HEAVY_FACTOR, (int)(c->lptFrame & 1u));
             c->launches += 1;
@@ -868,7 +878,7 @@ static int render_impl(rt_ctx* c, const rt_params* p, float* dev_rgba, int32_t* 
         cudaStream_t rs = (band & 1) ? c->stream2 : c->stream;
         const int items = F.nTilesMine * RT_WARPS_PER_TILE;
         const int needed = (items + RT_BLOCK_THREADS / 32 - 1) / (RT_BLOCK_THREADS / 32);
-        int grid = needed < c->gridBlocks[variant] ? needed : c->gridBlocks[variant];
+        int grid = needed < gridCap ? needed : gridCap;
         const dim3 blk(RT_BLOCK_THREADS);
         float4* o4 = reinterpret_cast<float4*>(dev_rgba);
         unsigned long long* tl = c->tally.p;

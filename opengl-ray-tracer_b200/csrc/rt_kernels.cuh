@@ -15,6 +15,13 @@
 #ifndef RT_MIN_BLOCKS_BIG
 #define RT_MIN_BLOCKS_BIG 10
 #endif
+#ifndef RT_FEW_BLOCKS_PER_SM
+#define RT_FEW_BLOCKS_PER_SM 6      // resident blocks per SM for launches with fewer than 8 items per warp (rt_api.cu: gridCap); 0 = as many as fit.
+                                    // Such a launch is bound by its slowest block's chain of dependent walks, and an iteration of that chain also waits
+                                    // for the issue slots of the other warps of its scheduler: 6 blocks instead of 8 give the eighth of the car's 4K frame
+                                    // 0.265 -> 0.260 ms, 800x600 0.272 -> 0.259 ms, monkey flat; 7: 0.255 / 0.268; 5 and 4 lose throughput
+                                    // (profiles/r2/few_blocks_sweep.txt; frames bit-identical)
+#endif
 #ifndef RT_BIG_SCENE_NODES
 #define RT_BIG_SCENE_NODES 100000
 #endif
