@@ -210,6 +210,16 @@ def hostlib():
     H.rh_anim_get.argtypes = [vp, ip, C.POINTER(ip), C.POINTER(ip), C.POINTER(C.c_float * 4)]; H.rh_anim_get.restype = vp
     H.rh_set_camera.argtypes = [vp, C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 3), C.c_float, C.c_float]
     H.rh_set_camera.restype = None
+    f3 = C.c_float * 3
+    H.rh_cam_create.argtypes = [f3, C.c_float]; H.rh_cam_create.restype = vp
+    H.rh_cam_destroy.argtypes = [vp]; H.rh_cam_destroy.restype = None
+    H.rh_cam_look_at.argtypes = [vp, f3]; H.rh_cam_look_at.restype = None
+    H.rh_cam_keyboard.argtypes = [vp, ip, C.c_float]; H.rh_cam_keyboard.restype = None
+    H.rh_cam_mouse.argtypes = [vp, C.c_float, C.c_float, ip]; H.rh_cam_mouse.restype = None
+    H.rh_cam_scroll.argtypes = [vp, C.c_float]; H.rh_cam_scroll.restype = None
+    H.rh_cam_shift.argtypes = [vp, ip]; H.rh_cam_shift.restype = None
+    H.rh_cam_state.argtypes = [vp, C.c_float * 4]; H.rh_cam_state.restype = None
+    H.rh_cam_serialize.argtypes = [vp, vp]; H.rh_cam_serialize.restype = None
     _hostlib = H
     return H
 
@@ -305,6 +315,55 @@ class Scene:
     def close(self):
         if self._h:
             self._H.rh_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Camera:
+    """The reference's interactive camera (camera.hpp:30-165) as its render loop drives it (processInput main.cpp:509-533,
+    mouse_callback :536-551); `flat` is serializeCamera's 80 bytes (:806-816), the argument of RayTracer.update_camera."""
+    FORWARD, BACKWARD, LEFT, RIGHT, UP, DOWN = range(6)
+
+    def __init__(self, position=(0.0, 0.0, 0.0), aspect=1.0):
+        self._H = hostlib()
+        self._h = self._H.rh_cam_create((C.c_float * 3)(*[float(v) for v in position]), float(aspect))
+
+    def look_at(self, target):
+        self._H.rh_cam_look_at(self._h, (C.c_float * 3)(*[float(v) for v in target]))
+
+    def keyboard(self, direction, dt):
+        self._H.rh_cam_keyboard(self._h, int(direction), float(dt))
+
+    def mouse(self, dx, dy, constrain_pitch=True):
+        self._H.rh_cam_mouse(self._h, float(dx), float(dy), int(bool(constrain_pitch)))
+
+    def scroll(self, dy):
+        self._H.rh_cam_scroll(self._h, float(dy))
+
+    def shift(self, pressed):
+        self._H.rh_cam_shift(self._h, int(bool(pressed)))
+
+    @property
+    def state(self):
+        out = (C.c_float * 4)()
+        self._H.rh_cam_state(self._h, out)
+        return dict(yaw=out[0], pitch=out[1], zoom=out[2], speed=out[3])
+
+    @property
+    def flat(self):
+        out = np.zeros(1, dtype=CAMERA_DTYPE)
+        assert out.nbytes == 80
+        self._H.rh_cam_serialize(self._h, _ptr(out))
+        return out
+
+    def close(self):
+        if self._h:
+            self._H.rh_cam_destroy(self._h)
             self._h = None
 
     def __del__(self):

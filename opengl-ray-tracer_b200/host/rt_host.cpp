@@ -601,3 +601,98 @@ void rh_set_camera(rh_scene* s, const float pos[3], const float target[3], float
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// The interactive camera: the reference's Camera class (camera.hpp:30-165) as its render loop drives it every frame
+// (processInput main.cpp:509-533, mouse_callback :536-551) and serializeCamera (:806-816), whose 80 bytes are the camera
+// sub-upload (:328-335) = rt_update_camera's argument.  Pinned bit for bit to the reference class compiled in place with
+// g++ (oracle/_ref/libref_camera.so, tests/test_camera.py).  One fact of that build decides the last bit: camera.hpp calls
+// cos / sin / asin / atan2 UNQUALIFIED on floats, which g++ resolves to the C library's double functions (only std:: has the
+// float overloads), so the products and glm::degrees of LookAt are evaluated in double and rounded once on assignment.
+// (look_at above, which places the synthetic scenes' cameras, keeps its float evaluation: the golden frames depend on it.)
+// ---------------------------------------------------------------------------
+struct rh_cam {
+    V3 Position, Front, Up, Right, WorldUp;
+    float Yaw, Pitch, MovementSpeed, MouseSensitivity, Zoom, fov, aspectRatio;
+};
+
+namespace {
+
+const float CAM_YAW = -90.0f, CAM_PITCH = 0.0f, CAM_SPEED = 15.f, CAM_SPEEDAMPLIFIER = 2.f, CAM_SENSITIVITY = 0.1f, CAM_ZOOM = 45.0f;   // camera.hpp:20-26
+inline float cam_radians(float deg) { return deg * 0.01745329251994329576923690768489f; }        // glm::radians<float>
+
+void update_camera_vectors(rh_cam& c) {                                                        // camera.hpp:152-163
+    V3 front;
+    front.x = (float)(std::cos((double)cam_radians(c.Yaw)) * std::cos((double)cam_radians(c.Pitch)));
+    front.y = (float)std::sin((double)cam_radians(c.Pitch));
+    front.z = (float)(std::sin((double)cam_radians(c.Yaw)) * std::cos((double)cam_radians(c.Pitch)));
+    c.Front = normalize(front);
+    c.Right = normalize(cross(c.Front, c.WorldUp));
+    c.Up = normalize(cross(c.Right, c.Front));
+}
+
+}  // namespace
+
+extern "C" {
+
+rh_cam* rh_cam_create(const float pos[3], float aspect) {
+    rh_cam* c = new rh_cam();
+    // Camera() (camera.hpp:49-56): position 0, up +y, yaw -90, pitch 0, fov 60, aspect 1; then Position / aspectRatio as
+    // generateScene1/2/3 set them (main.cpp:587-588, 721-722, 1198-1200)
+    c->Front = v3(0.0f, 0.0f, -1.0f); c->MovementSpeed = CAM_SPEED; c->MouseSensitivity = CAM_SENSITIVITY; c->Zoom = CAM_ZOOM;
+    c->fov = 60.0f; c->aspectRatio = 1.0f;
+    c->Position = v3(0.0f, 0.0f, 0.0f); c->WorldUp = v3(0.0f, 1.0f, 0.0f); c->Yaw = CAM_YAW; c->Pitch = CAM_PITCH;
+    update_camera_vectors(*c);
+    if (pos) c->Position = v3(pos);
+    c->aspectRatio = aspect;
+    return c;
+}
+void rh_cam_destroy(rh_cam* c) { delete c; }
+
+void rh_cam_look_at(rh_cam* c, const float target[3]) {                                     // camera.hpp:139-150
+    const V3 direction = normalize(v3(target) - c->Position);
+    c->Pitch = (float)(std::asin((double)direction.y) * 57.295779513082320876798154814105);       // glm::degrees<double>
+    c->Yaw = (float)(std::atan2((double)direction.z, (double)direction.x) * 57.295779513082320876798154814105);
+    update_camera_vectors(*c);
+}
+
+void rh_cam_keyboard(rh_cam* c, int direction, float deltaTime) {                           // camera.hpp:75-90
+    const float velocity = c->MovementSpeed * deltaTime;
+    if (direction == 0) c->Position = c->Position + c->Front * velocity;        // FORWARD
+    if (direction == 1) c->Position = c->Position - c->Front * velocity;        // BACKWARD
+    if (direction == 2) c->Position = c->Position - c->Right * velocity;        // LEFT
+    if (direction == 3) c->Position = c->Position + c->Right * velocity;        // RIGHT
+    if (direction == 4) c->Position = c->Position - c->Up * velocity;           // UP   (the reference's sign: its Up axis points down the screen)
+    if (direction == 5) c->Position = c->Position + c->Up * velocity;           // DOWN
+}
+
+void rh_cam_mouse(rh_cam* c, float xoffset, float yoffset, int constrainPitch) {            // camera.hpp:93-112
+    xoffset *= c->MouseSensitivity;
+    yoffset *= c->MouseSensitivity;
+    c->Yaw += xoffset;
+    c->Pitch += yoffset;
+    if (constrainPitch) {
+        if (c->Pitch > 89.0f) c->Pitch = 89.0f;
+        if (c->Pitch < -89.0f) c->Pitch = -89.0f;
+    }
+    update_camera_vectors(*c);
+}
+
+void rh_cam_scroll(rh_cam* c, float yoffset) {                                              // camera.hpp:115-122
+    c->Zoom -= yoffset;
+    if (c->Zoom < 1.0f) c->Zoom = 1.0f;
+    if (c->Zoom > 45.0f) c->Zoom = 45.0f;
+}
+
+void rh_cam_shift(rh_cam* c, int pressed) { c->MovementSpeed = pressed ? CAM_SPEED * CAM_SPEEDAMPLIFIER : CAM_SPEED; }   // main.cpp:528
+
+void rh_cam_state(const rh_cam* c, float out[4]) { out[0] = c->Yaw; out[1] = c->Pitch; out[2] = c->Zoom; out[3] = c->MovementSpeed; }
+
+void rh_cam_serialize(const rh_cam* c, rt_flat_camera* out) {                               // serializeCamera main.cpp:806-816
+    std::memset(out, 0, sizeof *out);
+    put(out->Position, c->Position); out->aspectRatio = c->aspectRatio;
+    put(out->Front, c->Front); put(out->Up, c->Up); put(out->Right, c->Right);
+    out->fov = c->fov;
+}
+
+}  // extern "C"

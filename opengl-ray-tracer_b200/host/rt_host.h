@@ -74,6 +74,21 @@ const int32_t* rh_anim_get(const rh_scene* s, int k, int* kind, int* count, floa
 /* Camera helper (camera.hpp:139-163): place + LookAt, fov in degrees. */
 void rh_set_camera(rh_scene* s, const float pos[3], const float target[3], float fov, float aspect);
 
+/* The interactive camera of the reference's render loop (camera.hpp:30-165; processInput main.cpp:509-533, mouse_callback
+ * :536-551): what the host does to the camera between two frames before serializeCamera (:806-816) and the camera
+ * sub-upload (:328-335) -> rt_update_camera.  direction: 0 FORWARD, 1 BACKWARD, 2 LEFT, 3 RIGHT, 4 UP, 5 DOWN
+ * (camera.hpp:11-18).  Bit-identical to the reference class compiled in place (tests/test_camera.py). */
+typedef struct rh_cam rh_cam;
+rh_cam* rh_cam_create(const float pos[3], float aspect);          /* Camera(), then Position / aspectRatio */
+void rh_cam_destroy(rh_cam* c);
+void rh_cam_look_at(rh_cam* c, const float target[3]);            /* Camera::LookAt            :139-150 */
+void rh_cam_keyboard(rh_cam* c, int direction, float deltaTime);  /* Camera::ProcessKeyboard   :75-90   */
+void rh_cam_mouse(rh_cam* c, float xoffset, float yoffset, int constrainPitch);   /* ProcessMouseMovement :93-112 */
+void rh_cam_scroll(rh_cam* c, float yoffset);                     /* Camera::ProcessMouseScroll :115-122 */
+void rh_cam_shift(rh_cam* c, int pressed);                        /* MovementSpeed, main.cpp:528 */
+void rh_cam_state(const rh_cam* c, float out[4]);                 /* Yaw, Pitch, Zoom, MovementSpeed */
+void rh_cam_serialize(const rh_cam* c, rt_flat_camera* out);      /* serializeCamera main.cpp:806-816 */
+
 #ifdef __cplusplus
 }
 #endif

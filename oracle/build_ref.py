@@ -132,6 +132,15 @@ def main() -> int:
     rc = subprocess.call(cmd)
     if rc != 0:
         return rc
+    # the reference's own Camera class + serializeCamera's field copies (pins the headless host's rh_camera_*); the one OpenGL
+    # type camera.hpp names (GLboolean) comes from oracle/stubs/glad/glad.h
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared",
+           "-I", os.path.join(ref, "src"), "-I", glm, "-I", os.path.join(HERE, "stubs"),
+           os.path.join(HERE, "ref_camera_glue.cpp"), "-o", os.path.join(outdir, "libref_camera.so")]
+    print(" ".join(cmd))
+    rc = subprocess.call(cmd)
+    if rc != 0:
+        return rc
     # the reference's own builder / serialiser / animation step cut out of main.cpp (pins host builder, K6, K7, K8)
     extract_main(ref, outdir)
     cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-w", "-fPIC", "-shared",
