@@ -5,10 +5,12 @@
  * own FlatCamera (src/flatStructures.hpp) behind a C interface — the per-frame camera step of the render loop
  * (processInput main.cpp:509-533, mouse_callback :536-551, the camera sub-upload :328-335) that feeds
  * rt_update_camera.  Pins the headless host's rh_cam_* (opengl-ray-tracer_b200/host/rt_host.cpp).
+ * Also the reference's Light (light.hpp) + serializeLight (main.cpp:818-823): the light SSBO's 32 bytes.
  * Built by oracle/build_ref.py into oracle/_ref/libref_camera.so; oracle/stubs/glad/glad.h supplies GLboolean.
  */
 #include <cstring>
 #include "camera.hpp"
+#include "light.hpp"
 #include "flatStructures.hpp"
 
 extern "C" {
@@ -42,6 +44,17 @@ void refcam_serialize(void* h, void* out80) {
     f.fov = cam.fov;
     static_assert(sizeof(FlatCamera) == 80, "FlatCamera is 80 bytes (SURVEY 8b)");
     std::memcpy(out80, &f, sizeof f);
+}
+
+/* Light (light.hpp:6-35) + serializeLight (main.cpp:818-823): the 32 bytes of the light SSBO / rt_update_light */
+void reflight_serialize(const float pos[3], const float base[3], float intensity, void* out32) {
+    Light light(glm::vec3(pos[0], pos[1], pos[2]), glm::vec3(base[0], base[1], base[2]), intensity);
+    FlatLight f;
+    std::memset(&f, 0, sizeof f);
+    f.position = light.position;
+    f.color = light.color;
+    static_assert(sizeof(FlatLight) == 32, "FlatLight is 32 bytes (SURVEY 8b)");
+    std::memcpy(out32, &f, sizeof f);
 }
 
 }  // extern "C"

@@ -135,3 +135,18 @@ def test_traces_equal_the_reference_class_live(rt, host_camera, seed):
         a, b = np.asarray(ref.flat).view(np.uint8).ravel(), np.asarray(mine.flat).view(np.uint8).ravel()
         assert np.array_equal(a, b), "seed %d: camera bytes after event %d %r: %s vs %s" % (seed, i, e, a.view(np.float32), b.view(np.float32))
         assert ref.state == mine.state
+
+
+@pytest.mark.parametrize("scene,pos,intensity", [("monkey", (0.0, -14.0, 0.0), 50.0), ("car", (14.8, -17.0, 17.0), 26.0), ("triangle", (14.8, -17.0, 17.0), 26.0)])
+def test_scene_lights_equal_the_reference_light_class(rt, scene, pos, intensity):
+    """Light(position, vec3(1), intensity) (light.hpp:22-35; main.cpp:591, :725, :1203) through serializeLight (:818-823):
+    the 32 bytes of the headless scenes' lights equal those of the reference class compiled in place."""
+    if not os.path.exists(REF_SO):
+        pytest.skip("oracle/_ref/libref_camera.so not built (no reference tree here)")
+    L = C.CDLL(REF_SO)
+    f3 = C.c_float * 3
+    L.reflight_serialize.argtypes = [f3, f3, C.c_float, C.c_void_p]
+    out = np.zeros(32, np.uint8)
+    L.reflight_serialize(f3(*pos), f3(1.0, 1.0, 1.0), intensity, out.ctypes.data)
+    sc = rt.Scene(scene, 800, 600)
+    assert np.array_equal(np.asarray(sc.light).view(np.uint8).ravel(), out), (out.view(np.float32), sc.light)
