@@ -216,8 +216,6 @@ struct SubBuilder {
     }
     static double centroid(const Box& b, int a) { return 0.5 * ((double)b.mn[a] + b.mx[a]); }
 
-    struct Task { int node, first, count; };          // a node whose subtree another thread builds
-
     // One node over recs[first, first + count): bounds, binned-SAH split, stable partition.  Returns the split
     // position, or -1 for a leaf.  `out` receives the node's fields.
     int split_node(Rec* recs, Rec* scratch, int first, int count, SubNode& out) const {
@@ -280,62 +278,109 @@ struct SubBuilder {
         return mid;
     }
 
-    // Subtree over recs[first, first + count) into `out` (ids local to `out`); ranges of more than `defer` items below
-    // the root of this call are not descended into but listed in `tasks` (defer <= 0: never).
-    int build_rec(Rec* recs, Rec* scratch, int first, int count, std::vector<SubNode>& out, int defer, std::vector<Task>* tasks, bool root) const {
+    // Subtree over recs[first, first + count) into `out` (ids local to `out`), sequentially.
+    int build_rec(Rec* recs, Rec* scratch, int first, int count, std::vector<SubNode>& out) const {
         const int id = (int)out.size();
         out.emplace_back();
-        if (!root && tasks && count > maxLeaf && count <= defer) { tasks->push_back({id, first, count}); return id; }
         SubNode nd;
         const int mid = split_node(recs, scratch, first, count, nd);
         out[(size_t)id] = nd;
         if (mid < 0) return id;
-        const int l = build_rec(recs, scratch, first, mid - first, out, defer, tasks, false);
-        const int r = build_rec(recs, scratch, mid, first + count - mid, out, defer, tasks, false);
+        const int l = build_rec(recs, scratch, first, mid - first, out);
+        const int r = build_rec(recs, scratch, mid, first + count - mid, out);
         out[(size_t)id].left = l; out[(size_t)id].right = r;
         return id;
+    }
+
+    // The same subtree with its two halves built side by side while `forks` levels of forking are left: the right half goes
+    // to a new thread and into a node list of its own (disjoint record ranges, nothing shared but the read-only bounds),
+    // which is appended when both are done.  The sweep over a node's items stays sequential, so the critical path is the
+    // root's sweep plus half of it, a quarter ... (two sweeps of the whole range) instead of one sweep per level until the
+    // ranges were small enough to hand out (round 2's first form: five levels for a million leaves).
+    static constexpr int PAR_MIN = 8192;             // halves smaller than this are not worth a thread
+    int build_par(Rec* recs, Rec* scratch, int first, int count, std::vector<SubNode>& out, int forks) const {
+        if (forks <= 0 || count < 2 * PAR_MIN) return build_rec(recs, scratch, first, count, out);
+        const int id = (int)out.size();
+        out.emplace_back();
+        SubNode nd;
+        const int mid = split_node(recs, scratch, first, count, nd);
+        out[(size_t)id] = nd;
+        if (mid < 0) return id;
+        const int nl = mid - first, nr = first + count - mid;
+        int l, r;
+        std::vector<SubNode> other;
+        std::thread th;
+        bool forked = false;
+        if (nl >= PAR_MIN && nr >= PAR_MIN) {
+            try { th = std::thread([&, this] { build_par(recs, scratch, mid, nr, other, forks - 1); }); forked = true; }
+            catch (...) {}                               // no more threads to be had: this one does both halves
+        }
+        l = build_par(recs, scratch, first, nl, out, forked ? forks - 1 : forks);
+        if (forked) {
+            th.join();
+            const int off = (int)out.size();             // local id j of `other`  ->  off + j; its root is its element 0
+            out.reserve(out.size() + other.size());
+            for (SubNode x : other) {
+                if (x.left >= 0) { x.left += off; x.right += off; }
+                out.push_back(x);
+            }
+            r = off;
+        } else {
+            r = build_par(recs, scratch, mid, nr, out, forks);
+        }
+        out[(size_t)id].left = l; out[(size_t)id].right = r;
+        return id;
+    }
+
+    // maxLeaf == 1: every leaf holds exactly one item and every inner node has two non-empty children, so the subtree over
+    // `count` items has exactly 2 * count - 1 nodes: ids are handed out in advance (the node itself, then the left subtree's
+    // 2 * nl - 1 ids, then the right subtree's) and the halves write into the one pre-sized list without ever moving a node.
+    void build_fixed(Rec* recs, Rec* scratch, int first, int count, SubNode* out, int id, int forks) const {
+        SubNode nd;
+        const int mid = split_node(recs, scratch, first, count, nd);
+        if (mid < 0) { out[id] = nd; return; }
+        const int nl = mid - first, nr = first + count - mid;
+        nd.left = id + 1; nd.right = id + 2 * nl;
+        out[id] = nd;
+        std::thread th;
+        bool forked = false;
+        if (forks > 0 && nl >= PAR_MIN && nr >= PAR_MIN) {
+            try { th = std::thread([=] { build_fixed(recs, scratch, mid, nr, out, nd.right, forks - 1); }); forked = true; }
+            catch (...) {}
+        }
+        build_fixed(recs, scratch, first, nl, out, nd.left, forked ? forks - 1 : forks);
+        if (forked) th.join();
+        else build_fixed(recs, scratch, mid, nr, out, nd.right, forks);
     }
 
     int build(int first, int count);
 };
 
-// Large ranges (the tree over a million reference leaves) are split among the host's cores: the top of the tree is
-// built here until the ranges are small, the subtrees below are independent (disjoint record ranges) and are built by
-// worker threads into their own node lists, which are appended afterwards.  Node ids differ from a sequential build,
-// the TREE (boxes, children, item order) is the same, and only that reaches the layout.
+// Large ranges (the tree over a million reference leaves) are split among the host's cores (build_par).  Node ids differ
+// from a sequential build, the TREE (boxes, children, item order) is the same, and only that reaches the layout.
 inline int SubBuilder::build(int first, int count) {
     if (count <= 0) return -1;
     std::vector<Rec> recs((size_t)count), scratch((size_t)count);
     for (int i = 0; i < count; ++i) { recs[(size_t)i].item = items[(size_t)(first + i)]; recs[(size_t)i].b = pb[(size_t)recs[(size_t)i].item]; }
     const int base = (int)nodes.size();
-    std::vector<Task> tasks;
-    unsigned hw = std::thread::hardware_concurrency();
-    const int nThreads = count >= (1 << 16) ? (int)(hw == 0 ? 1 : hw > 16 ? 16 : hw) : 1;
-    const int root = build_rec(recs.data(), scratch.data(), 0, count, nodes, nThreads > 1 ? count / (4 * nThreads) : 0, nThreads > 1 ? &tasks : nullptr, true);
-    if (!tasks.empty()) {
-        std::vector<std::vector<SubNode>> local(tasks.size());
-        std::atomic<size_t> next{0};
-        auto work = [&]() {
-            for (size_t t = next.fetch_add(1); t < tasks.size(); t = next.fetch_add(1))
-                build_rec(recs.data(), scratch.data(), tasks[t].first, tasks[t].count, local[t], 0, nullptr, true);
-        };
-        std::vector<std::thread> pool;
-        try { for (int t = 1; t < nThreads; ++t) pool.emplace_back(work); }
-        catch (...) {}                                       // no more threads to be had: the ones we got (and this one) do it
-        work();
-        for (auto& th : pool) th.join();
-        for (size_t t = 0; t < tasks.size(); ++t) {
-            // local[t][0] is the subtree's root: it takes the place of the placeholder node, the rest is appended
-            const int off = (int)nodes.size() - 1;               // local id j >= 1  ->  off + j
-            SubNode r = local[t][0];
-            if (r.left >= 0) { r.left += off; r.right += off; }
-            nodes[(size_t)tasks[t].node] = r;
-            for (size_t j = 1; j < local[t].size(); ++j) {
-                SubNode x = local[t][j];
-                if (x.left >= 0) { x.left += off; x.right += off; }
-                nodes.push_back(x);
-            }
-        }
+    int forks = 0;
+    if (count >= (1 << 16)) {
+        unsigned hw = std::thread::hardware_concurrency();
+        const unsigned nThreads = hw == 0 ? 1 : hw > 16 ? 16 : hw;
+        while ((1u << forks) < nThreads) ++forks;
+        if (nThreads > 1) forks += 2;                    // four times as many halves as cores: the halves are not equally deep
+    }
+    int root;
+    if (forks > 0 && maxLeaf == 1) {
+        nodes.resize((size_t)base + 2 * (size_t)count - 1);
+        build_fixed(recs.data(), scratch.data(), 0, count, nodes.data(), base, forks);
+        root = base;
+    } else if (base == 0) root = build_par(recs.data(), scratch.data(), 0, count, nodes, forks);
+    else {                                               // ids local to a list of their own, then appended (as a forked half is)
+        std::vector<SubNode> mine;
+        build_par(recs.data(), scratch.data(), 0, count, mine, forks);
+        root = base;
+        for (SubNode x : mine) { if (x.left >= 0) { x.left += base; x.right += base; } nodes.push_back(x); }
     }
     // node ranges are relative to `first`; the permutation goes back into items
     if (first != 0) for (size_t j = (size_t)base; j < nodes.size(); ++j) nodes[j].first += first;
@@ -659,6 +704,11 @@ inline void build_top(Layout& L, const rt_flat_node* nd, int nNodes) {
     sb.build(0, (int)items.size());
     // emit B in pre-order with an explicit stack; a top inner node's link is patched when its subtree is complete
     struct Item { int node; int patch; };      // node >= 0: visit; node < 0: patch link of B position `patch`
+    {   // B holds A's entries (every node of A that is not a reference inner node, at most all of A) plus one top node per inner node of the tree
+        const size_t cap = L.src.size() + sb.nodes.size() / 2 + 1;
+        L.srcB.reserve(cap); L.linkB.reserve(cap); L.cwB.reserve(cap);
+        L.topPos.reserve(sb.nodes.size() / 2 + 1); L.subBox.reserve(L.subBox.size() + sb.nodes.size() / 2 + 1);
+    }
     std::vector<Item> st; st.push_back({0, -1});
     while (!st.empty()) {
         const Item it = st.back(); st.pop_back();

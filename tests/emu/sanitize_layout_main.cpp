@@ -7,7 +7,8 @@
 #include "../../opengl-ray-tracer_b200/host/rt_host.h"
 int main(int argc, char** argv) {
     const char* name = argc > 1 ? argv[1] : "car"; const int n = argc > 2 ? atoi(argv[2]) : 0;
-    rh_scene* sc = rh_scene_create(name, 800, 600, n, 0);
+    const int depth = argc > 3 ? atoi(argv[3]) : 0;            // 0: the scene's own BVH depth
+    rh_scene* sc = rh_scene_create(name, 800, 600, n, depth);
     if (!sc) return 2;
     int ns, nn, ni; const rt_flat_shape* sh = rh_shapes(sc, &ns); const rt_flat_node* nd = rh_nodes(sc, &nn); const int32_t* ix = rh_indices(sc, &ni);
     rtl::Layout L;

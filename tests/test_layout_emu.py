@@ -371,6 +371,17 @@ def test_layout_is_the_validated_one(rt, emu, name, n, want):
     assert emu.emu_layout_hash(e.h) == want, "%s: layout hash %016x" % (name, emu.emu_layout_hash(e.h))
 
 
+@pytest.mark.parametrize("name,n,depth,want", [("soup", 140000, 1, 0x11f969cb14bdb73c), ("soup", 300000, 2, 0x5fafe17f02e94c90)])
+def test_threaded_fat_leaf_subtrees_are_the_validated_ones(rt, emu, name, n, depth, want):
+    """Fat leaves of 65 536 shapes and more (a soup under a tree of depth 1 / 2: leaves of 70 k - 100 k shapes) take
+    SubBuilder::build_par, the forked build with leaves of several shapes; the soup of 80 000 above takes build_fixed (list B's
+    tree, one item per leaf).  Both give the layout the sequential builder gave (hashes recorded before the builders were
+    threaded this way; node ids may differ, the tree may not)."""
+    sc = rt.Scene(name, 800, 600, n_override=n, bvh_depth=depth)
+    e = Emu(emu, sc.shapes, sc.nodes, sc.indices, omax=200.0)
+    assert emu.emu_layout_hash(e.h) == want, "%s %d depth %d: layout hash %016x" % (name, n, depth, emu.emu_layout_hash(e.h))
+
+
 def test_scan_nodes_equals_the_three_passes(emu, rt):
     """rtl::scan_nodes (one pass over an uploaded node array: topology compare with the shadow, copy, safe coordinates,
     nestedness) against the three separate passes it replaced, on real trees and on every kind of damage."""

@@ -49,6 +49,11 @@ def test_layout_builder_under_sanitizers(rt, flags, tag):
         r = _run([exe, name, str(n)])
         assert r.returncode == 0, r.stderr[-3000:]
         assert "layout hash %016x" % want[(name, n)] in r.stdout, r.stdout
+    # fat leaves of 70 000 shapes (a soup under a tree of depth 1): SubBuilder::build_par, the forked build with leaves of
+    # several shapes (hash: tests/test_layout_emu.py::test_threaded_fat_leaf_subtrees_are_the_validated_ones)
+    r = _run([exe, "soup", "140000", "1"])
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert "layout hash 11f969cb14bdb73c" in r.stdout, r.stdout
 
 
 def test_walk_emulation_under_asan_ubsan(rt):
